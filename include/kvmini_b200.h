@@ -1,0 +1,247 @@
+/* kvmini_b200.h - C ABI of libkvmini_b200.so (sm_100a).
+ *
+ * Drop-in boundary for the run-analysis hot path of Siryoos/kserve-vllm-mini.  The
+ * reference has no FFI of its own: its boundary is the
+ * CLI + three importable function sets, all Python.  The Python host in
+ * kserve-vllm-mini_b200/ keeps those names and calls the entry points below through
+ * ctypes; each entry point cites the reference code whose arithmetic it replaces.
+ *
+ * Conventions
+ *  - every pointer is a DEVICE pointer owned by the caller (torch tensors are only
+ *    buffers) unless the parameter name ends in _host;
+ *  - `stream` is a cudaStream_t passed as void*; calls are stream-ordered and do not
+ *    synchronise unless stated;
+ *  - no entry point allocates: scratch comes from the caller (`workspace`, sized by
+ *    the matching *_workspace_bytes) - workspaces need 256-byte alignment;
+ *  - return value: KVM_OK or a negative KVM_ERR_*; kvm_last_error() gives the text
+ *    (thread-local);
+ *  - fp64 columns use NaN for "missing"; int64 columns are plain counts / codes.
+ */
+#ifndef KVMINI_B200_H
+#define KVMINI_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define KVM_ABI_VERSION 1
+
+#define KVM_OK 0
+#define KVM_ERR_INVALID (-1)   /* bad argument */
+#define KVM_ERR_CUDA (-2)      /* CUDA runtime error; text in kvm_last_error() */
+#define KVM_ERR_WORKSPACE (-3) /* workspace_bytes too small */
+
+const char* kvm_last_error(void);
+int kvm_abi_version(void);
+/* Number of SMs of the current device (grids are sized as multiples of it). */
+int kvm_sm_count(void);
+
+/* ------------------------------------------------------------------ request log */
+
+/* Columnar request log.  Replaces the list-of-dicts of analyze.py:34-56. */
+typedef struct kvm_request_log {
+  const double* start_ms;
+  const double* latency_ms;
+  const double* ttfb_ms;            /* NaN = missing */
+  const double* tllt_ms;            /* NaN = missing */
+  const int64_t* status;            /* success == 200 (analyze.py:127 `str(int(status))=="200"`) */
+  const int64_t* completion_tokens; /* 0 where the reference's `or 0` applies */
+  const int64_t* total_tokens;
+  int64_t n;
+} kvm_request_log;
+
+/* Row flags written by kvm_log_scan (one byte per row). */
+#define KVM_F_SUCCESS 0x01 /* status == 200 */
+#define KVM_F_COLD 0x02    /* analyze.py:402-419 */
+#define KVM_F_TOKENS 0x04  /* completion_tokens > 0 */
+#define KVM_F_GEN 0x08     /* row contributes to generation / per-token sets (analyze.py:143) */
+
+/* The seven disjoint "base sets" of (value, row-predicate) the analysis ranks.
+ * Every percentile multiset of analyze.py is a union of these:
+ *   latency all = LAT_COLD|LAT_WARM, ttfb all = TTFB_COLD|TTFB_WARM, ... */
+enum {
+  KVM_SET_LAT_COLD = 0, /* latency_ms | success & cold & !nan   (analyze.py:437) */
+  KVM_SET_LAT_WARM = 1,
+  KVM_SET_TTFB_COLD = 2, /* ttfb_ms | success & cold & !nan     (analyze.py:438-442) */
+  KVM_SET_TTFB_WARM = 3,
+  KVM_SET_TLLT = 4,   /* tllt_ms | success & !nan               (analyze.py:131,150) */
+  KVM_SET_GEN = 5,    /* tllt-ttfb | success & both !nan & tokens>0 (analyze.py:143-145) */
+  KVM_SET_PERTOK = 6, /* (tllt-ttfb)/tokens, same rows            (analyze.py:146) */
+  KVM_LOG_NSETS = 7
+};
+/* value columns of the request log (digit parameters are per column) */
+enum { KVM_COL_LAT = 0, KVM_COL_TTFB = 1, KVM_COL_TLLT = 2, KVM_COL_GEN = 3, KVM_COL_PERTOK = 4,
+       KVM_LOG_NCOLS = 5 };
+
+#define KVM_MAX_SETS 8
+#define KVM_MAX_COLS 8
+
+/* Counts / ranges of the base sets of one select problem. Keys are the order-preserving
+ * uint64 image of the fp64 value (sign-flip encoding). */
+typedef struct kvm_set_info {
+  int64_t count[KVM_MAX_SETS];
+  uint64_t kmin[KVM_MAX_COLS]; /* per value column, over all of its sets */
+  uint64_t kmax[KVM_MAX_COLS];
+  int32_t set_col[KVM_MAX_SETS]; /* column of each base set */
+  int32_t nsets;
+  int32_t ncols;
+} kvm_set_info;
+
+/* Result of the fused first pass over the log.
+ * Replaces analyze.py:183-189 (window), :402-419 (cold/warm), :496-514 (counts, token
+ * sums), cost_estimator.py:117-124,293-308 and the NaN filters of :68,:89. */
+typedef struct kvm_log_stats {
+  int64_t n_total;
+  int64_t n_success;
+  int64_t n_cold;         /* rows classified cold (any status) */
+  int64_t n_cold_success; /* cold & success */
+  int64_t sum_completion_tokens; /* over success rows */
+  int64_t sum_total_tokens;      /* over success rows */
+  int64_t sum_total_tokens_cold; /* over success & cold rows (warm = total - cold) */
+  int64_t n_gen_rows;            /* rows passing analyze.py:143 (incl. NaN differences) */
+  double min_start_ms;           /* over ALL rows (analyze.py:185) */
+  double max_end_ms;             /* max(start_ms+latency_ms) over ALL rows (analyze.py:187) */
+  double ttfb_sum_hi;            /* double-double sum of ttfb over success & !nan (analyze.py:581) */
+  double ttfb_sum_lo;
+  double lat_sum_hi; /* double-double sum of latency over success rows (cost_calculator.py:48) */
+  double lat_sum_lo;
+  kvm_set_info sets; /* the seven base sets / five columns above */
+} kvm_log_stats;
+
+size_t kvm_log_scan_workspace_bytes(void);
+
+/* K1+K7.  One pass over all seven columns.  `cold_times` = sorted cold-start times in
+ * seconds (may be NULL when n_cold_times == 0); a row is cold iff some c has
+ * c <= start_ms/1000 <= c + cold_window_s.  Writes flags[n] (may be NULL) and *stats. */
+int kvm_log_scan(const kvm_request_log* log_host, const double* cold_times, int32_t n_cold_times,
+                 double cold_window_s, uint8_t* flags, kvm_log_stats* stats, void* workspace,
+                 size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------ exact selection */
+
+/* How a query turns (n, p) into a 0-based rank. */
+enum {
+  KVM_RANK_LERP_LO = 0,     /* floor(clamp(p,0,1)*(n-1))   analyze.py:75-76 */
+  KVM_RANK_LERP_HI = 1,     /* ceil (clamp(p,0,1)*(n-1))   analyze.py:77   */
+  KVM_RANK_ABSOLUTE = 2,    /* rank given                                   */
+  KVM_RANK_UPPER_MEDIAN = 3,/* n/2  `sorted(v)[len(v)//2]`  collector.py:333 */
+  KVM_RANK_FLOOR_PN = 4,    /* int(p*n)      runners/backends/tgi/invoke.sh:208-210 */
+  KVM_RANK_FLOOR_PNM1 = 5   /* int(p*(n-1))  scripts/fairness_dual_tenant.py:59-65 */
+};
+
+#define KVM_MAX_QUERIES 48
+
+typedef struct kvm_query {
+  uint32_t set_mask; /* union of base sets (bit b = set b); all of one column */
+  int32_t rank_kind;
+  double p;
+  int64_t rank; /* KVM_RANK_ABSOLUTE only */
+} kvm_query;
+
+#define KVM_Q_OK 0
+#define KVM_Q_EMPTY 1        /* multiset empty: value = NaN */
+#define KVM_Q_OUT_OF_RANGE 2 /* rank >= n (reference would raise IndexError) */
+
+typedef struct kvm_query_result {
+  double value; /* the order statistic */
+  int64_t n;    /* size of the multiset (NaNs excluded) */
+  int64_t rank; /* resolved 0-based rank */
+  int32_t status;
+  int32_t pad;
+} kvm_query_result;
+
+/* Workspace for a select problem whose candidate arena holds `arena_capacity` keys.
+ * kvm_select_default_arena(n) is a size that fits unless the data is pathologically
+ * concentrated; on overflow the select returns KVM_ERR_ARENA in the status word and
+ * the caller retries with capacity = total number of elements. */
+size_t kvm_select_workspace_bytes(int64_t arena_capacity);
+int64_t kvm_select_default_arena(int64_t n);
+#define KVM_ERR_ARENA (-4) /* candidate arena too small: retry with a larger one */
+
+/* Fused multi-rank exact select over the request log (K2+K6).  Replaces the 25
+ * `percentile()` calls of one analyze.py run (analyze.py:59-81, call sites :159-176,
+ * :447-451, :574-583).  `stats` is the device struct kvm_log_scan wrote, `flags` its
+ * flag bytes.  Stream-ordered; results[nq] land in device memory.  After the stream
+ * is synchronised, kvm_select_status(workspace) tells whether the arena overflowed. */
+int kvm_log_select(const kvm_request_log* log_host, const uint8_t* flags,
+                   const kvm_log_stats* stats, const kvm_query* queries_host, int32_t nq,
+                   kvm_query_result* results, void* workspace, size_t workspace_bytes,
+                   int64_t arena_capacity, void* stream);
+
+/* Generic single-column variant.  Set membership of element i:
+ *   mode 0: every element is in set 0
+ *   mode 1: set_ids[i] (uint8; 255 = excluded)
+ *   mode 2: status[i] == 200 -> set 0, else excluded   (the 16 B/record percentile path)
+ * NaN values are always excluded.  Replaces analyze.py:59-81 for one list. */
+enum { KVM_MEMBER_ALL = 0, KVM_MEMBER_SET_IDS = 1, KVM_MEMBER_STATUS = 2 };
+
+int kvm_column_select(const double* values, int64_t n, int32_t member_mode, const void* member,
+                      int32_t nsets, const kvm_query* queries_host, int32_t nq,
+                      kvm_query_result* results, void* workspace, size_t workspace_bytes,
+                      int64_t arena_capacity, void* stream);
+
+/* Reads back the status word of the last select run in `workspace` (synchronises the
+ * stream): KVM_OK or KVM_ERR_ARENA. */
+int kvm_select_status(const void* workspace, void* stream);
+
+/* ---- staged form of the same select, for multi-GPU runs where the host all-reduces
+ * between the stages.  Stage order:
+ *   column_stats -> [allreduce set_info: counts sum, kmin min, kmax max] -> plan ->
+ *   hist -> [allreduce hist: sum] -> resolve -> compact -> [allgather arena+counts] -> finish
+ */
+int kvm_column_stats(const double* values, int64_t n, int32_t member_mode, const void* member,
+                     int32_t nsets, kvm_set_info* info, void* workspace, size_t workspace_bytes,
+                     void* stream);
+/* device addresses inside a select workspace, so the host can hand them to NCCL */
+uint64_t* kvm_select_hist_ptr(void* workspace);   /* [KVM_MAX_SETS][kvm_select_bins()] u64 */
+int32_t kvm_select_bins(void);
+uint64_t* kvm_select_arena_ptr(void* workspace);  /* candidate keys */
+int64_t* kvm_select_bucket_counts_ptr(void* workspace); /* [KVM_MAX_QUERIES] local counts */
+int64_t* kvm_select_bucket_offsets_ptr(void* workspace); /* [KVM_MAX_QUERIES+1] arena offsets */
+
+int kvm_select_plan(const kvm_set_info* info, const kvm_query* queries_host, int32_t nq,
+                    void* workspace, size_t workspace_bytes, int64_t arena_capacity, void* stream);
+int kvm_column_select_hist(const double* values, int64_t n, int32_t member_mode, const void* member,
+                           void* workspace, void* stream);
+int kvm_log_select_hist(const kvm_request_log* log_host, const uint8_t* flags, void* workspace,
+                        void* stream);
+int kvm_select_resolve(void* workspace, void* stream);
+int kvm_column_select_compact(const double* values, int64_t n, int32_t member_mode,
+                              const void* member, void* workspace, void* stream);
+int kvm_log_select_compact(const kvm_request_log* log_host, const uint8_t* flags, void* workspace,
+                           void* stream);
+/* Finish from `nsrc` arenas (own + gathered peers), each laid out with the same bucket
+ * offsets; src_counts[s*KVM_MAX_QUERIES + b] = keys source s holds for bucket b. */
+int kvm_select_finish(void* workspace, const uint64_t* const* arenas_host, int32_t nsrc,
+                      const int64_t* src_counts, kvm_query_result* results, void* stream);
+
+/* ------------------------------------------------------------------ histograms / series */
+
+/* K5: the four 20-bin value histograms of analyze.py:84-122,149-152 in one pass.
+ * counts[4][num_bins] int64 in the order ttfb, tllt, generation, per-token; bin index is
+ * min(num_bins-1, int((v-min)/w)) with w=(max-min)/num_bins, bit-exact.  min/max come
+ * from `stats`.  Degenerate cases (empty, min==max) are resolved by the host from stats. */
+int kvm_log_histograms(const kvm_request_log* log_host, const uint8_t* flags,
+                       const kvm_log_stats* stats, int32_t num_bins, int64_t* counts,
+                       void* workspace, size_t workspace_bytes, void* stream);
+size_t kvm_log_histograms_workspace_bytes(int32_t num_bins);
+
+/* Generic K5 for one column (used by `compute_histograms`, analyze.py:84-122):
+ * NaNs skipped; lo/hi given by the caller. */
+int kvm_column_histogram(const double* values, int64_t n, double lo, double hi, int32_t num_bins,
+                         int64_t* counts, void* workspace, size_t workspace_bytes, void* stream);
+
+/* K8 (extension A12; no reference function): per window of `window_ms` starting at
+ * stats->min_start_ms: requests, successes, completion tokens of successes.
+ * series[3][max_bins] int64; rows whose bin >= max_bins are counted in *dropped. */
+int kvm_log_series(const kvm_request_log* log_host, const uint8_t* flags,
+                   const kvm_log_stats* stats, double window_ms, int64_t max_bins, int64_t* series,
+                   int64_t* dropped, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KVMINI_B200_H */

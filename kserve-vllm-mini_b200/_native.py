@@ -1,0 +1,131 @@
+"""ctypes binding of libkvmini_b200.so (the C ABI declared in include/kvmini_b200.h).
+
+There is no CPU fallback: if the shared library is missing or a call fails, the caller
+gets an exception.  torch tensors appear here only as device buffers (`.data_ptr()`).
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "csrc", "libkvmini_b200.so")
+
+KVM_OK = 0
+KVM_ERR_ARENA = -4
+KVM_MAX_SETS = 8
+KVM_MAX_COLS = 8
+KVM_MAX_QUERIES = 48
+
+# row flags (kvm_log_scan)
+F_SUCCESS, F_COLD, F_TOKENS, F_GEN = 0x01, 0x02, 0x04, 0x08
+# base sets / columns of the request log
+SET_LAT_COLD, SET_LAT_WARM, SET_TTFB_COLD, SET_TTFB_WARM, SET_TLLT, SET_GEN, SET_PERTOK = range(7)
+COL_LAT, COL_TTFB, COL_TLLT, COL_GEN, COL_PERTOK = range(5)
+# rank kinds
+RANK_LERP_LO, RANK_LERP_HI, RANK_ABSOLUTE, RANK_UPPER_MEDIAN, RANK_FLOOR_PN, RANK_FLOOR_PNM1 = range(6)
+# member modes
+MEMBER_ALL, MEMBER_SET_IDS, MEMBER_STATUS = range(3)
+# query status
+Q_OK, Q_EMPTY, Q_OUT_OF_RANGE = range(3)
+
+
+class NativeError(RuntimeError):
+    """A libkvmini_b200 entry point returned an error code."""
+
+
+class RequestLogC(C.Structure):
+    _fields_ = [("start_ms", C.c_void_p), ("latency_ms", C.c_void_p), ("ttfb_ms", C.c_void_p),
+                ("tllt_ms", C.c_void_p), ("status", C.c_void_p), ("completion_tokens", C.c_void_p),
+                ("total_tokens", C.c_void_p), ("n", C.c_int64)]
+
+
+class SetInfoC(C.Structure):
+    _fields_ = [("count", C.c_int64 * KVM_MAX_SETS), ("kmin", C.c_uint64 * KVM_MAX_COLS),
+                ("kmax", C.c_uint64 * KVM_MAX_COLS), ("set_col", C.c_int32 * KVM_MAX_SETS),
+                ("nsets", C.c_int32), ("ncols", C.c_int32)]
+
+
+class LogStatsC(C.Structure):
+    _fields_ = [("n_total", C.c_int64), ("n_success", C.c_int64), ("n_cold", C.c_int64),
+                ("n_cold_success", C.c_int64), ("sum_completion_tokens", C.c_int64),
+                ("sum_total_tokens", C.c_int64), ("sum_total_tokens_cold", C.c_int64),
+                ("n_gen_rows", C.c_int64), ("min_start_ms", C.c_double), ("max_end_ms", C.c_double),
+                ("ttfb_sum_hi", C.c_double), ("ttfb_sum_lo", C.c_double),
+                ("lat_sum_hi", C.c_double), ("lat_sum_lo", C.c_double), ("sets", SetInfoC)]
+
+
+class QueryC(C.Structure):
+    _fields_ = [("set_mask", C.c_uint32), ("rank_kind", C.c_int32), ("p", C.c_double),
+                ("rank", C.c_int64)]
+
+
+class QueryResultC(C.Structure):
+    _fields_ = [("value", C.c_double), ("n", C.c_int64), ("rank", C.c_int64),
+                ("status", C.c_int32), ("pad", C.c_int32)]
+
+
+_lib: Optional[C.CDLL] = None
+
+
+def _declare(lib: C.CDLL) -> None:
+    vp, i32, i64, f64, sz = C.c_void_p, C.c_int32, C.c_int64, C.c_double, C.c_size_t
+    P = C.POINTER
+    sigs = {
+        "kvm_last_error": (C.c_char_p, []),
+        "kvm_abi_version": (C.c_int, []),
+        "kvm_sm_count": (C.c_int, []),
+        "kvm_log_scan_workspace_bytes": (sz, []),
+        "kvm_log_scan": (C.c_int, [P(RequestLogC), vp, i32, f64, vp, vp, vp, sz, vp]),
+        "kvm_select_workspace_bytes": (sz, [i64]),
+        "kvm_select_default_arena": (i64, [i64]),
+        "kvm_log_select": (C.c_int, [P(RequestLogC), vp, vp, P(QueryC), i32, vp, vp, sz, i64, vp]),
+        "kvm_column_select": (C.c_int, [vp, i64, i32, vp, i32, P(QueryC), i32, vp, vp, sz, i64, vp]),
+        "kvm_select_status": (C.c_int, [vp, vp]),
+        "kvm_column_stats": (C.c_int, [vp, i64, i32, vp, i32, vp, vp, sz, vp]),
+        "kvm_select_hist_ptr": (vp, [vp]),
+        "kvm_select_bins": (i32, []),
+        "kvm_select_arena_ptr": (vp, [vp]),
+        "kvm_select_bucket_counts_ptr": (vp, [vp]),
+        "kvm_select_bucket_offsets_ptr": (vp, [vp]),
+        "kvm_select_info_ptr": (vp, [vp]),
+        "kvm_select_plan": (C.c_int, [vp, P(QueryC), i32, vp, sz, i64, vp]),
+        "kvm_column_select_hist": (C.c_int, [vp, i64, i32, vp, vp, vp]),
+        "kvm_log_select_hist": (C.c_int, [P(RequestLogC), vp, vp, vp]),
+        "kvm_select_resolve": (C.c_int, [vp, vp]),
+        "kvm_column_select_compact": (C.c_int, [vp, i64, i32, vp, vp, vp]),
+        "kvm_log_select_compact": (C.c_int, [P(RequestLogC), vp, vp, vp]),
+        "kvm_select_finish": (C.c_int, [vp, P(vp), i32, vp, vp, vp]),
+        "kvm_log_histograms_workspace_bytes": (sz, [i32]),
+        "kvm_log_histograms": (C.c_int, [P(RequestLogC), vp, vp, i32, vp, vp, sz, vp]),
+        "kvm_column_histogram": (C.c_int, [vp, i64, f64, f64, i32, vp, vp, sz, vp]),
+        "kvm_log_series": (C.c_int, [P(RequestLogC), vp, vp, f64, i64, vp, vp, vp]),
+    }
+    for name, (res, args) in sigs.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    lib._kvm_declared = tuple(sigs)
+
+
+def lib() -> C.CDLL:
+    """Load the shared library (once).  Fails loudly when it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise NativeError(
+                f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; "
+                "g.build()'` (or `make -C kserve-vllm-mini_b200/csrc`). There is no CPU fallback.")
+        loaded = C.CDLL(LIB_PATH)
+        _declare(loaded)
+        _lib = loaded
+    return _lib
+
+
+def check(rc: int, what: str = "") -> int:
+    if rc != KVM_OK:
+        msg = lib().kvm_last_error().decode("utf-8", "replace")
+        raise NativeError(f"{what or 'libkvmini_b200'} failed (rc={rc}): {msg}")
+    return rc

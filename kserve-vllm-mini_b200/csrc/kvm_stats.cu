@@ -1,0 +1,458 @@
+// kvm_stats.cu - K1 (+K7): fused first pass over the request log, and the generic
+// one-column count/min/max pass that feeds the select planner.
+//
+// Replaces (reference file:line)
+//   analyze.py:183-189   window bounds            -> min_start_ms / max_end_ms
+//   analyze.py:402-419   cold/warm classification -> KVM_F_COLD flag
+//   analyze.py:496-514   success / token sums     -> int64 sums (exact)
+//   analyze.py:68,89,143 NaN / tokens>0 filters   -> per-set counts + key ranges
+//   analyze.py:581       statistics.mean(ttfs)    -> double-double sum
+//   cost_estimator.py:117-124,293-308; cost_calculator.py:42-50
+//
+// Roofline: HBM.  Algorithmic bytes = 56 B/row read (4 fp64 + 3 int64) + 1 B/row written.
+// Layout: each thread owns two consecutive rows per tile so that every column is read
+// with one 128-bit load per thread; a warp reads 512 contiguous bytes per column.
+
+#include "kvm_common.cuh"
+
+namespace {
+
+constexpr int STATS_THREADS = 256;
+constexpr int STATS_WARPS = STATS_THREADS / 32;
+constexpr int COLD_SMEM = 1024;  // cold-start times staged in shared memory
+
+// 64-bit slots of one partial.  [0,NSUM) summed, [NSUM,NSUM+NMIN) min, then max, then dd pairs.
+enum {
+  S_SUCCESS = 0, S_COLD, S_COLD_SUCCESS, S_CTOK, S_TTOK, S_TTOK_COLD, S_GEN_ROWS,
+  S_CNT0,                      // 7 set counts
+  NSUM = S_CNT0 + KVM_LOG_NSETS,
+  M_KMIN0 = NSUM,              // 5 column minima + start
+  M_START = M_KMIN0 + KVM_LOG_NCOLS,
+  NMIN_END = M_START + 1,
+  X_KMAX0 = NMIN_END,          // 5 column maxima + end
+  X_END = X_KMAX0 + KVM_LOG_NCOLS,
+  NMAX_END = X_END + 1,
+  D_TTFB = NMAX_END,           // dd pairs (hi, lo)
+  D_LAT = D_TTFB + 2,
+  NSLOTS = D_LAT + 2
+};
+
+struct StatsWs {
+  unsigned int ticket;
+  unsigned int pad[63];
+  uint64_t partial[1];  // [grid][NSLOTS]
+};
+
+struct LogAcc {
+  int64_t sum[NSUM];
+  uint64_t kmin[KVM_LOG_NCOLS + 1];
+  uint64_t kmax[KVM_LOG_NCOLS + 1];
+  kvm_dd ttfb, lat;
+
+  __device__ __forceinline__ void init() {
+#pragma unroll
+    for (int i = 0; i < NSUM; ++i) sum[i] = 0;
+#pragma unroll
+    for (int i = 0; i <= KVM_LOG_NCOLS; ++i) {
+      kmin[i] = ~0ull;
+      kmax[i] = 0ull;
+    }
+    ttfb = {0.0, 0.0};
+    lat = {0.0, 0.0};
+  }
+  __device__ __forceinline__ void range(int c, double v) {
+    uint64_t k = kvm_key(v);
+    kmin[c] = k < kmin[c] ? k : kmin[c];
+    kmax[c] = k > kmax[c] ? k : kmax[c];
+  }
+};
+
+__device__ __forceinline__ bool is_cold(double t_s, const double* cold, int nc, double window) {
+  // largest c <= t decides (c + window is monotone in c)
+  int lo = 0, hi = nc;
+  while (lo < hi) {
+    int mid = (lo + hi) >> 1;
+    if (cold[mid] <= t_s) lo = mid + 1; else hi = mid;
+  }
+  return lo > 0 && t_s <= cold[lo - 1] + window;
+}
+
+__device__ __forceinline__ uint8_t process_row(LogAcc& a, double start, double lat, double ttfb,
+                                               double tllt, int64_t status, int64_t ctok,
+                                               int64_t ttok, const double* cold, int nc,
+                                               double window) {
+  const bool ok = status == 200;
+  const bool cold_row = nc > 0 && is_cold(start / 1000.0, cold, nc, window);
+  if (!kvm_isnan(start)) {
+    uint64_t ks = kvm_key(start);
+    a.kmin[KVM_LOG_NCOLS] = ks < a.kmin[KVM_LOG_NCOLS] ? ks : a.kmin[KVM_LOG_NCOLS];
+  }
+  const double end = start + lat;
+  if (!kvm_isnan(end)) {
+    uint64_t ke = kvm_key(end);
+    a.kmax[KVM_LOG_NCOLS] = ke > a.kmax[KVM_LOG_NCOLS] ? ke : a.kmax[KVM_LOG_NCOLS];
+  }
+  a.sum[S_COLD] += cold_row;
+  uint8_t f = (ok ? KVM_F_SUCCESS : 0) | (cold_row ? KVM_F_COLD : 0) | (ctok > 0 ? KVM_F_TOKENS : 0);
+  if (ok) {
+    a.sum[S_SUCCESS] += 1;
+    a.sum[S_COLD_SUCCESS] += cold_row;
+    a.sum[S_CTOK] += ctok;
+    a.sum[S_TTOK] += ttok;
+    a.sum[S_TTOK_COLD] += cold_row ? ttok : 0;
+    if (!kvm_isnan(lat)) {
+      a.sum[S_CNT0 + (cold_row ? KVM_SET_LAT_COLD : KVM_SET_LAT_WARM)] += 1;
+      a.range(KVM_COL_LAT, lat);
+      a.lat = kvm_dd_add(a.lat, lat);
+    }
+    const bool has_ttfb = !kvm_isnan(ttfb), has_tllt = !kvm_isnan(tllt);
+    if (has_ttfb) {
+      a.sum[S_CNT0 + (cold_row ? KVM_SET_TTFB_COLD : KVM_SET_TTFB_WARM)] += 1;
+      a.range(KVM_COL_TTFB, ttfb);
+      a.ttfb = kvm_dd_add(a.ttfb, ttfb);
+    }
+    if (has_tllt) {
+      a.sum[S_CNT0 + KVM_SET_TLLT] += 1;
+      a.range(KVM_COL_TLLT, tllt);
+    }
+    if (has_ttfb && has_tllt && ctok > 0) {
+      f |= KVM_F_GEN;
+      a.sum[S_GEN_ROWS] += 1;
+      const double g = tllt - ttfb;  // analyze.py:144
+      if (!kvm_isnan(g)) {
+        a.sum[S_CNT0 + KVM_SET_GEN] += 1;
+        a.range(KVM_COL_GEN, g);
+        const double pt = g / (double)ctok;  // analyze.py:146
+        if (!kvm_isnan(pt)) {
+          a.sum[S_CNT0 + KVM_SET_PERTOK] += 1;
+          a.range(KVM_COL_PERTOK, pt);
+        }
+      }
+    }
+  }
+  return f;
+}
+
+template <bool VEC>
+__global__ void __launch_bounds__(STATS_THREADS, 2)
+log_scan_kernel(kvm_request_log log, const double* __restrict__ cold_g, int nc, double window,
+                uint8_t* __restrict__ flags, kvm_log_stats* __restrict__ out, StatsWs* ws) {
+  __shared__ double cold_s[COLD_SMEM];
+  __shared__ uint64_t red[STATS_WARPS][NSLOTS];
+  __shared__ bool is_last;
+
+  const double* cold = cold_g;
+  if (nc > 0 && nc <= COLD_SMEM) {
+    for (int i = threadIdx.x; i < nc; i += STATS_THREADS) cold_s[i] = cold_g[i];
+    cold = cold_s;
+    __syncthreads();
+  }
+
+  LogAcc a;
+  a.init();
+  const int64_t n = log.n;
+
+  if (VEC) {
+    const int64_t npairs = n >> 1;
+    for (int64_t p = (int64_t)blockIdx.x * STATS_THREADS + threadIdx.x; p < npairs;
+         p += (int64_t)gridDim.x * STATS_THREADS) {
+      const int64_t i = p << 1;
+      const double2 st = kvm_ld2(log.start_ms + i);
+      const double2 la = kvm_ld2(log.latency_ms + i);
+      const double2 tf = kvm_ld2(log.ttfb_ms + i);
+      const double2 tl = kvm_ld2(log.tllt_ms + i);
+      const longlong2 ss = kvm_ld2(log.status + i);
+      const longlong2 ct = kvm_ld2(log.completion_tokens + i);
+      const longlong2 tt = kvm_ld2(log.total_tokens + i);
+      const uint8_t f0 = process_row(a, st.x, la.x, tf.x, tl.x, ss.x, ct.x, tt.x, cold, nc, window);
+      const uint8_t f1 = process_row(a, st.y, la.y, tf.y, tl.y, ss.y, ct.y, tt.y, cold, nc, window);
+      if (flags) *reinterpret_cast<uint16_t*>(flags + i) = (uint16_t)f0 | ((uint16_t)f1 << 8);
+    }
+    if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
+      const int64_t i = n - 1;
+      const uint8_t f = process_row(a, log.start_ms[i], log.latency_ms[i], log.ttfb_ms[i],
+                                    log.tllt_ms[i], log.status[i], log.completion_tokens[i],
+                                    log.total_tokens[i], cold, nc, window);
+      if (flags) flags[i] = f;
+    }
+  } else {
+    for (int64_t i = (int64_t)blockIdx.x * STATS_THREADS + threadIdx.x; i < n;
+         i += (int64_t)gridDim.x * STATS_THREADS) {
+      const uint8_t f = process_row(a, kvm_ld1(log.start_ms + i), kvm_ld1(log.latency_ms + i),
+                                    kvm_ld1(log.ttfb_ms + i), kvm_ld1(log.tllt_ms + i),
+                                    kvm_ld1(log.status + i), kvm_ld1(log.completion_tokens + i),
+                                    kvm_ld1(log.total_tokens + i), cold, nc, window);
+      if (flags) flags[i] = f;
+    }
+  }
+
+  // ---- warp reduction, then fixed-order reduction across warps and across CTAs
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int s = 0; s < NSUM; ++s) {
+    int64_t v = kvm_warp_sum(a.sum[s]);
+    if (lane == 0) red[warp][s] = (uint64_t)v;
+  }
+#pragma unroll
+  for (int c = 0; c <= KVM_LOG_NCOLS; ++c) {
+    uint64_t lo = kvm_warp_min(a.kmin[c]), hi = kvm_warp_max(a.kmax[c]);
+    if (lane == 0) {
+      red[warp][M_KMIN0 + c] = lo;
+      red[warp][X_KMAX0 + c] = hi;
+    }
+  }
+  {
+    kvm_dd t = kvm_warp_sum(a.ttfb), l = kvm_warp_sum(a.lat);
+    if (lane == 0) {
+      red[warp][D_TTFB] = (uint64_t)__double_as_longlong(t.hi);
+      red[warp][D_TTFB + 1] = (uint64_t)__double_as_longlong(t.lo);
+      red[warp][D_LAT] = (uint64_t)__double_as_longlong(l.hi);
+      red[warp][D_LAT + 1] = (uint64_t)__double_as_longlong(l.lo);
+    }
+  }
+  __syncthreads();
+
+  auto combine = [](int slot, uint64_t acc, uint64_t v) -> uint64_t {
+    if (slot < NSUM) return (uint64_t)((int64_t)acc + (int64_t)v);
+    if (slot < NMIN_END) return v < acc ? v : acc;
+    return v > acc ? v : acc;
+  };
+
+  uint64_t* mine = ws->partial + (size_t)blockIdx.x * NSLOTS;
+  if (threadIdx.x < NMAX_END) {
+    const int s = threadIdx.x;
+    uint64_t acc = red[0][s];
+    for (int w = 1; w < STATS_WARPS; ++w) acc = combine(s, acc, red[w][s]);
+    mine[s] = acc;
+  } else if (threadIdx.x == NMAX_END || threadIdx.x == NMAX_END + 1) {
+    const int s = threadIdx.x == NMAX_END ? D_TTFB : D_LAT;
+    kvm_dd acc{__longlong_as_double((long long)red[0][s]), __longlong_as_double((long long)red[0][s + 1])};
+    for (int w = 1; w < STATS_WARPS; ++w)
+      acc = kvm_dd_add(acc, kvm_dd{__longlong_as_double((long long)red[w][s]),
+                                   __longlong_as_double((long long)red[w][s + 1])});
+    mine[s] = (uint64_t)__double_as_longlong(acc.hi);
+    mine[s + 1] = (uint64_t)__double_as_longlong(acc.lo);
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned int t = atomicAdd(&ws->ticket, 1u);
+    is_last = (t == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+
+  // last CTA: every slot is reduced by one thread over the CTAs in index order
+  __shared__ uint64_t fin[NSLOTS];
+  const volatile uint64_t* part = ws->partial;
+  if (threadIdx.x < NMAX_END) {
+    const int s = threadIdx.x;
+    uint64_t acc = part[s];
+    for (unsigned b = 1; b < gridDim.x; ++b) acc = combine(s, acc, part[(size_t)b * NSLOTS + s]);
+    fin[s] = acc;
+  } else if (threadIdx.x == NMAX_END || threadIdx.x == NMAX_END + 1) {
+    const int s = threadIdx.x == NMAX_END ? D_TTFB : D_LAT;
+    kvm_dd acc{__longlong_as_double((long long)part[s]), __longlong_as_double((long long)part[s + 1])};
+    for (unsigned b = 1; b < gridDim.x; ++b) {
+      const size_t o = (size_t)b * NSLOTS + s;
+      acc = kvm_dd_add(acc, kvm_dd{__longlong_as_double((long long)part[o]),
+                                   __longlong_as_double((long long)part[o + 1])});
+    }
+    fin[s] = (uint64_t)__double_as_longlong(acc.hi);
+    fin[s + 1] = (uint64_t)__double_as_longlong(acc.lo);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    kvm_log_stats r;
+    r.n_total = n;
+    r.n_success = (int64_t)fin[S_SUCCESS];
+    r.n_cold = (int64_t)fin[S_COLD];
+    r.n_cold_success = (int64_t)fin[S_COLD_SUCCESS];
+    r.sum_completion_tokens = (int64_t)fin[S_CTOK];
+    r.sum_total_tokens = (int64_t)fin[S_TTOK];
+    r.sum_total_tokens_cold = (int64_t)fin[S_TTOK_COLD];
+    r.n_gen_rows = (int64_t)fin[S_GEN_ROWS];
+    r.min_start_ms = fin[M_START] == ~0ull ? __longlong_as_double(0x7ff8000000000000ll)
+                                           : kvm_unkey(fin[M_START]);
+    r.max_end_ms = fin[X_END] == 0ull ? __longlong_as_double(0x7ff8000000000000ll)
+                                      : kvm_unkey(fin[X_END]);
+    r.ttfb_sum_hi = __longlong_as_double((long long)fin[D_TTFB]);
+    r.ttfb_sum_lo = __longlong_as_double((long long)fin[D_TTFB + 1]);
+    r.lat_sum_hi = __longlong_as_double((long long)fin[D_LAT]);
+    r.lat_sum_lo = __longlong_as_double((long long)fin[D_LAT + 1]);
+    for (int s = 0; s < KVM_MAX_SETS; ++s) {
+      r.sets.count[s] = s < KVM_LOG_NSETS ? (int64_t)fin[S_CNT0 + s] : 0;
+      r.sets.set_col[s] = 0;
+    }
+    for (int c = 0; c < KVM_MAX_COLS; ++c) {
+      r.sets.kmin[c] = c < KVM_LOG_NCOLS ? fin[M_KMIN0 + c] : ~0ull;
+      r.sets.kmax[c] = c < KVM_LOG_NCOLS ? fin[X_KMAX0 + c] : 0ull;
+    }
+    r.sets.set_col[KVM_SET_LAT_COLD] = KVM_COL_LAT;
+    r.sets.set_col[KVM_SET_LAT_WARM] = KVM_COL_LAT;
+    r.sets.set_col[KVM_SET_TTFB_COLD] = KVM_COL_TTFB;
+    r.sets.set_col[KVM_SET_TTFB_WARM] = KVM_COL_TTFB;
+    r.sets.set_col[KVM_SET_TLLT] = KVM_COL_TLLT;
+    r.sets.set_col[KVM_SET_GEN] = KVM_COL_GEN;
+    r.sets.set_col[KVM_SET_PERTOK] = KVM_COL_PERTOK;
+    r.sets.nsets = KVM_LOG_NSETS;
+    r.sets.ncols = KVM_LOG_NCOLS;
+    *out = r;
+    ws->ticket = 0;  // ready for the next launch on this workspace
+  }
+}
+
+// ------------------------------------------------------------------ generic column stats
+constexpr int CS_SLOTS = KVM_MAX_SETS + 2;  // counts, kmin, kmax
+
+struct ColStatsWs {
+  unsigned int ticket;
+  unsigned int pad[63];
+  uint64_t partial[1];  // [grid][CS_SLOTS]
+};
+
+__device__ __forceinline__ int member_set(int mode, const void* member, int64_t i) {
+  if (mode == KVM_MEMBER_ALL) return 0;
+  if (mode == KVM_MEMBER_SET_IDS) return (int)kvm_ld_u8(reinterpret_cast<const uint8_t*>(member) + i);
+  return kvm_ld1(reinterpret_cast<const int64_t*>(member) + i) == 200 ? 0 : 255;
+}
+
+__global__ void __launch_bounds__(STATS_THREADS, 4)
+column_stats_kernel(const double* __restrict__ values, int64_t n, int mode,
+                    const void* __restrict__ member, int nsets, kvm_set_info* out, ColStatsWs* ws) {
+  __shared__ uint64_t red[STATS_WARPS][CS_SLOTS];
+  __shared__ bool is_last;
+  int64_t cnt[KVM_MAX_SETS];
+#pragma unroll
+  for (int s = 0; s < KVM_MAX_SETS; ++s) cnt[s] = 0;
+  uint64_t kmin = ~0ull, kmax = 0ull;
+  for (int64_t i = (int64_t)blockIdx.x * STATS_THREADS + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * STATS_THREADS) {
+    const double v = kvm_ld1(values + i);
+    const int s = member_set(mode, member, i);
+    if (s < nsets && !kvm_isnan(v)) {
+#pragma unroll
+      for (int k = 0; k < KVM_MAX_SETS; ++k) cnt[k] += (s == k);
+      const uint64_t key = kvm_key(v);
+      kmin = key < kmin ? key : kmin;
+      kmax = key > kmax ? key : kmax;
+    }
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int s = 0; s < KVM_MAX_SETS; ++s) {
+    int64_t v = kvm_warp_sum(cnt[s]);
+    if (lane == 0) red[warp][s] = (uint64_t)v;
+  }
+  kmin = kvm_warp_min(kmin);
+  kmax = kvm_warp_max(kmax);
+  if (lane == 0) {
+    red[warp][KVM_MAX_SETS] = kmin;
+    red[warp][KVM_MAX_SETS + 1] = kmax;
+  }
+  __syncthreads();
+  auto combine = [](int slot, uint64_t acc, uint64_t v) -> uint64_t {
+    if (slot < KVM_MAX_SETS) return acc + v;
+    if (slot == KVM_MAX_SETS) return v < acc ? v : acc;
+    return v > acc ? v : acc;
+  };
+  if (threadIdx.x < CS_SLOTS) {
+    const int s = threadIdx.x;
+    uint64_t acc = red[0][s];
+    for (int w = 1; w < STATS_WARPS; ++w) acc = combine(s, acc, red[w][s]);
+    ws->partial[(size_t)blockIdx.x * CS_SLOTS + s] = acc;
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) is_last = (atomicAdd(&ws->ticket, 1u) == gridDim.x - 1);
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  __shared__ uint64_t fin[CS_SLOTS];
+  const volatile uint64_t* part = ws->partial;
+  if (threadIdx.x < CS_SLOTS) {
+    const int s = threadIdx.x;
+    uint64_t acc = part[s];
+    for (unsigned b = 1; b < gridDim.x; ++b) acc = combine(s, acc, part[(size_t)b * CS_SLOTS + s]);
+    fin[s] = acc;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    kvm_set_info r;
+    for (int s = 0; s < KVM_MAX_SETS; ++s) {
+      r.count[s] = s < nsets ? (int64_t)fin[s] : 0;
+      r.set_col[s] = 0;
+    }
+    for (int c = 0; c < KVM_MAX_COLS; ++c) {
+      r.kmin[c] = ~0ull;
+      r.kmax[c] = 0ull;
+    }
+    r.kmin[0] = fin[KVM_MAX_SETS];
+    r.kmax[0] = fin[KVM_MAX_SETS + 1];
+    r.nsets = nsets;
+    r.ncols = 1;
+    *out = r;
+    ws->ticket = 0;
+  }
+}
+
+constexpr int MAX_GRID = 148 * 8;  // workspace sizing bound (B200: 148 SMs)
+
+}  // namespace
+
+extern "C" size_t kvm_log_scan_workspace_bytes(void) {
+  return kvm_align_up(256 + sizeof(uint64_t) * (size_t)NSLOTS * MAX_GRID, 256);
+}
+
+static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+extern "C" int kvm_log_scan(const kvm_request_log* log, const double* cold_times, int32_t n_cold,
+                            double cold_window_s, uint8_t* flags, kvm_log_stats* stats,
+                            void* workspace, size_t workspace_bytes, void* stream) {
+  KVM_REQUIRE(log && stats && workspace, "kvm_log_scan: null argument");
+  KVM_REQUIRE(log->n >= 0 && n_cold >= 0, "kvm_log_scan: negative size");
+  KVM_REQUIRE(n_cold == 0 || cold_times, "kvm_log_scan: cold_times is null");
+  if (workspace_bytes < kvm_log_scan_workspace_bytes()) {
+    kvm_set_error("kvm_log_scan: workspace %zu < %zu bytes", workspace_bytes,
+                  kvm_log_scan_workspace_bytes());
+    return KVM_ERR_WORKSPACE;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  StatsWs* ws = reinterpret_cast<StatsWs*>(workspace);
+  KVM_CUDA_CHECK(cudaMemsetAsync(ws, 0, 256, st));
+  int grid = kvm_grid_for(log->n, STATS_THREADS * 2 * 4, 2);
+  if (grid > MAX_GRID) grid = MAX_GRID;
+  const bool vec = aligned16(log->start_ms) && aligned16(log->latency_ms) &&
+                   aligned16(log->ttfb_ms) && aligned16(log->tllt_ms) && aligned16(log->status) &&
+                   aligned16(log->completion_tokens) && aligned16(log->total_tokens) &&
+                   (flags == nullptr || (reinterpret_cast<uintptr_t>(flags) & 1u) == 0);
+  if (vec)
+    log_scan_kernel<true><<<grid, STATS_THREADS, 0, st>>>(*log, cold_times, n_cold, cold_window_s,
+                                                          flags, stats, ws);
+  else
+    log_scan_kernel<false><<<grid, STATS_THREADS, 0, st>>>(*log, cold_times, n_cold,
+                                                           cold_window_s, flags, stats, ws);
+  KVM_CUDA_CHECK(cudaGetLastError());
+  return KVM_OK;
+}
+
+extern "C" int kvm_column_stats(const double* values, int64_t n, int32_t mode, const void* member,
+                                int32_t nsets, kvm_set_info* info, void* workspace,
+                                size_t workspace_bytes, void* stream) {
+  KVM_REQUIRE(info && workspace && (values || n == 0), "kvm_column_stats: null argument");
+  KVM_REQUIRE(n >= 0 && nsets >= 1 && nsets <= KVM_MAX_SETS, "kvm_column_stats: bad n/nsets");
+  KVM_REQUIRE(mode == KVM_MEMBER_ALL || member, "kvm_column_stats: member array is null");
+  const size_t need = kvm_align_up(256 + sizeof(uint64_t) * (size_t)CS_SLOTS * MAX_GRID, 256);
+  if (workspace_bytes < need) {
+    kvm_set_error("kvm_column_stats: workspace %zu < %zu bytes", workspace_bytes, need);
+    return KVM_ERR_WORKSPACE;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  ColStatsWs* ws = reinterpret_cast<ColStatsWs*>(workspace);
+  KVM_CUDA_CHECK(cudaMemsetAsync(ws, 0, 256, st));
+  int grid = kvm_grid_for(n, STATS_THREADS * 8, 4);
+  column_stats_kernel<<<grid, STATS_THREADS, 0, st>>>(values, n, mode, member, nsets, info, ws);
+  KVM_CUDA_CHECK(cudaGetLastError());
+  return KVM_OK;
+}

@@ -1,0 +1,332 @@
+"""Device side of the run analysis: columnar log in HBM -> raw statistics.
+
+Host code here only owns buffers (torch tensors), builds the query list and launches the
+C ABI (ctypes).  All arithmetic on the records happens in libkvmini_b200.so; all final
+scalar expressions (interpolation, ratios, histogram edges) are evaluated by
+`report.py` in Python floats, in the reference's order.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+import math
+from dataclasses import dataclass, field
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from . import _native as N
+from .columns import F64_COLS, I64_COLS, RequestLog
+
+
+def _stream_ptr(device: torch.device) -> int:
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+def require_cuda() -> torch.device:
+    if not torch.cuda.is_available():
+        raise N.NativeError("no CUDA device: the run analysis has no CPU path "
+                            "(kserve-vllm-mini_b200 runs on sm_100a only)")
+    N.lib()
+    return torch.device("cuda", torch.cuda.current_device())
+
+
+# --------------------------------------------------------------------------- device log
+@dataclass
+class DeviceLog:
+    """Seven device-resident columns (fp64 x4, int64 x3) of one request log."""
+
+    cols: Dict[str, torch.Tensor]
+    n: int
+    device: torch.device
+
+    @staticmethod
+    def from_host(log: RequestLog, device: Optional[torch.device] = None,
+                  pinned: bool = False) -> "DeviceLog":
+        device = device or require_cuda()
+        cols = {}
+        for k in F64_COLS + I64_COLS:
+            t = torch.from_numpy(np.ascontiguousarray(log.cols[k]))
+            if pinned:
+                t = t.pin_memory()
+            cols[k] = t.to(device, non_blocking=pinned)
+        return DeviceLog(cols=cols, n=log.n, device=device)
+
+    @staticmethod
+    def from_tensors(cols: Dict[str, torch.Tensor]) -> "DeviceLog":
+        n = int(cols["status"].shape[0])
+        for k in F64_COLS:
+            assert cols[k].dtype == torch.float64 and cols[k].is_contiguous() and cols[k].shape[0] == n, k
+        for k in I64_COLS:
+            assert cols[k].dtype == torch.int64 and cols[k].is_contiguous() and cols[k].shape[0] == n, k
+        return DeviceLog(cols=dict(cols), n=n, device=cols["status"].device)
+
+    def c_struct(self) -> N.RequestLogC:
+        c = self.cols
+        return N.RequestLogC(c["start_ms"].data_ptr(), c["latency_ms"].data_ptr(),
+                             c["ttfb_ms"].data_ptr(), c["tllt_ms"].data_ptr(),
+                             c["status"].data_ptr(), c["completion_tokens"].data_ptr(),
+                             c["total_tokens"].data_ptr(), self.n)
+
+
+# --------------------------------------------------------------------------- queries
+@dataclass(frozen=True)
+class Quantile:
+    """One percentile() call site: a multiset (union of base sets) and a p."""
+    name: str
+    set_mask: int
+    p: float
+
+
+LAT_ALL = (1 << N.SET_LAT_COLD) | (1 << N.SET_LAT_WARM)
+TTFB_ALL = (1 << N.SET_TTFB_COLD) | (1 << N.SET_TTFB_WARM)
+
+# The 23 distinct (multiset, p) pairs behind analyze.py's 25 percentile() calls
+# (ttft_p50/p95 and ttfb_p50/p95 rank the same multiset - SURVEY.md A2).
+ANALYZE_QUANTILES: Tuple[Quantile, ...] = (
+    Quantile("lat_p50", LAT_ALL, 0.50), Quantile("lat_p95", LAT_ALL, 0.95), Quantile("lat_p99", LAT_ALL, 0.99),
+    Quantile("cold_lat_p50", 1 << N.SET_LAT_COLD, 0.50), Quantile("cold_lat_p95", 1 << N.SET_LAT_COLD, 0.95),
+    Quantile("cold_lat_p99", 1 << N.SET_LAT_COLD, 0.99),
+    Quantile("warm_lat_p50", 1 << N.SET_LAT_WARM, 0.50), Quantile("warm_lat_p95", 1 << N.SET_LAT_WARM, 0.95),
+    Quantile("warm_lat_p99", 1 << N.SET_LAT_WARM, 0.99),
+    Quantile("ttfb_p50", TTFB_ALL, 0.50), Quantile("ttfb_p95", TTFB_ALL, 0.95), Quantile("ttfb_p99", TTFB_ALL, 0.99),
+    Quantile("cold_ttfb_p50", 1 << N.SET_TTFB_COLD, 0.50), Quantile("cold_ttfb_p95", 1 << N.SET_TTFB_COLD, 0.95),
+    Quantile("warm_ttfb_p50", 1 << N.SET_TTFB_WARM, 0.50), Quantile("warm_ttfb_p95", 1 << N.SET_TTFB_WARM, 0.95),
+    Quantile("tllt_p50", 1 << N.SET_TLLT, 0.50), Quantile("tllt_p95", 1 << N.SET_TLLT, 0.95),
+    Quantile("tllt_p99", 1 << N.SET_TLLT, 0.99),
+    Quantile("gen_p50", 1 << N.SET_GEN, 0.50), Quantile("gen_p95", 1 << N.SET_GEN, 0.95),
+    Quantile("pertok_p50", 1 << N.SET_PERTOK, 0.50), Quantile("pertok_p95", 1 << N.SET_PERTOK, 0.95),
+)
+
+
+@dataclass
+class OrderStat:
+    """What the device returns for one quantile: the two neighbouring order statistics."""
+    n: int
+    v_lo: float
+    v_hi: float
+    status: int = 0
+
+    def interpolate(self, p: float) -> float:
+        """analyze.py:65-81 given (n, vals[lo], vals[hi])."""
+        if self.n == 0:
+            return float("nan")
+        if self.n == 1:
+            return self.v_lo
+        pos = max(0.0, min(p, 1.0)) * (self.n - 1)
+        lo = int(math.floor(pos))
+        hi = int(math.ceil(pos))
+        if lo == hi:
+            return self.v_lo
+        frac = pos - lo
+        return self.v_lo + frac * (self.v_hi - self.v_lo)
+
+
+def build_queries(quantiles: Sequence[Quantile]) -> "C.Array":
+    arr = (N.QueryC * (2 * len(quantiles)))()
+    for i, q in enumerate(quantiles):
+        arr[2 * i] = N.QueryC(q.set_mask, N.RANK_LERP_LO, q.p, 0)
+        arr[2 * i + 1] = N.QueryC(q.set_mask, N.RANK_LERP_HI, q.p, 0)
+    return arr
+
+
+def results_to_orderstats(res: np.ndarray, quantiles: Sequence[Quantile]) -> Dict[str, OrderStat]:
+    out = {}
+    for i, q in enumerate(quantiles):
+        lo, hi = res[2 * i], res[2 * i + 1]
+        out[q.name] = OrderStat(int(lo["n"]), float(lo["value"]), float(hi["value"]), int(lo["status"]))
+    return out
+
+
+RESULT_DTYPE = np.dtype([("value", "<f8"), ("n", "<i8"), ("rank", "<i8"), ("status", "<i4"), ("pad", "<i4")])
+assert RESULT_DTYPE.itemsize == C.sizeof(N.QueryResultC)
+
+
+# --------------------------------------------------------------------------- raw analysis
+@dataclass
+class RawAnalysis:
+    """Everything the device produced for one log; consumed by report.py."""
+    stats: N.LogStatsC
+    order: Dict[str, OrderStat]
+    hist_counts: np.ndarray                 # int64 [4][num_bins]: ttfb, tllt, generation, per-token
+    num_bins: int
+    series: Optional[np.ndarray] = None     # int64 [3][nb]: requests, success, completion tokens
+    series_window_s: float = 1.0
+    flags: Optional[torch.Tensor] = None    # uint8 [n] on device (KVM_F_*)
+    timings_ms: Dict[str, float] = field(default_factory=dict)
+
+    def key_to_float(self, key: int) -> float:
+        bits = key ^ (0x8000000000000000 if (key >> 63) else 0xFFFFFFFFFFFFFFFF)
+        return float(np.array([bits], dtype=np.uint64).view(np.float64)[0])
+
+    def col_range(self, col: int) -> Optional[Tuple[float, float]]:
+        kmin, kmax = int(self.stats.sets.kmin[col]), int(self.stats.sets.kmax[col])
+        if kmin > kmax:
+            return None
+        return self.key_to_float(kmin), self.key_to_float(kmax)
+
+
+class LogAnalyzer:
+    """Reusable buffers + launch sequence for one log size (workspaces are cached so a
+    steady-state call allocates nothing)."""
+
+    def __init__(self, device: Optional[torch.device] = None):
+        self.device = device or require_cuda()
+        self.lib = N.lib()
+        self._scan_ws = torch.empty(self.lib.kvm_log_scan_workspace_bytes(), dtype=torch.uint8, device=self.device)
+        self._stats_d = torch.zeros(C.sizeof(N.LogStatsC), dtype=torch.uint8, device=self.device)
+        self._stats_h = torch.zeros(C.sizeof(N.LogStatsC), dtype=torch.uint8).pin_memory()
+        self._hist_ws = torch.empty(self.lib.kvm_log_histograms_workspace_bytes(256), dtype=torch.uint8, device=self.device)
+        self._sel_ws: Optional[torch.Tensor] = None
+        self._sel_cap = 0
+        self._flags: Optional[torch.Tensor] = None
+        self._results_d = torch.zeros(N.KVM_MAX_QUERIES * C.sizeof(N.QueryResultC), dtype=torch.uint8, device=self.device)
+        self._results_h = torch.zeros(N.KVM_MAX_QUERIES * C.sizeof(N.QueryResultC), dtype=torch.uint8).pin_memory()
+        self._empty_cold = torch.zeros(1, dtype=torch.float64, device=self.device)
+        self.launches = 0   # kernels launched by the last analyze() (for bench accounting)
+
+    # -- buffers
+    def _ensure(self, n: int, arena: Optional[int] = None) -> None:
+        if self._flags is None or self._flags.shape[0] < n + 2:
+            self._flags = torch.empty(n + 2, dtype=torch.uint8, device=self.device)
+        cap = arena if arena is not None else int(self.lib.kvm_select_default_arena(n))
+        if self._sel_ws is None or self._sel_cap < cap:
+            self._sel_ws = torch.empty(self.lib.kvm_select_workspace_bytes(cap), dtype=torch.uint8, device=self.device)
+            self._sel_cap = cap
+
+    def scan(self, dlog: DeviceLog, cold_times: Sequence[float], cold_window_s: float = 30.0) -> N.LogStatsC:
+        """K1: one pass, returns the stats struct (synchronises)."""
+        self._ensure(dlog.n)
+        st = _stream_ptr(self.device)
+        cold = sorted(float(c) for c in cold_times)
+        cold_d = (torch.tensor(cold, dtype=torch.float64, device=self.device) if cold else self._empty_cold)
+        self._cold_d = cold_d
+        log_c = dlog.c_struct()
+        N.check(self.lib.kvm_log_scan(C.byref(log_c), cold_d.data_ptr(), len(cold), float(cold_window_s),
+                                      self._flags.data_ptr(), self._stats_d.data_ptr(),
+                                      self._scan_ws.data_ptr(), self._scan_ws.numel(), st), "kvm_log_scan")
+        self.launches += 1
+        self._stats_h.copy_(self._stats_d, non_blocking=True)
+        torch.cuda.current_stream(self.device).synchronize()
+        return N.LogStatsC.from_buffer_copy(self._stats_h.numpy().tobytes())
+
+    def analyze(self, dlog: DeviceLog, cold_times: Sequence[float] = (), num_bins: int = 20,
+                series_window_s: Optional[float] = 1.0, max_series_bins: int = 1 << 24,
+                quantiles: Sequence[Quantile] = ANALYZE_QUANTILES) -> RawAnalysis:
+        """scan -> (sync) -> select + histograms + series -> (sync).  Two host round trips."""
+        self.launches = 0
+        stats = self.scan(dlog, cold_times)
+        st = _stream_ptr(self.device)
+        log_c = dlog.c_struct()
+        queries = build_queries(quantiles)
+        nq = len(queries)
+        assert nq <= N.KVM_MAX_QUERIES
+
+        hist_d = torch.empty((4, num_bins), dtype=torch.int64, device=self.device)
+        series_d = None
+        nb = 0
+        if series_window_s is not None and dlog.n > 0 and not math.isnan(stats.min_start_ms):
+            # number of windows: ceil(duration/window), at least the bin of the last start
+            t0, t1 = stats.min_start_ms / 1000.0, stats.max_end_ms / 1000.0
+            nb = max(1, int(math.ceil((t1 - t0) / series_window_s)) + 1)
+            nb = min(nb, max_series_bins)
+            series_d = torch.empty((3, nb), dtype=torch.int64, device=self.device)
+            dropped_d = torch.empty(1, dtype=torch.int64, device=self.device)
+
+        arena = self._sel_cap
+        while True:
+            N.check(self.lib.kvm_log_select(C.byref(log_c), self._flags.data_ptr(), self._stats_d.data_ptr(),
+                                            queries, nq, self._results_d.data_ptr(), self._sel_ws.data_ptr(),
+                                            self._sel_ws.numel(), arena, st), "kvm_log_select")
+            self.launches += 5
+            N.check(self.lib.kvm_log_histograms(C.byref(log_c), self._flags.data_ptr(), self._stats_d.data_ptr(),
+                                                num_bins, hist_d.data_ptr(), self._hist_ws.data_ptr(),
+                                                self._hist_ws.numel(), st), "kvm_log_histograms")
+            self.launches += 2
+            if series_d is not None:
+                N.check(self.lib.kvm_log_series(C.byref(log_c), self._flags.data_ptr(), self._stats_d.data_ptr(),
+                                                float(series_window_s) * 1000.0, nb, series_d.data_ptr(),
+                                                dropped_d.data_ptr(), st), "kvm_log_series")
+                self.launches += 1
+            self._results_h.copy_(self._results_d, non_blocking=True)
+            rc = self.lib.kvm_select_status(self._sel_ws.data_ptr(), st)   # synchronises
+            if rc == N.KVM_ERR_ARENA:
+                # pathological concentration: retry once with room for every key of every query
+                arena = max(2 * arena, dlog.n * 4 + 1024)
+                self._ensure(dlog.n, arena)
+                continue
+            N.check(rc, "kvm_log_select")
+            break
+
+        res = np.frombuffer(self._results_h.numpy().tobytes(), dtype=RESULT_DTYPE)[:nq]
+        series = None
+        if series_d is not None:
+            series = series_d.cpu().numpy()
+            if int(dropped_d.item()) != 0:
+                raise N.NativeError("kvm_log_series dropped rows: raise max_series_bins")
+        return RawAnalysis(stats=stats, order=results_to_orderstats(res, quantiles),
+                           hist_counts=hist_d.cpu().numpy(), num_bins=num_bins, series=series,
+                           series_window_s=series_window_s or 1.0, flags=self._flags[:dlog.n])
+
+
+# --------------------------------------------------------------------------- single columns
+class ColumnOps:
+    """Generic one-column entry points behind `percentile()` / `compute_histograms()`."""
+
+    def __init__(self, device: Optional[torch.device] = None):
+        self.device = device or require_cuda()
+        self.lib = N.lib()
+
+    def order_stats(self, values: torch.Tensor, queries: Sequence[Tuple[int, int, float, int]],
+                    member_mode: int = N.MEMBER_ALL, member: Optional[torch.Tensor] = None,
+                    nsets: int = 1) -> np.ndarray:
+        """queries: (set_mask, rank_kind, p, rank).  Returns structured array of results."""
+        assert values.dtype == torch.float64 and values.is_contiguous()
+        n = int(values.shape[0])
+        nq = len(queries)
+        arr = (N.QueryC * nq)(*[N.QueryC(*q) for q in queries])
+        res_d = torch.zeros(N.KVM_MAX_QUERIES * C.sizeof(N.QueryResultC), dtype=torch.uint8, device=self.device)
+        st = _stream_ptr(self.device)
+        arena = int(self.lib.kvm_select_default_arena(n))
+        while True:
+            ws = torch.empty(self.lib.kvm_select_workspace_bytes(arena), dtype=torch.uint8, device=self.device)
+            N.check(self.lib.kvm_column_select(values.data_ptr(), n, member_mode,
+                                               member.data_ptr() if member is not None else None, nsets,
+                                               arr, nq, res_d.data_ptr(), ws.data_ptr(), ws.numel(), arena, st),
+                    "kvm_column_select")
+            rc = self.lib.kvm_select_status(ws.data_ptr(), st)
+            if rc == N.KVM_ERR_ARENA:
+                arena = max(2 * arena, n * nq + 1024)
+                continue
+            N.check(rc, "kvm_column_select")
+            break
+        return np.frombuffer(res_d.cpu().numpy().tobytes(), dtype=RESULT_DTYPE)[:nq]
+
+    def quantile_stat(self, values: torch.Tensor, p: float, **kw) -> OrderStat:
+        r = self.order_stats(values, [(1, N.RANK_LERP_LO, p, 0), (1, N.RANK_LERP_HI, p, 0)], **kw)
+        return OrderStat(int(r[0]["n"]), float(r[0]["value"]), float(r[1]["value"]), int(r[0]["status"]))
+
+    def minmax_count(self, values: torch.Tensor) -> Tuple[int, float, float]:
+        """count / min / max over non-NaN values via kvm_column_stats."""
+        n = int(values.shape[0])
+        info_d = torch.zeros(C.sizeof(N.SetInfoC), dtype=torch.uint8, device=self.device)
+        ws = torch.empty(256 + 8 * 10 * 148 * 8, dtype=torch.uint8, device=self.device)
+        N.check(self.lib.kvm_column_stats(values.data_ptr(), n, N.MEMBER_ALL, None, 1, info_d.data_ptr(),
+                                          ws.data_ptr(), ws.numel(), _stream_ptr(self.device)), "kvm_column_stats")
+        info = N.SetInfoC.from_buffer_copy(info_d.cpu().numpy().tobytes())
+        cnt = int(info.count[0])
+        if cnt == 0:
+            return 0, float("nan"), float("nan")
+        def unkey(k):
+            bits = k ^ (0x8000000000000000 if (k >> 63) else 0xFFFFFFFFFFFFFFFF)
+            return float(np.array([bits], dtype=np.uint64).view(np.float64)[0])
+        return cnt, unkey(int(info.kmin[0])), unkey(int(info.kmax[0]))
+
+    def histogram_counts(self, values: torch.Tensor, lo: float, hi: float, num_bins: int) -> List[int]:
+        counts = torch.empty(num_bins, dtype=torch.int64, device=self.device)
+        ws = torch.empty(self.lib.kvm_log_histograms_workspace_bytes(num_bins), dtype=torch.uint8, device=self.device)
+        N.check(self.lib.kvm_column_histogram(values.data_ptr(), int(values.shape[0]), lo, hi, num_bins,
+                                              counts.data_ptr(), ws.data_ptr(), ws.numel(),
+                                              _stream_ptr(self.device)), "kvm_column_histogram")
+        return counts.cpu().tolist()

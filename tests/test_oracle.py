@@ -1,0 +1,192 @@
+"""The oracle against the reference's golden vectors (CPU).  If these fail the oracle is
+wrong and every parity claim built on it is void."""
+import json
+import math
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, diff_keys, load_json, same, unj
+from kvmini_b200 import columns
+from oracle import np_port, py_port
+
+
+def log_cols(path):
+    log = columns.load_requests_csv(path)
+    columns.check_analyzable(log)
+    return log
+
+
+def as_lists(log):
+    return {k: v.tolist() for k, v in log.cols.items()}
+
+
+def test_percentile_golden(known_answers):
+    for case in known_answers["percentile"]:
+        vals, exp = unj(case["values"]), unj(case["expected"])
+        assert same(py_port.percentile(vals, case["p"]), exp), case
+        assert same(np_port.percentile(np.array(vals, dtype=np.float64), case["p"]), exp), case
+
+
+def test_percentile_ci_vectors():
+    # .github/workflows/lint-test.yml:119-123
+    data = [10, 20, 30, 40, 50, 60, 70, 80, 90, 100]
+    assert py_port.percentile(data, 0.5) == 55
+    assert py_port.percentile(data, 0.95) == 95.49999999999999
+
+
+def test_histogram_golden(known_answers):
+    for case in known_answers["histogram"]:
+        vals, exp = unj(case["values"]), unj(case["expected"])
+        assert same(py_port.histogram(vals, case["num_bins"]), exp), case["num_bins"]
+        assert same(np_port.histogram(np.array(vals, dtype=np.float64), case["num_bins"]), exp)
+
+
+def test_trapezoid_golden(known_answers):
+    for case in known_answers["trapezoid"]:
+        exp = case["expected"]
+        got = py_port.trapezoid_wh(case["ts"], case["watts"], case["t0"], case["t1"])
+        assert same(got, exp), case
+        w = np.array([np.nan if x is None else x for x in case["watts"]], dtype=np.float64)
+        got_np = np_port.trapezoid_wh(np.array(case["ts"], dtype=np.float64), w, case["t0"], case["t1"])
+        assert same(got_np, exp), case
+
+
+def test_trapezoid_reference_unit_tests():
+    # tests/test_energy.py:4-24 of the reference
+    assert abs(py_port.trapezoid_wh([0.0, 5.0, 10.0], [100.0] * 3, 0.0, 10.0) - 100.0 * 10.0 / 3600.0) < 1e-6
+    wh = py_port.trapezoid_wh([0.0, 5.0, 10.0, 12.0], [None, 100.0, 100.0, None], 0.0, 12.0)
+    assert abs(wh - 100.0 * 5.0 / 3600.0) < 1e-6
+
+
+def test_window_bounds_golden(known_answers):
+    for case in known_answers["window_bounds"]:
+        rows = case["rows"]
+        got = py_port.window_bounds([r["start_ms"] for r in rows], [r["latency_ms"] for r in rows])
+        assert same(list(got), case["expected"])
+
+
+@pytest.mark.parametrize("name,expected,cold", [
+    ("ci5", "expected_results.json", None),
+    ("cfg1", "expected_results_analyze.json", "kube"),
+    ("repro100", "expected_results_analyze.json", None),
+])
+def test_analyze_matches_reference_cli(name, expected, cold):
+    d = os.path.join(GOLDEN, name)
+    exp = load_json(os.path.join(d, expected))
+    log = log_cols(os.path.join(d, "requests.csv"))
+    cold_times = []
+    if cold:
+        # what the reference derived from the fake pod: count is in the fixture, times from pods.json
+        import datetime as dt
+        pods = load_json(os.path.join(d, cold, "pods.json"))
+        for p in pods["items"]:
+            st = p["status"]["containerStatuses"][0]["state"]["running"]["startedAt"]
+            cold_times.append(dt.datetime.fromisoformat(st.replace("Z", "+00:00")).timestamp())
+    got = py_port.analyze(as_lists(log), cold_times)
+    assert diff_keys(got, exp) == []
+    got_np = np_port.analyze(log.cols, cold_times)
+    assert diff_keys(got_np, exp, rel={"time_to_first_token_ms": 1e-15}) == []
+
+
+def test_classification_matches_reference_csv():
+    d = os.path.join(GOLDEN, "cfg1")
+    log = log_cols(os.path.join(d, "requests.csv"))
+    import csv
+    import datetime as dt
+    pods = load_json(os.path.join(d, "kube", "pods.json"))
+    st = pods["items"][0]["status"]["containerStatuses"][0]["state"]["running"]["startedAt"]
+    cold = [dt.datetime.fromisoformat(st.replace("Z", "+00:00")).timestamp()]
+    with open(os.path.join(d, "expected_classified.csv"), newline="") as f:
+        exp = [r["is_cold_start"] == "True" for r in csv.DictReader(f)]
+    assert py_port.classify_cold(log.cols["start_ms"].tolist(), cold) == exp
+    assert np_port.classify_cold(log.cols["start_ms"], cold).tolist() == exp
+
+
+def power_arrays(path):
+    data = load_json(path)
+    ts = [float(s.get("ts_s", s.get("ts", 0))) for s in data["samples"]]
+    w = [None if s.get("watts") is None else float(s["watts"]) for s in data["samples"]]
+    return ts, w
+
+
+@pytest.mark.parametrize("mode,kw", [
+    ("plain", {}), ("series", {"idle_tax": "series"}), ("baseline", {"idle_tax": "baseline"}),
+    ("warmup", {"include_warmup": True}),
+])
+def test_energy_matches_reference_cli(mode, kw):
+    d = os.path.join(GOLDEN, "cfg1")
+    exp = load_json(os.path.join(d, f"expected_energy_{mode}.json"))
+    log = log_cols(os.path.join(d, "requests.csv"))
+    ts, w = power_arrays(os.path.join(d, "power.json"))
+    got = py_port.integrate_energy(as_lists(log), ts, w, **kw)
+    got["samples"] = "power.json"
+    assert diff_keys(got, exp) == []
+
+
+def test_cost_matches_reference_cli():
+    for name in ("cfg1", "repro100"):
+        d = os.path.join(GOLDEN, name)
+        exp = load_json(os.path.join(d, "expected_results_cost.json"))
+        bd = exp["cost_breakdown"]
+        # expected_classified.csv is what cost_estimator.py read (cost_estimator.py:410-412)
+        log = log_cols(os.path.join(d, "expected_classified.csv"))
+        cols = as_lists(log)
+        success = sum(1 for s in cols["status"] if s == 200)
+        tokens = py_port.total_tokens_success(cols)
+        roll = py_port.cost_rollup(bd["gpu_seconds"], bd["cpu_core_seconds"], bd["mem_gib_seconds"],
+                                   bd["gpu_hourly"], bd["cpu_hourly_per_core"], bd["mem_hourly_per_gib"],
+                                   bd["overhead_fraction"], success, tokens)
+        assert same(roll["total_cost"], bd["total_cost"])
+        assert same(roll["cost_per_request"], exp["cost_per_request"])
+        assert same(roll["cost_per_1k_tokens"], exp["cost_per_1k_tokens"])
+        cw = py_port.cold_warm_costs(cols, log.is_cold_csv.tolist(), roll["total_cost"], success)
+        for k, v in cw.items():
+            assert same(v, exp[k]), (name, k, v, exp[k])
+
+
+def test_cost_calculator_matches_reference_cli():
+    d = os.path.join(GOLDEN, "costcalc")
+    lat, status = [], []
+    for line in open(os.path.join(d, "lat.txt")):
+        a, b = line.split()[:2]
+        lat.append(float(a))
+        status.append(b)
+    got = py_port.cost_calculator(lat, status, 1.50, 10)
+    text = open(os.path.join(d, "expected_stdout.txt")).read()
+    assert f"Successful requests: {got['successful']}" in text
+    assert f"Average latency: {got['avg_latency_ms']:.2f}ms ({got['avg_latency_s']:.4f}s)" in text
+    assert f"Cost per 1K tokens: ${got['cost_per_1k_tokens']:.6f}" in text
+    assert py_port.cost_calculator([100.0], ["500"], 1.5) is None
+
+
+# ---- np_port == py_port beyond the fixtures (random logs, incl. cold starts and NaNs)
+@pytest.mark.parametrize("seed,n", [(1, 1), (2, 2), (3, 57), (4, 1000), (5, 5000)])
+def test_np_port_equals_py_port(seed, n):
+    from kvmini_b200 import synth
+    cols = synth.request_columns(n, seed=seed, span_ms=90_000.0)
+    rng = np.random.default_rng(seed)
+    if n > 10:
+        cols["ttfb_ms"][rng.integers(0, n, 3)] = np.nan
+        cols["completion_tokens"][rng.integers(0, n, 3)] = 0
+    t0 = float(cols["start_ms"].min()) / 1000.0
+    cold = [t0 + 5.0, t0 + 50.0] if n > 2 else []
+    a = py_port.analyze({k: v.tolist() for k, v in cols.items()}, cold)
+    b = np_port.analyze(cols, cold)
+    assert diff_keys(b, a, rel={"time_to_first_token_ms": 1e-15}) == []
+    sa = py_port.window_series({k: v.tolist() for k, v in cols.items()})
+    sb = np_port.window_series(cols)
+    assert same(sa, sb)
+
+
+def test_interval_energy_oracles_agree():
+    from kvmini_b200 import synth
+    ts, w = synth.power_trace(20000, hz=100.0, t0_s=1.7e9, null_p=0.01)
+    cols = synth.request_columns(300, seed=9, span_ms=190_000.0, t_epoch_ms=1.7e12 + 2000.0)
+    a = py_port.interval_energy(ts.tolist(), [None if math.isnan(x) else x for x in w.tolist()],
+                                cols["start_ms"].tolist(), cols["latency_ms"].tolist())
+    b = np_port.interval_energy(ts, w, cols["start_ms"], cols["latency_ms"])
+    a = np.array(a)
+    assert np.all(np.abs(a - b) <= 1e-12 * np.maximum(np.abs(a), 1e-300))
+    assert (a > 0).sum() > 200
