@@ -73,9 +73,11 @@ def histogram(values: np.ndarray, num_bins: int = 20) -> Dict[str, Any]:
 
 
 def window_bounds(start_ms: np.ndarray, latency_ms: np.ndarray) -> Tuple[float, float]:
+    """NaN cells are skipped: Python's min()/max() over a list holding NaN is order-dependent
+    (analyze.py:185-188), so that case has no well-defined reference answer."""
     if start_ms.size == 0:
         return (0.0, 0.0)
-    return float(start_ms.min()) / 1000.0, float((start_ms + latency_ms).max()) / 1000.0
+    return float(np.nanmin(start_ms)) / 1000.0, float(np.nanmax(start_ms + latency_ms)) / 1000.0
 
 
 def classify_cold(start_ms: np.ndarray, cold_times: Sequence[float], window: float = 30.0) -> np.ndarray:

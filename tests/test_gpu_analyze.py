@@ -1,0 +1,248 @@
+"""Parity of the CUDA analyze path (through the C ABI / the drop-in functions) against the
+oracle and the reference's golden fixtures.  Counts, ranks, order statistics, histogram
+counts and everything derived from them: bit-exact.  Mean TTFT: <= 1e-12 relative
+(BASELINE.json north_star)."""
+import csv
+import datetime as dt
+import json
+import math
+import os
+import shutil
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from conftest import FAKE_BIN, GOLDEN, REPO, diff_keys, load_json, same, unj
+
+pytestmark = pytest.mark.gpu
+
+MEAN_TOL = {"time_to_first_token_ms": 1e-12}
+
+
+@pytest.fixture(scope="module")
+def api():
+    import analyze
+    return analyze
+
+
+@pytest.fixture(scope="module")
+def analyzer():
+    from kvmini_b200 import engine
+    return engine.LogAnalyzer()
+
+
+def test_native_library_is_loaded():
+    from kvmini_b200 import _native
+    assert _native.lib().kvm_sm_count() >= 100  # B200: 148
+    loaded = open("/proc/self/maps").read()
+    assert "libkvmini_b200.so" in loaded
+
+
+def test_percentile_golden(api, known_answers):
+    for case in known_answers["percentile"]:
+        vals, exp = unj(case["values"]), unj(case["expected"])
+        assert same(api.percentile(vals, case["p"]), exp), (len(vals), case["p"])
+
+
+def test_histogram_golden(api, known_answers):
+    for case in known_answers["histogram"]:
+        vals, exp = unj(case["values"]), unj(case["expected"])
+        assert same(api.compute_histograms(vals, case["num_bins"]), exp), case["num_bins"]
+
+
+def _cold_from_pods(path):
+    out = []
+    for p in load_json(path)["items"]:
+        st = p["status"]["containerStatuses"][0]["state"]["running"]["startedAt"]
+        out.append(dt.datetime.fromisoformat(st.replace("Z", "+00:00")).timestamp())
+    return out
+
+
+@pytest.mark.parametrize("name,expected,kube", [
+    ("ci5", "expected_results.json", None),
+    ("cfg1", "expected_results_analyze.json", "kube"),
+    ("repro100", "expected_results_analyze.json", None),
+])
+def test_analyze_log_matches_reference(name, expected, kube, analyzer):
+    from kvmini_b200 import analyze_api, columns
+    d = os.path.join(GOLDEN, name)
+    exp = load_json(os.path.join(d, expected))
+    log = columns.load_requests_csv(os.path.join(d, "requests.csv"))
+    cold = _cold_from_pods(os.path.join(d, kube, "pods.json")) if kube else []
+    got, _raw = analyze_api.analyze_log(log, cold, analyzer)
+    exp_core = {k: v for k, v in exp.items() if k in got}
+    assert diff_keys(got, exp_core, rel=MEAN_TOL) == []
+
+
+@pytest.mark.parametrize("name,expected,kube", [
+    ("ci5", "expected_results.json", None),
+    ("cfg1", "expected_results_analyze.json", "kube"),
+    ("repro100", "expected_results_analyze.json", None),
+])
+def test_analyze_cli_drop_in(name, expected, kube, tmp_path):
+    """`python analyze.py --run-dir ...` writes the reference's results.json and
+    requests_classified.csv (byte-identical CSV; JSON equal key by key, same order, plus the
+    additive `timeseries` key)."""
+    d = os.path.join(GOLDEN, name)
+    run = tmp_path / "run"
+    run.mkdir()
+    shutil.copy(os.path.join(d, "requests.csv"), run / "requests.csv")
+    env = dict(os.environ)
+    env["PATH"] = FAKE_BIN + os.pathsep + env["PATH"]
+    if kube:
+        env["KVM_FAKE_KUBECTL_DIR"] = os.path.join(d, kube)
+    r = subprocess.run([sys.executable, os.path.join(REPO, "analyze.py"), "--run-dir", str(run),
+                        "--namespace", "ml-prod", "--service", "demo-llm"], env=env,
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    got = load_json(run / "results.json")
+    exp = load_json(os.path.join(d, expected))
+    assert "timeseries" in got
+    ts = got.pop("timeseries")
+    assert sum(ts["requests"]) == exp["requests"]["total"]
+    assert sum(ts["success"]) == exp["requests"]["success"]
+    assert diff_keys(got, exp, rel=MEAN_TOL) == []
+    assert json.loads(r.stdout)["p95_ms"] == exp["p95_ms"] or math.isnan(exp["p95_ms"])
+    assert (run / "requests_classified.csv").read_bytes() == \
+        open(os.path.join(d, "expected_classified.csv"), "rb").read()
+
+
+def test_cli_empty_csv_exits_1(tmp_path):
+    (tmp_path / "requests.csv").write_text("id,start_ms,latency_ms,status\n")
+    r = subprocess.run([sys.executable, os.path.join(REPO, "analyze.py"), "--run-dir", str(tmp_path),
+                        "--namespace", "n", "--service", "s"], capture_output=True, text=True)
+    assert r.returncode == 1 and "No request rows found" in r.stderr
+
+
+def test_cli_success_row_without_ttfb_raises_like_reference(tmp_path):
+    # math.isnan("") -> TypeError
+    (tmp_path / "requests.csv").write_text(
+        "id,start_ms,ttfb_ms,tllt_ms,latency_ms,status,completion_tokens,total_tokens\n"
+        "1,1000.0,,,150.0,200,5,10\n")
+    r = subprocess.run([sys.executable, os.path.join(REPO, "analyze.py"), "--run-dir", str(tmp_path),
+                        "--namespace", "n", "--service", "s"], capture_output=True, text=True)
+    assert r.returncode != 0 and "TypeError: must be real number, not str" in r.stderr
+
+
+def _random_log(n, seed, nan_rows=0, zero_tok_rows=0, span_ms=900_000.0, **kw):
+    from kvmini_b200 import synth
+    cols = synth.request_columns(n, seed=seed, span_ms=span_ms, **kw)
+    rng = np.random.default_rng(seed + 1000)
+    if nan_rows:
+        idx = rng.integers(0, n, nan_rows)
+        cols["ttfb_ms"][idx] = np.nan
+        idx = rng.integers(0, n, nan_rows)
+        cols["tllt_ms"][idx] = np.nan
+        idx = rng.integers(0, n, nan_rows)
+        cols["latency_ms"][idx] = np.nan
+    if zero_tok_rows:
+        cols["completion_tokens"][rng.integers(0, n, zero_tok_rows)] = 0
+    return cols
+
+
+def _check_against_oracle(cols, cold, analyzer):
+    from kvmini_b200 import analyze_api, columns, report
+    from oracle import np_port
+    log = columns.columns_from_arrays(**cols)
+    got, raw = analyze_api.analyze_log(log, cold, analyzer)
+    exp = np_port.analyze(cols, cold)
+    assert diff_keys(got, {k: exp[k] for k in got}, rel=MEAN_TOL) == []
+    # is_cold flags, row by row
+    from kvmini_b200 import _native as N
+    flags = raw.flags.cpu().numpy()
+    assert np.array_equal((flags & N.F_COLD) != 0, np_port.classify_cold(cols["start_ms"], cold))
+    assert np.array_equal((flags & N.F_SUCCESS) != 0, cols["status"] == 200)
+    # extension A12
+    series = report.trim_series(raw)
+    assert same(series, np_port.window_series(cols))
+    return got
+
+
+@pytest.mark.parametrize("n,seed", [(1, 11), (2, 12), (3, 13), (31, 14), (1000, 15), (4097, 16),
+                                    (100_000, 17), (1_000_001, 18)])
+def test_random_logs_vs_oracle(n, seed, analyzer):
+    cols = _random_log(n, seed, nan_rows=n // 50, zero_tok_rows=n // 40)
+    t0 = float(cols["start_ms"].min()) / 1000.0
+    cold = [t0 + 1.0, t0 + 120.0, t0 + 121.0, t0 + 700.0] if n > 3 else []
+    _check_against_oracle(cols, cold, analyzer)
+
+
+def test_all_failures(analyzer):
+    cols = _random_log(5000, 21)
+    cols["status"][:] = 500
+    got = _check_against_oracle(cols, [], analyzer)
+    assert math.isnan(got["p50_ms"]) and got["throughput_rps"] == 0.0 and got["ttft_p50_ms"] is None
+
+
+def test_constant_latency_and_heavy_duplicates(analyzer):
+    cols = _random_log(200_000, 22)
+    cols["latency_ms"][:] = 123.456                      # one distinct key: width 0
+    cols["ttfb_ms"][cols["status"] == 200] = 7.0
+    cols["tllt_ms"][::2] = 30000.0                       # half of the rows share one value
+    _check_against_oracle(cols, [float(cols["start_ms"].min()) / 1000.0 + 3.0], analyzer)
+
+
+def test_negative_and_mixed_sign_values(analyzer):
+    cols = _random_log(50_000, 23)
+    rng = np.random.default_rng(5)
+    cols["tllt_ms"] = np.where(cols["status"] == 200, rng.normal(0.0, 100.0, 50_000), np.nan)  # gen < 0 too
+    _check_against_oracle(cols, [], analyzer)
+
+
+def test_unaligned_columns_take_the_scalar_path(analyzer):
+    """A shard that starts at an odd row has 8-byte- but not 16-byte-aligned columns."""
+    import torch
+    from kvmini_b200 import engine, report
+    from oracle import np_port
+    cols = _random_log(100_001, 24, nan_rows=50)
+    dev = {k: torch.from_numpy(v).cuda() for k, v in cols.items()}
+    sliced = {k: v[1:] for k, v in dev.items()}
+    assert sliced["latency_ms"].data_ptr() % 16 == 8
+    dlog = engine.DeviceLog(cols=sliced, n=100_000, device=sliced["status"].device)
+    raw = analyzer.analyze(dlog, [])
+    got = report.core_results(raw, 0)
+    exp = np_port.analyze({k: v[1:] for k, v in cols.items()}, [])
+    assert diff_keys(got, {k: exp[k] for k in got}, rel=MEAN_TOL) == []
+
+
+def test_many_cold_starts_use_global_table(analyzer):
+    cols = _random_log(20_000, 25, span_ms=3.0e6)
+    t0 = float(cols["start_ms"].min()) / 1000.0
+    cold = [t0 + 2.0 * i for i in range(1500)]           # > shared-memory staging limit
+    _check_against_oracle(cols, cold, analyzer)
+
+
+def test_rank_dialects_match_python(api):
+    """F4: the other percentile dialects of the repo on one column."""
+    import torch
+    from kvmini_b200 import _native as N
+    from kvmini_b200 import engine
+    rng = np.random.default_rng(3)
+    v = np.round(rng.lognormal(5.0, 1.0, 9999), 3)
+    s = sorted(v.tolist())
+    ops = engine.ColumnOps()
+    res = ops.order_stats(torch.from_numpy(v).cuda(), [
+        (1, N.RANK_FLOOR_PN, 0.95, 0), (1, N.RANK_FLOOR_PNM1, 0.95, 0), (1, N.RANK_UPPER_MEDIAN, 0.0, 0),
+        (1, N.RANK_ABSOLUTE, 0.0, 17), (1, N.RANK_FLOOR_PN, 1.0, 0)])
+    n = len(s)
+    assert res[0]["value"] == s[int(0.95 * n)]          # runners/backends/tgi/invoke.sh:208-210
+    assert res[1]["value"] == s[int(0.95 * (n - 1))]    # scripts/fairness_dual_tenant.py:59-65
+    assert res[2]["value"] == s[n // 2]                 # energy/collector.py:333
+    assert res[3]["value"] == s[17]
+    assert res[4]["status"] == N.Q_OUT_OF_RANGE         # sorted(x)[int(1.0*n)] -> IndexError
+
+
+def test_status_member_mode_is_the_16_byte_path(api):
+    import torch
+    from kvmini_b200 import _native as N
+    from kvmini_b200 import engine
+    from oracle import np_port
+    cols = _random_log(300_000, 26)
+    ops = engine.ColumnOps()
+    lat, st = torch.from_numpy(cols["latency_ms"]).cuda(), torch.from_numpy(cols["status"]).cuda()
+    for p in (0.5, 0.95, 0.99):
+        stat = ops.quantile_stat(lat, p, member_mode=N.MEMBER_STATUS, member=st)
+        exp = np_port.percentile(cols["latency_ms"][cols["status"] == 200], p)
+        assert stat.interpolate(p) == exp
