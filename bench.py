@@ -1,0 +1,323 @@
+#!/usr/bin/env python3
+"""bench.py - request-records analysed per second on B200 (BASELINE.json metric).
+
+  python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
+  python bench.py --impl reference --gpus N --steps K ...  # the reference's CPU algorithm
+
+A "step" = one full run analysis of one synthetic request log: K1 scan (window, cold/warm,
+counts, token sums) -> exact select of the 23 quantiles of analyze.py -> four 20-bin
+histograms -> 1 s window series -> results.json fields + the cost-per-1K-token rollup on
+the host.  N=1 workload: BASELINE.json configs[1] (10M-request log).  N>1: the log is
+sharded by time range over the ranks (configs[4] layout, weak scaling, 10M rows per rank
+by default) with exact global quantiles through NCCL histogram all-reduce.
+
+Prints ONE JSON line (rank 0).  See DESIGN.md "Measurement" for how each field is taken.
+"""
+
+import argparse
+import json
+import math
+import os
+import sys
+import threading
+import time
+
+REPO = os.path.dirname(os.path.abspath(__file__))
+if REPO not in sys.path:
+    sys.path.insert(0, REPO)
+
+METRIC = "request_records_analyzed_per_sec"
+UNIT = "records/s"
+ROW_BYTES = 56  # 4 fp64 + 3 int64 columns
+
+
+def measured_peaks():
+    path = os.path.join(REPO, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        try:
+            with open(path) as f:
+                return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """Samples SM clock / throttle reasons during the timed region (pynvml)."""
+
+    def __init__(self, index: int):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._thr = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _run(self):
+        nv = self.nv
+        names = {
+            getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
+        }
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop.wait(0.05)
+
+    def start(self):
+        if self.nv is not None:
+            self._thr = threading.Thread(target=self._run, daemon=True)
+            self._thr.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._thr is not None:
+            self._thr.join(timeout=2)
+        s = sorted(self.samples)
+        return {"sm_mhz": (s[len(s) // 2] if s else None), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(s)}
+
+
+# --------------------------------------------------------------------------- CPU arm
+def cpu_port_rate(cols, cold, rows, repeats=1):
+    """records/s of the pure-Python port of analyze.py (+ cost rollup) on `rows` rows."""
+    from oracle import py_port
+    sub = {k: v[:rows].tolist() for k, v in cols.items()}
+    best = None
+    for _ in range(repeats):
+        t = time.perf_counter()
+        res = py_port.analyze(sub, cold)
+        tokens = py_port.total_tokens_success(sub)
+        py_port.cost_rollup(3600.0, 14400.0, 57600.2, 1.5, 0.04, 0.005, 0.10,
+                            res["requests"]["success"], tokens)
+        dt = time.perf_counter() - t
+        best = dt if best is None else min(best, dt)
+    return rows / best, best
+
+
+def run_reference(args):
+    """--impl reference: the reference's own algorithm (pure-Python port, 1 thread - the
+    reference is single-threaded by construction) on a bounded sample of the same workload."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from kvmini_b200 import synth
+    n = args.rows
+    # calibrate on 20k rows, then size each step for ~120 s total
+    cal_cols = synth.request_columns(20_000, seed=1234)
+    t0 = float(cal_cols["start_ms"].min()) / 1000.0
+    rate, _ = cpu_port_rate(cal_cols, [t0 + 5.0], 20_000)
+    rows = int(min(n, max(10_000, rate * 120.0 / (args.steps + args.warmup))))
+    cols = synth.request_columns(rows, seed=1234, span_ms=3.6e6 * rows / n)
+    t0 = float(cols["start_ms"].min()) / 1000.0
+    cold = [t0 + 5.0]
+    for _ in range(args.warmup):
+        cpu_port_rate(cols, cold, rows)
+    t = time.perf_counter()
+    for _ in range(args.steps):
+        cpu_port_rate(cols, cold, rows)
+    dt = time.perf_counter() - t
+    value = rows * args.steps / dt
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(args, args.gpus),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": 1, "kind": "port",
+                         "sample": f"first {rows} rows of the {n}-row log per step; oracle/py_port.analyze "
+                                   "(pure-Python restatement of analyze.py + cost rollup), single thread"},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def workload_config(args, n_gpus):
+    return {
+        "workload": ("configs[1]: synthetic 10M-request log, full analyze (p50/p95/p99 latency+TTFT, cold/warm, "
+                     "4 histograms, tokens/sec, 1s series) + cost per 1K tokens" if n_gpus == 1 else
+                     "configs[4] layout: log sharded by time range, exact global quantiles via NCCL histogram "
+                     "all-reduce + 1s-window series"),
+        "rows_per_gpu": args.rows, "rows_total": args.rows * n_gpus,
+        "bytes_per_row": ROW_BYTES,
+        "l2": f"inputs ({args.rows * ROW_BYTES / 1e6:.0f} MB per GPU) exceed the 126 MB L2; no flush needed",
+        "parallelism": f"time-range shards x{n_gpus}" if n_gpus > 1 else "single GPU",
+    }
+
+
+# --------------------------------------------------------------------------- our arm
+def run_ours(args):
+    import numpy as np
+    import torch
+
+    from kvmini_b200 import _native as N
+    from kvmini_b200 import columns, engine, report, synth
+    from kvmini_b200 import cost_api
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.gpus > 1 and world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} needs torchrun with {args.gpus} ranks (WORLD_SIZE={world})")
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=device)
+
+    n = args.rows
+    # synthetic shard of this rank: cfg2 distribution, shard r covers hour r of the log
+    host = synth.request_columns(n, seed=1234 + rank, t_epoch_ms=1.7e12 + rank * 3.6e6)
+    log = columns.columns_from_arrays(**host)
+    pinned = {k: torch.from_numpy(v).pin_memory() for k, v in log.cols.items()}
+    resident = {k: v.to(device) for k, v in pinned.items()}
+    t0 = float(host["start_ms"].min()) / 1000.0
+    cold = [1.7e9 + 5.0, 1.7e9 + 1800.0]
+    pricing = cost_api.UnitPricing(1.5, {}, 0.04, 0.005, 0.10, True, False)
+    rsecs = {"gpu_seconds": 3600.0, "cpu_core_seconds": 14400.0, "mem_gib_seconds": 57600.2}
+
+    if world > 1:
+        from kvmini_b200 import dist_api
+        analyzer = dist_api.ShardedAnalyzer(device)
+    else:
+        analyzer = engine.LogAnalyzer(device)
+
+    def step(cols_dev):
+        dlog = engine.DeviceLog.from_tensors(cols_dev)
+        raw = analyzer.analyze(dlog, cold)
+        core = report.core_results(raw, len(cold))
+        cost = cost_api.rollup(raw, pricing, rsecs, 1.5, None)
+        return core, cost, raw
+
+    def e2e_step():
+        dev = {k: v.to(device, non_blocking=True) for k, v in pinned.items()}
+        return step(dev)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize(device)
+
+    # ---- warm-up
+    for _ in range(args.warmup):
+        step(resident)
+    barrier()
+
+    # ---- timed region 1: inputs resident in HBM
+    timer = engine.StageTimer(device)
+    analyzer.timer = timer
+    sampler = ClockSampler(local)
+    sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record()
+    launches = 0
+    for _ in range(args.steps):
+        core, cost, raw = step(resident)
+        launches += analyzer.launches
+    ev1.record()
+    barrier()
+    clocks = sampler.stop()
+    ms_total = ev0.elapsed_time(ev1)
+    stage_ms = timer.totals_ms()
+    analyzer.timer = engine._NoTimer()
+
+    # ---- timed region 2: end to end from pinned host buffers
+    e2e_step()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        core, cost, raw = e2e_step()
+    e1.record()
+    barrier()
+    ms_e2e = e0.elapsed_time(e1)
+
+    if dist is not None:
+        t = torch.tensor([ms_total, ms_e2e], dtype=torch.float64, device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total, ms_e2e = float(t[0]), float(t[1])
+
+    if rank == 0:
+        peak, peak_src = measured_peaks()
+        # algorithmic bytes per launch of each streaming kernel (DESIGN.md "Kernels")
+        alg = {"log_scan": 57.0 * n, "select_hist": 33.0 * n, "select_compact": 33.0 * n,
+               "histograms": 25.0 * n, "series": 17.0 * n}
+        kernels = {}
+        for name, (ms, cnt) in stage_ms.items():
+            avg = ms / cnt
+            k = {"avg_ms": avg, "launches": cnt}
+            if name in alg:
+                k["algorithmic_bytes"] = alg[name]
+                k["achieved_gbs"] = alg[name] / (avg * 1e-3) / 1e9
+                k["frac"] = k["achieved_gbs"] / peak
+            kernels[name] = k
+        dom = max((k for k in kernels if k in alg), key=lambda k: kernels[k]["avg_ms"])
+        d2h = (raw.hist_counts.nbytes + (raw.series.nbytes if raw.series is not None else 0)
+               + 48 * 32 + 312)
+        value = n * world * args.steps / (ms_total * 1e-3)
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": workload_config(args, world),
+            "e2e": {"value": n * world * args.steps / (ms_e2e * 1e-3), "unit": UNIT,
+                    "h2d_bytes_per_step": ROW_BYTES * n, "d2h_bytes_per_step": int(d2h)},
+            "gpu_launches": launches,
+            "clocks": clocks,
+            "roofline": {"bound": "hbm", "kernel": dom, "achieved": kernels[dom]["achieved_gbs"],
+                         "peak": peak, "unit": "GB/s", "frac": kernels[dom]["frac"], "traffic": None,
+                         "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch": kernels[dom]["algorithmic_bytes"]},
+            "kernels": kernels,
+            "effective_gbs_whole_step": ROW_BYTES * n / (ms_total / args.steps * 1e-3) / 1e9,
+            "check": {"p50_ms": core["p50_ms"], "p99_ms": core["p99_ms"],
+                      "cost_per_1k_tokens": cost["cost_per_1k_tokens"]},
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            rows = min(n, 300_000)
+            rate, secs = cpu_port_rate({k: v for k, v in host.items()}, cold, rows)
+            line["cpu_baseline"] = {
+                "value": rate, "unit": UNIT, "cores": 1, "kind": "port",
+                "sample": f"first {rows} of {n} rows, one pass of oracle/py_port.analyze + cost rollup "
+                          f"({secs:.1f} s, single thread: the reference is single-threaded)"}
+        print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--rows", type=int, default=10_000_000, help="rows per GPU")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

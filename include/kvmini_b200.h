@@ -115,10 +115,12 @@ size_t kvm_log_scan_workspace_bytes(void);
 
 /* K1+K7.  One pass over all seven columns.  `cold_times` = sorted cold-start times in
  * seconds (may be NULL when n_cold_times == 0); a row is cold iff some c has
- * c <= start_ms/1000 <= c + cold_window_s.  Writes flags[n] (may be NULL) and *stats. */
+ * c <= start_ms/1000 <= c + cold_window_s.  When `cold_mask` is non-NULL it is a per-row
+ * 0/1 byte array that REPLACES that classification (cost_estimator.py:108-111 reads
+ * `is_cold_start` from requests_classified.csv).  Writes flags[n] (may be NULL) and *stats. */
 int kvm_log_scan(const kvm_request_log* log_host, const double* cold_times, int32_t n_cold_times,
-                 double cold_window_s, uint8_t* flags, kvm_log_stats* stats, void* workspace,
-                 size_t workspace_bytes, void* stream);
+                 double cold_window_s, const uint8_t* cold_mask, uint8_t* flags, kvm_log_stats* stats,
+                 void* workspace, size_t workspace_bytes, void* stream);
 
 /* ------------------------------------------------------------------ exact selection */
 
@@ -201,6 +203,7 @@ int32_t kvm_select_bins(void);
 uint64_t* kvm_select_arena_ptr(void* workspace);  /* candidate keys */
 int64_t* kvm_select_bucket_counts_ptr(void* workspace); /* [KVM_MAX_QUERIES] local counts */
 int64_t* kvm_select_bucket_offsets_ptr(void* workspace); /* [KVM_MAX_QUERIES+1] arena offsets */
+kvm_set_info* kvm_select_info_ptr(void* workspace);      /* set info block inside the workspace */
 
 int kvm_select_plan(const kvm_set_info* info, const kvm_query* queries_host, int32_t nq,
                     void* workspace, size_t workspace_bytes, int64_t arena_capacity, void* stream);

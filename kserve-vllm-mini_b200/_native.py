@@ -78,7 +78,7 @@ def _declare(lib: C.CDLL) -> None:
         "kvm_abi_version": (C.c_int, []),
         "kvm_sm_count": (C.c_int, []),
         "kvm_log_scan_workspace_bytes": (sz, []),
-        "kvm_log_scan": (C.c_int, [P(RequestLogC), vp, i32, f64, vp, vp, vp, sz, vp]),
+        "kvm_log_scan": (C.c_int, [P(RequestLogC), vp, i32, f64, vp, vp, vp, vp, sz, vp]),
         "kvm_select_workspace_bytes": (sz, [i64]),
         "kvm_select_default_arena": (i64, [i64]),
         "kvm_log_select": (C.c_int, [P(RequestLogC), vp, vp, P(QueryC), i32, vp, vp, sz, i64, vp]),

@@ -80,9 +80,10 @@ __device__ __forceinline__ bool is_cold(double t_s, const double* cold, int nc, 
 __device__ __forceinline__ uint8_t process_row(LogAcc& a, double start, double lat, double ttfb,
                                                double tllt, int64_t status, int64_t ctok,
                                                int64_t ttok, const double* cold, int nc,
-                                               double window) {
+                                               double window, int cold_override) {
   const bool ok = status == 200;
-  const bool cold_row = nc > 0 && is_cold(start / 1000.0, cold, nc, window);
+  const bool cold_row = cold_override >= 0 ? cold_override != 0
+                                           : (nc > 0 && is_cold(start / 1000.0, cold, nc, window));
   if (!kvm_isnan(start)) {
     uint64_t ks = kvm_key(start);
     a.kmin[KVM_LOG_NCOLS] = ks < a.kmin[KVM_LOG_NCOLS] ? ks : a.kmin[KVM_LOG_NCOLS];
@@ -136,7 +137,8 @@ __device__ __forceinline__ uint8_t process_row(LogAcc& a, double start, double l
 template <bool VEC>
 __global__ void __launch_bounds__(STATS_THREADS, 2)
 log_scan_kernel(kvm_request_log log, const double* __restrict__ cold_g, int nc, double window,
-                uint8_t* __restrict__ flags, kvm_log_stats* __restrict__ out, StatsWs* ws) {
+                const uint8_t* __restrict__ cold_mask, uint8_t* __restrict__ flags,
+                kvm_log_stats* __restrict__ out, StatsWs* ws) {
   __shared__ double cold_s[COLD_SMEM];
   __shared__ uint64_t red[STATS_WARPS][NSLOTS];
   __shared__ bool is_last;
@@ -164,15 +166,22 @@ log_scan_kernel(kvm_request_log log, const double* __restrict__ cold_g, int nc, 
       const longlong2 ss = kvm_ld2(log.status + i);
       const longlong2 ct = kvm_ld2(log.completion_tokens + i);
       const longlong2 tt = kvm_ld2(log.total_tokens + i);
-      const uint8_t f0 = process_row(a, st.x, la.x, tf.x, tl.x, ss.x, ct.x, tt.x, cold, nc, window);
-      const uint8_t f1 = process_row(a, st.y, la.y, tf.y, tl.y, ss.y, ct.y, tt.y, cold, nc, window);
+      int c0 = -1, c1 = -1;
+      if (cold_mask) {
+        const uint16_t cm = kvm_ld_u8x2(cold_mask + i);
+        c0 = cm & 0xff;
+        c1 = cm >> 8;
+      }
+      const uint8_t f0 = process_row(a, st.x, la.x, tf.x, tl.x, ss.x, ct.x, tt.x, cold, nc, window, c0);
+      const uint8_t f1 = process_row(a, st.y, la.y, tf.y, tl.y, ss.y, ct.y, tt.y, cold, nc, window, c1);
       if (flags) *reinterpret_cast<uint16_t*>(flags + i) = (uint16_t)f0 | ((uint16_t)f1 << 8);
     }
     if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
       const int64_t i = n - 1;
       const uint8_t f = process_row(a, log.start_ms[i], log.latency_ms[i], log.ttfb_ms[i],
                                     log.tllt_ms[i], log.status[i], log.completion_tokens[i],
-                                    log.total_tokens[i], cold, nc, window);
+                                    log.total_tokens[i], cold, nc, window,
+                                    cold_mask ? (int)cold_mask[i] : -1);
       if (flags) flags[i] = f;
     }
   } else {
@@ -181,7 +190,8 @@ log_scan_kernel(kvm_request_log log, const double* __restrict__ cold_g, int nc, 
       const uint8_t f = process_row(a, kvm_ld1(log.start_ms + i), kvm_ld1(log.latency_ms + i),
                                     kvm_ld1(log.ttfb_ms + i), kvm_ld1(log.tllt_ms + i),
                                     kvm_ld1(log.status + i), kvm_ld1(log.completion_tokens + i),
-                                    kvm_ld1(log.total_tokens + i), cold, nc, window);
+                                    kvm_ld1(log.total_tokens + i), cold, nc, window,
+                                    cold_mask ? (int)kvm_ld_u8(cold_mask + i) : -1);
       if (flags) flags[i] = f;
     }
   }
@@ -408,8 +418,9 @@ extern "C" size_t kvm_log_scan_workspace_bytes(void) {
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
 extern "C" int kvm_log_scan(const kvm_request_log* log, const double* cold_times, int32_t n_cold,
-                            double cold_window_s, uint8_t* flags, kvm_log_stats* stats,
-                            void* workspace, size_t workspace_bytes, void* stream) {
+                            double cold_window_s, const uint8_t* cold_mask, uint8_t* flags,
+                            kvm_log_stats* stats, void* workspace, size_t workspace_bytes,
+                            void* stream) {
   KVM_REQUIRE(log && stats && workspace, "kvm_log_scan: null argument");
   KVM_REQUIRE(log->n >= 0 && n_cold >= 0, "kvm_log_scan: negative size");
   KVM_REQUIRE(n_cold == 0 || cold_times, "kvm_log_scan: cold_times is null");
@@ -426,13 +437,14 @@ extern "C" int kvm_log_scan(const kvm_request_log* log, const double* cold_times
   const bool vec = aligned16(log->start_ms) && aligned16(log->latency_ms) &&
                    aligned16(log->ttfb_ms) && aligned16(log->tllt_ms) && aligned16(log->status) &&
                    aligned16(log->completion_tokens) && aligned16(log->total_tokens) &&
-                   (flags == nullptr || (reinterpret_cast<uintptr_t>(flags) & 1u) == 0);
+                   (flags == nullptr || (reinterpret_cast<uintptr_t>(flags) & 1u) == 0) &&
+                   (cold_mask == nullptr || (reinterpret_cast<uintptr_t>(cold_mask) & 1u) == 0);
   if (vec)
     log_scan_kernel<true><<<grid, STATS_THREADS, 0, st>>>(*log, cold_times, n_cold, cold_window_s,
-                                                          flags, stats, ws);
+                                                          cold_mask, flags, stats, ws);
   else
     log_scan_kernel<false><<<grid, STATS_THREADS, 0, st>>>(*log, cold_times, n_cold,
-                                                           cold_window_s, flags, stats, ws);
+                                                           cold_window_s, cold_mask, flags, stats, ws);
   KVM_CUDA_CHECK(cudaGetLastError());
   return KVM_OK;
 }

@@ -143,6 +143,54 @@ RESULT_DTYPE = np.dtype([("value", "<f8"), ("n", "<i8"), ("rank", "<i8"), ("stat
 assert RESULT_DTYPE.itemsize == C.sizeof(N.QueryResultC)
 
 
+# --------------------------------------------------------------------------- stage timing
+class StageTimer:
+    """CUDA-event timing of individual launches on the launching stream (bench.py uses it
+    for the per-kernel roofline).  `with timer.stage("scan"): launch(...)`."""
+
+    def __init__(self, device: torch.device):
+        self.device = device
+        self.events: List[Tuple[str, torch.cuda.Event, torch.cuda.Event]] = []
+
+    class _Ctx:
+        def __init__(self, owner, name):
+            self.owner, self.name = owner, name
+
+        def __enter__(self):
+            self.a = torch.cuda.Event(enable_timing=True)
+            self.b = torch.cuda.Event(enable_timing=True)
+            self.a.record(torch.cuda.current_stream(self.owner.device))
+
+        def __exit__(self, *exc):
+            self.b.record(torch.cuda.current_stream(self.owner.device))
+            self.owner.events.append((self.name, self.a, self.b))
+
+    def stage(self, name: str):
+        return StageTimer._Ctx(self, name)
+
+    def totals_ms(self) -> Dict[str, Tuple[float, int]]:
+        """{stage: (total ms, launches)}; call after a synchronize."""
+        out: Dict[str, Tuple[float, int]] = {}
+        for name, a, b in self.events:
+            t, c = out.get(name, (0.0, 0))
+            out[name] = (t + a.elapsed_time(b), c + 1)
+        return out
+
+
+class _NoTimer:
+    class _Ctx:
+        def __enter__(self):
+            return None
+
+        def __exit__(self, *exc):
+            return None
+
+    _ctx = _Ctx()
+
+    def stage(self, name: str):
+        return self._ctx
+
+
 # --------------------------------------------------------------------------- raw analysis
 @dataclass
 class RawAnalysis:
@@ -185,6 +233,7 @@ class LogAnalyzer:
         self._results_h = torch.zeros(N.KVM_MAX_QUERIES * C.sizeof(N.QueryResultC), dtype=torch.uint8).pin_memory()
         self._empty_cold = torch.zeros(1, dtype=torch.float64, device=self.device)
         self.launches = 0   # kernels launched by the last analyze() (for bench accounting)
+        self.timer = _NoTimer()   # bench.py swaps in a StageTimer
 
     # -- buffers
     def _ensure(self, n: int, arena: Optional[int] = None) -> None:
@@ -195,17 +244,21 @@ class LogAnalyzer:
             self._sel_ws = torch.empty(self.lib.kvm_select_workspace_bytes(cap), dtype=torch.uint8, device=self.device)
             self._sel_cap = cap
 
-    def scan(self, dlog: DeviceLog, cold_times: Sequence[float], cold_window_s: float = 30.0) -> N.LogStatsC:
-        """K1: one pass, returns the stats struct (synchronises)."""
+    def scan(self, dlog: DeviceLog, cold_times: Sequence[float], cold_window_s: float = 30.0,
+             cold_mask: Optional[torch.Tensor] = None) -> N.LogStatsC:
+        """K1: one pass, returns the stats struct (synchronises).  `cold_mask` (uint8 per row)
+        replaces the time-based classification (cost_estimator's is_cold_start column)."""
         self._ensure(dlog.n)
         st = _stream_ptr(self.device)
         cold = sorted(float(c) for c in cold_times)
         cold_d = (torch.tensor(cold, dtype=torch.float64, device=self.device) if cold else self._empty_cold)
         self._cold_d = cold_d
         log_c = dlog.c_struct()
-        N.check(self.lib.kvm_log_scan(C.byref(log_c), cold_d.data_ptr(), len(cold), float(cold_window_s),
-                                      self._flags.data_ptr(), self._stats_d.data_ptr(),
-                                      self._scan_ws.data_ptr(), self._scan_ws.numel(), st), "kvm_log_scan")
+        with self.timer.stage("log_scan"):
+            N.check(self.lib.kvm_log_scan(C.byref(log_c), cold_d.data_ptr(), len(cold), float(cold_window_s),
+                                          cold_mask.data_ptr() if cold_mask is not None else None,
+                                          self._flags.data_ptr(), self._stats_d.data_ptr(),
+                                          self._scan_ws.data_ptr(), self._scan_ws.numel(), st), "kvm_log_scan")
         self.launches += 1
         self._stats_h.copy_(self._stats_d, non_blocking=True)
         torch.cuda.current_stream(self.device).synchronize()
@@ -236,18 +289,30 @@ class LogAnalyzer:
 
         arena = self._sel_cap
         while True:
-            N.check(self.lib.kvm_log_select(C.byref(log_c), self._flags.data_ptr(), self._stats_d.data_ptr(),
-                                            queries, nq, self._results_d.data_ptr(), self._sel_ws.data_ptr(),
-                                            self._sel_ws.numel(), arena, st), "kvm_log_select")
+            ws, fl = self._sel_ws.data_ptr(), self._flags.data_ptr()
+            lib, tm = self.lib, self.timer
+            with tm.stage("select_plan"):
+                N.check(lib.kvm_select_plan(self._stats_d.data_ptr() + N.LogStatsC.sets.offset, queries, nq, ws,
+                                            self._sel_ws.numel(), arena, st), "kvm_select_plan")
+            with tm.stage("select_hist"):
+                N.check(lib.kvm_log_select_hist(C.byref(log_c), fl, ws, st), "kvm_log_select_hist")
+            with tm.stage("select_resolve"):
+                N.check(lib.kvm_select_resolve(ws, st), "kvm_select_resolve")
+            with tm.stage("select_compact"):
+                N.check(lib.kvm_log_select_compact(C.byref(log_c), fl, ws, st), "kvm_log_select_compact")
+            with tm.stage("select_finish"):
+                N.check(lib.kvm_select_finish(ws, None, 0, None, self._results_d.data_ptr(), st), "kvm_select_finish")
             self.launches += 5
-            N.check(self.lib.kvm_log_histograms(C.byref(log_c), self._flags.data_ptr(), self._stats_d.data_ptr(),
-                                                num_bins, hist_d.data_ptr(), self._hist_ws.data_ptr(),
-                                                self._hist_ws.numel(), st), "kvm_log_histograms")
+            with tm.stage("histograms"):
+                N.check(lib.kvm_log_histograms(C.byref(log_c), fl, self._stats_d.data_ptr(),
+                                               num_bins, hist_d.data_ptr(), self._hist_ws.data_ptr(),
+                                               self._hist_ws.numel(), st), "kvm_log_histograms")
             self.launches += 2
             if series_d is not None:
-                N.check(self.lib.kvm_log_series(C.byref(log_c), self._flags.data_ptr(), self._stats_d.data_ptr(),
-                                                float(series_window_s) * 1000.0, nb, series_d.data_ptr(),
-                                                dropped_d.data_ptr(), st), "kvm_log_series")
+                with tm.stage("series"):
+                    N.check(lib.kvm_log_series(C.byref(log_c), fl, self._stats_d.data_ptr(),
+                                               float(series_window_s) * 1000.0, nb, series_d.data_ptr(),
+                                               dropped_d.data_ptr(), st), "kvm_log_series")
                 self.launches += 1
             self._results_h.copy_(self._results_d, non_blocking=True)
             rc = self.lib.kvm_select_status(self._sel_ws.data_ptr(), st)   # synchronises
