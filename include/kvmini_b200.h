@@ -185,6 +185,25 @@ int kvm_column_select(const double* values, int64_t n, int32_t member_mode, cons
                       kvm_query_result* results, void* workspace, size_t workspace_bytes,
                       int64_t arena_capacity, void* stream);
 
+/* No counterpart in the reference.  kvm_column_select for callers that cannot give the
+ * library a workspace because they must not (or cannot) allocate device memory - e.g. a
+ * latency monitor sharing the GPU with an inference server that has claimed the whole HBM
+ * pool, where a cudaMalloc would fail or eat into the server's KV cache.  The scratch is a
+ * fixed array inside the library image (about 8.7 MB per GPU that loads the library, held
+ * until exit), which bounds the input: n <= kvm_column_select_static_max_n() (1,048,576
+ * values), member modes KVM_MEMBER_ALL / KVM_MEMBER_STATUS only; larger or multi-set inputs
+ * are rejected with KVM_ERR_INVALID and a message.  Inputs and `results[nq]` are still the
+ * caller's device buffers.  Calls cudaMalloc / cudaFree never.
+ *  - The first call on each device looks up the scratch's device address (that device must
+ *    be current); make that first call before starting any stream capture.
+ *  - All calls on a device share the one scratch: calls whose GPU work can overlap (two
+ *    streams, two threads) race.  Serialise them or use kvm_column_select.
+ *  - The scratch keeps the previous call's contents; the call clears what it needs. */
+int kvm_column_select_static(const double* values, int64_t n, int32_t member_mode, const void* member,
+                             const kvm_query* queries_host, int32_t nq, kvm_query_result* results,
+                             void* stream);
+int64_t kvm_column_select_static_max_n(void);
+
 /* Reads back the status word of the last select run in `workspace` (synchronises the
  * stream): KVM_OK or KVM_ERR_ARENA. */
 int kvm_select_status(const void* workspace, void* stream);

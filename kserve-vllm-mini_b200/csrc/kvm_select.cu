@@ -745,3 +745,60 @@ extern "C" int kvm_column_select(const double* values, int64_t n, int32_t mode, 
   if ((rc = kvm_column_select_compact(values, n, mode, member, workspace, stream))) return rc;
   return kvm_select_finish(workspace, nullptr, 0, nullptr, results, stream);
 }
+
+// ------------------------------------------------------------------ allocation-free variant
+// kvm_column_select_static: the same select as kvm_column_select, for callers that have no
+// device memory of their own to offer as a workspace.  Typical case: a latency monitor
+// that shares the GPU with an inference server which has already claimed the HBM pool for
+// weights and KV cache - a cudaMalloc from the monitor either fails or takes memory the
+// server counted on - and host processes whose policy forbids runtime allocation once
+// serving has started.  The scratch lives in the array below: it is part of the library
+// image, so every GPU that loads libkvmini_b200.so holds these bytes until the process exits.
+namespace {
+
+constexpr int64_t STATIC_MAX_N = 1 << 20;  // values per call
+constexpr size_t STATIC_SCRATCH_BYTES = WS_HEADER + (size_t)STATIC_MAX_N * sizeof(uint64_t) + 256;
+constexpr int STATIC_MAX_DEVICES = 64;
+
+static __device__ __align__(256) unsigned char g_select_scratch[STATIC_SCRATCH_BYTES];
+
+// In host code `g_select_scratch` is only a handle for the runtime, not an address a
+// kernel can use; the device address is looked up once per device (that device current).
+static void* g_scratch_addr[STATIC_MAX_DEVICES];
+static bool g_scratch_ready[STATIC_MAX_DEVICES];
+
+static int static_scratch_for_current_device(void** out) {
+  int dev = -1;
+  KVM_CUDA_CHECK(cudaGetDevice(&dev));
+  KVM_REQUIRE(dev >= 0 && dev < STATIC_MAX_DEVICES, "kvm_column_select_static: device %d unsupported", dev);
+  if (!g_scratch_ready[dev]) {
+    void* ptr = nullptr;
+    KVM_CUDA_CHECK(cudaGetSymbolAddress(&ptr, g_select_scratch));
+    g_scratch_addr[dev] = ptr;
+    g_scratch_ready[dev] = true;
+  }
+  *out = g_scratch_addr[dev];
+  return KVM_OK;
+}
+
+}  // namespace
+
+extern "C" int64_t kvm_column_select_static_max_n(void) { return STATIC_MAX_N; }
+
+extern "C" int kvm_column_select_static(const double* values, int64_t n, int32_t mode,
+                                        const void* member, const kvm_query* queries, int32_t nq,
+                                        kvm_query_result* results, void* stream) {
+  KVM_REQUIRE(mode == KVM_MEMBER_ALL || mode == KVM_MEMBER_STATUS,
+              "kvm_column_select_static: member mode %d not supported (only ALL and STATUS: one set, "
+              "so the candidates of all queries together never exceed n)", mode);
+  KVM_REQUIRE(n >= 0 && n <= STATIC_MAX_N,
+              "kvm_column_select_static: n=%lld exceeds the built-in scratch (max %lld values); use "
+              "kvm_column_select with a caller-provided workspace", (long long)n, (long long)STATIC_MAX_N);
+  void* scratch = nullptr;
+  int rc = static_scratch_for_current_device(&scratch);
+  if (rc) return rc;
+  // Everything that must start from zero is cleared inside the pipeline itself (stats
+  // ticket, histograms, append cursors), so stale contents of the previous call are harmless.
+  return kvm_column_select(values, n, mode, member, 1, queries, nq, results, scratch,
+                           STATIC_SCRATCH_BYTES, STATIC_MAX_N, stream);
+}
