@@ -263,6 +263,57 @@ int kvm_log_series(const kvm_request_log* log_host, const uint8_t* flags,
                    const kvm_log_stats* stats, double window_ms, int64_t max_bins, int64_t* series,
                    int64_t* dropped, void* stream);
 
+/* ------------------------------------------------------------------ sort */
+
+/* K3: stable ascending sort of (key, payload) fp64 pairs by key (LSD radix, 8-bit digits).
+ * Replaces `ss.sort(key=lambda s: s.ts)` of energy/collector.py:141 for traces that arrive
+ * out of order.  Synchronises the stream once (constant digits are skipped).  Out-of-place. */
+size_t kvm_sort_pairs_workspace_bytes(int64_t m);
+int kvm_sort_pairs_f64(const double* keys_in, const double* vals_in, double* keys_out,
+                       double* vals_out, int64_t m, void* workspace, size_t workspace_bytes,
+                       void* stream);
+
+/* ------------------------------------------------------------------ energy */
+
+/* Whole-trace facts integrate_energy needs (energy/collector.py:296-347). */
+typedef struct kvm_power_stats {
+  int64_t m;
+  int64_t n_valid;         /* samples with non-null watts */
+  int64_t n_outside;       /* ts < t0 or ts > t1, nulls included   (collector.py:345) */
+  int64_t n_outside_valid; /* of those, non-null                   (collector.py:327-331) */
+  int64_t n_unsorted;      /* #i with ts[i+1] < ts[i]; 0 = already ascending */
+  double ts_min, ts_max;   /* over all samples                     (collector.py:299-300,313-314) */
+  double step_sum_hi;      /* double-double sum of ts[i+1]-ts[i] in load order (collector.py:338-341) */
+  double step_sum_lo;
+} kvm_power_stats;
+
+size_t kvm_energy_workspace_bytes(int64_t m);
+
+/* One pass over (ts, watts).  outside_ids (may be NULL) receives 0 for non-null samples
+ * outside [t0,t1] and 255 otherwise - the set-id array kvm_column_select ranks for the
+ * upper-median idle power (collector.py:333). */
+int kvm_power_scan(const double* ts, const double* watts, int64_t m, double t0, double t1,
+                   uint8_t* outside_ids, kvm_power_stats* stats, void* workspace,
+                   size_t workspace_bytes, void* stream);
+
+/* K9: trapezoidal Wh over up to 8 windows in one pass; ts ascending.  windows_host = k pairs
+ * (t0,t1) on the host; out_dd[k][2] = double-double (hi,lo) on the device.
+ * Replaces trapezoidal_wh, energy/collector.py:133-149. */
+int kvm_trapezoid_wh(const double* ts, const double* watts, int64_t m, const double* windows_host,
+                     int32_t k, double* out_dd, void* workspace, size_t workspace_bytes, void* stream);
+
+/* K10 (extension A16): inclusive double-double prefix of the segment energies of a trace,
+ * then per request interval [start_ms, start_ms+latency_ms]/1000 the trapezoidal energy of
+ * the samples inside it (membership clip, like trapezoidal_wh).  accumulate != 0 adds to
+ * energy_wh[] (several GPU traces are summed in call order - PromQL `sum(...)`,
+ * collector.py:45). */
+int kvm_energy_prefix(const double* ts, const double* watts, int64_t m, double* p_hi, double* p_lo,
+                      void* workspace, size_t workspace_bytes, void* stream);
+int kvm_interval_energy(const double* ts, const double* watts, const double* p_hi,
+                        const double* p_lo, int64_t m, const double* start_ms,
+                        const double* latency_ms, int64_t n, double* energy_wh, int32_t accumulate,
+                        void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -57,6 +57,12 @@ class LogStatsC(C.Structure):
                 ("lat_sum_hi", C.c_double), ("lat_sum_lo", C.c_double), ("sets", SetInfoC)]
 
 
+class PowerStatsC(C.Structure):
+    _fields_ = [("m", C.c_int64), ("n_valid", C.c_int64), ("n_outside", C.c_int64),
+                ("n_outside_valid", C.c_int64), ("n_unsorted", C.c_int64), ("ts_min", C.c_double),
+                ("ts_max", C.c_double), ("step_sum_hi", C.c_double), ("step_sum_lo", C.c_double)]
+
+
 class QueryC(C.Structure):
     _fields_ = [("set_mask", C.c_uint32), ("rank_kind", C.c_int32), ("p", C.c_double),
                 ("rank", C.c_int64)]
@@ -104,6 +110,13 @@ def _declare(lib: C.CDLL) -> None:
         "kvm_log_histograms": (C.c_int, [P(RequestLogC), vp, vp, i32, vp, vp, sz, vp]),
         "kvm_column_histogram": (C.c_int, [vp, i64, f64, f64, i32, vp, vp, sz, vp]),
         "kvm_log_series": (C.c_int, [P(RequestLogC), vp, vp, f64, i64, vp, vp, vp]),
+        "kvm_sort_pairs_workspace_bytes": (sz, [i64]),
+        "kvm_sort_pairs_f64": (C.c_int, [vp, vp, vp, vp, i64, vp, sz, vp]),
+        "kvm_energy_workspace_bytes": (sz, [i64]),
+        "kvm_power_scan": (C.c_int, [vp, vp, i64, f64, f64, vp, vp, vp, sz, vp]),
+        "kvm_trapezoid_wh": (C.c_int, [vp, vp, i64, P(f64), i32, vp, vp, sz, vp]),
+        "kvm_energy_prefix": (C.c_int, [vp, vp, i64, vp, vp, vp, sz, vp]),
+        "kvm_interval_energy": (C.c_int, [vp, vp, vp, vp, i64, vp, vp, i64, vp, i32, vp]),
     }
     for name, (res, args) in sigs.items():
         fn = getattr(lib, name)
