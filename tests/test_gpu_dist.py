@@ -1,0 +1,23 @@
+"""Sharded (multi-GPU) analysis equals whole-log analysis; needs >= 2 GPUs on the box."""
+import os
+import subprocess
+import sys
+
+import pytest
+
+from conftest import REPO
+
+pytestmark = pytest.mark.gpu
+
+
+def test_sharded_equals_whole_log():
+    import torch
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs at least 2 GPUs")
+    world = 2 if n < 4 else 4
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+                        "--master-addr", "127.0.0.1", "--master-port", "29533",
+                        os.path.join(REPO, "tests", "dist_gpu_check.py"), "400000"],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "DIST_CHECK OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
