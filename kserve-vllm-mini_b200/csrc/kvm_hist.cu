@@ -15,6 +15,7 @@
 // and lanes that hit the same bin are merged with __match_any_sync before the atomic.
 
 #include "kvm_common.cuh"
+#include "kvm_log_device.cuh"
 
 namespace {
 
@@ -27,32 +28,12 @@ struct HistPlan {
   int32_t active[LOG_NHIST];          // 0: empty or min==max (host resolves from stats)
 };
 
-__device__ __forceinline__ int ref_bin(double v, double lo, double w, int nb) {
-  // analyze.py:110 - same operations, same order
-  const double x = (v - lo) / w;
-  long long i = (long long)x;  // int() truncates toward zero
-  return (int)(i < (long long)(nb - 1) ? i : (long long)(nb - 1));
-}
-
 // thr for one histogram: thread b-1 bisects for bin b
 __device__ void plan_thresholds(uint64_t klo, uint64_t khi, int nb, uint64_t* thr, int32_t* active) {
   const bool ok = klo < khi;
   if (threadIdx.x == 0) *active = ok ? 1 : 0;
   if (!ok) return;
-  const double lo = kvm_unkey(klo), hi = kvm_unkey(khi);
-  const double w = (hi - lo) / (double)nb;  // analyze.py:104
-  for (int b = 1 + threadIdx.x; b < nb; b += blockDim.x) {
-    uint64_t a = klo, z = khi;  // f(a) < b <= f(z)
-    if (ref_bin(hi, lo, w, nb) < b) {
-      thr[b - 1] = ~0ull;  // no key reaches bin b
-      continue;
-    }
-    while (z - a > 1) {
-      const uint64_t mid = a + ((z - a) >> 1);
-      if (ref_bin(kvm_unkey(mid), lo, w, nb) >= b) z = mid; else a = mid;
-    }
-    thr[b - 1] = z;
-  }
+  for (int b = 1 + threadIdx.x; b < nb; b += blockDim.x) thr[b - 1] = bin_threshold(klo, khi, nb, b);
 }
 
 __global__ void log_hist_plan_kernel(const kvm_log_stats* stats, int nb, HistPlan* plan) {
@@ -63,16 +44,6 @@ __global__ void log_hist_plan_kernel(const kvm_log_stats* stats, int nb, HistPla
 
 __global__ void column_hist_plan_kernel(double lo, double hi, int nb, HistPlan* plan) {
   plan_thresholds(kvm_key(lo), kvm_key(hi), nb, plan->thr[0], &plan->active[0]);
-}
-
-__device__ __forceinline__ int bin_of(uint64_t key, const uint64_t* thr, int nb) {
-  // number of thresholds <= key  (thr non-decreasing, nb-1 entries)
-  int lo = 0, hi = nb - 1;
-  while (lo < hi) {
-    const int mid = (lo + hi) >> 1;
-    if (thr[mid] <= key) lo = mid + 1; else hi = mid;
-  }
-  return lo;
 }
 
 // Warp-merged shared-memory increment; bin < 0 = lane has nothing to add.  Must be

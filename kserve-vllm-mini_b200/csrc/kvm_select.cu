@@ -22,11 +22,10 @@
 // stages; every rank then resolves / finishes identically.
 
 #include "kvm_common.cuh"
+#include "kvm_log_device.cuh"
 
 namespace {
 
-constexpr int BINS_LOG2 = 11;
-constexpr int BINS = 1 << BINS_LOG2;
 constexpr int SEL_THREADS = 512;
 constexpr int MAXQ = KVM_MAX_QUERIES;
 constexpr int MAX_SRC = 16;
@@ -90,24 +89,6 @@ struct SrcPack {
 };
 
 // ------------------------------------------------------------------ plan
-__device__ __forceinline__ int64_t resolve_rank(int kind, double p, int64_t n, int64_t given) {
-  switch (kind) {
-    case KVM_RANK_LERP_LO: {  // analyze.py:75-76
-      double pos = fmax(0.0, fmin(p, 1.0)) * (double)(n - 1);
-      return (int64_t)floor(pos);
-    }
-    case KVM_RANK_LERP_HI: {  // analyze.py:77
-      double pos = fmax(0.0, fmin(p, 1.0)) * (double)(n - 1);
-      return (int64_t)ceil(pos);
-    }
-    case KVM_RANK_ABSOLUTE: return given;
-    case KVM_RANK_UPPER_MEDIAN: return n / 2;               // collector.py:333
-    case KVM_RANK_FLOOR_PN: return (int64_t)(p * (double)n);  // tgi/invoke.sh:208-210
-    case KVM_RANK_FLOOR_PNM1: return (int64_t)(p * (double)(n - 1));
-  }
-  return -1;
-}
-
 __global__ void select_plan_kernel(SelWs* ws, const kvm_set_info* info_in, QueryPack qp,
                                    int64_t arena_capacity) {
   __shared__ kvm_set_info info;
@@ -162,30 +143,6 @@ struct ColParams {
   uint64_t kbase[KVM_MAX_COLS];
   int32_t shift[KVM_MAX_COLS];
 };
-
-__device__ __forceinline__ uint32_t digit_of(uint64_t key, uint64_t kbase, int shift) {
-  uint64_t d = (key - kbase) >> shift;
-  return d < (uint64_t)BINS ? (uint32_t)d : (uint32_t)(BINS - 1);
-}
-
-// Calls f(set, col, key) for every base set the row belongs to (KVM_SET_* semantics).
-template <class F>
-__device__ __forceinline__ void log_row_keys(uint8_t fl, double lat, double ttfb, double tllt,
-                                             int64_t ctok, F&& f) {
-  if (!(fl & KVM_F_SUCCESS)) return;
-  const bool cold = fl & KVM_F_COLD;
-  if (!kvm_isnan(lat)) f(cold ? KVM_SET_LAT_COLD : KVM_SET_LAT_WARM, KVM_COL_LAT, kvm_key(lat));
-  if (!kvm_isnan(ttfb)) f(cold ? KVM_SET_TTFB_COLD : KVM_SET_TTFB_WARM, KVM_COL_TTFB, kvm_key(ttfb));
-  if (!kvm_isnan(tllt)) f(KVM_SET_TLLT, KVM_COL_TLLT, kvm_key(tllt));
-  if (fl & KVM_F_GEN) {
-    const double g = tllt - ttfb;  // analyze.py:144
-    if (!kvm_isnan(g)) {
-      f(KVM_SET_GEN, KVM_COL_GEN, kvm_key(g));
-      const double pt = g / (double)ctok;  // analyze.py:146
-      if (!kvm_isnan(pt)) f(KVM_SET_PERTOK, KVM_COL_PERTOK, kvm_key(pt));
-    }
-  }
-}
 
 // Streams the log two rows per thread (128-bit loads) and hands every (set,col,key) to f.
 template <class F>

@@ -14,6 +14,7 @@
 // with one 128-bit load per thread; a warp reads 512 contiguous bytes per column.
 
 #include "kvm_common.cuh"
+#include "kvm_log_device.cuh"
 
 namespace {
 
@@ -21,118 +22,11 @@ constexpr int STATS_THREADS = 256;
 constexpr int STATS_WARPS = STATS_THREADS / 32;
 constexpr int COLD_SMEM = 1024;  // cold-start times staged in shared memory
 
-// 64-bit slots of one partial.  [0,NSUM) summed, [NSUM,NSUM+NMIN) min, then max, then dd pairs.
-enum {
-  S_SUCCESS = 0, S_COLD, S_COLD_SUCCESS, S_CTOK, S_TTOK, S_TTOK_COLD, S_GEN_ROWS,
-  S_CNT0,                      // 7 set counts
-  NSUM = S_CNT0 + KVM_LOG_NSETS,
-  M_KMIN0 = NSUM,              // 5 column minima + start
-  M_START = M_KMIN0 + KVM_LOG_NCOLS,
-  NMIN_END = M_START + 1,
-  X_KMAX0 = NMIN_END,          // 5 column maxima + end
-  X_END = X_KMAX0 + KVM_LOG_NCOLS,
-  NMAX_END = X_END + 1,
-  D_TTFB = NMAX_END,           // dd pairs (hi, lo)
-  D_LAT = D_TTFB + 2,
-  NSLOTS = D_LAT + 2
-};
-
 struct StatsWs {
   unsigned int ticket;
   unsigned int pad[63];
   uint64_t partial[1];  // [grid][NSLOTS]
 };
-
-struct LogAcc {
-  int64_t sum[NSUM];
-  uint64_t kmin[KVM_LOG_NCOLS + 1];
-  uint64_t kmax[KVM_LOG_NCOLS + 1];
-  kvm_dd ttfb, lat;
-
-  __device__ __forceinline__ void init() {
-#pragma unroll
-    for (int i = 0; i < NSUM; ++i) sum[i] = 0;
-#pragma unroll
-    for (int i = 0; i <= KVM_LOG_NCOLS; ++i) {
-      kmin[i] = ~0ull;
-      kmax[i] = 0ull;
-    }
-    ttfb = {0.0, 0.0};
-    lat = {0.0, 0.0};
-  }
-  __device__ __forceinline__ void range(int c, double v) {
-    uint64_t k = kvm_key(v);
-    kmin[c] = k < kmin[c] ? k : kmin[c];
-    kmax[c] = k > kmax[c] ? k : kmax[c];
-  }
-};
-
-__device__ __forceinline__ bool is_cold(double t_s, const double* cold, int nc, double window) {
-  // largest c <= t decides (c + window is monotone in c)
-  int lo = 0, hi = nc;
-  while (lo < hi) {
-    int mid = (lo + hi) >> 1;
-    if (cold[mid] <= t_s) lo = mid + 1; else hi = mid;
-  }
-  return lo > 0 && t_s <= cold[lo - 1] + window;
-}
-
-__device__ __forceinline__ uint8_t process_row(LogAcc& a, double start, double lat, double ttfb,
-                                               double tllt, int64_t status, int64_t ctok,
-                                               int64_t ttok, const double* cold, int nc,
-                                               double window, int cold_override) {
-  const bool ok = status == 200;
-  const bool cold_row = cold_override >= 0 ? cold_override != 0
-                                           : (nc > 0 && is_cold(start / 1000.0, cold, nc, window));
-  if (!kvm_isnan(start)) {
-    uint64_t ks = kvm_key(start);
-    a.kmin[KVM_LOG_NCOLS] = ks < a.kmin[KVM_LOG_NCOLS] ? ks : a.kmin[KVM_LOG_NCOLS];
-  }
-  const double end = start + lat;
-  if (!kvm_isnan(end)) {
-    uint64_t ke = kvm_key(end);
-    a.kmax[KVM_LOG_NCOLS] = ke > a.kmax[KVM_LOG_NCOLS] ? ke : a.kmax[KVM_LOG_NCOLS];
-  }
-  a.sum[S_COLD] += cold_row;
-  uint8_t f = (ok ? KVM_F_SUCCESS : 0) | (cold_row ? KVM_F_COLD : 0) | (ctok > 0 ? KVM_F_TOKENS : 0);
-  if (ok) {
-    a.sum[S_SUCCESS] += 1;
-    a.sum[S_COLD_SUCCESS] += cold_row;
-    a.sum[S_CTOK] += ctok;
-    a.sum[S_TTOK] += ttok;
-    a.sum[S_TTOK_COLD] += cold_row ? ttok : 0;
-    if (!kvm_isnan(lat)) {
-      a.sum[S_CNT0 + (cold_row ? KVM_SET_LAT_COLD : KVM_SET_LAT_WARM)] += 1;
-      a.range(KVM_COL_LAT, lat);
-      a.lat = kvm_dd_add(a.lat, lat);
-    }
-    const bool has_ttfb = !kvm_isnan(ttfb), has_tllt = !kvm_isnan(tllt);
-    if (has_ttfb) {
-      a.sum[S_CNT0 + (cold_row ? KVM_SET_TTFB_COLD : KVM_SET_TTFB_WARM)] += 1;
-      a.range(KVM_COL_TTFB, ttfb);
-      a.ttfb = kvm_dd_add(a.ttfb, ttfb);
-    }
-    if (has_tllt) {
-      a.sum[S_CNT0 + KVM_SET_TLLT] += 1;
-      a.range(KVM_COL_TLLT, tllt);
-    }
-    if (has_ttfb && has_tllt && ctok > 0) {
-      f |= KVM_F_GEN;
-      a.sum[S_GEN_ROWS] += 1;
-      const double g = tllt - ttfb;  // analyze.py:144
-      if (!kvm_isnan(g)) {
-        a.sum[S_CNT0 + KVM_SET_GEN] += 1;
-        a.range(KVM_COL_GEN, g);
-        const double pt = g / (double)ctok;  // analyze.py:146
-        if (!kvm_isnan(pt)) {
-          a.sum[S_CNT0 + KVM_SET_PERTOK] += 1;
-          a.range(KVM_COL_PERTOK, pt);
-        }
-      }
-    }
-  }
-  return f;
-}
 
 template <bool VEC>
 __global__ void __launch_bounds__(STATS_THREADS, 2)

@@ -1,0 +1,97 @@
+"""Sweep roll-up: analyse many runs stored back to back in one launch (BASELINE.json
+configs[2]: 4096 runs x 250k requests).
+
+The reference does this with one `analyze.py` process per run (grid-sweep.sh:103-174 ->
+bench.sh:263) and then pulls 11 keys out of each results.json (grid-sweep.sh:136-161).
+Here the runs are CSR segments of one columnar log; `kvm_seg_analyze` gives every run to one
+persistent CTA.  Runs whose candidate set does not fit on chip are redone through the flat
+path, so every run's result equals `analyze_api.analyze_log` on that run alone.
+Runs are independent, so multi-GPU = whole runs per GPU and no collective.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+from typing import Any, Dict, List, Optional, Sequence
+
+import numpy as np
+import torch
+
+from . import _native as N
+from . import engine, report
+
+# the keys grid-sweep.sh copies into its CSV row (grid-sweep.sh:137-160)
+SWEEP_KEYS = ("p50_ms", "p95_ms", "p99_ms", "throughput_rps", "tokens_per_sec", "error_rate",
+              "ttft_p50_ms", "ttft_p95_ms", "cost_per_request", "cost_per_1k_tokens", "gpu_util_avg")
+
+
+class SweepAnalyzer:
+    def __init__(self, device: Optional[torch.device] = None):
+        self.device = device or engine.require_cuda()
+        self.lib = N.lib()
+        self._flat: Optional[engine.LogAnalyzer] = None
+        self.fallback_runs = 0
+
+    def analyze(self, dlog: engine.DeviceLog, run_offsets: Sequence[int],
+                cold_times: Optional[Sequence[Sequence[float]]] = None, num_bins: int = 20,
+                quantiles: Sequence[engine.Quantile] = engine.ANALYZE_QUANTILES) -> List[engine.RawAnalysis]:
+        """One RawAnalysis per run (series not computed in sweep mode)."""
+        dev, lib = self.device, self.lib
+        offs = np.ascontiguousarray(run_offsets, dtype=np.int64)
+        runs = int(offs.shape[0]) - 1
+        assert runs >= 0 and int(offs[-1]) == dlog.n and int(offs[0]) == 0
+        offs_d = torch.from_numpy(offs).to(dev)
+        cold_off_d = cold_d = None
+        if cold_times is not None:
+            lens = [len(c) for c in cold_times]
+            co = np.zeros(runs + 1, dtype=np.int64)
+            np.cumsum(lens, out=co[1:])
+            flat = np.array([t for c in cold_times for t in sorted(c)], dtype=np.float64)
+            cold_off_d = torch.from_numpy(co).to(dev)
+            cold_d = torch.from_numpy(flat if flat.size else np.zeros(1)).to(dev)
+        queries = engine.build_queries(quantiles)
+        nq = len(queries)
+        flags = torch.empty(dlog.n + 2, dtype=torch.uint8, device=dev)
+        stats_d = torch.zeros(max(runs, 1) * C.sizeof(N.LogStatsC), dtype=torch.uint8, device=dev)
+        res_d = torch.zeros(max(runs, 1) * nq * C.sizeof(N.QueryResultC), dtype=torch.uint8, device=dev)
+        hist_d = torch.zeros((max(runs, 1), 4, num_bins), dtype=torch.int64, device=dev)
+        status_d = torch.zeros(max(runs, 1), dtype=torch.int32, device=dev)
+        log_c = dlog.c_struct()
+        N.check(lib.kvm_seg_analyze(C.byref(log_c), offs_d.data_ptr(), runs,
+                                    cold_off_d.data_ptr() if cold_off_d is not None else None,
+                                    cold_d.data_ptr() if cold_d is not None else None, 30.0,
+                                    queries, nq, num_bins, flags.data_ptr(), stats_d.data_ptr(),
+                                    res_d.data_ptr(), hist_d.data_ptr(), status_d.data_ptr(),
+                                    engine._stream_ptr(dev)), "kvm_seg_analyze")
+        self._last = (flags, stats_d, res_d, hist_d, status_d)
+        stats_b = stats_d.cpu().numpy().tobytes()
+        res = np.frombuffer(res_d.cpu().numpy().tobytes(), dtype=engine.RESULT_DTYPE).reshape(max(runs, 1), nq)
+        hist = hist_d.cpu().numpy()
+        status = status_d.cpu().numpy()
+        out: List[engine.RawAnalysis] = []
+        ssz = C.sizeof(N.LogStatsC)
+        self.fallback_runs = 0
+        for r in range(runs):
+            if status[r] != 0:
+                out.append(self._flat_run(dlog, int(offs[r]), int(offs[r + 1]),
+                                          cold_times[r] if cold_times is not None else (), num_bins, quantiles))
+                self.fallback_runs += 1
+                continue
+            st = N.LogStatsC.from_buffer_copy(stats_b[r * ssz:(r + 1) * ssz])
+            out.append(engine.RawAnalysis(stats=st, order=engine.results_to_orderstats(res[r], quantiles),
+                                          hist_counts=hist[r], num_bins=num_bins, series=None,
+                                          flags=flags[int(offs[r]):int(offs[r + 1])]))
+        return out
+
+    def _flat_run(self, dlog, r0, r1, cold, num_bins, quantiles) -> engine.RawAnalysis:
+        if self._flat is None:
+            self._flat = engine.LogAnalyzer(self.device)
+        sub = engine.DeviceLog(cols={k: v[r0:r1] for k, v in dlog.cols.items()}, n=r1 - r0, device=self.device)
+        return self._flat.analyze(sub, cold, num_bins=num_bins, series_window_s=None, quantiles=quantiles)
+
+    def rollup(self, dlog: engine.DeviceLog, run_offsets: Sequence[int],
+               cold_times: Optional[Sequence[Sequence[float]]] = None) -> List[Dict[str, Any]]:
+        """results.json core per run."""
+        raws = self.analyze(dlog, run_offsets, cold_times)
+        return [report.core_results(raw, len(cold_times[i]) if cold_times is not None else 0)
+                for i, raw in enumerate(raws)]
