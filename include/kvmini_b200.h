@@ -155,6 +155,30 @@ typedef struct kvm_query_result {
   int32_t pad;
 } kvm_query_result;
 
+/* Value histograms produced as a by-product of a select problem (K5 folded into K2): up to
+ * KVM_MAX_HISTS histograms of num_bins (<= KVM_HIST_MAX_BINS) uniform bins each, over one value
+ * column and a union of its base sets; bin index = min(nb-1, int((v-min)/w)), w=(max-min)/nb,
+ * exactly as analyze.py:104-111 (min/max = the column's range in kvm_set_info). */
+#define KVM_MAX_HISTS 4
+#define KVM_HIST_MAX_BINS 64
+typedef struct kvm_hist_spec {
+  int32_t nhist;
+  int32_t num_bins;
+  int32_t col[KVM_MAX_HISTS];
+  uint32_t set_mask[KVM_MAX_HISTS];
+} kvm_hist_spec;
+
+/* Optional by-products of kvm_log_select (all device pointers; zero / NULL = not wanted). */
+typedef struct kvm_log_extras {
+  int32_t num_bins;        /* > 0: the four histograms of analyze.py:149-152 (ttfb, tllt, generation, per-token) */
+  int32_t pad;
+  int64_t* hist_counts;    /* [4][num_bins] */
+  double series_window_ms; /* > 0: extension A12 window series, binned in the histogram pass */
+  int64_t series_max_bins;
+  int64_t* series;         /* [3][series_max_bins]: requests, successes, completion tokens */
+  int64_t* series_dropped; /* [1]: rows whose window index >= series_max_bins */
+} kvm_log_extras;
+
 /* Workspace for a select problem whose candidate arena holds `arena_capacity` keys.
  * kvm_select_default_arena(n) is a size that fits unless the data is pathologically
  * concentrated; on overflow the select returns KVM_ERR_ARENA in the status word and
@@ -163,15 +187,17 @@ size_t kvm_select_workspace_bytes(int64_t arena_capacity);
 int64_t kvm_select_default_arena(int64_t n);
 #define KVM_ERR_ARENA (-4) /* candidate arena too small: retry with a larger one */
 
-/* Fused multi-rank exact select over the request log (K2+K6).  Replaces the 25
- * `percentile()` calls of one analyze.py run (analyze.py:59-81, call sites :159-176,
- * :447-451, :574-583).  `stats` is the device struct kvm_log_scan wrote, `flags` its
- * flag bytes.  Stream-ordered; results[nq] land in device memory.  After the stream
- * is synchronised, kvm_select_status(workspace) tells whether the arena overflowed. */
+/* Fused multi-rank exact select over the request log (K2+K6, with K5 and K8 riding on the
+ * same two passes when `extras` asks for them).  Replaces the 25 `percentile()` calls of one
+ * analyze.py run (analyze.py:59-81, call sites :159-176, :447-451, :574-583) and its four
+ * compute_histograms calls (:149-152).  `stats` is the DEVICE struct kvm_log_scan wrote,
+ * `flags` its flag bytes; `extras` is a host struct (may be NULL).  Stream-ordered;
+ * results[nq] land in device memory.  After the stream is synchronised,
+ * kvm_select_status(workspace) tells whether the arena overflowed. */
 int kvm_log_select(const kvm_request_log* log_host, const uint8_t* flags,
                    const kvm_log_stats* stats, const kvm_query* queries_host, int32_t nq,
-                   kvm_query_result* results, void* workspace, size_t workspace_bytes,
-                   int64_t arena_capacity, void* stream);
+                   kvm_query_result* results, const kvm_log_extras* extras_host, void* workspace,
+                   size_t workspace_bytes, int64_t arena_capacity, void* stream);
 
 /* Generic single-column variant.  Set membership of element i:
  *   mode 0: every element is in set 0
@@ -211,13 +237,15 @@ int kvm_select_status(const void* workspace, void* stream);
 /* ---- staged form of the same select, for multi-GPU runs where the host all-reduces
  * between the stages.  Stage order:
  *   column_stats -> [allreduce set_info: counts sum, kmin min, kmax max] -> plan ->
- *   hist -> [allreduce hist: sum] -> resolve -> compact -> [allgather arena+counts] -> finish
+ *   hist -> [allreduce hist: sum] -> resolve -> compact -> [allgather arena+counts,
+ *   allreduce edge counters: sum] -> finish
  */
 int kvm_column_stats(const double* values, int64_t n, int32_t member_mode, const void* member,
                      int32_t nsets, kvm_set_info* info, void* workspace, size_t workspace_bytes,
                      void* stream);
 /* device addresses inside a select workspace, so the host can hand them to NCCL */
 uint64_t* kvm_select_hist_ptr(void* workspace);   /* [KVM_MAX_SETS][kvm_select_bins()] u64 */
+uint64_t* kvm_select_edge_ptr(void* workspace);   /* [KVM_MAX_HISTS][KVM_HIST_MAX_BINS] u64 edge counters */
 int32_t kvm_select_bins(void);
 uint64_t* kvm_select_arena_ptr(void* workspace);  /* candidate keys */
 int64_t* kvm_select_bucket_counts_ptr(void* workspace); /* [KVM_MAX_QUERIES] local counts */
@@ -225,11 +253,13 @@ int64_t* kvm_select_bucket_offsets_ptr(void* workspace); /* [KVM_MAX_QUERIES+1] 
 kvm_set_info* kvm_select_info_ptr(void* workspace);      /* set info block inside the workspace */
 
 int kvm_select_plan(const kvm_set_info* info, const kvm_query* queries_host, int32_t nq,
-                    void* workspace, size_t workspace_bytes, int64_t arena_capacity, void* stream);
+                    const kvm_hist_spec* hists_host, void* workspace, size_t workspace_bytes,
+                    int64_t arena_capacity, void* stream);
 int kvm_column_select_hist(const double* values, int64_t n, int32_t member_mode, const void* member,
                            void* workspace, void* stream);
-int kvm_log_select_hist(const kvm_request_log* log_host, const uint8_t* flags, void* workspace,
-                        void* stream);
+int kvm_log_select_hist(const kvm_request_log* log_host, const uint8_t* flags,
+                        const kvm_log_stats* stats, const kvm_log_extras* extras_host,
+                        void* workspace, void* stream);
 int kvm_select_resolve(void* workspace, void* stream);
 int kvm_column_select_compact(const double* values, int64_t n, int32_t member_mode,
                               const void* member, void* workspace, void* stream);
@@ -238,7 +268,9 @@ int kvm_log_select_compact(const kvm_request_log* log_host, const uint8_t* flags
 /* Finish from `nsrc` arenas (own + gathered peers), each laid out with the same bucket
  * offsets; src_counts[s*KVM_MAX_QUERIES + b] = keys source s holds for bucket b. */
 int kvm_select_finish(void* workspace, const uint64_t* const* arenas_host, int32_t nsrc,
-                      const int64_t* src_counts, kvm_query_result* results, void* stream);
+                      const int64_t* src_counts, kvm_query_result* results,
+                      int64_t* hist_counts /* zeroed by the caller; NULL = no histograms */,
+                      void* stream);
 
 /* ------------------------------------------------------------------ histograms / series */
 

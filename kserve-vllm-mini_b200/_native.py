@@ -18,6 +18,8 @@ KVM_ERR_ARENA = -4
 KVM_MAX_SETS = 8
 KVM_MAX_COLS = 8
 KVM_MAX_QUERIES = 48
+KVM_MAX_HISTS = 4
+KVM_HIST_MAX_BINS = 64
 
 # row flags (kvm_log_scan)
 F_SUCCESS, F_COLD, F_TOKENS, F_GEN = 0x01, 0x02, 0x04, 0x08
@@ -63,6 +65,17 @@ class PowerStatsC(C.Structure):
                 ("ts_max", C.c_double), ("step_sum_hi", C.c_double), ("step_sum_lo", C.c_double)]
 
 
+class HistSpecC(C.Structure):
+    _fields_ = [("nhist", C.c_int32), ("num_bins", C.c_int32), ("col", C.c_int32 * 4),
+                ("set_mask", C.c_uint32 * 4)]
+
+
+class LogExtrasC(C.Structure):
+    _fields_ = [("num_bins", C.c_int32), ("pad", C.c_int32), ("hist_counts", C.c_void_p),
+                ("series_window_ms", C.c_double), ("series_max_bins", C.c_int64),
+                ("series", C.c_void_p), ("series_dropped", C.c_void_p)]
+
+
 class QueryC(C.Structure):
     _fields_ = [("set_mask", C.c_uint32), ("rank_kind", C.c_int32), ("p", C.c_double),
                 ("rank", C.c_int64)]
@@ -87,25 +100,26 @@ def _declare(lib: C.CDLL) -> None:
         "kvm_log_scan": (C.c_int, [P(RequestLogC), vp, i32, f64, vp, vp, vp, vp, sz, vp]),
         "kvm_select_workspace_bytes": (sz, [i64]),
         "kvm_select_default_arena": (i64, [i64]),
-        "kvm_log_select": (C.c_int, [P(RequestLogC), vp, vp, P(QueryC), i32, vp, vp, sz, i64, vp]),
+        "kvm_log_select": (C.c_int, [P(RequestLogC), vp, vp, P(QueryC), i32, vp, P(LogExtrasC), vp, sz, i64, vp]),
         "kvm_column_select": (C.c_int, [vp, i64, i32, vp, i32, P(QueryC), i32, vp, vp, sz, i64, vp]),
         "kvm_column_select_static": (C.c_int, [vp, i64, i32, vp, P(QueryC), i32, vp, vp]),
         "kvm_column_select_static_max_n": (i64, []),
         "kvm_select_status": (C.c_int, [vp, vp]),
         "kvm_column_stats": (C.c_int, [vp, i64, i32, vp, i32, vp, vp, sz, vp]),
         "kvm_select_hist_ptr": (vp, [vp]),
+        "kvm_select_edge_ptr": (vp, [vp]),
         "kvm_select_bins": (i32, []),
         "kvm_select_arena_ptr": (vp, [vp]),
         "kvm_select_bucket_counts_ptr": (vp, [vp]),
         "kvm_select_bucket_offsets_ptr": (vp, [vp]),
         "kvm_select_info_ptr": (vp, [vp]),
-        "kvm_select_plan": (C.c_int, [vp, P(QueryC), i32, vp, sz, i64, vp]),
+        "kvm_select_plan": (C.c_int, [vp, P(QueryC), i32, P(HistSpecC), vp, sz, i64, vp]),
         "kvm_column_select_hist": (C.c_int, [vp, i64, i32, vp, vp, vp]),
-        "kvm_log_select_hist": (C.c_int, [P(RequestLogC), vp, vp, vp]),
+        "kvm_log_select_hist": (C.c_int, [P(RequestLogC), vp, vp, P(LogExtrasC), vp, vp]),
         "kvm_select_resolve": (C.c_int, [vp, vp]),
         "kvm_column_select_compact": (C.c_int, [vp, i64, i32, vp, vp, vp]),
         "kvm_log_select_compact": (C.c_int, [P(RequestLogC), vp, vp, vp]),
-        "kvm_select_finish": (C.c_int, [vp, P(vp), i32, vp, vp, vp]),
+        "kvm_select_finish": (C.c_int, [vp, P(vp), i32, vp, vp, vp, vp]),
         "kvm_log_histograms_workspace_bytes": (sz, [i32]),
         "kvm_log_histograms": (C.c_int, [P(RequestLogC), vp, vp, i32, vp, vp, sz, vp]),
         "kvm_column_histogram": (C.c_int, [vp, i64, f64, f64, i32, vp, vp, sz, vp]),

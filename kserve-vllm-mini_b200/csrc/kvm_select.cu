@@ -1,25 +1,31 @@
-// kvm_select.cu - K2 (+K6): exact multi-rank radix select over fp64 keys.
+// kvm_select.cu - K2 (+K5, K6, K8 folded in): exact multi-rank radix select over fp64 keys,
+// with the 20-bin value histograms and the windowed series produced by the same two passes.
 //
-// Replaces analyze.py:59-81 `percentile()` (25 calls / run over 9 multisets, each a
-// fresh NaN filter + list.sort) and the upper-median of energy/collector.py:333.
-// The kernels return exact ORDER STATISTICS; the host evaluates the reference's
-// interpolation expression in Python floats, so the result is bit-identical.
+// Replaces analyze.py:59-81 `percentile()` (25 calls / run over 9 multisets, each a fresh NaN
+// filter + list.sort), analyze.py:84-122 `compute_histograms` (4 calls / run) and the
+// upper-median of energy/collector.py:333.  The kernels return exact ORDER STATISTICS and
+// exact COUNTS; the host evaluates the reference's interpolation / edge expressions in Python
+// floats, so the results are bit-identical.
 //
-// Algorithm (range-adaptive radix select; DESIGN.md "select"):
-//   plan     per value column: kbase = min key, width = bits(max-min),
-//            shift = max(0, width-11): digit(key) = (key-kbase) >> shift   (< 2048)
-//            per query: n = sum of its base-set counts, rank from (kind, p, n)
-//   hist     ONE pass over the data: per base set a 2048-bin histogram of digit(key),
-//            privatised in shared memory, flushed with 64-bit global atomics
-//   resolve  per query: bin holding the rank, residual rank, candidate bucket
-//            (column, set mask, bin); buckets de-duplicated and laid out in the arena
-//   compact  ONE pass over the data: keys whose digit hits a bucket are appended to it
-//   finish   one CTA per query: 11-bit-per-pass radix select inside its bucket
-// With adaptive digits a bucket holds ~n/2048 of the populated range, so everything
-// after `compact` is tiny; the two streaming passes are HBM-bound.
+// Algorithm (range-adaptive radix select):
+//   plan     per value column: kbase = min key, width = bits(max-min), shift = max(0,width-11):
+//            digit(key) = (key-kbase) >> shift  (< 2048).  Per query: n and rank.  Per value
+//            histogram: the nb-1 bin edges as keys (bisection with the reference expression) and
+//            the fine bins that contain an edge.
+//   hist     ONE pass over the data: per base set a 2048-bin histogram of digit(key), privatised
+//            in shared memory, flushed with 64-bit global atomics.  The log variant also bins
+//            start_ms into the 1-window series in the same pass (K8).
+//   resolve  per query: bin holding the rank, residual rank, candidate bucket (column, set
+//            mask, bin); buckets de-duplicated, sorted by (column, bin), laid out in the arena
+//   compact  ONE pass over the data: keys whose digit hits a bucket are appended to it; keys
+//            whose fine bin contains a histogram edge are binned exactly (edge counters)
+//   finish   one CTA per query: radix select inside its bucket; one more CTA assembles the
+//            value histograms = edge counters + fine bins without an edge added wholesale
+// With adaptive digits a bucket holds ~n/2048 of the populated range, so everything after
+// `compact` is tiny; the two streaming passes are HBM-bound.
 //
-// Multi-GPU: `hist` is all-reduced and the arenas all-gathered by the host between the
-// stages; every rank then resolves / finishes identically.
+// Multi-GPU: `hist` and the edge counters are all-reduced and the arenas all-gathered by the
+// host between the stages; every rank resolves / finishes identically.
 
 #include "kvm_common.cuh"
 #include "kvm_log_device.cuh"
@@ -30,6 +36,8 @@ constexpr int SEL_THREADS = 512;
 constexpr int MAXQ = KVM_MAX_QUERIES;
 constexpr int MAX_SRC = 16;
 constexpr int STATS_SCRATCH = 256 + 8 * (KVM_MAX_SETS + 2) * 148 * 8;
+constexpr int NH = KVM_MAX_HISTS;   // value histograms per problem
+constexpr int NB_MAX = KVM_HIST_MAX_BINS;
 
 struct ColParam {
   uint64_t kbase;
@@ -44,6 +52,8 @@ struct Bucket {
   uint32_t set_mask;
   uint32_t bin;
   int64_t count;  // global number of keys in the bucket
+  int32_t run;    // buckets sharing (col, bin) starting at this one (valid in the first)
+  int32_t pad;
 };
 
 struct QState {
@@ -71,7 +81,13 @@ struct SelWs {
   Bucket bucket[MAXQ];
   int64_t bucket_offsets[MAXQ + 1];
   int64_t bucket_counts[MAXQ];  // local append cursors (compact)
-  uint32_t col_bitmap[KVM_MAX_COLS][BINS / 32];
+  kvm_hist_spec hspec;
+  int32_t active20[NH];
+  int32_t col_hist[KVM_MAX_COLS];  // value histogram fed by each column, -1 = none
+  uint64_t thr20[NH][NB_MAX];
+  uint32_t flag20[NH][BINS / 32];
+  unsigned long long edge20[NH][NB_MAX];
+  uint8_t slot[KVM_MAX_COLS][BINS];  // first bucket with that (col, bin); 255 = none
   uint64_t hist[KVM_MAX_SETS][BINS];
   unsigned char stats_scratch[STATS_SCRATCH];
 };
@@ -88,11 +104,25 @@ struct SrcPack {
   int32_t nsrc;
 };
 
+struct SeriesArgs {
+  const double* start_ms;
+  const kvm_log_stats* stats;  // min_start_ms read on the device
+  double window_ms;
+  int64_t max_bins;
+  unsigned long long* series;  // [3][max_bins]
+  unsigned long long* dropped;
+};
+
 // ------------------------------------------------------------------ plan
-__global__ void select_plan_kernel(SelWs* ws, const kvm_set_info* info_in, QueryPack qp,
-                                   int64_t arena_capacity) {
+constexpr int PLAN_THREADS = 512;
+
+__global__ void __launch_bounds__(PLAN_THREADS)
+select_plan_kernel(SelWs* ws, const kvm_set_info* info_in, QueryPack qp, kvm_hist_spec hs,
+                   int64_t arena_capacity) {
   __shared__ kvm_set_info info;
-  if (threadIdx.x == 0) {
+  __shared__ ColParam cps[KVM_MAX_COLS];
+  const int t = threadIdx.x;
+  if (t == 0) {
     info = *info_in;
     ws->info = info;
     ws->status = KVM_OK;
@@ -100,9 +130,16 @@ __global__ void select_plan_kernel(SelWs* ws, const kvm_set_info* info_in, Query
     ws->nbuckets = 0;
     ws->arena_capacity = arena_capacity;
     ws->arena_used = 0;
+    ws->hspec = hs;
   }
+  // zero what the passes accumulate into
+  for (int i = t; i < KVM_MAX_SETS * BINS; i += PLAN_THREADS) (&ws->hist[0][0])[i] = 0;
+  for (int i = t; i < NH * NB_MAX; i += PLAN_THREADS) {
+    (&ws->edge20[0][0])[i] = 0;
+    (&ws->thr20[0][0])[i] = ~0ull;
+  }
+  for (int i = t; i < NH * (BINS / 32); i += PLAN_THREADS) (&ws->flag20[0][0])[i] = 0;
   __syncthreads();
-  const int t = threadIdx.x;
   if (t < KVM_MAX_COLS) {
     ColParam cp{0, 0, 0};
     if (t < info.ncols && info.kmin[t] <= info.kmax[t]) {
@@ -112,13 +149,28 @@ __global__ void select_plan_kernel(SelWs* ws, const kvm_set_info* info_in, Query
       cp.shift = cp.width > BINS_LOG2 ? cp.width - BINS_LOG2 : 0;
     }
     ws->col[t] = cp;
+    cps[t] = cp;
+    int h = -1;
+    for (int k = 0; k < hs.nhist; ++k)
+      if (hs.col[k] == t) h = k;
+    ws->col_hist[t] = h;
   }
-  if (t < MAXQ) {
+  if (t >= 32 && t < 32 + NH) {
+    const int h = t - 32;
+    int act = 0;
+    if (h < hs.nhist) {
+      const int c = hs.col[h];
+      act = info.kmin[c] < info.kmax[c];
+    }
+    ws->active20[h] = act;
+  }
+  if (t >= 64 && t < 64 + MAXQ) {
+    const int qi = t - 64;
     QState s{0, 0, 0, 0, KVM_Q_EMPTY, -1, 0, 1};
-    ws->bucket_counts[t] = 0;
-    if (t < qp.nq) {
-      const kvm_query q = qp.q[t];
-      ws->queries[t] = q;
+    ws->bucket_counts[qi] = 0;
+    if (qi < qp.nq) {
+      const kvm_query q = qp.q[qi];
+      ws->queries[qi] = q;
       int64_t n = 0;
       int col = -1;
       for (int b = 0; b < info.nsets; ++b)
@@ -134,7 +186,24 @@ __global__ void select_plan_kernel(SelWs* ws, const kvm_set_info* info_in, Query
         s.resolved = s.status != KVM_Q_OK;
       }
     }
-    ws->q[t] = s;
+    ws->q[qi] = s;
+  }
+  __syncthreads();
+  // histogram edges as keys + the fine bins that contain one (threads 128..)
+  if (t >= 128 && t < 128 + NH * (NB_MAX - 1)) {
+    const int e = t - 128, h = e / (NB_MAX - 1), b = 1 + e % (NB_MAX - 1);
+    if (h < hs.nhist && b < hs.num_bins) {
+      const int c = hs.col[h];
+      const uint64_t klo = info.kmin[c], khi = info.kmax[c];
+      if (klo < khi) {
+        const uint64_t T = bin_threshold(klo, khi, hs.num_bins, b);
+        ws->thr20[h][b - 1] = T;
+        if (T != ~0ull) {
+          const uint32_t d = digit_of(T, cps[c].kbase, cps[c].shift);
+          atomicOr(&ws->flag20[h][d >> 5], 1u << (d & 31));
+        }
+      }
+    }
   }
 }
 
@@ -222,19 +291,15 @@ __device__ __forceinline__ void for_each_column_key(const double* __restrict__ v
 }
 
 // ------------------------------------------------------------------ hist
-template <class Stream>
-__device__ __forceinline__ void hist_body(SelWs* ws, int nsets, Stream&& stream) {
-  extern __shared__ uint32_t sh[];  // [nsets][BINS]
-  __shared__ ColParams cp;
+__device__ __forceinline__ void hist_prologue(SelWs* ws, uint32_t* sh, int nsets, ColParams& cp) {
   for (int i = threadIdx.x; i < nsets * BINS; i += blockDim.x) sh[i] = 0;
   if (threadIdx.x < KVM_MAX_COLS) {
     cp.kbase[threadIdx.x] = ws->col[threadIdx.x].kbase;
     cp.shift[threadIdx.x] = ws->col[threadIdx.x].shift;
   }
   __syncthreads();
-  stream([&](int set, int col, uint64_t key) {
-    atomicAdd(&sh[set * BINS + digit_of(key, cp.kbase[col], cp.shift[col])], 1u);
-  });
+}
+__device__ __forceinline__ void hist_epilogue(SelWs* ws, const uint32_t* sh, int nsets) {
   __syncthreads();
   for (int i = threadIdx.x; i < nsets * BINS; i += blockDim.x) {
     const uint32_t c = sh[i];
@@ -242,40 +307,162 @@ __device__ __forceinline__ void hist_body(SelWs* ws, int nsets, Stream&& stream)
   }
 }
 
+// series bin of one row: >= 0 bin, -1 nothing to add (NaN start), -2 outside [0, max_bins)
+__device__ __forceinline__ long long series_bin(double st, double s0, double window_ms, int64_t max_bins) {
+  const double b = floor((st - s0) / window_ms);
+  if (b >= 0.0 && b < (double)max_bins) return (long long)b;
+  return b == b ? -2 : -1;
+}
+__device__ __forceinline__ void series_add_row(const SeriesArgs& sa, long long bin, bool ok, long long tok) {
+  if (bin >= 0) {
+    atomicAdd(&sa.series[bin], 1ull);
+    if (ok) {
+      atomicAdd(&sa.series[sa.max_bins + bin], 1ull);
+      atomicAdd(&sa.series[2 * sa.max_bins + bin], (unsigned long long)tok);
+    }
+  } else if (bin == -2) {
+    atomicAdd(sa.dropped, 1ull);
+  }
+}
+
+// Log histogram pass; ROWS = 2 (128-bit loads) or 1 (unaligned shard).  With SERIES the same
+// pass bins start_ms into the window series: rows are time-ordered, so the 32/64 rows of a
+// warp iteration almost always share one window and are merged into three atomics.
+template <int ROWS, bool SERIES>
 __global__ void __launch_bounds__(SEL_THREADS, 2)
-log_hist_kernel(kvm_request_log log, const uint8_t* __restrict__ flags, bool vec, SelWs* ws) {
-  hist_body(ws, KVM_LOG_NSETS, [&](auto&& f) { for_each_log_key(log, flags, vec, f); });
+log_hist_kernel(kvm_request_log log, const uint8_t* __restrict__ flags, SelWs* ws, SeriesArgs sa) {
+  extern __shared__ uint32_t sh[];  // [KVM_LOG_NSETS][BINS]
+  __shared__ ColParams cp;
+  hist_prologue(ws, sh, KVM_LOG_NSETS, cp);
+  auto add = [&](int set, int col, uint64_t key) {
+    atomicAdd(&sh[set * BINS + digit_of(key, cp.kbase[col], cp.shift[col])], 1u);
+  };
+  const int lane = threadIdx.x & 31;
+  const int64_t n = log.n;
+  const int64_t nunits = ROWS == 2 ? (n >> 1) : n;
+  double s0 = 0.0;
+  if (SERIES) s0 = sa.stats->min_start_ms;
+  for (int64_t base = (int64_t)blockIdx.x * SEL_THREADS + (threadIdx.x & ~31); base < nunits;
+       base += (int64_t)gridDim.x * SEL_THREADS) {
+    const int64_t u = base + lane;
+    const bool live = u < nunits;
+    const int64_t i = ROWS == 2 ? (u << 1) : u;
+    uint8_t f0 = 0, f1 = 0;
+    long long tok0 = 0, tok1 = 0;
+    if (live) {
+      if (ROWS == 2) {
+        const uint16_t ff = kvm_ld_u8x2(flags + i);
+        f0 = (uint8_t)(ff & 0xff);
+        f1 = (uint8_t)(ff >> 8);
+      } else {
+        f0 = kvm_ld_u8(flags + i);
+      }
+      if ((f0 | f1) & KVM_F_SUCCESS) {
+        if (ROWS == 2) {
+          const double2 la = kvm_ld2(log.latency_ms + i), tf = kvm_ld2(log.ttfb_ms + i);
+          const double2 tl = kvm_ld2(log.tllt_ms + i);
+          const longlong2 ct = kvm_ld2(log.completion_tokens + i);
+          log_row_keys(f0, la.x, tf.x, tl.x, ct.x, add);
+          log_row_keys(f1, la.y, tf.y, tl.y, ct.y, add);
+          tok0 = ct.x;
+          tok1 = ct.y;
+        } else {
+          const long long ct = kvm_ld1(log.completion_tokens + i);
+          log_row_keys(f0, kvm_ld1(log.latency_ms + i), kvm_ld1(log.ttfb_ms + i), kvm_ld1(log.tllt_ms + i), ct, add);
+          tok0 = ct;
+        }
+      }
+    }
+    if (SERIES) {
+      long long b0 = -1, b1 = -1;
+      if (live) {
+        if (ROWS == 2) {
+          const double2 st = kvm_ld2(sa.start_ms + i);
+          b0 = series_bin(st.x, s0, sa.window_ms, sa.max_bins);
+          b1 = series_bin(st.y, s0, sa.window_ms, sa.max_bins);
+        } else {
+          b0 = series_bin(kvm_ld1(sa.start_ms + i), s0, sa.window_ms, sa.max_bins);
+          b1 = b0;
+        }
+      }
+      const bool ok0 = f0 & KVM_F_SUCCESS, ok1 = (ROWS == 2) && (f1 & KVM_F_SUCCESS);
+      const long long lead = __shfl_sync(KVM_FULL, b0, 0);
+      if (__all_sync(KVM_FULL, live && b0 == lead && b1 == lead && lead >= 0)) {
+        const int nok = __popc(__ballot_sync(KVM_FULL, ok0)) + __popc(__ballot_sync(KVM_FULL, ok1));
+        const int64_t tsum = kvm_warp_sum((int64_t)((ok0 ? tok0 : 0) + (ok1 ? tok1 : 0)));
+        if (lane == 0) {
+          atomicAdd(&sa.series[lead], (unsigned long long)(32 * ROWS));
+          if (nok) {
+            atomicAdd(&sa.series[sa.max_bins + lead], (unsigned long long)nok);
+            atomicAdd(&sa.series[2 * sa.max_bins + lead], (unsigned long long)tsum);
+          }
+        }
+      } else if (live) {
+        series_add_row(sa, b0, ok0, tok0);
+        if (ROWS == 2) series_add_row(sa, b1, ok1, tok1);
+      }
+    }
+  }
+  if (ROWS == 2 && (n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {  // odd tail row
+    const int64_t i = n - 1;
+    const uint8_t fl = flags[i];
+    log_row_keys(fl, log.latency_ms[i], log.ttfb_ms[i], log.tllt_ms[i], log.completion_tokens[i], add);
+    if (SERIES)
+      series_add_row(sa, series_bin(sa.start_ms[i], s0, sa.window_ms, sa.max_bins), fl & KVM_F_SUCCESS,
+                     log.completion_tokens[i]);
+  }
+  hist_epilogue(ws, sh, KVM_LOG_NSETS);
 }
 
 __global__ void __launch_bounds__(SEL_THREADS, 2)
 column_hist_kernel(const double* __restrict__ values, int64_t n, int mode,
                    const void* __restrict__ member, bool vec, int nsets, SelWs* ws) {
-  hist_body(ws, nsets, [&](auto&& f) { for_each_column_key(values, n, mode, member, vec, f); });
+  extern __shared__ uint32_t sh[];
+  __shared__ ColParams cp;
+  hist_prologue(ws, sh, nsets, cp);
+  for_each_column_key(values, n, mode, member, vec, [&](int set, int col, uint64_t key) {
+    atomicAdd(&sh[set * BINS + digit_of(key, cp.kbase[col], cp.shift[col])], 1u);
+  });
+  hist_epilogue(ws, sh, nsets);
 }
 
 // ------------------------------------------------------------------ resolve
-// One warp per query walks the (summed) histogram of its sets to the bin holding the rank.
-__global__ void __launch_bounds__(1024, 1) select_resolve_kernel(SelWs* ws) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+constexpr int RES_THREADS = 1024;
+
+// The global histograms are staged in shared memory; one warp per query then walks the
+// (summed) histogram of its sets to the bin holding the rank.
+__global__ void __launch_bounds__(RES_THREADS, 1) select_resolve_kernel(SelWs* ws) {
+  extern __shared__ uint64_t hs[];  // [nsets][BINS]
   __shared__ uint32_t q_bin[MAXQ];
   __shared__ int64_t q_cnt[MAXQ];
+  __shared__ QState qs[MAXQ];
+  __shared__ uint32_t qmask[MAXQ];
+  __shared__ ColParam cps[KVM_MAX_COLS];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = RES_THREADS / 32;
   const int nq = ws->nq;
   const int nsets = ws->info.nsets;
 
-  for (int i = threadIdx.x; i < KVM_MAX_COLS * (BINS / 32); i += blockDim.x)
-    (&ws->col_bitmap[0][0])[i] = 0;
+  for (int i = threadIdx.x; i < nsets * BINS; i += RES_THREADS) hs[i] = (&ws->hist[0][0])[i];
+  for (int i = threadIdx.x; i < KVM_MAX_COLS * BINS / 4; i += RES_THREADS)
+    reinterpret_cast<uint32_t*>(&ws->slot[0][0])[i] = 0xffffffffu;
+  if (threadIdx.x < MAXQ) {
+    qs[threadIdx.x] = ws->q[threadIdx.x];
+    qmask[threadIdx.x] = ws->queries[threadIdx.x].set_mask;
+  }
+  if (threadIdx.x < KVM_MAX_COLS) cps[threadIdx.x] = ws->col[threadIdx.x];
+  __syncthreads();
 
   for (int q = warp; q < nq; q += nwarps) {
-    QState s = ws->q[q];
+    QState s = qs[q];
     if (s.status != KVM_Q_OK) continue;
-    const ColParam cp = ws->col[s.col];
-    const uint32_t mask = ws->queries[q].set_mask;
+    const ColParam cp = cps[s.col];
+    const uint32_t mask = qmask[q];
     if (cp.width == 0) {  // one distinct key in the column
       if (lane == 0) {
         s.key = cp.kbase;
         s.resolved = 1;
         s.bucket = -1;
-        ws->q[q] = s;
+        qs[q] = s;
       }
       continue;
     }
@@ -284,7 +471,7 @@ __global__ void __launch_bounds__(1024, 1) select_resolve_kernel(SelWs* ws) {
     for (int base = 0; base < BINS && !found; base += 32) {
       int64_t c = 0;
       for (int b = 0; b < nsets; ++b)
-        if ((mask >> b) & 1u) c += (int64_t)ws->hist[b][base + lane];
+        if ((mask >> b) & 1u) c += (int64_t)hs[b * BINS + base + lane];
       int64_t incl = c;
 #pragma unroll
       for (int d = 1; d < 32; d <<= 1) {
@@ -308,7 +495,7 @@ __global__ void __launch_bounds__(1024, 1) select_resolve_kernel(SelWs* ws) {
             s.resolved = 0;
             s.bucket = -2;  // assigned below
           }
-          ws->q[q] = s;
+          qs[q] = s;
         }
         found = true;
       }
@@ -317,112 +504,204 @@ __global__ void __launch_bounds__(1024, 1) select_resolve_kernel(SelWs* ws) {
     if (!found && lane == 0) {  // histogram inconsistent with counts (caller error)
       s.status = KVM_Q_OUT_OF_RANGE;
       s.resolved = 1;
-      ws->q[q] = s;
+      qs[q] = s;
     }
   }
   __syncthreads();
-  __threadfence_block();
+  __shared__ Bucket bk[MAXQ];
+  __shared__ int order[MAXQ];
+  __shared__ int newpos[MAXQ];
+  __shared__ int nb_s;
   if (threadIdx.x == 0) {
+    // distinct (col, mask, bin) buckets, then sorted by (col, bin) so that buckets sharing a
+    // fine bin are contiguous (the compact pass finds them through slot[col][bin])
     int nb = 0;
-    int64_t off = 0;
     for (int q = 0; q < nq; ++q) {
-      QState s = ws->q[q];
+      QState& s = qs[q];
       if (s.status != KVM_Q_OK || s.resolved) continue;
-      const uint32_t mask = ws->queries[q].set_mask;
       int j = -1;
       for (int k = 0; k < nb; ++k)
-        if (ws->bucket[k].col == s.col && ws->bucket[k].set_mask == mask &&
-            ws->bucket[k].bin == q_bin[q]) {
+        if (bk[k].col == s.col && bk[k].set_mask == qmask[q] && bk[k].bin == q_bin[q]) {
           j = k;
           break;
         }
       if (j < 0) {
         j = nb++;
-        const ColParam cp = ws->col[s.col];
+        const ColParam cp = cps[s.col];
         Bucket b;
         b.base = cp.kbase + ((uint64_t)q_bin[q] << cp.shift);
         b.shift = cp.shift;
         b.col = s.col;
-        b.set_mask = mask;
+        b.set_mask = qmask[q];
         b.bin = q_bin[q];
         b.count = q_cnt[q];
-        ws->bucket[j] = b;
-        ws->bucket_offsets[j] = off;
-        off += b.count;
-        ws->col_bitmap[s.col][q_bin[q] >> 5] |= 1u << (q_bin[q] & 31);
+        b.run = 0;
+        b.pad = 0;
+        bk[j] = b;
       }
-      ws->q[q].bucket = j;
+      s.bucket = j;  // index before sorting; remapped below
     }
-    ws->bucket_offsets[nb] = off;
-    for (int k = nb + 1; k <= MAXQ; ++k) ws->bucket_offsets[k] = off;
+    for (int k = 0; k < nb; ++k) order[k] = k;
+    for (int a = 1; a < nb; ++a) {  // insertion sort by (col, bin)
+      const int v = order[a];
+      int p = a - 1;
+      while (p >= 0 && (bk[order[p]].col > bk[v].col ||
+                        (bk[order[p]].col == bk[v].col && bk[order[p]].bin > bk[v].bin))) {
+        order[p + 1] = order[p];
+        --p;
+      }
+      order[p + 1] = v;
+    }
+    for (int k = 0; k < nb; ++k) newpos[order[k]] = k;
+    int64_t off = 0;
+    for (int k = 0; k < nb; ++k) {
+      Bucket b = bk[order[k]];
+      int run = 1;
+      while (k + run < nb && bk[order[k + run]].col == b.col && bk[order[k + run]].bin == b.bin) ++run;
+      const bool first = k == 0 || bk[order[k - 1]].col != b.col || bk[order[k - 1]].bin != b.bin;
+      b.run = first ? run : 0;
+      ws->bucket[k] = b;
+      ws->bucket_offsets[k] = off;
+      off += b.count;
+      if (first) ws->slot[b.col][b.bin] = (uint8_t)k;
+    }
+    for (int k = nb; k <= MAXQ; ++k) ws->bucket_offsets[k] = off;
     ws->nbuckets = nb;
     ws->arena_used = off;
     if (off > ws->arena_capacity) ws->status = KVM_ERR_ARENA;
+    nb_s = nb;
+  }
+  __syncthreads();
+  if (threadIdx.x < MAXQ) {
+    QState s = qs[threadIdx.x];
+    if (s.status == KVM_Q_OK && !s.resolved && s.bucket >= 0) s.bucket = newpos[s.bucket];
+    ws->q[threadIdx.x] = s;
   }
 }
 
 // ------------------------------------------------------------------ compact
+struct CompactSmem {
+  ColParams cp;
+  Bucket bk[MAXQ];
+  int64_t bk_off[MAXQ];
+  uint64_t thr[NH][NB_MAX];
+  uint32_t flag[NH][BINS / 32];
+  uint32_t edge[NH][NB_MAX];
+  int32_t col_hist[KVM_MAX_COLS];
+  int32_t active[NH];
+  int32_t nb;         // buckets
+  int32_t num_bins;   // value histogram bins
+  uint8_t slot[KVM_MAX_COLS][BINS];
+};
+
 template <class Stream>
-__device__ __forceinline__ void compact_body(SelWs* ws, uint64_t* __restrict__ arena,
+__device__ __forceinline__ void compact_body(SelWs* ws, uint64_t* __restrict__ arena, int ncols,
                                              Stream&& stream) {
-  __shared__ ColParams cp;
-  __shared__ uint32_t bitmap[KVM_MAX_COLS][BINS / 32];
-  __shared__ Bucket bk[MAXQ];
-  __shared__ int64_t bk_off[MAXQ];
-  __shared__ int nb_s;
+  extern __shared__ __align__(16) unsigned char craw[];
+  CompactSmem& S = *reinterpret_cast<CompactSmem*>(craw);
   if (ws->status != KVM_OK) return;
-  if (threadIdx.x == 0) nb_s = ws->nbuckets;
-  if (threadIdx.x < KVM_MAX_COLS) {
-    cp.kbase[threadIdx.x] = ws->col[threadIdx.x].kbase;
-    cp.shift[threadIdx.x] = ws->col[threadIdx.x].shift;
+  if (threadIdx.x == 0) {
+    S.nb = ws->nbuckets;
+    S.num_bins = ws->hspec.num_bins;
   }
-  for (int i = threadIdx.x; i < KVM_MAX_COLS * (BINS / 32); i += blockDim.x)
-    (&bitmap[0][0])[i] = (&ws->col_bitmap[0][0])[i];
+  if (threadIdx.x < KVM_MAX_COLS) {
+    S.cp.kbase[threadIdx.x] = ws->col[threadIdx.x].kbase;
+    S.cp.shift[threadIdx.x] = ws->col[threadIdx.x].shift;
+    S.col_hist[threadIdx.x] = ws->col_hist[threadIdx.x];
+  }
+  if (threadIdx.x < NH) S.active[threadIdx.x] = ws->active20[threadIdx.x];
+  for (int i = threadIdx.x; i < ncols * BINS / 4; i += blockDim.x)
+    reinterpret_cast<uint32_t*>(&S.slot[0][0])[i] = reinterpret_cast<const uint32_t*>(&ws->slot[0][0])[i];
+  for (int i = threadIdx.x; i < NH * NB_MAX; i += blockDim.x) {
+    (&S.thr[0][0])[i] = (&ws->thr20[0][0])[i];
+    (&S.edge[0][0])[i] = 0;
+  }
+  for (int i = threadIdx.x; i < NH * (BINS / 32); i += blockDim.x) (&S.flag[0][0])[i] = (&ws->flag20[0][0])[i];
   for (int i = threadIdx.x; i < MAXQ; i += blockDim.x) {
-    bk[i] = ws->bucket[i];
-    bk_off[i] = ws->bucket_offsets[i];
+    S.bk[i] = ws->bucket[i];
+    S.bk_off[i] = ws->bucket_offsets[i];
   }
   __syncthreads();
-  const int nb = nb_s;
-  if (nb == 0) return;
   stream([&](int set, int col, uint64_t key) {
-    const uint32_t d = digit_of(key, cp.kbase[col], cp.shift[col]);
-    if (!((bitmap[col][d >> 5] >> (d & 31)) & 1u)) return;
-    for (int j = 0; j < nb; ++j) {
-      if (bk[j].col == col && bk[j].bin == d && ((bk[j].set_mask >> set) & 1u)) {
-        const unsigned long long pos =
-            atomicAdd(reinterpret_cast<unsigned long long*>(&ws->bucket_counts[j]), 1ull);
-        if ((int64_t)pos < bk[j].count) arena[bk_off[j] + (int64_t)pos] = key;
-      }
+    const uint32_t d = digit_of(key, S.cp.kbase[col], S.cp.shift[col]);
+    const uint32_t j0 = S.slot[col][d];
+    if (j0 != 255u) {
+      const int run = S.bk[j0].run;
+      for (int j = j0; j < (int)j0 + run; ++j)
+        if ((S.bk[j].set_mask >> set) & 1u) {
+          const unsigned long long pos =
+              atomicAdd(reinterpret_cast<unsigned long long*>(&ws->bucket_counts[j]), 1ull);
+          if ((int64_t)pos < S.bk[j].count) arena[S.bk_off[j] + (int64_t)pos] = key;
+        }
     }
+    const int h = S.col_hist[col];
+    if (h >= 0 && S.active[h] && ((S.flag[h][d >> 5] >> (d & 31)) & 1u))
+      atomicAdd(&S.edge[h][bin_of(key, S.thr[h], S.num_bins)], 1u);
   });
+  __syncthreads();
+  for (int i = threadIdx.x; i < NH * NB_MAX; i += blockDim.x) {
+    const uint32_t c = (&S.edge[0][0])[i];
+    if (c) atomicAdd(&ws->edge20[0][0] + i, (unsigned long long)c);
+  }
 }
 
 __global__ void __launch_bounds__(SEL_THREADS, 2)
 log_compact_kernel(kvm_request_log log, const uint8_t* __restrict__ flags, bool vec, SelWs* ws,
                    uint64_t* arena) {
-  compact_body(ws, arena, [&](auto&& f) { for_each_log_key(log, flags, vec, f); });
+  compact_body(ws, arena, KVM_LOG_NCOLS, [&](auto&& f) { for_each_log_key(log, flags, vec, f); });
 }
 
 __global__ void __launch_bounds__(SEL_THREADS, 2)
 column_compact_kernel(const double* __restrict__ values, int64_t n, int mode,
                       const void* __restrict__ member, bool vec, SelWs* ws, uint64_t* arena) {
-  compact_body(ws, arena, [&](auto&& f) { for_each_column_key(values, n, mode, member, vec, f); });
+  compact_body(ws, arena, 1, [&](auto&& f) { for_each_column_key(values, n, mode, member, vec, f); });
 }
 
 // ------------------------------------------------------------------ finish
-constexpr int FIN_THREADS = 512;
+constexpr int FIN_THREADS = 256;
 constexpr int FIN_BITS = 11;
 constexpr int FIN_BINS = 1 << FIN_BITS;
+constexpr int FIN_SMALL = 1024;  // candidates ranked by counting once this few remain
 
-// One CTA per query: radix select inside the query's bucket, FIN_BITS per pass.
+// CTAs 0..MAXQ-1: one query each - radix select inside the query's bucket, FIN_BITS per pass,
+// switching to rank-by-counting in shared memory once <= FIN_SMALL candidates remain.
+// CTA MAXQ: assembles the value histograms (edge counters + fine bins without an edge).
 __global__ void __launch_bounds__(FIN_THREADS, 1)
 select_finish_kernel(SelWs* ws, SrcPack src, const int64_t* __restrict__ src_counts,
-                     kvm_query_result* __restrict__ results) {
+                     kvm_query_result* __restrict__ results, int64_t* __restrict__ hist_out) {
   __shared__ uint32_t hist[FIN_BINS];
   __shared__ uint32_t chunk_sum[FIN_THREADS];
-  __shared__ uint32_t sel_digit;
+  __shared__ uint64_t small[FIN_SMALL];
+  __shared__ uint32_t sel_digit, sel_count, small_n;
   __shared__ int64_t sel_below;
+  __shared__ uint64_t answer;
+
+  if (blockIdx.x == MAXQ) {
+    // ---- value histograms (hist_out is zero-initialised by the caller)
+    const kvm_hist_spec hs = ws->hspec;
+    if (hist_out == nullptr || hs.nhist == 0 || ws->status != KVM_OK) return;
+    const int nbins = hs.num_bins;
+    unsigned long long* out = reinterpret_cast<unsigned long long*>(hist_out);
+    for (int t = threadIdx.x; t < hs.nhist * BINS; t += FIN_THREADS) {
+      const int h = t / BINS, d = t % BINS;
+      if (!ws->active20[h] || ((ws->flag20[h][d >> 5] >> (d & 31)) & 1u)) continue;
+      int64_t c = 0;
+      for (int b = 0; b < ws->info.nsets; ++b)
+        if ((hs.set_mask[h] >> b) & 1u) c += (int64_t)ws->hist[b][d];
+      if (c) {
+        const ColParam cp = ws->col[hs.col[h]];
+        const uint64_t lowkey = cp.kbase + ((uint64_t)d << cp.shift);
+        atomicAdd(out + h * nbins + bin_of(lowkey, ws->thr20[h], nbins), (unsigned long long)c);
+      }
+    }
+    for (int t = threadIdx.x; t < hs.nhist * nbins; t += FIN_THREADS) {
+      const int h = t / nbins, b = t % nbins;
+      const unsigned long long e = ws->edge20[h][b];
+      if (e) atomicAdd(out + t, e);
+    }
+    return;
+  }
+
   const int q = blockIdx.x;
   if (q >= ws->nq) return;
   const QState s = ws->q[q];
@@ -444,8 +723,41 @@ select_finish_kernel(SelWs* ws, SrcPack src, const int64_t* __restrict__ src_cou
   int rem = b.shift;        // unresolved low bits
   uint64_t prefix = 0;      // resolved part of (key - b.base) >> rem
   int64_t resid = s.resid;
+  int64_t live = b.count;   // candidates matching the prefix
+  bool done = false;
 
-  while (rem > 0) {
+  while (rem > 0 && !done) {
+    if (live <= FIN_SMALL) {
+      // gather the survivors and rank by counting
+      if (threadIdx.x == 0) small_n = 0;
+      __syncthreads();
+      for (int sidx = 0; sidx < src.nsrc; ++sidx) {
+        const int64_t cnt = src_counts[(size_t)sidx * MAXQ + s.bucket];
+        const uint64_t* __restrict__ keys = src.arena[sidx] + off;
+        for (int64_t i = threadIdx.x; i < cnt; i += FIN_THREADS) {
+          const uint64_t k = keys[i];
+          if (((k - b.base) >> rem) == prefix) {
+            const uint32_t p = atomicAdd(&small_n, 1u);
+            if (p < FIN_SMALL) small[p] = k;
+          }
+        }
+      }
+      __syncthreads();
+      const uint32_t m = small_n < FIN_SMALL ? small_n : FIN_SMALL;
+      for (uint32_t i = threadIdx.x; i < m; i += FIN_THREADS) {
+        const uint64_t k = small[i];
+        uint32_t less = 0, leq = 0;
+        for (uint32_t j = 0; j < m; ++j) {
+          const uint64_t o = small[j];
+          less += o < k;
+          leq += o <= k;
+        }
+        if ((int64_t)less <= resid && resid < (int64_t)leq) answer = k;  // all writers agree
+      }
+      __syncthreads();
+      done = true;
+      break;
+    }
     const int take = rem < FIN_BITS ? rem : FIN_BITS;
     const int sh = rem - take;
     const uint32_t dmask = (1u << take) - 1u;
@@ -456,7 +768,7 @@ select_finish_kernel(SelWs* ws, SrcPack src, const int64_t* __restrict__ src_cou
       const uint64_t* __restrict__ keys = src.arena[sidx] + off;
       for (int64_t i = threadIdx.x; i < cnt; i += FIN_THREADS) {
         const uint64_t low = keys[i] - b.base;
-        if ((rem >= 64 ? 0 : (low >> rem)) == prefix) atomicAdd(&hist[(uint32_t)(low >> sh) & dmask], 1u);
+        if ((low >> rem) == prefix) atomicAdd(&hist[(uint32_t)(low >> sh) & dmask], 1u);
       }
     }
     __syncthreads();
@@ -468,7 +780,6 @@ select_finish_kernel(SelWs* ws, SrcPack src, const int64_t* __restrict__ src_cou
     chunk_sum[threadIdx.x] = local;
     __syncthreads();
     if (threadIdx.x < 32) {
-      // warp 0 scans the chunk sums (16 per lane)
       constexpr int CH = FIN_THREADS / 32;
       uint32_t mine = 0;
       for (int k = 0; k < CH; ++k) mine += chunk_sum[threadIdx.x * CH + k];
@@ -489,21 +800,24 @@ select_finish_kernel(SelWs* ws, SrcPack src, const int64_t* __restrict__ src_cou
         }
         sel_digit = (uint32_t)bin;
         sel_below = below;
+        sel_count = hist[bin];
       }
       if (!hit && threadIdx.x == 0) {  // cannot happen with consistent counts
         sel_digit = 0;
         sel_below = 0;
+        sel_count = 0;
       }
     }
     __syncthreads();
     prefix = (prefix << take) | sel_digit;
     resid -= sel_below;
+    live = sel_count;
     rem = sh;
     __syncthreads();
   }
   if (threadIdx.x == 0) {
     kvm_query_result r;
-    r.value = kvm_unkey(b.base + prefix);
+    r.value = kvm_unkey(done ? answer : b.base + prefix);
     r.n = s.n;
     r.rank = s.rank;
     r.status = KVM_Q_OK;
@@ -535,6 +849,23 @@ static uint64_t* arena_of(void* workspace) {
   return reinterpret_cast<uint64_t*>(reinterpret_cast<unsigned char*>(workspace) + WS_HEADER);
 }
 
+static const kvm_hist_spec kNoHists = {0, 0, {0, 0, 0, 0}, {0, 0, 0, 0}};
+
+static kvm_hist_spec log_hist_spec(int32_t num_bins) {
+  kvm_hist_spec hs;
+  hs.nhist = 4;
+  hs.num_bins = num_bins;
+  hs.col[0] = KVM_COL_TTFB;
+  hs.col[1] = KVM_COL_TLLT;
+  hs.col[2] = KVM_COL_GEN;
+  hs.col[3] = KVM_COL_PERTOK;
+  hs.set_mask[0] = (1u << KVM_SET_TTFB_COLD) | (1u << KVM_SET_TTFB_WARM);
+  hs.set_mask[1] = 1u << KVM_SET_TLLT;
+  hs.set_mask[2] = 1u << KVM_SET_GEN;
+  hs.set_mask[3] = 1u << KVM_SET_PERTOK;
+  return hs;
+}
+
 }  // namespace
 
 extern "C" size_t kvm_select_workspace_bytes(int64_t arena_capacity) {
@@ -545,47 +876,77 @@ extern "C" size_t kvm_select_workspace_bytes(int64_t arena_capacity) {
 extern "C" int64_t kvm_select_default_arena(int64_t n) {
   // buckets hold ~1/2048 of the populated key range; n/16 + 1M leaves a wide margin for
   // up to KVM_MAX_QUERIES buckets of concentrated data.
-  int64_t cap = n / 16 + (1 << 20);
-  return cap;
+  return n / 16 + (1 << 20);
 }
 
 extern "C" int32_t kvm_select_bins(void) { return BINS; }
 extern "C" uint64_t* kvm_select_hist_ptr(void* ws) { return &reinterpret_cast<SelWs*>(ws)->hist[0][0]; }
+extern "C" uint64_t* kvm_select_edge_ptr(void* ws) {
+  return reinterpret_cast<uint64_t*>(&reinterpret_cast<SelWs*>(ws)->edge20[0][0]);
+}
 extern "C" uint64_t* kvm_select_arena_ptr(void* ws) { return arena_of(ws); }
 extern "C" int64_t* kvm_select_bucket_counts_ptr(void* ws) { return reinterpret_cast<SelWs*>(ws)->bucket_counts; }
 extern "C" int64_t* kvm_select_bucket_offsets_ptr(void* ws) { return reinterpret_cast<SelWs*>(ws)->bucket_offsets; }
 extern "C" kvm_set_info* kvm_select_info_ptr(void* ws) { return &reinterpret_cast<SelWs*>(ws)->info; }
 
 extern "C" int kvm_select_plan(const kvm_set_info* info, const kvm_query* queries, int32_t nq,
-                               void* workspace, size_t workspace_bytes, int64_t arena_capacity,
-                               void* stream) {
+                               const kvm_hist_spec* hists, void* workspace, size_t workspace_bytes,
+                               int64_t arena_capacity, void* stream) {
   KVM_REQUIRE(info && queries && workspace, "kvm_select_plan: null argument");
   KVM_REQUIRE(nq >= 1 && nq <= MAXQ, "kvm_select_plan: nq=%d outside [1,%d]", nq, MAXQ);
+  const kvm_hist_spec hs = hists ? *hists : kNoHists;
+  KVM_REQUIRE(hs.nhist >= 0 && hs.nhist <= NH, "kvm_select_plan: nhist=%d outside [0,%d]", hs.nhist, NH);
+  KVM_REQUIRE(hs.nhist == 0 || (hs.num_bins >= 1 && hs.num_bins <= NB_MAX),
+              "kvm_select_plan: num_bins=%d outside [1,%d]", hs.num_bins, NB_MAX);
   if (workspace_bytes < kvm_select_workspace_bytes(arena_capacity)) {
     kvm_set_error("kvm_select_plan: workspace %zu < %zu bytes", workspace_bytes,
                   kvm_select_workspace_bytes(arena_capacity));
     return KVM_ERR_WORKSPACE;
   }
-  cudaStream_t st = (cudaStream_t)stream;
   SelWs* ws = reinterpret_cast<SelWs*>(workspace);
   QueryPack qp;
   for (int i = 0; i < MAXQ; ++i) qp.q[i] = i < nq ? queries[i] : kvm_query{0, 0, 0.0, 0};
   qp.nq = nq;
-  KVM_CUDA_CHECK(cudaMemsetAsync(&ws->hist[0][0], 0, sizeof(ws->hist), st));
-  select_plan_kernel<<<1, 64, 0, st>>>(ws, info, qp, arena_capacity);
+  select_plan_kernel<<<1, PLAN_THREADS, 0, (cudaStream_t)stream>>>(ws, info, qp, hs, arena_capacity);
   KVM_CUDA_CHECK(cudaGetLastError());
   return KVM_OK;
 }
 
 extern "C" int kvm_log_select_hist(const kvm_request_log* log, const uint8_t* flags,
+                                   const kvm_log_stats* stats, const kvm_log_extras* extras,
                                    void* workspace, void* stream) {
   KVM_REQUIRE(log && flags && workspace, "kvm_log_select_hist: null argument");
+  const bool series = extras && extras->series_window_ms > 0.0;
+  if (series)
+    KVM_REQUIRE(stats && extras->series && extras->series_dropped && extras->series_max_bins >= 1,
+                "kvm_log_select_hist: series requested without stats / buffers");
+  cudaStream_t st = (cudaStream_t)stream;
+  SeriesArgs sa{};
+  if (series) {
+    sa.start_ms = log->start_ms;
+    sa.stats = stats;
+    sa.window_ms = extras->series_window_ms;
+    sa.max_bins = extras->series_max_bins;
+    sa.series = reinterpret_cast<unsigned long long*>(extras->series);
+    sa.dropped = reinterpret_cast<unsigned long long*>(extras->series_dropped);
+    KVM_CUDA_CHECK(cudaMemsetAsync(extras->series, 0, sizeof(int64_t) * 3 * (size_t)extras->series_max_bins, st));
+    KVM_CUDA_CHECK(cudaMemsetAsync(extras->series_dropped, 0, sizeof(int64_t), st));
+  }
   const size_t smem = (size_t)KVM_LOG_NSETS * BINS * sizeof(uint32_t);
-  int rc = ensure_smem((const void*)log_hist_kernel, smem);
-  if (rc) return rc;
+  const bool vec = log_vec_ok(log, flags) && (!series || aligned16(log->start_ms));
   const int grid = kvm_grid_for(log->n, SEL_THREADS * 2 * 4, 2);
-  log_hist_kernel<<<grid, SEL_THREADS, smem, (cudaStream_t)stream>>>(
-      *log, flags, log_vec_ok(log, flags), reinterpret_cast<SelWs*>(workspace));
+  SelWs* ws = reinterpret_cast<SelWs*>(workspace);
+#define KVM_LAUNCH_HIST(R, S)                                                    \
+  do {                                                                           \
+    int rc = ensure_smem((const void*)log_hist_kernel<R, S>, smem);              \
+    if (rc) return rc;                                                           \
+    log_hist_kernel<R, S><<<grid, SEL_THREADS, smem, st>>>(*log, flags, ws, sa); \
+  } while (0)
+  if (vec && series) KVM_LAUNCH_HIST(2, true);
+  else if (vec) KVM_LAUNCH_HIST(2, false);
+  else if (series) KVM_LAUNCH_HIST(1, true);
+  else KVM_LAUNCH_HIST(1, false);
+#undef KVM_LAUNCH_HIST
   KVM_CUDA_CHECK(cudaGetLastError());
   return KVM_OK;
 }
@@ -608,7 +969,10 @@ extern "C" int kvm_column_select_hist(const double* values, int64_t n, int32_t m
 
 extern "C" int kvm_select_resolve(void* workspace, void* stream) {
   KVM_REQUIRE(workspace, "kvm_select_resolve: null workspace");
-  select_resolve_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(reinterpret_cast<SelWs*>(workspace));
+  const size_t smem = (size_t)KVM_MAX_SETS * BINS * sizeof(uint64_t);
+  int rc = ensure_smem((const void*)select_resolve_kernel, smem);
+  if (rc) return rc;
+  select_resolve_kernel<<<1, RES_THREADS, smem, (cudaStream_t)stream>>>(reinterpret_cast<SelWs*>(workspace));
   KVM_CUDA_CHECK(cudaGetLastError());
   return KVM_OK;
 }
@@ -616,8 +980,10 @@ extern "C" int kvm_select_resolve(void* workspace, void* stream) {
 extern "C" int kvm_log_select_compact(const kvm_request_log* log, const uint8_t* flags,
                                       void* workspace, void* stream) {
   KVM_REQUIRE(log && flags && workspace, "kvm_log_select_compact: null argument");
+  int rc = ensure_smem((const void*)log_compact_kernel, sizeof(CompactSmem));
+  if (rc) return rc;
   const int grid = kvm_grid_for(log->n, SEL_THREADS * 2 * 4, 2);
-  log_compact_kernel<<<grid, SEL_THREADS, 0, (cudaStream_t)stream>>>(
+  log_compact_kernel<<<grid, SEL_THREADS, sizeof(CompactSmem), (cudaStream_t)stream>>>(
       *log, flags, log_vec_ok(log, flags), reinterpret_cast<SelWs*>(workspace), arena_of(workspace));
   KVM_CUDA_CHECK(cudaGetLastError());
   return KVM_OK;
@@ -626,8 +992,10 @@ extern "C" int kvm_log_select_compact(const kvm_request_log* log, const uint8_t*
 extern "C" int kvm_column_select_compact(const double* values, int64_t n, int32_t mode,
                                          const void* member, void* workspace, void* stream) {
   KVM_REQUIRE(workspace && (values || n == 0), "kvm_column_select_compact: null argument");
+  int rc = ensure_smem((const void*)column_compact_kernel, sizeof(CompactSmem));
+  if (rc) return rc;
   const int grid = kvm_grid_for(n, SEL_THREADS * 2 * 4, 2);
-  column_compact_kernel<<<grid, SEL_THREADS, 0, (cudaStream_t)stream>>>(
+  column_compact_kernel<<<grid, SEL_THREADS, sizeof(CompactSmem), (cudaStream_t)stream>>>(
       values, n, mode, member, column_vec_ok(values, mode, member),
       reinterpret_cast<SelWs*>(workspace), arena_of(workspace));
   KVM_CUDA_CHECK(cudaGetLastError());
@@ -636,7 +1004,7 @@ extern "C" int kvm_column_select_compact(const double* values, int64_t n, int32_
 
 extern "C" int kvm_select_finish(void* workspace, const uint64_t* const* arenas, int32_t nsrc,
                                  const int64_t* src_counts, kvm_query_result* results,
-                                 void* stream) {
+                                 int64_t* hist_counts, void* stream) {
   KVM_REQUIRE(workspace && results, "kvm_select_finish: null argument");
   KVM_REQUIRE(nsrc >= 0 && nsrc <= MAX_SRC, "kvm_select_finish: nsrc=%d outside [0,%d]", nsrc, MAX_SRC);
   SelWs* ws = reinterpret_cast<SelWs*>(workspace);
@@ -651,7 +1019,8 @@ extern "C" int kvm_select_finish(void* workspace, const uint64_t* const* arenas,
     sp.nsrc = nsrc;
     for (int i = 0; i < nsrc; ++i) sp.arena[i] = arenas[i];
   }
-  select_finish_kernel<<<MAXQ, FIN_THREADS, 0, (cudaStream_t)stream>>>(ws, sp, src_counts, results);
+  select_finish_kernel<<<MAXQ + 1, FIN_THREADS, 0, (cudaStream_t)stream>>>(ws, sp, src_counts, results,
+                                                                          hist_counts);
   KVM_CUDA_CHECK(cudaGetLastError());
   return KVM_OK;
 }
@@ -668,15 +1037,22 @@ extern "C" int kvm_select_status(const void* workspace, void* stream) {
 
 extern "C" int kvm_log_select(const kvm_request_log* log, const uint8_t* flags,
                               const kvm_log_stats* stats, const kvm_query* queries, int32_t nq,
-                              kvm_query_result* results, void* workspace, size_t workspace_bytes,
-                              int64_t arena_capacity, void* stream) {
+                              kvm_query_result* results, const kvm_log_extras* extras,
+                              void* workspace, size_t workspace_bytes, int64_t arena_capacity,
+                              void* stream) {
   KVM_REQUIRE(log && flags && stats && results, "kvm_log_select: null argument");
-  int rc = kvm_select_plan(&stats->sets, queries, nq, workspace, workspace_bytes, arena_capacity, stream);
+  const bool hists = extras && extras->num_bins > 0;
+  KVM_REQUIRE(!hists || extras->hist_counts, "kvm_log_select: hist_counts is null");
+  const kvm_hist_spec hs = hists ? log_hist_spec(extras->num_bins) : kNoHists;
+  int rc = kvm_select_plan(&stats->sets, queries, nq, &hs, workspace, workspace_bytes, arena_capacity, stream);
   if (rc) return rc;
-  if ((rc = kvm_log_select_hist(log, flags, workspace, stream))) return rc;
+  if (hists)
+    KVM_CUDA_CHECK(cudaMemsetAsync(extras->hist_counts, 0, sizeof(int64_t) * 4 * (size_t)extras->num_bins,
+                                   (cudaStream_t)stream));
+  if ((rc = kvm_log_select_hist(log, flags, stats, extras, workspace, stream))) return rc;
   if ((rc = kvm_select_resolve(workspace, stream))) return rc;
   if ((rc = kvm_log_select_compact(log, flags, workspace, stream))) return rc;
-  return kvm_select_finish(workspace, nullptr, 0, nullptr, results, stream);
+  return kvm_select_finish(workspace, nullptr, 0, nullptr, results, hists ? extras->hist_counts : nullptr, stream);
 }
 
 extern "C" int kvm_column_select(const double* values, int64_t n, int32_t mode, const void* member,
@@ -696,11 +1072,11 @@ extern "C" int kvm_column_select(const double* values, int64_t n, int32_t mode, 
   int rc = kvm_column_stats(values, n, mode, member, nsets, &ws->info, ws->stats_scratch,
                             sizeof(ws->stats_scratch), stream);
   if (rc) return rc;
-  if ((rc = kvm_select_plan(&ws->info, queries, nq, workspace, workspace_bytes, arena_capacity, stream))) return rc;
+  if ((rc = kvm_select_plan(&ws->info, queries, nq, nullptr, workspace, workspace_bytes, arena_capacity, stream))) return rc;
   if ((rc = kvm_column_select_hist(values, n, mode, member, workspace, stream))) return rc;
   if ((rc = kvm_select_resolve(workspace, stream))) return rc;
   if ((rc = kvm_column_select_compact(values, n, mode, member, workspace, stream))) return rc;
-  return kvm_select_finish(workspace, nullptr, 0, nullptr, results, stream);
+  return kvm_select_finish(workspace, nullptr, 0, nullptr, results, nullptr, stream);
 }
 
 // ------------------------------------------------------------------ allocation-free variant

@@ -128,22 +128,32 @@ class ShardedAnalyzer(engine.LogAnalyzer):
         nq = len(queries)
         n_global = int(stats.n_total)
 
-        hist_d = torch.empty((4, num_bins), dtype=torch.int64, device=dev)
+        assert num_bins <= N.KVM_HIST_MAX_BINS, "sharded analysis folds the histograms into the select"
+        hist_d = torch.zeros((4, num_bins), dtype=torch.int64, device=dev)
+        hspec = self.hist_spec(num_bins)
         series_d, nb = None, 0
+        extras = N.LogExtrasC()
         if series_window_s is not None and n_global > 0 and not math.isnan(stats.min_start_ms):
             t0, t1 = stats.min_start_ms / 1000.0, stats.max_end_ms / 1000.0
-            nb = min(max(1, int(math.ceil((t1 - t0) / series_window_s)) + 1), max_series_bins)
+            nb = max(1, int(math.ceil((t1 - t0) / series_window_s)) + 1)
+            if nb > max_series_bins:
+                raise N.NativeError("window series needs more than max_series_bins windows")
             series_d = torch.empty((3, nb), dtype=torch.int64, device=dev)
             dropped_d = torch.empty(1, dtype=torch.int64, device=dev)
+            extras.series_window_ms = float(series_window_s) * 1000.0
+            extras.series_max_bins = nb
+            extras.series = series_d.data_ptr()
+            extras.series_dropped = dropped_d.data_ptr()
 
         arena = self._sel_cap
         while True:
             ws, fl = self._sel_ws.data_ptr(), self._flags.data_ptr()
             with tm.stage("select_plan"):
-                N.check(lib.kvm_select_plan(self._stats_d.data_ptr() + N.LogStatsC.sets.offset, queries, nq, ws,
-                                            self._sel_ws.numel(), arena, st), "kvm_select_plan")
+                N.check(lib.kvm_select_plan(self._stats_d.data_ptr() + N.LogStatsC.sets.offset, queries, nq,
+                                            C.byref(hspec), ws, self._sel_ws.numel(), arena, st), "kvm_select_plan")
             with tm.stage("select_hist"):
-                N.check(lib.kvm_log_select_hist(C.byref(log_c), fl, ws, st), "kvm_log_select_hist")
+                N.check(lib.kvm_log_select_hist(C.byref(log_c), fl, self._stats_d.data_ptr(), C.byref(extras),
+                                                ws, st), "kvm_log_select_hist")
             hist = self._wrap(lib.kvm_select_hist_ptr(ws), N.KVM_MAX_SETS * self._bins)
             with tm.stage("allreduce_hist"):
                 dist.all_reduce(hist, op=dist.ReduceOp.SUM, group=grp)
@@ -166,27 +176,18 @@ class ShardedAnalyzer(engine.LogAnalyzer):
         counts_all = torch.empty(self.world * N.KVM_MAX_QUERIES, dtype=torch.int64, device=dev)
         arena_local = self._wrap(lib.kvm_select_arena_ptr(ws), max(used, 1))
         arena_all = torch.empty(self.world * max(used, 1), dtype=torch.int64, device=dev)
+        edge = self._wrap(lib.kvm_select_edge_ptr(ws), N.KVM_MAX_HISTS * N.KVM_HIST_MAX_BINS)
         with tm.stage("allgather_candidates"):
             dist.all_gather_into_tensor(counts_all, counts_local, group=grp)
             dist.all_gather_into_tensor(arena_all, arena_local, group=grp)
+            dist.all_reduce(edge, op=dist.ReduceOp.SUM, group=grp)
         ptrs = (C.c_void_p * self.world)(*[arena_all.data_ptr() + 8 * r * max(used, 1) for r in range(self.world)])
         with tm.stage("select_finish"):
+            # global fine histogram + global edge counters -> global value histograms on every rank
             N.check(lib.kvm_select_finish(ws, ptrs, self.world, counts_all.data_ptr(),
-                                          self._results_d.data_ptr(), st), "kvm_select_finish")
+                                          self._results_d.data_ptr(), hist_d.data_ptr(), st), "kvm_select_finish")
         self.launches += 1
-
-        with tm.stage("histograms"):
-            N.check(lib.kvm_log_histograms(C.byref(log_c), fl, self._stats_d.data_ptr(), num_bins,
-                                           hist_d.data_ptr(), self._hist_ws.data_ptr(), self._hist_ws.numel(), st),
-                    "kvm_log_histograms")
-        self.launches += 2
-        dist.all_reduce(hist_d, op=dist.ReduceOp.SUM, group=grp)
         if series_d is not None:
-            with tm.stage("series"):
-                N.check(lib.kvm_log_series(C.byref(log_c), fl, self._stats_d.data_ptr(),
-                                           float(series_window_s) * 1000.0, nb, series_d.data_ptr(),
-                                           dropped_d.data_ptr(), st), "kvm_log_series")
-            self.launches += 1
             dist.all_reduce(series_d, op=dist.ReduceOp.SUM, group=grp)
             dist.all_reduce(dropped_d, op=dist.ReduceOp.SUM, group=grp)
         self._results_h.copy_(self._results_d, non_blocking=True)

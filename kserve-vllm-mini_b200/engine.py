@@ -244,10 +244,9 @@ class LogAnalyzer:
             self._sel_ws = torch.empty(self.lib.kvm_select_workspace_bytes(cap), dtype=torch.uint8, device=self.device)
             self._sel_cap = cap
 
-    def scan(self, dlog: DeviceLog, cold_times: Sequence[float], cold_window_s: float = 30.0,
-             cold_mask: Optional[torch.Tensor] = None) -> N.LogStatsC:
-        """K1: one pass, returns the stats struct (synchronises).  `cold_mask` (uint8 per row)
-        replaces the time-based classification (cost_estimator's is_cold_start column)."""
+    def _launch_scan(self, dlog: DeviceLog, cold_times: Sequence[float], cold_window_s: float = 30.0,
+                     cold_mask: Optional[torch.Tensor] = None) -> None:
+        """K1, stream-ordered: stats land in self._stats_d, flags in self._flags."""
         self._ensure(dlog.n)
         st = _stream_ptr(self.device)
         cold = sorted(float(c) for c in cold_times)
@@ -260,76 +259,105 @@ class LogAnalyzer:
                                           self._flags.data_ptr(), self._stats_d.data_ptr(),
                                           self._scan_ws.data_ptr(), self._scan_ws.numel(), st), "kvm_log_scan")
         self.launches += 1
+
+    def scan(self, dlog: DeviceLog, cold_times: Sequence[float], cold_window_s: float = 30.0,
+             cold_mask: Optional[torch.Tensor] = None) -> N.LogStatsC:
+        """K1: one pass, returns the stats struct (synchronises).  `cold_mask` (uint8 per row)
+        replaces the time-based classification (cost_estimator's is_cold_start column)."""
+        self._launch_scan(dlog, cold_times, cold_window_s, cold_mask)
         self._stats_h.copy_(self._stats_d, non_blocking=True)
         torch.cuda.current_stream(self.device).synchronize()
         return N.LogStatsC.from_buffer_copy(self._stats_h.numpy().tobytes())
 
+    @staticmethod
+    def hist_spec(num_bins: int) -> N.HistSpecC:
+        """The four histograms of analyze.py:149-152 as a kvm_hist_spec."""
+        hs = N.HistSpecC()
+        hs.nhist, hs.num_bins = 4, num_bins
+        for i, (col, mask) in enumerate(((N.COL_TTFB, TTFB_ALL), (N.COL_TLLT, 1 << N.SET_TLLT),
+                                         (N.COL_GEN, 1 << N.SET_GEN), (N.COL_PERTOK, 1 << N.SET_PERTOK))):
+            hs.col[i], hs.set_mask[i] = col, mask
+        return hs
+
     def analyze(self, dlog: DeviceLog, cold_times: Sequence[float] = (), num_bins: int = 20,
                 series_window_s: Optional[float] = 1.0, max_series_bins: int = 1 << 24,
                 quantiles: Sequence[Quantile] = ANALYZE_QUANTILES) -> RawAnalysis:
-        """scan -> (sync) -> select + histograms + series -> (sync).  Two host round trips."""
+        """scan -> plan -> hist(+series) -> resolve -> compact -> finish, all stream-ordered;
+        ONE host synchronisation at the end (plus a small read-back of the series)."""
         self.launches = 0
-        stats = self.scan(dlog, cold_times)
-        st = _stream_ptr(self.device)
+        lib, tm, dev = self.lib, self.timer, self.device
+        self._launch_scan(dlog, cold_times)
+        st = _stream_ptr(dev)
         log_c = dlog.c_struct()
         queries = build_queries(quantiles)
         nq = len(queries)
         assert nq <= N.KVM_MAX_QUERIES
+        fused_hists = num_bins <= N.KVM_HIST_MAX_BINS
+        hist_d = torch.zeros((4, num_bins), dtype=torch.int64, device=dev)
+        hspec = self.hist_spec(num_bins) if fused_hists else None
 
-        hist_d = torch.empty((4, num_bins), dtype=torch.int64, device=self.device)
-        series_d = None
-        nb = 0
-        if series_window_s is not None and dlog.n > 0 and not math.isnan(stats.min_start_ms):
-            # number of windows: ceil(duration/window), at least the bin of the last start
-            t0, t1 = stats.min_start_ms / 1000.0, stats.max_end_ms / 1000.0
-            nb = max(1, int(math.ceil((t1 - t0) / series_window_s)) + 1)
-            nb = min(nb, max_series_bins)
-            series_d = torch.empty((3, nb), dtype=torch.int64, device=self.device)
-            dropped_d = torch.empty(1, dtype=torch.int64, device=self.device)
-
+        want_series = series_window_s is not None and dlog.n > 0
+        cap = getattr(self, "_series_cap", 1 << 16)
         arena = self._sel_cap
         while True:
+            extras = N.LogExtrasC()
+            if want_series:
+                if getattr(self, "_series_d", None) is None or self._series_d.shape[1] < cap:
+                    self._series_d = torch.empty((3, cap), dtype=torch.int64, device=dev)
+                    self._dropped_d = torch.empty(1, dtype=torch.int64, device=dev)
+                extras.series_window_ms = float(series_window_s) * 1000.0
+                extras.series_max_bins = int(self._series_d.shape[1])
+                extras.series = self._series_d.data_ptr()
+                extras.series_dropped = self._dropped_d.data_ptr()
             ws, fl = self._sel_ws.data_ptr(), self._flags.data_ptr()
-            lib, tm = self.lib, self.timer
             with tm.stage("select_plan"):
-                N.check(lib.kvm_select_plan(self._stats_d.data_ptr() + N.LogStatsC.sets.offset, queries, nq, ws,
+                N.check(lib.kvm_select_plan(self._stats_d.data_ptr() + N.LogStatsC.sets.offset, queries, nq,
+                                            C.byref(hspec) if hspec is not None else None, ws,
                                             self._sel_ws.numel(), arena, st), "kvm_select_plan")
             with tm.stage("select_hist"):
-                N.check(lib.kvm_log_select_hist(C.byref(log_c), fl, ws, st), "kvm_log_select_hist")
+                N.check(lib.kvm_log_select_hist(C.byref(log_c), fl, self._stats_d.data_ptr(), C.byref(extras),
+                                                ws, st), "kvm_log_select_hist")
             with tm.stage("select_resolve"):
                 N.check(lib.kvm_select_resolve(ws, st), "kvm_select_resolve")
             with tm.stage("select_compact"):
                 N.check(lib.kvm_log_select_compact(C.byref(log_c), fl, ws, st), "kvm_log_select_compact")
             with tm.stage("select_finish"):
-                N.check(lib.kvm_select_finish(ws, None, 0, None, self._results_d.data_ptr(), st), "kvm_select_finish")
+                N.check(lib.kvm_select_finish(ws, None, 0, None, self._results_d.data_ptr(),
+                                              hist_d.data_ptr() if fused_hists else None, st), "kvm_select_finish")
             self.launches += 5
-            with tm.stage("histograms"):
-                N.check(lib.kvm_log_histograms(C.byref(log_c), fl, self._stats_d.data_ptr(),
-                                               num_bins, hist_d.data_ptr(), self._hist_ws.data_ptr(),
-                                               self._hist_ws.numel(), st), "kvm_log_histograms")
-            self.launches += 2
-            if series_d is not None:
-                with tm.stage("series"):
-                    N.check(lib.kvm_log_series(C.byref(log_c), fl, self._stats_d.data_ptr(),
-                                               float(series_window_s) * 1000.0, nb, series_d.data_ptr(),
-                                               dropped_d.data_ptr(), st), "kvm_log_series")
-                self.launches += 1
+            if not fused_hists:
+                with tm.stage("histograms"):
+                    N.check(lib.kvm_log_histograms(C.byref(log_c), fl, self._stats_d.data_ptr(),
+                                                   num_bins, hist_d.data_ptr(), self._hist_ws.data_ptr(),
+                                                   self._hist_ws.numel(), st), "kvm_log_histograms")
+                self.launches += 2
+            self._stats_h.copy_(self._stats_d, non_blocking=True)
             self._results_h.copy_(self._results_d, non_blocking=True)
-            rc = self.lib.kvm_select_status(self._sel_ws.data_ptr(), st)   # synchronises
+            rc = self.lib.kvm_select_status(self._sel_ws.data_ptr(), st)   # the one synchronisation
+            stats = N.LogStatsC.from_buffer_copy(self._stats_h.numpy().tobytes())
             if rc == N.KVM_ERR_ARENA:
                 # pathological concentration: retry once with room for every key of every query
                 arena = max(2 * arena, dlog.n * 4 + 1024)
                 self._ensure(dlog.n, arena)
+                self.launches -= 5
                 continue
             N.check(rc, "kvm_log_select")
+            series = None
+            if want_series and not math.isnan(stats.min_start_ms):
+                t0, t1 = stats.min_start_ms / 1000.0, stats.max_end_ms / 1000.0
+                nb = max(1, int(math.ceil((t1 - t0) / series_window_s)) + 1)
+                if int(self._dropped_d.item()) != 0:
+                    if nb > max_series_bins:
+                        raise N.NativeError("window series needs more than max_series_bins windows")
+                    cap = nb + 1           # now known exactly: redo with room for every window
+                    self._series_cap = cap
+                    self._series_d = None
+                    self.launches -= 5
+                    continue
+                series = self._series_d[:, :min(nb, self._series_d.shape[1])].cpu().numpy()
             break
 
         res = np.frombuffer(self._results_h.numpy().tobytes(), dtype=RESULT_DTYPE)[:nq]
-        series = None
-        if series_d is not None:
-            series = series_d.cpu().numpy()
-            if int(dropped_d.item()) != 0:
-                raise N.NativeError("kvm_log_series dropped rows: raise max_series_bins")
         return RawAnalysis(stats=stats, order=results_to_orderstats(res, quantiles),
                            hist_counts=hist_d.cpu().numpy(), num_bins=num_bins, series=series,
                            series_window_s=series_window_s or 1.0, flags=self._flags[:dlog.n])
