@@ -26,95 +26,201 @@ enum {
   NSLOTS = D_LAT + 2
 };
 
+// Per-thread accumulator of the scan.  Row counts are 32-bit (a thread sees far fewer than
+// 2^31 rows), token sums 64-bit, ranges tracked as doubles (fmin/fmax skip NaN) and turned
+// into ordered keys only in the reduction.
 struct LogAcc {
-  int64_t sum[NSUM];
-  uint64_t kmin[KVM_LOG_NCOLS + 1];
-  uint64_t kmax[KVM_LOG_NCOLS + 1];
+  int32_t cnt[NSUM];        // counters; the three token slots are unused here
+  int64_t tok[3];           // S_CTOK, S_TTOK, S_TTOK_COLD
+  double vmin[KVM_LOG_NCOLS + 1];
+  double vmax[KVM_LOG_NCOLS + 1];
   kvm_dd ttfb, lat;
 
   __device__ __forceinline__ void init() {
+    const double inf = __longlong_as_double(0x7ff0000000000000ll);
 #pragma unroll
-    for (int i = 0; i < NSUM; ++i) sum[i] = 0;
+    for (int i = 0; i < NSUM; ++i) cnt[i] = 0;
+    tok[0] = tok[1] = tok[2] = 0;
 #pragma unroll
     for (int i = 0; i <= KVM_LOG_NCOLS; ++i) {
-      kmin[i] = ~0ull;
-      kmax[i] = 0ull;
+      vmin[i] = inf;
+      vmax[i] = -inf;
     }
     ttfb = {0.0, 0.0};
     lat = {0.0, 0.0};
   }
   __device__ __forceinline__ void range(int c, double v) {
-    uint64_t k = kvm_key(v);
-    kmin[c] = k < kmin[c] ? k : kmin[c];
-    kmax[c] = k > kmax[c] ? k : kmax[c];
+    vmin[c] = fmin(vmin[c], v);
+    vmax[c] = fmax(vmax[c], v);
+  }
+  __device__ __forceinline__ int64_t sum(int s) const {
+    return s == S_CTOK ? tok[0] : s == S_TTOK ? tok[1] : s == S_TTOK_COLD ? tok[2] : (int64_t)cnt[s];
+  }
+  // ordered keys of the range; an untouched range gives kmin > kmax.  A zero bound is widened
+  // to cover both signed zeros (fmin/fmax do not order -0.0 against +0.0).
+  __device__ __forceinline__ uint64_t kmin(int c) const {
+    return vmin[c] == 0.0 ? kvm_key(-0.0) : kvm_key(vmin[c]);
+  }
+  __device__ __forceinline__ uint64_t kmax(int c) const {
+    return vmax[c] == 0.0 ? kvm_key(0.0) : kvm_key(vmax[c]);
   }
 };
 
-__device__ __forceinline__ bool is_cold(double t_s, const double* cold, int nc, double window) {
-  // largest c <= t decides (c + window is monotone in c)
-  int lo = 0, hi = nc;
-  while (lo < hi) {
-    int mid = (lo + hi) >> 1;
-    if (cold[mid] <= t_s) lo = mid + 1; else hi = mid;
+// Cold-start classification (analyze.py:402-419): row is cold iff some cold start c has
+// c <= start_ms/1000.0 <= c + window.  x/1000.0 is monotone in x, so each cold start is turned
+// once into the closed interval [lo, hi] of start_ms values that satisfy the reference
+// expression (bisection over the ordered doubles, evaluating that expression), and rows are
+// classified with comparisons only.  With sorted cold starts lo[] and hi[] are both ascending,
+// so the last interval with lo <= start decides.
+struct ColdTable {
+  const double* lo;
+  const double* hi;
+  int n;
+};
+
+__device__ __forceinline__ void cold_interval(double c, double window, double* lo, double* hi) {
+  const double c_end = c + window;
+  // smallest s with s/1000.0 >= c
+  uint64_t a = kvm_key(-1.7976931348623157e308), z = kvm_key(1.7976931348623157e308);
+  if (kvm_unkey(a) / 1000.0 >= c) z = a;
+  while (z - a > 1) {
+    const uint64_t mid = a + ((z - a) >> 1);
+    if (kvm_unkey(mid) / 1000.0 >= c) z = mid; else a = mid;
   }
-  return lo > 0 && t_s <= cold[lo - 1] + window;
+  *lo = kvm_unkey(z);
+  // largest s with s/1000.0 <= c_end  ==  predecessor of the smallest s with s/1000.0 > c_end
+  a = kvm_key(-1.7976931348623157e308);
+  z = kvm_key(1.7976931348623157e308);
+  if (!(kvm_unkey(z) / 1000.0 > c_end)) {
+    *hi = kvm_unkey(z);
+    return;
+  }
+  while (z - a > 1) {
+    const uint64_t mid = a + ((z - a) >> 1);
+    if (kvm_unkey(mid) / 1000.0 > c_end) z = mid; else a = mid;
+  }
+  *hi = kvm_unkey(a);
+}
+
+__device__ __forceinline__ bool is_cold(double start_ms, const ColdTable& t) {
+  int lo = 0, hi = t.n;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (t.lo[mid] <= start_ms) lo = mid + 1; else hi = mid;
+  }
+  return lo > 0 && start_ms <= t.hi[lo - 1];
 }
 
 __device__ __forceinline__ uint8_t process_row(LogAcc& a, double start, double lat, double ttfb,
                                                double tllt, int64_t status, int64_t ctok,
-                                               int64_t ttok, const double* cold, int nc,
-                                               double window, int cold_override) {
+                                               int64_t ttok, const ColdTable& cold, int cold_override) {
   const bool ok = status == 200;
-  const bool cold_row = cold_override >= 0 ? cold_override != 0
-                                           : (nc > 0 && is_cold(start / 1000.0, cold, nc, window));
-  if (!kvm_isnan(start)) {
-    uint64_t ks = kvm_key(start);
-    a.kmin[KVM_LOG_NCOLS] = ks < a.kmin[KVM_LOG_NCOLS] ? ks : a.kmin[KVM_LOG_NCOLS];
-  }
-  const double end = start + lat;
-  if (!kvm_isnan(end)) {
-    uint64_t ke = kvm_key(end);
-    a.kmax[KVM_LOG_NCOLS] = ke > a.kmax[KVM_LOG_NCOLS] ? ke : a.kmax[KVM_LOG_NCOLS];
-  }
-  a.sum[S_COLD] += cold_row;
+  const bool cold_row = cold_override >= 0 ? cold_override != 0 : (cold.n > 0 && is_cold(start, cold));
+  a.vmin[KVM_LOG_NCOLS] = fmin(a.vmin[KVM_LOG_NCOLS], start);        // NaN skipped by fmin/fmax
+  a.vmax[KVM_LOG_NCOLS] = fmax(a.vmax[KVM_LOG_NCOLS], start + lat);  // analyze.py:187
+  a.cnt[S_COLD] += cold_row;
   uint8_t f = (ok ? KVM_F_SUCCESS : 0) | (cold_row ? KVM_F_COLD : 0) | (ctok > 0 ? KVM_F_TOKENS : 0);
   if (ok) {
-    a.sum[S_SUCCESS] += 1;
-    a.sum[S_COLD_SUCCESS] += cold_row;
-    a.sum[S_CTOK] += ctok;
-    a.sum[S_TTOK] += ttok;
-    a.sum[S_TTOK_COLD] += cold_row ? ttok : 0;
+    a.cnt[S_SUCCESS] += 1;
+    a.cnt[S_COLD_SUCCESS] += cold_row;
+    a.tok[0] += ctok;
+    a.tok[1] += ttok;
+    a.tok[2] += cold_row ? ttok : 0;
     if (!kvm_isnan(lat)) {
-      a.sum[S_CNT0 + (cold_row ? KVM_SET_LAT_COLD : KVM_SET_LAT_WARM)] += 1;
+      a.cnt[S_CNT0 + KVM_SET_LAT_COLD] += cold_row;
+      a.cnt[S_CNT0 + KVM_SET_LAT_WARM] += !cold_row;
       a.range(KVM_COL_LAT, lat);
       a.lat = kvm_dd_add(a.lat, lat);
     }
     const bool has_ttfb = !kvm_isnan(ttfb), has_tllt = !kvm_isnan(tllt);
     if (has_ttfb) {
-      a.sum[S_CNT0 + (cold_row ? KVM_SET_TTFB_COLD : KVM_SET_TTFB_WARM)] += 1;
+      a.cnt[S_CNT0 + KVM_SET_TTFB_COLD] += cold_row;
+      a.cnt[S_CNT0 + KVM_SET_TTFB_WARM] += !cold_row;
       a.range(KVM_COL_TTFB, ttfb);
       a.ttfb = kvm_dd_add(a.ttfb, ttfb);
     }
     if (has_tllt) {
-      a.sum[S_CNT0 + KVM_SET_TLLT] += 1;
+      a.cnt[S_CNT0 + KVM_SET_TLLT] += 1;
       a.range(KVM_COL_TLLT, tllt);
     }
     if (has_ttfb && has_tllt && ctok > 0) {
       f |= KVM_F_GEN;
-      a.sum[S_GEN_ROWS] += 1;
+      a.cnt[S_GEN_ROWS] += 1;
       const double g = tllt - ttfb;  // analyze.py:144
       if (!kvm_isnan(g)) {
-        a.sum[S_CNT0 + KVM_SET_GEN] += 1;
+        a.cnt[S_CNT0 + KVM_SET_GEN] += 1;
         a.range(KVM_COL_GEN, g);
         const double pt = g / (double)ctok;  // analyze.py:146
         if (!kvm_isnan(pt)) {
-          a.sum[S_CNT0 + KVM_SET_PERTOK] += 1;
+          a.cnt[S_CNT0 + KVM_SET_PERTOK] += 1;
           a.range(KVM_COL_PERTOK, pt);
         }
       }
     }
   }
   return f;
+}
+
+// Warp-level reduction of an accumulator into one row of 64-bit slots (lane 0 writes).
+__device__ __forceinline__ void acc_warp_reduce(const LogAcc& a, uint64_t* slots, int lane) {
+#pragma unroll
+  for (int s = 0; s < NSUM; ++s) {
+    const int64_t v = kvm_warp_sum(a.sum(s));
+    if (lane == 0) slots[s] = (uint64_t)v;
+  }
+#pragma unroll
+  for (int c = 0; c <= KVM_LOG_NCOLS; ++c) {
+    const uint64_t lo = kvm_warp_min(a.kmin(c)), hi = kvm_warp_max(a.kmax(c));
+    if (lane == 0) {
+      slots[M_KMIN0 + c] = lo;
+      slots[X_KMAX0 + c] = hi;
+    }
+  }
+  const kvm_dd t = kvm_warp_sum(a.ttfb), l = kvm_warp_sum(a.lat);
+  if (lane == 0) {
+    slots[D_TTFB] = (uint64_t)__double_as_longlong(t.hi);
+    slots[D_TTFB + 1] = (uint64_t)__double_as_longlong(t.lo);
+    slots[D_LAT] = (uint64_t)__double_as_longlong(l.hi);
+    slots[D_LAT + 1] = (uint64_t)__double_as_longlong(l.lo);
+  }
+}
+
+// Final slots -> kvm_log_stats (thread 0 of whoever holds the totals).
+__device__ __forceinline__ void stats_from_slots(const uint64_t* fin, int64_t n, kvm_log_stats& r) {
+  const double nan = __longlong_as_double(0x7ff8000000000000ll);
+  r.n_total = n;
+  r.n_success = (int64_t)fin[S_SUCCESS];
+  r.n_cold = (int64_t)fin[S_COLD];
+  r.n_cold_success = (int64_t)fin[S_COLD_SUCCESS];
+  r.sum_completion_tokens = (int64_t)fin[S_CTOK];
+  r.sum_total_tokens = (int64_t)fin[S_TTOK];
+  r.sum_total_tokens_cold = (int64_t)fin[S_TTOK_COLD];
+  r.n_gen_rows = (int64_t)fin[S_GEN_ROWS];
+  // start / end: an untouched (or all-NaN) range has min > max
+  r.min_start_ms = fin[M_START] > kvm_key(1.7976931348623157e308) ? nan : kvm_unkey(fin[M_START]);
+  r.max_end_ms = fin[X_END] < kvm_key(-1.7976931348623157e308) ? nan : kvm_unkey(fin[X_END]);
+  r.ttfb_sum_hi = __longlong_as_double((long long)fin[D_TTFB]);
+  r.ttfb_sum_lo = __longlong_as_double((long long)fin[D_TTFB + 1]);
+  r.lat_sum_hi = __longlong_as_double((long long)fin[D_LAT]);
+  r.lat_sum_lo = __longlong_as_double((long long)fin[D_LAT + 1]);
+  for (int s = 0; s < KVM_MAX_SETS; ++s) {
+    r.sets.count[s] = s < KVM_LOG_NSETS ? (int64_t)fin[S_CNT0 + s] : 0;
+    r.sets.set_col[s] = 0;
+  }
+  for (int c = 0; c < KVM_MAX_COLS; ++c) {
+    const bool used = c < KVM_LOG_NCOLS && fin[M_KMIN0 + c] <= fin[X_KMAX0 + c];
+    r.sets.kmin[c] = used ? fin[M_KMIN0 + c] : ~0ull;
+    r.sets.kmax[c] = used ? fin[X_KMAX0 + c] : 0ull;
+  }
+  r.sets.set_col[KVM_SET_LAT_COLD] = KVM_COL_LAT;
+  r.sets.set_col[KVM_SET_LAT_WARM] = KVM_COL_LAT;
+  r.sets.set_col[KVM_SET_TTFB_COLD] = KVM_COL_TTFB;
+  r.sets.set_col[KVM_SET_TTFB_WARM] = KVM_COL_TTFB;
+  r.sets.set_col[KVM_SET_TLLT] = KVM_COL_TLLT;
+  r.sets.set_col[KVM_SET_GEN] = KVM_COL_GEN;
+  r.sets.set_col[KVM_SET_PERTOK] = KVM_COL_PERTOK;
+  r.sets.nsets = KVM_LOG_NSETS;
+  r.sets.ncols = KVM_LOG_NCOLS;
 }
 
 __device__ __forceinline__ int64_t resolve_rank(int kind, double p, int64_t n, int64_t given) {

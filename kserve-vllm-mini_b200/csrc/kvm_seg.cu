@@ -64,7 +64,8 @@ struct SegSmem {
   uint32_t cnt20[NH][SEG_NB_MAX];
   uint32_t flag20[NH][BINS / 32];
   uint32_t bmap[KVM_LOG_NCOLS][BINS / 32];
-  double cold[SEG_COLD];
+  double cold_lo[SEG_COLD];
+  double cold_hi[SEG_COLD];
   SegBucket bk[SEG_MAXQ];
   SegQ q[SEG_MAXQ];
   SegCol col[KVM_MAX_COLS];
@@ -175,15 +176,16 @@ seg_analyze_kernel(kvm_request_log log, const int64_t* __restrict__ run_offsets,
     const int64_t r0 = run_offsets[run], r1 = run_offsets[run + 1];
     const bool vec = base_aligned;
     // ---------------- P1 scan
-    int nc = 0;
-    const double* cold = nullptr;
+    ColdTable cold{S.cold_lo, S.cold_hi, 0};
+    bool cold_too_many = false;
     if (cold_offsets) {
       const int64_t c0 = cold_offsets[run], c1 = cold_offsets[run + 1];
-      nc = (int)(c1 - c0);
-      cold = cold_times + c0;
-      if (nc > 0 && nc <= SEG_COLD) {
-        for (int i = tid; i < nc; i += SEG_THREADS) S.cold[i] = cold[i];
-        cold = S.cold;
+      const int nc = (int)(c1 - c0);
+      if (nc > SEG_COLD) cold_too_many = true;   // host redoes this run through the flat path
+      else {
+        cold.n = nc;
+        for (int i = tid; i < nc; i += SEG_THREADS)
+          cold_interval(cold_times[c0 + i], cold_window, &S.cold_lo[i], &S.cold_hi[i]);
       }
     }
     for (int i = tid; i < KVM_LOG_NSETS * BINS; i += SEG_THREADS) (&S.hist[0][0])[i] = 0;
@@ -205,30 +207,9 @@ seg_analyze_kernel(kvm_request_log log, const int64_t* __restrict__ run_offsets,
     a.init();
     seg_rows_full(log, r0, r1, vec, [&](int64_t i, double st, double la, double tf, double tl, int64_t ss,
                                         int64_t ct, int64_t tt) {
-      flags[i] = process_row(a, st, la, tf, tl, ss, ct, tt, cold, nc, cold_window, -1);
+      flags[i] = process_row(a, st, la, tf, tl, ss, ct, tt, cold, -1);
     });
-#pragma unroll
-    for (int s = 0; s < NSUM; ++s) {
-      const int64_t v = kvm_warp_sum(a.sum[s]);
-      if (lane == 0) S.red[warp][s] = (uint64_t)v;
-    }
-#pragma unroll
-    for (int c = 0; c <= KVM_LOG_NCOLS; ++c) {
-      const uint64_t lo = kvm_warp_min(a.kmin[c]), hi = kvm_warp_max(a.kmax[c]);
-      if (lane == 0) {
-        S.red[warp][M_KMIN0 + c] = lo;
-        S.red[warp][X_KMAX0 + c] = hi;
-      }
-    }
-    {
-      const kvm_dd t = kvm_warp_sum(a.ttfb), l = kvm_warp_sum(a.lat);
-      if (lane == 0) {
-        S.red[warp][D_TTFB] = (uint64_t)__double_as_longlong(t.hi);
-        S.red[warp][D_TTFB + 1] = (uint64_t)__double_as_longlong(t.lo);
-        S.red[warp][D_LAT] = (uint64_t)__double_as_longlong(l.hi);
-        S.red[warp][D_LAT + 1] = (uint64_t)__double_as_longlong(l.lo);
-      }
-    }
+    acc_warp_reduce(a, S.red[warp], lane);
     __syncthreads();
     if (tid < NMAX_END) {
       uint64_t acc = S.red[0][tid];
@@ -251,38 +232,8 @@ seg_analyze_kernel(kvm_request_log log, const int64_t* __restrict__ run_offsets,
     __syncthreads();
     // ---------------- P2 plan
     if (tid == 0) {
-      kvm_log_stats& r = S.stats;
-      r.n_total = r1 - r0;
-      r.n_success = (int64_t)S.fin[S_SUCCESS];
-      r.n_cold = (int64_t)S.fin[S_COLD];
-      r.n_cold_success = (int64_t)S.fin[S_COLD_SUCCESS];
-      r.sum_completion_tokens = (int64_t)S.fin[S_CTOK];
-      r.sum_total_tokens = (int64_t)S.fin[S_TTOK];
-      r.sum_total_tokens_cold = (int64_t)S.fin[S_TTOK_COLD];
-      r.n_gen_rows = (int64_t)S.fin[S_GEN_ROWS];
-      r.min_start_ms = S.fin[M_START] == ~0ull ? nan : kvm_unkey(S.fin[M_START]);
-      r.max_end_ms = S.fin[X_END] == 0ull ? nan : kvm_unkey(S.fin[X_END]);
-      r.ttfb_sum_hi = __longlong_as_double((long long)S.fin[D_TTFB]);
-      r.ttfb_sum_lo = __longlong_as_double((long long)S.fin[D_TTFB + 1]);
-      r.lat_sum_hi = __longlong_as_double((long long)S.fin[D_LAT]);
-      r.lat_sum_lo = __longlong_as_double((long long)S.fin[D_LAT + 1]);
-      for (int s = 0; s < KVM_MAX_SETS; ++s) {
-        r.sets.count[s] = s < KVM_LOG_NSETS ? (int64_t)S.fin[S_CNT0 + s] : 0;
-        r.sets.set_col[s] = 0;
-      }
-      for (int c = 0; c < KVM_MAX_COLS; ++c) {
-        r.sets.kmin[c] = c < KVM_LOG_NCOLS ? S.fin[M_KMIN0 + c] : ~0ull;
-        r.sets.kmax[c] = c < KVM_LOG_NCOLS ? S.fin[X_KMAX0 + c] : 0ull;
-      }
-      r.sets.set_col[KVM_SET_LAT_COLD] = KVM_COL_LAT;
-      r.sets.set_col[KVM_SET_LAT_WARM] = KVM_COL_LAT;
-      r.sets.set_col[KVM_SET_TTFB_COLD] = KVM_COL_TTFB;
-      r.sets.set_col[KVM_SET_TTFB_WARM] = KVM_COL_TTFB;
-      r.sets.set_col[KVM_SET_TLLT] = KVM_COL_TLLT;
-      r.sets.set_col[KVM_SET_GEN] = KVM_COL_GEN;
-      r.sets.set_col[KVM_SET_PERTOK] = KVM_COL_PERTOK;
-      r.sets.nsets = KVM_LOG_NSETS;
-      r.sets.ncols = KVM_LOG_NCOLS;
+      stats_from_slots(S.fin, r1 - r0, S.stats);
+      if (cold_too_many) S.overflow = 1;
     }
     __syncthreads();
     if (tid < KVM_MAX_COLS) {

@@ -87,7 +87,10 @@ struct SelWs {
   uint64_t thr20[NH][NB_MAX];
   uint32_t flag20[NH][BINS / 32];
   unsigned long long edge20[NH][NB_MAX];
-  uint8_t slot[KVM_MAX_COLS][BINS];  // first bucket with that (col, bin); 255 = none
+  uint8_t edge_code[KVM_MAX_COLS][BINS];  // 0: no histogram edge in this fine bin; b: exactly edge b;
+                                          // 255: several edges (rank against all of them)
+  uint16_t tab[KVM_MAX_COLS][BINS];       // low byte: first bucket with that (col, bin), 255 = none;
+                                          // high byte: edge_code
   uint64_t hist[KVM_MAX_SETS][BINS];
   unsigned char stats_scratch[STATS_SCRATCH];
 };
@@ -139,6 +142,8 @@ select_plan_kernel(SelWs* ws, const kvm_set_info* info_in, QueryPack qp, kvm_his
     (&ws->thr20[0][0])[i] = ~0ull;
   }
   for (int i = t; i < NH * (BINS / 32); i += PLAN_THREADS) (&ws->flag20[0][0])[i] = 0;
+  for (int i = t; i < KVM_MAX_COLS * BINS / 4; i += PLAN_THREADS)
+    reinterpret_cast<uint32_t*>(&ws->edge_code[0][0])[i] = 0;
   __syncthreads();
   if (t < KVM_MAX_COLS) {
     ColParam cp{0, 0, 0};
@@ -202,6 +207,21 @@ select_plan_kernel(SelWs* ws, const kvm_set_info* info_in, QueryPack qp, kvm_his
           const uint32_t d = digit_of(T, cps[c].kbase, cps[c].shift);
           atomicOr(&ws->flag20[h][d >> 5], 1u << (d & 31));
         }
+      }
+    }
+  }
+  __syncthreads();
+  // per histogram: which edge (if exactly one) lives in each flagged fine bin
+  if (t < hs.nhist) {
+    const int h = t, c = hs.col[h];
+    if (info.kmin[c] < info.kmax[c]) {
+      uint32_t prev = 0xffffffffu;
+      for (int b = 1; b < hs.num_bins; ++b) {
+        const uint64_t T = ws->thr20[h][b - 1];
+        if (T == ~0ull) break;
+        const uint32_t d = digit_of(T, cps[c].kbase, cps[c].shift);
+        ws->edge_code[c][d] = d == prev ? 255 : (uint8_t)b;
+        prev = d;
       }
     }
   }
@@ -334,8 +354,16 @@ log_hist_kernel(kvm_request_log log, const uint8_t* __restrict__ flags, SelWs* w
   extern __shared__ uint32_t sh[];  // [KVM_LOG_NSETS][BINS]
   __shared__ ColParams cp;
   hist_prologue(ws, sh, KVM_LOG_NSETS, cp);
+  // column parameters in registers: `col` is a literal at every call site of log_row_keys
+  uint64_t kb[KVM_LOG_NCOLS];
+  int shf[KVM_LOG_NCOLS];
+#pragma unroll
+  for (int c = 0; c < KVM_LOG_NCOLS; ++c) {
+    kb[c] = cp.kbase[c];
+    shf[c] = cp.shift[c];
+  }
   auto add = [&](int set, int col, uint64_t key) {
-    atomicAdd(&sh[set * BINS + digit_of(key, cp.kbase[col], cp.shift[col])], 1u);
+    atomicAdd(&sh[set * BINS + digit_of(key, kb[col], shf[col])], 1u);
   };
   const int lane = threadIdx.x & 31;
   const int64_t n = log.n;
@@ -443,8 +471,6 @@ __global__ void __launch_bounds__(RES_THREADS, 1) select_resolve_kernel(SelWs* w
   const int nsets = ws->info.nsets;
 
   for (int i = threadIdx.x; i < nsets * BINS; i += RES_THREADS) hs[i] = (&ws->hist[0][0])[i];
-  for (int i = threadIdx.x; i < KVM_MAX_COLS * BINS / 4; i += RES_THREADS)
-    reinterpret_cast<uint32_t*>(&ws->slot[0][0])[i] = 0xffffffffu;
   if (threadIdx.x < MAXQ) {
     qs[threadIdx.x] = ws->q[threadIdx.x];
     qmask[threadIdx.x] = ws->queries[threadIdx.x].set_mask;
@@ -508,74 +534,91 @@ __global__ void __launch_bounds__(RES_THREADS, 1) select_resolve_kernel(SelWs* w
     }
   }
   __syncthreads();
-  __shared__ Bucket bk[MAXQ];
-  __shared__ int order[MAXQ];
-  __shared__ int newpos[MAXQ];
+  // ---- buckets = distinct (col, bin, mask) among the unresolved queries, in (col, bin, mask)
+  // order so that buckets sharing a fine bin are contiguous.  All O(nq) loops run one thread
+  // per query in parallel.
+  __shared__ uint64_t bkey[MAXQ];   // sort key; ~0 = query needs no bucket
+  __shared__ int is_first[MAXQ];
+  __shared__ int pos_of[MAXQ];
+  __shared__ int64_t off_of[MAXQ];
   __shared__ int nb_s;
-  if (threadIdx.x == 0) {
-    // distinct (col, mask, bin) buckets, then sorted by (col, bin) so that buckets sharing a
-    // fine bin are contiguous (the compact pass finds them through slot[col][bin])
-    int nb = 0;
-    for (int q = 0; q < nq; ++q) {
-      QState& s = qs[q];
-      if (s.status != KVM_Q_OK || s.resolved) continue;
-      int j = -1;
-      for (int k = 0; k < nb; ++k)
-        if (bk[k].col == s.col && bk[k].set_mask == qmask[q] && bk[k].bin == q_bin[q]) {
-          j = k;
-          break;
-        }
-      if (j < 0) {
-        j = nb++;
-        const ColParam cp = cps[s.col];
-        Bucket b;
-        b.base = cp.kbase + ((uint64_t)q_bin[q] << cp.shift);
-        b.shift = cp.shift;
-        b.col = s.col;
-        b.set_mask = qmask[q];
-        b.bin = q_bin[q];
-        b.count = q_cnt[q];
-        b.run = 0;
-        b.pad = 0;
-        bk[j] = b;
-      }
-      s.bucket = j;  // index before sorting; remapped below
-    }
-    for (int k = 0; k < nb; ++k) order[k] = k;
-    for (int a = 1; a < nb; ++a) {  // insertion sort by (col, bin)
-      const int v = order[a];
-      int p = a - 1;
-      while (p >= 0 && (bk[order[p]].col > bk[v].col ||
-                        (bk[order[p]].col == bk[v].col && bk[order[p]].bin > bk[v].bin))) {
-        order[p + 1] = order[p];
-        --p;
-      }
-      order[p + 1] = v;
-    }
-    for (int k = 0; k < nb; ++k) newpos[order[k]] = k;
-    int64_t off = 0;
-    for (int k = 0; k < nb; ++k) {
-      Bucket b = bk[order[k]];
-      int run = 1;
-      while (k + run < nb && bk[order[k + run]].col == b.col && bk[order[k + run]].bin == b.bin) ++run;
-      const bool first = k == 0 || bk[order[k - 1]].col != b.col || bk[order[k - 1]].bin != b.bin;
-      b.run = first ? run : 0;
-      ws->bucket[k] = b;
-      ws->bucket_offsets[k] = off;
-      off += b.count;
-      if (first) ws->slot[b.col][b.bin] = (uint8_t)k;
-    }
-    for (int k = nb; k <= MAXQ; ++k) ws->bucket_offsets[k] = off;
-    ws->nbuckets = nb;
-    ws->arena_used = off;
-    if (off > ws->arena_capacity) ws->status = KVM_ERR_ARENA;
-    nb_s = nb;
+  __shared__ int64_t used_s;
+  const int t = threadIdx.x;
+  for (int i = t; i < KVM_MAX_COLS * BINS; i += RES_THREADS)
+    (&ws->tab[0][0])[i] = (uint16_t)(0x00ffu | ((uint32_t)(&ws->edge_code[0][0])[i] << 8));
+  if (t < MAXQ) {
+    const QState s = qs[t];
+    const bool need = t < nq && s.status == KVM_Q_OK && !s.resolved;
+    bkey[t] = need ? (((uint64_t)s.col << 44) | ((uint64_t)q_bin[t] << 32) | qmask[t]) : ~0ull;
   }
   __syncthreads();
-  if (threadIdx.x < MAXQ) {
-    QState s = qs[threadIdx.x];
-    if (s.status == KVM_Q_OK && !s.resolved && s.bucket >= 0) s.bucket = newpos[s.bucket];
-    ws->q[threadIdx.x] = s;
+  if (t < MAXQ) {
+    const uint64_t k = bkey[t];
+    int first = k != ~0ull;
+    for (int o = 0; o < t && first; ++o) first = bkey[o] != k;
+    is_first[t] = first;
+  }
+  __syncthreads();
+  if (t < MAXQ) {
+    const uint64_t k = bkey[t];
+    int pos = 0;
+    int64_t off = 0;
+    if (k != ~0ull)
+      for (int o = 0; o < MAXQ; ++o)
+        if (is_first[o] && bkey[o] < k) {
+          ++pos;
+          off += q_cnt[o];
+        }
+    pos_of[t] = pos;   // same for every query of the bucket
+    off_of[t] = off;
+  }
+  if (t == 0) {
+    int nb = 0;
+    int64_t used = 0;
+    for (int o = 0; o < MAXQ; ++o)
+      if (is_first[o]) {
+        ++nb;
+        used += q_cnt[o];
+      }
+    nb_s = nb;
+    used_s = used;
+  }
+  __syncthreads();
+  if (t < MAXQ && is_first[t]) {
+    const QState s = qs[t];
+    const ColParam cp = cps[s.col];
+    const uint64_t k = bkey[t];
+    // (col, bin) group: first bucket of the group carries the group's length
+    int smaller_same = 0, group = 0;
+    for (int o = 0; o < MAXQ; ++o)
+      if (is_first[o] && (bkey[o] >> 32) == (k >> 32)) {
+        ++group;
+        smaller_same += bkey[o] < k;
+      }
+    Bucket b;
+    b.base = cp.kbase + ((uint64_t)q_bin[t] << cp.shift);
+    b.shift = cp.shift;
+    b.col = s.col;
+    b.set_mask = qmask[t];
+    b.bin = q_bin[t];
+    b.count = q_cnt[t];
+    b.run = smaller_same == 0 ? group : 0;
+    b.pad = 0;
+    ws->bucket[pos_of[t]] = b;
+    ws->bucket_offsets[pos_of[t]] = off_of[t];
+    if (smaller_same == 0)
+      ws->tab[s.col][b.bin] = (uint16_t)((uint32_t)pos_of[t] | ((uint32_t)ws->edge_code[s.col][b.bin] << 8));
+  }
+  if (t <= MAXQ && t >= nb_s) ws->bucket_offsets[t] = used_s;
+  if (t == 0) {
+    ws->nbuckets = nb_s;
+    ws->arena_used = used_s;
+    if (used_s > ws->arena_capacity) ws->status = KVM_ERR_ARENA;
+  }
+  if (t < MAXQ) {
+    QState s = qs[t];
+    if (bkey[t] != ~0ull) s.bucket = pos_of[t];
+    ws->q[t] = s;
   }
 }
 
@@ -585,46 +628,46 @@ struct CompactSmem {
   Bucket bk[MAXQ];
   int64_t bk_off[MAXQ];
   uint64_t thr[NH][NB_MAX];
-  uint32_t flag[NH][BINS / 32];
   uint32_t edge[NH][NB_MAX];
   int32_t col_hist[KVM_MAX_COLS];
-  int32_t active[NH];
-  int32_t nb;         // buckets
   int32_t num_bins;   // value histogram bins
-  uint8_t slot[KVM_MAX_COLS][BINS];
+  uint16_t tab[KVM_MAX_COLS][BINS];
 };
 
-template <class Stream>
-__device__ __forceinline__ void compact_body(SelWs* ws, uint64_t* __restrict__ arena, int ncols,
-                                             Stream&& stream) {
+template <int NCOLS, class Stream>
+__device__ __forceinline__ void compact_body(SelWs* ws, uint64_t* __restrict__ arena, Stream&& stream) {
   extern __shared__ __align__(16) unsigned char craw[];
   CompactSmem& S = *reinterpret_cast<CompactSmem*>(craw);
   if (ws->status != KVM_OK) return;
-  if (threadIdx.x == 0) {
-    S.nb = ws->nbuckets;
-    S.num_bins = ws->hspec.num_bins;
-  }
+  if (threadIdx.x == 0) S.num_bins = ws->hspec.num_bins;
   if (threadIdx.x < KVM_MAX_COLS) {
     S.cp.kbase[threadIdx.x] = ws->col[threadIdx.x].kbase;
     S.cp.shift[threadIdx.x] = ws->col[threadIdx.x].shift;
     S.col_hist[threadIdx.x] = ws->col_hist[threadIdx.x];
   }
-  if (threadIdx.x < NH) S.active[threadIdx.x] = ws->active20[threadIdx.x];
-  for (int i = threadIdx.x; i < ncols * BINS / 4; i += blockDim.x)
-    reinterpret_cast<uint32_t*>(&S.slot[0][0])[i] = reinterpret_cast<const uint32_t*>(&ws->slot[0][0])[i];
+  for (int i = threadIdx.x; i < NCOLS * BINS / 2; i += blockDim.x)
+    reinterpret_cast<uint32_t*>(&S.tab[0][0])[i] = reinterpret_cast<const uint32_t*>(&ws->tab[0][0])[i];
   for (int i = threadIdx.x; i < NH * NB_MAX; i += blockDim.x) {
     (&S.thr[0][0])[i] = (&ws->thr20[0][0])[i];
     (&S.edge[0][0])[i] = 0;
   }
-  for (int i = threadIdx.x; i < NH * (BINS / 32); i += blockDim.x) (&S.flag[0][0])[i] = (&ws->flag20[0][0])[i];
   for (int i = threadIdx.x; i < MAXQ; i += blockDim.x) {
     S.bk[i] = ws->bucket[i];
     S.bk_off[i] = ws->bucket_offsets[i];
   }
   __syncthreads();
+  uint64_t kb[NCOLS];
+  int shf[NCOLS];
+#pragma unroll
+  for (int c = 0; c < NCOLS; ++c) {
+    kb[c] = S.cp.kbase[c];
+    shf[c] = S.cp.shift[c];
+  }
   stream([&](int set, int col, uint64_t key) {
-    const uint32_t d = digit_of(key, S.cp.kbase[col], S.cp.shift[col]);
-    const uint32_t j0 = S.slot[col][d];
+    const uint32_t d = digit_of(key, kb[col], shf[col]);
+    const uint32_t e = S.tab[col][d];   // one 16-bit lookup decides both rare paths
+    if (e == 0x00ffu) return;
+    const uint32_t j0 = e & 0xffu;
     if (j0 != 255u) {
       const int run = S.bk[j0].run;
       for (int j = j0; j < (int)j0 + run; ++j)
@@ -634,9 +677,13 @@ __device__ __forceinline__ void compact_body(SelWs* ws, uint64_t* __restrict__ a
           if ((int64_t)pos < S.bk[j].count) arena[S.bk_off[j] + (int64_t)pos] = key;
         }
     }
-    const int h = S.col_hist[col];
-    if (h >= 0 && S.active[h] && ((S.flag[h][d >> 5] >> (d & 31)) & 1u))
-      atomicAdd(&S.edge[h][bin_of(key, S.thr[h], S.num_bins)], 1u);
+    const uint32_t code = e >> 8;
+    if (code) {
+      const int h = S.col_hist[col];
+      const int bin = code == 255u ? bin_of(key, S.thr[h], S.num_bins)
+                                   : (int)code - (key < S.thr[h][code - 1] ? 1 : 0);
+      atomicAdd(&S.edge[h][bin], 1u);
+    }
   });
   __syncthreads();
   for (int i = threadIdx.x; i < NH * NB_MAX; i += blockDim.x) {
@@ -648,13 +695,13 @@ __device__ __forceinline__ void compact_body(SelWs* ws, uint64_t* __restrict__ a
 __global__ void __launch_bounds__(SEL_THREADS, 2)
 log_compact_kernel(kvm_request_log log, const uint8_t* __restrict__ flags, bool vec, SelWs* ws,
                    uint64_t* arena) {
-  compact_body(ws, arena, KVM_LOG_NCOLS, [&](auto&& f) { for_each_log_key(log, flags, vec, f); });
+  compact_body<KVM_LOG_NCOLS>(ws, arena, [&](auto&& f) { for_each_log_key(log, flags, vec, f); });
 }
 
 __global__ void __launch_bounds__(SEL_THREADS, 2)
 column_compact_kernel(const double* __restrict__ values, int64_t n, int mode,
                       const void* __restrict__ member, bool vec, SelWs* ws, uint64_t* arena) {
-  compact_body(ws, arena, 1, [&](auto&& f) { for_each_column_key(values, n, mode, member, vec, f); });
+  compact_body<1>(ws, arena, [&](auto&& f) { for_each_column_key(values, n, mode, member, vec, f); });
 }
 
 // ------------------------------------------------------------------ finish
@@ -662,10 +709,11 @@ constexpr int FIN_THREADS = 256;
 constexpr int FIN_BITS = 11;
 constexpr int FIN_BINS = 1 << FIN_BITS;
 constexpr int FIN_SMALL = 1024;  // candidates ranked by counting once this few remain
+constexpr int HIST_CTAS = 16;    // extra CTAs that assemble the value histograms
 
 // CTAs 0..MAXQ-1: one query each - radix select inside the query's bucket, FIN_BITS per pass,
 // switching to rank-by-counting in shared memory once <= FIN_SMALL candidates remain.
-// CTA MAXQ: assembles the value histograms (edge counters + fine bins without an edge).
+// CTAs MAXQ..: assemble the value histograms (edge counters + fine bins without an edge).
 __global__ void __launch_bounds__(FIN_THREADS, 1)
 select_finish_kernel(SelWs* ws, SrcPack src, const int64_t* __restrict__ src_counts,
                      kvm_query_result* __restrict__ results, int64_t* __restrict__ hist_out) {
@@ -676,17 +724,20 @@ select_finish_kernel(SelWs* ws, SrcPack src, const int64_t* __restrict__ src_cou
   __shared__ int64_t sel_below;
   __shared__ uint64_t answer;
 
-  if (blockIdx.x == MAXQ) {
-    // ---- value histograms (hist_out is zero-initialised by the caller)
+  if (blockIdx.x >= MAXQ) {
+    // ---- value histograms (hist_out is zero-initialised by the caller): every CTA takes a
+    // slice of the fine bins; bins without an edge go wholesale into the bin of their lowest key
     const kvm_hist_spec hs = ws->hspec;
     if (hist_out == nullptr || hs.nhist == 0 || ws->status != KVM_OK) return;
     const int nbins = hs.num_bins;
+    const int part = blockIdx.x - MAXQ;
     unsigned long long* out = reinterpret_cast<unsigned long long*>(hist_out);
-    for (int t = threadIdx.x; t < hs.nhist * BINS; t += FIN_THREADS) {
+    const int nsets = ws->info.nsets;
+    for (int t = part * FIN_THREADS + threadIdx.x; t < hs.nhist * BINS; t += HIST_CTAS * FIN_THREADS) {
       const int h = t / BINS, d = t % BINS;
       if (!ws->active20[h] || ((ws->flag20[h][d >> 5] >> (d & 31)) & 1u)) continue;
       int64_t c = 0;
-      for (int b = 0; b < ws->info.nsets; ++b)
+      for (int b = 0; b < nsets; ++b)
         if ((hs.set_mask[h] >> b) & 1u) c += (int64_t)ws->hist[b][d];
       if (c) {
         const ColParam cp = ws->col[hs.col[h]];
@@ -694,11 +745,12 @@ select_finish_kernel(SelWs* ws, SrcPack src, const int64_t* __restrict__ src_cou
         atomicAdd(out + h * nbins + bin_of(lowkey, ws->thr20[h], nbins), (unsigned long long)c);
       }
     }
-    for (int t = threadIdx.x; t < hs.nhist * nbins; t += FIN_THREADS) {
-      const int h = t / nbins, b = t % nbins;
-      const unsigned long long e = ws->edge20[h][b];
-      if (e) atomicAdd(out + t, e);
-    }
+    if (part == 0)
+      for (int t = threadIdx.x; t < hs.nhist * nbins; t += FIN_THREADS) {
+        const int h = t / nbins, b = t % nbins;
+        const unsigned long long e = ws->edge20[h][b];
+        if (e) atomicAdd(out + t, e);
+      }
     return;
   }
 
@@ -1019,7 +1071,7 @@ extern "C" int kvm_select_finish(void* workspace, const uint64_t* const* arenas,
     sp.nsrc = nsrc;
     for (int i = 0; i < nsrc; ++i) sp.arena[i] = arenas[i];
   }
-  select_finish_kernel<<<MAXQ + 1, FIN_THREADS, 0, (cudaStream_t)stream>>>(ws, sp, src_counts, results,
+  select_finish_kernel<<<MAXQ + HIST_CTAS, FIN_THREADS, 0, (cudaStream_t)stream>>>(ws, sp, src_counts, results,
                                                                           hist_counts);
   KVM_CUDA_CHECK(cudaGetLastError());
   return KVM_OK;

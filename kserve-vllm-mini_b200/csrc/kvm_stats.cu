@@ -20,7 +20,7 @@ namespace {
 
 constexpr int STATS_THREADS = 256;
 constexpr int STATS_WARPS = STATS_THREADS / 32;
-constexpr int COLD_SMEM = 1024;  // cold-start times staged in shared memory
+constexpr int COLD_SMEM = 512;  // cold-start intervals staged in shared memory
 
 struct StatsWs {
   unsigned int ticket;
@@ -28,19 +28,31 @@ struct StatsWs {
   uint64_t partial[1];  // [grid][NSLOTS]
 };
 
+// One thread per cold start: the closed start_ms interval that the reference classifies cold.
+__global__ void cold_table_kernel(const double* __restrict__ cold_times, int nc, double window,
+                                  double* __restrict__ lo, double* __restrict__ hi) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < nc) cold_interval(cold_times[i], window, lo + i, hi + i);
+}
+
 template <bool VEC>
 __global__ void __launch_bounds__(STATS_THREADS, 2)
-log_scan_kernel(kvm_request_log log, const double* __restrict__ cold_g, int nc, double window,
+log_scan_kernel(kvm_request_log log, const double* __restrict__ cold_lo_g,
+                const double* __restrict__ cold_hi_g, int nc,
                 const uint8_t* __restrict__ cold_mask, uint8_t* __restrict__ flags,
                 kvm_log_stats* __restrict__ out, StatsWs* ws) {
-  __shared__ double cold_s[COLD_SMEM];
+  __shared__ double cold_lo_s[COLD_SMEM], cold_hi_s[COLD_SMEM];
   __shared__ uint64_t red[STATS_WARPS][NSLOTS];
   __shared__ bool is_last;
 
-  const double* cold = cold_g;
+  ColdTable cold{cold_lo_g, cold_hi_g, nc};
   if (nc > 0 && nc <= COLD_SMEM) {
-    for (int i = threadIdx.x; i < nc; i += STATS_THREADS) cold_s[i] = cold_g[i];
-    cold = cold_s;
+    for (int i = threadIdx.x; i < nc; i += STATS_THREADS) {
+      cold_lo_s[i] = cold_lo_g[i];
+      cold_hi_s[i] = cold_hi_g[i];
+    }
+    cold.lo = cold_lo_s;
+    cold.hi = cold_hi_s;
     __syncthreads();
   }
 
@@ -66,16 +78,15 @@ log_scan_kernel(kvm_request_log log, const double* __restrict__ cold_g, int nc, 
         c0 = cm & 0xff;
         c1 = cm >> 8;
       }
-      const uint8_t f0 = process_row(a, st.x, la.x, tf.x, tl.x, ss.x, ct.x, tt.x, cold, nc, window, c0);
-      const uint8_t f1 = process_row(a, st.y, la.y, tf.y, tl.y, ss.y, ct.y, tt.y, cold, nc, window, c1);
+      const uint8_t f0 = process_row(a, st.x, la.x, tf.x, tl.x, ss.x, ct.x, tt.x, cold, c0);
+      const uint8_t f1 = process_row(a, st.y, la.y, tf.y, tl.y, ss.y, ct.y, tt.y, cold, c1);
       if (flags) *reinterpret_cast<uint16_t*>(flags + i) = (uint16_t)f0 | ((uint16_t)f1 << 8);
     }
     if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
       const int64_t i = n - 1;
       const uint8_t f = process_row(a, log.start_ms[i], log.latency_ms[i], log.ttfb_ms[i],
                                     log.tllt_ms[i], log.status[i], log.completion_tokens[i],
-                                    log.total_tokens[i], cold, nc, window,
-                                    cold_mask ? (int)cold_mask[i] : -1);
+                                    log.total_tokens[i], cold, cold_mask ? (int)cold_mask[i] : -1);
       if (flags) flags[i] = f;
     }
   } else {
@@ -84,7 +95,7 @@ log_scan_kernel(kvm_request_log log, const double* __restrict__ cold_g, int nc, 
       const uint8_t f = process_row(a, kvm_ld1(log.start_ms + i), kvm_ld1(log.latency_ms + i),
                                     kvm_ld1(log.ttfb_ms + i), kvm_ld1(log.tllt_ms + i),
                                     kvm_ld1(log.status + i), kvm_ld1(log.completion_tokens + i),
-                                    kvm_ld1(log.total_tokens + i), cold, nc, window,
+                                    kvm_ld1(log.total_tokens + i), cold,
                                     cold_mask ? (int)kvm_ld_u8(cold_mask + i) : -1);
       if (flags) flags[i] = f;
     }
@@ -92,34 +103,16 @@ log_scan_kernel(kvm_request_log log, const double* __restrict__ cold_g, int nc, 
 
   // ---- warp reduction, then fixed-order reduction across warps and across CTAs
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-#pragma unroll
-  for (int s = 0; s < NSUM; ++s) {
-    int64_t v = kvm_warp_sum(a.sum[s]);
-    if (lane == 0) red[warp][s] = (uint64_t)v;
-  }
-#pragma unroll
-  for (int c = 0; c <= KVM_LOG_NCOLS; ++c) {
-    uint64_t lo = kvm_warp_min(a.kmin[c]), hi = kvm_warp_max(a.kmax[c]);
-    if (lane == 0) {
-      red[warp][M_KMIN0 + c] = lo;
-      red[warp][X_KMAX0 + c] = hi;
-    }
-  }
-  {
-    kvm_dd t = kvm_warp_sum(a.ttfb), l = kvm_warp_sum(a.lat);
-    if (lane == 0) {
-      red[warp][D_TTFB] = (uint64_t)__double_as_longlong(t.hi);
-      red[warp][D_TTFB + 1] = (uint64_t)__double_as_longlong(t.lo);
-      red[warp][D_LAT] = (uint64_t)__double_as_longlong(l.hi);
-      red[warp][D_LAT + 1] = (uint64_t)__double_as_longlong(l.lo);
-    }
-  }
+  acc_warp_reduce(a, red[warp], lane);
   __syncthreads();
 
   auto combine = [](int slot, uint64_t acc, uint64_t v) -> uint64_t {
     if (slot < NSUM) return (uint64_t)((int64_t)acc + (int64_t)v);
     if (slot < NMIN_END) return v < acc ? v : acc;
     return v > acc ? v : acc;
+  };
+  auto dd_of = [](uint64_t hi, uint64_t lo) -> kvm_dd {
+    return kvm_dd{__longlong_as_double((long long)hi), __longlong_as_double((long long)lo)};
   };
 
   uint64_t* mine = ws->partial + (size_t)blockIdx.x * NSLOTS;
@@ -130,10 +123,8 @@ log_scan_kernel(kvm_request_log log, const double* __restrict__ cold_g, int nc, 
     mine[s] = acc;
   } else if (threadIdx.x == NMAX_END || threadIdx.x == NMAX_END + 1) {
     const int s = threadIdx.x == NMAX_END ? D_TTFB : D_LAT;
-    kvm_dd acc{__longlong_as_double((long long)red[0][s]), __longlong_as_double((long long)red[0][s + 1])};
-    for (int w = 1; w < STATS_WARPS; ++w)
-      acc = kvm_dd_add(acc, kvm_dd{__longlong_as_double((long long)red[w][s]),
-                                   __longlong_as_double((long long)red[w][s + 1])});
+    kvm_dd acc = dd_of(red[0][s], red[0][s + 1]);
+    for (int w = 1; w < STATS_WARPS; ++w) acc = kvm_dd_add(acc, dd_of(red[w][s], red[w][s + 1]));
     mine[s] = (uint64_t)__double_as_longlong(acc.hi);
     mine[s + 1] = (uint64_t)__double_as_longlong(acc.lo);
   }
@@ -153,15 +144,14 @@ log_scan_kernel(kvm_request_log log, const double* __restrict__ cold_g, int nc, 
   if (threadIdx.x < NMAX_END) {
     const int s = threadIdx.x;
     uint64_t acc = part[s];
-    for (unsigned b = 1; b < gridDim.x; ++b) acc = combine(s, acc, part[(size_t)b * NSLOTS + s]);
+    for (unsigned g = 1; g < gridDim.x; ++g) acc = combine(s, acc, part[(size_t)g * NSLOTS + s]);
     fin[s] = acc;
   } else if (threadIdx.x == NMAX_END || threadIdx.x == NMAX_END + 1) {
     const int s = threadIdx.x == NMAX_END ? D_TTFB : D_LAT;
-    kvm_dd acc{__longlong_as_double((long long)part[s]), __longlong_as_double((long long)part[s + 1])};
-    for (unsigned b = 1; b < gridDim.x; ++b) {
-      const size_t o = (size_t)b * NSLOTS + s;
-      acc = kvm_dd_add(acc, kvm_dd{__longlong_as_double((long long)part[o]),
-                                   __longlong_as_double((long long)part[o + 1])});
+    kvm_dd acc = dd_of(part[s], part[s + 1]);
+    for (unsigned g = 1; g < gridDim.x; ++g) {
+      const size_t o = (size_t)g * NSLOTS + s;
+      acc = kvm_dd_add(acc, dd_of(part[o], part[o + 1]));
     }
     fin[s] = (uint64_t)__double_as_longlong(acc.hi);
     fin[s + 1] = (uint64_t)__double_as_longlong(acc.lo);
@@ -169,39 +159,7 @@ log_scan_kernel(kvm_request_log log, const double* __restrict__ cold_g, int nc, 
   __syncthreads();
   if (threadIdx.x == 0) {
     kvm_log_stats r;
-    r.n_total = n;
-    r.n_success = (int64_t)fin[S_SUCCESS];
-    r.n_cold = (int64_t)fin[S_COLD];
-    r.n_cold_success = (int64_t)fin[S_COLD_SUCCESS];
-    r.sum_completion_tokens = (int64_t)fin[S_CTOK];
-    r.sum_total_tokens = (int64_t)fin[S_TTOK];
-    r.sum_total_tokens_cold = (int64_t)fin[S_TTOK_COLD];
-    r.n_gen_rows = (int64_t)fin[S_GEN_ROWS];
-    r.min_start_ms = fin[M_START] == ~0ull ? __longlong_as_double(0x7ff8000000000000ll)
-                                           : kvm_unkey(fin[M_START]);
-    r.max_end_ms = fin[X_END] == 0ull ? __longlong_as_double(0x7ff8000000000000ll)
-                                      : kvm_unkey(fin[X_END]);
-    r.ttfb_sum_hi = __longlong_as_double((long long)fin[D_TTFB]);
-    r.ttfb_sum_lo = __longlong_as_double((long long)fin[D_TTFB + 1]);
-    r.lat_sum_hi = __longlong_as_double((long long)fin[D_LAT]);
-    r.lat_sum_lo = __longlong_as_double((long long)fin[D_LAT + 1]);
-    for (int s = 0; s < KVM_MAX_SETS; ++s) {
-      r.sets.count[s] = s < KVM_LOG_NSETS ? (int64_t)fin[S_CNT0 + s] : 0;
-      r.sets.set_col[s] = 0;
-    }
-    for (int c = 0; c < KVM_MAX_COLS; ++c) {
-      r.sets.kmin[c] = c < KVM_LOG_NCOLS ? fin[M_KMIN0 + c] : ~0ull;
-      r.sets.kmax[c] = c < KVM_LOG_NCOLS ? fin[X_KMAX0 + c] : 0ull;
-    }
-    r.sets.set_col[KVM_SET_LAT_COLD] = KVM_COL_LAT;
-    r.sets.set_col[KVM_SET_LAT_WARM] = KVM_COL_LAT;
-    r.sets.set_col[KVM_SET_TTFB_COLD] = KVM_COL_TTFB;
-    r.sets.set_col[KVM_SET_TTFB_WARM] = KVM_COL_TTFB;
-    r.sets.set_col[KVM_SET_TLLT] = KVM_COL_TLLT;
-    r.sets.set_col[KVM_SET_GEN] = KVM_COL_GEN;
-    r.sets.set_col[KVM_SET_PERTOK] = KVM_COL_PERTOK;
-    r.sets.nsets = KVM_LOG_NSETS;
-    r.sets.ncols = KVM_LOG_NCOLS;
+    stats_from_slots(fin, n, r);
     *out = r;
     ws->ticket = 0;  // ready for the next launch on this workspace
   }
@@ -305,8 +263,11 @@ constexpr int MAX_GRID = 148 * 8;  // workspace sizing bound (B200: 148 SMs)
 
 }  // namespace
 
+constexpr int MAX_COLD = 16384;  // cold starts per log the workspace has room for
+static size_t scan_partials_bytes() { return kvm_align_up(256 + sizeof(uint64_t) * (size_t)NSLOTS * MAX_GRID, 256); }
+
 extern "C" size_t kvm_log_scan_workspace_bytes(void) {
-  return kvm_align_up(256 + sizeof(uint64_t) * (size_t)NSLOTS * MAX_GRID, 256);
+  return scan_partials_bytes() + 2 * sizeof(double) * (size_t)MAX_COLD;
 }
 
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
@@ -318,6 +279,7 @@ extern "C" int kvm_log_scan(const kvm_request_log* log, const double* cold_times
   KVM_REQUIRE(log && stats && workspace, "kvm_log_scan: null argument");
   KVM_REQUIRE(log->n >= 0 && n_cold >= 0, "kvm_log_scan: negative size");
   KVM_REQUIRE(n_cold == 0 || cold_times, "kvm_log_scan: cold_times is null");
+  KVM_REQUIRE(n_cold <= MAX_COLD, "kvm_log_scan: %d cold starts exceed the supported %d", n_cold, MAX_COLD);
   if (workspace_bytes < kvm_log_scan_workspace_bytes()) {
     kvm_set_error("kvm_log_scan: workspace %zu < %zu bytes", workspace_bytes,
                   kvm_log_scan_workspace_bytes());
@@ -333,12 +295,15 @@ extern "C" int kvm_log_scan(const kvm_request_log* log, const double* cold_times
                    aligned16(log->completion_tokens) && aligned16(log->total_tokens) &&
                    (flags == nullptr || (reinterpret_cast<uintptr_t>(flags) & 1u) == 0) &&
                    (cold_mask == nullptr || (reinterpret_cast<uintptr_t>(cold_mask) & 1u) == 0);
+  double* cold_lo = reinterpret_cast<double*>(reinterpret_cast<unsigned char*>(workspace) + scan_partials_bytes());
+  double* cold_hi = cold_lo + MAX_COLD;
+  if (cold_mask) n_cold = 0;  // the mask replaces the time-based classification
+  if (n_cold > 0)
+    cold_table_kernel<<<(n_cold + 127) / 128, 128, 0, st>>>(cold_times, n_cold, cold_window_s, cold_lo, cold_hi);
   if (vec)
-    log_scan_kernel<true><<<grid, STATS_THREADS, 0, st>>>(*log, cold_times, n_cold, cold_window_s,
-                                                          cold_mask, flags, stats, ws);
+    log_scan_kernel<true><<<grid, STATS_THREADS, 0, st>>>(*log, cold_lo, cold_hi, n_cold, cold_mask, flags, stats, ws);
   else
-    log_scan_kernel<false><<<grid, STATS_THREADS, 0, st>>>(*log, cold_times, n_cold,
-                                                           cold_window_s, cold_mask, flags, stats, ws);
+    log_scan_kernel<false><<<grid, STATS_THREADS, 0, st>>>(*log, cold_lo, cold_hi, n_cold, cold_mask, flags, stats, ws);
   KVM_CUDA_CHECK(cudaGetLastError());
   return KVM_OK;
 }
