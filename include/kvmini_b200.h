@@ -172,7 +172,7 @@ typedef struct kvm_hist_spec {
 typedef struct kvm_log_extras {
   int32_t num_bins;        /* > 0: the four histograms of analyze.py:149-152 (ttfb, tllt, generation, per-token) */
   int32_t pad;
-  int64_t* hist_counts;    /* [4][num_bins] */
+  int64_t* hist_counts;    /* [4][num_bins], in a buffer of KVM_MAX_HISTS*KVM_HIST_MAX_BINS int64 */
   double series_window_ms; /* > 0: extension A12 window series, binned in the histogram pass */
   int64_t series_max_bins;
   int64_t* series;         /* [3][series_max_bins]: requests, successes, completion tokens */
@@ -269,7 +269,8 @@ int kvm_log_select_compact(const kvm_request_log* log_host, const uint8_t* flags
  * offsets; src_counts[s*KVM_MAX_QUERIES + b] = keys source s holds for bucket b. */
 int kvm_select_finish(void* workspace, const uint64_t* const* arenas_host, int32_t nsrc,
                       const int64_t* src_counts, kvm_query_result* results,
-                      int64_t* hist_counts /* zeroed by the caller; NULL = no histograms */,
+                      int64_t* hist_counts /* [KVM_MAX_HISTS*KVM_HIST_MAX_BINS] capacity, histogram h at
+                                              h*num_bins; zeroed here; NULL = no histograms */,
                       void* stream);
 
 /* ------------------------------------------------------------------ histograms / series */

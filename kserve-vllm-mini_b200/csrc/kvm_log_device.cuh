@@ -78,28 +78,50 @@ struct ColdTable {
   int n;
 };
 
+// smallest key whose value v satisfies pred(v) (pred monotone: false ... false true ... true),
+// searched by galloping from `guess`; the key range is all finite doubles.
+template <class Pred>
+__device__ __forceinline__ uint64_t first_key_where(double guess, Pred pred) {
+  const uint64_t kmin = kvm_key(-1.7976931348623157e308), kmax = kvm_key(1.7976931348623157e308);
+  uint64_t g = kvm_key(guess);
+  g = g < kmin ? kmin : (g > kmax ? kmax : g);
+  uint64_t a, z;  // pred(a) false, pred(z) true
+  if (pred(kvm_unkey(g))) {
+    z = g;
+    uint64_t step = 1;
+    for (;;) {
+      if (z == kmin) return kmin;
+      a = (z - kmin > step) ? z - step : kmin;
+      if (!pred(kvm_unkey(a))) break;
+      z = a;
+      step <<= 1;
+    }
+  } else {
+    a = g;
+    uint64_t step = 1;
+    for (;;) {
+      if (a == kmax) return ~0ull;  // never true
+      z = (kmax - a > step) ? a + step : kmax;
+      if (pred(kvm_unkey(z))) break;
+      a = z;
+      step <<= 1;
+    }
+  }
+  while (z - a > 1) {
+    const uint64_t mid = a + ((z - a) >> 1);
+    if (pred(kvm_unkey(mid))) z = mid; else a = mid;
+  }
+  return z;
+}
+
 __device__ __forceinline__ void cold_interval(double c, double window, double* lo, double* hi) {
-  const double c_end = c + window;
+  const double c_end = c + window;                       // analyze.py:415
   // smallest s with s/1000.0 >= c
-  uint64_t a = kvm_key(-1.7976931348623157e308), z = kvm_key(1.7976931348623157e308);
-  if (kvm_unkey(a) / 1000.0 >= c) z = a;
-  while (z - a > 1) {
-    const uint64_t mid = a + ((z - a) >> 1);
-    if (kvm_unkey(mid) / 1000.0 >= c) z = mid; else a = mid;
-  }
-  *lo = kvm_unkey(z);
-  // largest s with s/1000.0 <= c_end  ==  predecessor of the smallest s with s/1000.0 > c_end
-  a = kvm_key(-1.7976931348623157e308);
-  z = kvm_key(1.7976931348623157e308);
-  if (!(kvm_unkey(z) / 1000.0 > c_end)) {
-    *hi = kvm_unkey(z);
-    return;
-  }
-  while (z - a > 1) {
-    const uint64_t mid = a + ((z - a) >> 1);
-    if (kvm_unkey(mid) / 1000.0 > c_end) z = mid; else a = mid;
-  }
-  *hi = kvm_unkey(a);
+  const uint64_t k_lo = first_key_where(c * 1000.0, [&](double s) { return s / 1000.0 >= c; });
+  *lo = k_lo == ~0ull ? __longlong_as_double(0x7ff0000000000000ll) : kvm_unkey(k_lo);
+  // largest s with s/1000.0 <= c_end == predecessor of the smallest s with s/1000.0 > c_end
+  const uint64_t k_hi = first_key_where(c_end * 1000.0, [&](double s) { return s / 1000.0 > c_end; });
+  *hi = k_hi == ~0ull ? 1.7976931348623157e308 : kvm_unkey(k_hi - 1);
 }
 
 __device__ __forceinline__ bool is_cold(double start_ms, const ColdTable& t) {
@@ -283,12 +305,35 @@ __device__ __forceinline__ int bin_of(uint64_t key, const uint64_t* thr, int nb)
 }
 
 
-// smallest key in [klo, khi] whose reference bin index reaches b (klo < khi); ~0 if none does
+// smallest key in [klo, khi] whose reference bin index reaches b (klo < khi); ~0 if none does.
+// The edge sits within a few ulps of lo + b*w, so the search gallops outward from that guess
+// and bisects the bracket it finds (a handful of evaluations instead of 64).
 __device__ __forceinline__ uint64_t bin_threshold(uint64_t klo, uint64_t khi, int nb, int b) {
   const double lo = kvm_unkey(klo), hi = kvm_unkey(khi);
   const double w = (hi - lo) / (double)nb;  // analyze.py:104
   if (ref_bin(hi, lo, w, nb) < b) return ~0ull;
-  uint64_t a = klo, z = khi;  // f(a) < b <= f(z)
+  uint64_t g = kvm_key(lo + (double)b * w);
+  g = g < klo ? klo : (g > khi ? khi : g);
+  uint64_t a, z;  // f(a) < b <= f(z)
+  if (ref_bin(kvm_unkey(g), lo, w, nb) >= b) {
+    z = g;
+    uint64_t step = 1;
+    for (;;) {
+      a = (z - klo > step) ? z - step : klo;
+      if (a == klo || ref_bin(kvm_unkey(a), lo, w, nb) < b) break;
+      z = a;
+      step <<= 1;
+    }
+  } else {
+    a = g;
+    uint64_t step = 1;
+    for (;;) {
+      z = (khi - a > step) ? a + step : khi;
+      if (z == khi || ref_bin(kvm_unkey(z), lo, w, nb) >= b) break;
+      a = z;
+      step <<= 1;
+    }
+  }
   while (z - a > 1) {
     const uint64_t mid = a + ((z - a) >> 1);
     if (ref_bin(kvm_unkey(mid), lo, w, nb) >= b) z = mid; else a = mid;

@@ -623,6 +623,8 @@ __global__ void __launch_bounds__(RES_THREADS, 1) select_resolve_kernel(SelWs* w
 }
 
 // ------------------------------------------------------------------ compact
+constexpr int STAGE_SLOTS = 48;  // candidates a CTA stages per bucket before going to global memory
+
 struct CompactSmem {
   ColParams cp;
   Bucket bk[MAXQ];
@@ -631,6 +633,9 @@ struct CompactSmem {
   uint32_t edge[NH][NB_MAX];
   int32_t col_hist[KVM_MAX_COLS];
   int32_t num_bins;   // value histogram bins
+  uint32_t stage_n[MAXQ];                 // candidates staged per bucket
+  unsigned long long stage_pos[MAXQ];
+  uint64_t stage[MAXQ][STAGE_SLOTS];
   uint16_t tab[KVM_MAX_COLS][BINS];
 };
 
@@ -654,6 +659,7 @@ __device__ __forceinline__ void compact_body(SelWs* ws, uint64_t* __restrict__ a
   for (int i = threadIdx.x; i < MAXQ; i += blockDim.x) {
     S.bk[i] = ws->bucket[i];
     S.bk_off[i] = ws->bucket_offsets[i];
+    S.stage_n[i] = 0;
   }
   __syncthreads();
   uint64_t kb[NCOLS];
@@ -672,9 +678,16 @@ __device__ __forceinline__ void compact_body(SelWs* ws, uint64_t* __restrict__ a
       const int run = S.bk[j0].run;
       for (int j = j0; j < (int)j0 + run; ++j)
         if ((S.bk[j].set_mask >> set) & 1u) {
-          const unsigned long long pos =
-              atomicAdd(reinterpret_cast<unsigned long long*>(&ws->bucket_counts[j]), 1ull);
-          if ((int64_t)pos < S.bk[j].count) arena[S.bk_off[j] + (int64_t)pos] = key;
+          // staged in shared memory (no round trip to L2 in the streaming loop); a bucket
+          // that outgrows its stage falls back to a direct append
+          const uint32_t sp = atomicAdd(&S.stage_n[j], 1u);
+          if (sp < (uint32_t)STAGE_SLOTS) {
+            S.stage[j][sp] = key;
+          } else {
+            const unsigned long long pos =
+                atomicAdd(reinterpret_cast<unsigned long long*>(&ws->bucket_counts[j]), 1ull);
+            if ((int64_t)pos < S.bk[j].count) arena[S.bk_off[j] + (int64_t)pos] = key;
+          }
         }
     }
     const uint32_t code = e >> 8;
@@ -686,6 +699,21 @@ __device__ __forceinline__ void compact_body(SelWs* ws, uint64_t* __restrict__ a
     }
   });
   __syncthreads();
+  // flush the stages: one global cursor bump per non-empty bucket, then a cooperative copy
+  if (threadIdx.x < MAXQ) {
+    const uint32_t c = S.stage_n[threadIdx.x] < (uint32_t)STAGE_SLOTS ? S.stage_n[threadIdx.x] : (uint32_t)STAGE_SLOTS;
+    S.stage_n[threadIdx.x] = c;
+    if (c) S.stage_pos[threadIdx.x] =
+        atomicAdd(reinterpret_cast<unsigned long long*>(&ws->bucket_counts[threadIdx.x]), (unsigned long long)c);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < MAXQ * STAGE_SLOTS; i += blockDim.x) {
+    const int j = i / STAGE_SLOTS, k = i % STAGE_SLOTS;
+    if ((uint32_t)k < S.stage_n[j]) {
+      const int64_t pos = (int64_t)S.stage_pos[j] + k;
+      if (pos < S.bk[j].count) arena[S.bk_off[j] + pos] = S.stage[j][k];
+    }
+  }
   for (int i = threadIdx.x; i < NH * NB_MAX; i += blockDim.x) {
     const uint32_t c = (&S.edge[0][0])[i];
     if (c) atomicAdd(&ws->edge20[0][0] + i, (unsigned long long)c);
@@ -705,7 +733,7 @@ column_compact_kernel(const double* __restrict__ values, int64_t n, int mode,
 }
 
 // ------------------------------------------------------------------ finish
-constexpr int FIN_THREADS = 256;
+constexpr int FIN_THREADS = 1024;
 constexpr int FIN_BITS = 11;
 constexpr int FIN_BINS = 1 << FIN_BITS;
 constexpr int FIN_SMALL = 1024;  // candidates ranked by counting once this few remain
@@ -818,9 +846,19 @@ select_finish_kernel(SelWs* ws, SrcPack src, const int64_t* __restrict__ src_cou
     for (int sidx = 0; sidx < src.nsrc; ++sidx) {
       const int64_t cnt = src_counts[(size_t)sidx * MAXQ + s.bucket];
       const uint64_t* __restrict__ keys = src.arena[sidx] + off;
-      for (int64_t i = threadIdx.x; i < cnt; i += FIN_THREADS) {
-        const uint64_t low = keys[i] - b.base;
-        if ((low >> rem) == prefix) atomicAdd(&hist[(uint32_t)(low >> sh) & dmask], 1u);
+      for (int64_t i0 = threadIdx.x; i0 < cnt; i0 += 4 * FIN_THREADS) {
+        uint64_t kk[4];  // four independent loads in flight before the shared-memory atomics
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int64_t i = i0 + (int64_t)u * FIN_THREADS;
+          kk[u] = i < cnt ? keys[i] : b.base + ~0ull;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int64_t i = i0 + (int64_t)u * FIN_THREADS;
+          const uint64_t low = kk[u] - b.base;
+          if (i < cnt && (low >> rem) == prefix) atomicAdd(&hist[(uint32_t)(low >> sh) & dmask], 1u);
+        }
       }
     }
     __syncthreads();
@@ -1071,6 +1109,9 @@ extern "C" int kvm_select_finish(void* workspace, const uint64_t* const* arenas,
     sp.nsrc = nsrc;
     for (int i = 0; i < nsrc; ++i) sp.arena[i] = arenas[i];
   }
+  if (hist_counts)  // the assembling CTAs accumulate into it
+    KVM_CUDA_CHECK(cudaMemsetAsync(hist_counts, 0, sizeof(int64_t) * KVM_MAX_HISTS * KVM_HIST_MAX_BINS,
+                                   (cudaStream_t)stream));
   select_finish_kernel<<<MAXQ + HIST_CTAS, FIN_THREADS, 0, (cudaStream_t)stream>>>(ws, sp, src_counts, results,
                                                                           hist_counts);
   KVM_CUDA_CHECK(cudaGetLastError());
@@ -1098,9 +1139,6 @@ extern "C" int kvm_log_select(const kvm_request_log* log, const uint8_t* flags,
   const kvm_hist_spec hs = hists ? log_hist_spec(extras->num_bins) : kNoHists;
   int rc = kvm_select_plan(&stats->sets, queries, nq, &hs, workspace, workspace_bytes, arena_capacity, stream);
   if (rc) return rc;
-  if (hists)
-    KVM_CUDA_CHECK(cudaMemsetAsync(extras->hist_counts, 0, sizeof(int64_t) * 4 * (size_t)extras->num_bins,
-                                   (cudaStream_t)stream));
   if ((rc = kvm_log_select_hist(log, flags, stats, extras, workspace, stream))) return rc;
   if ((rc = kvm_select_resolve(workspace, stream))) return rc;
   if ((rc = kvm_log_select_compact(log, flags, workspace, stream))) return rc;

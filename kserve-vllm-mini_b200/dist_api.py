@@ -120,8 +120,7 @@ class ShardedAnalyzer(engine.LogAnalyzer):
         local = self.scan(dlog, cold_times)
         stats = combine_stats(local, dev, grp)
         # the global stats drive plan / histogram thresholds / series origin on every rank
-        self._stats_h.copy_(torch.frombuffer(bytearray(bytes(stats)), dtype=torch.uint8))
-        self._stats_d.copy_(self._stats_h, non_blocking=True)
+        self._stats_d.copy_(torch.frombuffer(bytearray(bytes(stats)), dtype=torch.uint8))
         st = engine._stream_ptr(dev)
         log_c = dlog.c_struct()
         queries = engine.build_queries(quantiles)
@@ -129,7 +128,7 @@ class ShardedAnalyzer(engine.LogAnalyzer):
         n_global = int(stats.n_total)
 
         assert num_bins <= N.KVM_HIST_MAX_BINS, "sharded analysis folds the histograms into the select"
-        hist_d = torch.zeros((4, num_bins), dtype=torch.int64, device=dev)
+        hist_d = torch.zeros(N.KVM_MAX_HISTS * N.KVM_HIST_MAX_BINS, dtype=torch.int64, device=dev)
         hspec = self.hist_spec(num_bins)
         series_d, nb = None, 0
         extras = N.LogExtrasC()
@@ -185,20 +184,20 @@ class ShardedAnalyzer(engine.LogAnalyzer):
         with tm.stage("select_finish"):
             # global fine histogram + global edge counters -> global value histograms on every rank
             N.check(lib.kvm_select_finish(ws, ptrs, self.world, counts_all.data_ptr(),
-                                          self._results_d.data_ptr(), hist_d.data_ptr(), st), "kvm_select_finish")
+                                          self._results_ptr, hist_d.data_ptr(), st), "kvm_select_finish")
         self.launches += 1
         if series_d is not None:
             dist.all_reduce(series_d, op=dist.ReduceOp.SUM, group=grp)
             dist.all_reduce(dropped_d, op=dist.ReduceOp.SUM, group=grp)
-        self._results_h.copy_(self._results_d, non_blocking=True)
-        torch.cuda.current_stream(dev).synchronize()
+        out = self._read_outbox()
 
-        res = np.frombuffer(self._results_h.numpy().tobytes(), dtype=engine.RESULT_DTYPE)[:nq]
+        res = np.frombuffer(out, dtype=engine.RESULT_DTYPE, count=nq, offset=self._OFF_RESULTS)
         series = None
         if series_d is not None:
             series = series_d.cpu().numpy()
             if int(dropped_d.item()) != 0:
                 raise N.NativeError("kvm_log_series dropped rows: raise max_series_bins")
         return engine.RawAnalysis(stats=stats, order=engine.results_to_orderstats(res, quantiles),
-                                  hist_counts=hist_d.cpu().numpy(), num_bins=num_bins, series=series,
+                                  hist_counts=hist_d[:4 * num_bins].view(4, num_bins).cpu().numpy(),
+                                  num_bins=num_bins, series=series,
                                   series_window_s=series_window_s or 1.0, flags=self._flags[:dlog.n])

@@ -216,22 +216,42 @@ class RawAnalysis:
 
 
 class LogAnalyzer:
-    """Reusable buffers + launch sequence for one log size (workspaces are cached so a
-    steady-state call allocates nothing)."""
+    """Reusable buffers + launch sequence for one log (workspaces and output staging are cached,
+    so a steady-state call allocates nothing and synchronises once)."""
+
+    # layout of the device "outbox" that comes back in ONE device->host copy
+    _OFF_STATS = 0
+    _OFF_RESULTS = 512
+    _OFF_HIST = _OFF_RESULTS + N.KVM_MAX_QUERIES * 32
+    _OFF_DROPPED = _OFF_HIST + N.KVM_MAX_HISTS * N.KVM_HIST_MAX_BINS * 8
+    _OUTBOX = _OFF_DROPPED + 64
 
     def __init__(self, device: Optional[torch.device] = None):
         self.device = device or require_cuda()
         self.lib = N.lib()
+        assert C.sizeof(N.LogStatsC) <= self._OFF_RESULTS and C.sizeof(N.QueryResultC) == 32
         self._scan_ws = torch.empty(self.lib.kvm_log_scan_workspace_bytes(), dtype=torch.uint8, device=self.device)
-        self._stats_d = torch.zeros(C.sizeof(N.LogStatsC), dtype=torch.uint8, device=self.device)
-        self._stats_h = torch.zeros(C.sizeof(N.LogStatsC), dtype=torch.uint8).pin_memory()
+        self._out_d = torch.zeros(self._OUTBOX, dtype=torch.uint8, device=self.device)
+        self._out_h = torch.zeros(self._OUTBOX, dtype=torch.uint8).pin_memory()
+        base = self._out_d.data_ptr()
+        self._stats_ptr = base + self._OFF_STATS
+        self._results_ptr = base + self._OFF_RESULTS
+        self._hist_ptr = base + self._OFF_HIST
+        self._dropped_ptr = base + self._OFF_DROPPED
+        # views used by subclasses / tests
+        self._stats_d = self._out_d[self._OFF_STATS:self._OFF_STATS + C.sizeof(N.LogStatsC)]
+        self._results_d = self._out_d[self._OFF_RESULTS:self._OFF_HIST]
         self._hist_ws = torch.empty(self.lib.kvm_log_histograms_workspace_bytes(256), dtype=torch.uint8, device=self.device)
         self._sel_ws: Optional[torch.Tensor] = None
         self._sel_cap = 0
         self._flags: Optional[torch.Tensor] = None
-        self._results_d = torch.zeros(N.KVM_MAX_QUERIES * C.sizeof(N.QueryResultC), dtype=torch.uint8, device=self.device)
-        self._results_h = torch.zeros(N.KVM_MAX_QUERIES * C.sizeof(N.QueryResultC), dtype=torch.uint8).pin_memory()
         self._empty_cold = torch.zeros(1, dtype=torch.float64, device=self.device)
+        self._cold_key: Optional[tuple] = None
+        self._cold_d = self._empty_cold
+        self._series_d: Optional[torch.Tensor] = None
+        self._series_h: Optional[torch.Tensor] = None
+        self._series_cap = 1 << 16
+        self._query_cache: Dict[int, tuple] = {}
         self.launches = 0   # kernels launched by the last analyze() (for bench accounting)
         self.timer = _NoTimer()   # bench.py swaps in a StageTimer
 
@@ -244,30 +264,46 @@ class LogAnalyzer:
             self._sel_ws = torch.empty(self.lib.kvm_select_workspace_bytes(cap), dtype=torch.uint8, device=self.device)
             self._sel_cap = cap
 
+    def _cold_device(self, cold_times: Sequence[float]) -> Tuple[torch.Tensor, int]:
+        key = tuple(sorted(float(c) for c in cold_times))
+        if key != self._cold_key:
+            self._cold_d = (torch.tensor(key, dtype=torch.float64, device=self.device) if key else self._empty_cold)
+            self._cold_key = key
+        return self._cold_d, len(key)
+
+    def _queries(self, quantiles: Sequence[Quantile]):
+        hit = self._query_cache.get(id(quantiles))
+        if hit is None or hit[0] is not quantiles:
+            hit = (quantiles, build_queries(quantiles))
+            self._query_cache[id(quantiles)] = hit
+        return hit[1]
+
+    def _read_outbox(self) -> bytes:
+        """One D2H copy of stats + results + histogram counts + dropped counter, then sync."""
+        self._out_h.copy_(self._out_d, non_blocking=True)
+        torch.cuda.current_stream(self.device).synchronize()
+        return self._out_h.numpy().tobytes()
+
     def _launch_scan(self, dlog: DeviceLog, cold_times: Sequence[float], cold_window_s: float = 30.0,
                      cold_mask: Optional[torch.Tensor] = None) -> None:
-        """K1, stream-ordered: stats land in self._stats_d, flags in self._flags."""
+        """K1, stream-ordered: stats land in the outbox, flags in self._flags."""
         self._ensure(dlog.n)
-        st = _stream_ptr(self.device)
-        cold = sorted(float(c) for c in cold_times)
-        cold_d = (torch.tensor(cold, dtype=torch.float64, device=self.device) if cold else self._empty_cold)
-        self._cold_d = cold_d
+        cold_d, nc = self._cold_device(cold_times)
         log_c = dlog.c_struct()
         with self.timer.stage("log_scan"):
-            N.check(self.lib.kvm_log_scan(C.byref(log_c), cold_d.data_ptr(), len(cold), float(cold_window_s),
+            N.check(self.lib.kvm_log_scan(C.byref(log_c), cold_d.data_ptr(), nc, float(cold_window_s),
                                           cold_mask.data_ptr() if cold_mask is not None else None,
-                                          self._flags.data_ptr(), self._stats_d.data_ptr(),
-                                          self._scan_ws.data_ptr(), self._scan_ws.numel(), st), "kvm_log_scan")
-        self.launches += 1
+                                          self._flags.data_ptr(), self._stats_ptr,
+                                          self._scan_ws.data_ptr(), self._scan_ws.numel(),
+                                          _stream_ptr(self.device)), "kvm_log_scan")
+        self.launches += 1 + (1 if nc and cold_mask is None else 0)
 
     def scan(self, dlog: DeviceLog, cold_times: Sequence[float], cold_window_s: float = 30.0,
              cold_mask: Optional[torch.Tensor] = None) -> N.LogStatsC:
         """K1: one pass, returns the stats struct (synchronises).  `cold_mask` (uint8 per row)
         replaces the time-based classification (cost_estimator's is_cold_start column)."""
         self._launch_scan(dlog, cold_times, cold_window_s, cold_mask)
-        self._stats_h.copy_(self._stats_d, non_blocking=True)
-        torch.cuda.current_stream(self.device).synchronize()
-        return N.LogStatsC.from_buffer_copy(self._stats_h.numpy().tobytes())
+        return N.LogStatsC.from_buffer_copy(self._read_outbox()[:C.sizeof(N.LogStatsC)])
 
     @staticmethod
     def hist_spec(num_bins: int) -> N.HistSpecC:
@@ -283,84 +319,86 @@ class LogAnalyzer:
                 series_window_s: Optional[float] = 1.0, max_series_bins: int = 1 << 24,
                 quantiles: Sequence[Quantile] = ANALYZE_QUANTILES) -> RawAnalysis:
         """scan -> plan -> hist(+series) -> resolve -> compact -> finish, all stream-ordered;
-        ONE host synchronisation at the end (plus a small read-back of the series)."""
+        ONE host synchronisation for everything but the series, which is read back once its
+        length is known from the stats."""
         self.launches = 0
         lib, tm, dev = self.lib, self.timer, self.device
-        self._launch_scan(dlog, cold_times)
-        st = _stream_ptr(dev)
-        log_c = dlog.c_struct()
-        queries = build_queries(quantiles)
+        queries = self._queries(quantiles)
         nq = len(queries)
         assert nq <= N.KVM_MAX_QUERIES
         fused_hists = num_bins <= N.KVM_HIST_MAX_BINS
-        hist_d = torch.zeros((4, num_bins), dtype=torch.int64, device=dev)
         hspec = self.hist_spec(num_bins) if fused_hists else None
-
+        hist_big = None if fused_hists else torch.zeros((4, num_bins), dtype=torch.int64, device=dev)
         want_series = series_window_s is not None and dlog.n > 0
-        cap = getattr(self, "_series_cap", 1 << 16)
+        log_c = dlog.c_struct()
+        st = _stream_ptr(dev)
+        self._ensure(dlog.n)
         arena = self._sel_cap
         while True:
+            self._launch_scan(dlog, cold_times)
             extras = N.LogExtrasC()
             if want_series:
-                if getattr(self, "_series_d", None) is None or self._series_d.shape[1] < cap:
-                    self._series_d = torch.empty((3, cap), dtype=torch.int64, device=dev)
-                    self._dropped_d = torch.empty(1, dtype=torch.int64, device=dev)
+                if self._series_d is None or self._series_d.shape[1] < self._series_cap:
+                    self._series_d = torch.empty((3, self._series_cap), dtype=torch.int64, device=dev)
                 extras.series_window_ms = float(series_window_s) * 1000.0
                 extras.series_max_bins = int(self._series_d.shape[1])
                 extras.series = self._series_d.data_ptr()
-                extras.series_dropped = self._dropped_d.data_ptr()
+                extras.series_dropped = self._dropped_ptr
             ws, fl = self._sel_ws.data_ptr(), self._flags.data_ptr()
             with tm.stage("select_plan"):
-                N.check(lib.kvm_select_plan(self._stats_d.data_ptr() + N.LogStatsC.sets.offset, queries, nq,
+                N.check(lib.kvm_select_plan(self._stats_ptr + N.LogStatsC.sets.offset, queries, nq,
                                             C.byref(hspec) if hspec is not None else None, ws,
                                             self._sel_ws.numel(), arena, st), "kvm_select_plan")
             with tm.stage("select_hist"):
-                N.check(lib.kvm_log_select_hist(C.byref(log_c), fl, self._stats_d.data_ptr(), C.byref(extras),
-                                                ws, st), "kvm_log_select_hist")
+                N.check(lib.kvm_log_select_hist(C.byref(log_c), fl, self._stats_ptr, C.byref(extras), ws, st),
+                        "kvm_log_select_hist")
             with tm.stage("select_resolve"):
                 N.check(lib.kvm_select_resolve(ws, st), "kvm_select_resolve")
             with tm.stage("select_compact"):
                 N.check(lib.kvm_log_select_compact(C.byref(log_c), fl, ws, st), "kvm_log_select_compact")
             with tm.stage("select_finish"):
-                N.check(lib.kvm_select_finish(ws, None, 0, None, self._results_d.data_ptr(),
-                                              hist_d.data_ptr() if fused_hists else None, st), "kvm_select_finish")
+                N.check(lib.kvm_select_finish(ws, None, 0, None, self._results_ptr,
+                                              self._hist_ptr if fused_hists else None, st), "kvm_select_finish")
             self.launches += 5
             if not fused_hists:
                 with tm.stage("histograms"):
-                    N.check(lib.kvm_log_histograms(C.byref(log_c), fl, self._stats_d.data_ptr(),
-                                                   num_bins, hist_d.data_ptr(), self._hist_ws.data_ptr(),
+                    N.check(lib.kvm_log_histograms(C.byref(log_c), fl, self._stats_ptr, num_bins,
+                                                   hist_big.data_ptr(), self._hist_ws.data_ptr(),
                                                    self._hist_ws.numel(), st), "kvm_log_histograms")
                 self.launches += 2
-            self._stats_h.copy_(self._stats_d, non_blocking=True)
-            self._results_h.copy_(self._results_d, non_blocking=True)
-            rc = self.lib.kvm_select_status(self._sel_ws.data_ptr(), st)   # the one synchronisation
-            stats = N.LogStatsC.from_buffer_copy(self._stats_h.numpy().tobytes())
+            # the select status word rides in the same read-back: copy it next to the outbox
+            out = self._read_outbox()                      # the one synchronisation
+            rc = lib.kvm_select_status(self._sel_ws.data_ptr(), st)
+            stats = N.LogStatsC.from_buffer_copy(out[:C.sizeof(N.LogStatsC)])
             if rc == N.KVM_ERR_ARENA:
                 # pathological concentration: retry once with room for every key of every query
                 arena = max(2 * arena, dlog.n * 4 + 1024)
                 self._ensure(dlog.n, arena)
-                self.launches -= 5
+                self.launches = 0
                 continue
             N.check(rc, "kvm_log_select")
             series = None
             if want_series and not math.isnan(stats.min_start_ms):
                 t0, t1 = stats.min_start_ms / 1000.0, stats.max_end_ms / 1000.0
                 nb = max(1, int(math.ceil((t1 - t0) / series_window_s)) + 1)
-                if int(self._dropped_d.item()) != 0:
+                dropped = int(np.frombuffer(out, dtype=np.int64, count=1, offset=self._OFF_DROPPED)[0])
+                if dropped != 0:
                     if nb > max_series_bins:
                         raise N.NativeError("window series needs more than max_series_bins windows")
-                    cap = nb + 1           # now known exactly: redo with room for every window
-                    self._series_cap = cap
-                    self._series_d = None
-                    self.launches -= 5
+                    self._series_cap = nb + 1      # now known exactly: redo with room for every window
+                    self.launches = 0
                     continue
                 series = self._series_d[:, :min(nb, self._series_d.shape[1])].cpu().numpy()
             break
 
-        res = np.frombuffer(self._results_h.numpy().tobytes(), dtype=RESULT_DTYPE)[:nq]
-        return RawAnalysis(stats=stats, order=results_to_orderstats(res, quantiles),
-                           hist_counts=hist_d.cpu().numpy(), num_bins=num_bins, series=series,
-                           series_window_s=series_window_s or 1.0, flags=self._flags[:dlog.n])
+        res = np.frombuffer(out, dtype=RESULT_DTYPE, count=nq, offset=self._OFF_RESULTS)
+        if fused_hists:
+            hist = np.frombuffer(out, dtype=np.int64, count=4 * num_bins, offset=self._OFF_HIST).reshape(4, num_bins).copy()
+        else:
+            hist = hist_big.cpu().numpy()
+        return RawAnalysis(stats=stats, order=results_to_orderstats(res, quantiles), hist_counts=hist,
+                           num_bins=num_bins, series=series, series_window_s=series_window_s or 1.0,
+                           flags=self._flags[:dlog.n])
 
 
 # --------------------------------------------------------------------------- single columns
