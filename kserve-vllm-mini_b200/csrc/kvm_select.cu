@@ -720,10 +720,192 @@ __device__ __forceinline__ void compact_body(SelWs* ws, uint64_t* __restrict__ a
   }
 }
 
+// Slow path of the compact pass for one key whose fine bin is "interesting" (table entry e).
+__device__ __forceinline__ void compact_hit(SelWs* ws, CompactSmem& S, uint64_t* __restrict__ arena,
+                                            int set, int col, uint32_t e, uint64_t key) {
+  const uint32_t j0 = e & 0xffu;
+  if (j0 != 255u) {
+    const int run = S.bk[j0].run;
+    for (int j = j0; j < (int)j0 + run; ++j)
+      if ((S.bk[j].set_mask >> set) & 1u) {
+        const uint32_t sp = atomicAdd(&S.stage_n[j], 1u);
+        if (sp < (uint32_t)STAGE_SLOTS) {
+          S.stage[j][sp] = key;
+        } else {
+          const unsigned long long pos =
+              atomicAdd(reinterpret_cast<unsigned long long*>(&ws->bucket_counts[j]), 1ull);
+          if ((int64_t)pos < S.bk[j].count) arena[S.bk_off[j] + (int64_t)pos] = key;
+        }
+      }
+  }
+  const uint32_t code = e >> 8;
+  if (code) {
+    const int h = S.col_hist[col];
+    const int bin = code == 255u ? bin_of(key, S.thr[h], S.num_bins)
+                                 : (int)code - (key < S.thr[h][code - 1] ? 1 : 0);
+    atomicAdd(&S.edge[h][bin], 1u);
+  }
+}
+
+constexpr int CQ_CAP = 128;  // per-warp queue of interesting keys
+
+struct CompactQueue {
+  uint64_t key[SEL_THREADS / 32][CQ_CAP];
+  uint32_t meta[SEL_THREADS / 32][CQ_CAP];  // set | col << 8 | table entry << 16
+};
+
+// Log compact pass.  Only ~3% of the keys fall into a fine bin that holds a requested rank or
+// a histogram edge, but with 10 key sites per lane-iteration almost every warp iteration has a
+// few: handling them in place would serialise the warp on every site.  Instead each site
+// ballots its hits into a per-warp shared-memory queue (no atomics, no divergence in the
+// streaming loop) and the queue is drained 32 entries at a time with all lanes busy.
+template <int ROWS>
 __global__ void __launch_bounds__(SEL_THREADS, 2)
-log_compact_kernel(kvm_request_log log, const uint8_t* __restrict__ flags, bool vec, SelWs* ws,
-                   uint64_t* arena) {
-  compact_body<KVM_LOG_NCOLS>(ws, arena, [&](auto&& f) { for_each_log_key(log, flags, vec, f); });
+log_compact_kernel(kvm_request_log log, const uint8_t* __restrict__ flags, SelWs* ws, uint64_t* arena) {
+  extern __shared__ __align__(16) unsigned char craw[];
+  CompactSmem& S = *reinterpret_cast<CompactSmem*>(craw);
+  CompactQueue& Q = *reinterpret_cast<CompactQueue*>(craw + ((sizeof(CompactSmem) + 15) / 16) * 16);
+  if (ws->status != KVM_OK) return;
+  if (threadIdx.x == 0) S.num_bins = ws->hspec.num_bins;
+  if (threadIdx.x < KVM_MAX_COLS) {
+    S.cp.kbase[threadIdx.x] = ws->col[threadIdx.x].kbase;
+    S.cp.shift[threadIdx.x] = ws->col[threadIdx.x].shift;
+    S.col_hist[threadIdx.x] = ws->col_hist[threadIdx.x];
+  }
+  for (int i = threadIdx.x; i < KVM_LOG_NCOLS * BINS / 2; i += SEL_THREADS)
+    reinterpret_cast<uint32_t*>(&S.tab[0][0])[i] = reinterpret_cast<const uint32_t*>(&ws->tab[0][0])[i];
+  for (int i = threadIdx.x; i < NH * NB_MAX; i += SEL_THREADS) {
+    (&S.thr[0][0])[i] = (&ws->thr20[0][0])[i];
+    (&S.edge[0][0])[i] = 0;
+  }
+  for (int i = threadIdx.x; i < MAXQ; i += SEL_THREADS) {
+    S.bk[i] = ws->bucket[i];
+    S.bk_off[i] = ws->bucket_offsets[i];
+    S.stage_n[i] = 0;
+  }
+  __syncthreads();
+  uint64_t kb[KVM_LOG_NCOLS];
+  int shf[KVM_LOG_NCOLS];
+#pragma unroll
+  for (int c = 0; c < KVM_LOG_NCOLS; ++c) {
+    kb[c] = S.cp.kbase[c];
+    shf[c] = S.cp.shift[c];
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const unsigned lt = (1u << lane) - 1u;
+  int qn = 0;  // warp-uniform queue length
+  auto drain = [&]() {
+    __syncwarp();
+    for (int i = lane; i < qn; i += 32) {
+      const uint32_t m = Q.meta[warp][i];
+      compact_hit(ws, S, arena, m & 0xff, (m >> 8) & 0xff, m >> 16, Q.key[warp][i]);
+    }
+    __syncwarp();
+    qn = 0;
+  };
+  // one key site, executed by all 32 lanes: `valid` lanes look their digit up, hits are queued
+  auto site = [&](bool valid, int set, int col, uint64_t key) {
+    uint32_t e = 0x00ffu;
+    if (valid) e = S.tab[col][digit_of(key, kb[col], shf[col])];
+    const unsigned hits = __ballot_sync(KVM_FULL, e != 0x00ffu);
+    if (hits) {
+      const int cnt = __popc(hits);
+      if (qn + cnt > CQ_CAP) drain();
+      if (e != 0x00ffu) {
+        const int pos = qn + __popc(hits & lt);
+        Q.key[warp][pos] = key;
+        Q.meta[warp][pos] = (uint32_t)set | ((uint32_t)col << 8) | (e << 16);
+      }
+      qn += cnt;
+    }
+  };
+  auto row = [&](uint8_t fl, double la, double tf, double tl, long long ct) {
+    const bool ok = fl & KVM_F_SUCCESS;
+    const bool cold = fl & KVM_F_COLD;
+    site(ok && !kvm_isnan(la), cold ? KVM_SET_LAT_COLD : KVM_SET_LAT_WARM, KVM_COL_LAT, kvm_key(la));
+    site(ok && !kvm_isnan(tf), cold ? KVM_SET_TTFB_COLD : KVM_SET_TTFB_WARM, KVM_COL_TTFB, kvm_key(tf));
+    site(ok && !kvm_isnan(tl), KVM_SET_TLLT, KVM_COL_TLLT, kvm_key(tl));
+    const bool gen = ok && (fl & KVM_F_GEN);
+    const double g = tl - tf;                       // analyze.py:144
+    const bool gv = gen && !kvm_isnan(g);
+    site(gv, KVM_SET_GEN, KVM_COL_GEN, kvm_key(g));
+    double pt = 0.0;
+    if (gv) pt = g / (double)ct;                    // analyze.py:146
+    site(gv && !kvm_isnan(pt), KVM_SET_PERTOK, KVM_COL_PERTOK, kvm_key(pt));
+  };
+
+  const int64_t n = log.n;
+  const int64_t nunits = ROWS == 2 ? (n >> 1) : n;
+  for (int64_t base = (int64_t)blockIdx.x * SEL_THREADS + (threadIdx.x & ~31); base < nunits;
+       base += (int64_t)gridDim.x * SEL_THREADS) {
+    const int64_t u = base + lane;
+    const bool live = u < nunits;
+    const int64_t i = ROWS == 2 ? (u << 1) : u;
+    uint8_t f0 = 0, f1 = 0;
+    if (live) {
+      if (ROWS == 2) {
+        const uint16_t ff = kvm_ld_u8x2(flags + i);
+        f0 = (uint8_t)(ff & 0xff);
+        f1 = (uint8_t)(ff >> 8);
+      } else {
+        f0 = kvm_ld_u8(flags + i);
+      }
+    }
+    // skip the loads of a warp whose rows all failed
+    if (!__any_sync(KVM_FULL, (f0 | f1) & KVM_F_SUCCESS)) continue;
+    if (ROWS == 2) {
+      double2 la{0.0, 0.0}, tf{0.0, 0.0}, tl{0.0, 0.0};
+      longlong2 ct{0, 0};
+      if ((f0 | f1) & KVM_F_SUCCESS) {
+        la = kvm_ld2(log.latency_ms + i);
+        tf = kvm_ld2(log.ttfb_ms + i);
+        tl = kvm_ld2(log.tllt_ms + i);
+        ct = kvm_ld2(log.completion_tokens + i);
+      }
+      row(f0, la.x, tf.x, tl.x, ct.x);
+      row(f1, la.y, tf.y, tl.y, ct.y);
+    } else {
+      double la = 0.0, tf = 0.0, tl = 0.0;
+      long long ct = 0;
+      if (f0 & KVM_F_SUCCESS) {
+        la = kvm_ld1(log.latency_ms + i);
+        tf = kvm_ld1(log.ttfb_ms + i);
+        tl = kvm_ld1(log.tllt_ms + i);
+        ct = kvm_ld1(log.completion_tokens + i);
+      }
+      row(f0, la, tf, tl, ct);
+    }
+    if (qn >= 32) drain();
+  }
+  drain();
+  if (ROWS == 2 && (n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {  // odd tail row
+    const int64_t i = n - 1;
+    log_row_keys(flags[i], log.latency_ms[i], log.ttfb_ms[i], log.tllt_ms[i], log.completion_tokens[i],
+                 [&](int set, int col, uint64_t key) {
+                   const uint32_t e = S.tab[col][digit_of(key, kb[col], shf[col])];
+                   if (e != 0x00ffu) compact_hit(ws, S, arena, set, col, e, key);
+                 });
+  }
+  __syncthreads();
+  // flush the stages: one global cursor bump per non-empty bucket, then a cooperative copy
+  if (threadIdx.x < MAXQ) {
+    const uint32_t c = S.stage_n[threadIdx.x] < (uint32_t)STAGE_SLOTS ? S.stage_n[threadIdx.x] : (uint32_t)STAGE_SLOTS;
+    S.stage_n[threadIdx.x] = c;
+    if (c) S.stage_pos[threadIdx.x] =
+        atomicAdd(reinterpret_cast<unsigned long long*>(&ws->bucket_counts[threadIdx.x]), (unsigned long long)c);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < MAXQ * STAGE_SLOTS; i += SEL_THREADS) {
+    const int j = i / STAGE_SLOTS, k = i % STAGE_SLOTS;
+    if ((uint32_t)k < S.stage_n[j]) {
+      const int64_t pos = (int64_t)S.stage_pos[j] + k;
+      if (pos < S.bk[j].count) arena[S.bk_off[j] + pos] = S.stage[j][k];
+    }
+  }
+  for (int i = threadIdx.x; i < NH * NB_MAX; i += SEL_THREADS) {
+    const uint32_t c = (&S.edge[0][0])[i];
+    if (c) atomicAdd(&ws->edge20[0][0] + i, (unsigned long long)c);
+  }
 }
 
 __global__ void __launch_bounds__(SEL_THREADS, 2)
@@ -1070,11 +1252,18 @@ extern "C" int kvm_select_resolve(void* workspace, void* stream) {
 extern "C" int kvm_log_select_compact(const kvm_request_log* log, const uint8_t* flags,
                                       void* workspace, void* stream) {
   KVM_REQUIRE(log && flags && workspace, "kvm_log_select_compact: null argument");
-  int rc = ensure_smem((const void*)log_compact_kernel, sizeof(CompactSmem));
-  if (rc) return rc;
+  const size_t smem = ((sizeof(CompactSmem) + 15) / 16) * 16 + sizeof(CompactQueue);
   const int grid = kvm_grid_for(log->n, SEL_THREADS * 2 * 4, 2);
-  log_compact_kernel<<<grid, SEL_THREADS, sizeof(CompactSmem), (cudaStream_t)stream>>>(
-      *log, flags, log_vec_ok(log, flags), reinterpret_cast<SelWs*>(workspace), arena_of(workspace));
+  int rc;
+  if (log_vec_ok(log, flags)) {
+    if ((rc = ensure_smem((const void*)log_compact_kernel<2>, smem))) return rc;
+    log_compact_kernel<2><<<grid, SEL_THREADS, smem, (cudaStream_t)stream>>>(
+        *log, flags, reinterpret_cast<SelWs*>(workspace), arena_of(workspace));
+  } else {
+    if ((rc = ensure_smem((const void*)log_compact_kernel<1>, smem))) return rc;
+    log_compact_kernel<1><<<grid, SEL_THREADS, smem, (cudaStream_t)stream>>>(
+        *log, flags, reinterpret_cast<SelWs*>(workspace), arena_of(workspace));
+  }
   KVM_CUDA_CHECK(cudaGetLastError());
   return KVM_OK;
 }

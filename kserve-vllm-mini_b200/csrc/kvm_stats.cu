@@ -35,7 +35,7 @@ __global__ void cold_table_kernel(const double* __restrict__ cold_times, int nc,
   if (i < nc) cold_interval(cold_times[i], window, lo + i, hi + i);
 }
 
-template <bool VEC>
+template <bool VEC, bool COLD_SMEM_TABLE>
 __global__ void __launch_bounds__(STATS_THREADS, 2)
 log_scan_kernel(kvm_request_log log, const double* __restrict__ cold_lo_g,
                 const double* __restrict__ cold_hi_g, int nc,
@@ -45,14 +45,13 @@ log_scan_kernel(kvm_request_log log, const double* __restrict__ cold_lo_g,
   __shared__ uint64_t red[STATS_WARPS][NSLOTS];
   __shared__ bool is_last;
 
-  ColdTable cold{cold_lo_g, cold_hi_g, nc};
-  if (nc > 0 && nc <= COLD_SMEM) {
+  // the table pointer is known at compile time to be shared or global (no generic loads)
+  ColdTable cold{COLD_SMEM_TABLE ? cold_lo_s : cold_lo_g, COLD_SMEM_TABLE ? cold_hi_s : cold_hi_g, nc};
+  if (COLD_SMEM_TABLE) {
     for (int i = threadIdx.x; i < nc; i += STATS_THREADS) {
       cold_lo_s[i] = cold_lo_g[i];
       cold_hi_s[i] = cold_hi_g[i];
     }
-    cold.lo = cold_lo_s;
-    cold.hi = cold_hi_s;
     __syncthreads();
   }
 
@@ -300,10 +299,14 @@ extern "C" int kvm_log_scan(const kvm_request_log* log, const double* cold_times
   if (cold_mask) n_cold = 0;  // the mask replaces the time-based classification
   if (n_cold > 0)
     cold_table_kernel<<<(n_cold + 127) / 128, 128, 0, st>>>(cold_times, n_cold, cold_window_s, cold_lo, cold_hi);
-  if (vec)
-    log_scan_kernel<true><<<grid, STATS_THREADS, 0, st>>>(*log, cold_lo, cold_hi, n_cold, cold_mask, flags, stats, ws);
-  else
-    log_scan_kernel<false><<<grid, STATS_THREADS, 0, st>>>(*log, cold_lo, cold_hi, n_cold, cold_mask, flags, stats, ws);
+  const bool smem_table = n_cold <= COLD_SMEM;
+#define KVM_LAUNCH_SCAN(V, T) \
+  log_scan_kernel<V, T><<<grid, STATS_THREADS, 0, st>>>(*log, cold_lo, cold_hi, n_cold, cold_mask, flags, stats, ws)
+  if (vec && smem_table) KVM_LAUNCH_SCAN(true, true);
+  else if (vec) KVM_LAUNCH_SCAN(true, false);
+  else if (smem_table) KVM_LAUNCH_SCAN(false, true);
+  else KVM_LAUNCH_SCAN(false, false);
+#undef KVM_LAUNCH_SCAN
   KVM_CUDA_CHECK(cudaGetLastError());
   return KVM_OK;
 }

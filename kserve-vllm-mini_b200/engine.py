@@ -224,6 +224,7 @@ class LogAnalyzer:
     _OFF_RESULTS = 512
     _OFF_HIST = _OFF_RESULTS + N.KVM_MAX_QUERIES * 32
     _OFF_DROPPED = _OFF_HIST + N.KVM_MAX_HISTS * N.KVM_HIST_MAX_BINS * 8
+    _OFF_STATUS = _OFF_DROPPED + 8
     _OUTBOX = _OFF_DROPPED + 64
 
     def __init__(self, device: Optional[torch.device] = None):
@@ -252,6 +253,7 @@ class LogAnalyzer:
         self._series_h: Optional[torch.Tensor] = None
         self._series_cap = 1 << 16
         self._query_cache: Dict[int, tuple] = {}
+        self._graphs: Dict[tuple, tuple] = {}
         self.launches = 0   # kernels launched by the last analyze() (for bench accounting)
         self.timer = _NoTimer()   # bench.py swaps in a StageTimer
 
@@ -315,68 +317,107 @@ class LogAnalyzer:
             hs.col[i], hs.set_mask[i] = col, mask
         return hs
 
-    def analyze(self, dlog: DeviceLog, cold_times: Sequence[float] = (), num_bins: int = 20,
-                series_window_s: Optional[float] = 1.0, max_series_bins: int = 1 << 24,
-                quantiles: Sequence[Quantile] = ANALYZE_QUANTILES) -> RawAnalysis:
-        """scan -> plan -> hist(+series) -> resolve -> compact -> finish, all stream-ordered;
-        ONE host synchronisation for everything but the series, which is read back once its
-        length is known from the stats."""
-        self.launches = 0
+    def _enqueue(self, dlog: DeviceLog, cold_times: Sequence[float], num_bins: int,
+                 series_window_s: Optional[float], quantiles: Sequence[Quantile], arena: int,
+                 hist_big: Optional[torch.Tensor]) -> None:
+        """Everything of one analysis, stream-ordered, ending with the outbox copy (no sync).
+        This is the sequence a CUDA graph captures."""
         lib, tm, dev = self.lib, self.timer, self.device
         queries = self._queries(quantiles)
         nq = len(queries)
-        assert nq <= N.KVM_MAX_QUERIES
-        fused_hists = num_bins <= N.KVM_HIST_MAX_BINS
+        fused_hists = hist_big is None
         hspec = self.hist_spec(num_bins) if fused_hists else None
-        hist_big = None if fused_hists else torch.zeros((4, num_bins), dtype=torch.int64, device=dev)
-        want_series = series_window_s is not None and dlog.n > 0
         log_c = dlog.c_struct()
         st = _stream_ptr(dev)
+        self._launch_scan(dlog, cold_times)
+        extras = N.LogExtrasC()
+        if series_window_s is not None and dlog.n > 0:
+            extras.series_window_ms = float(series_window_s) * 1000.0
+            extras.series_max_bins = int(self._series_d.shape[1])
+            extras.series = self._series_d.data_ptr()
+            extras.series_dropped = self._dropped_ptr
+        ws, fl = self._sel_ws.data_ptr(), self._flags.data_ptr()
+        with tm.stage("select_plan"):
+            N.check(lib.kvm_select_plan(self._stats_ptr + N.LogStatsC.sets.offset, queries, nq,
+                                        C.byref(hspec) if hspec is not None else None, ws,
+                                        self._sel_ws.numel(), arena, st), "kvm_select_plan")
+        with tm.stage("select_hist"):
+            N.check(lib.kvm_log_select_hist(C.byref(log_c), fl, self._stats_ptr, C.byref(extras), ws, st),
+                    "kvm_log_select_hist")
+        with tm.stage("select_resolve"):
+            N.check(lib.kvm_select_resolve(ws, st), "kvm_select_resolve")
+        with tm.stage("select_compact"):
+            N.check(lib.kvm_log_select_compact(C.byref(log_c), fl, ws, st), "kvm_log_select_compact")
+        with tm.stage("select_finish"):
+            N.check(lib.kvm_select_finish(ws, None, 0, None, self._results_ptr,
+                                          self._hist_ptr if fused_hists else None, st), "kvm_select_finish")
+        self.launches += 5
+        if not fused_hists:
+            with tm.stage("histograms"):
+                N.check(lib.kvm_log_histograms(C.byref(log_c), fl, self._stats_ptr, num_bins,
+                                               hist_big.data_ptr(), self._hist_ws.data_ptr(),
+                                               self._hist_ws.numel(), st), "kvm_log_histograms")
+            self.launches += 2
+        # select status word -> outbox, then the whole outbox -> pinned host memory
+        self._out_d[self._OFF_STATUS:self._OFF_STATUS + 4].copy_(self._sel_ws[0:4], non_blocking=True)
+        self._out_h.copy_(self._out_d, non_blocking=True)
+
+    def analyze(self, dlog: DeviceLog, cold_times: Sequence[float] = (), num_bins: int = 20,
+                series_window_s: Optional[float] = 1.0, max_series_bins: int = 1 << 24,
+                quantiles: Sequence[Quantile] = ANALYZE_QUANTILES, use_graph: bool = False) -> RawAnalysis:
+        """scan -> plan -> hist(+series) -> resolve -> compact -> finish, all stream-ordered;
+        ONE host synchronisation for everything but the series, which is read back once its
+        length is known from the stats.  use_graph=True replays a captured CUDA graph when
+        the same device buffers are analysed again (steady-state monitoring, benchmarks)."""
+        dev = self.device
+        nq = 2 * len(quantiles)
+        assert nq <= N.KVM_MAX_QUERIES
+        fused_hists = num_bins <= N.KVM_HIST_MAX_BINS
+        hist_big = None if fused_hists else torch.zeros((4, num_bins), dtype=torch.int64, device=dev)
+        want_series = series_window_s is not None and dlog.n > 0
         self._ensure(dlog.n)
         arena = self._sel_cap
         while True:
-            self._launch_scan(dlog, cold_times)
-            extras = N.LogExtrasC()
-            if want_series:
-                if self._series_d is None or self._series_d.shape[1] < self._series_cap:
-                    self._series_d = torch.empty((3, self._series_cap), dtype=torch.int64, device=dev)
-                extras.series_window_ms = float(series_window_s) * 1000.0
-                extras.series_max_bins = int(self._series_d.shape[1])
-                extras.series = self._series_d.data_ptr()
-                extras.series_dropped = self._dropped_ptr
-            ws, fl = self._sel_ws.data_ptr(), self._flags.data_ptr()
-            with tm.stage("select_plan"):
-                N.check(lib.kvm_select_plan(self._stats_ptr + N.LogStatsC.sets.offset, queries, nq,
-                                            C.byref(hspec) if hspec is not None else None, ws,
-                                            self._sel_ws.numel(), arena, st), "kvm_select_plan")
-            with tm.stage("select_hist"):
-                N.check(lib.kvm_log_select_hist(C.byref(log_c), fl, self._stats_ptr, C.byref(extras), ws, st),
-                        "kvm_log_select_hist")
-            with tm.stage("select_resolve"):
-                N.check(lib.kvm_select_resolve(ws, st), "kvm_select_resolve")
-            with tm.stage("select_compact"):
-                N.check(lib.kvm_log_select_compact(C.byref(log_c), fl, ws, st), "kvm_log_select_compact")
-            with tm.stage("select_finish"):
-                N.check(lib.kvm_select_finish(ws, None, 0, None, self._results_ptr,
-                                              self._hist_ptr if fused_hists else None, st), "kvm_select_finish")
-            self.launches += 5
-            if not fused_hists:
-                with tm.stage("histograms"):
-                    N.check(lib.kvm_log_histograms(C.byref(log_c), fl, self._stats_ptr, num_bins,
-                                                   hist_big.data_ptr(), self._hist_ws.data_ptr(),
-                                                   self._hist_ws.numel(), st), "kvm_log_histograms")
-                self.launches += 2
-            # the select status word rides in the same read-back: copy it next to the outbox
-            out = self._read_outbox()                      # the one synchronisation
-            rc = lib.kvm_select_status(self._sel_ws.data_ptr(), st)
+            if want_series and (self._series_d is None or self._series_d.shape[1] < self._series_cap):
+                self._series_d = torch.empty((3, self._series_cap), dtype=torch.int64, device=dev)
+            self.launches = 0
+            graph_key = None
+            if use_graph and isinstance(self.timer, _NoTimer):
+                graph_key = (tuple(dlog.cols[k].data_ptr() for k in F64_COLS + I64_COLS), dlog.n,
+                             tuple(sorted(float(c) for c in cold_times)), num_bins, series_window_s,
+                             id(quantiles), arena, self._sel_ws.data_ptr(), self._flags.data_ptr(),
+                             self._series_d.data_ptr() if want_series else 0)
+                entry = self._graphs.get(graph_key)
+                if entry is None:
+                    # eager run first (sets function attributes, fills caches), then capture
+                    self._enqueue(dlog, cold_times, num_bins, series_window_s if want_series else None,
+                                  quantiles, arena, hist_big)
+                    torch.cuda.current_stream(dev).synchronize()
+                    g = torch.cuda.CUDAGraph()
+                    self.launches = 0
+                    with torch.cuda.graph(g):
+                        self._enqueue(dlog, cold_times, num_bins, series_window_s if want_series else None,
+                                      quantiles, arena, hist_big)
+                    if len(self._graphs) >= 4:
+                        self._graphs.pop(next(iter(self._graphs)))
+                    entry = (g, self.launches)
+                    self._graphs[graph_key] = entry
+                entry[0].replay()
+                self.launches = entry[1]
+            else:
+                self._enqueue(dlog, cold_times, num_bins, series_window_s if want_series else None,
+                              quantiles, arena, hist_big)
+            torch.cuda.current_stream(dev).synchronize()   # the one synchronisation
+            out = self._out_h.numpy().tobytes()
+            rc = int(np.frombuffer(out, dtype=np.int32, count=1, offset=self._OFF_STATUS)[0])
             stats = N.LogStatsC.from_buffer_copy(out[:C.sizeof(N.LogStatsC)])
             if rc == N.KVM_ERR_ARENA:
                 # pathological concentration: retry once with room for every key of every query
                 arena = max(2 * arena, dlog.n * 4 + 1024)
                 self._ensure(dlog.n, arena)
-                self.launches = 0
                 continue
-            N.check(rc, "kvm_log_select")
+            if rc != N.KVM_OK:
+                raise N.NativeError(f"select failed with status {rc}")
             series = None
             if want_series and not math.isnan(stats.min_start_ms):
                 t0, t1 = stats.min_start_ms / 1000.0, stats.max_end_ms / 1000.0
@@ -386,9 +427,13 @@ class LogAnalyzer:
                     if nb > max_series_bins:
                         raise N.NativeError("window series needs more than max_series_bins windows")
                     self._series_cap = nb + 1      # now known exactly: redo with room for every window
-                    self.launches = 0
                     continue
-                series = self._series_d[:, :min(nb, self._series_d.shape[1])].cpu().numpy()
+                nb = min(nb, self._series_d.shape[1])
+                if self._series_h is None or self._series_h.shape[1] < nb:
+                    self._series_h = torch.empty((3, max(nb, 4096)), dtype=torch.int64).pin_memory()
+                self._series_h[:, :nb].copy_(self._series_d[:, :nb], non_blocking=True)
+                torch.cuda.current_stream(dev).synchronize()
+                series = self._series_h[:, :nb].numpy().copy()
             break
 
         res = np.frombuffer(out, dtype=RESULT_DTYPE, count=nq, offset=self._OFF_RESULTS)
