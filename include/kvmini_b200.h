@@ -177,6 +177,9 @@ typedef struct kvm_log_extras {
   int64_t series_max_bins;
   int64_t* series;         /* [3][series_max_bins]: requests, successes, completion tokens */
   int64_t* series_dropped; /* [1]: rows whose window index >= series_max_bins */
+  uint64_t* digit_records; /* [n] scratch, optional: the histogram pass stores each row's five
+                              fine-bin indices (12 bits each) so the compact pass streams 9 B/row
+                              instead of re-reading and re-keying four columns */
 } kvm_log_extras;
 
 /* Workspace for a select problem whose candidate arena holds `arena_capacity` keys.
@@ -263,8 +266,9 @@ int kvm_log_select_hist(const kvm_request_log* log_host, const uint8_t* flags,
 int kvm_select_resolve(void* workspace, void* stream);
 int kvm_column_select_compact(const double* values, int64_t n, int32_t member_mode,
                               const void* member, void* workspace, void* stream);
-int kvm_log_select_compact(const kvm_request_log* log_host, const uint8_t* flags, void* workspace,
-                           void* stream);
+int kvm_log_select_compact(const kvm_request_log* log_host, const uint8_t* flags,
+                           const uint64_t* digit_records /* from the hist pass, or NULL */,
+                           void* workspace, void* stream);
 /* Finish from `nsrc` arenas (own + gathered peers), each laid out with the same bucket
  * offsets; src_counts[s*KVM_MAX_QUERIES + b] = keys source s holds for bucket b. */
 int kvm_select_finish(void* workspace, const uint64_t* const* arenas_host, int32_t nsrc,

@@ -73,7 +73,7 @@ class HistSpecC(C.Structure):
 class LogExtrasC(C.Structure):
     _fields_ = [("num_bins", C.c_int32), ("pad", C.c_int32), ("hist_counts", C.c_void_p),
                 ("series_window_ms", C.c_double), ("series_max_bins", C.c_int64),
-                ("series", C.c_void_p), ("series_dropped", C.c_void_p)]
+                ("series", C.c_void_p), ("series_dropped", C.c_void_p), ("digit_records", C.c_void_p)]
 
 
 class QueryC(C.Structure):
@@ -118,7 +118,7 @@ def _declare(lib: C.CDLL) -> None:
         "kvm_log_select_hist": (C.c_int, [P(RequestLogC), vp, vp, P(LogExtrasC), vp, vp]),
         "kvm_select_resolve": (C.c_int, [vp, vp]),
         "kvm_column_select_compact": (C.c_int, [vp, i64, i32, vp, vp, vp]),
-        "kvm_log_select_compact": (C.c_int, [P(RequestLogC), vp, vp, vp]),
+        "kvm_log_select_compact": (C.c_int, [P(RequestLogC), vp, vp, vp, vp]),
         "kvm_select_finish": (C.c_int, [vp, P(vp), i32, vp, vp, vp, vp]),
         "kvm_log_histograms_workspace_bytes": (sz, [i32]),
         "kvm_log_histograms": (C.c_int, [P(RequestLogC), vp, vp, i32, vp, vp, sz, vp]),

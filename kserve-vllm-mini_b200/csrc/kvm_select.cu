@@ -107,6 +107,8 @@ struct SrcPack {
   int32_t nsrc;
 };
 
+constexpr uint64_t DIGITS_NONE = 0x0FFFFFFFFFFFFFFFull;  // five 12-bit fields, all "not in a set"
+
 struct SeriesArgs {
   const double* start_ms;
   const kvm_log_stats* stats;  // min_start_ms read on the device
@@ -350,7 +352,8 @@ __device__ __forceinline__ void series_add_row(const SeriesArgs& sa, long long b
 // warp iteration almost always share one window and are merged into three atomics.
 template <int ROWS, bool SERIES>
 __global__ void __launch_bounds__(SEL_THREADS, 2)
-log_hist_kernel(kvm_request_log log, const uint8_t* __restrict__ flags, SelWs* ws, SeriesArgs sa) {
+log_hist_kernel(kvm_request_log log, const uint8_t* __restrict__ flags, SelWs* ws, SeriesArgs sa,
+                uint64_t* __restrict__ digit_records) {
   extern __shared__ uint32_t sh[];  // [KVM_LOG_NSETS][BINS]
   __shared__ ColParams cp;
   hist_prologue(ws, sh, KVM_LOG_NSETS, cp);
@@ -362,8 +365,13 @@ log_hist_kernel(kvm_request_log log, const uint8_t* __restrict__ flags, SelWs* w
     kb[c] = cp.kbase[c];
     shf[c] = cp.shift[c];
   }
+  // digit record of the current row: 12 bits per value column, 0xFFF = row not in any set of
+  // that column.  The compact pass reads these 8 bytes instead of recomputing five keys.
+  uint64_t rec = DIGITS_NONE;
   auto add = [&](int set, int col, uint64_t key) {
-    atomicAdd(&sh[set * BINS + digit_of(key, kb[col], shf[col])], 1u);
+    const uint32_t d = digit_of(key, kb[col], shf[col]);
+    atomicAdd(&sh[set * BINS + d], 1u);
+    rec ^= (uint64_t)(0xFFFu ^ d) << (12 * col);
   };
   const int lane = threadIdx.x & 31;
   const int64_t n = log.n;
@@ -390,15 +398,25 @@ log_hist_kernel(kvm_request_log log, const uint8_t* __restrict__ flags, SelWs* w
           const double2 la = kvm_ld2(log.latency_ms + i), tf = kvm_ld2(log.ttfb_ms + i);
           const double2 tl = kvm_ld2(log.tllt_ms + i);
           const longlong2 ct = kvm_ld2(log.completion_tokens + i);
+          rec = DIGITS_NONE;
           log_row_keys(f0, la.x, tf.x, tl.x, ct.x, add);
+          const uint64_t rec0 = rec;
+          rec = DIGITS_NONE;
           log_row_keys(f1, la.y, tf.y, tl.y, ct.y, add);
+          if (digit_records)
+            *reinterpret_cast<ulonglong2*>(digit_records + i) = make_ulonglong2(rec0, rec);
           tok0 = ct.x;
           tok1 = ct.y;
         } else {
           const long long ct = kvm_ld1(log.completion_tokens + i);
+          rec = DIGITS_NONE;
           log_row_keys(f0, kvm_ld1(log.latency_ms + i), kvm_ld1(log.ttfb_ms + i), kvm_ld1(log.tllt_ms + i), ct, add);
+          if (digit_records) digit_records[i] = rec;
           tok0 = ct;
         }
+      } else if (digit_records) {
+        if (ROWS == 2) *reinterpret_cast<ulonglong2*>(digit_records + i) = make_ulonglong2(DIGITS_NONE, DIGITS_NONE);
+        else digit_records[i] = DIGITS_NONE;
       }
     }
     if (SERIES) {
@@ -434,7 +452,9 @@ log_hist_kernel(kvm_request_log log, const uint8_t* __restrict__ flags, SelWs* w
   if (ROWS == 2 && (n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {  // odd tail row
     const int64_t i = n - 1;
     const uint8_t fl = flags[i];
+    rec = DIGITS_NONE;
     log_row_keys(fl, log.latency_ms[i], log.ttfb_ms[i], log.tllt_ms[i], log.completion_tokens[i], add);
+    if (digit_records) digit_records[i] = rec;
     if (SERIES)
       series_add_row(sa, series_bin(sa.start_ms[i], s0, sa.window_ms, sa.max_bins), fl & KVM_F_SUCCESS,
                      log.completion_tokens[i]);
@@ -623,7 +643,7 @@ __global__ void __launch_bounds__(RES_THREADS, 1) select_resolve_kernel(SelWs* w
 }
 
 // ------------------------------------------------------------------ compact
-constexpr int STAGE_SLOTS = 48;  // candidates a CTA stages per bucket before going to global memory
+constexpr int STAGE_SLOTS = 112;  // candidates a CTA stages per bucket before going to global memory
 
 struct CompactSmem {
   ColParams cp;
@@ -636,7 +656,7 @@ struct CompactSmem {
   uint32_t stage_n[MAXQ];                 // candidates staged per bucket
   unsigned long long stage_pos[MAXQ];
   uint64_t stage[MAXQ][STAGE_SLOTS];
-  uint16_t tab[KVM_MAX_COLS][BINS];
+  uint16_t tab[KVM_LOG_NCOLS][BINS];
 };
 
 template <int NCOLS, class Stream>
@@ -747,6 +767,50 @@ __device__ __forceinline__ void compact_hit(SelWs* ws, CompactSmem& S, uint64_t*
   }
 }
 
+// Warp-cooperative form of compact_hit for the drain phase: all 32 lanes call it (lanes
+// without an entry pass valid=false).  Lanes that append to the same bucket are merged with
+// __match_any_sync so that one shared-memory atomic reserves the slots of the whole group.
+__device__ __forceinline__ void compact_hits_warp(SelWs* ws, CompactSmem& S, uint64_t* __restrict__ arena,
+                                                  bool valid, int set, int col, uint32_t e, uint64_t key) {
+  const int lane = threadIdx.x & 31;
+  const unsigned lt = (1u << lane) - 1u;
+  const uint32_t j0 = valid ? (e & 0xffu) : 255u;
+  int run = 0;
+  if (j0 != 255u) run = S.bk[j0].run;
+  int maxrun = run;
+#pragma unroll
+  for (int m = 16; m; m >>= 1) {
+    const int o = __shfl_xor_sync(KVM_FULL, maxrun, m);
+    maxrun = o > maxrun ? o : maxrun;
+  }
+  for (int r = 0; r < maxrun; ++r) {
+    int j = -1;
+    if (r < run && ((S.bk[j0 + r].set_mask >> set) & 1u)) j = (int)j0 + r;
+    const unsigned peers = __match_any_sync(KVM_FULL, j);
+    if (j >= 0) {
+      const int leader = __ffs(peers) - 1;
+      uint32_t base = 0;
+      if (lane == leader) base = atomicAdd(&S.stage_n[j], (uint32_t)__popc(peers));
+      base = __shfl_sync(peers, base, leader);
+      const uint32_t sp = base + (uint32_t)__popc(peers & lt);
+      if (sp < (uint32_t)STAGE_SLOTS) {
+        S.stage[j][sp] = key;
+      } else {
+        const unsigned long long pos =
+            atomicAdd(reinterpret_cast<unsigned long long*>(&ws->bucket_counts[j]), 1ull);
+        if ((int64_t)pos < S.bk[j].count) arena[S.bk_off[j] + (int64_t)pos] = key;
+      }
+    }
+  }
+  const uint32_t code = valid ? (e >> 8) : 0u;
+  if (code) {
+    const int h = S.col_hist[col];
+    const int bin = code == 255u ? bin_of(key, S.thr[h], S.num_bins)
+                                 : (int)code - (key < S.thr[h][code - 1] ? 1 : 0);
+    atomicAdd(&S.edge[h][bin], 1u);
+  }
+}
+
 constexpr int CQ_CAP = 128;  // per-warp queue of interesting keys
 
 struct CompactQueue {
@@ -796,9 +860,11 @@ log_compact_kernel(kvm_request_log log, const uint8_t* __restrict__ flags, SelWs
   int qn = 0;  // warp-uniform queue length
   auto drain = [&]() {
     __syncwarp();
-    for (int i = lane; i < qn; i += 32) {
-      const uint32_t m = Q.meta[warp][i];
-      compact_hit(ws, S, arena, m & 0xff, (m >> 8) & 0xff, m >> 16, Q.key[warp][i]);
+    for (int i0 = 0; i0 < qn; i0 += 32) {
+      const int i = i0 + lane;
+      const bool valid = i < qn;
+      const uint32_t m = valid ? Q.meta[warp][i] : 0u;
+      compact_hits_warp(ws, S, arena, valid, m & 0xff, (m >> 8) & 0xff, m >> 16, valid ? Q.key[warp][i] : 0ull);
     }
     __syncwarp();
     qn = 0;
@@ -885,6 +951,144 @@ log_compact_kernel(kvm_request_log log, const uint8_t* __restrict__ flags, SelWs
                    const uint32_t e = S.tab[col][digit_of(key, kb[col], shf[col])];
                    if (e != 0x00ffu) compact_hit(ws, S, arena, set, col, e, key);
                  });
+  }
+  __syncthreads();
+  // flush the stages: one global cursor bump per non-empty bucket, then a cooperative copy
+  if (threadIdx.x < MAXQ) {
+    const uint32_t c = S.stage_n[threadIdx.x] < (uint32_t)STAGE_SLOTS ? S.stage_n[threadIdx.x] : (uint32_t)STAGE_SLOTS;
+    S.stage_n[threadIdx.x] = c;
+    if (c) S.stage_pos[threadIdx.x] =
+        atomicAdd(reinterpret_cast<unsigned long long*>(&ws->bucket_counts[threadIdx.x]), (unsigned long long)c);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < MAXQ * STAGE_SLOTS; i += SEL_THREADS) {
+    const int j = i / STAGE_SLOTS, k = i % STAGE_SLOTS;
+    if ((uint32_t)k < S.stage_n[j]) {
+      const int64_t pos = (int64_t)S.stage_pos[j] + k;
+      if (pos < S.bk[j].count) arena[S.bk_off[j] + pos] = S.stage[j][k];
+    }
+  }
+  for (int i = threadIdx.x; i < NH * NB_MAX; i += SEL_THREADS) {
+    const uint32_t c = (&S.edge[0][0])[i];
+    if (c) atomicAdd(&ws->edge20[0][0] + i, (unsigned long long)c);
+  }
+}
+
+// ---- compact pass driven by the digit records of the hist pass --------------------------------
+// Streams 9 B/row (8 B record + 1 B flags).  A row's value is fetched from its column only when
+// one of its fine bins is interesting (~3% of the sites), in the dense drain phase.
+struct RecQueue {
+  int64_t row[SEL_THREADS / 32][CQ_CAP];
+  uint32_t meta[SEL_THREADS / 32][CQ_CAP];  // value column | table entry << 8
+};
+
+template <int ROWS>
+__global__ void __launch_bounds__(SEL_THREADS, 2)
+log_compact_rec_kernel(kvm_request_log log, const uint8_t* __restrict__ flags,
+                       const uint64_t* __restrict__ recs, SelWs* ws, uint64_t* arena) {
+  extern __shared__ __align__(16) unsigned char craw[];
+  CompactSmem& S = *reinterpret_cast<CompactSmem*>(craw);
+  RecQueue& Q = *reinterpret_cast<RecQueue*>(craw + ((sizeof(CompactSmem) + 15) / 16) * 16);
+  if (ws->status != KVM_OK) return;
+  if (threadIdx.x == 0) S.num_bins = ws->hspec.num_bins;
+  if (threadIdx.x < KVM_MAX_COLS) S.col_hist[threadIdx.x] = ws->col_hist[threadIdx.x];
+  for (int i = threadIdx.x; i < KVM_LOG_NCOLS * BINS / 2; i += SEL_THREADS)
+    reinterpret_cast<uint32_t*>(&S.tab[0][0])[i] = reinterpret_cast<const uint32_t*>(&ws->tab[0][0])[i];
+  for (int i = threadIdx.x; i < NH * NB_MAX; i += SEL_THREADS) {
+    (&S.thr[0][0])[i] = (&ws->thr20[0][0])[i];
+    (&S.edge[0][0])[i] = 0;
+  }
+  for (int i = threadIdx.x; i < MAXQ; i += SEL_THREADS) {
+    S.bk[i] = ws->bucket[i];
+    S.bk_off[i] = ws->bucket_offsets[i];
+    S.stage_n[i] = 0;
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const unsigned lt = (1u << lane) - 1u;
+  int qn = 0;  // warp-uniform queue length
+  auto drain = [&]() {
+    __syncwarp();
+    for (int k0 = 0; k0 < qn; k0 += 32) {
+      const int k = k0 + lane;
+      const bool valid = k < qn;
+      const int64_t r = valid ? Q.row[warp][k] : 0;
+      const uint32_t m = valid ? Q.meta[warp][k] : 0u;
+      const int col = m & 0xff;
+      const uint32_t e = m >> 8;
+      const uint8_t fl = valid ? flags[r] : 0;
+      const bool cold = fl & KVM_F_COLD;
+      double v = 0.0;
+      int set = 0;
+      if (!valid) {
+      } else if (col == KVM_COL_LAT) {
+        v = log.latency_ms[r];
+        set = cold ? KVM_SET_LAT_COLD : KVM_SET_LAT_WARM;
+      } else if (col == KVM_COL_TTFB) {
+        v = log.ttfb_ms[r];
+        set = cold ? KVM_SET_TTFB_COLD : KVM_SET_TTFB_WARM;
+      } else if (col == KVM_COL_TLLT) {
+        v = log.tllt_ms[r];
+        set = KVM_SET_TLLT;
+      } else {
+        v = log.tllt_ms[r] - log.ttfb_ms[r];               // analyze.py:144
+        set = KVM_SET_GEN;
+        if (col == KVM_COL_PERTOK) {
+          v = v / (double)log.completion_tokens[r];         // analyze.py:146
+          set = KVM_SET_PERTOK;
+        }
+      }
+      compact_hits_warp(ws, S, arena, valid, set, col, e, kvm_key(v));
+    }
+    __syncwarp();
+    qn = 0;
+  };
+  auto row = [&](int64_t r, uint64_t rec) {
+#pragma unroll
+    for (int c = 0; c < KVM_LOG_NCOLS; ++c) {
+      const uint32_t d = (uint32_t)(rec >> (12 * c)) & 0xFFFu;
+      uint32_t e = 0x00ffu;
+      if (d != 0xFFFu) e = S.tab[c][d];
+      const unsigned hits = __ballot_sync(KVM_FULL, e != 0x00ffu);
+      if (hits) {
+        const int cnt = __popc(hits);
+        if (qn + cnt > CQ_CAP) drain();
+        if (e != 0x00ffu) {
+          const int pos = qn + __popc(hits & lt);
+          Q.row[warp][pos] = r;
+          Q.meta[warp][pos] = (uint32_t)c | (e << 8);
+        }
+        qn += cnt;
+      }
+    }
+  };
+  const int64_t n = log.n;
+  const int64_t nunits = ROWS == 2 ? (n >> 1) : n;
+  for (int64_t base = (int64_t)blockIdx.x * SEL_THREADS + (threadIdx.x & ~31); base < nunits;
+       base += (int64_t)gridDim.x * SEL_THREADS) {
+    const int64_t u = base + lane;
+    const bool live = u < nunits;
+    const int64_t i = ROWS == 2 ? (u << 1) : u;
+    uint64_t r0 = DIGITS_NONE, r1 = DIGITS_NONE;
+    if (live) {
+      if (ROWS == 2) {
+        const longlong2 rr = kvm_ld2(reinterpret_cast<const int64_t*>(recs) + i);
+        r0 = (uint64_t)rr.x;
+        r1 = (uint64_t)rr.y;
+      } else {
+        r0 = kvm_ld1(recs + i);
+      }
+    }
+    if (!__any_sync(KVM_FULL, (r0 & r1) != DIGITS_NONE)) continue;
+    row(i, r0);
+    if (ROWS == 2) row(i + 1, r1);
+    if (qn >= 32) drain();
+  }
+  drain();
+  if (ROWS == 2 && (n & 1) && blockIdx.x == 0 && threadIdx.x < 32) {  // odd tail row, one warp
+    const int64_t i = n - 1;
+    row(i, lane == 0 ? recs[i] : DIGITS_NONE);
+    drain();
   }
   __syncthreads();
   // flush the stages: one global cursor bump per non-empty bucket, then a cooperative copy
@@ -1205,14 +1409,16 @@ extern "C" int kvm_log_select_hist(const kvm_request_log* log, const uint8_t* fl
     KVM_CUDA_CHECK(cudaMemsetAsync(extras->series_dropped, 0, sizeof(int64_t), st));
   }
   const size_t smem = (size_t)KVM_LOG_NSETS * BINS * sizeof(uint32_t);
-  const bool vec = log_vec_ok(log, flags) && (!series || aligned16(log->start_ms));
+  uint64_t* digits = extras ? reinterpret_cast<uint64_t*>(extras->digit_records) : nullptr;
+  const bool vec = log_vec_ok(log, flags) && (!series || aligned16(log->start_ms)) &&
+                   (digits == nullptr || aligned16(digits));
   const int grid = kvm_grid_for(log->n, SEL_THREADS * 2 * 4, 2);
   SelWs* ws = reinterpret_cast<SelWs*>(workspace);
 #define KVM_LAUNCH_HIST(R, S)                                                    \
   do {                                                                           \
     int rc = ensure_smem((const void*)log_hist_kernel<R, S>, smem);              \
     if (rc) return rc;                                                           \
-    log_hist_kernel<R, S><<<grid, SEL_THREADS, smem, st>>>(*log, flags, ws, sa); \
+    log_hist_kernel<R, S><<<grid, SEL_THREADS, smem, st>>>(*log, flags, ws, sa, digits); \
   } while (0)
   if (vec && series) KVM_LAUNCH_HIST(2, true);
   else if (vec) KVM_LAUNCH_HIST(2, false);
@@ -1250,8 +1456,24 @@ extern "C" int kvm_select_resolve(void* workspace, void* stream) {
 }
 
 extern "C" int kvm_log_select_compact(const kvm_request_log* log, const uint8_t* flags,
-                                      void* workspace, void* stream) {
+                                      const uint64_t* digit_records, void* workspace, void* stream) {
   KVM_REQUIRE(log && flags && workspace, "kvm_log_select_compact: null argument");
+  if (digit_records) {
+    const size_t smem_r = ((sizeof(CompactSmem) + 15) / 16) * 16 + sizeof(RecQueue);
+    const int grid_r = kvm_grid_for(log->n, SEL_THREADS * 2 * 8, 2);
+    int rc_r;
+    if (aligned16(digit_records) && (reinterpret_cast<uintptr_t>(flags) & 1u) == 0) {
+      if ((rc_r = ensure_smem((const void*)log_compact_rec_kernel<2>, smem_r))) return rc_r;
+      log_compact_rec_kernel<2><<<grid_r, SEL_THREADS, smem_r, (cudaStream_t)stream>>>(
+          *log, flags, digit_records, reinterpret_cast<SelWs*>(workspace), arena_of(workspace));
+    } else {
+      if ((rc_r = ensure_smem((const void*)log_compact_rec_kernel<1>, smem_r))) return rc_r;
+      log_compact_rec_kernel<1><<<grid_r, SEL_THREADS, smem_r, (cudaStream_t)stream>>>(
+          *log, flags, digit_records, reinterpret_cast<SelWs*>(workspace), arena_of(workspace));
+    }
+    KVM_CUDA_CHECK(cudaGetLastError());
+    return KVM_OK;
+  }
   const size_t smem = ((sizeof(CompactSmem) + 15) / 16) * 16 + sizeof(CompactQueue);
   const int grid = kvm_grid_for(log->n, SEL_THREADS * 2 * 4, 2);
   int rc;
@@ -1330,7 +1552,8 @@ extern "C" int kvm_log_select(const kvm_request_log* log, const uint8_t* flags,
   if (rc) return rc;
   if ((rc = kvm_log_select_hist(log, flags, stats, extras, workspace, stream))) return rc;
   if ((rc = kvm_select_resolve(workspace, stream))) return rc;
-  if ((rc = kvm_log_select_compact(log, flags, workspace, stream))) return rc;
+  if ((rc = kvm_log_select_compact(log, flags, extras ? reinterpret_cast<const uint64_t*>(extras->digit_records) : nullptr,
+                                   workspace, stream))) return rc;
   return kvm_select_finish(workspace, nullptr, 0, nullptr, results, hists ? extras->hist_counts : nullptr, stream);
 }
 

@@ -144,6 +144,7 @@ class ShardedAnalyzer(engine.LogAnalyzer):
             extras.series = series_d.data_ptr()
             extras.series_dropped = dropped_d.data_ptr()
 
+        extras.digit_records = self._digits.data_ptr()
         arena = self._sel_cap
         while True:
             ws, fl = self._sel_ws.data_ptr(), self._flags.data_ptr()
@@ -159,7 +160,8 @@ class ShardedAnalyzer(engine.LogAnalyzer):
             with tm.stage("select_resolve"):
                 N.check(lib.kvm_select_resolve(ws, st), "kvm_select_resolve")
             with tm.stage("select_compact"):
-                N.check(lib.kvm_log_select_compact(C.byref(log_c), fl, ws, st), "kvm_log_select_compact")
+                N.check(lib.kvm_log_select_compact(C.byref(log_c), fl, self._digits.data_ptr(), ws, st),
+                        "kvm_log_select_compact")
             rc = lib.kvm_select_status(ws, st)   # synchronises; identical on every rank (global counts)
             if rc == N.KVM_ERR_ARENA:
                 arena = max(2 * arena, n_global * 4 + 1024)

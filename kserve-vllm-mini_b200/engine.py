@@ -261,6 +261,7 @@ class LogAnalyzer:
     def _ensure(self, n: int, arena: Optional[int] = None) -> None:
         if self._flags is None or self._flags.shape[0] < n + 2:
             self._flags = torch.empty(n + 2, dtype=torch.uint8, device=self.device)
+            self._digits = torch.empty(n + 2, dtype=torch.int64, device=self.device)   # 8 B/row scratch
         cap = arena if arena is not None else int(self.lib.kvm_select_default_arena(n))
         if self._sel_ws is None or self._sel_cap < cap:
             self._sel_ws = torch.empty(self.lib.kvm_select_workspace_bytes(cap), dtype=torch.uint8, device=self.device)
@@ -336,6 +337,7 @@ class LogAnalyzer:
             extras.series_max_bins = int(self._series_d.shape[1])
             extras.series = self._series_d.data_ptr()
             extras.series_dropped = self._dropped_ptr
+        extras.digit_records = self._digits.data_ptr()
         ws, fl = self._sel_ws.data_ptr(), self._flags.data_ptr()
         with tm.stage("select_plan"):
             N.check(lib.kvm_select_plan(self._stats_ptr + N.LogStatsC.sets.offset, queries, nq,
@@ -347,7 +349,8 @@ class LogAnalyzer:
         with tm.stage("select_resolve"):
             N.check(lib.kvm_select_resolve(ws, st), "kvm_select_resolve")
         with tm.stage("select_compact"):
-            N.check(lib.kvm_log_select_compact(C.byref(log_c), fl, ws, st), "kvm_log_select_compact")
+            N.check(lib.kvm_log_select_compact(C.byref(log_c), fl, self._digits.data_ptr(), ws, st),
+                    "kvm_log_select_compact")
         with tm.stage("select_finish"):
             N.check(lib.kvm_select_finish(ws, None, 0, None, self._results_ptr,
                                           self._hist_ptr if fused_hists else None, st), "kvm_select_finish")
