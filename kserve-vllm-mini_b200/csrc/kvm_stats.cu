@@ -60,26 +60,40 @@ log_scan_kernel(kvm_request_log log, const double* __restrict__ cold_lo_g,
   const int64_t n = log.n;
 
   if (VEC) {
+    // software-pipelined: the seven 128-bit loads of the next pair are in flight while the
+    // current pair is processed (the per-row arithmetic is a long dependent chain)
     const int64_t npairs = n >> 1;
-    for (int64_t p = (int64_t)blockIdx.x * STATS_THREADS + threadIdx.x; p < npairs;
-         p += (int64_t)gridDim.x * STATS_THREADS) {
+    const int64_t stride = (int64_t)gridDim.x * STATS_THREADS;
+    int64_t p = (int64_t)blockIdx.x * STATS_THREADS + threadIdx.x;
+    double2 st, la, tf, tl;
+    longlong2 ss, ct, tt;
+    uint16_t cm = 0;
+    auto load = [&](int64_t q, double2& st_, double2& la_, double2& tf_, double2& tl_, longlong2& ss_,
+                    longlong2& ct_, longlong2& tt_, uint16_t& cm_) {
+      const int64_t i = q << 1;
+      st_ = kvm_ld2(log.start_ms + i);
+      la_ = kvm_ld2(log.latency_ms + i);
+      tf_ = kvm_ld2(log.ttfb_ms + i);
+      tl_ = kvm_ld2(log.tllt_ms + i);
+      ss_ = kvm_ld2(log.status + i);
+      ct_ = kvm_ld2(log.completion_tokens + i);
+      tt_ = kvm_ld2(log.total_tokens + i);
+      if (cold_mask) cm_ = kvm_ld_u8x2(cold_mask + i);
+    };
+    if (p < npairs) load(p, st, la, tf, tl, ss, ct, tt, cm);
+    while (p < npairs) {
+      const int64_t pn = p + stride;
+      double2 st2 = st, la2 = la, tf2 = tf, tl2 = tl;
+      longlong2 ss2 = ss, ct2 = ct, tt2 = tt;
+      uint16_t cm2 = cm;
+      if (pn < npairs) load(pn, st2, la2, tf2, tl2, ss2, ct2, tt2, cm2);
       const int64_t i = p << 1;
-      const double2 st = kvm_ld2(log.start_ms + i);
-      const double2 la = kvm_ld2(log.latency_ms + i);
-      const double2 tf = kvm_ld2(log.ttfb_ms + i);
-      const double2 tl = kvm_ld2(log.tllt_ms + i);
-      const longlong2 ss = kvm_ld2(log.status + i);
-      const longlong2 ct = kvm_ld2(log.completion_tokens + i);
-      const longlong2 tt = kvm_ld2(log.total_tokens + i);
-      int c0 = -1, c1 = -1;
-      if (cold_mask) {
-        const uint16_t cm = kvm_ld_u8x2(cold_mask + i);
-        c0 = cm & 0xff;
-        c1 = cm >> 8;
-      }
+      const int c0 = cold_mask ? (int)(cm & 0xff) : -1, c1 = cold_mask ? (int)(cm >> 8) : -1;
       const uint8_t f0 = process_row(a, st.x, la.x, tf.x, tl.x, ss.x, ct.x, tt.x, cold, c0);
       const uint8_t f1 = process_row(a, st.y, la.y, tf.y, tl.y, ss.y, ct.y, tt.y, cold, c1);
       if (flags) *reinterpret_cast<uint16_t*>(flags + i) = (uint16_t)f0 | ((uint16_t)f1 << 8);
+      st = st2; la = la2; tf = tf2; tl = tl2; ss = ss2; ct = ct2; tt = tt2; cm = cm2;
+      p = pn;
     }
     if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
       const int64_t i = n - 1;
