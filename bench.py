@@ -204,11 +204,33 @@ def run_ours(args):
     staging = {k: torch.empty_like(v) for k, v in resident.items()}   # fixed device buffers for e2e
     dlog_staging = engine.DeviceLog.from_tensors(staging)
 
-    def step(dlog, use_graph):
-        raw = analyzer.analyze(dlog, cold, use_graph=use_graph) if world == 1 else analyzer.analyze(dlog, cold)
+    def finish(raw):
         core = report.core_results(raw, len(cold))
         cost = cost_api.rollup(raw, pricing, rsecs, 1.5, None)
         return core, cost, raw
+
+    def step(dlog, use_graph):
+        raw = analyzer.analyze(dlog, cold, use_graph=use_graph) if world == 1 else analyzer.analyze(dlog, cold)
+        return finish(raw)
+
+    # two analyzers with their own buffers: the host turns analysis k into results.json fields
+    # while analysis k+1 is on the GPU (single-GPU path)
+    analyzer_b = engine.LogAnalyzer(device) if world == 1 else None
+
+    def run_pipelined(dlog, k, before_submit=None):
+        pair = (analyzer, analyzer_b)
+        pending, out, launches = None, None, 0
+        for it in range(k):
+            an = pair[it & 1]
+            if before_submit is not None:
+                before_submit()
+            nxt = an.analyze_async(dlog, cold, use_graph=True)
+            launches += an.launches
+            if pending is not None:
+                out = finish(pending())
+            pending = nxt
+        out = finish(pending())
+        return out, launches
 
     def e2e_step():
         for k, v in pinned.items():
@@ -220,9 +242,11 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize(device)
 
-    # ---- warm-up (also captures the graph)
+    # ---- warm-up (also captures the graphs)
     for _ in range(args.warmup):
         step(dlog_resident, graphs)
+    if graphs:
+        run_pipelined(dlog_resident, 2 * args.warmup)
     barrier()
 
     # ---- timed region 1: inputs resident in HBM
@@ -232,9 +256,12 @@ def run_ours(args):
     barrier()
     ev0.record()
     launches = 0
-    for _ in range(args.steps):
-        core, cost, raw = step(dlog_resident, graphs)
-        launches += analyzer.launches
+    if graphs:
+        (core, cost, raw), launches = run_pipelined(dlog_resident, args.steps)
+    else:
+        for _ in range(args.steps):
+            core, cost, raw = step(dlog_resident, graphs)
+            launches += analyzer.launches
     ev1.record()
     barrier()
     ms_total = ev0.elapsed_time(ev1)

@@ -193,26 +193,64 @@ __device__ __forceinline__ int member_set(int mode, const void* member, int64_t 
   return kvm_ld1(reinterpret_cast<const int64_t*>(member) + i) == 200 ? 0 : 255;
 }
 
+// MODE is a compile-time constant so the single-set modes (all / status==200) stream with
+// 128-bit loads and one counter; only the set-id mode pays for per-set counters.
+template <int MODE, bool VEC>
 __global__ void __launch_bounds__(STATS_THREADS, 4)
-column_stats_kernel(const double* __restrict__ values, int64_t n, int mode,
-                    const void* __restrict__ member, int nsets, kvm_set_info* out, ColStatsWs* ws) {
+column_stats_kernel(const double* __restrict__ values, int64_t n, const void* __restrict__ member,
+                    int nsets, kvm_set_info* out, ColStatsWs* ws) {
   __shared__ uint64_t red[STATS_WARPS][CS_SLOTS];
   __shared__ bool is_last;
   int64_t cnt[KVM_MAX_SETS];
 #pragma unroll
   for (int s = 0; s < KVM_MAX_SETS; ++s) cnt[s] = 0;
-  uint64_t kmin = ~0ull, kmax = 0ull;
-  for (int64_t i = (int64_t)blockIdx.x * STATS_THREADS + threadIdx.x; i < n;
-       i += (int64_t)gridDim.x * STATS_THREADS) {
-    const double v = kvm_ld1(values + i);
-    const int s = member_set(mode, member, i);
-    if (s < nsets && !kvm_isnan(v)) {
-#pragma unroll
-      for (int k = 0; k < KVM_MAX_SETS; ++k) cnt[k] += (s == k);
-      const uint64_t key = kvm_key(v);
-      kmin = key < kmin ? key : kmin;
-      kmax = key > kmax ? key : kmax;
+  const double inf = __longlong_as_double(0x7ff0000000000000ll);
+  double vmin = inf, vmax = -inf;
+  int32_t c0 = 0;
+  if (MODE != KVM_MEMBER_SET_IDS && VEC) {
+    const int64_t npairs = n >> 1;
+    const int64_t* st = reinterpret_cast<const int64_t*>(member);
+    for (int64_t p = (int64_t)blockIdx.x * STATS_THREADS + threadIdx.x; p < npairs;
+         p += (int64_t)gridDim.x * STATS_THREADS) {
+      const int64_t i = p << 1;
+      double2 v = kvm_ld2(values + i);
+      if (MODE == KVM_MEMBER_STATUS) {
+        const longlong2 s2 = kvm_ld2(st + i);
+        if (s2.x != 200) v.x = __longlong_as_double(0x7ff8000000000000ll);
+        if (s2.y != 200) v.y = __longlong_as_double(0x7ff8000000000000ll);
+      }
+      c0 += (v.x == v.x) + (v.y == v.y);
+      vmin = fmin(vmin, fmin(v.x, v.y));   // fmin / fmax skip NaN
+      vmax = fmax(vmax, fmax(v.x, v.y));
     }
+    if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
+      const int64_t i = n - 1;
+      double v = values[i];
+      if (MODE == KVM_MEMBER_STATUS && st[i] != 200) v = __longlong_as_double(0x7ff8000000000000ll);
+      c0 += (v == v);
+      vmin = fmin(vmin, v);
+      vmax = fmax(vmax, v);
+    }
+    cnt[0] = c0;
+  } else {
+    for (int64_t i = (int64_t)blockIdx.x * STATS_THREADS + threadIdx.x; i < n;
+         i += (int64_t)gridDim.x * STATS_THREADS) {
+      const double v = kvm_ld1(values + i);
+      const int s = member_set(MODE, member, i);
+      if (s < nsets && !kvm_isnan(v)) {
+#pragma unroll
+        for (int k = 0; k < KVM_MAX_SETS; ++k) cnt[k] += (s == k);
+        vmin = fmin(vmin, v);
+        vmax = fmax(vmax, v);
+      }
+    }
+  }
+  // ordered keys; a zero bound covers both signed zeros; untouched range -> kmin > kmax
+  uint64_t kmin = vmin == 0.0 ? kvm_key(-0.0) : kvm_key(vmin);
+  uint64_t kmax = vmax == 0.0 ? kvm_key(0.0) : kvm_key(vmax);
+  if (vmin > vmax) {
+    kmin = ~0ull;
+    kmax = 0ull;
   }
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
@@ -340,7 +378,14 @@ extern "C" int kvm_column_stats(const double* values, int64_t n, int32_t mode, c
   ColStatsWs* ws = reinterpret_cast<ColStatsWs*>(workspace);
   KVM_CUDA_CHECK(cudaMemsetAsync(ws, 0, 256, st));
   int grid = kvm_grid_for(n, STATS_THREADS * 8, 4);
-  column_stats_kernel<<<grid, STATS_THREADS, 0, st>>>(values, n, mode, member, nsets, info, ws);
+  const bool vec = (reinterpret_cast<uintptr_t>(values) & 15u) == 0 &&
+                   (mode != KVM_MEMBER_STATUS || (reinterpret_cast<uintptr_t>(member) & 15u) == 0);
+#define KVM_LAUNCH_CS(M, V) \
+  column_stats_kernel<M, V><<<grid, STATS_THREADS, 0, st>>>(values, n, member, nsets, info, ws)
+  if (mode == KVM_MEMBER_ALL) { if (vec) KVM_LAUNCH_CS(KVM_MEMBER_ALL, true); else KVM_LAUNCH_CS(KVM_MEMBER_ALL, false); }
+  else if (mode == KVM_MEMBER_STATUS) { if (vec) KVM_LAUNCH_CS(KVM_MEMBER_STATUS, true); else KVM_LAUNCH_CS(KVM_MEMBER_STATUS, false); }
+  else KVM_LAUNCH_CS(KVM_MEMBER_SET_IDS, false);
+#undef KVM_LAUNCH_CS
   KVM_CUDA_CHECK(cudaGetLastError());
   return KVM_OK;
 }

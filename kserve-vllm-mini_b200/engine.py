@@ -254,6 +254,7 @@ class LogAnalyzer:
         self._series_cap = 1 << 16
         self._query_cache: Dict[int, tuple] = {}
         self._graphs: Dict[tuple, tuple] = {}
+        self._done = torch.cuda.Event()
         self.launches = 0   # kernels launched by the last analyze() (for bench accounting)
         self.timer = _NoTimer()   # bench.py swaps in a StageTimer
 
@@ -364,89 +365,120 @@ class LogAnalyzer:
         # select status word -> outbox, then the whole outbox -> pinned host memory
         self._out_d[self._OFF_STATUS:self._OFF_STATUS + 4].copy_(self._sel_ws[0:4], non_blocking=True)
         self._out_h.copy_(self._out_d, non_blocking=True)
+        if series_window_s is not None and dlog.n > 0:
+            p = self._series_h.shape[1]
+            self._series_h.copy_(self._series_d[:, :p], non_blocking=True)
 
-    def analyze(self, dlog: DeviceLog, cold_times: Sequence[float] = (), num_bins: int = 20,
-                series_window_s: Optional[float] = 1.0, max_series_bins: int = 1 << 24,
-                quantiles: Sequence[Quantile] = ANALYZE_QUANTILES, use_graph: bool = False) -> RawAnalysis:
-        """scan -> plan -> hist(+series) -> resolve -> compact -> finish, all stream-ordered;
-        ONE host synchronisation for everything but the series, which is read back once its
-        length is known from the stats.  use_graph=True replays a captured CUDA graph when
-        the same device buffers are analysed again (steady-state monitoring, benchmarks)."""
+    SERIES_PREFIX = 8192   # windows read back together with the outbox (longer series: one more copy)
+
+    def _submit(self, dlog: DeviceLog, cold_times: Sequence[float], num_bins: int,
+                series_window_s: Optional[float], quantiles: Sequence[Quantile], arena: int,
+                hist_big: Optional[torch.Tensor], use_graph: bool) -> None:
+        """Put one analysis on the stream (graph replay when possible) followed by the read-back
+        of the series prefix and the completion event."""
+        dev = self.device
+        want_series = series_window_s is not None
+        self.launches = 0
+        if use_graph and isinstance(self.timer, _NoTimer):
+            graph_key = (tuple(dlog.cols[k].data_ptr() for k in F64_COLS + I64_COLS), dlog.n,
+                         tuple(sorted(float(c) for c in cold_times)), num_bins, series_window_s,
+                         id(quantiles), arena, self._sel_ws.data_ptr(), self._flags.data_ptr(),
+                         self._series_d.data_ptr() if want_series else 0)
+            entry = self._graphs.get(graph_key)
+            if entry is None:
+                # eager run first (sets function attributes, fills caches), then capture
+                self._enqueue(dlog, cold_times, num_bins, series_window_s, quantiles, arena, hist_big)
+                torch.cuda.current_stream(dev).synchronize()
+                g = torch.cuda.CUDAGraph()
+                self.launches = 0
+                with torch.cuda.graph(g):
+                    self._enqueue(dlog, cold_times, num_bins, series_window_s, quantiles, arena, hist_big)
+                if len(self._graphs) >= 4:
+                    self._graphs.pop(next(iter(self._graphs)))
+                entry = (g, self.launches)
+                self._graphs[graph_key] = entry
+            entry[0].replay()
+            self.launches = entry[1]
+        else:
+            self._enqueue(dlog, cold_times, num_bins, series_window_s, quantiles, arena, hist_big)
+        self._done.record(torch.cuda.current_stream(dev))
+
+    def analyze_async(self, dlog: DeviceLog, cold_times: Sequence[float] = (), num_bins: int = 20,
+                      series_window_s: Optional[float] = 1.0, max_series_bins: int = 1 << 24,
+                      quantiles: Sequence[Quantile] = ANALYZE_QUANTILES, use_graph: bool = False):
+        """Submit an analysis and return a zero-argument callable that waits for it and builds
+        the RawAnalysis.  Lets a caller post-process analysis k on the host while analysis k+1
+        (on another LogAnalyzer) runs on the GPU.  One submission per analyzer at a time."""
         dev = self.device
         nq = 2 * len(quantiles)
         assert nq <= N.KVM_MAX_QUERIES
         fused_hists = num_bins <= N.KVM_HIST_MAX_BINS
         hist_big = None if fused_hists else torch.zeros((4, num_bins), dtype=torch.int64, device=dev)
         want_series = series_window_s is not None and dlog.n > 0
+        win = series_window_s if want_series else None
         self._ensure(dlog.n)
-        arena = self._sel_cap
-        while True:
+        state = {"arena": self._sel_cap}
+
+        def submit():
             if want_series and (self._series_d is None or self._series_d.shape[1] < self._series_cap):
                 self._series_d = torch.empty((3, self._series_cap), dtype=torch.int64, device=dev)
-            self.launches = 0
-            graph_key = None
-            if use_graph and isinstance(self.timer, _NoTimer):
-                graph_key = (tuple(dlog.cols[k].data_ptr() for k in F64_COLS + I64_COLS), dlog.n,
-                             tuple(sorted(float(c) for c in cold_times)), num_bins, series_window_s,
-                             id(quantiles), arena, self._sel_ws.data_ptr(), self._flags.data_ptr(),
-                             self._series_d.data_ptr() if want_series else 0)
-                entry = self._graphs.get(graph_key)
-                if entry is None:
-                    # eager run first (sets function attributes, fills caches), then capture
-                    self._enqueue(dlog, cold_times, num_bins, series_window_s if want_series else None,
-                                  quantiles, arena, hist_big)
-                    torch.cuda.current_stream(dev).synchronize()
-                    g = torch.cuda.CUDAGraph()
-                    self.launches = 0
-                    with torch.cuda.graph(g):
-                        self._enqueue(dlog, cold_times, num_bins, series_window_s if want_series else None,
-                                      quantiles, arena, hist_big)
-                    if len(self._graphs) >= 4:
-                        self._graphs.pop(next(iter(self._graphs)))
-                    entry = (g, self.launches)
-                    self._graphs[graph_key] = entry
-                entry[0].replay()
-                self.launches = entry[1]
-            else:
-                self._enqueue(dlog, cold_times, num_bins, series_window_s if want_series else None,
-                              quantiles, arena, hist_big)
-            torch.cuda.current_stream(dev).synchronize()   # the one synchronisation
-            out = self._out_h.numpy().tobytes()
-            rc = int(np.frombuffer(out, dtype=np.int32, count=1, offset=self._OFF_STATUS)[0])
-            stats = N.LogStatsC.from_buffer_copy(out[:C.sizeof(N.LogStatsC)])
-            if rc == N.KVM_ERR_ARENA:
-                # pathological concentration: retry once with room for every key of every query
-                arena = max(2 * arena, dlog.n * 4 + 1024)
-                self._ensure(dlog.n, arena)
-                continue
-            if rc != N.KVM_OK:
-                raise N.NativeError(f"select failed with status {rc}")
-            series = None
-            if want_series and not math.isnan(stats.min_start_ms):
-                t0, t1 = stats.min_start_ms / 1000.0, stats.max_end_ms / 1000.0
-                nb = max(1, int(math.ceil((t1 - t0) / series_window_s)) + 1)
-                dropped = int(np.frombuffer(out, dtype=np.int64, count=1, offset=self._OFF_DROPPED)[0])
-                if dropped != 0:
-                    if nb > max_series_bins:
-                        raise N.NativeError("window series needs more than max_series_bins windows")
-                    self._series_cap = nb + 1      # now known exactly: redo with room for every window
-                    continue
-                nb = min(nb, self._series_d.shape[1])
-                if self._series_h is None or self._series_h.shape[1] < nb:
-                    self._series_h = torch.empty((3, max(nb, 4096)), dtype=torch.int64).pin_memory()
-                self._series_h[:, :nb].copy_(self._series_d[:, :nb], non_blocking=True)
-                torch.cuda.current_stream(dev).synchronize()
-                series = self._series_h[:, :nb].numpy().copy()
-            break
+                self._series_h = torch.empty((3, min(self._series_cap, self.SERIES_PREFIX)),
+                                             dtype=torch.int64).pin_memory()
+            self._submit(dlog, cold_times, num_bins, win, quantiles, state["arena"], hist_big, use_graph)
 
-        res = np.frombuffer(out, dtype=RESULT_DTYPE, count=nq, offset=self._OFF_RESULTS)
-        if fused_hists:
-            hist = np.frombuffer(out, dtype=np.int64, count=4 * num_bins, offset=self._OFF_HIST).reshape(4, num_bins).copy()
-        else:
-            hist = hist_big.cpu().numpy()
-        return RawAnalysis(stats=stats, order=results_to_orderstats(res, quantiles), hist_counts=hist,
-                           num_bins=num_bins, series=series, series_window_s=series_window_s or 1.0,
-                           flags=self._flags[:dlog.n])
+        submit()
+
+        def result() -> RawAnalysis:
+            while True:
+                self._done.synchronize()
+                out = self._out_h.numpy().tobytes()
+                rc = int(np.frombuffer(out, dtype=np.int32, count=1, offset=self._OFF_STATUS)[0])
+                stats = N.LogStatsC.from_buffer_copy(out[:C.sizeof(N.LogStatsC)])
+                if rc == N.KVM_ERR_ARENA:
+                    # pathological concentration: retry with room for every key of every query
+                    state["arena"] = max(2 * state["arena"], dlog.n * 4 + 1024)
+                    self._ensure(dlog.n, state["arena"])
+                    submit()
+                    continue
+                if rc != N.KVM_OK:
+                    raise N.NativeError(f"select failed with status {rc}")
+                series = None
+                if want_series and not math.isnan(stats.min_start_ms):
+                    t0, t1 = stats.min_start_ms / 1000.0, stats.max_end_ms / 1000.0
+                    nb = max(1, int(math.ceil((t1 - t0) / series_window_s)) + 1)
+                    dropped = int(np.frombuffer(out, dtype=np.int64, count=1, offset=self._OFF_DROPPED)[0])
+                    if dropped != 0:
+                        if nb > max_series_bins:
+                            raise N.NativeError("window series needs more than max_series_bins windows")
+                        self._series_cap = nb + 1   # now known exactly: redo with room for every window
+                        submit()
+                        continue
+                    nb = min(nb, self._series_d.shape[1])
+                    if nb <= self._series_h.shape[1]:
+                        series = self._series_h[:, :nb].numpy().copy()   # came back with the outbox
+                    else:
+                        series = self._series_d[:, :nb].cpu().numpy()
+                break
+            res = np.frombuffer(out, dtype=RESULT_DTYPE, count=nq, offset=self._OFF_RESULTS)
+            if fused_hists:
+                hist = np.frombuffer(out, dtype=np.int64, count=4 * num_bins,
+                                     offset=self._OFF_HIST).reshape(4, num_bins).copy()
+            else:
+                hist = hist_big.cpu().numpy()
+            return RawAnalysis(stats=stats, order=results_to_orderstats(res, quantiles), hist_counts=hist,
+                               num_bins=num_bins, series=series, series_window_s=series_window_s or 1.0,
+                               flags=self._flags[:dlog.n])
+
+        return result
+
+    def analyze(self, dlog: DeviceLog, cold_times: Sequence[float] = (), num_bins: int = 20,
+                series_window_s: Optional[float] = 1.0, max_series_bins: int = 1 << 24,
+                quantiles: Sequence[Quantile] = ANALYZE_QUANTILES, use_graph: bool = False) -> RawAnalysis:
+        """scan -> plan -> hist(+series) -> resolve -> compact -> finish, all stream-ordered, ONE
+        host synchronisation.  use_graph=True replays a captured CUDA graph when the same device
+        buffers are analysed again (steady-state monitoring, benchmarks)."""
+        return self.analyze_async(dlog, cold_times, num_bins, series_window_s, max_series_bins,
+                                  quantiles, use_graph)()
 
 
 # --------------------------------------------------------------------------- single columns
