@@ -151,23 +151,31 @@ log_scan_kernel(kvm_request_log log, const double* __restrict__ cold_lo_g,
   if (!is_last) return;
   __threadfence();
 
-  // last CTA: every slot is reduced by one thread over the CTAs in index order
+  // last CTA: warp w reduces slots w, w+8, ... - its lanes stride over the CTAs' partials (the
+  // loads are independent and go to L2), then a fixed-shape shuffle tree combines the lanes.
+  // Integer sums / min / max are order-independent; the double-double sums always follow the
+  // same tree for a given grid size, so the result is run-to-run deterministic.
   __shared__ uint64_t fin[NSLOTS];
-  const volatile uint64_t* part = ws->partial;
-  if (threadIdx.x < NMAX_END) {
-    const int s = threadIdx.x;
-    uint64_t acc = part[s];
-    for (unsigned g = 1; g < gridDim.x; ++g) acc = combine(s, acc, part[(size_t)g * NSLOTS + s]);
-    fin[s] = acc;
-  } else if (threadIdx.x == NMAX_END || threadIdx.x == NMAX_END + 1) {
-    const int s = threadIdx.x == NMAX_END ? D_TTFB : D_LAT;
-    kvm_dd acc = dd_of(part[s], part[s + 1]);
-    for (unsigned g = 1; g < gridDim.x; ++g) {
-      const size_t o = (size_t)g * NSLOTS + s;
-      acc = kvm_dd_add(acc, dd_of(part[o], part[o + 1]));
+  const uint64_t* part = ws->partial;
+  for (int s = warp; s < NSLOTS; s += STATS_WARPS) {
+    if (s < NMAX_END) {
+      uint64_t acc = s < NSUM ? 0ull : (s < NMIN_END ? ~0ull : 0ull);
+      for (unsigned g = lane; g < gridDim.x; g += 32) acc = combine(s, acc, __ldcg(part + (size_t)g * NSLOTS + s));
+#pragma unroll
+      for (int m = 16; m; m >>= 1) acc = combine(s, acc, kvm_shfl_xor(acc, m));
+      if (lane == 0) fin[s] = acc;
+    } else if (s == D_TTFB || s == D_LAT) {
+      kvm_dd acc{0.0, 0.0};
+      for (unsigned g = lane; g < gridDim.x; g += 32) {
+        const size_t o = (size_t)g * NSLOTS + s;
+        acc = kvm_dd_add(acc, dd_of(__ldcg(part + o), __ldcg(part + o + 1)));
+      }
+      acc = kvm_warp_sum(acc);
+      if (lane == 0) {
+        fin[s] = (uint64_t)__double_as_longlong(acc.hi);
+        fin[s + 1] = (uint64_t)__double_as_longlong(acc.lo);
+      }
     }
-    fin[s] = (uint64_t)__double_as_longlong(acc.hi);
-    fin[s + 1] = (uint64_t)__double_as_longlong(acc.lo);
   }
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -283,12 +291,13 @@ column_stats_kernel(const double* __restrict__ values, int64_t n, const void* __
   if (!is_last) return;
   __threadfence();
   __shared__ uint64_t fin[CS_SLOTS];
-  const volatile uint64_t* part = ws->partial;
-  if (threadIdx.x < CS_SLOTS) {
-    const int s = threadIdx.x;
-    uint64_t acc = part[s];
-    for (unsigned b = 1; b < gridDim.x; ++b) acc = combine(s, acc, part[(size_t)b * CS_SLOTS + s]);
-    fin[s] = acc;
+  const uint64_t* part = ws->partial;
+  for (int s = warp; s < CS_SLOTS; s += STATS_WARPS) {
+    uint64_t acc = s < KVM_MAX_SETS ? 0ull : (s == KVM_MAX_SETS ? ~0ull : 0ull);
+    for (unsigned g = lane; g < gridDim.x; g += 32) acc = combine(s, acc, __ldcg(part + (size_t)g * CS_SLOTS + s));
+#pragma unroll
+    for (int m = 16; m; m >>= 1) acc = combine(s, acc, kvm_shfl_xor(acc, m));
+    if (lane == 0) fin[s] = acc;
   }
   __syncthreads();
   if (threadIdx.x == 0) {

@@ -492,27 +492,40 @@ class ColumnOps:
     def order_stats(self, values: torch.Tensor, queries: Sequence[Tuple[int, int, float, int]],
                     member_mode: int = N.MEMBER_ALL, member: Optional[torch.Tensor] = None,
                     nsets: int = 1) -> np.ndarray:
-        """queries: (set_mask, rank_kind, p, rank).  Returns structured array of results."""
+        """queries: (set_mask, rank_kind, p, rank).  Returns structured array of results.
+        Workspace and read-back buffers are cached; one synchronisation per call."""
         assert values.dtype == torch.float64 and values.is_contiguous()
         n = int(values.shape[0])
         nq = len(queries)
         arr = (N.QueryC * nq)(*[N.QueryC(*q) for q in queries])
-        res_d = torch.zeros(N.KVM_MAX_QUERIES * C.sizeof(N.QueryResultC), dtype=torch.uint8, device=self.device)
         st = _stream_ptr(self.device)
-        arena = int(self.lib.kvm_select_default_arena(n))
+        arena = max(int(self.lib.kvm_select_default_arena(n)), getattr(self, "_arena", 0))
+        if getattr(self, "_res_d", None) is None:
+            self._res_d = torch.zeros(N.KVM_MAX_QUERIES * C.sizeof(N.QueryResultC) + 64, dtype=torch.uint8,
+                                      device=self.device)
+            self._res_h = torch.zeros_like(self._res_d, device="cpu").pin_memory()
+        status_off = N.KVM_MAX_QUERIES * C.sizeof(N.QueryResultC)
         while True:
-            ws = torch.empty(self.lib.kvm_select_workspace_bytes(arena), dtype=torch.uint8, device=self.device)
+            if getattr(self, "_ws", None) is None or self._arena < arena:
+                self._ws = torch.empty(self.lib.kvm_select_workspace_bytes(arena), dtype=torch.uint8, device=self.device)
+                self._arena = arena
+            ws = self._ws
             N.check(self.lib.kvm_column_select(values.data_ptr(), n, member_mode,
                                                member.data_ptr() if member is not None else None, nsets,
-                                               arr, nq, res_d.data_ptr(), ws.data_ptr(), ws.numel(), arena, st),
-                    "kvm_column_select")
-            rc = self.lib.kvm_select_status(ws.data_ptr(), st)
+                                               arr, nq, self._res_d.data_ptr(), ws.data_ptr(), ws.numel(),
+                                               self._arena, st), "kvm_column_select")
+            self._res_d[status_off:status_off + 4].copy_(ws[0:4], non_blocking=True)
+            self._res_h.copy_(self._res_d, non_blocking=True)
+            torch.cuda.current_stream(self.device).synchronize()
+            out = self._res_h.numpy().tobytes()
+            rc = int(np.frombuffer(out, dtype=np.int32, count=1, offset=status_off)[0])
             if rc == N.KVM_ERR_ARENA:
                 arena = max(2 * arena, n * nq + 1024)
                 continue
-            N.check(rc, "kvm_column_select")
+            if rc != N.KVM_OK:
+                raise N.NativeError(f"kvm_column_select failed with status {rc}")
             break
-        return np.frombuffer(res_d.cpu().numpy().tobytes(), dtype=RESULT_DTYPE)[:nq]
+        return np.frombuffer(out, dtype=RESULT_DTYPE, count=nq).copy()
 
     def quantile_stat(self, values: torch.Tensor, p: float, **kw) -> OrderStat:
         r = self.order_stats(values, [(1, N.RANK_LERP_LO, p, 0), (1, N.RANK_LERP_HI, p, 0)], **kw)
