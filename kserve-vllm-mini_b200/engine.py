@@ -227,9 +227,12 @@ class LogAnalyzer:
     _OFF_STATUS = _OFF_DROPPED + 8
     _OUTBOX = _OFF_DROPPED + 64
 
-    def __init__(self, device: Optional[torch.device] = None):
+    def __init__(self, device: Optional[torch.device] = None, stream: Optional[torch.cuda.Stream] = None):
         self.device = device or require_cuda()
         self.lib = N.lib()
+        # own stream (optional): lets two analyzers overlap on the GPU - the single-CTA planning /
+        # resolving kernels of one analysis run beside the streaming passes of the other
+        self.stream = stream
         assert C.sizeof(N.LogStatsC) <= self._OFF_RESULTS and C.sizeof(N.QueryResultC) == 32
         self._scan_ws = torch.empty(self.lib.kvm_log_scan_workspace_bytes(), dtype=torch.uint8, device=self.device)
         self._out_d = torch.zeros(self._OUTBOX, dtype=torch.uint8, device=self.device)
@@ -424,7 +427,12 @@ class LogAnalyzer:
                 self._series_d = torch.empty((3, self._series_cap), dtype=torch.int64, device=dev)
                 self._series_h = torch.empty((3, min(self._series_cap, self.SERIES_PREFIX)),
                                              dtype=torch.int64).pin_memory()
-            self._submit(dlog, cold_times, num_bins, win, quantiles, state["arena"], hist_big, use_graph)
+            if self.stream is None:
+                self._submit(dlog, cold_times, num_bins, win, quantiles, state["arena"], hist_big, use_graph)
+            else:
+                self.stream.wait_stream(torch.cuda.current_stream(dev))   # inputs were produced there
+                with torch.cuda.stream(self.stream):
+                    self._submit(dlog, cold_times, num_bins, win, quantiles, state["arena"], hist_big, use_graph)
 
         submit()
 
