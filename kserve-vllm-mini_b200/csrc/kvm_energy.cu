@@ -150,20 +150,31 @@ power_scan_kernel(const double* __restrict__ ts, const double* __restrict__ watt
     is_last = (atomicAdd(&ws->ticket, 1u) == gridDim.x - 1);
   }
   __syncthreads();
-  if (!is_last || threadIdx.x != 0) return;
+  if (!is_last || threadIdx.x >= 32) return;
   __threadfence();
-  const volatile double* part = ws->partial;
-  kvm_power_stats r;
+  // last CTA, warp 0: lanes stride over the CTAs' partials (independent L2 loads), then a
+  // fixed-shape shuffle tree - deterministic for a given grid size
+  const double* part = ws->partial;
+  const int ln = threadIdx.x;
   int64_t sums[PS_NSUM] = {0, 0, 0, 0};
   double a = inf, b = -inf;
   kvm_dd st{0.0, 0.0};
-  for (unsigned g = 0; g < gridDim.x; ++g) {
-    const volatile double* p = part + (size_t)g * SLOTS;
-    for (int c = 0; c < PS_NSUM; ++c) sums[c] += __double_as_longlong(p[c]);
-    a = fmin(a, p[PS_NSUM]);
-    b = fmax(b, p[PS_NSUM + 1]);
-    st = kvm_dd_add(st, kvm_dd{p[PS_NSUM + 2], p[PS_NSUM + 3]});
+  for (unsigned g = ln; g < gridDim.x; g += 32) {
+    const double* p = part + (size_t)g * SLOTS;
+    for (int c = 0; c < PS_NSUM; ++c) sums[c] += __double_as_longlong(__ldcg(p + c));
+    a = fmin(a, __ldcg(p + PS_NSUM));
+    b = fmax(b, __ldcg(p + PS_NSUM + 1));
+    st = kvm_dd_add(st, kvm_dd{__ldcg(p + PS_NSUM + 2), __ldcg(p + PS_NSUM + 3)});
   }
+  for (int c = 0; c < PS_NSUM; ++c) sums[c] = kvm_warp_sum(sums[c]);
+#pragma unroll
+  for (int sft = 16; sft; sft >>= 1) {
+    a = fmin(a, kvm_shfl_xor(a, sft));
+    b = fmax(b, kvm_shfl_xor(b, sft));
+  }
+  st = kvm_warp_sum(st);
+  if (ln != 0) return;
+  kvm_power_stats r;
   r.m = m;
   r.n_valid = sums[PS_VALID];
   r.n_outside = sums[PS_OUT];
@@ -178,14 +189,15 @@ power_scan_kernel(const double* __restrict__ ts, const double* __restrict__ watt
 }
 
 // ------------------------------------------------------------------ K9 trapezoid over k windows
+template <int K>   // accumulators for K windows live in registers (K = 1, 3 or 8)
 __global__ void __launch_bounds__(E_THREADS)
 trapezoid_kernel(const double* __restrict__ ts, const double* __restrict__ watts, int64_t m,
                  Windows win, double* __restrict__ out /* [k][2] */, PartialWs* ws) {
-  __shared__ kvm_dd red[E_WARPS][MAX_WINDOWS];
+  __shared__ kvm_dd red[E_WARPS][K];
   __shared__ bool is_last;
-  kvm_dd acc[MAX_WINDOWS];
+  kvm_dd acc[K];
 #pragma unroll
-  for (int w = 0; w < MAX_WINDOWS; ++w) acc[w] = {0.0, 0.0};
+  for (int w = 0; w < K; ++w) acc[w] = {0.0, 0.0};
   for (int64_t i = (int64_t)blockIdx.x * E_THREADS + threadIdx.x; i < m;
        i += (int64_t)gridDim.x * E_THREADS) {
     const double ti = kvm_ld1(ts + i), wi = kvm_ld1(watts + i);
@@ -193,16 +205,16 @@ trapezoid_kernel(const double* __restrict__ ts, const double* __restrict__ watts
     const double area = segment_wh(ts, watts, i, ti, wi, &tj);
     if (area != 0.0) {
 #pragma unroll
-      for (int w = 0; w < MAX_WINDOWS; ++w)
+      for (int w = 0; w < K; ++w)
         if (w < win.k && win.t1[w] > win.t0[w] && win.t0[w] <= tj && ti <= win.t1[w])
           acc[w] = kvm_dd_add(acc[w], area);
     }
   }
-  kvm_dd tot[MAX_WINDOWS];
-  block_reduce_dd<MAX_WINDOWS>(acc, red, tot);
+  kvm_dd tot[K];
+  block_reduce_dd<K>(acc, red, tot);
   double* mine = ws->partial + (size_t)blockIdx.x * (2 * MAX_WINDOWS);
   if (threadIdx.x == 0) {
-    for (int w = 0; w < MAX_WINDOWS; ++w) {
+    for (int w = 0; w < K; ++w) {
       mine[2 * w] = tot[w].hi;
       mine[2 * w + 1] = tot[w].lo;
     }
@@ -212,15 +224,21 @@ trapezoid_kernel(const double* __restrict__ ts, const double* __restrict__ watts
   __syncthreads();
   if (!is_last) return;
   __threadfence();
-  if (threadIdx.x < win.k) {
-    const volatile double* part = ws->partial;
-    const int w = threadIdx.x;
-    kvm_dd a{0.0, 0.0};
-    for (unsigned g = 0; g < gridDim.x; ++g)
-      a = kvm_dd_add(a, kvm_dd{part[(size_t)g * 2 * MAX_WINDOWS + 2 * w],
-                               part[(size_t)g * 2 * MAX_WINDOWS + 2 * w + 1]});
-    out[2 * w] = a.hi;
-    out[2 * w + 1] = a.lo;
+  {
+    // warp w reduces window w: lanes stride over the partials, fixed-shape tree at the end
+    const double* part = ws->partial;
+    const int w = threadIdx.x >> 5, ln = threadIdx.x & 31;
+    if (w < win.k) {
+      kvm_dd a{0.0, 0.0};
+      for (unsigned g = ln; g < gridDim.x; g += 32)
+        a = kvm_dd_add(a, kvm_dd{__ldcg(part + (size_t)g * 2 * MAX_WINDOWS + 2 * w),
+                                 __ldcg(part + (size_t)g * 2 * MAX_WINDOWS + 2 * w + 1)});
+      a = kvm_warp_sum(a);
+      if (ln == 0) {
+        out[2 * w] = a.hi;
+        out[2 * w + 1] = a.lo;
+      }
+    }
   }
   __syncthreads();
   if (threadIdx.x == 0) ws->ticket = 0;
@@ -292,11 +310,24 @@ prefix_apply_kernel(const double* __restrict__ ts, const double* __restrict__ wa
       a[r] = i < m ? segment_wh(ts, watts, i, ts[i], watts[i], &tj) : 0.0;
       acc = kvm_dd_add(acc, a[r]);
     }
-    thread_tot[threadIdx.x] = acc;
+    // exclusive prefix over the threads of the tile: inclusive shuffle scan inside each warp,
+    // then the warp totals are folded in warp order (fixed shape -> deterministic)
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    kvm_dd incl = acc;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const kvm_dd o{__shfl_up_sync(KVM_FULL, incl.hi, d), __shfl_up_sync(KVM_FULL, incl.lo, d)};
+      if (lane >= d) incl = kvm_dd_add(o, incl);
+    }
+    if (lane == 31) thread_tot[warp] = incl;
     __syncthreads();
-    // exclusive prefix over the threads of the tile (sequential in thread order; 256 dd adds)
     kvm_dd run{tile_excl[2 * tile], tile_excl[2 * tile + 1]};
-    for (int k = 0; k < (int)threadIdx.x; ++k) run = kvm_dd_add(run, thread_tot[k]);
+    for (int w = 0; w < warp; ++w) run = kvm_dd_add(run, thread_tot[w]);
+    {
+      kvm_dd excl{__shfl_up_sync(KVM_FULL, incl.hi, 1), __shfl_up_sync(KVM_FULL, incl.lo, 1)};
+      if (lane == 0) excl = kvm_dd{0.0, 0.0};
+      run = kvm_dd_add(run, excl);   // + exclusive prefix inside the warp
+    }
 #pragma unroll
     for (int r = 0; r < PFX_ITEMS; ++r) {
       const int64_t i = base + r;
@@ -399,8 +430,11 @@ extern "C" int kvm_trapezoid_wh(const double* ts, const double* watts, int64_t m
   win.k = k;
   cudaStream_t st = (cudaStream_t)stream;
   KVM_CUDA_CHECK(cudaMemsetAsync(workspace, 0, 256, st));
-  trapezoid_kernel<<<grid_for(m, E_THREADS * 8), E_THREADS, 0, st>>>(
-      ts, watts, m, win, out_dd, reinterpret_cast<PartialWs*>(workspace));
+  const int grid = grid_for(m, E_THREADS * 8);
+  PartialWs* pws = reinterpret_cast<PartialWs*>(workspace);
+  if (k == 1) trapezoid_kernel<1><<<grid, E_THREADS, 0, st>>>(ts, watts, m, win, out_dd, pws);
+  else if (k <= 3) trapezoid_kernel<3><<<grid, E_THREADS, 0, st>>>(ts, watts, m, win, out_dd, pws);
+  else trapezoid_kernel<8><<<grid, E_THREADS, 0, st>>>(ts, watts, m, win, out_dd, pws);
   KVM_CUDA_CHECK(cudaGetLastError());
   return KVM_OK;
 }

@@ -57,17 +57,22 @@ class SweepAnalyzer:
         hist_d = torch.zeros((max(runs, 1), 4, num_bins), dtype=torch.int64, device=dev)
         status_d = torch.zeros(max(runs, 1), dtype=torch.int32, device=dev)
         log_c = dlog.c_struct()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record(torch.cuda.current_stream(dev))
         N.check(lib.kvm_seg_analyze(C.byref(log_c), offs_d.data_ptr(), runs,
                                     cold_off_d.data_ptr() if cold_off_d is not None else None,
                                     cold_d.data_ptr() if cold_d is not None else None, 30.0,
                                     queries, nq, num_bins, flags.data_ptr(), stats_d.data_ptr(),
                                     res_d.data_ptr(), hist_d.data_ptr(), status_d.data_ptr(),
                                     engine._stream_ptr(dev)), "kvm_seg_analyze")
+        ev1.record(torch.cuda.current_stream(dev))
         self._last = (flags, stats_d, res_d, hist_d, status_d)
+        self._events = (ev0, ev1)
         stats_b = stats_d.cpu().numpy().tobytes()
         res = np.frombuffer(res_d.cpu().numpy().tobytes(), dtype=engine.RESULT_DTYPE).reshape(max(runs, 1), nq)
         hist = hist_d.cpu().numpy()
         status = status_d.cpu().numpy()
+        self.last_kernel_ms = ev0.elapsed_time(ev1)   # device time of the one segmented launch
         out: List[engine.RawAnalysis] = []
         ssz = C.sizeof(N.LogStatsC)
         self.fallback_runs = 0
