@@ -122,6 +122,23 @@ int kvm_log_scan(const kvm_request_log* log_host, const double* cold_times, int3
                  double cold_window_s, const uint8_t* cold_mask, uint8_t* flags, kvm_log_stats* stats,
                  void* workspace, size_t workspace_bytes, void* stream);
 
+/* Multi-GPU (log sharded by time range): shard statistics are combined
+ * on the device with two all-reduces issued by the host between these calls -
+ * sums[kvm_log_stats_pack_sums()] with SUM, mins[kvm_log_stats_pack_mins()] with MIN (maxima
+ * travel complemented).  The double-double sums are NOT combined here: they are gathered and
+ * added in rank order by the host (deterministic).  No reference counterpart (the reference
+ * is single-process); replaces analyze.py:183-189,496-514 across shards. */
+int32_t kvm_log_stats_pack_sums(void);
+int32_t kvm_log_stats_pack_mins(void);
+int kvm_log_stats_pack(const kvm_log_stats* stats, int64_t* sums, int64_t* mins, void* stream);
+int kvm_log_stats_unpack(kvm_log_stats* stats, const int64_t* sums, const int64_t* mins, void* stream);
+/* One-collective form: pack a shard's statistics (sums, mins, the two double-double sums) into
+ * kvm_log_stats_pack_words() int64 words, all-gather them, and combine the `world` records
+ * locally - integer fields exactly, the double-double sums in rank order. */
+int32_t kvm_log_stats_pack_words(void);
+int kvm_log_stats_pack_words_into(const kvm_log_stats* stats, int64_t* packed, void* stream);
+int kvm_log_stats_combine(kvm_log_stats* stats, const int64_t* gathered, int32_t world, void* stream);
+
 /* ------------------------------------------------------------------ exact selection */
 
 /* How a query turns (n, p) into a 0-based rank. */

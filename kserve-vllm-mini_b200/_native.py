@@ -98,6 +98,13 @@ def _declare(lib: C.CDLL) -> None:
         "kvm_sm_count": (C.c_int, []),
         "kvm_log_scan_workspace_bytes": (sz, []),
         "kvm_log_scan": (C.c_int, [P(RequestLogC), vp, i32, f64, vp, vp, vp, vp, sz, vp]),
+        "kvm_log_stats_pack_sums": (i32, []),
+        "kvm_log_stats_pack_mins": (i32, []),
+        "kvm_log_stats_pack": (C.c_int, [vp, vp, vp, vp]),
+        "kvm_log_stats_unpack": (C.c_int, [vp, vp, vp, vp]),
+        "kvm_log_stats_pack_words": (i32, []),
+        "kvm_log_stats_pack_words_into": (C.c_int, [vp, vp, vp]),
+        "kvm_log_stats_combine": (C.c_int, [vp, vp, i32, vp]),
         "kvm_select_workspace_bytes": (sz, [i64]),
         "kvm_select_default_arena": (i64, [i64]),
         "kvm_log_select": (C.c_int, [P(RequestLogC), vp, vp, P(QueryC), i32, vp, P(LogExtrasC), vp, sz, i64, vp]),

@@ -398,3 +398,197 @@ extern "C" int kvm_column_stats(const double* values, int64_t n, int32_t mode, c
   KVM_CUDA_CHECK(cudaGetLastError());
   return KVM_OK;
 }
+
+// ------------------------------------------------------------------ multi-GPU combine helpers
+// A log sharded over several GPUs is scanned per shard; the shard statistics are combined with
+// two NCCL all-reduces the host issues between these two kernels: `sums` (int64, SUM) and
+// `mins` (int64, MIN).  Minima and maxima both travel through the MIN reduction: keys are
+// mapped to order-preserving signed integers and maxima are complemented (~x reverses order).
+namespace {
+constexpr int PACK_SUMS = 8 + KVM_MAX_SETS;
+constexpr int PACK_MINS = 2 * KVM_MAX_COLS + 2;
+constexpr long long MIN64 = (long long)0x8000000000000000ull;
+
+__device__ __forceinline__ long long ordered_of_double(double v) {  // NaN handled by the caller
+  const long long b = __double_as_longlong(v);
+  return b < 0 ? (b ^ 0x7fffffffffffffffll) : b;
+}
+__device__ __forceinline__ double double_of_ordered(long long o) {
+  return __longlong_as_double(o < 0 ? (o ^ 0x7fffffffffffffffll) : o);
+}
+
+__global__ void stats_pack_kernel(const kvm_log_stats* st, long long* sums, long long* mins) {
+  const int t = threadIdx.x;
+  const double inf = __longlong_as_double(0x7ff0000000000000ll);
+  if (t == 0) {
+    sums[0] = st->n_total;
+    sums[1] = st->n_success;
+    sums[2] = st->n_cold;
+    sums[3] = st->n_cold_success;
+    sums[4] = st->sum_completion_tokens;
+    sums[5] = st->sum_total_tokens;
+    sums[6] = st->sum_total_tokens_cold;
+    sums[7] = st->n_gen_rows;
+    const double a = st->min_start_ms, b = st->max_end_ms;
+    mins[2 * KVM_MAX_COLS] = ordered_of_double(a != a ? inf : a);
+    mins[2 * KVM_MAX_COLS + 1] = ~ordered_of_double(b != b ? -inf : b);
+  }
+  if (t < KVM_MAX_SETS) sums[8 + t] = st->sets.count[t];
+  if (t < KVM_MAX_COLS) {
+    mins[t] = (long long)(st->sets.kmin[t]) ^ MIN64;
+    mins[KVM_MAX_COLS + t] = ~((long long)(st->sets.kmax[t]) ^ MIN64);
+  }
+}
+
+__global__ void stats_unpack_kernel(kvm_log_stats* st, const long long* sums, const long long* mins) {
+  const int t = threadIdx.x;
+  const double inf = __longlong_as_double(0x7ff0000000000000ll);
+  const double nan = __longlong_as_double(0x7ff8000000000000ll);
+  if (t == 0) {
+    st->n_total = sums[0];
+    st->n_success = sums[1];
+    st->n_cold = sums[2];
+    st->n_cold_success = sums[3];
+    st->sum_completion_tokens = sums[4];
+    st->sum_total_tokens = sums[5];
+    st->sum_total_tokens_cold = sums[6];
+    st->n_gen_rows = sums[7];
+    const double a = double_of_ordered(mins[2 * KVM_MAX_COLS]);
+    const double b = double_of_ordered(~mins[2 * KVM_MAX_COLS + 1]);
+    st->min_start_ms = a == inf ? nan : a;
+    st->max_end_ms = b == -inf ? nan : b;
+  }
+  if (t < KVM_MAX_SETS) st->sets.count[t] = sums[8 + t];
+  if (t < KVM_MAX_COLS) {
+    st->sets.kmin[t] = (uint64_t)(mins[t] ^ MIN64);
+    st->sets.kmax[t] = (uint64_t)((~mins[KVM_MAX_COLS + t]) ^ MIN64);
+  }
+}
+}  // namespace
+
+extern "C" int32_t kvm_log_stats_pack_sums(void) { return PACK_SUMS; }
+extern "C" int32_t kvm_log_stats_pack_mins(void) { return PACK_MINS; }
+
+extern "C" int kvm_log_stats_pack(const kvm_log_stats* stats, int64_t* sums, int64_t* mins, void* stream) {
+  KVM_REQUIRE(stats && sums && mins, "kvm_log_stats_pack: null argument");
+  stats_pack_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(stats, reinterpret_cast<long long*>(sums),
+                                                       reinterpret_cast<long long*>(mins));
+  KVM_CUDA_CHECK(cudaGetLastError());
+  return KVM_OK;
+}
+
+extern "C" int kvm_log_stats_unpack(kvm_log_stats* stats, const int64_t* sums, const int64_t* mins, void* stream) {
+  KVM_REQUIRE(stats && sums && mins, "kvm_log_stats_unpack: null argument");
+  stats_unpack_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(stats, reinterpret_cast<const long long*>(sums),
+                                                         reinterpret_cast<const long long*>(mins));
+  KVM_CUDA_CHECK(cudaGetLastError());
+  return KVM_OK;
+}
+
+// ---- one-collective form: every rank all-gathers its packed partial
+// [sums | mins | ttfb_hi, ttfb_lo, lat_hi, lat_lo] and combines all of them locally, the
+// double-double sums in RANK ORDER (every rank computes bit-identical totals).
+namespace {
+constexpr int PACK_WORDS = PACK_SUMS + PACK_MINS + 4;
+
+__global__ void stats_pack_words_kernel(const kvm_log_stats* st, long long* packed) {
+  // same packing as stats_pack_kernel, into one contiguous record
+  const int t = threadIdx.x;
+  const double inf = __longlong_as_double(0x7ff0000000000000ll);
+  long long* sums = packed;
+  long long* mins = packed + PACK_SUMS;
+  if (t == 0) {
+    sums[0] = st->n_total;
+    sums[1] = st->n_success;
+    sums[2] = st->n_cold;
+    sums[3] = st->n_cold_success;
+    sums[4] = st->sum_completion_tokens;
+    sums[5] = st->sum_total_tokens;
+    sums[6] = st->sum_total_tokens_cold;
+    sums[7] = st->n_gen_rows;
+    const double a = st->min_start_ms, b = st->max_end_ms;
+    mins[2 * KVM_MAX_COLS] = ordered_of_double(a != a ? inf : a);
+    mins[2 * KVM_MAX_COLS + 1] = ~ordered_of_double(b != b ? -inf : b);
+    long long* dd = packed + PACK_SUMS + PACK_MINS;
+    dd[0] = __double_as_longlong(st->ttfb_sum_hi);
+    dd[1] = __double_as_longlong(st->ttfb_sum_lo);
+    dd[2] = __double_as_longlong(st->lat_sum_hi);
+    dd[3] = __double_as_longlong(st->lat_sum_lo);
+  }
+  if (t < KVM_MAX_SETS) sums[8 + t] = st->sets.count[t];
+  if (t < KVM_MAX_COLS) {
+    mins[t] = (long long)(st->sets.kmin[t]) ^ MIN64;
+    mins[KVM_MAX_COLS + t] = ~((long long)(st->sets.kmax[t]) ^ MIN64);
+  }
+}
+
+__global__ void stats_combine_kernel(kvm_log_stats* st, const long long* gathered, int world) {
+  __shared__ long long sums[PACK_SUMS];
+  __shared__ long long mins[PACK_MINS];
+  const int t = threadIdx.x;
+  if (t < PACK_SUMS) {
+    long long a = 0;
+    for (int r = 0; r < world; ++r) a += gathered[(size_t)r * PACK_WORDS + t];
+    sums[t] = a;
+  } else if (t < PACK_SUMS + PACK_MINS) {
+    const int k = t - PACK_SUMS;
+    long long a = gathered[PACK_SUMS + k];
+    for (int r = 1; r < world; ++r) {
+      const long long v = gathered[(size_t)r * PACK_WORDS + PACK_SUMS + k];
+      a = v < a ? v : a;
+    }
+    mins[k] = a;
+  } else if (t == PACK_SUMS + PACK_MINS || t == PACK_SUMS + PACK_MINS + 1) {
+    const int o = PACK_SUMS + PACK_MINS + 2 * (t - PACK_SUMS - PACK_MINS);
+    kvm_dd acc{0.0, 0.0};
+    for (int r = 0; r < world; ++r)   // rank order
+      acc = kvm_dd_add(acc, kvm_dd{__longlong_as_double(gathered[(size_t)r * PACK_WORDS + o]),
+                                   __longlong_as_double(gathered[(size_t)r * PACK_WORDS + o + 1])});
+    if (o == PACK_SUMS + PACK_MINS) {
+      st->ttfb_sum_hi = acc.hi;
+      st->ttfb_sum_lo = acc.lo;
+    } else {
+      st->lat_sum_hi = acc.hi;
+      st->lat_sum_lo = acc.lo;
+    }
+  }
+  __syncthreads();
+  const double inf = __longlong_as_double(0x7ff0000000000000ll);
+  const double nan = __longlong_as_double(0x7ff8000000000000ll);
+  if (t == 0) {
+    st->n_total = sums[0];
+    st->n_success = sums[1];
+    st->n_cold = sums[2];
+    st->n_cold_success = sums[3];
+    st->sum_completion_tokens = sums[4];
+    st->sum_total_tokens = sums[5];
+    st->sum_total_tokens_cold = sums[6];
+    st->n_gen_rows = sums[7];
+    const double a = double_of_ordered(mins[2 * KVM_MAX_COLS]);
+    const double b = double_of_ordered(~mins[2 * KVM_MAX_COLS + 1]);
+    st->min_start_ms = a == inf ? nan : a;
+    st->max_end_ms = b == -inf ? nan : b;
+  }
+  if (t < KVM_MAX_SETS) st->sets.count[t] = sums[8 + t];
+  if (t < KVM_MAX_COLS) {
+    st->sets.kmin[t] = (uint64_t)(mins[t] ^ MIN64);
+    st->sets.kmax[t] = (uint64_t)((~mins[KVM_MAX_COLS + t]) ^ MIN64);
+  }
+}
+}  // namespace
+
+extern "C" int32_t kvm_log_stats_pack_words(void) { return PACK_WORDS; }
+
+extern "C" int kvm_log_stats_pack_words_into(const kvm_log_stats* stats, int64_t* packed, void* stream) {
+  KVM_REQUIRE(stats && packed, "kvm_log_stats_pack_words_into: null argument");
+  stats_pack_words_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(stats, reinterpret_cast<long long*>(packed));
+  KVM_CUDA_CHECK(cudaGetLastError());
+  return KVM_OK;
+}
+
+extern "C" int kvm_log_stats_combine(kvm_log_stats* stats, const int64_t* gathered, int32_t world, void* stream) {
+  KVM_REQUIRE(stats && gathered && world >= 1, "kvm_log_stats_combine: bad argument");
+  stats_combine_kernel<<<1, 64, 0, (cudaStream_t)stream>>>(stats, reinterpret_cast<const long long*>(gathered), world);
+  KVM_CUDA_CHECK(cudaGetLastError());
+  return KVM_OK;
+}

@@ -98,7 +98,11 @@ def combine_stats(local: N.LogStatsC, device: torch.device, group=None) -> N.Log
 
 class ShardedAnalyzer(engine.LogAnalyzer):
     """LogAnalyzer whose analyze() returns GLOBAL results for a log sharded over the ranks of
-    the default process group (one rank per GPU)."""
+    the default process group (one rank per GPU).  Everything between the first launch and the
+    final read-back is stream-ordered: collectives are enqueued between the kernels, the host
+    synchronises once at the end."""
+
+    GATHER_KEYS = 1 << 19   # candidate keys exchanged per rank (4 MB); more -> one exact retry
 
     def __init__(self, device: Optional[torch.device] = None, group=None):
         super().__init__(device)
@@ -106,6 +110,19 @@ class ShardedAnalyzer(engine.LogAnalyzer):
         self.world = dist.get_world_size(group)
         self.rank = dist.get_rank(group)
         self._bins = int(self.lib.kvm_select_bins())
+        dev = self.device
+        words = int(self.lib.kvm_log_stats_pack_words())
+        self._pack_local = torch.zeros(words, dtype=torch.int64, device=dev)
+        self._pack_all = torch.zeros(self.world * words, dtype=torch.int64, device=dev)
+        # after the compact pass: [bucket counts | histogram edge counters | dropped] per rank
+        self._post_words = N.KVM_MAX_QUERIES + N.KVM_MAX_HISTS * N.KVM_HIST_MAX_BINS + 1
+        self._post_local = torch.zeros(self._post_words, dtype=torch.int64, device=dev)
+        self._post_all = torch.zeros(self.world * self._post_words, dtype=torch.int64, device=dev)
+        self._used_h = torch.zeros(1, dtype=torch.int64).pin_memory()
+        self._counts_all = torch.zeros(self.world * N.KVM_MAX_QUERIES, dtype=torch.int64, device=dev)
+        self._gather_n = self.GATHER_KEYS
+        self._arena_all: Optional[torch.Tensor] = None
+        self._hist_glob = torch.zeros(N.KVM_MAX_HISTS * N.KVM_HIST_MAX_BINS, dtype=torch.int64, device=dev)
 
     def _wrap(self, ptr: int, count: int, dtype=torch.int64) -> torch.Tensor:
         """A tensor view over `count` 8-byte words inside the select workspace."""
@@ -114,46 +131,47 @@ class ShardedAnalyzer(engine.LogAnalyzer):
 
     def analyze(self, dlog: engine.DeviceLog, cold_times: Sequence[float] = (), num_bins: int = 20,
                 series_window_s: Optional[float] = 1.0, max_series_bins: int = 1 << 24,
-                quantiles: Sequence[engine.Quantile] = engine.ANALYZE_QUANTILES) -> engine.RawAnalysis:
-        self.launches = 0
+                quantiles: Sequence[engine.Quantile] = engine.ANALYZE_QUANTILES, **_kw) -> engine.RawAnalysis:
         lib, tm, dev, grp = self.lib, self.timer, self.device, self.group
-        local = self.scan(dlog, cold_times)
-        stats = combine_stats(local, dev, grp)
-        # the global stats drive plan / histogram thresholds / series origin on every rank
-        self._stats_d.copy_(torch.frombuffer(bytearray(bytes(stats)), dtype=torch.uint8))
-        st = engine._stream_ptr(dev)
-        log_c = dlog.c_struct()
-        queries = engine.build_queries(quantiles)
-        nq = len(queries)
-        n_global = int(stats.n_total)
-
         assert num_bins <= N.KVM_HIST_MAX_BINS, "sharded analysis folds the histograms into the select"
-        hist_d = torch.zeros(N.KVM_MAX_HISTS * N.KVM_HIST_MAX_BINS, dtype=torch.int64, device=dev)
+        queries = self._queries(quantiles)
+        nq = len(queries)
         hspec = self.hist_spec(num_bins)
-        series_d, nb = None, 0
-        extras = N.LogExtrasC()
-        if series_window_s is not None and n_global > 0 and not math.isnan(stats.min_start_ms):
-            t0, t1 = stats.min_start_ms / 1000.0, stats.max_end_ms / 1000.0
-            nb = max(1, int(math.ceil((t1 - t0) / series_window_s)) + 1)
-            if nb > max_series_bins:
-                raise N.NativeError("window series needs more than max_series_bins windows")
-            series_d = torch.empty((3, nb), dtype=torch.int64, device=dev)
-            dropped_d = torch.empty(1, dtype=torch.int64, device=dev)
-            extras.series_window_ms = float(series_window_s) * 1000.0
-            extras.series_max_bins = nb
-            extras.series = series_d.data_ptr()
-            extras.series_dropped = dropped_d.data_ptr()
-
-        extras.digit_records = self._digits.data_ptr()
+        want_series = series_window_s is not None
+        self._ensure(dlog.n)
         arena = self._sel_cap
+        log_c = dlog.c_struct()
+        st = engine._stream_ptr(dev)
         while True:
+            self.launches = 0
+            if want_series and (self._series_d is None or self._series_d.shape[1] < self._series_cap):
+                self._series_d = torch.empty((3, self._series_cap), dtype=torch.int64, device=dev)
+                self._series_h = torch.empty((3, min(self._series_cap, self.SERIES_PREFIX)),
+                                             dtype=torch.int64).pin_memory()
+            if self._arena_all is None or self._arena_all.shape[0] < self.world * self._gather_n:
+                self._arena_all = torch.empty(self.world * self._gather_n, dtype=torch.int64, device=dev)
+            # ---- K1 on the shard, then the shard statistics become global ones on the device
+            self._launch_scan(dlog, cold_times)
+            N.check(lib.kvm_log_stats_pack_words_into(self._stats_ptr, self._pack_local.data_ptr(), st))
+            with tm.stage("allgather_stats"):
+                dist.all_gather_into_tensor(self._pack_all, self._pack_local, group=grp)
+            N.check(lib.kvm_log_stats_combine(self._stats_ptr, self._pack_all.data_ptr(), self.world, st))
+            self.launches += 2
+            # ---- select with global digit parameters
+            extras = N.LogExtrasC()
+            if want_series:
+                extras.series_window_ms = float(series_window_s) * 1000.0
+                extras.series_max_bins = int(self._series_d.shape[1])
+                extras.series = self._series_d.data_ptr()
+                extras.series_dropped = self._dropped_ptr
+            extras.digit_records = self._digits.data_ptr()
             ws, fl = self._sel_ws.data_ptr(), self._flags.data_ptr()
             with tm.stage("select_plan"):
-                N.check(lib.kvm_select_plan(self._stats_d.data_ptr() + N.LogStatsC.sets.offset, queries, nq,
+                N.check(lib.kvm_select_plan(self._stats_ptr + N.LogStatsC.sets.offset, queries, nq,
                                             C.byref(hspec), ws, self._sel_ws.numel(), arena, st), "kvm_select_plan")
             with tm.stage("select_hist"):
-                N.check(lib.kvm_log_select_hist(C.byref(log_c), fl, self._stats_d.data_ptr(), C.byref(extras),
-                                                ws, st), "kvm_log_select_hist")
+                N.check(lib.kvm_log_select_hist(C.byref(log_c), fl, self._stats_ptr, C.byref(extras), ws, st),
+                        "kvm_log_select_hist")
             hist = self._wrap(lib.kvm_select_hist_ptr(ws), N.KVM_MAX_SETS * self._bins)
             with tm.stage("allreduce_hist"):
                 dist.all_reduce(hist, op=dist.ReduceOp.SUM, group=grp)
@@ -162,44 +180,72 @@ class ShardedAnalyzer(engine.LogAnalyzer):
             with tm.stage("select_compact"):
                 N.check(lib.kvm_log_select_compact(C.byref(log_c), fl, self._digits.data_ptr(), ws, st),
                         "kvm_log_select_compact")
-            rc = lib.kvm_select_status(ws, st)   # synchronises; identical on every rank (global counts)
+            # ---- candidates of every rank -> every rank (fixed-size exchange, no host round trip)
+            counts_local = self._wrap(lib.kvm_select_bucket_counts_ptr(ws), N.KVM_MAX_QUERIES)
+            arena_local = self._wrap(lib.kvm_select_arena_ptr(ws), self._gather_n)
+            edge = self._wrap(lib.kvm_select_edge_ptr(ws), N.KVM_MAX_HISTS * N.KVM_HIST_MAX_BINS)
+            nqm, ne = N.KVM_MAX_QUERIES, N.KVM_MAX_HISTS * N.KVM_HIST_MAX_BINS
+            dropped = self._out_d[self._OFF_DROPPED:self._OFF_DROPPED + 8].view(torch.int64)
+            self._post_local[:nqm].copy_(counts_local, non_blocking=True)
+            self._post_local[nqm:nqm + ne].copy_(edge, non_blocking=True)
+            self._post_local[nqm + ne:].copy_(dropped, non_blocking=True)
+            with tm.stage("allgather_candidates"):
+                dist.all_gather_into_tensor(self._post_all, self._post_local, group=grp)
+                dist.all_gather_into_tensor(self._arena_all[: self.world * self._gather_n], arena_local, group=grp)
+                if want_series:
+                    dist.all_reduce(self._series_d, op=dist.ReduceOp.SUM, group=grp)
+            post = self._post_all.view(self.world, self._post_words)
+            self._counts_all.copy_(post[:, :nqm].reshape(-1), non_blocking=True)
+            edge.copy_(post[:, nqm:nqm + ne].sum(dim=0), non_blocking=True)
+            dropped.copy_(post[:, nqm + ne:].sum(dim=0), non_blocking=True)
+            ptrs = (C.c_void_p * self.world)(*[self._arena_all.data_ptr() + 8 * r * self._gather_n
+                                               for r in range(self.world)])
+            with tm.stage("select_finish"):
+                # global fine histogram + global edge counters -> global value histograms on every rank
+                N.check(lib.kvm_select_finish(ws, ptrs, self.world, self._counts_all.data_ptr(),
+                                              self._results_ptr, self._hist_ptr, st), "kvm_select_finish")
+            self.launches += 5
+            # ---- one read-back: outbox (+status), gathered fp partials, arena fill, series prefix
+            offsets = self._wrap(lib.kvm_select_bucket_offsets_ptr(ws), N.KVM_MAX_QUERIES + 1)
+            self._out_d[self._OFF_STATUS:self._OFF_STATUS + 4].copy_(self._sel_ws[0:4], non_blocking=True)
+            self._out_h.copy_(self._out_d, non_blocking=True)
+            self._used_h.copy_(offsets[N.KVM_MAX_QUERIES:N.KVM_MAX_QUERIES + 1], non_blocking=True)
+            if want_series:
+                p = self._series_h.shape[1]
+                self._series_h.copy_(self._series_d[:, :p], non_blocking=True)
+            torch.cuda.current_stream(dev).synchronize()   # the one synchronisation
+            out = self._out_h.numpy().tobytes()
+            rc = int(np.frombuffer(out, dtype=np.int32, count=1, offset=self._OFF_STATUS)[0])
+            stats = N.LogStatsC.from_buffer_copy(out[:C.sizeof(N.LogStatsC)])
+            n_global = int(stats.n_total)
             if rc == N.KVM_ERR_ARENA:
                 arena = max(2 * arena, n_global * 4 + 1024)
                 self._ensure(dlog.n, arena)
                 continue
-            N.check(rc, "select")
+            if rc != N.KVM_OK:
+                raise N.NativeError(f"select failed with status {rc}")
+            used = int(self._used_h[0])
+            if used > self._gather_n:       # more candidates than the fixed exchange carries: redo exactly
+                self._gather_n = used + 1024
+                continue
+            series = None
+            if want_series and n_global > 0 and not math.isnan(stats.min_start_ms):
+                t0, t1 = stats.min_start_ms / 1000.0, stats.max_end_ms / 1000.0
+                nb = max(1, int(math.ceil((t1 - t0) / series_window_s)) + 1)
+                dropped = int(np.frombuffer(out, dtype=np.int64, count=1, offset=self._OFF_DROPPED)[0])
+                if dropped != 0:
+                    if nb > max_series_bins:
+                        raise N.NativeError("window series needs more than max_series_bins windows")
+                    self._series_cap = nb + 1
+                    continue
+                nb = min(nb, self._series_d.shape[1])
+                series = (self._series_h[:, :nb].numpy().copy() if nb <= self._series_h.shape[1]
+                          else self._series_d[:, :nb].cpu().numpy())
             break
-        self.launches += 4
-
-        offsets = self._wrap(lib.kvm_select_bucket_offsets_ptr(ws), N.KVM_MAX_QUERIES + 1)
-        used = int(offsets[N.KVM_MAX_QUERIES].item())
-        counts_local = self._wrap(lib.kvm_select_bucket_counts_ptr(ws), N.KVM_MAX_QUERIES)
-        counts_all = torch.empty(self.world * N.KVM_MAX_QUERIES, dtype=torch.int64, device=dev)
-        arena_local = self._wrap(lib.kvm_select_arena_ptr(ws), max(used, 1))
-        arena_all = torch.empty(self.world * max(used, 1), dtype=torch.int64, device=dev)
-        edge = self._wrap(lib.kvm_select_edge_ptr(ws), N.KVM_MAX_HISTS * N.KVM_HIST_MAX_BINS)
-        with tm.stage("allgather_candidates"):
-            dist.all_gather_into_tensor(counts_all, counts_local, group=grp)
-            dist.all_gather_into_tensor(arena_all, arena_local, group=grp)
-            dist.all_reduce(edge, op=dist.ReduceOp.SUM, group=grp)
-        ptrs = (C.c_void_p * self.world)(*[arena_all.data_ptr() + 8 * r * max(used, 1) for r in range(self.world)])
-        with tm.stage("select_finish"):
-            # global fine histogram + global edge counters -> global value histograms on every rank
-            N.check(lib.kvm_select_finish(ws, ptrs, self.world, counts_all.data_ptr(),
-                                          self._results_ptr, hist_d.data_ptr(), st), "kvm_select_finish")
-        self.launches += 1
-        if series_d is not None:
-            dist.all_reduce(series_d, op=dist.ReduceOp.SUM, group=grp)
-            dist.all_reduce(dropped_d, op=dist.ReduceOp.SUM, group=grp)
-        out = self._read_outbox()
-
+        # (fp sums were combined on the device in rank order - identical on every rank)
         res = np.frombuffer(out, dtype=engine.RESULT_DTYPE, count=nq, offset=self._OFF_RESULTS)
-        series = None
-        if series_d is not None:
-            series = series_d.cpu().numpy()
-            if int(dropped_d.item()) != 0:
-                raise N.NativeError("kvm_log_series dropped rows: raise max_series_bins")
+        hist_counts = np.frombuffer(out, dtype=np.int64, count=4 * num_bins,
+                                    offset=self._OFF_HIST).reshape(4, num_bins).copy()
         return engine.RawAnalysis(stats=stats, order=engine.results_to_orderstats(res, quantiles),
-                                  hist_counts=hist_d[:4 * num_bins].view(4, num_bins).cpu().numpy(),
-                                  num_bins=num_bins, series=series,
+                                  hist_counts=hist_counts, num_bins=num_bins, series=series,
                                   series_window_s=series_window_s or 1.0, flags=self._flags[:dlog.n])
