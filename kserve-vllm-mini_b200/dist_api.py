@@ -129,9 +129,103 @@ class ShardedAnalyzer(engine.LogAnalyzer):
         off = ptr - self._sel_ws.data_ptr()
         return self._sel_ws[off: off + 8 * count].view(dtype)
 
+    def _enqueue_sharded(self, dlog, cold_times, queries, nq, hspec, want_series, series_window_s, arena, log_c):
+        """One sharded analysis, stream-ordered (kernels + collectives + read-back copies)."""
+        lib, tm, dev, grp = self.lib, self.timer, self.device, self.group
+        st = engine._stream_ptr(dev)
+        # ---- K1 on the shard, then the shard statistics become global ones on the device
+        self._launch_scan(dlog, cold_times)
+        N.check(lib.kvm_log_stats_pack_words_into(self._stats_ptr, self._pack_local.data_ptr(), st))
+        with tm.stage("allgather_stats"):
+            dist.all_gather_into_tensor(self._pack_all, self._pack_local, group=grp)
+        N.check(lib.kvm_log_stats_combine(self._stats_ptr, self._pack_all.data_ptr(), self.world, st))
+        self.launches += 2
+        # ---- select with global digit parameters
+        extras = N.LogExtrasC()
+        if want_series:
+            extras.series_window_ms = float(series_window_s) * 1000.0
+            extras.series_max_bins = int(self._series_d.shape[1])
+            extras.series = self._series_d.data_ptr()
+            extras.series_dropped = self._dropped_ptr
+        extras.digit_records = self._digits.data_ptr()
+        ws, fl = self._sel_ws.data_ptr(), self._flags.data_ptr()
+        with tm.stage("select_plan"):
+            N.check(lib.kvm_select_plan(self._stats_ptr + N.LogStatsC.sets.offset, queries, nq,
+                                        C.byref(hspec), ws, self._sel_ws.numel(), arena, st), "kvm_select_plan")
+        with tm.stage("select_hist"):
+            N.check(lib.kvm_log_select_hist(C.byref(log_c), fl, self._stats_ptr, C.byref(extras), ws, st),
+                    "kvm_log_select_hist")
+        hist = self._wrap(lib.kvm_select_hist_ptr(ws), N.KVM_MAX_SETS * self._bins)
+        with tm.stage("allreduce_hist"):
+            dist.all_reduce(hist, op=dist.ReduceOp.SUM, group=grp)
+        with tm.stage("select_resolve"):
+            N.check(lib.kvm_select_resolve(ws, st), "kvm_select_resolve")
+        with tm.stage("select_compact"):
+            N.check(lib.kvm_log_select_compact(C.byref(log_c), fl, self._digits.data_ptr(), ws, st),
+                    "kvm_log_select_compact")
+        # ---- candidates of every rank -> every rank (fixed-size exchange, no host round trip)
+        counts_local = self._wrap(lib.kvm_select_bucket_counts_ptr(ws), N.KVM_MAX_QUERIES)
+        arena_local = self._wrap(lib.kvm_select_arena_ptr(ws), self._gather_n)
+        edge = self._wrap(lib.kvm_select_edge_ptr(ws), N.KVM_MAX_HISTS * N.KVM_HIST_MAX_BINS)
+        nqm, ne = N.KVM_MAX_QUERIES, N.KVM_MAX_HISTS * N.KVM_HIST_MAX_BINS
+        dropped = self._out_d[self._OFF_DROPPED:self._OFF_DROPPED + 8].view(torch.int64)
+        self._post_local[:nqm].copy_(counts_local, non_blocking=True)
+        self._post_local[nqm:nqm + ne].copy_(edge, non_blocking=True)
+        self._post_local[nqm + ne:].copy_(dropped, non_blocking=True)
+        with tm.stage("allgather_candidates"):
+            dist.all_gather_into_tensor(self._post_all, self._post_local, group=grp)
+            dist.all_gather_into_tensor(self._arena_all[: self.world * self._gather_n], arena_local, group=grp)
+            if want_series:
+                dist.all_reduce(self._series_d, op=dist.ReduceOp.SUM, group=grp)
+        post = self._post_all.view(self.world, self._post_words)
+        self._counts_all.copy_(post[:, :nqm].reshape(-1), non_blocking=True)
+        edge.copy_(post[:, nqm:nqm + ne].sum(dim=0), non_blocking=True)
+        dropped.copy_(post[:, nqm + ne:].sum(dim=0), non_blocking=True)
+        ptrs = (C.c_void_p * self.world)(*[self._arena_all.data_ptr() + 8 * r * self._gather_n
+                                           for r in range(self.world)])
+        with tm.stage("select_finish"):
+            # global fine histogram + global edge counters -> global value histograms on every rank
+            N.check(lib.kvm_select_finish(ws, ptrs, self.world, self._counts_all.data_ptr(),
+                                          self._results_ptr, self._hist_ptr, st), "kvm_select_finish")
+        self.launches += 5
+        # ---- one read-back: outbox (+status), gathered fp partials, arena fill, series prefix
+        offsets = self._wrap(lib.kvm_select_bucket_offsets_ptr(ws), N.KVM_MAX_QUERIES + 1)
+        self._out_d[self._OFF_STATUS:self._OFF_STATUS + 4].copy_(self._sel_ws[0:4], non_blocking=True)
+        self._out_h.copy_(self._out_d, non_blocking=True)
+        self._used_h.copy_(offsets[N.KVM_MAX_QUERIES:N.KVM_MAX_QUERIES + 1], non_blocking=True)
+        if want_series:
+            p = self._series_h.shape[1]
+            self._series_h.copy_(self._series_d[:, :p], non_blocking=True)
+
+    def _run(self, dlog, cold_times, queries, nq, hspec, want_series, series_window_s, arena, log_c, use_graph):
+        """Eager launch, or replay of a captured CUDA graph (kernels AND NCCL collectives) when the
+        same buffers are analysed again."""
+        if not (use_graph and isinstance(self.timer, engine._NoTimer)):
+            self._enqueue_sharded(dlog, cold_times, queries, nq, hspec, want_series, series_window_s, arena, log_c)
+            return
+        key = (tuple(dlog.cols[k].data_ptr() for k in engine.F64_COLS + engine.I64_COLS), dlog.n,
+               tuple(sorted(float(c) for c in cold_times)), hspec.num_bins, series_window_s, id(queries), arena,
+               self._sel_ws.data_ptr(), self._flags.data_ptr(), self._gather_n,
+               self._series_d.data_ptr() if want_series else 0, self._arena_all.data_ptr())
+        entry = self._graphs.get(key)
+        if entry is None:
+            self._enqueue_sharded(dlog, cold_times, queries, nq, hspec, want_series, series_window_s, arena, log_c)
+            torch.cuda.current_stream(self.device).synchronize()
+            g = torch.cuda.CUDAGraph()
+            self.launches = 0
+            with torch.cuda.graph(g):
+                self._enqueue_sharded(dlog, cold_times, queries, nq, hspec, want_series, series_window_s, arena, log_c)
+            if len(self._graphs) >= 4:
+                self._graphs.pop(next(iter(self._graphs)))
+            entry = (g, self.launches)
+            self._graphs[key] = entry
+        entry[0].replay()
+        self.launches = entry[1]
+
     def analyze(self, dlog: engine.DeviceLog, cold_times: Sequence[float] = (), num_bins: int = 20,
                 series_window_s: Optional[float] = 1.0, max_series_bins: int = 1 << 24,
-                quantiles: Sequence[engine.Quantile] = engine.ANALYZE_QUANTILES, **_kw) -> engine.RawAnalysis:
+                quantiles: Sequence[engine.Quantile] = engine.ANALYZE_QUANTILES,
+                use_graph: bool = False) -> engine.RawAnalysis:
         lib, tm, dev, grp = self.lib, self.timer, self.device, self.group
         assert num_bins <= N.KVM_HIST_MAX_BINS, "sharded analysis folds the histograms into the select"
         queries = self._queries(quantiles)
@@ -150,69 +244,7 @@ class ShardedAnalyzer(engine.LogAnalyzer):
                                              dtype=torch.int64).pin_memory()
             if self._arena_all is None or self._arena_all.shape[0] < self.world * self._gather_n:
                 self._arena_all = torch.empty(self.world * self._gather_n, dtype=torch.int64, device=dev)
-            # ---- K1 on the shard, then the shard statistics become global ones on the device
-            self._launch_scan(dlog, cold_times)
-            N.check(lib.kvm_log_stats_pack_words_into(self._stats_ptr, self._pack_local.data_ptr(), st))
-            with tm.stage("allgather_stats"):
-                dist.all_gather_into_tensor(self._pack_all, self._pack_local, group=grp)
-            N.check(lib.kvm_log_stats_combine(self._stats_ptr, self._pack_all.data_ptr(), self.world, st))
-            self.launches += 2
-            # ---- select with global digit parameters
-            extras = N.LogExtrasC()
-            if want_series:
-                extras.series_window_ms = float(series_window_s) * 1000.0
-                extras.series_max_bins = int(self._series_d.shape[1])
-                extras.series = self._series_d.data_ptr()
-                extras.series_dropped = self._dropped_ptr
-            extras.digit_records = self._digits.data_ptr()
-            ws, fl = self._sel_ws.data_ptr(), self._flags.data_ptr()
-            with tm.stage("select_plan"):
-                N.check(lib.kvm_select_plan(self._stats_ptr + N.LogStatsC.sets.offset, queries, nq,
-                                            C.byref(hspec), ws, self._sel_ws.numel(), arena, st), "kvm_select_plan")
-            with tm.stage("select_hist"):
-                N.check(lib.kvm_log_select_hist(C.byref(log_c), fl, self._stats_ptr, C.byref(extras), ws, st),
-                        "kvm_log_select_hist")
-            hist = self._wrap(lib.kvm_select_hist_ptr(ws), N.KVM_MAX_SETS * self._bins)
-            with tm.stage("allreduce_hist"):
-                dist.all_reduce(hist, op=dist.ReduceOp.SUM, group=grp)
-            with tm.stage("select_resolve"):
-                N.check(lib.kvm_select_resolve(ws, st), "kvm_select_resolve")
-            with tm.stage("select_compact"):
-                N.check(lib.kvm_log_select_compact(C.byref(log_c), fl, self._digits.data_ptr(), ws, st),
-                        "kvm_log_select_compact")
-            # ---- candidates of every rank -> every rank (fixed-size exchange, no host round trip)
-            counts_local = self._wrap(lib.kvm_select_bucket_counts_ptr(ws), N.KVM_MAX_QUERIES)
-            arena_local = self._wrap(lib.kvm_select_arena_ptr(ws), self._gather_n)
-            edge = self._wrap(lib.kvm_select_edge_ptr(ws), N.KVM_MAX_HISTS * N.KVM_HIST_MAX_BINS)
-            nqm, ne = N.KVM_MAX_QUERIES, N.KVM_MAX_HISTS * N.KVM_HIST_MAX_BINS
-            dropped = self._out_d[self._OFF_DROPPED:self._OFF_DROPPED + 8].view(torch.int64)
-            self._post_local[:nqm].copy_(counts_local, non_blocking=True)
-            self._post_local[nqm:nqm + ne].copy_(edge, non_blocking=True)
-            self._post_local[nqm + ne:].copy_(dropped, non_blocking=True)
-            with tm.stage("allgather_candidates"):
-                dist.all_gather_into_tensor(self._post_all, self._post_local, group=grp)
-                dist.all_gather_into_tensor(self._arena_all[: self.world * self._gather_n], arena_local, group=grp)
-                if want_series:
-                    dist.all_reduce(self._series_d, op=dist.ReduceOp.SUM, group=grp)
-            post = self._post_all.view(self.world, self._post_words)
-            self._counts_all.copy_(post[:, :nqm].reshape(-1), non_blocking=True)
-            edge.copy_(post[:, nqm:nqm + ne].sum(dim=0), non_blocking=True)
-            dropped.copy_(post[:, nqm + ne:].sum(dim=0), non_blocking=True)
-            ptrs = (C.c_void_p * self.world)(*[self._arena_all.data_ptr() + 8 * r * self._gather_n
-                                               for r in range(self.world)])
-            with tm.stage("select_finish"):
-                # global fine histogram + global edge counters -> global value histograms on every rank
-                N.check(lib.kvm_select_finish(ws, ptrs, self.world, self._counts_all.data_ptr(),
-                                              self._results_ptr, self._hist_ptr, st), "kvm_select_finish")
-            self.launches += 5
-            # ---- one read-back: outbox (+status), gathered fp partials, arena fill, series prefix
-            offsets = self._wrap(lib.kvm_select_bucket_offsets_ptr(ws), N.KVM_MAX_QUERIES + 1)
-            self._out_d[self._OFF_STATUS:self._OFF_STATUS + 4].copy_(self._sel_ws[0:4], non_blocking=True)
-            self._out_h.copy_(self._out_d, non_blocking=True)
-            self._used_h.copy_(offsets[N.KVM_MAX_QUERIES:N.KVM_MAX_QUERIES + 1], non_blocking=True)
-            if want_series:
-                p = self._series_h.shape[1]
-                self._series_h.copy_(self._series_d[:, :p], non_blocking=True)
+            self._run(dlog, cold_times, queries, nq, hspec, want_series, series_window_s, arena, log_c, use_graph)
             torch.cuda.current_stream(dev).synchronize()   # the one synchronisation
             out = self._out_h.numpy().tobytes()
             rc = int(np.frombuffer(out, dtype=np.int32, count=1, offset=self._OFF_STATUS)[0])
