@@ -272,6 +272,14 @@ int64_t* kvm_select_bucket_counts_ptr(void* workspace); /* [KVM_MAX_QUERIES] loc
 int64_t* kvm_select_bucket_offsets_ptr(void* workspace); /* [KVM_MAX_QUERIES+1] arena offsets */
 kvm_set_info* kvm_select_info_ptr(void* workspace);      /* set info block inside the workspace */
 
+/* one small record per rank after the compact pass: [bucket cursors | edge counters | dropped];
+ * pack -> all-gather -> unpack (cursors per rank into counts_all[world][KVM_MAX_QUERIES], the
+ * rest summed over ranks back into the workspace / *dropped) */
+int32_t kvm_select_post_words(void);
+int kvm_select_post_pack(const void* workspace, const int64_t* dropped, int64_t* record, void* stream);
+int kvm_select_post_unpack(void* workspace, const int64_t* gathered, int32_t world, int64_t* counts_all,
+                           int64_t* dropped, void* stream);
+
 int kvm_select_plan(const kvm_set_info* info, const kvm_query* queries_host, int32_t nq,
                     const kvm_hist_spec* hists_host, void* workspace, size_t workspace_bytes,
                     int64_t arena_capacity, void* stream);

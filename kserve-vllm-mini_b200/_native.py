@@ -120,6 +120,9 @@ def _declare(lib: C.CDLL) -> None:
         "kvm_select_bucket_counts_ptr": (vp, [vp]),
         "kvm_select_bucket_offsets_ptr": (vp, [vp]),
         "kvm_select_info_ptr": (vp, [vp]),
+        "kvm_select_post_words": (i32, []),
+        "kvm_select_post_pack": (C.c_int, [vp, vp, vp, vp]),
+        "kvm_select_post_unpack": (C.c_int, [vp, vp, i32, vp, vp, vp]),
         "kvm_select_plan": (C.c_int, [vp, P(QueryC), i32, P(HistSpecC), vp, sz, i64, vp]),
         "kvm_column_select_hist": (C.c_int, [vp, i64, i32, vp, vp, vp]),
         "kvm_log_select_hist": (C.c_int, [P(RequestLogC), vp, vp, P(LogExtrasC), vp, vp]),

@@ -1637,3 +1637,59 @@ extern "C" int kvm_column_select_static(const double* values, int64_t n, int32_t
   return kvm_column_select(values, n, mode, member, 1, queries, nq, results, scratch,
                            STATIC_SCRATCH_BYTES, STATIC_MAX_N, stream);
 }
+
+// ------------------------------------------------------------------ multi-GPU exchange helpers
+// After the compact pass every rank exchanges one small record
+//   [bucket cursors (KVM_MAX_QUERIES) | histogram edge counters (KVM_MAX_HISTS*KVM_HIST_MAX_BINS) | dropped]
+// with one all-gather; these two kernels pack it and fold the gathered records back in
+// (cursors stay per rank - the finish kernel reads them per source; edge counters and the
+// dropped counter are summed over the ranks).
+namespace {
+constexpr int POST_WORDS = MAXQ + NH * NB_MAX + 1;
+
+__global__ void post_pack_kernel(const SelWs* ws, const long long* dropped, long long* rec) {
+  for (int i = threadIdx.x; i < POST_WORDS; i += blockDim.x) {
+    long long v;
+    if (i < MAXQ) v = ws->bucket_counts[i];
+    else if (i < MAXQ + NH * NB_MAX) v = (long long)(&ws->edge20[0][0])[i - MAXQ];
+    else v = dropped ? *dropped : 0;
+    rec[i] = v;
+  }
+}
+
+__global__ void post_unpack_kernel(SelWs* ws, const long long* all, int world, long long* counts_all,
+                                   long long* dropped) {
+  for (int i = threadIdx.x; i < POST_WORDS; i += blockDim.x) {
+    if (i < MAXQ) {
+      for (int r = 0; r < world; ++r) counts_all[(size_t)r * MAXQ + i] = all[(size_t)r * POST_WORDS + i];
+    } else {
+      long long s = 0;
+      for (int r = 0; r < world; ++r) s += all[(size_t)r * POST_WORDS + i];
+      if (i < MAXQ + NH * NB_MAX) (&ws->edge20[0][0])[i - MAXQ] = (unsigned long long)s;
+      else if (dropped) *dropped = s;
+    }
+  }
+}
+}  // namespace
+
+extern "C" int32_t kvm_select_post_words(void) { return POST_WORDS; }
+
+extern "C" int kvm_select_post_pack(const void* workspace, const int64_t* dropped, int64_t* record, void* stream) {
+  KVM_REQUIRE(workspace && record, "kvm_select_post_pack: null argument");
+  post_pack_kernel<<<1, 128, 0, (cudaStream_t)stream>>>(reinterpret_cast<const SelWs*>(workspace),
+                                                       reinterpret_cast<const long long*>(dropped),
+                                                       reinterpret_cast<long long*>(record));
+  KVM_CUDA_CHECK(cudaGetLastError());
+  return KVM_OK;
+}
+
+extern "C" int kvm_select_post_unpack(void* workspace, const int64_t* gathered, int32_t world,
+                                      int64_t* counts_all, int64_t* dropped, void* stream) {
+  KVM_REQUIRE(workspace && gathered && counts_all && world >= 1, "kvm_select_post_unpack: bad argument");
+  post_unpack_kernel<<<1, 128, 0, (cudaStream_t)stream>>>(reinterpret_cast<SelWs*>(workspace),
+                                                         reinterpret_cast<const long long*>(gathered), world,
+                                                         reinterpret_cast<long long*>(counts_all),
+                                                         reinterpret_cast<long long*>(dropped));
+  KVM_CUDA_CHECK(cudaGetLastError());
+  return KVM_OK;
+}

@@ -115,7 +115,8 @@ class ShardedAnalyzer(engine.LogAnalyzer):
         self._pack_local = torch.zeros(words, dtype=torch.int64, device=dev)
         self._pack_all = torch.zeros(self.world * words, dtype=torch.int64, device=dev)
         # after the compact pass: [bucket counts | histogram edge counters | dropped] per rank
-        self._post_words = N.KVM_MAX_QUERIES + N.KVM_MAX_HISTS * N.KVM_HIST_MAX_BINS + 1
+        self._post_words = int(self.lib.kvm_select_post_words())
+        self._views: dict = {}
         self._post_local = torch.zeros(self._post_words, dtype=torch.int64, device=dev)
         self._post_all = torch.zeros(self.world * self._post_words, dtype=torch.int64, device=dev)
         self._used_h = torch.zeros(1, dtype=torch.int64).pin_memory()
@@ -164,23 +165,26 @@ class ShardedAnalyzer(engine.LogAnalyzer):
             N.check(lib.kvm_log_select_compact(C.byref(log_c), fl, self._digits.data_ptr(), ws, st),
                     "kvm_log_select_compact")
         # ---- candidates of every rank -> every rank (fixed-size exchange, no host round trip)
-        counts_local = self._wrap(lib.kvm_select_bucket_counts_ptr(ws), N.KVM_MAX_QUERIES)
-        arena_local = self._wrap(lib.kvm_select_arena_ptr(ws), self._gather_n)
-        edge = self._wrap(lib.kvm_select_edge_ptr(ws), N.KVM_MAX_HISTS * N.KVM_HIST_MAX_BINS)
-        nqm, ne = N.KVM_MAX_QUERIES, N.KVM_MAX_HISTS * N.KVM_HIST_MAX_BINS
-        dropped = self._out_d[self._OFF_DROPPED:self._OFF_DROPPED + 8].view(torch.int64)
-        self._post_local[:nqm].copy_(counts_local, non_blocking=True)
-        self._post_local[nqm:nqm + ne].copy_(edge, non_blocking=True)
-        self._post_local[nqm + ne:].copy_(dropped, non_blocking=True)
+        vk = (ws, self._gather_n)
+        views = self._views.get(vk)
+        if views is None:
+            self._views.clear()
+            views = (self._wrap(lib.kvm_select_hist_ptr(ws), N.KVM_MAX_SETS * self._bins),
+                     self._wrap(lib.kvm_select_arena_ptr(ws), self._gather_n),
+                     self._wrap(lib.kvm_select_bucket_offsets_ptr(ws), N.KVM_MAX_QUERIES + 1))
+            self._views[vk] = views
+        arena_local = views[1]
+        N.check(lib.kvm_select_post_pack(ws, self._dropped_ptr if want_series else None,
+                                         self._post_local.data_ptr(), st))
         with tm.stage("allgather_candidates"):
             dist.all_gather_into_tensor(self._post_all, self._post_local, group=grp)
             dist.all_gather_into_tensor(self._arena_all[: self.world * self._gather_n], arena_local, group=grp)
             if want_series:
                 dist.all_reduce(self._series_d, op=dist.ReduceOp.SUM, group=grp)
-        post = self._post_all.view(self.world, self._post_words)
-        self._counts_all.copy_(post[:, :nqm].reshape(-1), non_blocking=True)
-        edge.copy_(post[:, nqm:nqm + ne].sum(dim=0), non_blocking=True)
-        dropped.copy_(post[:, nqm + ne:].sum(dim=0), non_blocking=True)
+        N.check(lib.kvm_select_post_unpack(ws, self._post_all.data_ptr(), self.world,
+                                           self._counts_all.data_ptr(),
+                                           self._dropped_ptr if want_series else None, st))
+        self.launches += 2
         ptrs = (C.c_void_p * self.world)(*[self._arena_all.data_ptr() + 8 * r * self._gather_n
                                            for r in range(self.world)])
         with tm.stage("select_finish"):
@@ -189,7 +193,7 @@ class ShardedAnalyzer(engine.LogAnalyzer):
                                           self._results_ptr, self._hist_ptr, st), "kvm_select_finish")
         self.launches += 5
         # ---- one read-back: outbox (+status), gathered fp partials, arena fill, series prefix
-        offsets = self._wrap(lib.kvm_select_bucket_offsets_ptr(ws), N.KVM_MAX_QUERIES + 1)
+        offsets = views[2]
         self._out_d[self._OFF_STATUS:self._OFF_STATUS + 4].copy_(self._sel_ws[0:4], non_blocking=True)
         self._out_h.copy_(self._out_d, non_blocking=True)
         self._used_h.copy_(offsets[N.KVM_MAX_QUERIES:N.KVM_MAX_QUERIES + 1], non_blocking=True)
