@@ -95,19 +95,25 @@ class ClockSampler:
 
 
 # --------------------------------------------------------------------------- CPU arm
-def cpu_port_rate(cols, cold, rows, repeats=1):
-    """records/s of the pure-Python port of analyze.py (+ cost rollup) on `rows` rows."""
+def cpu_port_lists(cols, rows):
+    """Columns as Python lists - what the reference holds after parsing (not part of the timing)."""
+    return {k: v[:rows].tolist() for k, v in cols.items()}
+
+
+def cpu_port_step(sub, cold):
+    """One pass of the pure-Python port of analyze.py (+ cost rollup); returns seconds."""
     from oracle import py_port
-    sub = {k: v[:rows].tolist() for k, v in cols.items()}
-    best = None
-    for _ in range(repeats):
-        t = time.perf_counter()
-        res = py_port.analyze(sub, cold)
-        tokens = py_port.total_tokens_success(sub)
-        py_port.cost_rollup(3600.0, 14400.0, 57600.2, 1.5, 0.04, 0.005, 0.10,
-                            res["requests"]["success"], tokens)
-        dt = time.perf_counter() - t
-        best = dt if best is None else min(best, dt)
+    t = time.perf_counter()
+    res = py_port.analyze(sub, cold)
+    tokens = py_port.total_tokens_success(sub)
+    py_port.cost_rollup(3600.0, 14400.0, 57600.2, 1.5, 0.04, 0.005, 0.10, res["requests"]["success"], tokens)
+    return time.perf_counter() - t
+
+
+def cpu_port_rate(cols, cold, rows, repeats=1):
+    """records/s of the port on the first `rows` rows."""
+    sub = cpu_port_lists(cols, rows)
+    best = min(cpu_port_step(sub, cold) for _ in range(repeats))
     return rows / best, best
 
 
@@ -127,12 +133,10 @@ def run_reference(args):
     cols = synth.request_columns(rows, seed=1234, span_ms=3.6e6 * rows / n)
     t0 = float(cols["start_ms"].min()) / 1000.0
     cold = [t0 + 5.0]
+    sub = cpu_port_lists(cols, rows)
     for _ in range(args.warmup):
-        cpu_port_rate(cols, cold, rows)
-    t = time.perf_counter()
-    for _ in range(args.steps):
-        cpu_port_rate(cols, cold, rows)
-    dt = time.perf_counter() - t
+        cpu_port_step(sub, cold)
+    dt = sum(cpu_port_step(sub, cold) for _ in range(args.steps))
     value = rows * args.steps / dt
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
