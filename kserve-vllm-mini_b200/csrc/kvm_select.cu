@@ -126,10 +126,24 @@ select_plan_kernel(SelWs* ws, const kvm_set_info* info_in, QueryPack qp, kvm_his
                    int64_t arena_capacity) {
   __shared__ kvm_set_info info;
   __shared__ ColParam cps[KVM_MAX_COLS];
+  __shared__ uint64_t thr_s[NH][NB_MAX];
+  __shared__ uint8_t edge_s[KVM_MAX_COLS][BINS];
   const int t = threadIdx.x;
+  // the info block arrives as 8-byte words loaded in parallel (it may alias ws->info)
+  static_assert(sizeof(kvm_set_info) % 8 == 0, "kvm_set_info is copied as 8-byte words");
+  if (t < (int)(sizeof(kvm_set_info) / 8))
+    reinterpret_cast<uint64_t*>(&info)[t] = reinterpret_cast<const uint64_t*>(info_in)[t];
+  // zero what the passes accumulate into
+  for (int i = t; i < KVM_MAX_SETS * BINS; i += PLAN_THREADS) (&ws->hist[0][0])[i] = 0;
+  for (int i = t; i < NH * NB_MAX; i += PLAN_THREADS) {
+    (&ws->edge20[0][0])[i] = 0;
+    (&thr_s[0][0])[i] = ~0ull;
+  }
+  for (int i = t; i < NH * (BINS / 32); i += PLAN_THREADS) (&ws->flag20[0][0])[i] = 0;
+  for (int i = t; i < KVM_MAX_COLS * BINS / 4; i += PLAN_THREADS)
+    reinterpret_cast<uint32_t*>(&edge_s[0][0])[i] = 0;
+  __syncthreads();
   if (t == 0) {
-    info = *info_in;
-    ws->info = info;
     ws->status = KVM_OK;
     ws->nq = qp.nq;
     ws->nbuckets = 0;
@@ -137,16 +151,8 @@ select_plan_kernel(SelWs* ws, const kvm_set_info* info_in, QueryPack qp, kvm_his
     ws->arena_used = 0;
     ws->hspec = hs;
   }
-  // zero what the passes accumulate into
-  for (int i = t; i < KVM_MAX_SETS * BINS; i += PLAN_THREADS) (&ws->hist[0][0])[i] = 0;
-  for (int i = t; i < NH * NB_MAX; i += PLAN_THREADS) {
-    (&ws->edge20[0][0])[i] = 0;
-    (&ws->thr20[0][0])[i] = ~0ull;
-  }
-  for (int i = t; i < NH * (BINS / 32); i += PLAN_THREADS) (&ws->flag20[0][0])[i] = 0;
-  for (int i = t; i < KVM_MAX_COLS * BINS / 4; i += PLAN_THREADS)
-    reinterpret_cast<uint32_t*>(&ws->edge_code[0][0])[i] = 0;
-  __syncthreads();
+  if (t < (int)(sizeof(kvm_set_info) / 8))
+    reinterpret_cast<uint64_t*>(&ws->info)[t] = reinterpret_cast<const uint64_t*>(&info)[t];
   if (t < KVM_MAX_COLS) {
     ColParam cp{0, 0, 0};
     if (t < info.ncols && info.kmin[t] <= info.kmax[t]) {
@@ -204,7 +210,7 @@ select_plan_kernel(SelWs* ws, const kvm_set_info* info_in, QueryPack qp, kvm_his
       const uint64_t klo = info.kmin[c], khi = info.kmax[c];
       if (klo < khi) {
         const uint64_t T = bin_threshold(klo, khi, hs.num_bins, b);
-        ws->thr20[h][b - 1] = T;
+        thr_s[h][b - 1] = T;
         if (T != ~0ull) {
           const uint32_t d = digit_of(T, cps[c].kbase, cps[c].shift);
           atomicOr(&ws->flag20[h][d >> 5], 1u << (d & 31));
@@ -219,13 +225,24 @@ select_plan_kernel(SelWs* ws, const kvm_set_info* info_in, QueryPack qp, kvm_his
     if (info.kmin[c] < info.kmax[c]) {
       uint32_t prev = 0xffffffffu;
       for (int b = 1; b < hs.num_bins; ++b) {
-        const uint64_t T = ws->thr20[h][b - 1];
+        const uint64_t T = thr_s[h][b - 1];
         if (T == ~0ull) break;
         const uint32_t d = digit_of(T, cps[c].kbase, cps[c].shift);
-        ws->edge_code[c][d] = d == prev ? 255 : (uint8_t)b;
+        edge_s[c][d] = d == prev ? 255 : (uint8_t)b;
         prev = d;
       }
     }
+  }
+  __syncthreads();
+  // publish thresholds, edge codes and the default lookup table (no bucket yet: low byte 255)
+  for (int i = t; i < NH * NB_MAX; i += PLAN_THREADS) (&ws->thr20[0][0])[i] = (&thr_s[0][0])[i];
+  for (int i = t; i < KVM_MAX_COLS * BINS / 4; i += PLAN_THREADS) {
+    const uint32_t e4 = reinterpret_cast<const uint32_t*>(&edge_s[0][0])[i];
+    reinterpret_cast<uint32_t*>(&ws->edge_code[0][0])[i] = e4;
+    uint2 t4;
+    t4.x = (0x00ffu | ((e4 & 0xffu) << 8)) | ((0x00ffu | (((e4 >> 8) & 0xffu) << 8)) << 16);
+    t4.y = (0x00ffu | (((e4 >> 16) & 0xffu) << 8)) | ((0x00ffu | (((e4 >> 24) & 0xffu) << 8)) << 16);
+    reinterpret_cast<uint2*>(&ws->tab[0][0])[i] = t4;
   }
 }
 
@@ -564,8 +581,6 @@ __global__ void __launch_bounds__(RES_THREADS, 1) select_resolve_kernel(SelWs* w
   __shared__ int nb_s;
   __shared__ int64_t used_s;
   const int t = threadIdx.x;
-  for (int i = t; i < KVM_MAX_COLS * BINS; i += RES_THREADS)
-    (&ws->tab[0][0])[i] = (uint16_t)(0x00ffu | ((uint32_t)(&ws->edge_code[0][0])[i] << 8));
   if (t < MAXQ) {
     const QState s = qs[t];
     const bool need = t < nq && s.status == KVM_Q_OK && !s.resolved;
@@ -979,7 +994,7 @@ log_compact_kernel(kvm_request_log log, const uint8_t* __restrict__ flags, SelWs
 // one of its fine bins is interesting (~3% of the sites), in the dense drain phase.
 struct RecQueue {
   int64_t row[SEL_THREADS / 32][CQ_CAP];
-  uint32_t meta[SEL_THREADS / 32][CQ_CAP];  // value column | table entry << 8
+  uint32_t hitmask[SEL_THREADS / 32][CQ_CAP];  // bit c: the row's value in column c is interesting
 };
 
 template <int ROWS>
@@ -991,7 +1006,11 @@ log_compact_rec_kernel(kvm_request_log log, const uint8_t* __restrict__ flags,
   RecQueue& Q = *reinterpret_cast<RecQueue*>(craw + ((sizeof(CompactSmem) + 15) / 16) * 16);
   if (ws->status != KVM_OK) return;
   if (threadIdx.x == 0) S.num_bins = ws->hspec.num_bins;
-  if (threadIdx.x < KVM_MAX_COLS) S.col_hist[threadIdx.x] = ws->col_hist[threadIdx.x];
+  if (threadIdx.x < KVM_MAX_COLS) {
+    S.col_hist[threadIdx.x] = ws->col_hist[threadIdx.x];
+    S.cp.kbase[threadIdx.x] = ws->col[threadIdx.x].kbase;
+    S.cp.shift[threadIdx.x] = ws->col[threadIdx.x].shift;
+  }
   for (int i = threadIdx.x; i < KVM_LOG_NCOLS * BINS / 2; i += SEL_THREADS)
     reinterpret_cast<uint32_t*>(&S.tab[0][0])[i] = reinterpret_cast<const uint32_t*>(&ws->tab[0][0])[i];
   for (int i = threadIdx.x; i < NH * NB_MAX; i += SEL_THREADS) {
@@ -1007,59 +1026,77 @@ log_compact_rec_kernel(kvm_request_log log, const uint8_t* __restrict__ flags,
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const unsigned lt = (1u << lane) - 1u;
   int qn = 0;  // warp-uniform queue length
+  // Drain: every lane takes one queued row; the five value columns are visited in a uniform loop
+  // (the column is a compile-time constant inside), lanes whose row is not interesting in that
+  // column sit the step out.
   auto drain = [&]() {
     __syncwarp();
     for (int k0 = 0; k0 < qn; k0 += 32) {
       const int k = k0 + lane;
-      const bool valid = k < qn;
-      const int64_t r = valid ? Q.row[warp][k] : 0;
-      const uint32_t m = valid ? Q.meta[warp][k] : 0u;
-      const int col = m & 0xff;
-      const uint32_t e = m >> 8;
-      const uint8_t fl = valid ? flags[r] : 0;
+      const bool have = k < qn;
+      const int64_t r = have ? Q.row[warp][k] : 0;
+      const uint32_t hm = have ? Q.hitmask[warp][k] : 0u;
+      const uint8_t fl = have ? flags[r] : 0;
       const bool cold = fl & KVM_F_COLD;
-      double v = 0.0;
-      int set = 0;
-      if (!valid) {
-      } else if (col == KVM_COL_LAT) {
-        v = log.latency_ms[r];
-        set = cold ? KVM_SET_LAT_COLD : KVM_SET_LAT_WARM;
-      } else if (col == KVM_COL_TTFB) {
-        v = log.ttfb_ms[r];
-        set = cold ? KVM_SET_TTFB_COLD : KVM_SET_TTFB_WARM;
-      } else if (col == KVM_COL_TLLT) {
-        v = log.tllt_ms[r];
-        set = KVM_SET_TLLT;
-      } else {
-        v = log.tllt_ms[r] - log.ttfb_ms[r];               // analyze.py:144
-        set = KVM_SET_GEN;
-        if (col == KVM_COL_PERTOK) {
-          v = v / (double)log.completion_tokens[r];         // analyze.py:146
-          set = KVM_SET_PERTOK;
-        }
+      double tf = 0.0, tl = 0.0;
+      if (hm & 0x1Eu) {            // ttfb / tllt feed four of the five columns
+        tf = log.ttfb_ms[r];
+        tl = log.tllt_ms[r];
       }
-      compact_hits_warp(ws, S, arena, valid, set, col, e, kvm_key(v));
+#pragma unroll
+      for (int c = 0; c < KVM_LOG_NCOLS; ++c) {
+        const bool valid = (hm >> c) & 1u;
+        if (!__any_sync(KVM_FULL, valid)) continue;
+        double v = 0.0;
+        int set = 0;
+        if (valid) {
+          if (c == KVM_COL_LAT) {
+            v = log.latency_ms[r];
+            set = cold ? KVM_SET_LAT_COLD : KVM_SET_LAT_WARM;
+          } else if (c == KVM_COL_TTFB) {
+            v = tf;
+            set = cold ? KVM_SET_TTFB_COLD : KVM_SET_TTFB_WARM;
+          } else if (c == KVM_COL_TLLT) {
+            v = tl;
+            set = KVM_SET_TLLT;
+          } else if (c == KVM_COL_GEN) {
+            v = tl - tf;                                        // analyze.py:144
+            set = KVM_SET_GEN;
+          } else {
+            v = (tl - tf) / (double)log.completion_tokens[r];   // analyze.py:146
+            set = KVM_SET_PERTOK;
+          }
+        }
+        const uint64_t key = kvm_key(v);
+        uint32_t e = 0x00ffu;
+        if (valid) e = S.tab[c][digit_of(key, S.cp.kbase[c], S.cp.shift[c])];
+        compact_hits_warp(ws, S, arena, valid, set, c, e, key);
+      }
     }
     __syncwarp();
     qn = 0;
   };
+  // Streaming side: five table lookups per row OR-ed into a hit mask, ONE ballot per row.
   auto row = [&](int64_t r, uint64_t rec) {
+    // branch-free: the lookup is always performed (index masked into the table), a digit of
+    // 0xFFF ("row not in a set of this column") is rejected arithmetically
+    uint32_t hm = 0;
 #pragma unroll
     for (int c = 0; c < KVM_LOG_NCOLS; ++c) {
       const uint32_t d = (uint32_t)(rec >> (12 * c)) & 0xFFFu;
-      uint32_t e = 0x00ffu;
-      if (d != 0xFFFu) e = S.tab[c][d];
-      const unsigned hits = __ballot_sync(KVM_FULL, e != 0x00ffu);
-      if (hits) {
-        const int cnt = __popc(hits);
-        if (qn + cnt > CQ_CAP) drain();
-        if (e != 0x00ffu) {
-          const int pos = qn + __popc(hits & lt);
-          Q.row[warp][pos] = r;
-          Q.meta[warp][pos] = (uint32_t)c | (e << 8);
-        }
-        qn += cnt;
+      const uint32_t e = S.tab[c][d & (BINS - 1)];
+      hm |= (uint32_t)((d != 0xFFFu) & (e != 0x00ffu)) << c;
+    }
+    const unsigned hits = __ballot_sync(KVM_FULL, hm != 0);
+    if (hits) {
+      const int cnt = __popc(hits);
+      if (qn + cnt > CQ_CAP) drain();
+      if (hm) {
+        const int pos = qn + __popc(hits & lt);
+        Q.row[warp][pos] = r;
+        Q.hitmask[warp][pos] = hm;
       }
+      qn += cnt;
     }
   };
   const int64_t n = log.n;
