@@ -188,11 +188,18 @@ def run_ours(args):
 
     n = args.rows
     # synthetic shard of this rank: cfg2 distribution, shard r covers hour r of the log
-    host = synth.request_columns(n, seed=1234 + rank, t_epoch_ms=1.7e12 + rank * 3.6e6)
-    log = columns.columns_from_arrays(**host)
-    pinned = {k: torch.from_numpy(v).pin_memory() for k, v in log.cols.items()}
-    resident = {k: v.to(device) for k, v in pinned.items()}
-    t0 = float(host["start_ms"].min()) / 1000.0
+    if args.device_data:
+        # generated on the device (sizes whose host copy would not fit comfortably); the host
+        # copy for the e2e leg is taken from it once, outside every timed region
+        resident = synth.request_columns_device(n, device, seed=1234 + rank, t_epoch_ms=1.7e12,
+                                                t_offset_ms=rank * 3.6e6)
+        host = None
+        pinned = {k: v.cpu().pin_memory() for k, v in resident.items()} if not args.no_e2e else None
+    else:
+        host = synth.request_columns(n, seed=1234 + rank, t_epoch_ms=1.7e12 + rank * 3.6e6)
+        log = columns.columns_from_arrays(**host)
+        pinned = {k: torch.from_numpy(v).pin_memory() for k, v in log.cols.items()}
+        resident = {k: v.to(device) for k, v in pinned.items()}
     cold = [1.7e9 + 5.0, 1.7e9 + 1800.0]
     pricing = cost_api.UnitPricing(1.5, {}, 0.04, 0.005, 0.10, True, False)
     rsecs = {"gpu_seconds": 3600.0, "cpu_core_seconds": 14400.0, "mem_gib_seconds": 57600.2}
@@ -207,8 +214,8 @@ def run_ours(args):
                           # the NCCL collectives in a graph hung on this stack)
     pipelined = world == 1
     dlog_resident = engine.DeviceLog.from_tensors(resident)
-    staging = {k: torch.empty_like(v) for k, v in resident.items()}   # fixed device buffers for e2e
-    dlog_staging = engine.DeviceLog.from_tensors(staging)
+    staging = ({k: torch.empty_like(v) for k, v in resident.items()} if pinned is not None else None)
+    dlog_staging = engine.DeviceLog.from_tensors(staging) if staging is not None else None
 
     def finish(raw):
         core = report.core_results(raw, len(cold))
@@ -293,15 +300,18 @@ def run_ours(args):
     analyzer.timer = engine._NoTimer()
 
     # ---- timed region 2: end to end from pinned host buffers
-    e2e_step()
-    barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(args.steps):
-        core, cost, raw = e2e_step()
-    e1.record()
-    barrier()
-    ms_e2e = e0.elapsed_time(e1)
+    ms_e2e = float("nan")
+    e2e_steps = max(3, min(args.steps, 20))
+    if pinned is not None:
+        e2e_step()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(e2e_steps):
+            core, cost, raw = e2e_step()
+        e1.record()
+        barrier()
+        ms_e2e = e0.elapsed_time(e1)
 
     if dist is not None:
         t = torch.tensor([ms_total, ms_e2e, ms_eager], dtype=torch.float64, device=device)
@@ -322,6 +332,14 @@ def run_ours(args):
                 k["frac"] = k["achieved_gbs"] / peak
             kernels[name] = k
         dom = max((k for k in kernels if k in alg), key=lambda k: kernels[k]["avg_ms"])
+        traffic = None
+        try:   # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu capture
+            with open(os.path.join(REPO, "profiles", "ncu_traffic.json")) as f:
+                tj = json.load(f)
+            if tj.get("rows") == n:
+                traffic = tj["kernels"].get(dom)
+        except Exception:
+            traffic = None
         d2h = (raw.hist_counts.nbytes + (raw.series.nbytes if raw.series is not None else 0)
                + 48 * 32 + 312)
         value = n * world * args.steps / (ms_total * 1e-3)
@@ -330,12 +348,13 @@ def run_ours(args):
             "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": workload_config(args, world),
-            "e2e": {"value": n * world * args.steps / (ms_e2e * 1e-3), "unit": UNIT,
-                    "h2d_bytes_per_step": ROW_BYTES * n, "d2h_bytes_per_step": int(d2h)},
+            "e2e": ({"value": n * world * e2e_steps / (ms_e2e * 1e-3), "unit": UNIT, "steps": e2e_steps,
+                     "h2d_bytes_per_step": ROW_BYTES * n, "d2h_bytes_per_step": int(d2h)}
+                    if pinned is not None else None),
             "gpu_launches": launches,
             "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": kernels[dom]["achieved_gbs"],
-                         "peak": peak, "unit": "GB/s", "frac": kernels[dom]["frac"], "traffic": None,
+                         "peak": peak, "unit": "GB/s", "frac": kernels[dom]["frac"], "traffic": traffic,
                          "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": kernels[dom]["algorithmic_bytes"]},
             "kernels": kernels,
@@ -349,7 +368,7 @@ def run_ours(args):
             "check": {"p50_ms": core["p50_ms"], "p99_ms": core["p99_ms"],
                       "cost_per_1k_tokens": cost["cost_per_1k_tokens"]},
         }
-        if world == 1 and not args.no_cpu_baseline:
+        if world == 1 and not args.no_cpu_baseline and host is not None:
             rows = min(n, 3_000_000)
             rate, secs = cpu_port_rate({k: v for k, v in host.items()}, cold, rows)
             line["cpu_baseline"] = {
@@ -369,6 +388,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--rows", type=int, default=10_000_000, help="rows per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--device-data", action="store_true", help="generate the shard on the GPU (large --rows)")
+    ap.add_argument("--no-e2e", action="store_true", help="with --device-data: skip the host-buffer leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
