@@ -321,7 +321,8 @@ def run_ours(args):
     if rank == 0:
         peak, peak_src = measured_peaks()
         # algorithmic bytes per launch of each streaming kernel (DESIGN.md "Kernels")
-        alg = {"log_scan": 57.0 * n, "select_hist": 41.0 * n, "select_compact": 33.0 * n}
+        alg = {"log_scan": 57.0 * n, "select_hist": 49.0 * n, "select_compact": 9.0 * n,
+               "select_refine_hist": 9.0 * n}
         kernels = {}
         for name, (ms, cnt) in stage_ms.items():
             avg = ms / cnt

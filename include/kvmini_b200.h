@@ -257,8 +257,8 @@ int kvm_select_status(const void* workspace, void* stream);
 /* ---- staged form of the same select, for multi-GPU runs where the host all-reduces
  * between the stages.  Stage order:
  *   column_stats -> [allreduce set_info: counts sum, kmin min, kmax max] -> plan ->
- *   hist -> [allreduce hist: sum] -> resolve -> compact -> [allgather arena+counts,
- *   allreduce edge counters: sum] -> finish
+ *   hist -> [allreduce hist: sum] -> resolve -> {refine_hist -> [allreduce hist2: sum] ->
+ *   refine}* -> compact -> [allgather arena+counts, allreduce edge counters: sum] -> finish
  */
 int kvm_column_stats(const double* values, int64_t n, int32_t member_mode, const void* member,
                      int32_t nsets, kvm_set_info* info, void* workspace, size_t workspace_bytes,
@@ -289,6 +289,33 @@ int kvm_log_select_hist(const kvm_request_log* log_host, const uint8_t* flags,
                         const kvm_log_stats* stats, const kvm_log_extras* extras_host,
                         void* workspace, void* stream);
 int kvm_select_resolve(void* workspace, void* stream);
+
+/* Refine rounds (large logs).  A level-1 bucket holds ~n/2048 keys of its column; at 1e8..1e9
+ * rows that is too many to exchange between ranks and to rank inside one CTA.  A refine round
+ * narrows every bucket to the 1/2048 sub-range that holds the requested rank:
+ *   refine_hist  pass over the digit records: per bucket, histogram of the next 11 key bits
+ *                (values are fetched only for the ~3% of rows that hit a bucket)
+ *   [allreduce kvm_select_hist2_ptr: sum, kvm_select_hist2_words() u64]
+ *   refine       walk each query's bucket histogram, replace the buckets by the sub-ranges
+ * kvm_select_plan_refine tells the device how many rounds the host will launch
+ * (`refine_rounds`, 0..4) and the total bucket population (`refine_min_keys`) above which a
+ * round does work; below it both kernels return at once, so the host may launch them
+ * unconditionally (all ranks take the same decision from the all-reduced histograms).
+ * The compact pass after a refine round must be the record-driven one (digit_records != NULL).
+ * kvm_log_select runs one round by itself when n >= KVM_REFINE_MIN_ROWS and digit records
+ * are given.  No counterpart in the reference (it sorts each list). */
+#define KVM_REFINE_MIN_ROWS (1ll << 25)
+#define KVM_REFINE_MIN_KEYS (1ll << 19)
+int kvm_select_plan_refine(const kvm_set_info* info, const kvm_query* queries_host, int32_t nq,
+                           const kvm_hist_spec* hists_host, void* workspace, size_t workspace_bytes,
+                           int64_t arena_capacity, int32_t refine_rounds, int64_t refine_min_keys,
+                           void* stream);
+int kvm_log_select_refine_hist(const kvm_request_log* log_host, const uint8_t* flags,
+                               const uint64_t* digit_records, void* workspace, void* stream);
+int kvm_select_refine(void* workspace, void* stream);
+uint64_t* kvm_select_hist2_ptr(void* workspace); /* [KVM_MAX_QUERIES][kvm_select_bins()] u64 */
+int64_t kvm_select_hist2_words(void);
+
 int kvm_column_select_compact(const double* values, int64_t n, int32_t member_mode,
                               const void* member, void* workspace, void* stream);
 int kvm_log_select_compact(const kvm_request_log* log_host, const uint8_t* flags,

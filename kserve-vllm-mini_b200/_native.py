@@ -124,6 +124,11 @@ def _declare(lib: C.CDLL) -> None:
         "kvm_select_post_pack": (C.c_int, [vp, vp, vp, vp]),
         "kvm_select_post_unpack": (C.c_int, [vp, vp, i32, vp, vp, vp]),
         "kvm_select_plan": (C.c_int, [vp, P(QueryC), i32, P(HistSpecC), vp, sz, i64, vp]),
+        "kvm_select_plan_refine": (C.c_int, [vp, P(QueryC), i32, P(HistSpecC), vp, sz, i64, i32, i64, vp]),
+        "kvm_log_select_refine_hist": (C.c_int, [P(RequestLogC), vp, vp, vp, vp]),
+        "kvm_select_refine": (C.c_int, [vp, vp]),
+        "kvm_select_hist2_ptr": (vp, [vp]),
+        "kvm_select_hist2_words": (i64, []),
         "kvm_column_select_hist": (C.c_int, [vp, i64, i32, vp, vp, vp]),
         "kvm_log_select_hist": (C.c_int, [P(RequestLogC), vp, vp, P(LogExtrasC), vp, vp]),
         "kvm_select_resolve": (C.c_int, [vp, vp]),

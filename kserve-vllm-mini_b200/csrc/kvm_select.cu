@@ -71,16 +71,25 @@ struct SelWs {
   int32_t status;
   int32_t nq;
   int32_t nbuckets;
-  int32_t pad0;
+  int32_t refine;          // 1: the candidate buckets are still too large - one more refine round runs
   int64_t arena_capacity;
   int64_t arena_used;
+  int32_t refine_budget;   // refine rounds the host will still launch
+  int32_t level;           // 1 after resolve, +1 per refine round that ran
+  int64_t refine_min;      // refine while the buckets hold more keys than this in total
+  int32_t nparents;        // level-1 buckets (the lookup table's targets)
+  int32_t pad1;
   kvm_set_info info;
   kvm_query queries[MAXQ];
   ColParam col[KVM_MAX_COLS];
   QState q[MAXQ];
-  Bucket bucket[MAXQ];
+  Bucket bucket[MAXQ];           // the candidate buckets keys are appended to ("targets")
   int64_t bucket_offsets[MAXQ + 1];
   int64_t bucket_counts[MAXQ];  // local append cursors (compact)
+  Bucket parent[MAXQ];           // the level-1 buckets the lookup table points at; after a refine
+  uint8_t child_first[MAXQ];     // round each one owns the contiguous targets
+  uint8_t child_n[MAXQ];         // [child_first, child_first + child_n) that subdivide it
+  int32_t tparent[MAXQ];         // level-1 bucket of each target
   kvm_hist_spec hspec;
   int32_t active20[NH];
   int32_t col_hist[KVM_MAX_COLS];  // value histogram fed by each column, -1 = none
@@ -92,6 +101,7 @@ struct SelWs {
   uint16_t tab[KVM_MAX_COLS][BINS];       // low byte: first bucket with that (col, bin), 255 = none;
                                           // high byte: edge_code
   uint64_t hist[KVM_MAX_SETS][BINS];
+  uint64_t hist2[MAXQ][BINS];  // refine round: per target, histogram of the next 11 key bits
   unsigned char stats_scratch[STATS_SCRATCH];
 };
 
@@ -123,7 +133,7 @@ constexpr int PLAN_THREADS = 512;
 
 __global__ void __launch_bounds__(PLAN_THREADS)
 select_plan_kernel(SelWs* ws, const kvm_set_info* info_in, QueryPack qp, kvm_hist_spec hs,
-                   int64_t arena_capacity) {
+                   int64_t arena_capacity, int refine_rounds, int64_t refine_min) {
   __shared__ kvm_set_info info;
   __shared__ ColParam cps[KVM_MAX_COLS];
   __shared__ uint64_t thr_s[NH][NB_MAX];
@@ -149,6 +159,11 @@ select_plan_kernel(SelWs* ws, const kvm_set_info* info_in, QueryPack qp, kvm_his
     ws->nbuckets = 0;
     ws->arena_capacity = arena_capacity;
     ws->arena_used = 0;
+    ws->refine = 0;
+    ws->refine_budget = refine_rounds;
+    ws->refine_min = refine_min;
+    ws->level = 0;
+    ws->nparents = 0;
     ws->hspec = hs;
   }
   if (t < (int)(sizeof(kvm_set_info) / 8))
@@ -640,6 +655,10 @@ __global__ void __launch_bounds__(RES_THREADS, 1) select_resolve_kernel(SelWs* w
     b.run = smaller_same == 0 ? group : 0;
     b.pad = 0;
     ws->bucket[pos_of[t]] = b;
+    ws->parent[pos_of[t]] = b;
+    ws->child_first[pos_of[t]] = (uint8_t)pos_of[t];
+    ws->child_n[pos_of[t]] = 1;
+    ws->tparent[pos_of[t]] = pos_of[t];
     ws->bucket_offsets[pos_of[t]] = off_of[t];
     if (smaller_same == 0)
       ws->tab[s.col][b.bin] = (uint16_t)((uint32_t)pos_of[t] | ((uint32_t)ws->edge_code[s.col][b.bin] << 8));
@@ -647,8 +666,170 @@ __global__ void __launch_bounds__(RES_THREADS, 1) select_resolve_kernel(SelWs* w
   if (t <= MAXQ && t >= nb_s) ws->bucket_offsets[t] = used_s;
   if (t == 0) {
     ws->nbuckets = nb_s;
+    ws->nparents = nb_s;
     ws->arena_used = used_s;
-    if (used_s > ws->arena_capacity) ws->status = KVM_ERR_ARENA;
+    ws->level = 1;
+    // every level-1 bucket has shift > 0, so a refine round can always narrow it
+    const int again = ws->refine_budget > 0 && used_s > ws->refine_min;
+    ws->refine = again;
+    if (!again && used_s > ws->arena_capacity) ws->status = KVM_ERR_ARENA;
+  }
+  if (t < MAXQ) {
+    QState s = qs[t];
+    if (bkey[t] != ~0ull) s.bucket = pos_of[t];
+    ws->q[t] = s;
+  }
+}
+
+// ------------------------------------------------------------------ refine
+// One refine round = a pass over the digit records that histograms, per candidate bucket, the
+// next 11 bits of its keys (log_rec_kernel<ROWS, 1> -> ws->hist2), then this kernel: every
+// unresolved query walks the histogram of its bucket to the sub-bin holding its residual rank
+// and the bucket is replaced by that sub-bin (2048x fewer keys).  The lookup table keeps
+// pointing at the level-1 buckets ("parents"); each parent owns the contiguous run of targets
+// that subdivide it, and a key belongs to a target iff (key - base) >> shift == 0.
+// Runs only while resolve / the previous round left ws->refine set, i.e. when the buckets
+// together hold more than refine_min keys (large logs).
+__global__ void __launch_bounds__(RES_THREADS, 1) select_refine_kernel(SelWs* ws) {
+  if (ws->status != KVM_OK || !ws->refine) return;
+  __shared__ QState qs[MAXQ];
+  __shared__ Bucket tg[MAXQ];
+  __shared__ int32_t tpar[MAXQ];
+  __shared__ uint32_t q_sub[MAXQ];
+  __shared__ int64_t q_cnt[MAXQ];
+  __shared__ uint64_t bkey[MAXQ];
+  __shared__ int is_first[MAXQ];
+  __shared__ int pos_of[MAXQ];
+  __shared__ int64_t off_of[MAXQ];
+  __shared__ int newpar[MAXQ];
+  __shared__ int nb_s;
+  __shared__ int64_t used_s;
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5, nwarps = RES_THREADS / 32;
+  const int nq = ws->nq;
+  if (t < MAXQ) {
+    qs[t] = ws->q[t];
+    tg[t] = ws->bucket[t];
+    tpar[t] = ws->tparent[t];
+    bkey[t] = ~0ull;
+    q_cnt[t] = 0;
+  }
+  __syncthreads();
+  for (int q = warp; q < nq; q += nwarps) {
+    QState s = qs[q];
+    if (s.status != KVM_Q_OK || s.resolved || s.bucket < 0) continue;
+    const Bucket T = tg[s.bucket];
+    const uint64_t* __restrict__ h = ws->hist2[s.bucket];
+    const int take = T.shift < BINS_LOG2 ? T.shift : BINS_LOG2;
+    const int sh2 = T.shift - take;
+    int64_t running = 0;
+    bool found = false;
+    for (int base = 0; base < (1 << take) && !found; base += 32) {
+      const int64_t c = (int64_t)h[base + lane];
+      int64_t incl = c;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        int64_t o = __shfl_up_sync(KVM_FULL, incl, d);
+        if (lane >= d) incl += o;
+      }
+      const unsigned hit = __ballot_sync(KVM_FULL, running + incl > s.resid);
+      if (hit) {
+        const int l = __ffs(hit) - 1;
+        const int64_t excl = __shfl_sync(KVM_FULL, incl - c, l);
+        const int64_t cnt = __shfl_sync(KVM_FULL, c, l);
+        if (lane == 0) {
+          const uint32_t sub = (uint32_t)(base + l);
+          s.resid = s.resid - (running + excl);
+          if (sh2 == 0) {  // the sub-digit completes the key
+            s.key = T.base + (uint64_t)sub;
+            s.resolved = 1;
+            s.bucket = -1;
+          } else {
+            q_sub[q] = sub;
+            q_cnt[q] = cnt;
+            bkey[q] = ((uint64_t)(uint32_t)s.bucket << 32) | sub;
+          }
+          qs[q] = s;
+        }
+        found = true;
+      }
+      running += __shfl_sync(KVM_FULL, incl, 31);
+    }
+    if (!found && lane == 0) {  // histogram inconsistent with the bucket count
+      s.status = KVM_Q_OUT_OF_RANGE;
+      s.resolved = 1;
+      qs[q] = s;
+    }
+  }
+  __syncthreads();
+  // new targets = distinct (old target, sub-bin), in that order: children of a parent stay contiguous
+  if (t < MAXQ) {
+    const uint64_t k = bkey[t];
+    int first = k != ~0ull;
+    for (int o = 0; o < t && first; ++o) first = bkey[o] != k;
+    is_first[t] = first;
+  }
+  __syncthreads();
+  if (t < MAXQ) {
+    const uint64_t k = bkey[t];
+    int pos = 0;
+    int64_t off = 0;
+    if (k != ~0ull)
+      for (int o = 0; o < MAXQ; ++o)
+        if (is_first[o] && bkey[o] < k) {
+          ++pos;
+          off += q_cnt[o];
+        }
+    pos_of[t] = pos;
+    off_of[t] = off;
+  }
+  if (t == 0) {
+    int nb = 0;
+    int64_t used = 0;
+    for (int o = 0; o < MAXQ; ++o)
+      if (is_first[o]) {
+        ++nb;
+        used += q_cnt[o];
+      }
+    nb_s = nb;
+    used_s = used;
+  }
+  __syncthreads();
+  if (t < MAXQ && is_first[t]) {
+    const int old = (int)(bkey[t] >> 32);
+    const Bucket T = tg[old];
+    const int sh2 = T.shift - BINS_LOG2;  // > 0 here
+    Bucket b = T;
+    b.base = T.base + ((uint64_t)q_sub[t] << sh2);
+    b.shift = sh2;
+    b.count = q_cnt[t];
+    b.run = 0;
+    const int p = pos_of[t];
+    ws->bucket[p] = b;
+    ws->bucket_offsets[p] = off_of[t];
+    ws->tparent[p] = tpar[old];
+    newpar[p] = tpar[old];
+  }
+  __syncthreads();
+  if (t < MAXQ) {  // t as a level-1 bucket: the run of targets below it
+    int first = 0, cnt = 0;
+    for (int p = nb_s - 1; p >= 0; --p)
+      if (newpar[p] == t) {
+        first = p;
+        ++cnt;
+      }
+    ws->child_first[t] = (uint8_t)first;
+    ws->child_n[t] = (uint8_t)cnt;
+  }
+  if (t <= MAXQ && t >= nb_s) ws->bucket_offsets[t] = used_s;
+  if (t == 0) {
+    ws->nbuckets = nb_s;
+    ws->arena_used = used_s;
+    ws->level = ws->level + 1;
+    const int budget = ws->refine_budget - 1;
+    ws->refine_budget = budget;
+    const int again = budget > 0 && used_s > ws->refine_min;
+    ws->refine = again;
+    if (!again && used_s > ws->arena_capacity) ws->status = KVM_ERR_ARENA;
   }
   if (t < MAXQ) {
     QState s = qs[t];
@@ -672,6 +853,13 @@ struct CompactSmem {
   unsigned long long stage_pos[MAXQ];
   uint64_t stage[MAXQ][STAGE_SLOTS];
   uint16_t tab[KVM_LOG_NCOLS][BINS];
+  // record-driven passes: bk[] holds the level-1 buckets (table targets), these the append targets
+  uint64_t tbase[MAXQ];
+  int64_t tcount[MAXQ];
+  int32_t tshift[MAXQ];
+  uint8_t cf[MAXQ];
+  uint8_t cn[MAXQ];
+  int32_t max_cn;
 };
 
 template <int NCOLS, class Stream>
@@ -679,6 +867,7 @@ __device__ __forceinline__ void compact_body(SelWs* ws, uint64_t* __restrict__ a
   extern __shared__ __align__(16) unsigned char craw[];
   CompactSmem& S = *reinterpret_cast<CompactSmem*>(craw);
   if (ws->status != KVM_OK) return;
+  if (ws->level > 1) return;  // refined buckets need the record-driven pass (host enforces it)
   if (threadIdx.x == 0) S.num_bins = ws->hspec.num_bins;
   if (threadIdx.x < KVM_MAX_COLS) {
     S.cp.kbase[threadIdx.x] = ws->col[threadIdx.x].kbase;
@@ -823,6 +1012,71 @@ __device__ __forceinline__ void compact_hits_warp(SelWs* ws, CompactSmem& S, uin
     const int bin = code == 255u ? bin_of(key, S.thr[h], S.num_bins)
                                  : (int)code - (key < S.thr[h][code - 1] ? 1 : 0);
     atomicAdd(&S.edge[h][bin], 1u);
+  }
+}
+
+// Warp-cooperative slow path of the record-driven passes: all 32 lanes call it (lanes without
+// an entry pass valid=false).  The table entry names the level-1 buckets of the key's fine bin;
+// each owns a run of targets, and the key belongs to the target whose key range contains it.
+// PHASE 0 (compact): append the key to the target - lanes appending to the same target are
+// merged with __match_any_sync so that one shared-memory atomic reserves the slots of the group;
+// keys in a fine bin with a histogram edge are also binned exactly.
+// PHASE 1 (refine): count the key's next 11 bits into the target's row of ws->hist2.
+template <int PHASE>
+__device__ __forceinline__ void target_hits_warp(SelWs* ws, CompactSmem& S, uint64_t* __restrict__ arena,
+                                                 bool valid, int set, int col, uint32_t e, uint64_t key) {
+  const int lane = threadIdx.x & 31;
+  const unsigned lt = (1u << lane) - 1u;
+  const uint32_t j0 = valid ? (e & 0xffu) : 255u;
+  int run = 0;
+  if (j0 != 255u) run = S.bk[j0].run;
+  int maxrun = run;
+#pragma unroll
+  for (int m = 16; m; m >>= 1) {
+    const int o = __shfl_xor_sync(KVM_FULL, maxrun, m);
+    maxrun = o > maxrun ? o : maxrun;
+  }
+  const int maxc = S.max_cn;
+  for (int r = 0; r < maxrun; ++r) {
+    int j = -1;
+    if (r < run && ((S.bk[j0 + r].set_mask >> set) & 1u)) j = (int)j0 + r;
+    const int cf = j >= 0 ? (int)S.cf[j] : 0, cn = j >= 0 ? (int)S.cn[j] : 0;
+    for (int cc = 0; cc < maxc; ++cc) {
+      int c = -1;
+      if (cc < cn && ((key - S.tbase[cf + cc]) >> S.tshift[cf + cc]) == 0) c = cf + cc;
+      if (PHASE == 1) {
+        if (c >= 0) {
+          const int sh2 = S.tshift[c] > BINS_LOG2 ? S.tshift[c] - BINS_LOG2 : 0;
+          atomicAdd(reinterpret_cast<unsigned long long*>(&ws->hist2[c][(uint32_t)((key - S.tbase[c]) >> sh2)]),
+                    1ull);
+        }
+      } else {
+        const unsigned peers = __match_any_sync(KVM_FULL, c);
+        if (c >= 0) {
+          const int leader = __ffs(peers) - 1;
+          uint32_t base = 0;
+          if (lane == leader) base = atomicAdd(&S.stage_n[c], (uint32_t)__popc(peers));
+          base = __shfl_sync(peers, base, leader);
+          const uint32_t sp = base + (uint32_t)__popc(peers & lt);
+          if (sp < (uint32_t)STAGE_SLOTS) {
+            S.stage[c][sp] = key;
+          } else {
+            const unsigned long long pos =
+                atomicAdd(reinterpret_cast<unsigned long long*>(&ws->bucket_counts[c]), 1ull);
+            if ((int64_t)pos < S.tcount[c]) arena[S.bk_off[c] + (int64_t)pos] = key;
+          }
+        }
+      }
+    }
+  }
+  if (PHASE == 0) {
+    const uint32_t code = valid ? (e >> 8) : 0u;
+    if (code) {
+      const int h = S.col_hist[col];
+      const int bin = code == 255u ? bin_of(key, S.thr[h], S.num_bins)
+                                   : (int)code - (key < S.thr[h][code - 1] ? 1 : 0);
+      atomicAdd(&S.edge[h][bin], 1u);
+    }
   }
 }
 
@@ -997,14 +1251,17 @@ struct RecQueue {
   uint32_t hitmask[SEL_THREADS / 32][CQ_CAP];  // bit c: the row's value in column c is interesting
 };
 
-template <int ROWS>
+// PHASE 0: the compact pass.  PHASE 1: the histogram pass of a refine round (same streaming side,
+// the drain counts sub-digits instead of appending; runs only while ws->refine is set).
+template <int ROWS, int PHASE>
 __global__ void __launch_bounds__(SEL_THREADS, 2)
-log_compact_rec_kernel(kvm_request_log log, const uint8_t* __restrict__ flags,
-                       const uint64_t* __restrict__ recs, SelWs* ws, uint64_t* arena) {
+log_rec_kernel(kvm_request_log log, const uint8_t* __restrict__ flags,
+               const uint64_t* __restrict__ recs, SelWs* ws, uint64_t* arena) {
   extern __shared__ __align__(16) unsigned char craw[];
   CompactSmem& S = *reinterpret_cast<CompactSmem*>(craw);
   RecQueue& Q = *reinterpret_cast<RecQueue*>(craw + ((sizeof(CompactSmem) + 15) / 16) * 16);
   if (ws->status != KVM_OK) return;
+  if (PHASE == 1 && !ws->refine) return;
   if (threadIdx.x == 0) S.num_bins = ws->hspec.num_bins;
   if (threadIdx.x < KVM_MAX_COLS) {
     S.col_hist[threadIdx.x] = ws->col_hist[threadIdx.x];
@@ -1017,10 +1274,23 @@ log_compact_rec_kernel(kvm_request_log log, const uint8_t* __restrict__ flags,
     (&S.thr[0][0])[i] = (&ws->thr20[0][0])[i];
     (&S.edge[0][0])[i] = 0;
   }
-  for (int i = threadIdx.x; i < MAXQ; i += SEL_THREADS) {
-    S.bk[i] = ws->bucket[i];
-    S.bk_off[i] = ws->bucket_offsets[i];
-    S.stage_n[i] = 0;
+  if (threadIdx.x == 0) S.max_cn = 0;
+  __syncthreads();
+  {
+    const int npar = ws->nparents;
+    for (int i = threadIdx.x; i < MAXQ; i += SEL_THREADS) {
+      const Bucket tg = ws->bucket[i];
+      S.bk[i] = ws->parent[i];
+      S.bk_off[i] = ws->bucket_offsets[i];
+      S.tbase[i] = tg.base;
+      S.tshift[i] = tg.shift;
+      S.tcount[i] = tg.count;
+      const int cn = i < npar ? ws->child_n[i] : 0;
+      S.cf[i] = ws->child_first[i];
+      S.cn[i] = (uint8_t)cn;
+      S.stage_n[i] = 0;
+      if (cn) atomicMax(&S.max_cn, cn);
+    }
   }
   __syncthreads();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -1070,7 +1340,7 @@ log_compact_rec_kernel(kvm_request_log log, const uint8_t* __restrict__ flags,
         const uint64_t key = kvm_key(v);
         uint32_t e = 0x00ffu;
         if (valid) e = S.tab[c][digit_of(key, S.cp.kbase[c], S.cp.shift[c])];
-        compact_hits_warp(ws, S, arena, valid, set, c, e, key);
+        target_hits_warp<PHASE>(ws, S, arena, valid, set, c, e, key);
       }
     }
     __syncwarp();
@@ -1085,7 +1355,8 @@ log_compact_rec_kernel(kvm_request_log log, const uint8_t* __restrict__ flags,
     for (int c = 0; c < KVM_LOG_NCOLS; ++c) {
       const uint32_t d = (uint32_t)(rec >> (12 * c)) & 0xFFFu;
       const uint32_t e = S.tab[c][d & (BINS - 1)];
-      hm |= (uint32_t)((d != 0xFFFu) & (e != 0x00ffu)) << c;
+      const uint32_t none = PHASE == 1 ? ((e & 0xffu) == 0xffu) : (e == 0x00ffu);
+      hm |= (uint32_t)((d != 0xFFFu) & !none) << c;
     }
     const unsigned hits = __ballot_sync(KVM_FULL, hm != 0);
     if (hits) {
@@ -1127,8 +1398,9 @@ log_compact_rec_kernel(kvm_request_log log, const uint8_t* __restrict__ flags,
     row(i, lane == 0 ? recs[i] : DIGITS_NONE);
     drain();
   }
+  if (PHASE == 1) return;
   __syncthreads();
-  // flush the stages: one global cursor bump per non-empty bucket, then a cooperative copy
+  // flush the stages: one global cursor bump per non-empty target, then a cooperative copy
   if (threadIdx.x < MAXQ) {
     const uint32_t c = S.stage_n[threadIdx.x] < (uint32_t)STAGE_SLOTS ? S.stage_n[threadIdx.x] : (uint32_t)STAGE_SLOTS;
     S.stage_n[threadIdx.x] = c;
@@ -1140,7 +1412,7 @@ log_compact_rec_kernel(kvm_request_log log, const uint8_t* __restrict__ flags,
     const int j = i / STAGE_SLOTS, k = i % STAGE_SLOTS;
     if ((uint32_t)k < S.stage_n[j]) {
       const int64_t pos = (int64_t)S.stage_pos[j] + k;
-      if (pos < S.bk[j].count) arena[S.bk_off[j] + pos] = S.stage[j][k];
+      if (pos < S.tcount[j]) arena[S.bk_off[j] + pos] = S.stage[j][k];
     }
   }
   for (int i = threadIdx.x; i < NH * NB_MAX; i += SEL_THREADS) {
@@ -1405,7 +1677,16 @@ extern "C" kvm_set_info* kvm_select_info_ptr(void* ws) { return &reinterpret_cas
 extern "C" int kvm_select_plan(const kvm_set_info* info, const kvm_query* queries, int32_t nq,
                                const kvm_hist_spec* hists, void* workspace, size_t workspace_bytes,
                                int64_t arena_capacity, void* stream) {
+  return kvm_select_plan_refine(info, queries, nq, hists, workspace, workspace_bytes, arena_capacity, 0, 0, stream);
+}
+
+extern "C" int kvm_select_plan_refine(const kvm_set_info* info, const kvm_query* queries, int32_t nq,
+                                      const kvm_hist_spec* hists, void* workspace, size_t workspace_bytes,
+                                      int64_t arena_capacity, int32_t refine_rounds, int64_t refine_min_keys,
+                                      void* stream) {
   KVM_REQUIRE(info && queries && workspace, "kvm_select_plan: null argument");
+  KVM_REQUIRE(refine_rounds >= 0 && refine_rounds <= 4 && refine_min_keys >= 0,
+              "kvm_select_plan: refine_rounds=%d outside [0,4] or negative refine_min_keys", refine_rounds);
   KVM_REQUIRE(nq >= 1 && nq <= MAXQ, "kvm_select_plan: nq=%d outside [1,%d]", nq, MAXQ);
   const kvm_hist_spec hs = hists ? *hists : kNoHists;
   KVM_REQUIRE(hs.nhist >= 0 && hs.nhist <= NH, "kvm_select_plan: nhist=%d outside [0,%d]", hs.nhist, NH);
@@ -1420,7 +1701,8 @@ extern "C" int kvm_select_plan(const kvm_set_info* info, const kvm_query* querie
   QueryPack qp;
   for (int i = 0; i < MAXQ; ++i) qp.q[i] = i < nq ? queries[i] : kvm_query{0, 0, 0.0, 0};
   qp.nq = nq;
-  select_plan_kernel<<<1, PLAN_THREADS, 0, (cudaStream_t)stream>>>(ws, info, qp, hs, arena_capacity);
+  select_plan_kernel<<<1, PLAN_THREADS, 0, (cudaStream_t)stream>>>(ws, info, qp, hs, arena_capacity,
+                                                                  refine_rounds, refine_min_keys);
   KVM_CUDA_CHECK(cudaGetLastError());
   return KVM_OK;
 }
@@ -1492,25 +1774,50 @@ extern "C" int kvm_select_resolve(void* workspace, void* stream) {
   return KVM_OK;
 }
 
+namespace {
+template <int PHASE>
+int launch_log_rec(const kvm_request_log* log, const uint8_t* flags, const uint64_t* digit_records,
+                   void* workspace, cudaStream_t st) {
+  const size_t smem = ((sizeof(CompactSmem) + 15) / 16) * 16 + sizeof(RecQueue);
+  const int grid = kvm_grid_for(log->n, SEL_THREADS * 2 * 8, 2);
+  int rc;
+  if (aligned16(digit_records) && (reinterpret_cast<uintptr_t>(flags) & 1u) == 0) {
+    if ((rc = ensure_smem((const void*)log_rec_kernel<2, PHASE>, smem))) return rc;
+    log_rec_kernel<2, PHASE><<<grid, SEL_THREADS, smem, st>>>(
+        *log, flags, digit_records, reinterpret_cast<SelWs*>(workspace), arena_of(workspace));
+  } else {
+    if ((rc = ensure_smem((const void*)log_rec_kernel<1, PHASE>, smem))) return rc;
+    log_rec_kernel<1, PHASE><<<grid, SEL_THREADS, smem, st>>>(
+        *log, flags, digit_records, reinterpret_cast<SelWs*>(workspace), arena_of(workspace));
+  }
+  KVM_CUDA_CHECK(cudaGetLastError());
+  return KVM_OK;
+}
+}  // namespace
+
+extern "C" uint64_t* kvm_select_hist2_ptr(void* ws) { return &reinterpret_cast<SelWs*>(ws)->hist2[0][0]; }
+extern "C" int64_t kvm_select_hist2_words(void) { return (int64_t)MAXQ * BINS; }
+
+extern "C" int kvm_log_select_refine_hist(const kvm_request_log* log, const uint8_t* flags,
+                                          const uint64_t* digit_records, void* workspace, void* stream) {
+  KVM_REQUIRE(log && flags && workspace && digit_records,
+              "kvm_log_select_refine_hist: null argument (a refine round needs the digit records)");
+  SelWs* ws = reinterpret_cast<SelWs*>(workspace);
+  KVM_CUDA_CHECK(cudaMemsetAsync(&ws->hist2[0][0], 0, sizeof(ws->hist2), (cudaStream_t)stream));
+  return launch_log_rec<1>(log, flags, digit_records, workspace, (cudaStream_t)stream);
+}
+
+extern "C" int kvm_select_refine(void* workspace, void* stream) {
+  KVM_REQUIRE(workspace, "kvm_select_refine: null workspace");
+  select_refine_kernel<<<1, RES_THREADS, 0, (cudaStream_t)stream>>>(reinterpret_cast<SelWs*>(workspace));
+  KVM_CUDA_CHECK(cudaGetLastError());
+  return KVM_OK;
+}
+
 extern "C" int kvm_log_select_compact(const kvm_request_log* log, const uint8_t* flags,
                                       const uint64_t* digit_records, void* workspace, void* stream) {
   KVM_REQUIRE(log && flags && workspace, "kvm_log_select_compact: null argument");
-  if (digit_records) {
-    const size_t smem_r = ((sizeof(CompactSmem) + 15) / 16) * 16 + sizeof(RecQueue);
-    const int grid_r = kvm_grid_for(log->n, SEL_THREADS * 2 * 8, 2);
-    int rc_r;
-    if (aligned16(digit_records) && (reinterpret_cast<uintptr_t>(flags) & 1u) == 0) {
-      if ((rc_r = ensure_smem((const void*)log_compact_rec_kernel<2>, smem_r))) return rc_r;
-      log_compact_rec_kernel<2><<<grid_r, SEL_THREADS, smem_r, (cudaStream_t)stream>>>(
-          *log, flags, digit_records, reinterpret_cast<SelWs*>(workspace), arena_of(workspace));
-    } else {
-      if ((rc_r = ensure_smem((const void*)log_compact_rec_kernel<1>, smem_r))) return rc_r;
-      log_compact_rec_kernel<1><<<grid_r, SEL_THREADS, smem_r, (cudaStream_t)stream>>>(
-          *log, flags, digit_records, reinterpret_cast<SelWs*>(workspace), arena_of(workspace));
-    }
-    KVM_CUDA_CHECK(cudaGetLastError());
-    return KVM_OK;
-  }
+  if (digit_records) return launch_log_rec<0>(log, flags, digit_records, workspace, (cudaStream_t)stream);
   const size_t smem = ((sizeof(CompactSmem) + 15) / 16) * 16 + sizeof(CompactQueue);
   const int grid = kvm_grid_for(log->n, SEL_THREADS * 2 * 4, 2);
   int rc;
@@ -1585,12 +1892,19 @@ extern "C" int kvm_log_select(const kvm_request_log* log, const uint8_t* flags,
   const bool hists = extras && extras->num_bins > 0;
   KVM_REQUIRE(!hists || extras->hist_counts, "kvm_log_select: hist_counts is null");
   const kvm_hist_spec hs = hists ? log_hist_spec(extras->num_bins) : kNoHists;
-  int rc = kvm_select_plan(&stats->sets, queries, nq, &hs, workspace, workspace_bytes, arena_capacity, stream);
+  const uint64_t* recs = extras ? reinterpret_cast<const uint64_t*>(extras->digit_records) : nullptr;
+  // large logs: one refine round keeps the candidate buckets (and the finish) small
+  const int rounds = (recs && log->n >= KVM_REFINE_MIN_ROWS) ? 1 : 0;
+  int rc = kvm_select_plan_refine(&stats->sets, queries, nq, &hs, workspace, workspace_bytes, arena_capacity,
+                                  rounds, KVM_REFINE_MIN_KEYS, stream);
   if (rc) return rc;
   if ((rc = kvm_log_select_hist(log, flags, stats, extras, workspace, stream))) return rc;
   if ((rc = kvm_select_resolve(workspace, stream))) return rc;
-  if ((rc = kvm_log_select_compact(log, flags, extras ? reinterpret_cast<const uint64_t*>(extras->digit_records) : nullptr,
-                                   workspace, stream))) return rc;
+  for (int r = 0; r < rounds; ++r) {
+    if ((rc = kvm_log_select_refine_hist(log, flags, recs, workspace, stream))) return rc;
+    if ((rc = kvm_select_refine(workspace, stream))) return rc;
+  }
+  if ((rc = kvm_log_select_compact(log, flags, recs, workspace, stream))) return rc;
   return kvm_select_finish(workspace, nullptr, 0, nullptr, results, hists ? extras->hist_counts : nullptr, stream);
 }
 

@@ -125,6 +125,11 @@ class ShardedAnalyzer(engine.LogAnalyzer):
         self._arena_all: Optional[torch.Tensor] = None
         self._hist_glob = torch.zeros(N.KVM_MAX_HISTS * N.KVM_HIST_MAX_BINS, dtype=torch.int64, device=dev)
 
+    def _refine_rounds(self, n_rows: int) -> int:
+        """Sharded runs always launch one refine round: the shard sizes of the other ranks are
+        unknown to this host, the device decides from the global bucket sizes."""
+        return 1 if self.refine_rounds is None else int(self.refine_rounds)
+
     def _wrap(self, ptr: int, count: int, dtype=torch.int64) -> torch.Tensor:
         """A tensor view over `count` 8-byte words inside the select workspace."""
         off = ptr - self._sel_ws.data_ptr()
@@ -150,30 +155,43 @@ class ShardedAnalyzer(engine.LogAnalyzer):
             extras.series_dropped = self._dropped_ptr
         extras.digit_records = self._digits.data_ptr()
         ws, fl = self._sel_ws.data_ptr(), self._flags.data_ptr()
-        with tm.stage("select_plan"):
-            N.check(lib.kvm_select_plan(self._stats_ptr + N.LogStatsC.sets.offset, queries, nq,
-                                        C.byref(hspec), ws, self._sel_ws.numel(), arena, st), "kvm_select_plan")
-        with tm.stage("select_hist"):
-            N.check(lib.kvm_log_select_hist(C.byref(log_c), fl, self._stats_ptr, C.byref(extras), ws, st),
-                    "kvm_log_select_hist")
-        hist = self._wrap(lib.kvm_select_hist_ptr(ws), N.KVM_MAX_SETS * self._bins)
-        with tm.stage("allreduce_hist"):
-            dist.all_reduce(hist, op=dist.ReduceOp.SUM, group=grp)
-        with tm.stage("select_resolve"):
-            N.check(lib.kvm_select_resolve(ws, st), "kvm_select_resolve")
-        with tm.stage("select_compact"):
-            N.check(lib.kvm_log_select_compact(C.byref(log_c), fl, self._digits.data_ptr(), ws, st),
-                    "kvm_log_select_compact")
-        # ---- candidates of every rank -> every rank (fixed-size exchange, no host round trip)
         vk = (ws, self._gather_n)
         views = self._views.get(vk)
         if views is None:
             self._views.clear()
             views = (self._wrap(lib.kvm_select_hist_ptr(ws), N.KVM_MAX_SETS * self._bins),
                      self._wrap(lib.kvm_select_arena_ptr(ws), self._gather_n),
-                     self._wrap(lib.kvm_select_bucket_offsets_ptr(ws), N.KVM_MAX_QUERIES + 1))
+                     self._wrap(lib.kvm_select_bucket_offsets_ptr(ws), N.KVM_MAX_QUERIES + 1),
+                     self._wrap(lib.kvm_select_hist2_ptr(ws), int(lib.kvm_select_hist2_words())))
             self._views[vk] = views
-        arena_local = views[1]
+        hist, arena_local, _, hist2 = views
+        rounds = self._refine_rounds(dlog.n)
+        with tm.stage("select_plan"):
+            N.check(lib.kvm_select_plan_refine(self._stats_ptr + N.LogStatsC.sets.offset, queries, nq,
+                                               C.byref(hspec), ws, self._sel_ws.numel(), arena, rounds,
+                                               int(self.refine_min_keys), st), "kvm_select_plan")
+        with tm.stage("select_hist"):
+            N.check(lib.kvm_log_select_hist(C.byref(log_c), fl, self._stats_ptr, C.byref(extras), ws, st),
+                    "kvm_log_select_hist")
+        with tm.stage("allreduce_hist"):
+            dist.all_reduce(hist, op=dist.ReduceOp.SUM, group=grp)
+        with tm.stage("select_resolve"):
+            N.check(lib.kvm_select_resolve(ws, st), "kvm_select_resolve")
+        # ---- refine: whether a round does work is decided on the device from the GLOBAL bucket
+        # sizes, so every rank takes the same branch and the collective below always matches
+        for _ in range(rounds):
+            with tm.stage("select_refine_hist"):
+                N.check(lib.kvm_log_select_refine_hist(C.byref(log_c), fl, self._digits.data_ptr(), ws, st),
+                        "kvm_log_select_refine_hist")
+            with tm.stage("allreduce_hist2"):
+                dist.all_reduce(hist2, op=dist.ReduceOp.SUM, group=grp)
+            with tm.stage("select_refine"):
+                N.check(lib.kvm_select_refine(ws, st), "kvm_select_refine")
+            self.launches += 2
+        with tm.stage("select_compact"):
+            N.check(lib.kvm_log_select_compact(C.byref(log_c), fl, self._digits.data_ptr(), ws, st),
+                    "kvm_log_select_compact")
+        # ---- candidates of every rank -> every rank (fixed-size exchange, no host round trip)
         N.check(lib.kvm_select_post_pack(ws, self._dropped_ptr if want_series else None,
                                          self._post_local.data_ptr(), st))
         with tm.stage("allgather_candidates"):
@@ -210,6 +228,7 @@ class ShardedAnalyzer(engine.LogAnalyzer):
         key = (tuple(dlog.cols[k].data_ptr() for k in engine.F64_COLS + engine.I64_COLS), dlog.n,
                tuple(sorted(float(c) for c in cold_times)), hspec.num_bins, series_window_s, id(queries), arena,
                self._sel_ws.data_ptr(), self._flags.data_ptr(), self._gather_n,
+               self._refine_rounds(dlog.n), self.refine_min_keys,
                self._series_d.data_ptr() if want_series else 0, self._arena_all.data_ptr())
         entry = self._graphs.get(key)
         if entry is None:
@@ -254,15 +273,18 @@ class ShardedAnalyzer(engine.LogAnalyzer):
             rc = int(np.frombuffer(out, dtype=np.int32, count=1, offset=self._OFF_STATUS)[0])
             stats = N.LogStatsC.from_buffer_copy(out[:C.sizeof(N.LogStatsC)])
             n_global = int(stats.n_total)
-            if rc == N.KVM_ERR_ARENA:
-                arena = max(2 * arena, n_global * 4 + 1024)
+            used = int(self._used_h[0])   # total of the GLOBAL bucket sizes (valid on overflow too)
+            if rc == N.KVM_ERR_ARENA:       # the local arena is laid out with the global bucket sizes
+                arena = max(2 * arena, used + 1024)
                 self._ensure(dlog.n, arena)
                 continue
             if rc != N.KVM_OK:
                 raise N.NativeError(f"select failed with status {rc}")
-            used = int(self._used_h[0])
             if used > self._gather_n:       # more candidates than the fixed exchange carries: redo exactly
-                self._gather_n = used + 1024
+                self._gather_n = used + 1024   # (`used` sums GLOBAL bucket sizes: same on every rank)
+                if arena < self._gather_n:
+                    arena = self._gather_n
+                    self._ensure(dlog.n, arena)
                 continue
             series = None
             if want_series and n_global > 0 and not math.isnan(stats.min_start_ms):

@@ -227,6 +227,9 @@ class LogAnalyzer:
     _OFF_STATUS = _OFF_DROPPED + 8
     _OUTBOX = _OFF_DROPPED + 64
 
+    REFINE_MIN_ROWS = 1 << 25   # KVM_REFINE_MIN_ROWS
+    REFINE_MIN_KEYS = 1 << 19   # KVM_REFINE_MIN_KEYS
+
     def __init__(self, device: Optional[torch.device] = None, stream: Optional[torch.cuda.Stream] = None):
         self.device = device or require_cuda()
         self.lib = N.lib()
@@ -260,6 +263,8 @@ class LogAnalyzer:
         self._done = torch.cuda.Event()
         self.launches = 0   # kernels launched by the last analyze() (for bench accounting)
         self.timer = _NoTimer()   # bench.py swaps in a StageTimer
+        self.refine_rounds: Optional[int] = None            # None: by log size (_refine_rounds)
+        self.refine_min_keys: int = self.REFINE_MIN_KEYS    # a round works only above this many candidates
 
     # -- buffers
     def _ensure(self, n: int, arena: Optional[int] = None) -> None:
@@ -270,6 +275,13 @@ class LogAnalyzer:
         if self._sel_ws is None or self._sel_cap < cap:
             self._sel_ws = torch.empty(self.lib.kvm_select_workspace_bytes(cap), dtype=torch.uint8, device=self.device)
             self._sel_cap = cap
+
+    def _refine_rounds(self, n_rows: int) -> int:
+        """Refine rounds to launch (kvm_select_plan_refine): `refine_rounds` when set, else one
+        round for logs of REFINE_MIN_ROWS rows and more (include/kvmini_b200.h)."""
+        if self.refine_rounds is not None:
+            return int(self.refine_rounds)
+        return 1 if n_rows >= self.REFINE_MIN_ROWS else 0
 
     def _cold_device(self, cold_times: Sequence[float]) -> Tuple[torch.Tensor, int]:
         key = tuple(sorted(float(c) for c in cold_times))
@@ -343,15 +355,24 @@ class LogAnalyzer:
             extras.series_dropped = self._dropped_ptr
         extras.digit_records = self._digits.data_ptr()
         ws, fl = self._sel_ws.data_ptr(), self._flags.data_ptr()
+        rounds = self._refine_rounds(dlog.n)
         with tm.stage("select_plan"):
-            N.check(lib.kvm_select_plan(self._stats_ptr + N.LogStatsC.sets.offset, queries, nq,
-                                        C.byref(hspec) if hspec is not None else None, ws,
-                                        self._sel_ws.numel(), arena, st), "kvm_select_plan")
+            N.check(lib.kvm_select_plan_refine(self._stats_ptr + N.LogStatsC.sets.offset, queries, nq,
+                                               C.byref(hspec) if hspec is not None else None, ws,
+                                               self._sel_ws.numel(), arena, rounds, int(self.refine_min_keys), st),
+                    "kvm_select_plan")
         with tm.stage("select_hist"):
             N.check(lib.kvm_log_select_hist(C.byref(log_c), fl, self._stats_ptr, C.byref(extras), ws, st),
                     "kvm_log_select_hist")
         with tm.stage("select_resolve"):
             N.check(lib.kvm_select_resolve(ws, st), "kvm_select_resolve")
+        for _ in range(rounds):   # large logs: narrow every candidate bucket 2048x before compacting
+            with tm.stage("select_refine_hist"):
+                N.check(lib.kvm_log_select_refine_hist(C.byref(log_c), fl, self._digits.data_ptr(), ws, st),
+                        "kvm_log_select_refine_hist")
+            with tm.stage("select_refine"):
+                N.check(lib.kvm_select_refine(ws, st), "kvm_select_refine")
+            self.launches += 2
         with tm.stage("select_compact"):
             N.check(lib.kvm_log_select_compact(C.byref(log_c), fl, self._digits.data_ptr(), ws, st),
                     "kvm_log_select_compact")
@@ -386,7 +407,8 @@ class LogAnalyzer:
             graph_key = (tuple(dlog.cols[k].data_ptr() for k in F64_COLS + I64_COLS), dlog.n,
                          tuple(sorted(float(c) for c in cold_times)), num_bins, series_window_s,
                          id(quantiles), arena, self._sel_ws.data_ptr(), self._flags.data_ptr(),
-                         self._series_d.data_ptr() if want_series else 0)
+                         self._series_d.data_ptr() if want_series else 0,
+                         self._refine_rounds(dlog.n), self.refine_min_keys)
             entry = self._graphs.get(graph_key)
             if entry is None:
                 # eager run first (sets function attributes, fills caches), then capture

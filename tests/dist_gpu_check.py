@@ -28,7 +28,11 @@ def main():
     from oracle import np_port
 
     failures = []
-    for seed, uneven in ((5, False), (6, True)):
+    # (seed, uneven shards, refine_min_keys, candidate keys per rank in the fixed exchange)
+    #   refine_min_keys = 0 forces the refine round (it is launched in every sharded run; the device
+    #   skips it for small logs); a tiny exchange forces the "redo with an exact size" path
+    for seed, uneven, refine_min, gather in ((5, False, None, None), (6, True, None, None),
+                                             (7, True, 0, None), (8, False, None, 64), (9, True, 0, 16)):
         full = synth.request_columns(rows, seed=seed, span_ms=600_000.0)
         rng = np.random.default_rng(seed)
         full["ttfb_ms"][rng.integers(0, rows, rows // 100)] = np.nan
@@ -40,6 +44,10 @@ def main():
         lo, hi = cuts[rank], cuts[rank + 1]
         shard = {k: torch.from_numpy(np.ascontiguousarray(v[lo:hi])).to(dev) for k, v in full.items()}
         an = dist_api.ShardedAnalyzer(dev)
+        if refine_min is not None:
+            an.refine_min_keys = refine_min
+        if gather is not None:
+            an._gather_n = gather
         raw = an.analyze(engine.DeviceLog.from_tensors(shard), cold)
         got = report.core_results(raw, len(cold))
         exp = np_port.analyze(full, cold)

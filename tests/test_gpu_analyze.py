@@ -246,3 +246,70 @@ def test_status_member_mode_is_the_16_byte_path(api):
         stat = ops.quantile_stat(lat, p, member_mode=N.MEMBER_STATUS, member=st)
         exp = np_port.percentile(cols["latency_ms"][cols["status"] == 200], p)
         assert stat.interpolate(p) == exp
+
+
+# ---- refine rounds (large logs narrow every candidate bucket before the compact pass) --------
+def _refining_analyzer(rounds):
+    from kvmini_b200 import engine
+    an = engine.LogAnalyzer()
+    an.refine_rounds = rounds
+    an.refine_min_keys = 0          # refine whenever a bucket exists, however small the log
+    return an
+
+
+@pytest.mark.parametrize("rounds", [1, 2, 3])
+@pytest.mark.parametrize("n,seed", [(3, 30), (1000, 31), (100_000, 32), (1_000_001, 33)])
+def test_refine_rounds_vs_oracle(n, seed, rounds):
+    cols = _random_log(n, seed, nan_rows=n // 50, zero_tok_rows=n // 40)
+    t0 = float(cols["start_ms"].min()) / 1000.0
+    cold = [t0 + 1.0, t0 + 120.0, t0 + 700.0] if n > 3 else []
+    _check_against_oracle(cols, cold, _refining_analyzer(rounds))
+
+
+@pytest.mark.parametrize("rounds", [1, 4])
+def test_refine_with_duplicates_and_mixed_signs(rounds):
+    an = _refining_analyzer(rounds)
+    cols = _random_log(200_000, 34)
+    cols["latency_ms"][:] = 123.456
+    cols["ttfb_ms"][cols["status"] == 200] = 7.0
+    cols["tllt_ms"][::2] = 30000.0                       # a refined bucket that cannot shrink
+    _check_against_oracle(cols, [float(cols["start_ms"].min()) / 1000.0 + 3.0], an)
+    cols = _random_log(50_000, 35)
+    rng = np.random.default_rng(6)
+    cols["tllt_ms"] = np.where(cols["status"] == 200, rng.normal(0.0, 100.0, 50_000), np.nan)
+    _check_against_oracle(cols, [], an)
+    cols = _random_log(60_000, 36)
+    cols["latency_ms"] = np.round(cols["latency_ms"])   # few distinct values, narrow key range
+    _check_against_oracle(cols, [], an)
+
+
+def test_refined_and_plain_select_agree_on_a_large_log(analyzer):
+    """40M rows on the device (above KVM_REFINE_MIN_ROWS, so refinement is on by default):
+    order statistics, counts, histograms are identical with and without the refine round."""
+    import torch
+    from kvmini_b200 import engine, report
+    n = 40_000_000
+    g = torch.Generator(device="cuda").manual_seed(7)
+    dev = torch.device("cuda")
+    start = torch.rand(n, generator=g, device=dev, dtype=torch.float64) * 3.6e6 + 1.7e12
+    ttfb = torch.rand(n, generator=g, device=dev, dtype=torch.float64) * 180.0 + 20.0
+    gen = torch.empty(n, device=dev, dtype=torch.float64).exponential_(1.0 / 900.0, generator=g)
+    tok = torch.randint(1, 512, (n,), generator=g, device=dev, dtype=torch.int64)
+    status = torch.where(torch.rand(n, generator=g, device=dev) < 0.97, 200, 500).to(torch.int64)
+    cols = {"start_ms": start, "ttfb_ms": ttfb, "tllt_ms": ttfb + gen, "latency_ms": ttfb + gen + 1.5,
+            "status": status, "completion_tokens": tok, "total_tokens": tok + 100}
+    dlog = engine.DeviceLog.from_tensors(cols)
+    cold = [1.7e9 + 5.0, 1.7e9 + 1800.0]
+    plain = engine.LogAnalyzer()
+    plain.refine_rounds = 0
+    auto = engine.LogAnalyzer()
+    assert auto._refine_rounds(n) == 1
+    a = report.core_results(plain.analyze(dlog, cold), len(cold))
+    b = report.core_results(auto.analyze(dlog, cold), len(cold))
+    assert diff_keys(a, b) == []
+    # the median really is an order statistic of the data: count below / at it on the device
+    lat_ok = cols["latency_ms"][status == 200]
+    p50 = b["p50_ms"]
+    below, upto = int((lat_ok < p50).sum()), int((lat_ok <= p50).sum())
+    k = 0.5 * (lat_ok.numel() - 1)
+    assert below <= math.ceil(k) and upto > math.floor(k)
