@@ -518,6 +518,7 @@ __global__ void __launch_bounds__(RES_THREADS, 1) select_resolve_kernel(SelWs* w
   __shared__ QState qs[MAXQ];
   __shared__ uint32_t qmask[MAXQ];
   __shared__ ColParam cps[KVM_MAX_COLS];
+  __shared__ int64_t gsum[KVM_MAX_SETS][BINS / 32];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = RES_THREADS / 32;
   const int nq = ws->nq;
   const int nsets = ws->info.nsets;
@@ -528,6 +529,14 @@ __global__ void __launch_bounds__(RES_THREADS, 1) select_resolve_kernel(SelWs* w
     qmask[threadIdx.x] = ws->queries[threadIdx.x].set_mask;
   }
   if (threadIdx.x < KVM_MAX_COLS) cps[threadIdx.x] = ws->col[threadIdx.x];
+  __syncthreads();
+  // totals of every 32-bin group of every set (one warp reduction each)
+  for (int g = warp; g < nsets * (BINS / 32); g += nwarps) {
+    int64_t v = (int64_t)hs[g * 32 + lane];
+#pragma unroll
+    for (int m = 16; m; m >>= 1) v += __shfl_xor_sync(KVM_FULL, v, m);
+    if (lane == 0) gsum[g / (BINS / 32)][g % (BINS / 32)] = v;
+  }
   __syncthreads();
 
   for (int q = warp; q < nq; q += nwarps) {
@@ -544,9 +553,31 @@ __global__ void __launch_bounds__(RES_THREADS, 1) select_resolve_kernel(SelWs* w
       }
       continue;
     }
-    int64_t running = 0;
-    bool found = false;
-    for (int base = 0; base < BINS && !found; base += 32) {
+    // two-level walk: 64 group totals (2 per lane) locate the 32-bin group, one scan finishes
+    int64_t g0 = 0, g1 = 0;
+    for (int b = 0; b < nsets; ++b)
+      if ((mask >> b) & 1u) {
+        g0 += gsum[b][lane];
+        g1 += gsum[b][32 + lane];
+      }
+    int64_t i0 = g0, i1 = g1;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int64_t o0 = __shfl_up_sync(KVM_FULL, i0, d), o1 = __shfl_up_sync(KVM_FULL, i1, d);
+      if (lane >= d) {
+        i0 += o0;
+        i1 += o1;
+      }
+    }
+    const int64_t half = __shfl_sync(KVM_FULL, i0, 31);
+    i1 += half;
+    const unsigned h0 = __ballot_sync(KVM_FULL, i0 > s.rank), h1 = __ballot_sync(KVM_FULL, i1 > s.rank);
+    bool found = (h0 | h1) != 0;
+    if (found) {
+      const int gl = h0 ? __ffs(h0) - 1 : __ffs(h1) - 1;
+      const int grp = h0 ? gl : 32 + gl;
+      const int64_t before = h0 ? __shfl_sync(KVM_FULL, i0 - g0, gl) : __shfl_sync(KVM_FULL, i1 - g1, gl);
+      const int base = grp * 32;
       int64_t c = 0;
       for (int b = 0; b < nsets; ++b)
         if ((mask >> b) & 1u) c += (int64_t)hs[b * BINS + base + lane];
@@ -556,7 +587,8 @@ __global__ void __launch_bounds__(RES_THREADS, 1) select_resolve_kernel(SelWs* w
         int64_t o = __shfl_up_sync(KVM_FULL, incl, d);
         if (lane >= d) incl += o;
       }
-      const unsigned hit = __ballot_sync(KVM_FULL, running + incl > s.rank);
+      const unsigned hit = __ballot_sync(KVM_FULL, before + incl > s.rank);
+      found = hit != 0;
       if (hit) {
         const int l = __ffs(hit) - 1;
         const int64_t excl = __shfl_sync(KVM_FULL, incl - c, l);
@@ -564,7 +596,7 @@ __global__ void __launch_bounds__(RES_THREADS, 1) select_resolve_kernel(SelWs* w
         if (lane == 0) {
           q_bin[q] = (uint32_t)(base + l);
           q_cnt[q] = cnt;
-          s.resid = s.rank - (running + excl);
+          s.resid = s.rank - (before + excl);
           if (cp.shift == 0) {  // the digit is the whole key
             s.key = cp.kbase + (uint64_t)(base + l);
             s.resolved = 1;
@@ -575,9 +607,7 @@ __global__ void __launch_bounds__(RES_THREADS, 1) select_resolve_kernel(SelWs* w
           }
           qs[q] = s;
         }
-        found = true;
       }
-      running += __shfl_sync(KVM_FULL, incl, 31);
     }
     if (!found && lane == 0) {  // histogram inconsistent with counts (caller error)
       s.status = KVM_Q_OUT_OF_RANGE;
@@ -690,7 +720,9 @@ __global__ void __launch_bounds__(RES_THREADS, 1) select_resolve_kernel(SelWs* w
 // that subdivide it, and a key belongs to a target iff (key - base) >> shift == 0.
 // Runs only while resolve / the previous round left ws->refine set, i.e. when the buckets
 // together hold more than refine_min keys (large logs).
-__global__ void __launch_bounds__(RES_THREADS, 1) select_refine_kernel(SelWs* ws) {
+constexpr int REF_THREADS = 512;
+
+__global__ void __launch_bounds__(REF_THREADS, 1) select_refine_kernel(SelWs* ws) {
   if (ws->status != KVM_OK || !ws->refine) return;
   __shared__ QState qs[MAXQ];
   __shared__ Bucket tg[MAXQ];
@@ -704,7 +736,7 @@ __global__ void __launch_bounds__(RES_THREADS, 1) select_refine_kernel(SelWs* ws
   __shared__ int newpar[MAXQ];
   __shared__ int nb_s;
   __shared__ int64_t used_s;
-  const int t = threadIdx.x, lane = t & 31, warp = t >> 5, nwarps = RES_THREADS / 32;
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5, nwarps = REF_THREADS / 32;
   const int nq = ws->nq;
   if (t < MAXQ) {
     qs[t] = ws->q[t];
@@ -723,8 +755,17 @@ __global__ void __launch_bounds__(RES_THREADS, 1) select_refine_kernel(SelWs* ws
     const int sh2 = T.shift - take;
     int64_t running = 0;
     bool found = false;
+    constexpr int CHUNK = 16;  // histogram words per lane loaded together (the row is L2-resident,
+    int64_t hv[CHUNK];         // a dependent load per step would cost a round trip each)
     for (int base = 0; base < (1 << take) && !found; base += 32) {
-      const int64_t c = (int64_t)h[base + lane];
+      const int ci = (base >> 5) % CHUNK;
+      if (ci == 0) {
+#pragma unroll
+        for (int u = 0; u < CHUNK; ++u) hv[u] = (int64_t)__ldcg(h + base + 32 * u + lane);  // rows are zero past 2^take
+      }
+      int64_t c = hv[0];
+#pragma unroll
+      for (int u = 1; u < CHUNK; ++u) c = ci == u ? hv[u] : c;
       int64_t incl = c;
 #pragma unroll
       for (int d = 1; d < 32; d <<= 1) {
@@ -1809,7 +1850,7 @@ extern "C" int kvm_log_select_refine_hist(const kvm_request_log* log, const uint
 
 extern "C" int kvm_select_refine(void* workspace, void* stream) {
   KVM_REQUIRE(workspace, "kvm_select_refine: null workspace");
-  select_refine_kernel<<<1, RES_THREADS, 0, (cudaStream_t)stream>>>(reinterpret_cast<SelWs*>(workspace));
+  select_refine_kernel<<<1, REF_THREADS, 0, (cudaStream_t)stream>>>(reinterpret_cast<SelWs*>(workspace));
   KVM_CUDA_CHECK(cudaGetLastError());
   return KVM_OK;
 }

@@ -124,6 +124,9 @@ class ShardedAnalyzer(engine.LogAnalyzer):
         self._gather_n = self.GATHER_KEYS
         self._arena_all: Optional[torch.Tensor] = None
         self._hist_glob = torch.zeros(N.KVM_MAX_HISTS * N.KVM_HIST_MAX_BINS, dtype=torch.int64, device=dev)
+        # a refine round costs about one more 9 B/row pass; it pays once the candidate exchange
+        # (world x candidates x 8 B into every rank) would cost more than that
+        self.refine_min_keys = max(self.REFINE_MIN_KEYS, (1 << 22) // self.world)
 
     def _refine_rounds(self, n_rows: int) -> int:
         """Sharded runs always launch one refine round: the shard sizes of the other ranks are
