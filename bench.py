@@ -156,8 +156,8 @@ def workload_config(args, n_gpus):
     return {
         "workload": ("configs[1]: synthetic 10M-request log, full analyze (p50/p95/p99 latency+TTFT, cold/warm, "
                      "4 histograms, tokens/sec, 1s series) + cost per 1K tokens" if n_gpus == 1 else
-                     "configs[4] layout: log sharded by time range, exact global quantiles via NCCL histogram "
-                     "all-reduce + 1s-window series"),
+                     "configs[4] layout: log sharded by time range, exact global quantiles (digit histograms "
+                     "summed across ranks, candidates exchanged) + 1s-window series"),
         "rows_per_gpu": args.rows, "rows_total": args.rows * n_gpus,
         "bytes_per_row": ROW_BYTES,
         "l2": f"inputs ({args.rows * ROW_BYTES / 1e6:.0f} MB per GPU) exceed the 126 MB L2; no flush needed",
@@ -206,13 +206,11 @@ def run_ours(args):
 
     if world > 1:
         from kvmini_b200 import dist_api
-        analyzer = dist_api.ShardedAnalyzer(device)
+        analyzer = dist_api.ShardedAnalyzer(device, exchange=args.exchange)
     else:
         analyzer = engine.LogAnalyzer(device)
 
-    graphs = world == 1   # CUDA-graph replay of the launch sequence (N>1 launches eagerly: capturing
-                          # the NCCL collectives in a graph hung on this stack)
-    pipelined = world == 1
+    graphs = not args.eager   # CUDA-graph replay of the launch sequence (N>1: kernels AND collectives)
     dlog_resident = engine.DeviceLog.from_tensors(resident)
     staging = ({k: torch.empty_like(v) for k, v in resident.items()} if pinned is not None else None)
     dlog_staging = engine.DeviceLog.from_tensors(staging) if staging is not None else None
@@ -232,6 +230,17 @@ def run_ours(args):
     if world == 1:
         pipe = (engine.LogAnalyzer(device, stream=torch.cuda.Stream(device)),
                 engine.LogAnalyzer(device, stream=torch.cuda.Stream(device)))
+    elif not args.no_pipeline:
+        # N>1: only with the peer-memory exchange (no collective library call on the data path, so
+        # two analyses can be in flight); every rank takes the same branch
+        analyzer.analyze(engine.DeviceLog.from_tensors(resident), cold)
+        if analyzer.exchange != "nccl":
+            pipe = tuple(dist_api.ShardedAnalyzer(device, exchange="peer", stream=torch.cuda.Stream(device))
+                         for _ in range(2))
+    pipelined = pipe is not None
+    if args.refine_min_keys is not None:
+        for an in (analyzer,) + tuple(pipe or ()):
+            an.refine_min_keys = args.refine_min_keys
 
     def run_pipelined(dlog, k, before_submit=None):
         pair = pipe
@@ -362,8 +371,15 @@ def run_ours(args):
             "launch_mode": ("timed region: CUDA-graph replay of the 7-kernel sequence, two analyses in flight on "
                             "two streams (host post-processing of step k and the single-CTA kernels of one "
                             "analysis overlap the streaming passes of the other); per-kernel durations from "
-                            "the same K steps launched eagerly on one stream with CUDA events" if pipelined else
-                            "eager launches, kernels and NCCL collectives stream-ordered, one host sync per step"),
+                            "the same K steps launched eagerly on one stream with CUDA events"
+                            if pipelined and world == 1 else
+                            ("timed region: CUDA-graph replay (kernels + exchanges), " +
+                             ("two analyses in flight on two streams, " if pipelined else "one analysis at a time, ") +
+                             "one host sync per step; per-kernel durations from the same K steps launched eagerly "
+                             "with CUDA events")),
+            "exchange": (None if world == 1 else
+                         ("peer memory over NVLink (kvm_peer_* kernels)" if analyzer.exchange != "nccl"
+                          else "NCCL collectives")),
             "ms_per_step_eager_instrumented": ms_eager / args.steps,
             "effective_gbs_whole_step": ROW_BYTES * n / (ms_total / args.steps * 1e-3) / 1e9,
             "check": {"p50_ms": core["p50_ms"], "p99_ms": core["p99_ms"],
@@ -376,8 +392,14 @@ def run_ours(args):
                 "value": rate, "unit": UNIT, "cores": 1, "kind": "port",
                 "sample": f"first {rows} of {n} rows, one pass of oracle/py_port.analyze + cost rollup "
                           f"({secs:.1f} s, single thread: the reference is single-threaded)"}
-        print(json.dumps(line))
+        print(json.dumps(line), flush=True)
     if dist is not None:
+        # graphs that hold captured collectives must be gone before the communicator is torn down
+        # (destroying the group with them alive hung this stack)
+        analyzer.close()
+        for an in pipe or ():
+            an.close()
+        barrier()
         dist.destroy_process_group()
 
 
@@ -391,6 +413,12 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--device-data", action="store_true", help="generate the shard on the GPU (large --rows)")
     ap.add_argument("--no-e2e", action="store_true", help="with --device-data: skip the host-buffer leg")
+    ap.add_argument("--eager", action="store_true", help="launch every step eagerly (no CUDA-graph replay)")
+    ap.add_argument("--no-pipeline", action="store_true", help="N>1: one analysis in flight at a time")
+    ap.add_argument("--refine-min-keys", type=int, default=None,
+                    help="candidate total above which a refine round runs (default: library policy)")
+    ap.add_argument("--exchange", default="auto", choices=["auto", "peer", "nccl"],
+                    help="N>1: how the ranks exchange intermediate results")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":

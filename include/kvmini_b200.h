@@ -329,6 +329,35 @@ int kvm_select_finish(void* workspace, const uint64_t* const* arenas_host, int32
                                               h*num_bins; zeroed here; NULL = no histograms */,
                       void* stream);
 
+/* ---- peer-memory exchange (multi-GPU, one NVSwitch node).  No counterpart in the reference.
+ * Every rank owns an "exchange buffer" of the same layout that the host has mapped into all
+ * ranks (`peers[r]` = device address of rank r's buffer in THIS process; peers[rank] is the
+ * own one).  The sharded analysis replaces its collectives by these stream-ordered kernels:
+ *   put / put_candidates  stores into every rank's buffer over NVLink
+ *   add_u64               system-scope 64-bit atomic adds of the non-zero words (histograms)
+ *   barrier               per-pair arrival counters in the flag block at `flags_offset`
+ *                         (kvm_peer_flag_bytes() bytes, zeroed once by the host before first
+ *                         use): releases everything this rank stored before, then waits for
+ *                         the same from every rank.  The epoch is kept on the device, so the
+ *                         call can be captured in a CUDA graph and replayed.  A peer that does
+ *                         not arrive within ~3 s sets word [KVM_PEER_MAX_WORLD+1] of the flag
+ *                         block non-zero instead of hanging the GPU.
+ * Buffers that peers accumulate into must be zeroed by their owner BEFORE the owner's previous
+ * barrier in stream order (the peers' adds only start after they have passed that barrier). */
+#define KVM_PEER_MAX_WORLD 16
+int64_t kvm_peer_flag_bytes(void);
+int kvm_peer_put(const void* src, int64_t bytes, int64_t dst_offset, void* const* peers_host,
+                 int32_t world, int32_t rank, void* stream);
+int kvm_peer_add_u64(const uint64_t* src, int64_t words, int64_t dst_offset, void* const* peers_host,
+                     int32_t world, int32_t rank, void* stream);
+int kvm_peer_barrier(int64_t flags_offset, void* const* peers_host, int32_t world, int32_t rank,
+                     void* stream);
+/* after the compact pass: the filled part of every candidate bucket of `workspace` goes to
+ * offset slot_offset (+ the bucket's arena offset) of every rank's buffer; more than
+ * slot_capacity candidates (global bucket sizes, so all ranks agree) -> status KVM_ERR_ARENA */
+int kvm_peer_put_candidates(void* workspace, int64_t slot_offset, int64_t slot_capacity,
+                            void* const* peers_host, int32_t world, int32_t rank, void* stream);
+
 /* ------------------------------------------------------------------ histograms / series */
 
 /* K5: the four 20-bin value histograms of analyze.py:84-122,149-152 in one pass.

@@ -20,6 +20,7 @@ KVM_MAX_COLS = 8
 KVM_MAX_QUERIES = 48
 KVM_MAX_HISTS = 4
 KVM_HIST_MAX_BINS = 64
+KVM_PEER_MAX_WORLD = 16
 
 # row flags (kvm_log_scan)
 F_SUCCESS, F_COLD, F_TOKENS, F_GEN = 0x01, 0x02, 0x04, 0x08
@@ -135,6 +136,11 @@ def _declare(lib: C.CDLL) -> None:
         "kvm_column_select_compact": (C.c_int, [vp, i64, i32, vp, vp, vp]),
         "kvm_log_select_compact": (C.c_int, [P(RequestLogC), vp, vp, vp, vp]),
         "kvm_select_finish": (C.c_int, [vp, P(vp), i32, vp, vp, vp, vp]),
+        "kvm_peer_flag_bytes": (i64, []),
+        "kvm_peer_put": (C.c_int, [vp, i64, i64, P(vp), i32, i32, vp]),
+        "kvm_peer_add_u64": (C.c_int, [vp, i64, i64, P(vp), i32, i32, vp]),
+        "kvm_peer_barrier": (C.c_int, [i64, P(vp), i32, i32, vp]),
+        "kvm_peer_put_candidates": (C.c_int, [vp, i64, i64, P(vp), i32, i32, vp]),
         "kvm_log_histograms_workspace_bytes": (sz, [i32]),
         "kvm_log_histograms": (C.c_int, [P(RequestLogC), vp, vp, i32, vp, vp, sz, vp]),
         "kvm_column_histogram": (C.c_int, [vp, i64, f64, f64, i32, vp, vp, sz, vp]),

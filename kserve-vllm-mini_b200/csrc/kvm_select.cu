@@ -29,6 +29,7 @@
 
 #include "kvm_common.cuh"
 #include "kvm_log_device.cuh"
+#include "kvm_peer.cuh"
 
 namespace {
 
@@ -755,45 +756,63 @@ __global__ void __launch_bounds__(REF_THREADS, 1) select_refine_kernel(SelWs* ws
     const int sh2 = T.shift - take;
     int64_t running = 0;
     bool found = false;
-    constexpr int CHUNK = 16;  // histogram words per lane loaded together (the row is L2-resident,
-    int64_t hv[CHUNK];         // a dependent load per step would cost a round trip each)
-    for (int base = 0; base < (1 << take) && !found; base += 32) {
-      const int ci = (base >> 5) % CHUNK;
-      if (ci == 0) {
+    // 16 groups of 32 bins at a time: coalesced loads issued together, group totals by 16
+    // independent warp reductions (pipelined), then one scan inside the group holding the rank
+    constexpr int CHUNK = 16;
+    for (int cbase = 0; cbase < (1 << take) && !found; cbase += 32 * CHUNK) {
+      int64_t hv[CHUNK], tot[CHUNK];
 #pragma unroll
-        for (int u = 0; u < CHUNK; ++u) hv[u] = (int64_t)__ldcg(h + base + 32 * u + lane);  // rows are zero past 2^take
+      for (int u = 0; u < CHUNK; ++u) {
+        hv[u] = (int64_t)__ldcg(h + cbase + 32 * u + lane);  // rows are zero past 2^take
+        tot[u] = hv[u];
       }
-      int64_t c = hv[0];
 #pragma unroll
-      for (int u = 1; u < CHUNK; ++u) c = ci == u ? hv[u] : c;
+      for (int m = 16; m; m >>= 1) {
+#pragma unroll
+        for (int u = 0; u < CHUNK; ++u) tot[u] += __shfl_xor_sync(KVM_FULL, tot[u], m);
+      }
+      int gu = -1;
+      int64_t before = running, c = 0;
+#pragma unroll
+      for (int u = 0; u < CHUNK; ++u) {
+        if (gu < 0) {
+          if (before + tot[u] > s.resid) {
+            gu = u;
+            c = hv[u];
+          } else {
+            before += tot[u];
+          }
+        }
+      }
+      if (gu < 0) {
+        running = before;
+        continue;
+      }
       int64_t incl = c;
 #pragma unroll
       for (int d = 1; d < 32; d <<= 1) {
         int64_t o = __shfl_up_sync(KVM_FULL, incl, d);
         if (lane >= d) incl += o;
       }
-      const unsigned hit = __ballot_sync(KVM_FULL, running + incl > s.resid);
-      if (hit) {
-        const int l = __ffs(hit) - 1;
-        const int64_t excl = __shfl_sync(KVM_FULL, incl - c, l);
-        const int64_t cnt = __shfl_sync(KVM_FULL, c, l);
-        if (lane == 0) {
-          const uint32_t sub = (uint32_t)(base + l);
-          s.resid = s.resid - (running + excl);
-          if (sh2 == 0) {  // the sub-digit completes the key
-            s.key = T.base + (uint64_t)sub;
-            s.resolved = 1;
-            s.bucket = -1;
-          } else {
-            q_sub[q] = sub;
-            q_cnt[q] = cnt;
-            bkey[q] = ((uint64_t)(uint32_t)s.bucket << 32) | sub;
-          }
-          qs[q] = s;
+      const unsigned hit = __ballot_sync(KVM_FULL, before + incl > s.resid);
+      const int l = __ffs(hit) - 1;   // hit != 0: the group total exceeds the remaining rank
+      const int64_t excl = __shfl_sync(KVM_FULL, incl - c, l);
+      const int64_t cnt = __shfl_sync(KVM_FULL, c, l);
+      if (lane == 0) {
+        const uint32_t sub = (uint32_t)(cbase + 32 * gu + l);
+        s.resid = s.resid - (before + excl);
+        if (sh2 == 0) {  // the sub-digit completes the key
+          s.key = T.base + (uint64_t)sub;
+          s.resolved = 1;
+          s.bucket = -1;
+        } else {
+          q_sub[q] = sub;
+          q_cnt[q] = cnt;
+          bkey[q] = ((uint64_t)(uint32_t)s.bucket << 32) | sub;
         }
-        found = true;
+        qs[q] = s;
       }
-      running += __shfl_sync(KVM_FULL, incl, 31);
+      found = true;
     }
     if (!found && lane == 0) {  // histogram inconsistent with the bucket count
       s.status = KVM_Q_OUT_OF_RANGE;
@@ -2082,6 +2101,55 @@ extern "C" int kvm_select_post_unpack(void* workspace, const int64_t* gathered, 
                                                          reinterpret_cast<const long long*>(gathered), world,
                                                          reinterpret_cast<long long*>(counts_all),
                                                          reinterpret_cast<long long*>(dropped));
+  KVM_CUDA_CHECK(cudaGetLastError());
+  return KVM_OK;
+}
+
+// ---- peer-memory form of the candidate exchange ---------------------------------------------
+// Every rank copies the filled part of each of its buckets straight into its slot of every
+// rank's exchange buffer (same bucket offsets everywhere), so no fixed-size gather and no host
+// round trip is needed: the device knows how many candidates there are.
+namespace {
+__global__ void __launch_bounds__(256)
+peer_put_candidates_kernel(SelWs* ws, const uint64_t* __restrict__ arena, KvmPeerTable pt,
+                           int64_t slot_offset, int64_t slot_capacity) {
+  if (ws->status != KVM_OK) return;
+  if (ws->bucket_offsets[MAXQ] > slot_capacity) {  // global bucket sizes: every rank takes this branch
+    if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) ws->status = KVM_ERR_ARENA;
+    return;
+  }
+  uint64_t* __restrict__ dst = reinterpret_cast<uint64_t*>(pt.base[blockIdx.y] + slot_offset);
+  const int nb = ws->nbuckets;
+  for (int j = 0; j < nb; ++j) {
+    const int64_t off = ws->bucket_offsets[j];
+    int64_t cnt = ws->bucket_counts[j];
+    const int64_t cap = ws->bucket[j].count;
+    cnt = cnt < cap ? cnt : cap;
+    // 16-byte stores over the aligned middle of the bucket, single words at its ends
+    const int64_t head = (off & 1) && cnt > 0 ? 1 : 0;
+    const int64_t pairs = (cnt - head) >> 1;
+    const uint64_t* s8 = arena + off;
+    uint64_t* d8 = dst + off;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+      if (head) d8[0] = s8[0];
+      if ((cnt - head) & 1) d8[cnt - 1] = s8[cnt - 1];
+    }
+    const ulonglong2* s16 = reinterpret_cast<const ulonglong2*>(s8 + head);
+    ulonglong2* d16 = reinterpret_cast<ulonglong2*>(d8 + head);
+    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < pairs; i += (int64_t)gridDim.x * 256)
+      d16[i] = s16[i];
+  }
+}
+}  // namespace
+
+extern "C" int kvm_peer_put_candidates(void* workspace, int64_t slot_offset, int64_t slot_capacity,
+                                       void* const* peers, int32_t world, int32_t rank, void* stream) {
+  KvmPeerTable pt;
+  KVM_REQUIRE(workspace && kvm_peer_table(&pt, peers, world, rank) == 0,
+              "kvm_peer_put_candidates: bad argument (world=%d rank=%d)", world, rank);
+  KVM_REQUIRE(slot_offset % 16 == 0 && slot_capacity >= 0, "kvm_peer_put_candidates: slot offset must be 16-byte aligned");
+  peer_put_candidates_kernel<<<dim3(48, world), 256, 0, (cudaStream_t)stream>>>(
+      reinterpret_cast<SelWs*>(workspace), arena_of(workspace), pt, slot_offset, slot_capacity);
   KVM_CUDA_CHECK(cudaGetLastError());
   return KVM_OK;
 }

@@ -276,6 +276,13 @@ class LogAnalyzer:
             self._sel_ws = torch.empty(self.lib.kvm_select_workspace_bytes(cap), dtype=torch.uint8, device=self.device)
             self._sel_cap = cap
 
+    def close(self) -> None:
+        """Release the captured CUDA graphs (and what they pin).  A ShardedAnalyzer must be closed
+        before torch.distributed.destroy_process_group(): tearing the communicator down under
+        live graphs that contain its collectives hangs."""
+        self._graphs.clear()
+        torch.cuda.synchronize(self.device)
+
     def _refine_rounds(self, n_rows: int) -> int:
         """Refine rounds to launch (kvm_select_plan_refine): `refine_rounds` when set, else one
         round for logs of REFINE_MIN_ROWS rows and more (include/kvmini_b200.h)."""

@@ -28,11 +28,16 @@ def main():
     from oracle import np_port
 
     failures = []
-    # (seed, uneven shards, refine_min_keys, candidate keys per rank in the fixed exchange)
+    # (seed, uneven shards, refine_min_keys, candidate keys per rank in the exchange, exchange mode)
     #   refine_min_keys = 0 forces the refine round (it is launched in every sharded run; the device
-    #   skips it for small logs); a tiny exchange forces the "redo with an exact size" path
-    for seed, uneven, refine_min, gather in ((5, False, None, None), (6, True, None, None),
-                                             (7, True, 0, None), (8, False, None, 64), (9, True, 0, 16)):
+    #   skips it for small logs); a tiny candidate slot forces the "redo with an exact size" path
+    cases = ((5, False, None, None, "nccl"), (6, True, None, None, "nccl"), (7, True, 0, None, "nccl"),
+             (8, False, None, 64, "nccl"), (9, True, 0, 16, "nccl"),
+             (5, False, None, None, "peer"), (6, True, None, None, "peer"), (7, True, 0, None, "peer"),
+             (8, False, None, 64, "peer"), (9, True, 0, 16, "peer"))
+    if os.environ.get("KVM_DIST_EXCHANGE"):
+        cases = tuple(c for c in cases if c[4] == os.environ["KVM_DIST_EXCHANGE"])
+    for seed, uneven, refine_min, gather, exchange in cases:
         full = synth.request_columns(rows, seed=seed, span_ms=600_000.0)
         rng = np.random.default_rng(seed)
         full["ttfb_ms"][rng.integers(0, rows, rows // 100)] = np.nan
@@ -43,18 +48,25 @@ def main():
         cuts = [0] + [(r * rows // world) + (7 * r + 1 if uneven else 0) for r in range(1, world)] + [rows]
         lo, hi = cuts[rank], cuts[rank + 1]
         shard = {k: torch.from_numpy(np.ascontiguousarray(v[lo:hi])).to(dev) for k, v in full.items()}
-        an = dist_api.ShardedAnalyzer(dev)
+        an = dist_api.ShardedAnalyzer(dev, exchange=exchange)
         if refine_min is not None:
             an.refine_min_keys = refine_min
         if gather is not None:
             an._gather_n = gather
+            an._fabric_slot = gather
         raw = an.analyze(engine.DeviceLog.from_tensors(shard), cold)
         got = report.core_results(raw, len(cold))
         exp = np_port.analyze(full, cold)
         d = diff_keys(got, {k: exp[k] for k in got}, rel={"time_to_first_token_ms": 1e-12})
         if not same(report.trim_series(raw), np_port.window_series(full)):
             d.append("timeseries differs")
-        failures += d
+        failures += [f"{exchange}/{seed}: {k}" for k in d]
+        if seed in (5, 7):   # the same analysis replayed from a CUDA graph (kernels + collectives)
+            for _ in range(3):
+                rep = report.core_results(an.analyze(engine.DeviceLog.from_tensors(shard), cold, use_graph=True),
+                                          len(cold))
+            failures += ["graph: " + k for k in diff_keys(rep, got)]
+        an.close()           # captured collectives must be released before the group is destroyed
     flag = torch.tensor([len(failures)], device=dev)
     dist.all_reduce(flag)
     if rank == 0:
