@@ -280,6 +280,11 @@ int kvm_select_post_pack(const void* workspace, const int64_t* dropped, int64_t*
 int kvm_select_post_unpack(void* workspace, const int64_t* gathered, int32_t world, int64_t* counts_all,
                            int64_t* dropped, void* stream);
 
+/* sets the status word to KVM_ERR_ARENA when the buckets hold more than `capacity_keys` keys in
+ * total (the size of the slots the candidates were exchanged through), so that the finish does
+ * not read past them; the caller retries with larger slots */
+int kvm_select_require_capacity(void* workspace, int64_t capacity_keys, void* stream);
+
 int kvm_select_plan(const kvm_set_info* info, const kvm_query* queries_host, int32_t nq,
                     const kvm_hist_spec* hists_host, void* workspace, size_t workspace_bytes,
                     int64_t arena_capacity, void* stream);

@@ -121,6 +121,7 @@ def _declare(lib: C.CDLL) -> None:
         "kvm_select_bucket_counts_ptr": (vp, [vp]),
         "kvm_select_bucket_offsets_ptr": (vp, [vp]),
         "kvm_select_info_ptr": (vp, [vp]),
+        "kvm_select_require_capacity": (C.c_int, [vp, i64, vp]),
         "kvm_select_post_words": (i32, []),
         "kvm_select_post_pack": (C.c_int, [vp, vp, vp, vp]),
         "kvm_select_post_unpack": (C.c_int, [vp, vp, i32, vp, vp, vp]),

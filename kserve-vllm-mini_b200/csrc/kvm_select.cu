@@ -2083,6 +2083,19 @@ __global__ void post_unpack_kernel(SelWs* ws, const long long* all, int world, l
 }
 }  // namespace
 
+// The exchanged candidate slots hold `capacity` keys per rank; with more candidates than that
+// (global bucket sizes - every rank agrees) the finish must not run over the slots.
+__global__ void require_capacity_kernel(SelWs* ws, long long capacity) {
+  if (ws->status == KVM_OK && ws->bucket_offsets[MAXQ] > capacity) ws->status = KVM_ERR_ARENA;
+}
+
+extern "C" int kvm_select_require_capacity(void* workspace, int64_t capacity_keys, void* stream) {
+  KVM_REQUIRE(workspace && capacity_keys >= 0, "kvm_select_require_capacity: bad argument");
+  require_capacity_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(reinterpret_cast<SelWs*>(workspace), capacity_keys);
+  KVM_CUDA_CHECK(cudaGetLastError());
+  return KVM_OK;
+}
+
 extern "C" int32_t kvm_select_post_words(void) { return POST_WORDS; }
 
 extern "C" int kvm_select_post_pack(const void* workspace, const int64_t* dropped, int64_t* record, void* stream) {

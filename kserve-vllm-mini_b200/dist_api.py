@@ -170,7 +170,7 @@ class ShardedAnalyzer(engine.LogAnalyzer):
     final read-back is stream-ordered: collectives are enqueued between the kernels, the host
     synchronises once at the end."""
 
-    GATHER_KEYS = 1 << 19   # candidate keys exchanged per rank (4 MB); more -> one exact retry
+    GATHER_KEYS = 1 << 17   # candidate keys exchanged per rank (1 MB); more -> one exact retry
 
     def __init__(self, device: Optional[torch.device] = None, group=None, exchange: str = "auto",
                  stream: Optional[torch.cuda.Stream] = None):
@@ -202,9 +202,10 @@ class ShardedAnalyzer(engine.LogAnalyzer):
         self._gather_n = self.GATHER_KEYS
         self._arena_all: Optional[torch.Tensor] = None
         self._hist_glob = torch.zeros(N.KVM_MAX_HISTS * N.KVM_HIST_MAX_BINS, dtype=torch.int64, device=dev)
-        # a refine round costs about one more 9 B/row pass; it pays once the candidate exchange
-        # (world x candidates x 8 B into every rank) would cost more than that
-        self.refine_min_keys = max(self.REFINE_MIN_KEYS, (1 << 22) // self.world)
+        # a refine round costs about one more 9 B/row pass and shrinks the candidate exchange
+        # (world x candidates x 8 B into every rank) and the finish to almost nothing; measured on
+        # 2 x 1e7 rows it already pays at 64K candidates (profiles/r1_scaling.md)
+        self.refine_min_keys = 1 << 16
 
     def _refine_rounds(self, n_rows: int) -> int:
         """Sharded runs always launch one refine round: the shard sizes of the other ranks are
@@ -399,7 +400,8 @@ class ShardedAnalyzer(engine.LogAnalyzer):
         N.check(lib.kvm_select_post_unpack(ws, self._post_all.data_ptr(), self.world,
                                            self._counts_all.data_ptr(),
                                            self._dropped_ptr if want_series else None, st))
-        self.launches += 2
+        N.check(lib.kvm_select_require_capacity(ws, self._gather_n, st))   # finish stays inside the slots
+        self.launches += 3
         ptrs = (C.c_void_p * self.world)(*[self._arena_all.data_ptr() + 8 * r * self._gather_n
                                            for r in range(self.world)])
         with tm.stage("select_finish"):
@@ -503,6 +505,12 @@ class ShardedAnalyzer(engine.LogAnalyzer):
                         grown = True
                     if self._fabric is not None and used > self._fabric.slot_keys:
                         self._fabric_slot = used + 1024
+                        grown = True
+                    if self._fabric is None and used > self._gather_n:
+                        self._gather_n = used + 1024   # (`used` sums GLOBAL bucket sizes: same on every rank)
+                        if state["arena"] < self._gather_n:
+                            state["arena"] = self._gather_n
+                            self._ensure(dlog.n, state["arena"])
                         grown = True
                     if not grown:
                         raise N.NativeError("select reported an arena overflow that no buffer explains")

@@ -48,6 +48,8 @@ def main():
         cuts = [0] + [(r * rows // world) + (7 * r + 1 if uneven else 0) for r in range(1, world)] + [rows]
         lo, hi = cuts[rank], cuts[rank + 1]
         shard = {k: torch.from_numpy(np.ascontiguousarray(v[lo:hi])).to(dev) for k, v in full.items()}
+        print(f"[rank {rank}] case seed={seed} uneven={uneven} refine_min={refine_min} slot={gather} {exchange}",
+              file=sys.stderr, flush=True)
         an = dist_api.ShardedAnalyzer(dev, exchange=exchange)
         if refine_min is not None:
             an.refine_min_keys = refine_min
