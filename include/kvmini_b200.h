@@ -235,7 +235,7 @@ int kvm_column_select(const double* values, int64_t n, int32_t member_mode, cons
  * library a workspace because they must not (or cannot) allocate device memory - e.g. a
  * latency monitor sharing the GPU with an inference server that has claimed the whole HBM
  * pool, where a cudaMalloc would fail or eat into the server's KV cache.  The scratch is a
- * fixed array inside the library image (about 8.7 MB per GPU that loads the library, held
+ * fixed array inside the library image (about 9.5 MB per GPU that loads the library, held
  * until exit), which bounds the input: n <= kvm_column_select_static_max_n() (1,048,576
  * values), member modes KVM_MEMBER_ALL / KVM_MEMBER_STATUS only; larger or multi-set inputs
  * are rejected with KVM_ERR_INVALID and a message.  Inputs and `results[nq]` are still the
