@@ -363,6 +363,42 @@ int kvm_peer_barrier(int64_t flags_offset, void* const* peers_host, int32_t worl
 int kvm_peer_put_candidates(void* workspace, int64_t slot_offset, int64_t slot_capacity,
                             void* const* peers_host, int32_t world, int32_t rank, void* stream);
 
+/* ------------------------------------------------------------------ CSV ingest (host only)
+ * SURVEY.md section 8f F1.  Columnar fast path for `read_requests_csv` (analyze.py:34-56) and the
+ * requests_classified.csv writer (analyze.py:597-604); no device work.  A cell that is a plain
+ * decimal literal is parsed here (std::from_chars: correctly rounded, same double as float());
+ * "" / "NaN" are reported as such; every other spelling is reported IRREGULAR and left to the
+ * caller's float().  Files this parser does not model carry flags and the caller uses the
+ * csv module instead. */
+typedef struct kvm_csv kvm_csv;
+enum { KVM_CSV_CELL_NUMBER = 0, KVM_CSV_CELL_EMPTY = 1, KVM_CSV_CELL_NAN_TEXT = 2, KVM_CSV_CELL_IRREGULAR = 3 };
+#define KVM_CSV_RAGGED 1      /* a row has more or fewer fields than the header */
+#define KVM_CSV_LONE_CR 2     /* '\r' used as a row terminator / inside an unquoted field */
+#define KVM_CSV_BARE_QUOTE 4  /* a '"' that csv.writer would not have produced */
+#define KVM_CSV_NEEDS_CSV_MODULE (KVM_CSV_RAGGED | KVM_CSV_LONE_CR | KVM_CSV_BARE_QUOTE)
+#define KVM_ERR_UNSUPPORTED (-5) /* input outside what the fast path models: use the fallback the text names */
+int kvm_csv_open(const char* path, kvm_csv** out);   /* mmap + header + quote-aware row index */
+int kvm_csv_close(kvm_csv* csv);
+int64_t kvm_csv_rows(const kvm_csv* csv);            /* data rows (blank lines skipped like csv.reader) */
+int32_t kvm_csv_ncols(const kvm_csv* csv);
+int32_t kvm_csv_flags(const kvm_csv* csv);
+const char* kvm_csv_col_name(const kvm_csv* csv, int32_t i);
+int32_t kvm_csv_find_col(const kvm_csv* csv, const char* name);  /* last column of that name, -1 if none */
+/* column `col` of every row: value[i] (NaN unless kind[i]==NUMBER) and kind[i] (KVM_CSV_CELL_*) */
+int kvm_csv_parse_f64(const kvm_csv* csv, int32_t col, double* value, uint8_t* kind, int32_t threads);
+/* several columns in one pass over the file (ncols <= 16) */
+int kvm_csv_parse_columns(const kvm_csv* csv, const int32_t* cols, int32_t ncols, double* const* values,
+                          uint8_t* const* kinds, int32_t threads);
+/* parsed text of one cell -> dst (no terminator); returns its length, -1 if out of range */
+int64_t kvm_csv_cell(const kvm_csv* csv, int64_t row, int32_t col, char* dst, int64_t cap);
+/* out[i] = 1 iff the cell equals one of the options (cost_estimator.py:108-111 is_cold_start) */
+int kvm_csv_match_any(const kvm_csv* csv, int32_t col, const char* const* options, int32_t noptions,
+                      uint8_t* out, int32_t threads);
+/* requests_classified.csv: all columns (+ is_cold_start), coerced columns re-serialised as
+ * repr(float); KVM_ERR_UNSUPPORTED when a coerced cell is IRREGULAR (the file is then incomplete) */
+int kvm_csv_write_classified(const kvm_csv* csv, const char* out_path, const uint8_t* is_cold,
+                             const int32_t* coerced_cols, int32_t ncoerced, int32_t threads);
+
 /* ------------------------------------------------------------------ histograms / series */
 
 /* K5: the four 20-bin value histograms of analyze.py:84-122,149-152 in one pass.

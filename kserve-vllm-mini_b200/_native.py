@@ -15,6 +15,9 @@ LIB_PATH = os.path.join(_HERE, "csrc", "libkvmini_b200.so")
 
 KVM_OK = 0
 KVM_ERR_ARENA = -4
+KVM_ERR_UNSUPPORTED = -5
+CSV_CELL_NUMBER, CSV_CELL_EMPTY, CSV_CELL_NAN_TEXT, CSV_CELL_IRREGULAR = range(4)
+CSV_NEEDS_CSV_MODULE = 7
 KVM_MAX_SETS = 8
 KVM_MAX_COLS = 8
 KVM_MAX_QUERIES = 48
@@ -142,6 +145,18 @@ def _declare(lib: C.CDLL) -> None:
         "kvm_peer_add_u64": (C.c_int, [vp, i64, i64, P(vp), i32, i32, vp]),
         "kvm_peer_barrier": (C.c_int, [i64, P(vp), i32, i32, vp]),
         "kvm_peer_put_candidates": (C.c_int, [vp, i64, i64, P(vp), i32, i32, vp]),
+        "kvm_csv_open": (C.c_int, [C.c_char_p, P(vp)]),
+        "kvm_csv_close": (C.c_int, [vp]),
+        "kvm_csv_rows": (i64, [vp]),
+        "kvm_csv_ncols": (i32, [vp]),
+        "kvm_csv_flags": (i32, [vp]),
+        "kvm_csv_col_name": (C.c_char_p, [vp, i32]),
+        "kvm_csv_find_col": (i32, [vp, C.c_char_p]),
+        "kvm_csv_parse_f64": (C.c_int, [vp, i32, vp, vp, i32]),
+        "kvm_csv_parse_columns": (C.c_int, [vp, vp, i32, P(vp), P(vp), i32]),
+        "kvm_csv_cell": (i64, [vp, i64, i32, vp, i64]),
+        "kvm_csv_match_any": (C.c_int, [vp, i32, P(C.c_char_p), i32, vp, i32]),
+        "kvm_csv_write_classified": (C.c_int, [vp, C.c_char_p, vp, vp, i32, i32]),
         "kvm_log_histograms_workspace_bytes": (sz, [i32]),
         "kvm_log_histograms": (C.c_int, [P(RequestLogC), vp, vp, i32, vp, vp, sz, vp]),
         "kvm_column_histogram": (C.c_int, [vp, i64, f64, f64, i32, vp, vp, sz, vp]),

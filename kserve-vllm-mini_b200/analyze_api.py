@@ -83,6 +83,10 @@ def analyze_log(log: columns.RequestLog, cold_times: Sequence[float],
 
 def _write_classified_csv(path: str, log: columns.RequestLog, is_cold: np.ndarray) -> None:
     """analyze.py:597-604: every row dict + is_cold_start, floats re-serialised by csv."""
+    if log.native is not None:
+        if log.native.write_classified(path, is_cold):
+            return
+        log.raw_rows = columns.read_rows(log.source_path)   # a cell only Python's float() can judge
     rows = log.raw_rows or []
     with open(path, "w", newline="") as f:
         if rows:
