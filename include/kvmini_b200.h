@@ -363,6 +363,20 @@ int kvm_peer_barrier(int64_t flags_offset, void* const* peers_host, int32_t worl
 int kvm_peer_put_candidates(void* workspace, int64_t slot_offset, int64_t slot_capacity,
                             void* const* peers_host, int32_t world, int32_t rank, void* stream);
 
+/* ------------------------------------------------------------------ nearest element (F2)
+ * Index of the member element whose value is closest to `target`; ties -> lowest index; NaN
+ * values never win; index -1 / distance NaN when no member qualifies.  Replaces the exemplar
+ * search of report_generator.py:437-454 (`sorted((abs(latency - p95), trace_id))[0]` over the
+ * status-200 rows): one 16 B/row pass instead of a CSV re-parse and a sort of tuples. */
+typedef struct {
+  int64_t index;
+  double distance; /* |values[index] - target| */
+} kvm_nearest_result;
+size_t kvm_column_nearest_workspace_bytes(void);
+int kvm_column_nearest(const double* values, int64_t n, int32_t member_mode, const void* member,
+                       double target, kvm_nearest_result* result /* device */, void* workspace,
+                       size_t workspace_bytes, void* stream);
+
 /* ------------------------------------------------------------------ CSV ingest (host only)
  * SURVEY.md section 8f F1.  Columnar fast path for `read_requests_csv` (analyze.py:34-56) and the
  * requests_classified.csv writer (analyze.py:597-604); no device work.  A cell that is a plain

@@ -81,6 +81,28 @@ def analyze_log(log: columns.RequestLog, cold_times: Sequence[float],
     return report.core_results(raw, len(cold_times)), raw
 
 
+def exemplar_trace_id(log: columns.RequestLog, target_ms: float,
+                      ops: Optional[engine.ColumnOps] = None) -> Optional[str]:
+    """trace_id of the successful request whose latency is closest to `target_ms` (the p95
+    exemplar behind the report's trace deep-link, report_generator.py:437-454: first row of
+    `sorted((abs(latency - p95), trace_id))` over rows with status 200 and a latency).  One
+    16 B/row pass on the GPU; the id itself is read from the CSV (native handle or kept rows).
+    The reference compares the raw status cell with "200"; here the coerced status == 200."""
+    if log.n == 0:
+        return None
+    ops = ops or engine.ColumnOps()
+    lat = torch.from_numpy(log.cols["latency_ms"]).to(ops.device)
+    status = torch.from_numpy(log.cols["status"]).to(ops.device)
+    idx, _ = ops.nearest(lat, target_ms, member_mode=N.MEMBER_STATUS, member=status)
+    if idx < 0:
+        return None
+    if log.native is not None and "trace_id" in log.native.header:
+        return log.native.cell(idx, "trace_id")
+    if log.raw_rows is not None:
+        return log.raw_rows[idx].get("trace_id")
+    return None
+
+
 def _write_classified_csv(path: str, log: columns.RequestLog, is_cold: np.ndarray) -> None:
     """analyze.py:597-604: every row dict + is_cold_start, floats re-serialised by csv."""
     if log.native is not None:

@@ -568,6 +568,22 @@ class ColumnOps:
         r = self.order_stats(values, [(1, N.RANK_LERP_LO, p, 0), (1, N.RANK_LERP_HI, p, 0)], **kw)
         return OrderStat(int(r[0]["n"]), float(r[0]["value"]), float(r[1]["value"]), int(r[0]["status"]))
 
+    def nearest(self, values: torch.Tensor, target: float, member_mode: int = N.MEMBER_ALL,
+                member: Optional[torch.Tensor] = None) -> Tuple[int, float]:
+        """(index, |value - target|) of the member element closest to `target` (lowest index on
+        ties, NaN never wins; (-1, nan) when there is none).  report_generator.py:437-454."""
+        assert values.dtype == torch.float64 and values.is_contiguous()
+        if getattr(self, "_near_ws", None) is None:
+            self._near_ws = torch.zeros(self.lib.kvm_column_nearest_workspace_bytes(), dtype=torch.uint8,
+                                        device=self.device)
+            self._near_d = torch.zeros(16, dtype=torch.uint8, device=self.device)
+        N.check(self.lib.kvm_column_nearest(values.data_ptr(), int(values.shape[0]), member_mode,
+                                            member.data_ptr() if member is not None else None, float(target),
+                                            self._near_d.data_ptr(), self._near_ws.data_ptr(), self._near_ws.numel(),
+                                            _stream_ptr(self.device)), "kvm_column_nearest")
+        raw = self._near_d.cpu().numpy().tobytes()
+        return int(np.frombuffer(raw, dtype=np.int64, count=1)[0]), float(np.frombuffer(raw, dtype=np.float64, count=1, offset=8)[0])
+
     def minmax_count(self, values: torch.Tensor) -> Tuple[int, float, float]:
         """count / min / max over non-NaN values via kvm_column_stats."""
         n = int(values.shape[0])

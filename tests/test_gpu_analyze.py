@@ -313,3 +313,57 @@ def test_refined_and_plain_select_agree_on_a_large_log(analyzer):
     below, upto = int((lat_ok < p50).sum()), int((lat_ok <= p50).sum())
     k = 0.5 * (lat_ok.numel() - 1)
     assert below <= math.ceil(k) and upto > math.floor(k)
+
+
+# ---- F2: exemplar search (report_generator.py:437-454) ---------------------------------------
+def _nearest_py(lat, status, target):
+    """The reference's expression: first element of a stable sort by |latency - target|."""
+    rows = [(abs(float(v) - target), i) for i, (v, s) in enumerate(zip(lat, status)) if s == 200 and not math.isnan(v)]
+    return sorted(rows, key=lambda x: x[0])[0][1] if rows else -1
+
+
+@pytest.mark.parametrize("n", [1, 2, 7, 1000, 100_001, 1_000_000])
+def test_nearest_matches_stable_sort(n):
+    import torch
+    from kvmini_b200 import _native as N
+    from kvmini_b200 import engine
+    ops = engine.ColumnOps()
+    rng = np.random.default_rng(n)
+    lat = np.round(rng.lognormal(5.5, 0.6, n), 1)            # coarse values: many exact ties
+    status = np.where(rng.random(n) < 0.9, 200, 500).astype(np.int64)
+    lat[rng.integers(0, n, max(1, n // 50))] = np.nan
+    target = float(np.nanpercentile(lat, 95)) if n > 2 else 100.0
+    d_lat, d_st = torch.from_numpy(lat).cuda(), torch.from_numpy(status).cuda()
+    idx, dist = ops.nearest(d_lat, target, member_mode=N.MEMBER_STATUS, member=d_st)
+    exp = _nearest_py(lat, status, target)
+    assert idx == exp
+    if exp >= 0:
+        assert dist == abs(lat[exp] - target)
+    # unaligned views take the scalar path
+    if n > 8:
+        idx2, _ = ops.nearest(d_lat[1:], target, member_mode=N.MEMBER_STATUS, member=d_st[1:])
+        assert idx2 == _nearest_py(lat[1:], status[1:], target)
+    # all elements are members
+    idx3, _ = ops.nearest(d_lat, target)
+    assert idx3 == _nearest_py(lat, np.full(n, 200), target)
+
+
+def test_nearest_without_members_and_trace_lookup(tmp_path):
+    import torch
+    from kvmini_b200 import _native as N
+    from kvmini_b200 import analyze_api, columns, engine
+    ops = engine.ColumnOps()
+    lat = torch.tensor([1.0, 2.0, float("nan")], dtype=torch.float64).cuda()
+    st = torch.tensor([500, 500, 200], dtype=torch.int64).cuda()
+    assert ops.nearest(lat, 1.5, member_mode=N.MEMBER_STATUS, member=st)[0] == -1
+    src = os.path.join(REPO, "tests", "golden", "cfg1", "requests.csv")
+    log = columns.load_requests_csv(src, keep_rows=True)
+    with open(os.path.join(REPO, "tests", "golden", "cfg1", "expected_results_analyze.json")) as f:
+        p95 = json.load(f)["p95_ms"]
+    got = analyze_api.exemplar_trace_id(log, p95, ops)
+    rows = []
+    with open(src, newline="") as f:                     # report_generator.py:440-451 verbatim in spirit
+        for row in csv.DictReader(f):
+            if row.get("status") == "200" and row.get("latency_ms"):
+                rows.append((abs(float(row["latency_ms"]) - p95), row.get("trace_id")))
+    assert got == sorted(rows, key=lambda x: x[0])[0][1]
