@@ -243,13 +243,16 @@ def run_ours(args):
             an.refine_min_keys = args.refine_min_keys
 
     def run_pipelined(dlog, k, before_submit=None):
+        """`dlog`: one DeviceLog, or one per analyzer of the pair (the e2e leg: each analyzer has
+        its own staging columns; before_submit(slot) fills them)."""
         pair = pipe
+        dlogs = dlog if isinstance(dlog, (tuple, list)) else (dlog, dlog)
         pending, out, launches = None, None, 0
         for it in range(k):
             an = pair[it & 1]
             if before_submit is not None:
-                before_submit()
-            nxt = an.analyze_async(dlog, cold, use_graph=True)
+                before_submit(it & 1)
+            nxt = an.analyze_async(dlogs[it & 1], cold, use_graph=graphs)
             launches += an.launches
             if pending is not None:
                 out = finish(pending())
@@ -263,6 +266,18 @@ def run_ours(args):
         for k, v in pinned.items():
             staging[k].copy_(v, non_blocking=True)   # H2D from pinned host memory, inside the timed region
         return step(dlog_staging, graphs)
+
+    # pipelined e2e: every analyzer of the pair owns a staging copy of the columns; the H2D copy of
+    # step k+1 (current stream) runs while step k computes on its analyzer's stream.  Slot s is
+    # refilled only after the analysis that used it has been collected (run_pipelined's order).
+    staging2 = dlog_staging2 = None
+    if pinned is not None and pipelined:
+        staging2 = (staging, {k: torch.empty_like(v) for k, v in resident.items()})
+        dlog_staging2 = tuple(engine.DeviceLog.from_tensors(s) for s in staging2)
+
+    def e2e_fill(slot):
+        for k, v in pinned.items():
+            staging2[slot][k].copy_(v, non_blocking=True)
 
     def barrier():
         if dist is not None:
@@ -312,12 +327,18 @@ def run_ours(args):
     ms_e2e = float("nan")
     e2e_steps = max(3, min(args.steps, 20))
     if pinned is not None:
-        e2e_step()
+        if dlog_staging2 is not None:
+            run_pipelined(dlog_staging2, 2, e2e_fill)
+        else:
+            e2e_step()
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        for _ in range(e2e_steps):
-            core, cost, raw = e2e_step()
+        if dlog_staging2 is not None:
+            (core, cost, raw), _ = run_pipelined(dlog_staging2, e2e_steps, e2e_fill)
+        else:
+            for _ in range(e2e_steps):
+                core, cost, raw = e2e_step()
         e1.record()
         barrier()
         ms_e2e = e0.elapsed_time(e1)
