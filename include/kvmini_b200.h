@@ -231,6 +231,21 @@ int kvm_column_select(const double* values, int64_t n, int32_t member_mode, cons
                       kvm_query_result* results, void* workspace, size_t workspace_bytes,
                       int64_t arena_capacity, void* stream);
 
+/* One-pass form of kvm_column_select for a few quantiles of ONE multiset (member mode ALL or
+ * STATUS, up to 8 queries of rank kinds that carry a p, at most 4 distinct p, 2^18 <= n < 2^31):
+ * a 4096-element stratified sample brackets every quantile, one 16 B/record pass counts exactly
+ * what lies below / inside each bracket and keeps the inside keys, two small kernels finish.
+ * Exact whenever it answers - the bracket is verified with the exact counts; otherwise (heavy
+ * duplicates, adversarial order, too few members) the status word - the first int32 of the
+ * workspace, stream-ordered - is KVM_ERR_UNSUPPORTED and the caller runs kvm_column_select.
+ * A host-side refusal (arguments outside the envelope) returns KVM_ERR_UNSUPPORTED at once.
+ * Replaces analyze.py:59-81 for the percentile path of SURVEY.md section 8d. */
+int kvm_column_select_sampled(const double* values, int64_t n, int32_t member_mode, const void* member,
+                              const kvm_query* queries_host, int32_t nq, kvm_query_result* results,
+                              void* workspace, size_t workspace_bytes, void* stream);
+size_t kvm_column_select_sampled_workspace_bytes(int64_t n);
+int64_t kvm_column_select_sampled_min_n(void);
+
 /* No counterpart in the reference.  kvm_column_select for callers that cannot give the
  * library a workspace because they must not (or cannot) allocate device memory - e.g. a
  * latency monitor sharing the GPU with an inference server that has claimed the whole HBM

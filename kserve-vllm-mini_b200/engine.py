@@ -526,16 +526,56 @@ class ColumnOps:
         self.device = device or require_cuda()
         self.lib = N.lib()
 
+    _P_KINDS = (N.RANK_LERP_LO, N.RANK_LERP_HI, N.RANK_UPPER_MEDIAN, N.RANK_FLOOR_PN, N.RANK_FLOOR_PNM1)
+
+    def _sampled(self, values, n, arr, queries, member_mode, member, st) -> Optional[np.ndarray]:
+        """The one-pass path (kvm_column_select_sampled); None when it does not apply or declines."""
+        nq = len(queries)
+        if (member_mode not in (N.MEMBER_ALL, N.MEMBER_STATUS) or nq > 8 or n >= 1 << 31
+                or n < int(self.lib.kvm_column_select_sampled_min_n())
+                or any(q[0] != 1 or q[1] not in self._P_KINDS for q in queries)
+                or len({0.5 if q[1] == N.RANK_UPPER_MEDIAN else q[2] for q in queries}) > 4):
+            return None
+        need = int(self.lib.kvm_column_select_sampled_workspace_bytes(n))
+        if getattr(self, "_qs_ws", None) is None or self._qs_ws.numel() < need:
+            self._qs_ws = torch.empty(need, dtype=torch.uint8, device=self.device)
+        ws = self._qs_ws
+        rc = self.lib.kvm_column_select_sampled(values.data_ptr(), n, member_mode,
+                                                member.data_ptr() if member is not None else None, arr, nq,
+                                                self._res_d.data_ptr(), ws.data_ptr(), ws.numel(), st)
+        if rc == N.KVM_ERR_UNSUPPORTED:
+            return None
+        N.check(rc, "kvm_column_select_sampled")
+        status_off = N.KVM_MAX_QUERIES * C.sizeof(N.QueryResultC)
+        self._res_d[status_off:status_off + 4].copy_(ws[0:4], non_blocking=True)
+        self._res_h.copy_(self._res_d, non_blocking=True)
+        torch.cuda.current_stream(self.device).synchronize()
+        out = self._res_h.numpy().tobytes()
+        if int(np.frombuffer(out, dtype=np.int32, count=1, offset=status_off)[0]) != N.KVM_OK:
+            return None    # bracket verification failed / overflow: the general select decides
+        self.last_path = "sampled"
+        return np.frombuffer(out, dtype=RESULT_DTYPE, count=nq).copy()
+
     def order_stats(self, values: torch.Tensor, queries: Sequence[Tuple[int, int, float, int]],
                     member_mode: int = N.MEMBER_ALL, member: Optional[torch.Tensor] = None,
-                    nsets: int = 1) -> np.ndarray:
+                    nsets: int = 1, sampled: bool = False) -> np.ndarray:
         """queries: (set_mask, rank_kind, p, rank).  Returns structured array of results.
-        Workspace and read-back buffers are cached; one synchronisation per call."""
+        Workspace and read-back buffers are cached; one synchronisation per call.  sampled=True tries the
+        one-pass sampled select first (exact or it declines; see csrc/kvm_quantile.cu)."""
         assert values.dtype == torch.float64 and values.is_contiguous()
         n = int(values.shape[0])
         nq = len(queries)
         arr = (N.QueryC * nq)(*[N.QueryC(*q) for q in queries])
         st = _stream_ptr(self.device)
+        if getattr(self, "_res_d", None) is None:
+            self._res_d = torch.zeros(N.KVM_MAX_QUERIES * C.sizeof(N.QueryResultC) + 64, dtype=torch.uint8,
+                                      device=self.device)
+            self._res_h = torch.zeros_like(self._res_d, device="cpu").pin_memory()
+        self.last_path = "general"
+        if sampled and nsets == 1:
+            got = self._sampled(values, n, arr, queries, member_mode, member, st)
+            if got is not None:
+                return got
         arena = max(int(self.lib.kvm_select_default_arena(n)), getattr(self, "_arena", 0))
         if getattr(self, "_res_d", None) is None:
             self._res_d = torch.zeros(N.KVM_MAX_QUERIES * C.sizeof(N.QueryResultC) + 64, dtype=torch.uint8,

@@ -367,3 +367,87 @@ def test_nearest_without_members_and_trace_lookup(tmp_path):
             if row.get("status") == "200" and row.get("latency_ms"):
                 rows.append((abs(float(row["latency_ms"]) - p95), row.get("trace_id")))
     assert got == sorted(rows, key=lambda x: x[0])[0][1]
+
+
+# ---- one-pass sampled select (csrc/kvm_quantile.cu) -------------------------------------------
+def _ref_stat(vals, kind, p):
+    """Order statistic the reference's expressions index (analyze.py:65-81 and the dialects)."""
+    from kvmini_b200 import _native as N
+    n = len(vals)
+    pc = min(max(p, 0.0), 1.0)
+    rank = {N.RANK_LERP_LO: lambda: int(math.floor(pc * (n - 1))), N.RANK_LERP_HI: lambda: int(math.ceil(pc * (n - 1))),
+            N.RANK_UPPER_MEDIAN: lambda: n // 2, N.RANK_FLOOR_PN: lambda: int(p * n),
+            N.RANK_FLOOR_PNM1: lambda: int(p * (n - 1))}[kind]()
+    return vals[rank] if 0 <= rank < n else None
+
+
+@pytest.mark.parametrize("shape", ["lognormal", "sorted", "reversed", "periodic", "rounded", "two_values", "few_members"])
+@pytest.mark.parametrize("n", [1 << 18, 1_000_003, 5_000_000])
+def test_sampled_select_is_exact_or_declines(shape, n):
+    import torch
+    from kvmini_b200 import _native as N
+    from kvmini_b200 import engine
+    ops = engine.ColumnOps()
+    rng = np.random.default_rng(n % 1000 + len(shape))
+    lat = rng.lognormal(5.5, 0.6, n)
+    if shape == "sorted":
+        lat.sort()
+    elif shape == "reversed":
+        lat = np.sort(lat)[::-1].copy()
+    elif shape == "periodic":
+        lat = 100.0 + (np.arange(n) % 4096) * 0.25 + rng.random(n) * 1e-3     # period = the sampling stratum count
+    elif shape == "rounded":
+        lat = np.round(lat, 0)                                                # ~1500 distinct values
+    elif shape == "two_values":
+        lat = np.where(rng.random(n) < 0.5, 10.0, 20.0)
+    status = np.where(rng.random(n) < (0.001 if shape == "few_members" else 0.97), 200, 500).astype(np.int64)
+    lat[rng.integers(0, n, n // 100)] = np.nan
+    d_lat, d_st = torch.from_numpy(lat).cuda(), torch.from_numpy(status).cuda()
+    ok = np.sort(lat[(status == 200) & ~np.isnan(lat)])
+    q = [(1, k, p, 0) for p in (0.5, 0.95, 0.99) for k in (N.RANK_LERP_LO, N.RANK_LERP_HI)]
+    q += [(1, N.RANK_UPPER_MEDIAN, 0.0, 0), (1, N.RANK_FLOOR_PN, 0.95, 0)]
+    got = ops.order_stats(d_lat, q, member_mode=N.MEMBER_STATUS, member=d_st, sampled=True)
+    path = ops.last_path
+    for (mask, kind, p, _), g in zip(q, got):
+        assert int(g["n"]) == len(ok)
+        assert float(g["value"]) == _ref_stat(ok, kind, p), (shape, kind, p, path)
+    if shape in ("lognormal", "sorted", "reversed", "periodic"):
+        assert path == "sampled"          # continuous data in any order takes the one-pass path
+    # and the general select agrees bit for bit
+    ref = ops.order_stats(d_lat, q, member_mode=N.MEMBER_STATUS, member=d_st, sampled=False)
+    assert ops.last_path == "general" and np.array_equal(got["value"], ref["value"]) and np.array_equal(got["rank"], ref["rank"])
+
+
+def test_sampled_select_edges():
+    import torch
+    from kvmini_b200 import _native as N
+    from kvmini_b200 import engine
+    ops = engine.ColumnOps()
+    n = 1 << 20
+    rng = np.random.default_rng(77)
+    lat = rng.normal(0.0, 50.0, n)                     # mixed signs
+    d = torch.from_numpy(lat).cuda()
+    srt = np.sort(lat)
+    q = [(1, k, p, 0) for p in (0.0, 1.0, 0.001, 0.9999) for k in (N.RANK_LERP_LO, N.RANK_LERP_HI)]
+    got = ops.order_stats(d, q, sampled=True)          # extremes: open-ended brackets
+    for (m, kind, p, _), g in zip(q, got):
+        assert float(g["value"]) == _ref_stat(srt, kind, p)
+    # unaligned view, member mode ALL
+    got = ops.order_stats(d[1:], [(1, N.RANK_LERP_LO, 0.5, 0), (1, N.RANK_LERP_HI, 0.5, 0)], sampled=True)
+    s1 = np.sort(lat[1:])
+    assert float(got[0]["value"]) == _ref_stat(s1, N.RANK_LERP_LO, 0.5)
+    assert float(got[1]["value"]) == _ref_stat(s1, N.RANK_LERP_HI, 0.5)
+    # no member at all: declines (too few sample members), the general path reports the empty set
+    st = torch.full((n,), 500, dtype=torch.int64).cuda()
+    got = ops.order_stats(d, [(1, N.RANK_LERP_LO, 0.5, 0)], member_mode=N.MEMBER_STATUS, member=st, sampled=True)
+    assert int(got[0]["n"]) == 0 and int(got[0]["status"]) == N.Q_EMPTY
+    # host-side refusals
+    lib = N.lib()
+    ws = torch.empty(lib.kvm_column_select_sampled_workspace_bytes(n), dtype=torch.uint8, device="cuda")
+    res = torch.zeros(8 * 32, dtype=torch.uint8, device="cuda")
+    absolute = (N.QueryC * 1)(N.QueryC(1, N.RANK_ABSOLUTE, 0.0, 5))
+    assert lib.kvm_column_select_sampled(d.data_ptr(), n, N.MEMBER_ALL, None, absolute, 1, res.data_ptr(),
+                                         ws.data_ptr(), ws.numel(), None) == N.KVM_ERR_UNSUPPORTED
+    five = (N.QueryC * 5)(*[N.QueryC(1, N.RANK_LERP_LO, p, 0) for p in (0.1, 0.2, 0.3, 0.4, 0.5)])
+    assert lib.kvm_column_select_sampled(d.data_ptr(), n, N.MEMBER_ALL, None, five, 5, res.data_ptr(),
+                                         ws.data_ptr(), ws.numel(), None) == N.KVM_ERR_UNSUPPORTED

@@ -157,6 +157,11 @@ def energy(args):
 
 
 def percentile(args):
+    """The 16 B/record percentile path: p50/p95/p99 of the status-200 latencies.  Reports the API
+    call (one host synchronisation + read-back per call) and the device time of the launch
+    sequence itself (K calls enqueued back to back, CUDA events around them), for the one-pass
+    sampled select and for the general three-pass select."""
+    import ctypes as C
     from kvmini_b200 import _native as N
     from kvmini_b200 import engine, synth
     dev = torch.device("cuda", 0)
@@ -165,12 +170,52 @@ def percentile(args):
     lat, st = c["latency_ms"], c["status"]
     ops = engine.ColumnOps(dev)
     q = [(1, k, p, 0) for p in (0.5, 0.95, 0.99) for k in (N.RANK_LERP_LO, N.RANK_LERP_HI)]
-    ms, r = timed(lambda: ops.order_stats(lat, q, member_mode=N.MEMBER_STATUS, member=st), warmup=3, steps=20)
+    ms, r = timed(lambda: ops.order_stats(lat, q, member_mode=N.MEMBER_STATUS, member=st, sampled=True),
+                  warmup=3, steps=20)
+    path = ops.last_path
     v = [float(x["value"]) for x in r]
     assert v == sorted(v)
-    print(json.dumps({"mode": "percentile", "rows": n, "ms": ms, "records_per_s": n / ms * 1e3,
-                      "algorithmic_bytes": 16.0 * n, "effective_gbs": 16.0 * n / ms / 1e6,
-                      "frac_of_peak_path_level": 16.0 * n / ms / 1e6 / peak(), "values": v}))
+    ms_gen, r2 = timed(lambda: ops.order_stats(lat, q, member_mode=N.MEMBER_STATUS, member=st, sampled=False),
+                       warmup=3, steps=20)
+    assert [float(x["value"]) for x in r2] == v, "sampled and general select disagree"
+    # device time of the launch sequences (no host synchronisation inside the loop)
+    lib = N.lib()
+    arr = (N.QueryC * len(q))(*[N.QueryC(*x) for x in q])
+    res = torch.zeros(len(q) * 32, dtype=torch.uint8, device=dev)
+    ws_s = torch.empty(lib.kvm_column_select_sampled_workspace_bytes(n), dtype=torch.uint8, device=dev)
+    cap = int(lib.kvm_select_default_arena(n))
+    ws_g = torch.empty(lib.kvm_select_workspace_bytes(cap), dtype=torch.uint8, device=dev)
+
+    def sampled_call():
+        N.check(lib.kvm_column_select_sampled(lat.data_ptr(), n, N.MEMBER_STATUS, st.data_ptr(), arr, len(q),
+                                              res.data_ptr(), ws_s.data_ptr(), ws_s.numel(),
+                                              torch.cuda.current_stream(dev).cuda_stream))
+
+    def general_call():
+        N.check(lib.kvm_column_select(lat.data_ptr(), n, N.MEMBER_STATUS, st.data_ptr(), 1, arr, len(q),
+                                      res.data_ptr(), ws_g.data_ptr(), ws_g.numel(), cap,
+                                      torch.cuda.current_stream(dev).cuda_stream))
+
+    out = {}
+    for name, call, ws in (("sampled", sampled_call, ws_s), ("general", general_call, ws_g)):
+        dms, _ = timed(call, warmup=3, steps=50)
+        torch.cuda.synchronize()
+        declined = int(ws[0:4].view(torch.int32).item()) != 0
+        if declined:
+            out[name] = {"declined": True}
+            continue
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            call()
+        gms, _ = timed(g.replay, warmup=3, steps=50)
+        got = np.frombuffer(res.cpu().numpy().tobytes(), dtype=engine.RESULT_DTYPE, count=len(q))
+        assert [float(x["value"]) for x in got] == v, name + " (direct) disagrees"
+        out[name] = {"device_ms_eager": dms, "device_ms_graph": gms,
+                     "effective_gbs_graph": 16.0 * n / gms / 1e6, "frac_of_peak_graph": 16.0 * n / gms / 1e6 / peak()}
+    print(json.dumps({"mode": "percentile", "rows": n, "api_path": path, "ms_api": ms, "ms_api_general": ms_gen,
+                      "records_per_s_api": n / ms * 1e3, "algorithmic_bytes": 16.0 * n,
+                      "frac_of_peak_api_level": 16.0 * n / ms / 1e6 / peak(), "device": out, "peak_gbs": peak(),
+                      "values": v}))
 
 
 if __name__ == "__main__":
