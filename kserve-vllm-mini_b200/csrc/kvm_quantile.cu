@@ -3,9 +3,10 @@
 //
 // The general select (kvm_select.cu) streams the column three times (range, histogram, compact).
 // For a handful of quantiles of one multiset a sample tells where to look:
-//   sample   4096 stratified pseudo-random members are sorted in shared memory (one CTA); for every
-//            requested p the sample positions p*m +- (7 sigma + 10) give a key bracket [lo, hi] that
-//            holds the wanted order statistic except with probability < 1e-11
+//   sample   4096 stratified pseudo-random members are binned in shared memory (one CTA, key-space
+//            histogram); for every requested p the sample ranks p*m +- (5 sigma + 6), widened to
+//            bin edges, give a key bracket [lo, hi] that holds the wanted order statistic except
+//            with probability ~1e-6 (then the verification below fails and the call declines)
 //   stream   ONE pass (16 B/record): per bracket the exact count of member keys below it, a
 //            2048-bin histogram of the keys inside it, and the inside keys themselves appended to
 //            a per-CTA region of the arena (no global atomics in the loop)
@@ -69,6 +70,7 @@ struct QsWs {
   unsigned long long hist[QS_NB][QS_BINS];
   QsPart part[QS_MAX_GRID];
   uint64_t list[QS_MAXQ][QS_LIST];
+  uint64_t rank_scratch[QS_MAXQ][QS_LIST];
 };
 
 constexpr size_t QS_HEADER = (sizeof(QsWs) + 255) / 256 * 256;
@@ -103,6 +105,9 @@ __global__ void __launch_bounds__(1024, 1)
 qs_sample_kernel(const double* __restrict__ values, int64_t n, const void* __restrict__ member, QsArgs a,
                  QsWs* ws, int grid, long long region_cap) {
   __shared__ uint64_t keys[QS_SAMPLE];
+  __shared__ uint32_t sh[QS_BINS];   // sample histogram, then (in place) its exclusive prefix
+  __shared__ uint64_t wmin[32], wmax[32];
+  __shared__ uint32_t wtot[32];
   __shared__ int m_eff_s;
   const int t = threadIdx.x;
   // clear what the streaming pass accumulates into
@@ -126,49 +131,112 @@ qs_sample_kernel(const double* __restrict__ values, int64_t n, const void* __res
     keys[s] = (qs_member<MODE>(member, i) && v == v) ? kvm_key(v) : QS_NONE;
   }
   __syncthreads();
-  // bitonic sort, ascending (non-members sort to the end)
-  for (int size = 2; size <= QS_SAMPLE; size <<= 1) {
-    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+  // No sort: a 2048-bin histogram of the sample in key space (range-adaptive between the sample's
+  // extremes) locates every wanted sample rank to within one bin; the bracket takes the outer
+  // edges of those bins, so it is a superset of the order-statistic bracket.
+  uint64_t mn = QS_NONE, mx = 0;
+  int cnt = 0;
 #pragma unroll
-      for (int k = 0; k < QS_SAMPLE / 2048; ++k) {
-        const int pair = t + 1024 * k;                    // 2048 compare-exchanges per step
-        const int lo = 2 * pair - (pair & (stride - 1));  // index of the lower element
-        const int hi = lo + stride;
-        const bool up = (lo & size) == 0;
-        const uint64_t x = keys[lo], y = keys[hi];
-        if ((x > y) == up) {
-          keys[lo] = y;
-          keys[hi] = x;
-        }
-      }
-      __syncthreads();
+  for (int k = 0; k < QS_SAMPLE / 1024; ++k) {
+    const uint64_t key = keys[t + 1024 * k];
+    if (key != QS_NONE) {
+      mn = key < mn ? key : mn;
+      mx = key > mx ? key : mx;
+      ++cnt;
     }
   }
-  // members in the sample = first index holding QS_NONE
-  {
-    int cnt = 0;
 #pragma unroll
-    for (int k = 0; k < QS_SAMPLE / 1024; ++k) cnt += keys[t + 1024 * k] != QS_NONE;
-    cnt = (int)kvm_warp_sum((int64_t)cnt);
-    if ((t & 31) == 0) atomicAdd(&m_eff_s, cnt);
+  for (int o = 16; o; o >>= 1) {
+    const uint64_t a0 = __shfl_xor_sync(KVM_FULL, mn, o), a1 = __shfl_xor_sync(KVM_FULL, mx, o);
+    mn = a0 < mn ? a0 : mn;
+    mx = a1 > mx ? a1 : mx;
+    cnt += __shfl_xor_sync(KVM_FULL, cnt, o);
+  }
+  if ((t & 31) == 0) {
+    wmin[t >> 5] = mn;
+    wmax[t >> 5] = mx;
+    atomicAdd(&m_eff_s, cnt);
+  }
+  sh[t] = 0;
+  sh[t + 1024] = 0;
+  __syncthreads();
+  if (t < 32) {
+    mn = wmin[t];
+    mx = wmax[t];
+#pragma unroll
+    for (int o = 16; o; o >>= 1) {
+      const uint64_t a0 = __shfl_xor_sync(KVM_FULL, mn, o), a1 = __shfl_xor_sync(KVM_FULL, mx, o);
+      mn = a0 < mn ? a0 : mn;
+      mx = a1 > mx ? a1 : mx;
+    }
+    if (t == 0) {
+      wmin[0] = mn;
+      wmax[0] = mx;
+    }
   }
   __syncthreads();
   const int m = m_eff_s;
+  const uint64_t kmin = wmin[0], kmax = wmax[0];
+  const uint64_t krange = m > 0 ? kmax - kmin : 0;
+  const int kbits = krange ? 64 - __clzll((long long)krange) : 0;
+  const int kshift = kbits > QS_BITS ? kbits - QS_BITS : 0;
+#pragma unroll
+  for (int k = 0; k < QS_SAMPLE / 1024; ++k) {
+    const uint64_t key = keys[t + 1024 * k];
+    if (key != QS_NONE) atomicAdd(&sh[(uint32_t)((key - kmin) >> kshift)], 1u);
+  }
+  __syncthreads();
+  // exclusive prefix over the 2048 bins: two bins per thread, warp scan, scan of the warp totals
+  {
+    const uint32_t c0 = sh[2 * t], c1 = sh[2 * t + 1];
+    uint32_t incl = c0 + c1;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t o = __shfl_up_sync(KVM_FULL, incl, d);
+      if ((t & 31) >= d) incl += o;
+    }
+    if ((t & 31) == 31) wtot[t >> 5] = incl;
+    __syncthreads();
+    if (t < 32) {
+      uint32_t w = wtot[t];
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t o = __shfl_up_sync(KVM_FULL, w, d);
+        if (t >= d) w += o;
+      }
+      wtot[t] = w;  // inclusive
+    }
+    __syncthreads();
+    const uint32_t before = incl - (c0 + c1) + ((t >> 5) ? wtot[(t >> 5) - 1] : 0u);
+    sh[2 * t] = before;          // every thread read its two bins before the barriers above
+    sh[2 * t + 1] = before + c0;
+  }
+  __syncthreads();
   if (t < QS_NB) {
     QsBracket b{QS_NONE, 0, 0, 0, 0};
     if (t < a.nb && m >= 512) {
       const double p = fmax(0.0, fmin(a.p[t], 1.0));
       const double pos = p * (double)(m - 1);
-      const double w = 7.0 * sqrt(p * (1.0 - p) * (double)m) + 10.0;
+      const double w = 5.0 * sqrt(p * (1.0 - p) * (double)m) + 6.0;
       const int li = (int)floor(pos - w), hi = (int)ceil(pos + w);
       const bool open_lo = li <= 0, open_hi = hi >= m - 1;
-      b.lo = open_lo ? 0ull : keys[li];
-      b.hi = open_hi ? QS_NONE - 1 : keys[hi];
+      // bin holding a sample rank r: the last bin whose exclusive prefix is <= r
+      auto bin_of_rank = [&](int r) {
+        int lo_b = 0, hi_b = QS_BINS - 1;
+        while (lo_b < hi_b) {
+          const int mid = (lo_b + hi_b + 1) >> 1;
+          if ((int)sh[mid] <= r) lo_b = mid;
+          else hi_b = mid - 1;
+        }
+        return lo_b;
+      };
+      b.lo = open_lo ? 0ull : kmin + ((uint64_t)bin_of_rank(li) << kshift);
+      b.hi = open_hi ? QS_NONE - 1 : kmin + (((uint64_t)bin_of_rank(hi) + 1) << kshift) - 1;
       // digits are scaled to the part of the bracket the sample has seen; an open end keeps the
       // outermost bin for whatever lies beyond the sample's extreme
-      b.base = open_lo ? keys[0] : b.lo;
-      const uint64_t top = open_hi ? keys[m - 1] : b.hi;
-      const uint64_t range = top - b.base;
+      b.base = open_lo ? kmin : b.lo;
+      const uint64_t top = open_hi ? kmax : b.hi;
+      const uint64_t range = top > b.base ? top - b.base : 0;
       const int bits = range ? 64 - __clzll((long long)range) : 0;
       const int span = (open_lo || open_hi) ? QS_BITS - 1 : QS_BITS;   // leave half of the bins beyond the sample
       b.shift = bits > span ? bits - span : 0;
@@ -192,19 +260,19 @@ struct QsSmem {
   uint32_t cursor[QS_NB];
 };
 
-template <int MODE, bool VEC>
+template <int MODE, bool VEC, int NBT>   // NBT = active brackets (the loops below are unrolled over them)
 __global__ void __launch_bounds__(QS_THREADS, 2)
 qs_stream_kernel(const double* __restrict__ values, int64_t n, const void* __restrict__ member, QsWs* ws,
                  uint64_t* __restrict__ arena) {
   __shared__ QsSmem S;
   __shared__ long long red[QS_THREADS / 32][1 + QS_NB];
   if (ws->status != KVM_OK) return;
-  for (int i = threadIdx.x; i < QS_NB * QS_BINS; i += QS_THREADS) (&S.hist[0][0])[i] = 0;
+  for (int i = threadIdx.x; i < NBT * QS_BINS; i += QS_THREADS) (&S.hist[0][0])[i] = 0;
   if (threadIdx.x < QS_NB) S.cursor[threadIdx.x] = 0;
-  uint64_t lo[QS_NB], hi[QS_NB], bs[QS_NB];
-  int sh[QS_NB];
+  uint64_t lo[NBT], hi[NBT], bs[NBT];
+  int sh[NBT];
 #pragma unroll
-  for (int b = 0; b < QS_NB; ++b) {
+  for (int b = 0; b < NBT; ++b) {
     lo[b] = ws->br[b].lo;
     hi[b] = ws->br[b].hi;
     bs[b] = ws->br[b].base;
@@ -214,32 +282,43 @@ qs_stream_kernel(const double* __restrict__ values, int64_t n, const void* __res
   __syncthreads();
   const int lane = threadIdx.x & 31;
   const unsigned lt = (1u << lane) - 1u;
-  int32_t members = 0, below[QS_NB];
+  int32_t members = 0, below[NBT];
 #pragma unroll
-  for (int b = 0; b < QS_NB; ++b) below[b] = 0;
+  for (int b = 0; b < NBT; ++b) below[b] = 0;
 
-  auto one = [&](double v, bool mem) {
-    mem = mem && (v == v);
-    const uint64_t key = kvm_key(v);
-    members += mem;
+  // two records per lane: their membership ballots share one cursor bump per bracket
+  auto two = [&](double v0, bool m0, double v1, bool m1) {
+    m0 = m0 && (v0 == v0);
+    m1 = m1 && (v1 == v1);
+    const uint64_t k0 = kvm_key(v0), k1 = kvm_key(v1);
+    members += (int)m0 + (int)m1;
 #pragma unroll
-    for (int b = 0; b < QS_NB; ++b) {
-      below[b] += mem & (key < lo[b]);
-      const bool in = mem & (key >= lo[b]) & (key <= hi[b]);
-      const unsigned mask = __ballot_sync(KVM_FULL, in);
-      if (mask) {
+    for (int b = 0; b < NBT; ++b) {
+      const bool l0 = k0 < lo[b], l1 = k1 < lo[b];
+      below[b] += (int)(m0 & l0) + (int)(m1 & l1);
+      const bool in0 = m0 & !l0 & (k0 <= hi[b]);
+      const bool in1 = m1 & !l1 & (k1 <= hi[b]);
+      const unsigned mk0 = __ballot_sync(KVM_FULL, in0), mk1 = __ballot_sync(KVM_FULL, in1);
+      if (mk0 | mk1) {
+        const int c0 = __popc(mk0);
         uint32_t base = 0;
-        const int leader = __ffs(mask) - 1;
-        if (lane == leader) base = atomicAdd(&S.cursor[b], (uint32_t)__popc(mask));
-        base = __shfl_sync(KVM_FULL, base, leader);
-        if (in) {
-          const long long pos = (long long)base + __popc(mask & lt);
-          if (pos < cap) arena[((size_t)blockIdx.x * QS_NB + b) * (size_t)cap + (size_t)pos] = key;
-          atomicAdd(&S.hist[b][qs_digit(key, bs[b], sh[b])], 1u);
+        if (lane == 0) base = atomicAdd(&S.cursor[b], (uint32_t)(c0 + __popc(mk1)));
+        base = __shfl_sync(KVM_FULL, base, 0);
+        uint64_t* __restrict__ region = arena + ((size_t)blockIdx.x * QS_NB + b) * (size_t)cap;
+        if (in0) {
+          const long long pos = (long long)base + __popc(mk0 & lt);
+          if (pos < cap) region[pos] = k0;
+          atomicAdd(&S.hist[b][qs_digit(k0, bs[b], sh[b])], 1u);
+        }
+        if (in1) {
+          const long long pos = (long long)base + c0 + __popc(mk1 & lt);
+          if (pos < cap) region[pos] = k1;
+          atomicAdd(&S.hist[b][qs_digit(k1, bs[b], sh[b])], 1u);
         }
       }
     }
   };
+  auto one = [&](double v, bool mem) { two(v, mem, 0.0, false); };
 
   if (VEC) {
     const int64_t npairs = n >> 1;
@@ -261,8 +340,7 @@ qs_stream_kernel(const double* __restrict__ values, int64_t n, const void* __res
           m0 = m1 = true;
         }
       }
-      one(v.x, m0);
-      one(v.y, m1);
+      two(v.x, m0, v.y, m1);
     }
     if ((n & 1) && blockIdx.x == 0 && threadIdx.x < 32) {
       const int64_t i = n - 1;
@@ -279,7 +357,7 @@ qs_stream_kernel(const double* __restrict__ values, int64_t n, const void* __res
   }
   __syncthreads();
   // flush: histogram, per-CTA partial counts
-  for (int i = threadIdx.x; i < QS_NB * QS_BINS; i += QS_THREADS) {
+  for (int i = threadIdx.x; i < NBT * QS_BINS; i += QS_THREADS) {
     const uint32_t c = (&S.hist[0][0])[i];
     if (c) atomicAdd(&ws->hist[0][0] + i, (unsigned long long)c);
   }
@@ -289,7 +367,7 @@ qs_stream_kernel(const double* __restrict__ values, int64_t n, const void* __res
     if (lane == 0) red[warp][0] = m;
 #pragma unroll
     for (int b = 0; b < QS_NB; ++b) {
-      const long long v = kvm_warp_sum((int64_t)below[b]);
+      const long long v = kvm_warp_sum((int64_t)(b < NBT ? below[b < NBT ? b : 0] : 0));
       if (lane == 0) red[warp][1 + b] = v;
     }
   }
@@ -305,9 +383,9 @@ qs_stream_kernel(const double* __restrict__ values, int64_t n, const void* __res
 }
 
 // ------------------------------------------------------------------ collect
-constexpr int QS_COLLECT_CTAS = 74;
+constexpr int QS_COLLECT_CTAS = 296;
 
-__global__ void __launch_bounds__(QS_THREADS, 1)
+__global__ void __launch_bounds__(QS_THREADS, 2)
 qs_collect_kernel(QsWs* ws, const uint64_t* __restrict__ arena) {
   __shared__ uint32_t hist[QS_NB][QS_BINS];  // n < 2^31 on this path (checked by the host)
   __shared__ long long tot[1 + 2 * QS_NB];  // members, below[], inside[]
@@ -398,11 +476,16 @@ qs_collect_kernel(QsWs* ws, const uint64_t* __restrict__ arena) {
     const uint64_t* __restrict__ keys = arena + ((size_t)cta * QS_NB + b) * (size_t)cap;
     const uint64_t base = br[b].base;
     const int sh = br[b].shift;
+    int want[QS_MAXQ];   // bins this bracket's queries need (-1: not this bracket)
+#pragma unroll
+    for (int q = 0; q < QS_MAXQ; ++q)
+      want[q] = (q < nq && qs[q].bracket == b && qs[q].qstatus == KVM_Q_OK) ? qs[q].bin : -1;
     for (long long i = t; i < cnt; i += QS_THREADS) {
       const uint64_t k = keys[i];
       const int d = (int)qs_digit(k, base, sh);
-      for (int q = 0; q < nq; ++q)
-        if (qs[q].bracket == b && qs[q].bin == d && qs[q].qstatus == KVM_Q_OK) {
+#pragma unroll
+      for (int q = 0; q < QS_MAXQ; ++q)
+        if (want[q] == d) {
           const unsigned long long pos = atomicAdd(&ws->list_n[q], 1ull);
           if (pos < (unsigned long long)QS_LIST) ws->list[q][pos] = k;
         }
@@ -414,7 +497,12 @@ qs_collect_kernel(QsWs* ws, const uint64_t* __restrict__ arena) {
 __global__ void __launch_bounds__(1024, 1)
 qs_rank_kernel(QsWs* ws, kvm_query_result* __restrict__ results) {
   __shared__ uint64_t keys[QS_LIST];
+  __shared__ uint32_t hist[QS_BINS];
+  __shared__ uint64_t wmin[32], wmax[32];
+  __shared__ uint32_t wtot[32];
+  __shared__ uint32_t sel_bin, sel_resid, small_n;
   __shared__ uint64_t answer;
+  uint64_t* small = reinterpret_cast<uint64_t*>(ws->rank_scratch[blockIdx.x]);  // m2 is tiny: L2-resident
   const int q = blockIdx.x;
   if (q >= ws->nq) return;
   const QsQuery s = ws->q[q];
@@ -434,17 +522,82 @@ qs_rank_kernel(QsWs* ws, kvm_query_result* __restrict__ results) {
     if (threadIdx.x == 0) results[q] = kvm_query_result{nan, s.n, s.rank, s.qstatus, 0};
     return;
   }
-  for (unsigned i = threadIdx.x; i < m; i += 1024) keys[i] = ws->list[q][i];
+  // narrow once with a range-adaptive 2048-bin histogram of the gathered keys, then rank the
+  // handful of keys in the bin that holds the residual rank by counting
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  uint64_t mn = QS_NONE, mx = 0;
+  for (unsigned i = t; i < m; i += 1024) {
+    const uint64_t k = ws->list[q][i];
+    keys[i] = k;
+    mn = k < mn ? k : mn;
+    mx = k > mx ? k : mx;
+  }
+#pragma unroll
+  for (int o = 16; o; o >>= 1) {
+    const uint64_t a0 = __shfl_xor_sync(KVM_FULL, mn, o), a1 = __shfl_xor_sync(KVM_FULL, mx, o);
+    mn = a0 < mn ? a0 : mn;
+    mx = a1 > mx ? a1 : mx;
+  }
+  if (lane == 0) {
+    wmin[warp] = mn;
+    wmax[warp] = mx;
+  }
+  hist[t] = 0;
+  hist[t + 1024] = 0;
+  if (t == 0) small_n = 0;
   __syncthreads();
-  for (unsigned i = threadIdx.x; i < m; i += 1024) {
+  mn = wmin[0];
+  mx = wmax[0];
+  for (int w = 1; w < 32; ++w) {
+    mn = wmin[w] < mn ? wmin[w] : mn;
+    mx = wmax[w] > mx ? wmax[w] : mx;
+  }
+  const uint64_t range = mx - mn;
+  const int bits = range ? 64 - __clzll((long long)range) : 0;
+  const int sh2 = bits > QS_BITS ? bits - QS_BITS : 0;
+  for (unsigned i = t; i < m; i += 1024) atomicAdd(&hist[(uint32_t)((keys[i] - mn) >> sh2)], 1u);
+  __syncthreads();
+  {
+    const uint32_t c0 = hist[2 * t], c1 = hist[2 * t + 1];
+    uint32_t incl = c0 + c1;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t o = __shfl_up_sync(KVM_FULL, incl, d);
+      if (lane >= d) incl += o;
+    }
+    if (lane == 31) wtot[warp] = incl;
+    __syncthreads();
+    uint32_t before = incl - (c0 + c1);
+    for (int w = 0; w < warp; ++w) before += wtot[w];
+    const long long r = s.resid;
+    if ((long long)before <= r && r < (long long)before + c0) {
+      sel_bin = 2 * t;
+      sel_resid = (uint32_t)(r - before);
+    } else if ((long long)before + c0 <= r && r < (long long)before + c0 + c1) {
+      sel_bin = 2 * t + 1;
+      sel_resid = (uint32_t)(r - before - c0);
+    }
+  }
+  __syncthreads();
+  const uint32_t sb = sel_bin, sr = sel_resid;
+  for (unsigned i = t; i < m; i += 1024) {
     const uint64_t k = keys[i];
-    long long less = 0, leq = 0;
-    for (unsigned j = 0; j < m; ++j) {
-      const uint64_t o = keys[j];
+    if ((uint32_t)((k - mn) >> sh2) == sb) {
+      const uint32_t pos = atomicAdd(&small_n, 1u);
+      small[pos] = k;   // at most m <= QS_LIST entries
+    }
+  }
+  __syncthreads();
+  const uint32_t m2 = small_n;
+  for (unsigned i = t; i < m2; i += 1024) {
+    const uint64_t k = small[i];
+    uint32_t less = 0, leq = 0;
+    for (unsigned j = 0; j < m2; ++j) {
+      const uint64_t o = small[j];
       less += o < k;
       leq += o <= k;
     }
-    if (less <= s.resid && s.resid < leq) answer = k;  // all writers agree
+    if (less <= sr && sr < leq) answer = k;  // all writers agree
   }
   __syncthreads();
   if (threadIdx.x == 0) results[q] = kvm_query_result{kvm_unkey(answer), s.n, s.rank, KVM_Q_OK, 0};
@@ -518,15 +671,26 @@ extern "C" int kvm_column_select_sampled(const double* values, int64_t n, int32_
   const long long cap = qs_region_cap(n, grid);
   const bool vec = (reinterpret_cast<uintptr_t>(values) & 15u) == 0 &&
                    (mode != KVM_MEMBER_STATUS || (reinterpret_cast<uintptr_t>(member) & 15u) == 0);
+#define KVM_QS_STREAM(M, V, NBT) \
+  qs_stream_kernel<M, V, NBT><<<grid, QS_THREADS, 0, st>>>(values, n, member, ws, arena)
+#define KVM_QS_NB(M, V)                 \
+  do {                                  \
+    if (a.nb == 1) KVM_QS_STREAM(M, V, 1);      \
+    else if (a.nb == 2) KVM_QS_STREAM(M, V, 2); \
+    else if (a.nb == 3) KVM_QS_STREAM(M, V, 3); \
+    else KVM_QS_STREAM(M, V, 4);                \
+  } while (0)
   if (mode == KVM_MEMBER_STATUS) {
     qs_sample_kernel<KVM_MEMBER_STATUS><<<1, 1024, 0, st>>>(values, n, member, a, ws, grid, cap);
-    if (vec) qs_stream_kernel<KVM_MEMBER_STATUS, true><<<grid, QS_THREADS, 0, st>>>(values, n, member, ws, arena);
-    else qs_stream_kernel<KVM_MEMBER_STATUS, false><<<grid, QS_THREADS, 0, st>>>(values, n, member, ws, arena);
+    if (vec) KVM_QS_NB(KVM_MEMBER_STATUS, true);
+    else KVM_QS_NB(KVM_MEMBER_STATUS, false);
   } else {
     qs_sample_kernel<KVM_MEMBER_ALL><<<1, 1024, 0, st>>>(values, n, member, a, ws, grid, cap);
-    if (vec) qs_stream_kernel<KVM_MEMBER_ALL, true><<<grid, QS_THREADS, 0, st>>>(values, n, member, ws, arena);
-    else qs_stream_kernel<KVM_MEMBER_ALL, false><<<grid, QS_THREADS, 0, st>>>(values, n, member, ws, arena);
+    if (vec) KVM_QS_NB(KVM_MEMBER_ALL, true);
+    else KVM_QS_NB(KVM_MEMBER_ALL, false);
   }
+#undef KVM_QS_NB
+#undef KVM_QS_STREAM
   qs_collect_kernel<<<QS_COLLECT_CTAS, QS_THREADS, 0, st>>>(ws, arena);
   qs_rank_kernel<<<nq, 1024, 0, st>>>(ws, results);
   KVM_CUDA_CHECK(cudaGetLastError());
