@@ -244,6 +244,13 @@ int kvm_column_select_sampled(const double* values, int64_t n, int32_t member_mo
                               const kvm_query* queries_host, int32_t nq, kvm_query_result* results,
                               void* workspace, size_t workspace_bytes, void* stream);
 size_t kvm_column_select_sampled_workspace_bytes(int64_t n);
+/* Same contract (exact or declines through the status word), different plan: the sample only
+ * estimates the key RANGE; one light pass histograms 12-bit digits and writes them as 2-byte
+ * records, a pass over those records fetches the ~0.1 % of values whose digit holds a rank. */
+int kvm_column_select_digit(const double* values, int64_t n, int32_t member_mode, const void* member,
+                            const kvm_query* queries_host, int32_t nq, kvm_query_result* results,
+                            void* workspace, size_t workspace_bytes, void* stream);
+size_t kvm_column_select_digit_workspace_bytes(int64_t n);
 int64_t kvm_column_select_sampled_min_n(void);
 
 /* No counterpart in the reference.  kvm_column_select for callers that cannot give the

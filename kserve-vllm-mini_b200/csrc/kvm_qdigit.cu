@@ -1,0 +1,543 @@
+// kvm_qdigit.cu - one-and-an-eighth-pass exact quantiles of one multiset (the 16 B/record
+// percentile path; analyze.py:59-81).
+//
+//   sample   4096 stratified pseudo-random members give an ESTIMATE of the key range (one CTA)
+//   hist     ONE pass over the data (16 B/record): 12-bit digit of every member key relative to
+//            the estimated range (bins 0 and 4095 catch what lies outside it), histogram in
+//            shared memory, and the digit written as a 2-byte record (0xFFFF = not a member)
+//   resolve  one CTA: exact member count = sum of the histogram, rank of every query, the bin
+//            holding it and the residual rank
+//   collect  pass over the 2 B/record digit records; the value of a record is fetched only when
+//            its digit is a wanted bin (~0.1 % of the records)
+//   rank     one CTA per query: one narrowing histogram over the gathered keys, then counting
+// Exact whenever it answers.  It declines (status word KVM_ERR_UNSUPPORTED, the caller runs the
+// general select) when a rank falls into a catch-all bin (the sample missed the range), when a
+// list overflows (heavy duplicates) or when the sample holds too few members.
+
+#include "kvm_common.cuh"
+#include "kvm_log_device.cuh"
+
+namespace {
+
+constexpr int QD_MAXQ = 8;
+constexpr int QD_SAMPLE = 4096;
+constexpr int QD_BINS = 4096;
+constexpr int QD_THREADS = 512;
+constexpr int QD_SMALL = 4096;     // keys ranked by counting at the very end
+constexpr int QD_STAGE = 512;      // keys a CTA stages per wanted bin before going to global memory
+constexpr uint64_t QD_NONE = ~0ull;
+
+struct QdQuery {
+  int32_t kind, slot;   // slot: index of the wanted bin this query reads its keys from
+  double p;
+  int32_t valid, bin;
+  long long resid, rank, n;
+  int32_t qstatus, pad;
+};
+
+struct QdWs {
+  int32_t status;
+  int32_t nq, nslots, pad;
+  uint64_t base;        // digit = key < base ? 0 : min(1 + ((key - base) >> shift), 4095)
+  int32_t shift, pad2;
+  long long list_cap;   // keys per slot list
+  QdQuery q[QD_MAXQ];
+  int32_t slot_bin[QD_MAXQ];
+  unsigned long long list_n[QD_MAXQ];
+  unsigned long long hist[QD_BINS];
+  uint64_t small[QD_MAXQ][QD_SMALL];
+};
+
+constexpr size_t QD_HEADER = (sizeof(QdWs) + 255) / 256 * 256;
+
+struct QdArgs {
+  int32_t nq;
+  int32_t kind[QD_MAXQ];
+  double p[QD_MAXQ];
+};
+
+__device__ __forceinline__ uint32_t qd_hash(uint32_t x) {
+  x ^= x >> 16;
+  x *= 0x7feb352du;
+  x ^= x >> 15;
+  x *= 0x846ca68bu;
+  x ^= x >> 16;
+  return x;
+}
+
+__device__ __forceinline__ uint32_t qd_digit(uint64_t key, uint64_t base, int shift) {
+  if (key < base) return 0u;
+  const uint64_t d = ((key - base) >> shift) + 1ull;
+  return d < (uint64_t)(QD_BINS - 1) ? (uint32_t)d : (uint32_t)(QD_BINS - 1);
+}
+
+template <int MODE>
+__device__ __forceinline__ bool qd_member(const void* member, int64_t i) {
+  if (MODE == KVM_MEMBER_STATUS) return reinterpret_cast<const int64_t*>(member)[i] == 200;
+  return true;
+}
+
+// ------------------------------------------------------------------ sample
+template <int MODE>
+__global__ void __launch_bounds__(1024, 1)
+qd_sample_kernel(const double* __restrict__ values, int64_t n, const void* __restrict__ member, QdArgs a,
+                 QdWs* ws, long long list_cap) {
+  __shared__ uint64_t wmin[32], wmax[32];
+  __shared__ int cnt_s;
+  const int t = threadIdx.x;
+  for (int i = t; i < QD_BINS; i += 1024) ws->hist[i] = 0;
+  if (t < QD_MAXQ) ws->list_n[t] = 0;
+  if (t == 0) cnt_s = 0;
+  __syncthreads();
+  const int64_t width = n / QD_SAMPLE;
+  uint64_t mn = QD_NONE, mx = 0;
+  int cnt = 0;
+#pragma unroll
+  for (int k = 0; k < QD_SAMPLE / 1024; ++k) {
+    const int s = t + 1024 * k;
+    const int64_t i = (int64_t)s * width + (int64_t)(qd_hash((uint32_t)s * 2654435761u + 12345u) % (uint64_t)width);
+    const double v = values[i];
+    if (qd_member<MODE>(member, i) && v == v) {
+      const uint64_t key = kvm_key(v);
+      mn = key < mn ? key : mn;
+      mx = key > mx ? key : mx;
+      ++cnt;
+    }
+  }
+#pragma unroll
+  for (int o = 16; o; o >>= 1) {
+    const uint64_t a0 = __shfl_xor_sync(KVM_FULL, mn, o), a1 = __shfl_xor_sync(KVM_FULL, mx, o);
+    mn = a0 < mn ? a0 : mn;
+    mx = a1 > mx ? a1 : mx;
+    cnt += __shfl_xor_sync(KVM_FULL, cnt, o);
+  }
+  if ((t & 31) == 0) {
+    wmin[t >> 5] = mn;
+    wmax[t >> 5] = mx;
+    atomicAdd(&cnt_s, cnt);
+  }
+  __syncthreads();
+  if (t == 0) {
+    for (int w = 1; w < 32; ++w) {
+      mn = wmin[w] < mn ? wmin[w] : mn;
+      mx = wmax[w] > mx ? wmax[w] : mx;
+    }
+    const int m = cnt_s;
+    ws->nq = a.nq;
+    ws->list_cap = list_cap;
+    if (m < 256) {
+      ws->status = KVM_ERR_UNSUPPORTED;  // too few members in the sample to trust its range
+    } else {
+      // widen the sampled range by a quarter on both sides (saturating), 2048 in-range bins at most
+      const uint64_t range = mx - mn, margin = (range >> 2) + 1;
+      const uint64_t lo = mn > margin ? mn - margin : 0ull;
+      const uint64_t hi = mx < QD_NONE - 1 - margin ? mx + margin : QD_NONE - 1;
+      const uint64_t r2 = hi - lo;
+      const int bits = r2 ? 64 - __clzll((long long)r2) : 0;
+      ws->base = lo;
+      ws->shift = bits > 11 ? bits - 11 : 0;
+      ws->status = KVM_OK;
+    }
+  }
+  if (t < QD_MAXQ) {
+    QdQuery q{};
+    q.kind = a.kind[t];
+    q.p = a.p[t];
+    ws->q[t] = q;
+  }
+}
+
+// ------------------------------------------------------------------ hist (+ digit records)
+template <int MODE, bool VEC>
+__global__ void __launch_bounds__(QD_THREADS, 2)
+qd_hist_kernel(const double* __restrict__ values, int64_t n, const void* __restrict__ member, QdWs* ws,
+               uint16_t* __restrict__ recs) {
+  __shared__ uint32_t hist[QD_BINS];
+  if (ws->status != KVM_OK) return;
+  for (int i = threadIdx.x; i < QD_BINS; i += QD_THREADS) hist[i] = 0;
+  const uint64_t base = ws->base;
+  const int shift = ws->shift;
+  __syncthreads();
+  auto digit_of_value = [&](double v, bool mem) -> uint32_t {
+    if (!(mem && v == v)) return 0xFFFFu;
+    const uint32_t d = qd_digit(kvm_key(v), base, shift);
+    atomicAdd(&hist[d], 1u);
+    return d;
+  };
+  if (VEC) {
+    // four records per thread and iteration: two 16-byte value loads, one 8-byte record store
+    const int64_t nquads = n >> 2;
+    for (int64_t qd = (int64_t)blockIdx.x * QD_THREADS + threadIdx.x; qd < nquads;
+         qd += (int64_t)gridDim.x * QD_THREADS) {
+      const int64_t i = qd << 2;
+      const double2 v0 = kvm_ld2(values + i), v1 = kvm_ld2(values + i + 2);
+      bool m0 = true, m1 = true, m2 = true, m3 = true;
+      if (MODE == KVM_MEMBER_STATUS) {
+        const int64_t* st = reinterpret_cast<const int64_t*>(member);
+        const longlong2 s0 = kvm_ld2(st + i), s1 = kvm_ld2(st + i + 2);
+        m0 = s0.x == 200;
+        m1 = s0.y == 200;
+        m2 = s1.x == 200;
+        m3 = s1.y == 200;
+      }
+      const uint32_t d0 = digit_of_value(v0.x, m0), d1 = digit_of_value(v0.y, m1);
+      const uint32_t d2 = digit_of_value(v1.x, m2), d3 = digit_of_value(v1.y, m3);
+      uint2 out;
+      out.x = d0 | (d1 << 16);
+      out.y = d2 | (d3 << 16);
+      *reinterpret_cast<uint2*>(recs + i) = out;
+    }
+    if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
+      const int64_t i = (n & ~3ll) + threadIdx.x;
+      recs[i] = (uint16_t)digit_of_value(values[i], qd_member<MODE>(member, i));
+    }
+  } else {
+    for (int64_t i = (int64_t)blockIdx.x * QD_THREADS + threadIdx.x; i < n; i += (int64_t)gridDim.x * QD_THREADS)
+      recs[i] = (uint16_t)digit_of_value(kvm_ld1(values + i), qd_member<MODE>(member, i));
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < QD_BINS; i += QD_THREADS) {
+    const uint32_t c = hist[i];
+    if (c) atomicAdd(&ws->hist[i], (unsigned long long)c);
+  }
+}
+
+// ------------------------------------------------------------------ resolve
+__global__ void __launch_bounds__(1024, 1) qd_resolve_kernel(QdWs* ws) {
+  __shared__ unsigned long long cum[QD_BINS];   // exclusive prefix of the histogram
+  __shared__ unsigned long long wtot[32];
+  __shared__ QdQuery qs[QD_MAXQ];
+  if (ws->status != KVM_OK) return;
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  constexpr int PER = QD_BINS / 1024;
+  unsigned long long c[PER], local = 0;
+#pragma unroll
+  for (int k = 0; k < PER; ++k) {
+    c[k] = ws->hist[t * PER + k];
+    local += c[k];
+  }
+  unsigned long long incl = local;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const unsigned long long o = __shfl_up_sync(KVM_FULL, incl, d);
+    if (lane >= d) incl += o;
+  }
+  if (lane == 31) wtot[warp] = incl;
+  if (t < QD_MAXQ) qs[t] = ws->q[t];
+  __syncthreads();
+  unsigned long long before = incl - local;
+  for (int w = 0; w < warp; ++w) before += wtot[w];
+#pragma unroll
+  for (int k = 0; k < PER; ++k) {
+    cum[t * PER + k] = before;
+    before += c[k];
+  }
+  __syncthreads();
+  unsigned long long total = 0;
+  for (int w = 0; w < 32; ++w) total += wtot[w];
+  const int nq = ws->nq;
+  if (t < nq) {
+    QdQuery s = qs[t];
+    s.n = (long long)total;
+    s.valid = 1;
+    s.bin = -1;
+    s.slot = -1;
+    if (total == 0) {
+      s.qstatus = KVM_Q_EMPTY;
+    } else {
+      s.rank = resolve_rank(s.kind, s.p, s.n, 0);
+      if (s.rank < 0 || s.rank >= s.n) {
+        s.qstatus = KVM_Q_OUT_OF_RANGE;
+      } else {
+        s.qstatus = KVM_Q_OK;
+        int lo = 0, hi = QD_BINS - 1;   // last bin whose exclusive prefix is <= rank
+        while (lo < hi) {
+          const int mid = (lo + hi + 1) >> 1;
+          if (cum[mid] <= (unsigned long long)s.rank) lo = mid;
+          else hi = mid - 1;
+        }
+        s.bin = lo;
+        s.resid = s.rank - (long long)cum[lo];
+        if (lo == 0 || lo == QD_BINS - 1) s.valid = 0;   // catch-all bins: the sample missed the range
+      }
+    }
+    qs[t] = s;
+  }
+  __syncthreads();
+  if (t == 0) {
+    int nslots = 0;
+    bool ok = true;
+    for (int q = 0; q < nq; ++q) {
+      QdQuery& s = qs[q];
+      if (!s.valid) ok = false;
+      if (s.qstatus != KVM_Q_OK || !s.valid) continue;
+      int slot = -1;
+      for (int k = 0; k < nslots; ++k)
+        if (ws->slot_bin[k] == s.bin) slot = k;
+      if (slot < 0) {
+        slot = nslots++;
+        ws->slot_bin[slot] = s.bin;
+      }
+      s.slot = slot;
+    }
+    for (int k = nslots; k < QD_MAXQ; ++k) ws->slot_bin[k] = -1;
+    ws->nslots = nslots;
+    if (!ok) ws->status = KVM_ERR_UNSUPPORTED;
+    for (int q = 0; q < QD_MAXQ; ++q) ws->q[q] = qs[q];
+  }
+}
+
+// ------------------------------------------------------------------ collect
+// Streams the 2 B/record digit records; a record whose digit is a wanted bin has its value
+// fetched and its key appended to that bin's list (staged per CTA, one cursor bump per flush).
+template <bool VEC>
+__global__ void __launch_bounds__(QD_THREADS, 2)
+qd_collect_kernel(const double* __restrict__ values, int64_t n, const uint16_t* __restrict__ recs, QdWs* ws,
+                  uint64_t* __restrict__ lists) {
+  __shared__ uint64_t stage[QD_MAXQ][QD_STAGE];
+  __shared__ uint32_t stage_n[QD_MAXQ];
+  __shared__ unsigned long long stage_pos[QD_MAXQ];
+  if (ws->status != KVM_OK) return;
+  const int nslots = ws->nslots;
+  const long long cap = ws->list_cap;
+  uint32_t want[QD_MAXQ];
+#pragma unroll
+  for (int k = 0; k < QD_MAXQ; ++k) want[k] = k < nslots ? (uint32_t)ws->slot_bin[k] : 0xFFFFFFFFu;
+  if (threadIdx.x < QD_MAXQ) stage_n[threadIdx.x] = 0;
+  __syncthreads();
+  auto hit = [&](int64_t i, uint32_t d) {
+#pragma unroll
+    for (int k = 0; k < QD_MAXQ; ++k)
+      if (d == want[k]) {
+        const uint64_t key = kvm_key(values[i]);
+        const uint32_t sp = atomicAdd(&stage_n[k], 1u);
+        if (sp < (uint32_t)QD_STAGE) {
+          stage[k][sp] = key;
+        } else {  // the stage is full: straight to the list
+          const unsigned long long pos = atomicAdd(&ws->list_n[k], 1ull);
+          if (pos < (unsigned long long)cap) lists[(size_t)k * (size_t)cap + pos] = key;
+        }
+      }
+  };
+  auto maybe = [&](int64_t i, uint32_t d) {
+    bool any = false;
+#pragma unroll
+    for (int k = 0; k < QD_MAXQ; ++k) any |= d == want[k];
+    if (any) hit(i, d);
+  };
+  if (VEC) {
+    const int64_t noct = n >> 3;
+    for (int64_t o = (int64_t)blockIdx.x * QD_THREADS + threadIdx.x; o < noct; o += (int64_t)gridDim.x * QD_THREADS) {
+      const uint4 r = __ldg(reinterpret_cast<const uint4*>(recs) + o);
+      const int64_t i = o << 3;
+      maybe(i + 0, r.x & 0xFFFFu);
+      maybe(i + 1, r.x >> 16);
+      maybe(i + 2, r.y & 0xFFFFu);
+      maybe(i + 3, r.y >> 16);
+      maybe(i + 4, r.z & 0xFFFFu);
+      maybe(i + 5, r.z >> 16);
+      maybe(i + 6, r.w & 0xFFFFu);
+      maybe(i + 7, r.w >> 16);
+    }
+    if (blockIdx.x == 0 && threadIdx.x < (n & 7)) {
+      const int64_t i = (n & ~7ll) + threadIdx.x;
+      maybe(i, recs[i]);
+    }
+  } else {
+    for (int64_t i = (int64_t)blockIdx.x * QD_THREADS + threadIdx.x; i < n; i += (int64_t)gridDim.x * QD_THREADS)
+      maybe(i, recs[i]);
+  }
+  __syncthreads();
+  if (threadIdx.x < QD_MAXQ) {
+    const uint32_t c = stage_n[threadIdx.x] < (uint32_t)QD_STAGE ? stage_n[threadIdx.x] : (uint32_t)QD_STAGE;
+    stage_n[threadIdx.x] = c;
+    if (c) stage_pos[threadIdx.x] = atomicAdd(&ws->list_n[threadIdx.x], (unsigned long long)c);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < QD_MAXQ * QD_STAGE; i += QD_THREADS) {
+    const int k = i / QD_STAGE, j = i % QD_STAGE;
+    if ((uint32_t)j < stage_n[k]) {
+      const unsigned long long pos = stage_pos[k] + j;
+      if (pos < (unsigned long long)cap) lists[(size_t)k * (size_t)cap + pos] = stage[k][j];
+    }
+  }
+}
+
+// ------------------------------------------------------------------ rank
+__global__ void __launch_bounds__(1024, 1)
+qd_rank_kernel(QdWs* ws, const uint64_t* __restrict__ lists, kvm_query_result* __restrict__ results) {
+  __shared__ uint32_t hist[2048];
+  __shared__ uint64_t wmin[32], wmax[32];
+  __shared__ uint32_t wtot[32];
+  __shared__ uint32_t sel_bin, sel_resid, small_n;
+  __shared__ uint64_t answer;
+  const int q = blockIdx.x;
+  if (q >= ws->nq) return;
+  const QdQuery s = ws->q[q];
+  const double nan = __longlong_as_double(0x7ff8000000000000ll);
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const bool need = ws->status == KVM_OK && s.valid && s.qstatus == KVM_Q_OK;
+  if (!need) {
+    // empty multiset / rank out of range: nothing to look up; a declined call reports NaN
+    if (t == 0) results[q] = kvm_query_result{nan, s.n, s.rank, s.qstatus, 0};
+    return;
+  }
+  const long long cap = ws->list_cap;
+  const unsigned long long m = ws->list_n[s.slot];
+  if (m > (unsigned long long)cap || (long long)m <= s.resid) {
+    if (t == 0) {
+      ws->status = KVM_ERR_UNSUPPORTED;  // all writers agree
+      results[q] = kvm_query_result{nan, s.n, s.rank, s.qstatus, 0};
+    }
+    return;
+  }
+  const uint64_t* __restrict__ keys = lists + (size_t)s.slot * (size_t)cap;
+  uint64_t* small = ws->small[q];
+  uint64_t mn = QD_NONE, mx = 0;
+  for (unsigned long long i = t; i < m; i += 1024) {
+    const uint64_t k = keys[i];
+    mn = k < mn ? k : mn;
+    mx = k > mx ? k : mx;
+  }
+#pragma unroll
+  for (int o = 16; o; o >>= 1) {
+    const uint64_t a0 = __shfl_xor_sync(KVM_FULL, mn, o), a1 = __shfl_xor_sync(KVM_FULL, mx, o);
+    mn = a0 < mn ? a0 : mn;
+    mx = a1 > mx ? a1 : mx;
+  }
+  if (lane == 0) {
+    wmin[warp] = mn;
+    wmax[warp] = mx;
+  }
+  hist[t] = 0;
+  hist[t + 1024] = 0;
+  if (t == 0) small_n = 0;
+  __syncthreads();
+  mn = wmin[0];
+  mx = wmax[0];
+  for (int w = 1; w < 32; ++w) {
+    mn = wmin[w] < mn ? wmin[w] : mn;
+    mx = wmax[w] > mx ? wmax[w] : mx;
+  }
+  const uint64_t range = mx - mn;
+  const int bits = range ? 64 - __clzll((long long)range) : 0;
+  const int sh2 = bits > 11 ? bits - 11 : 0;
+  for (unsigned long long i = t; i < m; i += 1024) atomicAdd(&hist[(uint32_t)((keys[i] - mn) >> sh2)], 1u);
+  __syncthreads();
+  {
+    const uint32_t c0 = hist[2 * t], c1 = hist[2 * t + 1];
+    uint32_t incl = c0 + c1;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t o = __shfl_up_sync(KVM_FULL, incl, d);
+      if (lane >= d) incl += o;
+    }
+    if (lane == 31) wtot[warp] = incl;
+    __syncthreads();
+    long long before = (long long)(incl - (c0 + c1));
+    for (int w = 0; w < warp; ++w) before += wtot[w];
+    const long long r = s.resid;
+    if (before <= r && r < before + c0) {
+      sel_bin = 2 * t;
+      sel_resid = (uint32_t)(r - before);
+    } else if (before + c0 <= r && r < before + c0 + c1) {
+      sel_bin = 2 * t + 1;
+      sel_resid = (uint32_t)(r - before - c0);
+    }
+  }
+  __syncthreads();
+  const uint32_t sb = sel_bin, sr = sel_resid;
+  for (unsigned long long i = t; i < m; i += 1024) {
+    const uint64_t k = keys[i];
+    if ((uint32_t)((k - mn) >> sh2) == sb) {
+      const uint32_t pos = atomicAdd(&small_n, 1u);
+      if (pos < (uint32_t)QD_SMALL) small[pos] = k;
+    }
+  }
+  __syncthreads();
+  const uint32_t m2 = small_n;
+  if (m2 > (uint32_t)QD_SMALL) {  // one value repeated thousands of times: the general select's job
+    if (t == 0) {
+      ws->status = KVM_ERR_UNSUPPORTED;
+      results[q] = kvm_query_result{nan, s.n, s.rank, s.qstatus, 0};
+    }
+    return;
+  }
+  for (unsigned i = t; i < m2; i += 1024) {
+    const uint64_t k = small[i];
+    uint32_t less = 0, leq = 0;
+    for (unsigned j = 0; j < m2; ++j) {
+      const uint64_t o = small[j];
+      less += o < k;
+      leq += o <= k;
+    }
+    if (less <= sr && sr < leq) answer = k;  // all writers agree
+  }
+  __syncthreads();
+  if (t == 0) results[q] = kvm_query_result{kvm_unkey(answer), s.n, s.rank, KVM_Q_OK, 0};
+}
+
+int qd_grid(int64_t n) { return kvm_grid_for(n, QD_THREADS * 4 * 4, 2); }
+long long qd_list_cap(int64_t n) {
+  const long long c = (long long)(n / 64) + 16384;   // a bin holds ~n/1500 of smooth data
+  return (c + 1) & ~1ll;
+}
+
+}  // namespace
+
+extern "C" size_t kvm_column_select_digit_workspace_bytes(int64_t n) {
+  if (n < 0) n = 0;
+  return QD_HEADER + kvm_align_up((size_t)n * sizeof(uint16_t) + 16, 256) +
+         (size_t)QD_MAXQ * (size_t)qd_list_cap(n) * sizeof(uint64_t) + 256;
+}
+
+extern "C" int kvm_column_select_digit(const double* values, int64_t n, int32_t mode, const void* member,
+                                       const kvm_query* queries, int32_t nq, kvm_query_result* results,
+                                       void* workspace, size_t workspace_bytes, void* stream) {
+  KVM_REQUIRE(values && queries && results && workspace, "kvm_column_select_digit: null argument");
+  if (!(mode == KVM_MEMBER_ALL || (mode == KVM_MEMBER_STATUS && member)) || nq < 1 || nq > QD_MAXQ ||
+      n < (1 << 18) || n >= (1ll << 31)) {
+    kvm_set_error("kvm_column_select_digit: needs member mode ALL/STATUS, 1..%d queries, 2^18 <= n < 2^31; "
+                  "use kvm_column_select", QD_MAXQ);
+    return KVM_ERR_UNSUPPORTED;
+  }
+  QdArgs a{};
+  a.nq = nq;
+  for (int q = 0; q < nq; ++q) {
+    const kvm_query& Q = queries[q];
+    if (Q.rank_kind == KVM_RANK_ABSOLUTE || Q.rank_kind < 0 || Q.rank_kind > KVM_RANK_FLOOR_PNM1 || Q.set_mask != 1u) {
+      kvm_set_error("kvm_column_select_digit: query %d is not a quantile of set 0; use kvm_column_select", q);
+      return KVM_ERR_UNSUPPORTED;
+    }
+    a.kind[q] = Q.rank_kind;
+    a.p[q] = Q.p;
+  }
+  if (workspace_bytes < kvm_column_select_digit_workspace_bytes(n)) {
+    kvm_set_error("kvm_column_select_digit: workspace %zu < %zu bytes", workspace_bytes,
+                  kvm_column_select_digit_workspace_bytes(n));
+    return KVM_ERR_WORKSPACE;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  unsigned char* wsb = reinterpret_cast<unsigned char*>(workspace);
+  QdWs* ws = reinterpret_cast<QdWs*>(wsb);
+  uint16_t* recs = reinterpret_cast<uint16_t*>(wsb + QD_HEADER);
+  uint64_t* lists = reinterpret_cast<uint64_t*>(wsb + QD_HEADER + kvm_align_up((size_t)n * sizeof(uint16_t) + 16, 256));
+  const long long cap = qd_list_cap(n);
+  const int grid = qd_grid(n);
+  const bool vec = (reinterpret_cast<uintptr_t>(values) & 15u) == 0 &&
+                   (mode != KVM_MEMBER_STATUS || (reinterpret_cast<uintptr_t>(member) & 15u) == 0);
+  if (mode == KVM_MEMBER_STATUS) {
+    qd_sample_kernel<KVM_MEMBER_STATUS><<<1, 1024, 0, st>>>(values, n, member, a, ws, cap);
+    if (vec) qd_hist_kernel<KVM_MEMBER_STATUS, true><<<grid, QD_THREADS, 0, st>>>(values, n, member, ws, recs);
+    else qd_hist_kernel<KVM_MEMBER_STATUS, false><<<grid, QD_THREADS, 0, st>>>(values, n, member, ws, recs);
+  } else {
+    qd_sample_kernel<KVM_MEMBER_ALL><<<1, 1024, 0, st>>>(values, n, member, a, ws, cap);
+    if (vec) qd_hist_kernel<KVM_MEMBER_ALL, true><<<grid, QD_THREADS, 0, st>>>(values, n, member, ws, recs);
+    else qd_hist_kernel<KVM_MEMBER_ALL, false><<<grid, QD_THREADS, 0, st>>>(values, n, member, ws, recs);
+  }
+  qd_resolve_kernel<<<1, 1024, 0, st>>>(ws);
+  qd_collect_kernel<true><<<kvm_grid_for(n, QD_THREADS * 8 * 4, 2), QD_THREADS, 0, st>>>(values, n, recs, ws, lists);
+  qd_rank_kernel<<<nq, 1024, 0, st>>>(ws, lists, results);
+  KVM_CUDA_CHECK(cudaGetLastError());
+  return KVM_OK;
+}

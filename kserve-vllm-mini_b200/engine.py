@@ -536,11 +536,14 @@ class ColumnOps:
                 or any(q[0] != 1 or q[1] not in self._P_KINDS for q in queries)
                 or len({0.5 if q[1] == N.RANK_UPPER_MEDIAN else q[2] for q in queries}) > 4):
             return None
-        need = int(self.lib.kvm_column_select_sampled_workspace_bytes(n))
+        digit = self.sampled_plan == "digit"
+        fn = self.lib.kvm_column_select_digit if digit else self.lib.kvm_column_select_sampled
+        need = int((self.lib.kvm_column_select_digit_workspace_bytes if digit
+                    else self.lib.kvm_column_select_sampled_workspace_bytes)(n))
         if getattr(self, "_qs_ws", None) is None or self._qs_ws.numel() < need:
             self._qs_ws = torch.empty(need, dtype=torch.uint8, device=self.device)
         ws = self._qs_ws
-        rc = self.lib.kvm_column_select_sampled(values.data_ptr(), n, member_mode,
+        rc = fn(values.data_ptr(), n, member_mode,
                                                 member.data_ptr() if member is not None else None, arr, nq,
                                                 self._res_d.data_ptr(), ws.data_ptr(), ws.numel(), st)
         if rc == N.KVM_ERR_UNSUPPORTED:
@@ -555,6 +558,8 @@ class ColumnOps:
             return None    # bracket verification failed / overflow: the general select decides
         self.last_path = "sampled"
         return np.frombuffer(out, dtype=RESULT_DTYPE, count=nq).copy()
+
+    sampled_plan = "digit"   # "digit": kvm_column_select_digit, "bracket": kvm_column_select_sampled
 
     def order_stats(self, values: torch.Tensor, queries: Sequence[Tuple[int, int, float, int]],
                     member_mode: int = N.MEMBER_ALL, member: Optional[torch.Tensor] = None,

@@ -383,11 +383,13 @@ def _ref_stat(vals, kind, p):
 
 @pytest.mark.parametrize("shape", ["lognormal", "sorted", "reversed", "periodic", "rounded", "two_values", "few_members"])
 @pytest.mark.parametrize("n", [1 << 18, 1_000_003, 5_000_000])
-def test_sampled_select_is_exact_or_declines(shape, n):
+@pytest.mark.parametrize("plan", ["digit", "bracket"])
+def test_sampled_select_is_exact_or_declines(shape, n, plan):
     import torch
     from kvmini_b200 import _native as N
     from kvmini_b200 import engine
     ops = engine.ColumnOps()
+    ops.sampled_plan = plan
     rng = np.random.default_rng(n % 1000 + len(shape))
     lat = rng.lognormal(5.5, 0.6, n)
     if shape == "sorted":
@@ -418,11 +420,13 @@ def test_sampled_select_is_exact_or_declines(shape, n):
     assert ops.last_path == "general" and np.array_equal(got["value"], ref["value"]) and np.array_equal(got["rank"], ref["rank"])
 
 
-def test_sampled_select_edges():
+@pytest.mark.parametrize("plan", ["digit", "bracket"])
+def test_sampled_select_edges(plan):
     import torch
     from kvmini_b200 import _native as N
     from kvmini_b200 import engine
     ops = engine.ColumnOps()
+    ops.sampled_plan = plan
     n = 1 << 20
     rng = np.random.default_rng(77)
     lat = rng.normal(0.0, 50.0, n)                     # mixed signs
