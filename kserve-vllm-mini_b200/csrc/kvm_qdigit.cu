@@ -2,8 +2,8 @@
 // percentile path; analyze.py:59-81).
 //
 //   sample   4096 stratified pseudo-random members give an ESTIMATE of the key range (one CTA)
-//   hist     ONE pass over the data (16 B/record): 12-bit digit of every member key relative to
-//            the estimated range (bins 0 and 4095 catch what lies outside it), histogram in
+//   hist     ONE pass over the data (16 B/record): 13-bit digit of every member key relative to
+//            the estimated range (bins 0 and 8191 catch what lies far outside it), histogram in
 //            shared memory, and the digit written as a 2-byte record (0xFFFF = not a member)
 //   resolve  one CTA: exact member count = sum of the histogram, rank of every query, the bin
 //            holding it and the residual rank
@@ -14,6 +14,8 @@
 // general select) when a rank falls into a catch-all bin (the sample missed the range), when a
 // list overflows (heavy duplicates) or when the sample holds too few members.
 
+#include <cstddef>
+
 #include "kvm_common.cuh"
 #include "kvm_log_device.cuh"
 
@@ -21,10 +23,12 @@ namespace {
 
 constexpr int QD_MAXQ = 8;
 constexpr int QD_SAMPLE = 4096;
-constexpr int QD_BINS = 4096;
+constexpr int QD_BINS = 8192;
+constexpr int QD_SPAN_BITS = 12;   // the widened sample range spans at most 4096 bins; the rest lies beyond it
 constexpr int QD_THREADS = 512;
 constexpr int QD_SMALL = 4096;     // keys ranked by counting at the very end
-constexpr int QD_STAGE = 512;      // keys a CTA stages per wanted bin before going to global memory
+constexpr int QD_QUEUE = 2048;     // wanted rows a CTA queues for the drain after its streaming loop
+constexpr int QD_STAGE = 384;      // keys a CTA stages per wanted bin before going to global memory
 constexpr uint64_t QD_NONE = ~0ull;
 
 struct QdQuery {
@@ -38,17 +42,22 @@ struct QdQuery {
 struct QdWs {
   int32_t status;
   int32_t nq, nslots, pad;
-  uint64_t base;        // digit = key < base ? 0 : min(1 + ((key - base) >> shift), 4095)
+  uint64_t base;        // digit = key < base ? 0 : min(1 + ((key - base) >> shift), 8191)
   int32_t shift, pad2;
   long long list_cap;   // keys per slot list
   QdQuery q[QD_MAXQ];
   int32_t slot_bin[QD_MAXQ];
+  // ---- cleared by one memset before every call (QD_CLEAR_* below)
+  unsigned long long s_inv_min, s_max;   // sample extremes (the minimum travels complemented)
+  unsigned int s_count, s_ticket;
   unsigned long long list_n[QD_MAXQ];
   unsigned long long hist[QD_BINS];
+  // ----
   uint64_t small[QD_MAXQ][QD_SMALL];
 };
 
 constexpr size_t QD_HEADER = (sizeof(QdWs) + 255) / 256 * 256;
+constexpr size_t QD_CLEAR_BEGIN = offsetof(QdWs, s_inv_min), QD_CLEAR_END = offsetof(QdWs, small);
 
 struct QdArgs {
   int32_t nq;
@@ -78,64 +87,58 @@ __device__ __forceinline__ bool qd_member(const void* member, int64_t i) {
 }
 
 // ------------------------------------------------------------------ sample
+// 16 CTAs x 256 threads, one sample each (one CTA would serialise 4096 random DRAM accesses);
+// the last CTA to finish turns the sample's extremes into the digit parameters.  The words the
+// CTAs accumulate into are cleared by the host-side memset in front of the launch.
+constexpr int QD_SAMPLE_CTAS = 16;
+
 template <int MODE>
-__global__ void __launch_bounds__(1024, 1)
+__global__ void __launch_bounds__(QD_SAMPLE / QD_SAMPLE_CTAS)
 qd_sample_kernel(const double* __restrict__ values, int64_t n, const void* __restrict__ member, QdArgs a,
                  QdWs* ws, long long list_cap) {
-  __shared__ uint64_t wmin[32], wmax[32];
-  __shared__ int cnt_s;
+  __shared__ bool is_last;
   const int t = threadIdx.x;
-  for (int i = t; i < QD_BINS; i += 1024) ws->hist[i] = 0;
-  if (t < QD_MAXQ) ws->list_n[t] = 0;
-  if (t == 0) cnt_s = 0;
-  __syncthreads();
+  const int s = blockIdx.x * blockDim.x + t;
   const int64_t width = n / QD_SAMPLE;
-  uint64_t mn = QD_NONE, mx = 0;
-  int cnt = 0;
-#pragma unroll
-  for (int k = 0; k < QD_SAMPLE / 1024; ++k) {
-    const int s = t + 1024 * k;
-    const int64_t i = (int64_t)s * width + (int64_t)(qd_hash((uint32_t)s * 2654435761u + 12345u) % (uint64_t)width);
-    const double v = values[i];
-    if (qd_member<MODE>(member, i) && v == v) {
-      const uint64_t key = kvm_key(v);
-      mn = key < mn ? key : mn;
-      mx = key > mx ? key : mx;
-      ++cnt;
-    }
-  }
+  const int64_t i = (int64_t)s * width + (int64_t)(qd_hash((uint32_t)s * 2654435761u + 12345u) % (uint64_t)width);
+  const double v = values[i];
+  const bool mem = qd_member<MODE>(member, i) && v == v;
+  uint64_t mx = mem ? kvm_key(v) : 0ull, inv_mn = mem ? ~kvm_key(v) : 0ull;
+  int cnt = mem;
 #pragma unroll
   for (int o = 16; o; o >>= 1) {
-    const uint64_t a0 = __shfl_xor_sync(KVM_FULL, mn, o), a1 = __shfl_xor_sync(KVM_FULL, mx, o);
-    mn = a0 < mn ? a0 : mn;
+    const uint64_t a0 = __shfl_xor_sync(KVM_FULL, inv_mn, o), a1 = __shfl_xor_sync(KVM_FULL, mx, o);
+    inv_mn = a0 > inv_mn ? a0 : inv_mn;
     mx = a1 > mx ? a1 : mx;
     cnt += __shfl_xor_sync(KVM_FULL, cnt, o);
   }
-  if ((t & 31) == 0) {
-    wmin[t >> 5] = mn;
-    wmax[t >> 5] = mx;
-    atomicAdd(&cnt_s, cnt);
+  if ((t & 31) == 0 && cnt) {
+    atomicMax(&ws->s_inv_min, (unsigned long long)inv_mn);
+    atomicMax(&ws->s_max, (unsigned long long)mx);
+    atomicAdd(&ws->s_count, (unsigned int)cnt);
   }
+  __threadfence();
   __syncthreads();
+  if (t == 0) is_last = atomicAdd(&ws->s_ticket, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
   if (t == 0) {
-    for (int w = 1; w < 32; ++w) {
-      mn = wmin[w] < mn ? wmin[w] : mn;
-      mx = wmax[w] > mx ? wmax[w] : mx;
-    }
-    const int m = cnt_s;
+    const uint64_t mn = ~__ldcg(&ws->s_inv_min), mxk = __ldcg(&ws->s_max);
+    const int m = (int)__ldcg(&ws->s_count);
     ws->nq = a.nq;
     ws->list_cap = list_cap;
     if (m < 256) {
       ws->status = KVM_ERR_UNSUPPORTED;  // too few members in the sample to trust its range
     } else {
-      // widen the sampled range by a quarter on both sides (saturating), 2048 in-range bins at most
-      const uint64_t range = mx - mn, margin = (range >> 2) + 1;
+      // widen the sampled range by an eighth on both sides (saturating), 4096 in-range bins at most
+      const uint64_t range = mxk - mn, margin = (range >> 3) + 1;
       const uint64_t lo = mn > margin ? mn - margin : 0ull;
-      const uint64_t hi = mx < QD_NONE - 1 - margin ? mx + margin : QD_NONE - 1;
+      const uint64_t hi = mxk < QD_NONE - 1 - margin ? mxk + margin : QD_NONE - 1;
       const uint64_t r2 = hi - lo;
       const int bits = r2 ? 64 - __clzll((long long)r2) : 0;
       ws->base = lo;
-      ws->shift = bits > 11 ? bits - 11 : 0;
+      ws->shift = bits > QD_SPAN_BITS ? bits - QD_SPAN_BITS : 0;
       ws->status = KVM_OK;
     }
   }
@@ -204,7 +207,7 @@ qd_hist_kernel(const double* __restrict__ values, int64_t n, const void* __restr
 
 // ------------------------------------------------------------------ resolve
 __global__ void __launch_bounds__(1024, 1) qd_resolve_kernel(QdWs* ws) {
-  __shared__ unsigned long long cum[QD_BINS];   // exclusive prefix of the histogram
+  __shared__ uint32_t cum[QD_BINS];   // exclusive prefix of the histogram (n < 2^31 on this path)
   __shared__ unsigned long long wtot[32];
   __shared__ QdQuery qs[QD_MAXQ];
   if (ws->status != KVM_OK) return;
@@ -229,7 +232,7 @@ __global__ void __launch_bounds__(1024, 1) qd_resolve_kernel(QdWs* ws) {
   for (int w = 0; w < warp; ++w) before += wtot[w];
 #pragma unroll
   for (int k = 0; k < PER; ++k) {
-    cum[t * PER + k] = before;
+    cum[t * PER + k] = (uint32_t)before;
     before += c[k];
   }
   __syncthreads();
@@ -253,7 +256,7 @@ __global__ void __launch_bounds__(1024, 1) qd_resolve_kernel(QdWs* ws) {
         int lo = 0, hi = QD_BINS - 1;   // last bin whose exclusive prefix is <= rank
         while (lo < hi) {
           const int mid = (lo + hi + 1) >> 1;
-          if (cum[mid] <= (unsigned long long)s.rank) lo = mid;
+          if ((long long)cum[mid] <= s.rank) lo = mid;
           else hi = mid - 1;
         }
         s.bin = lo;
@@ -297,6 +300,9 @@ qd_collect_kernel(const double* __restrict__ values, int64_t n, const uint16_t* 
   __shared__ uint64_t stage[QD_MAXQ][QD_STAGE];
   __shared__ uint32_t stage_n[QD_MAXQ];
   __shared__ unsigned long long stage_pos[QD_MAXQ];
+  __shared__ uint32_t bitmap[2048];
+  __shared__ uint32_t queue[QD_QUEUE];
+  __shared__ uint32_t queue_n;
   if (ws->status != KVM_OK) return;
   const int nslots = ws->nslots;
   const long long cap = ws->list_cap;
@@ -304,8 +310,20 @@ qd_collect_kernel(const double* __restrict__ values, int64_t n, const uint16_t* 
 #pragma unroll
   for (int k = 0; k < QD_MAXQ; ++k) want[k] = k < nslots ? (uint32_t)ws->slot_bin[k] : 0xFFFFFFFFu;
   if (threadIdx.x < QD_MAXQ) stage_n[threadIdx.x] = 0;
+  if (threadIdx.x == 0) queue_n = 0;
+  for (int i = threadIdx.x; i < 2048; i += QD_THREADS) bitmap[i] = 0;
   __syncthreads();
+  if (threadIdx.x < nslots) atomicOr(&bitmap[want[threadIdx.x] >> 5], 1u << (want[threadIdx.x] & 31));
+  __syncthreads();
+  // a wanted record only queues its row index: the value fetch (a random access) happens after
+  // the streaming loop, all lanes at once, instead of stalling the warp in the middle of it
   auto hit = [&](int64_t i, uint32_t d) {
+    const uint32_t qp = atomicAdd(&queue_n, 1u);
+    if (qp < (uint32_t)QD_QUEUE) {
+      queue[qp] = (uint32_t)i;   // n < 2^31 on this path
+      return;
+    }
+    // queue full (tens of thousands of wanted records in one CTA): handle it in place
 #pragma unroll
     for (int k = 0; k < QD_MAXQ; ++k)
       if (d == want[k]) {
@@ -319,33 +337,71 @@ qd_collect_kernel(const double* __restrict__ values, int64_t n, const uint16_t* 
         }
       }
   };
-  auto maybe = [&](int64_t i, uint32_t d) {
-    bool any = false;
+  // one bit per possible record value (65536 bits, 8 KB): a record costs a shift, a shared-memory
+  // load and a mask; the per-record path runs only for wanted digits (~0.1 % of the records)
+  // register filter first: bit g of `coarse` = some wanted bin lies in digits [128 g, 128 g + 128);
+  // ~5 % of the records pass it and go on to the exact bitmap
+  unsigned long long coarse = 0;
 #pragma unroll
-    for (int k = 0; k < QD_MAXQ; ++k) any |= d == want[k];
-    if (any) hit(i, d);
+  for (int k = 0; k < QD_MAXQ; ++k)
+    if (k < nslots) coarse |= 1ull << (want[k] >> 7);
+  auto word = [&](int64_t i, uint32_t w) {
+    const uint32_t d0 = w & 0xFFFFu, d1 = w >> 16;
+    if (d0 < (uint32_t)QD_BINS && ((coarse >> (d0 >> 7)) & 1ull) && ((bitmap[d0 >> 5] >> (d0 & 31)) & 1u)) hit(i, d0);
+    if (d1 < (uint32_t)QD_BINS && ((coarse >> (d1 >> 7)) & 1ull) && ((bitmap[d1 >> 5] >> (d1 & 31)) & 1u)) hit(i + 1, d1);
   };
   if (VEC) {
     const int64_t noct = n >> 3;
-    for (int64_t o = (int64_t)blockIdx.x * QD_THREADS + threadIdx.x; o < noct; o += (int64_t)gridDim.x * QD_THREADS) {
-      const uint4 r = __ldg(reinterpret_cast<const uint4*>(recs) + o);
-      const int64_t i = o << 3;
-      maybe(i + 0, r.x & 0xFFFFu);
-      maybe(i + 1, r.x >> 16);
-      maybe(i + 2, r.y & 0xFFFFu);
-      maybe(i + 3, r.y >> 16);
-      maybe(i + 4, r.z & 0xFFFFu);
-      maybe(i + 5, r.z >> 16);
-      maybe(i + 6, r.w & 0xFFFFu);
-      maybe(i + 7, r.w >> 16);
+    // 32 contiguous bytes (16 records) per thread and iteration, two loads in flight
+    const int64_t npair = noct >> 1;
+    const uint4* __restrict__ r16 = reinterpret_cast<const uint4*>(recs);
+    for (int64_t o = (int64_t)blockIdx.x * QD_THREADS + threadIdx.x; o < npair; o += (int64_t)gridDim.x * QD_THREADS) {
+      const uint4 r0 = __ldg(r16 + 2 * o), r1 = __ldg(r16 + 2 * o + 1);
+      const int64_t i = o << 4;
+      word(i, r0.x);
+      word(i + 2, r0.y);
+      word(i + 4, r0.z);
+      word(i + 6, r0.w);
+      word(i + 8, r1.x);
+      word(i + 10, r1.y);
+      word(i + 12, r1.z);
+      word(i + 14, r1.w);
+    }
+    if ((noct & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
+      const uint4 r0 = __ldg(r16 + noct - 1);
+      const int64_t i = (noct - 1) << 3;
+      word(i, r0.x);
+      word(i + 2, r0.y);
+      word(i + 4, r0.z);
+      word(i + 6, r0.w);
     }
     if (blockIdx.x == 0 && threadIdx.x < (n & 7)) {
       const int64_t i = (n & ~7ll) + threadIdx.x;
-      maybe(i, recs[i]);
+      word(i, (uint32_t)recs[i] | 0xFFFF0000u);   // upper half: "not a member"
     }
   } else {
     for (int64_t i = (int64_t)blockIdx.x * QD_THREADS + threadIdx.x; i < n; i += (int64_t)gridDim.x * QD_THREADS)
-      maybe(i, recs[i]);
+      word(i, (uint32_t)recs[i] | 0xFFFF0000u);
+  }
+  __syncthreads();
+  {  // drain the queue: every thread takes queued rows, fetches the value, appends the key
+    const uint32_t qn = queue_n < (uint32_t)QD_QUEUE ? queue_n : (uint32_t)QD_QUEUE;
+    for (uint32_t j = threadIdx.x; j < qn; j += QD_THREADS) {
+      const int64_t i = (int64_t)queue[j];
+      const uint32_t d = recs[i];
+      const uint64_t key = kvm_key(values[i]);
+#pragma unroll
+      for (int k = 0; k < QD_MAXQ; ++k)
+        if (d == want[k]) {
+          const uint32_t sp = atomicAdd(&stage_n[k], 1u);
+          if (sp < (uint32_t)QD_STAGE) {
+            stage[k][sp] = key;
+          } else {
+            const unsigned long long pos = atomicAdd(&ws->list_n[k], 1ull);
+            if (pos < (unsigned long long)cap) lists[(size_t)k * (size_t)cap + pos] = key;
+          }
+        }
+    }
   }
   __syncthreads();
   if (threadIdx.x < QD_MAXQ) {
@@ -393,36 +449,24 @@ qd_rank_kernel(QdWs* ws, const uint64_t* __restrict__ lists, kvm_query_result* _
   }
   const uint64_t* __restrict__ keys = lists + (size_t)s.slot * (size_t)cap;
   uint64_t* small = ws->small[q];
-  uint64_t mn = QD_NONE, mx = 0;
-  for (unsigned long long i = t; i < m; i += 1024) {
-    const uint64_t k = keys[i];
-    mn = k < mn ? k : mn;
-    mx = k > mx ? k : mx;
-  }
-#pragma unroll
-  for (int o = 16; o; o >>= 1) {
-    const uint64_t a0 = __shfl_xor_sync(KVM_FULL, mn, o), a1 = __shfl_xor_sync(KVM_FULL, mx, o);
-    mn = a0 < mn ? a0 : mn;
-    mx = a1 > mx ? a1 : mx;
-  }
-  if (lane == 0) {
-    wmin[warp] = mn;
-    wmax[warp] = mx;
-  }
+  // the keys of bin d lie in [base + (d-1) << shift, base + d << shift): no min/max pass needed
+  (void)wmin;
+  (void)wmax;
   hist[t] = 0;
   hist[t + 1024] = 0;
   if (t == 0) small_n = 0;
+  const int bshift = ws->shift;
+  const uint64_t mn = ws->base + ((uint64_t)(s.bin - 1) << bshift);
+  const int sh2 = bshift > 11 ? bshift - 11 : 0;
   __syncthreads();
-  mn = wmin[0];
-  mx = wmax[0];
-  for (int w = 1; w < 32; ++w) {
-    mn = wmin[w] < mn ? wmin[w] : mn;
-    mx = wmax[w] > mx ? wmax[w] : mx;
+  for (unsigned long long i0 = t; i0 < m; i0 += 4 * 1024) {
+    uint64_t kk[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) kk[u] = i0 + u * 1024 < m ? keys[i0 + u * 1024] : QD_NONE;
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (kk[u] != QD_NONE) atomicAdd(&hist[(uint32_t)((kk[u] - mn) >> sh2) & 2047u], 1u);
   }
-  const uint64_t range = mx - mn;
-  const int bits = range ? 64 - __clzll((long long)range) : 0;
-  const int sh2 = bits > 11 ? bits - 11 : 0;
-  for (unsigned long long i = t; i < m; i += 1024) atomicAdd(&hist[(uint32_t)((keys[i] - mn) >> sh2)], 1u);
   __syncthreads();
   {
     const uint32_t c0 = hist[2 * t], c1 = hist[2 * t + 1];
@@ -447,12 +491,16 @@ qd_rank_kernel(QdWs* ws, const uint64_t* __restrict__ lists, kvm_query_result* _
   }
   __syncthreads();
   const uint32_t sb = sel_bin, sr = sel_resid;
-  for (unsigned long long i = t; i < m; i += 1024) {
-    const uint64_t k = keys[i];
-    if ((uint32_t)((k - mn) >> sh2) == sb) {
-      const uint32_t pos = atomicAdd(&small_n, 1u);
-      if (pos < (uint32_t)QD_SMALL) small[pos] = k;
-    }
+  for (unsigned long long i0 = t; i0 < m; i0 += 4 * 1024) {
+    uint64_t kk[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) kk[u] = i0 + u * 1024 < m ? keys[i0 + u * 1024] : QD_NONE;
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (kk[u] != QD_NONE && ((uint32_t)((kk[u] - mn) >> sh2) & 2047u) == sb) {
+        const uint32_t pos = atomicAdd(&small_n, 1u);
+        if (pos < (uint32_t)QD_SMALL) small[pos] = kk[u];
+      }
   }
   __syncthreads();
   const uint32_t m2 = small_n;
@@ -526,12 +574,14 @@ extern "C" int kvm_column_select_digit(const double* values, int64_t n, int32_t 
   const int grid = qd_grid(n);
   const bool vec = (reinterpret_cast<uintptr_t>(values) & 15u) == 0 &&
                    (mode != KVM_MEMBER_STATUS || (reinterpret_cast<uintptr_t>(member) & 15u) == 0);
+  KVM_CUDA_CHECK(cudaMemsetAsync(wsb + QD_CLEAR_BEGIN, 0, QD_CLEAR_END - QD_CLEAR_BEGIN, st));
+  constexpr int STH = QD_SAMPLE / QD_SAMPLE_CTAS;
   if (mode == KVM_MEMBER_STATUS) {
-    qd_sample_kernel<KVM_MEMBER_STATUS><<<1, 1024, 0, st>>>(values, n, member, a, ws, cap);
+    qd_sample_kernel<KVM_MEMBER_STATUS><<<QD_SAMPLE_CTAS, STH, 0, st>>>(values, n, member, a, ws, cap);
     if (vec) qd_hist_kernel<KVM_MEMBER_STATUS, true><<<grid, QD_THREADS, 0, st>>>(values, n, member, ws, recs);
     else qd_hist_kernel<KVM_MEMBER_STATUS, false><<<grid, QD_THREADS, 0, st>>>(values, n, member, ws, recs);
   } else {
-    qd_sample_kernel<KVM_MEMBER_ALL><<<1, 1024, 0, st>>>(values, n, member, a, ws, cap);
+    qd_sample_kernel<KVM_MEMBER_ALL><<<QD_SAMPLE_CTAS, STH, 0, st>>>(values, n, member, a, ws, cap);
     if (vec) qd_hist_kernel<KVM_MEMBER_ALL, true><<<grid, QD_THREADS, 0, st>>>(values, n, member, ws, recs);
     else qd_hist_kernel<KVM_MEMBER_ALL, false><<<grid, QD_THREADS, 0, st>>>(values, n, member, ws, recs);
   }
