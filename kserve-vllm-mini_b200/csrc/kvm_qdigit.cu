@@ -300,7 +300,6 @@ qd_collect_kernel(const double* __restrict__ values, int64_t n, const uint16_t* 
   __shared__ uint64_t stage[QD_MAXQ][QD_STAGE];
   __shared__ uint32_t stage_n[QD_MAXQ];
   __shared__ unsigned long long stage_pos[QD_MAXQ];
-  __shared__ uint32_t bitmap[2048];
   __shared__ uint32_t queue[QD_QUEUE];
   __shared__ uint32_t queue_n;
   if (ws->status != KVM_OK) return;
@@ -311,9 +310,6 @@ qd_collect_kernel(const double* __restrict__ values, int64_t n, const uint16_t* 
   for (int k = 0; k < QD_MAXQ; ++k) want[k] = k < nslots ? (uint32_t)ws->slot_bin[k] : 0xFFFFFFFFu;
   if (threadIdx.x < QD_MAXQ) stage_n[threadIdx.x] = 0;
   if (threadIdx.x == 0) queue_n = 0;
-  for (int i = threadIdx.x; i < 2048; i += QD_THREADS) bitmap[i] = 0;
-  __syncthreads();
-  if (threadIdx.x < nslots) atomicOr(&bitmap[want[threadIdx.x] >> 5], 1u << (want[threadIdx.x] & 31));
   __syncthreads();
   // a wanted record only queues its row index: the value fetch (a random access) happens after
   // the streaming loop, all lanes at once, instead of stalling the warp in the middle of it
@@ -337,18 +333,36 @@ qd_collect_kernel(const double* __restrict__ values, int64_t n, const uint16_t* 
         }
       }
   };
-  // one bit per possible record value (65536 bits, 8 KB): a record costs a shift, a shared-memory
-  // load and a mask; the per-record path runs only for wanted digits (~0.1 % of the records)
-  // register filter first: bit g of `coarse` = some wanted bin lies in digits [128 g, 128 g + 128);
-  // ~5 % of the records pass it and go on to the exact bitmap
-  unsigned long long coarse = 0;
+  // branch-free membership test in registers: a record's digit is compared with the wanted bins
+  // (4 of them when that is all there are - the usual case: three percentiles whose lo and hi
+  // ranks share a bin); only a real hit leaves the straight-line code
+  // both 16-bit records of a word are tested at once: x = w ^ (bin | bin << 16) has a zero half
+  // where a record equals the bin, and (x - 0x00010001) & ~x & 0x80008000 flags zero halves (a
+  // borrow can only raise a false flag above a true one; the hit path re-checks exactly)
+  const bool few = nslots <= 4;
+  uint32_t want2[QD_MAXQ];
 #pragma unroll
-  for (int k = 0; k < QD_MAXQ; ++k)
-    if (k < nslots) coarse |= 1ull << (want[k] >> 7);
+  for (int k = 0; k < QD_MAXQ; ++k) want2[k] = k < nslots ? (want[k] & 0xFFFFu) * 0x00010001u : 0xFFFEFFFEu;  // 0xFFFE: no record has it
   auto word = [&](int64_t i, uint32_t w) {
-    const uint32_t d0 = w & 0xFFFFu, d1 = w >> 16;
-    if (d0 < (uint32_t)QD_BINS && ((coarse >> (d0 >> 7)) & 1ull) && ((bitmap[d0 >> 5] >> (d0 & 31)) & 1u)) hit(i, d0);
-    if (d1 < (uint32_t)QD_BINS && ((coarse >> (d1 >> 7)) & 1ull) && ((bitmap[d1 >> 5] >> (d1 & 31)) & 1u)) hit(i + 1, d1);
+    uint32_t z = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const uint32_t x = w ^ want2[k];
+      z |= (x - 0x00010001u) & ~x;
+    }
+    if (!few) {
+#pragma unroll
+      for (int k = 4; k < QD_MAXQ; ++k) {
+        const uint32_t x = w ^ want2[k];
+        z |= (x - 0x00010001u) & ~x;
+      }
+    }
+    z &= 0x80008000u;
+    if (z) {
+      const uint32_t d0 = w & 0xFFFFu, d1 = w >> 16;
+      if ((z & 0x8000u) && d0 != 0xFFFFu) hit(i, d0);
+      if ((z >> 16) && d1 != 0xFFFFu) hit(i + 1, d1);
+    }
   };
   if (VEC) {
     const int64_t noct = n >> 3;
@@ -459,12 +473,12 @@ qd_rank_kernel(QdWs* ws, const uint64_t* __restrict__ lists, kvm_query_result* _
   const uint64_t mn = ws->base + ((uint64_t)(s.bin - 1) << bshift);
   const int sh2 = bshift > 11 ? bshift - 11 : 0;
   __syncthreads();
-  for (unsigned long long i0 = t; i0 < m; i0 += 4 * 1024) {
-    uint64_t kk[4];
+  for (unsigned long long i0 = t; i0 < m; i0 += 8 * 1024) {
+    uint64_t kk[8];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) kk[u] = i0 + u * 1024 < m ? keys[i0 + u * 1024] : QD_NONE;
+    for (int u = 0; u < 8; ++u) kk[u] = i0 + u * 1024 < m ? __ldcg(keys + i0 + u * 1024) : QD_NONE;
 #pragma unroll
-    for (int u = 0; u < 4; ++u)
+    for (int u = 0; u < 8; ++u)
       if (kk[u] != QD_NONE) atomicAdd(&hist[(uint32_t)((kk[u] - mn) >> sh2) & 2047u], 1u);
   }
   __syncthreads();
@@ -491,12 +505,12 @@ qd_rank_kernel(QdWs* ws, const uint64_t* __restrict__ lists, kvm_query_result* _
   }
   __syncthreads();
   const uint32_t sb = sel_bin, sr = sel_resid;
-  for (unsigned long long i0 = t; i0 < m; i0 += 4 * 1024) {
-    uint64_t kk[4];
+  for (unsigned long long i0 = t; i0 < m; i0 += 8 * 1024) {
+    uint64_t kk[8];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) kk[u] = i0 + u * 1024 < m ? keys[i0 + u * 1024] : QD_NONE;
+    for (int u = 0; u < 8; ++u) kk[u] = i0 + u * 1024 < m ? __ldcg(keys + i0 + u * 1024) : QD_NONE;
 #pragma unroll
-    for (int u = 0; u < 4; ++u)
+    for (int u = 0; u < 8; ++u)
       if (kk[u] != QD_NONE && ((uint32_t)((kk[u] - mn) >> sh2) & 2047u) == sb) {
         const uint32_t pos = atomicAdd(&small_n, 1u);
         if (pos < (uint32_t)QD_SMALL) small[pos] = kk[u];

@@ -563,10 +563,11 @@ class ColumnOps:
 
     def order_stats(self, values: torch.Tensor, queries: Sequence[Tuple[int, int, float, int]],
                     member_mode: int = N.MEMBER_ALL, member: Optional[torch.Tensor] = None,
-                    nsets: int = 1, sampled: bool = False) -> np.ndarray:
+                    nsets: int = 1, sampled: bool = True) -> np.ndarray:
         """queries: (set_mask, rank_kind, p, rank).  Returns structured array of results.
-        Workspace and read-back buffers are cached; one synchronisation per call.  sampled=True tries the
-        one-pass sampled select first (exact or it declines; see csrc/kvm_quantile.cu)."""
+        Workspace and read-back buffers are cached; one synchronisation per call.  Few quantiles of one
+        multiset go through the sampled-range digit select first (csrc/kvm_qdigit.cu: exact, or it
+        declines and the general select below runs)."""
         assert values.dtype == torch.float64 and values.is_contiguous()
         n = int(values.shape[0])
         nq = len(queries)
