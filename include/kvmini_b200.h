@@ -231,26 +231,20 @@ int kvm_column_select(const double* values, int64_t n, int32_t member_mode, cons
                       kvm_query_result* results, void* workspace, size_t workspace_bytes,
                       int64_t arena_capacity, void* stream);
 
-/* One-pass form of kvm_column_select for a few quantiles of ONE multiset (member mode ALL or
- * STATUS, up to 8 queries of rank kinds that carry a p, at most 4 distinct p, 2^18 <= n < 2^31):
- * a 4096-element stratified sample brackets every quantile, one 16 B/record pass counts exactly
- * what lies below / inside each bracket and keeps the inside keys, two small kernels finish.
- * Exact whenever it answers - the bracket is verified with the exact counts; otherwise (heavy
- * duplicates, adversarial order, too few members) the status word - the first int32 of the
- * workspace, stream-ordered - is KVM_ERR_UNSUPPORTED and the caller runs kvm_column_select.
- * A host-side refusal (arguments outside the envelope) returns KVM_ERR_UNSUPPORTED at once.
- * Replaces analyze.py:59-81 for the percentile path of SURVEY.md section 8d. */
+/* Fast form of kvm_column_select for a few quantiles of ONE multiset (member mode ALL or STATUS,
+ * up to 8 queries of rank kinds that carry a p, 2^18 <= n < 2^31): the 16 B/record percentile
+ * path of SURVEY.md section 8d in one pass and an eighth.  A 4096-element stratified sample
+ * estimates the key range; ONE pass over the data histograms 13-bit digits relative to it and
+ * writes them as 2-byte records; a pass over those records fetches the ~0.1 % of values whose
+ * digit holds a requested rank; one CTA per query ranks them.  Exact whenever it answers;
+ * otherwise (a rank falls outside the sampled range, heavy duplicates, too few members) the
+ * status word - the first int32 of the workspace, stream-ordered - is KVM_ERR_UNSUPPORTED and
+ * the caller runs kvm_column_select.  Arguments outside the envelope are refused on the host
+ * with KVM_ERR_UNSUPPORTED.  Replaces analyze.py:59-81. */
 int kvm_column_select_sampled(const double* values, int64_t n, int32_t member_mode, const void* member,
                               const kvm_query* queries_host, int32_t nq, kvm_query_result* results,
                               void* workspace, size_t workspace_bytes, void* stream);
 size_t kvm_column_select_sampled_workspace_bytes(int64_t n);
-/* Same contract (exact or declines through the status word), different plan: the sample only
- * estimates the key RANGE; one light pass histograms 12-bit digits and writes them as 2-byte
- * records, a pass over those records fetches the ~0.1 % of values whose digit holds a rank. */
-int kvm_column_select_digit(const double* values, int64_t n, int32_t member_mode, const void* member,
-                            const kvm_query* queries_host, int32_t nq, kvm_query_result* results,
-                            void* workspace, size_t workspace_bytes, void* stream);
-size_t kvm_column_select_digit_workspace_bytes(int64_t n);
 int64_t kvm_column_select_sampled_min_n(void);
 
 /* No counterpart in the reference.  kvm_column_select for callers that cannot give the

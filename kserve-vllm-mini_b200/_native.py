@@ -116,8 +116,6 @@ def _declare(lib: C.CDLL) -> None:
         "kvm_column_select_sampled": (C.c_int, [vp, i64, i32, vp, P(QueryC), i32, vp, vp, sz, vp]),
         "kvm_column_select_sampled_workspace_bytes": (sz, [i64]),
         "kvm_column_select_sampled_min_n": (i64, []),
-        "kvm_column_select_digit": (C.c_int, [vp, i64, i32, vp, P(QueryC), i32, vp, vp, sz, vp]),
-        "kvm_column_select_digit_workspace_bytes": (sz, [i64]),
         "kvm_column_select_static": (C.c_int, [vp, i64, i32, vp, P(QueryC), i32, vp, vp]),
         "kvm_column_select_static_max_n": (i64, []),
         "kvm_select_status": (C.c_int, [vp, vp]),

@@ -547,19 +547,21 @@ long long qd_list_cap(int64_t n) {
 
 }  // namespace
 
-extern "C" size_t kvm_column_select_digit_workspace_bytes(int64_t n) {
+extern "C" int64_t kvm_column_select_sampled_min_n(void) { return 1 << 18; }
+
+extern "C" size_t kvm_column_select_sampled_workspace_bytes(int64_t n) {
   if (n < 0) n = 0;
   return QD_HEADER + kvm_align_up((size_t)n * sizeof(uint16_t) + 16, 256) +
          (size_t)QD_MAXQ * (size_t)qd_list_cap(n) * sizeof(uint64_t) + 256;
 }
 
-extern "C" int kvm_column_select_digit(const double* values, int64_t n, int32_t mode, const void* member,
+extern "C" int kvm_column_select_sampled(const double* values, int64_t n, int32_t mode, const void* member,
                                        const kvm_query* queries, int32_t nq, kvm_query_result* results,
                                        void* workspace, size_t workspace_bytes, void* stream) {
-  KVM_REQUIRE(values && queries && results && workspace, "kvm_column_select_digit: null argument");
+  KVM_REQUIRE(values && queries && results && workspace, "kvm_column_select_sampled: null argument");
   if (!(mode == KVM_MEMBER_ALL || (mode == KVM_MEMBER_STATUS && member)) || nq < 1 || nq > QD_MAXQ ||
       n < (1 << 18) || n >= (1ll << 31)) {
-    kvm_set_error("kvm_column_select_digit: needs member mode ALL/STATUS, 1..%d queries, 2^18 <= n < 2^31; "
+    kvm_set_error("kvm_column_select_sampled: needs member mode ALL/STATUS, 1..%d queries, 2^18 <= n < 2^31; "
                   "use kvm_column_select", QD_MAXQ);
     return KVM_ERR_UNSUPPORTED;
   }
@@ -568,15 +570,15 @@ extern "C" int kvm_column_select_digit(const double* values, int64_t n, int32_t 
   for (int q = 0; q < nq; ++q) {
     const kvm_query& Q = queries[q];
     if (Q.rank_kind == KVM_RANK_ABSOLUTE || Q.rank_kind < 0 || Q.rank_kind > KVM_RANK_FLOOR_PNM1 || Q.set_mask != 1u) {
-      kvm_set_error("kvm_column_select_digit: query %d is not a quantile of set 0; use kvm_column_select", q);
+      kvm_set_error("kvm_column_select_sampled: query %d is not a quantile of set 0; use kvm_column_select", q);
       return KVM_ERR_UNSUPPORTED;
     }
     a.kind[q] = Q.rank_kind;
     a.p[q] = Q.p;
   }
-  if (workspace_bytes < kvm_column_select_digit_workspace_bytes(n)) {
-    kvm_set_error("kvm_column_select_digit: workspace %zu < %zu bytes", workspace_bytes,
-                  kvm_column_select_digit_workspace_bytes(n));
+  if (workspace_bytes < kvm_column_select_sampled_workspace_bytes(n)) {
+    kvm_set_error("kvm_column_select_sampled: workspace %zu < %zu bytes", workspace_bytes,
+                  kvm_column_select_sampled_workspace_bytes(n));
     return KVM_ERR_WORKSPACE;
   }
   cudaStream_t st = (cudaStream_t)stream;

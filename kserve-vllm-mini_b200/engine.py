@@ -534,12 +534,10 @@ class ColumnOps:
         if (member_mode not in (N.MEMBER_ALL, N.MEMBER_STATUS) or nq > 8 or n >= 1 << 31
                 or n < int(self.lib.kvm_column_select_sampled_min_n())
                 or any(q[0] != 1 or q[1] not in self._P_KINDS for q in queries)
-                or len({0.5 if q[1] == N.RANK_UPPER_MEDIAN else q[2] for q in queries}) > 4):
+                ):
             return None
-        digit = self.sampled_plan == "digit"
-        fn = self.lib.kvm_column_select_digit if digit else self.lib.kvm_column_select_sampled
-        need = int((self.lib.kvm_column_select_digit_workspace_bytes if digit
-                    else self.lib.kvm_column_select_sampled_workspace_bytes)(n))
+        fn = self.lib.kvm_column_select_sampled
+        need = int(self.lib.kvm_column_select_sampled_workspace_bytes(n))
         if getattr(self, "_qs_ws", None) is None or self._qs_ws.numel() < need:
             self._qs_ws = torch.empty(need, dtype=torch.uint8, device=self.device)
         ws = self._qs_ws
@@ -555,11 +553,9 @@ class ColumnOps:
         torch.cuda.current_stream(self.device).synchronize()
         out = self._res_h.numpy().tobytes()
         if int(np.frombuffer(out, dtype=np.int32, count=1, offset=status_off)[0]) != N.KVM_OK:
-            return None    # bracket verification failed / overflow: the general select decides
+            return None    # the sample missed the range / duplicates: the general select decides
         self.last_path = "sampled"
         return np.frombuffer(out, dtype=RESULT_DTYPE, count=nq).copy()
-
-    sampled_plan = "digit"   # "digit": kvm_column_select_digit, "bracket": kvm_column_select_sampled
 
     def order_stats(self, values: torch.Tensor, queries: Sequence[Tuple[int, int, float, int]],
                     member_mode: int = N.MEMBER_ALL, member: Optional[torch.Tensor] = None,

@@ -191,20 +191,13 @@ def percentile(args):
                                               res.data_ptr(), ws_s.data_ptr(), ws_s.numel(),
                                               torch.cuda.current_stream(dev).cuda_stream))
 
-    ws_d = torch.empty(lib.kvm_column_select_digit_workspace_bytes(n), dtype=torch.uint8, device=dev)
-
-    def digit_call():
-        N.check(lib.kvm_column_select_digit(lat.data_ptr(), n, N.MEMBER_STATUS, st.data_ptr(), arr, len(q),
-                                            res.data_ptr(), ws_d.data_ptr(), ws_d.numel(),
-                                            torch.cuda.current_stream(dev).cuda_stream))
-
     def general_call():
         N.check(lib.kvm_column_select(lat.data_ptr(), n, N.MEMBER_STATUS, st.data_ptr(), 1, arr, len(q),
                                       res.data_ptr(), ws_g.data_ptr(), ws_g.numel(), cap,
                                       torch.cuda.current_stream(dev).cuda_stream))
 
     out = {}
-    for name, call, ws in (("digit", digit_call, ws_d), ("bracket", sampled_call, ws_s), ("general", general_call, ws_g)):
+    for name, call, ws in (("sampled", sampled_call, ws_s), ("general", general_call, ws_g)):
         dms, _ = timed(call, warmup=3, steps=50)
         torch.cuda.synchronize()
         declined = int(ws[0:4].view(torch.int32).item()) != 0
