@@ -34,8 +34,10 @@ class SweepAnalyzer:
 
     def analyze(self, dlog: engine.DeviceLog, run_offsets: Sequence[int],
                 cold_times: Optional[Sequence[Sequence[float]]] = None, num_bins: int = 20,
-                quantiles: Sequence[engine.Quantile] = engine.ANALYZE_QUANTILES) -> List[engine.RawAnalysis]:
-        """One RawAnalysis per run (series not computed in sweep mode)."""
+                quantiles: Sequence[engine.Quantile] = engine.ANALYZE_QUANTILES,
+                assemble: bool = True):
+        """One RawAnalysis per run (series not computed in sweep mode).  assemble=False returns the
+        raw per-run arrays (stats as a structured array, results [runs, nq], status) instead."""
         dev, lib = self.device, self.lib
         offs = np.ascontiguousarray(run_offsets, dtype=np.int64)
         runs = int(offs.shape[0]) - 1
@@ -73,6 +75,9 @@ class SweepAnalyzer:
         hist = hist_d.cpu().numpy()
         status = status_d.cpu().numpy()
         self.last_kernel_ms = ev0.elapsed_time(ev1)   # device time of the one segmented launch
+        if not assemble:
+            stats_arr = np.frombuffer(stats_b, dtype=np.dtype(N.LogStatsC), count=runs)
+            return stats_arr, res[:runs], status[:runs]
         out: List[engine.RawAnalysis] = []
         ssz = C.sizeof(N.LogStatsC)
         self.fallback_runs = 0
@@ -87,6 +92,66 @@ class SweepAnalyzer:
                                           hist_counts=hist[r], num_bins=num_bins, series=None,
                                           flags=flags[int(offs[r]):int(offs[r + 1])]))
         return out
+
+    # keys of results.json that grid-sweep.sh:137-160 copies into its CSV and that come from the
+    # request log (cost_* and gpu_util_avg come from cost_estimator / Prometheus)
+    SWEEP_KEYS = ("p50_ms", "p95_ms", "p99_ms", "throughput_rps", "tokens_per_sec", "error_rate",
+                  "ttft_p50_ms", "ttft_p95_ms")
+
+    def sweep_table(self, dlog: engine.DeviceLog, run_offsets: Sequence[int],
+                    cold_times: Optional[Sequence[Sequence[float]]] = None) -> Dict[str, np.ndarray]:
+        """The sweep CSV's log-derived columns for every run as float64 arrays, without building a
+        results dict per run: the same expressions as report.core_results, evaluated over all runs
+        at once (elementwise IEEE operations in the same order -> the same doubles).  Where the
+        reference yields None the value is NaN and `table["is_none"][key]` is True."""
+        quantiles = engine.ANALYZE_QUANTILES
+        raws = self.analyze(dlog, run_offsets, cold_times, assemble=False)
+        stats, res, status = raws
+        runs = int(stats.shape[0])
+        names = [q.name for q in quantiles]
+
+        def interp(name: str, p: float) -> np.ndarray:      # OrderStat.interpolate, vectorised
+            i = names.index(name)
+            n = res[:, 2 * i]["n"].astype(np.int64)
+            vlo, vhi = res[:, 2 * i]["value"], res[:, 2 * i + 1]["value"]
+            pos = max(0.0, min(p, 1.0)) * (n - 1).astype(np.float64)
+            lo, hi = np.floor(pos), np.ceil(pos)
+            with np.errstate(invalid="ignore"):
+                val = np.where(lo == hi, vlo, vlo + (pos - lo) * (vhi - vlo))
+            val = np.where(n == 1, vlo, val)
+            return np.where(n == 0, np.nan, val)
+
+        total, success = stats["n_total"].astype(np.int64), stats["n_success"].astype(np.int64)
+        start, end = stats["min_start_ms"] / 1000.0, stats["max_end_ms"] / 1000.0
+        has_dur = end > start                                # NaN compares False, like the reference's None
+        with np.errstate(invalid="ignore", divide="ignore"):
+            duration = np.where(has_dur, end - start, np.nan)
+            cnt = stats["sets"]["count"]
+            n_ttfb = cnt[:, N.SET_TTFB_COLD] + cnt[:, N.SET_TTFB_WARM]
+            table = {
+                "p50_ms": interp("lat_p50", 0.50), "p95_ms": interp("lat_p95", 0.95), "p99_ms": interp("lat_p99", 0.99),
+                "throughput_rps": np.where(has_dur, success / duration, np.nan),
+                "tokens_per_sec": np.where(has_dur, stats["sum_completion_tokens"].astype(np.float64) / duration, np.nan),
+                "error_rate": np.where(total > 0, (total - success) / np.where(total > 0, total, 1), np.nan),
+                "ttft_p50_ms": np.where(n_ttfb > 0, interp("ttfb_p50", 0.50), np.nan),
+                "ttft_p95_ms": np.where(n_ttfb > 0, interp("ttfb_p95", 0.95), np.nan),
+            }
+        none = {"p50_ms": np.zeros(runs, bool), "p95_ms": np.zeros(runs, bool), "p99_ms": np.zeros(runs, bool),
+                "throughput_rps": ~has_dur, "tokens_per_sec": ~has_dur, "error_rate": total == 0,
+                "ttft_p50_ms": n_ttfb <= 0, "ttft_p95_ms": n_ttfb <= 0}
+        # runs the segmented kernel handed back (they did not fit on chip) go through the flat path
+        self.fallback_runs = 0
+        offs = np.asarray(run_offsets, dtype=np.int64)
+        for r in np.nonzero(status != 0)[0].tolist():
+            cold = cold_times[r] if cold_times is not None else ()
+            core = report.core_results(self._flat_run(dlog, int(offs[r]), int(offs[r + 1]), cold, 20, quantiles),
+                                       len(cold))
+            for k in self.SWEEP_KEYS:
+                none[k][r] = core[k] is None
+                table[k][r] = np.nan if core[k] is None else core[k]
+            self.fallback_runs += 1
+        table["is_none"] = none
+        return table
 
     def _flat_run(self, dlog, r0, r1, cold, num_bins, quantiles) -> engine.RawAnalysis:
         if self._flat is None:

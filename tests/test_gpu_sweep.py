@@ -71,3 +71,37 @@ def test_sweep_concentrated_run_falls_back_to_flat_path():
     cols, offsets, colds = synth.sweep_columns(runs=3, rows_per_run=60_000)
     cols["latency_ms"][60_000:120_000:2] = 30000.0   # run 1: half the latencies identical -> bucket > on-chip arena
     _check(cols, offsets.tolist(), [c.tolist() for c in colds], expect_fallback=True)
+
+
+def test_sweep_table_equals_per_run_rollup():
+    """The vectorised sweep columns (grid-sweep.sh:137-160) are the same doubles as the per-run dicts,
+    including empty runs, all-failure runs, runs without ttfb values and a run on the flat path."""
+    import math
+    import torch
+    from kvmini_b200 import engine, sweep_api, synth
+    rng = np.random.default_rng(8)
+    sizes = [5000, 0, 1, 2, 70_000, 3000, 60_000, 999]
+    cols = synth.request_columns(sum(sizes), seed=41, span_ms=4.0e6)
+    n = sum(sizes)
+    offsets = np.concatenate([[0], np.cumsum(sizes)]).tolist()
+    cols["ttfb_ms"][rng.integers(0, n, n // 40)] = np.nan
+    cols["status"][offsets[5]:offsets[6]] = 500                        # all failures
+    cols["ttfb_ms"][offsets[7]:offsets[8]] = np.nan                    # success rows without ttfb
+    cols["latency_ms"][offsets[6]:offsets[7]:2] = 30000.0              # concentrated -> flat path
+    cols["start_ms"][offsets[2]:offsets[3]] = 1.7e12                   # one row: end > start still holds
+    colds = [[float(cols["start_ms"][offsets[r]]) / 1000.0 + 1.0] if sizes[r] else [] for r in range(len(sizes))]
+    dev = {k: torch.from_numpy(v).cuda() for k, v in cols.items()}
+    dlog = engine.DeviceLog.from_tensors(dev)
+    sw = sweep_api.SweepAnalyzer()
+    per_run = sw.rollup(dlog, offsets, colds)
+    table = sw.sweep_table(dlog, offsets, colds)
+    assert sw.fallback_runs == 1
+    for r in range(len(sizes)):
+        for k in sweep_api.SweepAnalyzer.SWEEP_KEYS:
+            exp, got, none = per_run[r][k], float(table[k][r]), bool(table["is_none"][k][r])
+            if exp is None:
+                assert none and math.isnan(got), (r, k)
+            elif isinstance(exp, float) and math.isnan(exp):
+                assert not none and math.isnan(got), (r, k)
+            else:
+                assert not none and got == exp, (r, k, got, exp)

@@ -83,10 +83,13 @@ def sweep(args):
         lo, hi = r.col_range(0)
         assert lo <= o["lat_p50"].v_lo and o["lat_p99"].v_hi <= hi
         assert int(r.hist_counts[0].sum()) == int(r.stats.sets.count[2] + r.stats.sets.count[3])
-    # device time of the one launch alone
-    flags, stats_d, res_d, hist_d, status_d = sw._last
+    # the sweep CSV's columns for all runs at once (no per-run dicts on the host)
+    ms_tab, table = timed(lambda: sw.sweep_table(dlog, offsets, colds), warmup=1, steps=2)
+    i = runs // 2
+    assert float(table["p95_ms"][i]) == raws[i].order["lat_p95"].interpolate(0.95)
     print(json.dumps({"mode": "sweep", "config": "configs[2]: %d runs x %d rows" % (runs, rows), "rows": n,
                       "ms_per_rollup_incl_host": ms, "records_per_s_incl_host": n / ms * 1e3,
+                      "ms_sweep_table_incl_host": ms_tab, "records_per_s_sweep_table": n / ms_tab * 1e3,
                       "fallback_runs": sw.fallback_runs, "seg_kernel_ms": sw.last_kernel_ms,
                       "records_per_s_kernel": n / sw.last_kernel_ms * 1e3,
                       "algorithmic_bytes": 123.0 * n, "achieved_gbs_kernel": 123.0 * n / sw.last_kernel_ms / 1e6,
