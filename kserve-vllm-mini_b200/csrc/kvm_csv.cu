@@ -549,7 +549,7 @@ extern "C" int kvm_csv_write_classified(const kvm_csv* h, const char* out_path, 
     fwrite(head.data(), 1, head.size(), f);
     const int t = worker_count(threads, rows);
     // bounded memory: blocks of rows are rendered in parallel, then written in order
-    const int64_t block = 1 << 18;
+    const int64_t block = 1 << 15;   // rows per worker and round: small enough that a 1M-row file keeps every core busy
     std::vector<std::string> bufs((size_t)t);
     int irregular = 0;
     for (int64_t b0 = 0; b0 < rows && rc == KVM_OK; b0 += block * t) {
