@@ -160,7 +160,9 @@ def workload_config(args, n_gpus):
                      "summed across ranks, candidates exchanged) + 1s-window series"),
         "rows_per_gpu": args.rows, "rows_total": args.rows * n_gpus,
         "bytes_per_row": ROW_BYTES,
-        "l2": f"inputs ({args.rows * ROW_BYTES / 1e6:.0f} MB per GPU) exceed the 126 MB L2; no flush needed",
+        "l2": (f"inputs ({args.rows * ROW_BYTES / 1e6:.0f} MB per GPU) exceed the 126 MB L2; no flush needed"
+               if args.rows * ROW_BYTES > 126e6 else
+               f"inputs ({args.rows * ROW_BYTES / 1e6:.0f} MB per GPU) FIT in the 126 MB L2: not a valid roofline run"),
         "parallelism": f"time-range shards x{n_gpus}" if n_gpus > 1 else "single GPU",
     }
 
