@@ -13,6 +13,8 @@ Fixtures
   cfg1/                config 1 (500 requests, concurrency 20) + fake-kubectl pod + power.json
                        -> analyze.py, cost_estimator.py, energy/collector.py outputs
   repro100/            repro-smoke.yml:43-88 seeded 100-row CSV -> analyze + cost outputs
+  edge5k/              5000 adversarial rows (ties, nan cells, zero tokens, negative generation, unsorted,
+                       cold starts) -> analyze.py outputs
   costcalc/            cost_calculator.py input text + stdout
 """
 
@@ -260,6 +262,56 @@ def repro100():
     os.rename(os.path.join(d, "requests_classified.csv"), os.path.join(d, "expected_classified.csv"))
 
 
+def edge5k():
+    """5000 rows built to stress what the two small fixtures do not: heavy ties (latencies rounded to
+    whole milliseconds), literal `nan` cells, zero completion tokens, tllt < ttfb (negative
+    generation time), several status codes, rows in file order that is NOT time order, three pods
+    (two started inside the window -> cold starts).  Outputs come from the reference's analyze.py."""
+    d = os.path.join(HERE, "edge5k")
+    fresh(d)
+    rnd = random.Random(20260101)
+    t0 = 1_700_000_000_000.0
+    rows = []
+    for i in range(5000):
+        status = rnd.choices([200, 500, 503, 404], weights=[90, 5, 3, 2])[0]
+        lat = float(round(rnd.lognormvariate(5.5, 0.7)))
+        start = t0 + rnd.uniform(0.0, 600_000.0)
+        ok = status == 200
+        ttfb = round(0.2 * lat + rnd.uniform(0.0, 3.0), 3) if ok else ""
+        tllt = round(0.9 * lat, 3) if ok else ""
+        if ok and i % 97 == 0:
+            ttfb = "nan"
+        if ok and i % 89 == 0:
+            tllt = round(0.1 * lat, 3)              # last token "before" the first one
+        ctok = rnd.randint(0, 40) if ok else ""     # zeros included
+        rows.append([f"r{i}", "%.3f" % start, "%.3f" % start, ttfb, tllt, "%.3f" % lat, status, 12, ctok,
+                     (12 + ctok) if ok else "", "" if ok else "upstream error, code %d" % status, "%032x" % i])
+    with open(os.path.join(d, "requests.csv"), "w", newline="") as f:
+        w = csv.writer(f)
+        w.writerow(["id", "scheduled_ms", "start_ms", "ttfb_ms", "tllt_ms", "latency_ms", "status",
+                    "prompt_tokens", "completion_tokens", "total_tokens", "error", "trace_id"])
+        w.writerows(rows)
+    kube = os.path.join(d, "kube")
+    os.makedirs(kube)
+    import datetime as dt
+
+    def iso(ms):
+        return dt.datetime.fromtimestamp(ms / 1000.0, dt.timezone.utc).strftime("%Y-%m-%dT%H:%M:%SZ")
+    pods = {"items": [{"metadata": {"name": f"demo-llm-predictor-{k}"},
+                       "status": {"containerStatuses": [{"state": {"running": {"startedAt": iso(ms)}}}]}}
+                      for k, ms in enumerate((t0 - 3_600_000.0, t0 + 20_000.0, t0 + 300_000.0))]}
+    synth.write_json(os.path.join(kube, "pods.json"), pods)
+    with open(os.path.join(d, "cost.yaml"), "w") as f:
+        f.write(COST_YAML)
+    env = {"KVM_FAKE_KUBECTL_DIR": kube}
+    common = ["--run-dir", d, "--namespace", "ml-prod", "--service", "demo-llm"]
+    r = run_ref("analyze.py", common, env)
+    assert r.returncode == 0, r.stderr
+    shutil.copy(os.path.join(d, "results.json"), os.path.join(d, "expected_results_analyze.json"))
+    os.remove(os.path.join(d, "results.json"))
+    os.rename(os.path.join(d, "requests_classified.csv"), os.path.join(d, "expected_classified.csv"))
+
+
 def costcalc():
     d = os.path.join(HERE, "costcalc")
     fresh(d)
@@ -284,5 +336,6 @@ if __name__ == "__main__":
     ci5()
     cfg1()
     repro100()
+    edge5k()
     costcalc()
     print("golden fixtures written under", HERE)

@@ -64,6 +64,7 @@ def _cold_from_pods(path):
     ("ci5", "expected_results.json", None),
     ("cfg1", "expected_results_analyze.json", "kube"),
     ("repro100", "expected_results_analyze.json", None),
+    ("edge5k", "expected_results_analyze.json", "kube"),
 ])
 def test_analyze_log_matches_reference(name, expected, kube, analyzer):
     from kvmini_b200 import analyze_api, columns
@@ -71,6 +72,7 @@ def test_analyze_log_matches_reference(name, expected, kube, analyzer):
     exp = load_json(os.path.join(d, expected))
     log = columns.load_requests_csv(os.path.join(d, "requests.csv"))
     cold = _cold_from_pods(os.path.join(d, kube, "pods.json")) if kube else []
+    cold = [c for c in cold if exp["window"]["start"] <= c <= exp["window"]["end"]]   # analyze.py:383-388
     got, _raw = analyze_api.analyze_log(log, cold, analyzer)
     exp_core = {k: v for k, v in exp.items() if k in got}
     assert diff_keys(got, exp_core, rel=MEAN_TOL) == []
@@ -80,6 +82,7 @@ def test_analyze_log_matches_reference(name, expected, kube, analyzer):
     ("ci5", "expected_results.json", None),
     ("cfg1", "expected_results_analyze.json", "kube"),
     ("repro100", "expected_results_analyze.json", None),
+    ("edge5k", "expected_results_analyze.json", "kube"),
 ])
 def test_analyze_cli_drop_in(name, expected, kube, tmp_path):
     """`python analyze.py --run-dir ...` writes the reference's results.json and

@@ -71,6 +71,7 @@ def test_window_bounds_golden(known_answers):
     ("ci5", "expected_results.json", None),
     ("cfg1", "expected_results_analyze.json", "kube"),
     ("repro100", "expected_results_analyze.json", None),
+    ("edge5k", "expected_results_analyze.json", "kube"),
 ])
 def test_analyze_matches_reference_cli(name, expected, cold):
     d = os.path.join(GOLDEN, name)
@@ -84,6 +85,8 @@ def test_analyze_matches_reference_cli(name, expected, cold):
         for p in pods["items"]:
             st = p["status"]["containerStatuses"][0]["state"]["running"]["startedAt"]
             cold_times.append(dt.datetime.fromisoformat(st.replace("Z", "+00:00")).timestamp())
+    # analyze.py:383-388 keeps only the pods started inside the run window
+    cold_times = [c for c in cold_times if exp["window"]["start"] <= c <= exp["window"]["end"]]
     got = py_port.analyze(as_lists(log), cold_times)
     assert diff_keys(got, exp) == []
     got_np = np_port.analyze(log.cols, cold_times)
