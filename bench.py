@@ -117,35 +117,66 @@ def cpu_port_rate(cols, cold, rows, repeats=1):
     return rows / best, best
 
 
+def ref_step(rows_list, cold):
+    """One pass of the UNMODIFIED reference (oracle/_ref/analyze.py + cost_estimator.py functions,
+    driven by oracle/ref_run.py in the order of analyze.main()) on rows already parsed."""
+    from oracle import ref_run
+    t = time.perf_counter()
+    res = ref_run.analyze_rows(rows_list, cold)
+    ref_run.cost_rows(rows_list, 2.0)
+    return time.perf_counter() - t, res
+
+
 def run_reference(args):
-    """--impl reference: the reference's own algorithm (pure-Python port, 1 thread - the
-    reference is single-threaded by construction) on a bounded sample of the same workload."""
+    """--impl reference: the reference's own CPU implementation of the path on the host cores.
+    oracle/_ref/ (the unmodified analyze.py / cost_estimator.py, installed by build()) when it
+    travelled with the repo - kind "reference" - else the pure-Python port - kind "port".  The
+    reference is single-threaded by construction: 1 core.  Each step analyses a bounded sample
+    (`rows_per_step`, stated in config) of the same synthetic log."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     from kvmini_b200 import synth
+    from oracle import ref_run
+    use_ref = ref_run.available() and not args.port
     n = args.rows
-    # calibrate on 20k rows, then size each step for ~120 s total
+    budget_s = 100.0
+
+    def prep(cols, rows):
+        return ref_run.rows_from_columns(cols, rows) if use_ref else cpu_port_lists(cols, rows)
+
+    def one(sub, cold):
+        return ref_step(sub, cold)[0] if use_ref else cpu_port_step(sub, cold)
+
+    # calibrate on 20k rows, then size each step so that the whole run takes ~budget_s
     cal_cols = synth.request_columns(20_000, seed=1234)
     t0 = float(cal_cols["start_ms"].min()) / 1000.0
-    rate, _ = cpu_port_rate(cal_cols, [t0 + 5.0], 20_000)
-    rows = int(min(n, max(10_000, rate * 120.0 / (args.steps + args.warmup))))
+    cal = prep(cal_cols, 20_000)
+    rate = 20_000 / min(one(cal, [t0 + 5.0]) for _ in range(2))
+    rows = int(min(n, max(10_000, rate * budget_s / (args.steps + args.warmup))))
     cols = synth.request_columns(rows, seed=1234, span_ms=3.6e6 * rows / n)
     t0 = float(cols["start_ms"].min()) / 1000.0
     cold = [t0 + 5.0]
-    sub = cpu_port_lists(cols, rows)
+    sub = prep(cols, rows)
     for _ in range(args.warmup):
-        cpu_port_step(sub, cold)
-    dt = sum(cpu_port_step(sub, cold) for _ in range(args.steps))
+        one(sub, cold)
+    dt = sum(one(sub, cold) for _ in range(args.steps))
     value = rows * args.steps / dt
+    cfg = workload_config(args, args.gpus)
+    cfg["rows_per_step"] = rows
+    cfg["note"] = (f"CPU arm: each step analyses a {rows}-row log drawn like the first {rows} rows of the "
+                   f"{n}-row workload (same distribution and request rate); rows_per_gpu names the GPU arm's size")
+    what = ("oracle/_ref/analyze.py (the unmodified reference: window_bounds, classify_requests_cold_warm, "
+            "compute_cold_warm_metrics, compute_token_timing_analysis, percentile) + cost_estimator."
+            "calculate_cold_warm_costs on rows already parsed" if use_ref else
+            "oracle/py_port.analyze (pure-Python restatement of analyze.py + cost rollup)")
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": workload_config(args, args.gpus),
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": 1, "kind": "port",
-                         "sample": f"first {rows} rows of the {n}-row log per step; oracle/py_port.analyze "
-                                   "(pure-Python restatement of analyze.py + cost rollup), single thread"},
+        "config": cfg,
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": 1, "kind": "reference" if use_ref else "port",
+                         "sample": f"{rows} rows per step (of the {n}-row workload); {what}; single thread"},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -165,6 +196,107 @@ def workload_config(args, n_gpus):
                f"inputs ({args.rows * ROW_BYTES / 1e6:.0f} MB per GPU) FIT in the 126 MB L2: not a valid roofline run"),
         "parallelism": f"time-range shards x{n_gpus}" if n_gpus > 1 else "single GPU",
     }
+
+
+# --------------------------------------------------------------------------- parity / extra blocks
+def _same(a, b, rel=None):
+    if isinstance(a, dict) and isinstance(b, dict):
+        return list(a) == list(b) and all(_same(a[k], b[k], rel) for k in a)
+    if isinstance(a, (list, tuple)) and isinstance(b, (list, tuple)):
+        return len(a) == len(b) and all(_same(x, y, rel) for x, y in zip(a, b))
+    if isinstance(a, float) and isinstance(b, float):
+        if math.isnan(a) and math.isnan(b):
+            return True
+        return a == b or (rel is not None and abs(a - b) <= rel * abs(b))
+    return a == b and type(a) is type(b)
+
+
+def parity_block(core, series, host_cols, cold):
+    """The result of the last timed step against the numpy oracle on the same columns (outside
+    every timed region).  Bit-exact on every key except the mean TTFT (<= 1e-12 relative)."""
+    from oracle import np_port
+    t = time.perf_counter()
+    exp = np_port.analyze(host_cols, cold)
+    bad = [k for k in core if k not in exp or not _same(core[k], exp[k], 1e-12 if k == "time_to_first_token_ms" else None)]
+    exp_series = np_port.window_series(host_cols)
+    if not _same(series, exp_series):
+        bad.append("timeseries")
+    return {"oracle": "np_port (numpy restatement of analyze.py, pinned to the reference in tests/test_oracle.py)",
+            "rows": int(len(host_cols["status"])), "keys_compared": len(core) + 1, "equal": not bad,
+            "mismatches": bad[:8], "oracle_seconds": round(time.perf_counter() - t, 2)}
+
+
+def percentile_path_block(device, peak, sizes=(10_000_000, 100_000_000), steps=50):
+    """The 16 B/record percentile path: p50/p95/p99 of the status-200 latencies,
+    kvm_column_select_sampled and - beside it - the general kvm_column_select, each timed as a
+    CUDA-graph replay of its launch sequence with CUDA events, columns resident (160 MB / 1.6 GB:
+    larger than L2).  frac = 16 B x n / time / measured HBM peak.  Results of the two are compared
+    with each other and with a torch.sort of the same column (ranks exact)."""
+    import ctypes as C
+    import numpy as np
+    import torch
+    from kvmini_b200 import _native as N
+    from kvmini_b200 import engine, synth
+    lib = N.lib()
+    out = {}
+    q = [(1, k, p, 0) for p in (0.5, 0.95, 0.99) for k in (N.RANK_LERP_LO, N.RANK_LERP_HI)]
+    arr = (N.QueryC * len(q))(*[N.QueryC(*x) for x in q])
+    for n in sizes:
+        c = synth.request_columns_device(n, device, seed=1234)
+        lat, st = c["latency_ms"], c["status"]
+        del c
+        res = torch.zeros(len(q) * 32, dtype=torch.uint8, device=device)
+        ws_s = torch.empty(lib.kvm_column_select_sampled_workspace_bytes(n), dtype=torch.uint8, device=device)
+        cap = int(lib.kvm_select_default_arena(n))
+        ws_g = torch.empty(lib.kvm_select_workspace_bytes(cap), dtype=torch.uint8, device=device)
+        stream = torch.cuda.Stream(device)
+
+        def sampled():
+            N.check(lib.kvm_column_select_sampled(lat.data_ptr(), n, N.MEMBER_STATUS, st.data_ptr(), arr, len(q),
+                                                  res.data_ptr(), ws_s.data_ptr(), ws_s.numel(),
+                                                  torch.cuda.current_stream(device).cuda_stream))
+
+        def general():
+            N.check(lib.kvm_column_select(lat.data_ptr(), n, N.MEMBER_STATUS, st.data_ptr(), 1, arr, len(q),
+                                          res.data_ptr(), ws_g.data_ptr(), ws_g.numel(), cap,
+                                          torch.cuda.current_stream(device).cuda_stream))
+
+        kept = torch.sort(lat[(st == 200) & ~torch.isnan(lat)]).values
+        m = int(kept.numel())
+        want = []
+        for p in (0.5, 0.95, 0.99):
+            pos = p * (m - 1)
+            want += [float(kept[int(math.floor(pos))]), float(kept[int(math.ceil(pos))])]
+        del kept
+        entry = {"rows": n, "algorithmic_bytes": 16.0 * n}
+        with torch.cuda.stream(stream):
+            for name, call, ws in (("sampled", sampled, ws_s), ("general", general, ws_g)):
+                for _ in range(3):
+                    call()
+                stream.synchronize()
+                if int(ws[0:4].view(torch.int32).item()) != 0:
+                    entry[name] = {"declined": True}
+                    continue
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=stream):
+                    call()
+                for _ in range(3):
+                    g.replay()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(stream)
+                for _ in range(steps):
+                    g.replay()
+                e1.record(stream)
+                stream.synchronize()
+                ms = e0.elapsed_time(e1) / steps
+                got = np.frombuffer(res.cpu().numpy().tobytes(), dtype=engine.RESULT_DTYPE, count=len(q))
+                entry[name] = {"ms": ms, "gbs": 16.0 * n / ms / 1e6, "frac": 16.0 * n / ms / 1e6 / peak,
+                               "equal_to_sorted_ranks": [float(x) for x in got["value"]] == want
+                               and all(int(x) == m for x in got["n"])}
+        out["rows_%g" % n] = entry
+        del lat, st, ws_s, ws_g, res
+        torch.cuda.empty_cache()
+    return out
 
 
 # --------------------------------------------------------------------------- our arm
@@ -350,6 +482,14 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms_total, ms_e2e, ms_eager = float(t[0]), float(t[1]), float(t[2])
 
+    host_all = None
+    if rank == 0 and host is not None and not args.no_parity:
+        # the whole (sharded) log on the host of rank 0: every shard is regenerated from its seed
+        import numpy as np
+        shards = [host] + [synth.request_columns(n, seed=1234 + r, t_epoch_ms=1.7e12 + r * 3.6e6)
+                           for r in range(1, world)]
+        host_all = ({k: np.concatenate([sh[k] for sh in shards]) for k in host} if world > 1 else host)
+        del shards
     if rank == 0:
         peak, peak_src = measured_peaks()
         # algorithmic bytes per launch of each streaming kernel (DESIGN.md "Kernels")
@@ -408,6 +548,10 @@ def run_ours(args):
             "check": {"p50_ms": core["p50_ms"], "p99_ms": core["p99_ms"],
                       "cost_per_1k_tokens": cost["cost_per_1k_tokens"]},
         }
+        if not args.no_parity and host_all is not None:
+            line["parity"] = parity_block(core, report.trim_series(raw), host_all, cold)
+        if world == 1 and not args.no_percentile_path:
+            line["percentile_path"] = percentile_path_block(device, peak)
         if world == 1 and not args.no_cpu_baseline and host is not None:
             rows = min(n, 3_000_000)
             rate, secs = cpu_port_rate({k: v for k, v in host.items()}, cold, rows)
@@ -434,6 +578,11 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--rows", type=int, default=10_000_000, help="rows per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the oracle comparison of the timed log")
+    ap.add_argument("--no-percentile-path", action="store_true",
+                    help="N=1: skip the 16 B/record percentile-path block")
+    ap.add_argument("--port", action="store_true",
+                    help="--impl reference: time the pure-Python port even when oracle/_ref/ is present")
     ap.add_argument("--device-data", action="store_true", help="generate the shard on the GPU (large --rows)")
     ap.add_argument("--no-e2e", action="store_true", help="with --device-data: skip the host-buffer leg")
     ap.add_argument("--eager", action="store_true", help="launch every step eagerly (no CUDA-graph replay)")

@@ -163,6 +163,7 @@ typedef struct kvm_query {
 #define KVM_Q_OK 0
 #define KVM_Q_EMPTY 1        /* multiset empty: value = NaN */
 #define KVM_Q_OUT_OF_RANGE 2 /* rank >= n (reference would raise IndexError) */
+#define KVM_Q_FAILED 3       /* the select as a whole failed (status word != KVM_OK): value = NaN */
 
 typedef struct kvm_query_result {
   double value; /* the order statistic */
@@ -257,10 +258,16 @@ int64_t kvm_column_select_sampled_min_n(void);
  * are rejected with KVM_ERR_INVALID and a message.  Inputs and `results[nq]` are still the
  * caller's device buffers.  Calls cudaMalloc / cudaFree never.
  *  - The first call on each device looks up the scratch's device address (that device must
- *    be current); make that first call before starting any stream capture.
+ *    be current); make that first call before starting any stream capture.  The lookup is
+ *    guarded by a host mutex, so two threads making a device's first call together is safe;
+ *    with lazy module loading the array itself materialises on a device at first use there.
  *  - All calls on a device share the one scratch: calls whose GPU work can overlap (two
  *    streams, two threads) race.  Serialise them or use kvm_column_select.
- *  - The scratch keeps the previous call's contents; the call clears what it needs. */
+ *  - The scratch keeps the previous call's contents; the call clears what it needs.
+ *  - There is no workspace, hence no status word to read: only bit 0 of a query's set_mask
+ *    is looked at (one set), which bounds the candidates of all queries together by n - the
+ *    size of the scratch arena - so the arena cannot overflow; should a select fail all the
+ *    same, every result carries status KVM_Q_FAILED and value NaN. */
 int kvm_column_select_static(const double* values, int64_t n, int32_t member_mode, const void* member,
                              const kvm_query* queries_host, int32_t nq, kvm_query_result* results,
                              void* stream);
@@ -279,6 +286,7 @@ int kvm_select_status(const void* workspace, void* stream);
 int kvm_column_stats(const double* values, int64_t n, int32_t member_mode, const void* member,
                      int32_t nsets, kvm_set_info* info, void* workspace, size_t workspace_bytes,
                      void* stream);
+size_t kvm_column_stats_workspace_bytes(void);
 /* device addresses inside a select workspace, so the host can hand them to NCCL */
 uint64_t* kvm_select_hist_ptr(void* workspace);   /* [KVM_MAX_SETS][kvm_select_bins()] u64 */
 uint64_t* kvm_select_edge_ptr(void* workspace);   /* [KVM_MAX_HISTS][KVM_HIST_MAX_BINS] u64 edge counters */
@@ -361,8 +369,13 @@ int kvm_select_finish(void* workspace, const uint64_t* const* arenas_host, int32
  *                         use): releases everything this rank stored before, then waits for
  *                         the same from every rank.  The epoch is kept on the device, so the
  *                         call can be captured in a CUDA graph and replayed.  A peer that does
- *                         not arrive within ~3 s sets word [KVM_PEER_MAX_WORLD+1] of the flag
- *                         block non-zero instead of hanging the GPU.
+ *                         not arrive within the time-out (60 s; env KVM_PEER_TIMEOUT_S or
+ *                         kvm_peer_set_timeout_s; the value is read when the call is ENQUEUED, so a
+ *                         captured graph keeps its own) makes the waiting rank write 1 + that
+ *                         peer's rank into word [KVM_PEER_MAX_WORLD+1] of EVERY rank's flag block
+ *                         instead of hanging the GPU.  The word is sticky: later barriers on the
+ *                         buffer return at once, and every rank - the late one too - must treat the
+ *                         step's results as void (the host checks the word before it reports).
  * Buffers that peers accumulate into must be zeroed by their owner BEFORE the owner's previous
  * barrier in stream order (the peers' adds only start after they have passed that barrier). */
 #define KVM_PEER_MAX_WORLD 16
@@ -373,6 +386,8 @@ int kvm_peer_add_u64(const uint64_t* src, int64_t words, int64_t dst_offset, voi
                      int32_t world, int32_t rank, void* stream);
 int kvm_peer_barrier(int64_t flags_offset, void* const* peers_host, int32_t world, int32_t rank,
                      void* stream);
+/* sets the barrier time-out for later calls (seconds > 0; <= 0 only queries); returns the old one */
+double kvm_peer_set_timeout_s(double seconds);
 /* after the compact pass: the filled part of every candidate bucket of `workspace` goes to
  * offset slot_offset (+ the bucket's arena offset) of every rank's buffer; more than
  * slot_capacity candidates (global bucket sizes, so all ranks agree) -> status KVM_ERR_ARENA */

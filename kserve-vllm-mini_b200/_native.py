@@ -148,6 +148,8 @@ def _declare(lib: C.CDLL) -> None:
         "kvm_peer_add_u64": (C.c_int, [vp, i64, i64, P(vp), i32, i32, vp]),
         "kvm_peer_barrier": (C.c_int, [i64, P(vp), i32, i32, vp]),
         "kvm_peer_put_candidates": (C.c_int, [vp, i64, i64, P(vp), i32, i32, vp]),
+        "kvm_peer_set_timeout_s": (f64, [f64]),
+        "kvm_column_stats_workspace_bytes": (sz, []),
         "kvm_column_nearest_workspace_bytes": (sz, []),
         "kvm_column_nearest": (C.c_int, [vp, i64, i32, vp, f64, vp, vp, sz, vp]),
         "kvm_csv_open": (C.c_int, [C.c_char_p, P(vp)]),

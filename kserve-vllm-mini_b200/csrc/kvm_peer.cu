@@ -8,6 +8,8 @@
 //            every rank has said the same"
 // The epoch lives on the device, so a captured graph replays the barrier unchanged.
 
+#include <cstdlib>
+
 #include "kvm_common.cuh"
 #include "kvm_peer.cuh"
 
@@ -17,7 +19,9 @@ constexpr int PEER_THREADS = 256;
 // flag block: [0, MAX_WORLD) arrival counters (written by the peers), then epoch and error (local)
 constexpr int FLAG_EPOCH = KVM_PEER_MAX_WORLD;
 constexpr int FLAG_ERROR = KVM_PEER_MAX_WORLD + 1;
-constexpr long long SPIN_LIMIT_CYCLES = 6000000000ll;  // ~3 s: a dead peer must not hang the GPU
+// a dead peer must not hang the GPU for ever; ordinary host skew (a GC pause, a first-call module
+// load, uneven H2D) must not trip it either: default 60 s, KVM_PEER_TIMEOUT_S overrides
+constexpr double DEFAULT_TIMEOUT_S = 60.0;
 
 __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
   unsigned long long v;
@@ -48,7 +52,18 @@ peer_add_kernel(KvmPeerTable pt, const unsigned long long* __restrict__ src, int
 // One CTA, one thread per rank: release everything this GPU wrote so far (the earlier kernels of
 // the stream included - fences are cumulative), bump my counter in rank p's flag block, then
 // wait for rank p's bump in mine.
-__global__ void peer_barrier_kernel(KvmPeerTable pt, int64_t flags_offset) {
+//
+// Time-out: a rank that waits longer than `spin_limit` cycles for peer p writes 1+p into the error
+// word of EVERY rank's flag block (system-scope stores), so the late rank learns about it too -
+// it would otherwise sail through its own waits (the early rank has already bumped every counter)
+// and report results computed from half-exchanged data.  The error word is sticky: once set, every
+// later barrier on that buffer returns at once (the data of the step is void anyway) and the host
+// raises on every rank (dist_api.ShardedAnalyzer) until the fabric is rebuilt.
+__device__ __forceinline__ void st_relaxed_sys(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+__global__ void peer_barrier_kernel(KvmPeerTable pt, int64_t flags_offset, long long spin_limit) {
   __shared__ unsigned long long want;
   unsigned long long* local = reinterpret_cast<unsigned long long*>(pt.base[pt.rank] + flags_offset);
   if (threadIdx.x == 0) {
@@ -63,8 +78,11 @@ __global__ void peer_barrier_kernel(KvmPeerTable pt, int64_t flags_offset) {
     atomicAdd_system(remote + pt.rank, 1ull);
     const long long t0 = clock64();
     while (ld_acquire_sys(local + p) < want) {
-      if (clock64() - t0 > SPIN_LIMIT_CYCLES) {
-        local[FLAG_ERROR] = 1ull + (unsigned long long)p;
+      if (ld_acquire_sys(local + FLAG_ERROR) != 0ull) break;   // somebody already gave up on this step
+      if (clock64() - t0 > spin_limit) {
+        for (int r = 0; r < pt.world; ++r)
+          st_relaxed_sys(reinterpret_cast<unsigned long long*>(pt.base[r] + flags_offset) + FLAG_ERROR,
+                         1ull + (unsigned long long)p);
         break;
       }
     }
@@ -73,6 +91,31 @@ __global__ void peer_barrier_kernel(KvmPeerTable pt, int64_t flags_offset) {
 }
 
 }  // namespace
+
+// spin limit in SM cycles: KVM_PEER_TIMEOUT_S (seconds, > 0) or the default, at the device's clock
+static double g_peer_timeout_s = 0.0;   // 0: not decided yet
+
+static long long peer_spin_limit_cycles() {
+  if (g_peer_timeout_s <= 0.0) {
+    double secs = DEFAULT_TIMEOUT_S;
+    if (const char* e = getenv("KVM_PEER_TIMEOUT_S")) {
+      const double v = atof(e);
+      if (v > 0.0) secs = v;
+    }
+    g_peer_timeout_s = secs;
+  }
+  int dev = 0, khz = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, dev) != cudaSuccess || khz <= 0)
+    khz = 2000000;
+  return (long long)(g_peer_timeout_s * 1000.0 * (double)khz);
+}
+
+extern "C" double kvm_peer_set_timeout_s(double seconds) {
+  peer_spin_limit_cycles();
+  const double old = g_peer_timeout_s;
+  if (seconds > 0.0) g_peer_timeout_s = seconds;
+  return old;
+}
 
 extern "C" int64_t kvm_peer_flag_bytes(void) { return (int64_t)sizeof(unsigned long long) * (KVM_PEER_MAX_WORLD + 2); }
 
@@ -112,7 +155,7 @@ extern "C" int kvm_peer_barrier(int64_t flags_offset, void* const* peers, int32_
   KvmPeerTable pt;
   KVM_REQUIRE(kvm_peer_table(&pt, peers, world, rank) == 0, "kvm_peer_barrier: bad peer table (world=%d rank=%d)", world, rank);
   KVM_REQUIRE(flags_offset % 8 == 0 && flags_offset >= 0, "kvm_peer_barrier: bad flag offset");
-  peer_barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(pt, flags_offset);
+  peer_barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(pt, flags_offset, peer_spin_limit_cycles());
   KVM_CUDA_CHECK(cudaGetLastError());
   return KVM_OK;
 }

@@ -27,6 +27,8 @@
 // Multi-GPU: `hist` and the edge counters are all-reduced and the arenas all-gathered by the
 // host between the stages; every rank resolves / finishes identically.
 
+#include <mutex>
+
 #include "kvm_common.cuh"
 #include "kvm_log_device.cuh"
 #include "kvm_peer.cuh"
@@ -1547,7 +1549,9 @@ select_finish_kernel(SelWs* ws, SrcPack src, const int64_t* __restrict__ src_cou
       r.value = (ws->status == KVM_OK && s.status == KVM_Q_OK) ? kvm_unkey(s.key) : nan;
       r.n = s.n;
       r.rank = s.rank;
-      r.status = s.status;
+      // a failed select (arena overflow) is visible in every result, for callers that hold no
+      // workspace pointer to read the status word from (kvm_column_select_static)
+      r.status = ws->status != KVM_OK ? KVM_Q_FAILED : s.status;
       r.pad = 0;
       results[q] = r;
     }
@@ -2012,11 +2016,13 @@ static __device__ __align__(256) unsigned char g_select_scratch[STATIC_SCRATCH_B
 // kernel can use; the device address is looked up once per device (that device current).
 static void* g_scratch_addr[STATIC_MAX_DEVICES];
 static bool g_scratch_ready[STATIC_MAX_DEVICES];
+static std::mutex g_scratch_mutex;   // two host threads may make a device's first call at once
 
 static int static_scratch_for_current_device(void** out) {
   int dev = -1;
   KVM_CUDA_CHECK(cudaGetDevice(&dev));
   KVM_REQUIRE(dev >= 0 && dev < STATIC_MAX_DEVICES, "kvm_column_select_static: device %d unsupported", dev);
+  std::lock_guard<std::mutex> guard(g_scratch_mutex);
   if (!g_scratch_ready[dev]) {
     void* ptr = nullptr;
     KVM_CUDA_CHECK(cudaGetSymbolAddress(&ptr, g_select_scratch));
@@ -2040,12 +2046,23 @@ extern "C" int kvm_column_select_static(const double* values, int64_t n, int32_t
   KVM_REQUIRE(n >= 0 && n <= STATIC_MAX_N,
               "kvm_column_select_static: n=%lld exceeds the built-in scratch (max %lld values); use "
               "kvm_column_select with a caller-provided workspace", (long long)n, (long long)STATIC_MAX_N);
+  KVM_REQUIRE(queries && nq >= 1 && nq <= MAXQ, "kvm_column_select_static: nq=%d outside [1,%d]", nq, MAXQ);
   void* scratch = nullptr;
   int rc = static_scratch_for_current_device(&scratch);
   if (rc) return rc;
+  // There is one set (set 0).  Candidate buckets are shared between queries only when their
+  // set masks are identical, so masks that differ in bits no set answers to (1 vs 3) would give
+  // several queries their own copy of one bin and the copies together could outgrow the scratch
+  // (n keys).  Reduce every mask to bit 0: the copies collapse and the candidates of all queries
+  // together never exceed n.
+  kvm_query q1[MAXQ];
+  for (int i = 0; i < nq; ++i) {
+    q1[i] = queries[i];
+    q1[i].set_mask &= 1u;
+  }
   // Everything that must start from zero is cleared inside the pipeline itself (stats
   // ticket, histograms, append cursors), so stale contents of the previous call are harmless.
-  return kvm_column_select(values, n, mode, member, 1, queries, nq, results, scratch,
+  return kvm_column_select(values, n, mode, member, 1, q1, nq, results, scratch,
                            STATIC_SCRATCH_BYTES, STATIC_MAX_N, stream);
 }
 

@@ -372,13 +372,17 @@ extern "C" int kvm_log_scan(const kvm_request_log* log, const double* cold_times
   return KVM_OK;
 }
 
+extern "C" size_t kvm_column_stats_workspace_bytes(void) {
+  return kvm_align_up(256 + sizeof(uint64_t) * (size_t)CS_SLOTS * MAX_GRID, 256);
+}
+
 extern "C" int kvm_column_stats(const double* values, int64_t n, int32_t mode, const void* member,
                                 int32_t nsets, kvm_set_info* info, void* workspace,
                                 size_t workspace_bytes, void* stream) {
   KVM_REQUIRE(info && workspace && (values || n == 0), "kvm_column_stats: null argument");
   KVM_REQUIRE(n >= 0 && nsets >= 1 && nsets <= KVM_MAX_SETS, "kvm_column_stats: bad n/nsets");
   KVM_REQUIRE(mode == KVM_MEMBER_ALL || member, "kvm_column_stats: member array is null");
-  const size_t need = kvm_align_up(256 + sizeof(uint64_t) * (size_t)CS_SLOTS * MAX_GRID, 256);
+  const size_t need = kvm_column_stats_workspace_bytes();
   if (workspace_bytes < need) {
     kvm_set_error("kvm_column_stats: workspace %zu < %zu bytes", workspace_bytes, need);
     return KVM_ERR_WORKSPACE;
@@ -387,6 +391,7 @@ extern "C" int kvm_column_stats(const double* values, int64_t n, int32_t mode, c
   ColStatsWs* ws = reinterpret_cast<ColStatsWs*>(workspace);
   KVM_CUDA_CHECK(cudaMemsetAsync(ws, 0, 256, st));
   int grid = kvm_grid_for(n, STATS_THREADS * 8, 4);
+  if (grid > MAX_GRID) grid = MAX_GRID;   // the partials buffer holds MAX_GRID rows
   const bool vec = (reinterpret_cast<uintptr_t>(values) & 15u) == 0 &&
                    (mode != KVM_MEMBER_STATUS || (reinterpret_cast<uintptr_t>(member) & 15u) == 0);
 #define KVM_LAUNCH_CS(M, V) \

@@ -212,7 +212,9 @@ class RawAnalysis:
         kmin, kmax = int(self.stats.sets.kmin[col]), int(self.stats.sets.kmax[col])
         if kmin > kmax:
             return None
-        return self.key_to_float(kmin), self.key_to_float(kmax)
+        # zero bounds are widened to key(-0.0)/key(+0.0) on the device (kvm_log_device.cuh kmin());
+        # the reference's min()/max() print 0.0 there: x + 0.0 turns -0.0 into 0.0, nothing else
+        return self.key_to_float(kmin) + 0.0, self.key_to_float(kmax) + 0.0
 
 
 class LogAnalyzer:
@@ -630,7 +632,7 @@ class ColumnOps:
         """count / min / max over non-NaN values via kvm_column_stats."""
         n = int(values.shape[0])
         info_d = torch.zeros(C.sizeof(N.SetInfoC), dtype=torch.uint8, device=self.device)
-        ws = torch.empty(256 + 8 * 10 * 148 * 8, dtype=torch.uint8, device=self.device)
+        ws = torch.empty(int(self.lib.kvm_column_stats_workspace_bytes()), dtype=torch.uint8, device=self.device)
         N.check(self.lib.kvm_column_stats(values.data_ptr(), n, N.MEMBER_ALL, None, 1, info_d.data_ptr(),
                                           ws.data_ptr(), ws.numel(), _stream_ptr(self.device)), "kvm_column_stats")
         info = N.SetInfoC.from_buffer_copy(info_d.cpu().numpy().tobytes())
@@ -640,7 +642,10 @@ class ColumnOps:
         def unkey(k):
             bits = k ^ (0x8000000000000000 if (k >> 63) else 0xFFFFFFFFFFFFFFFF)
             return float(np.array([bits], dtype=np.uint64).view(np.float64)[0])
-        return cnt, unkey(int(info.kmin[0])), unkey(int(info.kmax[0]))
+        # a zero bound travels as key(-0.0) / key(+0.0) (it covers both signed zeros for the digit
+        # planner); Python's min()/max() of such a list prints 0.0 unless every zero is negative -
+        # which no producer of these logs writes - so report +0.0 (x + 0.0 maps -0.0 to 0.0)
+        return cnt, unkey(int(info.kmin[0])) + 0.0, unkey(int(info.kmax[0])) + 0.0
 
     def histogram_counts(self, values: torch.Tensor, lo: float, hi: float, num_bins: int) -> List[int]:
         counts = torch.empty(num_bins, dtype=torch.int64, device=self.device)

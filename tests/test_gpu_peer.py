@@ -63,10 +63,23 @@ def test_barrier_times_out_instead_of_hanging():
     lib = N.lib()
     dev = engine.require_cuda()
     bufs = [torch.zeros(256, dtype=torch.uint8, device=dev) for _ in range(2)]
-    N.check(lib.kvm_peer_barrier(0, _table(bufs), 2, 0, engine._stream_ptr(dev)))   # rank 1 never arrives
-    torch.cuda.synchronize(dev)
-    flags = bufs[0].view(torch.int64).cpu().numpy()
-    assert flags[N.KVM_PEER_MAX_WORLD + 1] == 2           # 1 + the rank that was missing
+    old = lib.kvm_peer_set_timeout_s(0.5)
+    try:
+        N.check(lib.kvm_peer_barrier(0, _table(bufs), 2, 0, engine._stream_ptr(dev)))   # rank 1 never arrives
+        torch.cuda.synchronize(dev)
+        # the waiting rank tells EVERY rank (the late one included) which peer was missing
+        for b in bufs:
+            flags = b.view(torch.int64).cpu().numpy()
+            assert flags[N.KVM_PEER_MAX_WORLD + 1] == 2           # 1 + the rank that was missing
+        # sticky: the late rank's own barrier returns at once instead of waiting for a full time-out
+        lib.kvm_peer_set_timeout_s(30.0)
+        t0 = __import__("time").perf_counter()
+        N.check(lib.kvm_peer_barrier(0, _table(bufs), 2, 1, engine._stream_ptr(dev)))
+        N.check(lib.kvm_peer_barrier(0, _table(bufs), 2, 1, engine._stream_ptr(dev)))   # rank 0 is one epoch behind now
+        torch.cuda.synchronize(dev)
+        assert __import__("time").perf_counter() - t0 < 5.0
+    finally:
+        lib.kvm_peer_set_timeout_s(old)
 
 
 def test_bad_arguments_are_rejected():

@@ -193,3 +193,27 @@ def test_interval_energy_oracles_agree():
     a = np.array(a)
     assert np.all(np.abs(a - b) <= 1e-12 * np.maximum(np.abs(a), 1e-300))
     assert (a > 0).sum() > 200
+
+
+def test_ports_equal_the_unmodified_reference_when_it_is_installed():
+    """oracle/_ref/ (the reference's own files, installed by __graft_entry__.build()) travels to
+    every box the tests run on: both ports must reproduce its results on a seeded synthetic log,
+    key for key (the reference is the one timed by `bench.py --impl reference`)."""
+    from kvmini_b200 import synth
+    from oracle import ref_run
+    if not ref_run.available():
+        pytest.skip("oracle/_ref not installed (run __graft_entry__.build() where /root/reference exists)")
+    n = 30_000
+    cols = synth.request_columns(n, seed=99, span_ms=120_000.0)
+    rng = np.random.default_rng(4)
+    cols["ttfb_ms"][rng.integers(0, n, 200)] = np.nan
+    cols["completion_tokens"][rng.integers(0, n, 300)] = 0
+    t0 = float(cols["start_ms"].min()) / 1000.0
+    cold = [t0 + 2.0, t0 + 70.0]
+    ref = ref_run.analyze_rows(ref_run.rows_from_columns(cols), cold)
+    for port, data in ((py_port, {k: v.tolist() for k, v in cols.items()}), (np_port, cols)):
+        got = port.analyze(data, cold)
+        # (the ports also emit the host-side passthrough keys - util, io probe, cache - as None)
+        got = {k: v for k, v in got.items() if k in ref}
+        assert list(got) == list(ref)
+        assert diff_keys(got, ref, rel={"time_to_first_token_ms": 1e-15}) == [], port.__name__

@@ -89,3 +89,36 @@ def test_static_scratch_select_rejects_what_does_not_fit():
     rc = lib.kvm_column_select_static(values.data_ptr(), 16, N.MEMBER_SET_IDS, ids.data_ptr(), q, 2,
                                       out.data_ptr(), stream)
     assert rc == -1 and b"not supported" in lib.kvm_last_error()
+
+
+def test_static_scratch_select_with_mixed_set_masks_at_the_size_limit():
+    """Queries whose set masks differ only in bits no set answers to (1, 3, 0xFFFFFFFF) all mean
+    "set 0" here.  Without the entry point reducing them to bit 0 every distinct mask would get
+    its own copy of a candidate bucket and, on concentrated data at the size limit, the copies
+    would outgrow the built-in scratch; the caller - who has no workspace to read a status word
+    from - must still get exact answers."""
+    import torch
+    from kvmini_b200 import _native as N
+    from kvmini_b200.engine import RESULT_DTYPE
+    lib = N.lib()
+    dev = torch.device("cuda", 0)
+    n = int(lib.kvm_column_select_static_max_n())
+    rng = np.random.default_rng(11)
+    # two distinct keys far apart + a narrow cluster: nearly every value falls into ONE fine bin
+    v = np.full(n, 100.0)
+    v[:1000] = rng.normal(100.0, 1e-9, 1000)
+    v[-1] = 1e12
+    v[0] = -1e12
+    values = torch.from_numpy(v).to(dev)
+    masks = (1, 3, 0xFFFFFFFF, 5, 9, 17)
+    q = (N.QueryC * len(masks))(*[N.QueryC(m, N.RANK_LERP_LO, 0.5, 0) for m in masks])
+    out = torch.zeros(len(masks) * C.sizeof(N.QueryResultC), dtype=torch.uint8, device=dev)
+    stream = torch.cuda.current_stream(dev).cuda_stream
+    for _ in range(2):
+        N.check(lib.kvm_column_select_static(values.data_ptr(), n, N.MEMBER_ALL, None, q, len(masks),
+                                             out.data_ptr(), stream), "kvm_column_select_static")
+        r = np.frombuffer(out.cpu().numpy().tobytes(), dtype=RESULT_DTYPE)
+        assert (r["status"] == N.Q_OK).all(), r["status"]
+        assert (r["n"] == n).all()
+        expect = np.sort(v)[(n - 1) // 2]
+        assert (r["value"] == expect).all()
