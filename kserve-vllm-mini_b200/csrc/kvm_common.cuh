@@ -96,6 +96,43 @@ __device__ __forceinline__ uint8_t kvm_ld_u8(const uint8_t* p) {
   return (uint8_t)r;
 }
 
+// 256-bit streaming loads (sm_100: LDG.256): four 8-byte elements per thread, not allocated in
+// L1 and marked evict-first in L2 - the column is read once, so it should not push out what
+// later passes want to find in L2 (digit records, histograms).  32-byte aligned addresses only.
+struct kvm_u64x4 {
+  unsigned long long x, y, z, w;
+};
+__device__ __forceinline__ kvm_u64x4 kvm_ld4_stream(const void* p) {
+  kvm_u64x4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.L2::evict_first.v4.b64 {%0,%1,%2,%3}, [%4];"
+               : "=l"(r.x), "=l"(r.y), "=l"(r.z), "=l"(r.w)
+               : "l"(p));
+  return r;
+}
+// plain 256-bit load (data another kernel has just written and that should be served from L2)
+__device__ __forceinline__ kvm_u64x4 kvm_ld4(const void* p) {
+  kvm_u64x4 r;
+  asm volatile("ld.global.v4.b64 {%0,%1,%2,%3}, [%4];"
+               : "=l"(r.x), "=l"(r.y), "=l"(r.z), "=l"(r.w)
+               : "l"(p));
+  return r;
+}
+// L2 "keep" policy for small by-products that the next kernel reads back (evict-last)
+__device__ __forceinline__ unsigned long long kvm_policy_evict_last() {
+  unsigned long long pol;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ void kvm_st4_u32_keep(void* p, uint4 v, unsigned long long pol) {
+  asm volatile("st.global.L2::cache_hint.v4.u32 [%0], {%1,%2,%3,%4}, %5;" ::"l"(p), "r"(v.x), "r"(v.y),
+               "r"(v.z), "r"(v.w), "l"(pol)
+               : "memory");
+}
+// programmatic dependent launch (PDL): the dependent kernel may be made resident while this one
+// still runs / wait until every kernel this one depends on has completed and its writes are visible
+__device__ __forceinline__ void kvm_pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;"); }
+__device__ __forceinline__ void kvm_pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // ------------------------------------------------------------------ warp reductions (64-bit)
 __device__ __forceinline__ int64_t kvm_shfl_xor(int64_t v, int m) {
   return (int64_t)__shfl_xor_sync(KVM_FULL, (long long)v, m);

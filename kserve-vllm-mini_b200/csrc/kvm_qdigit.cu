@@ -1,20 +1,30 @@
 // kvm_qdigit.cu - one-and-an-eighth-pass exact quantiles of one multiset (the 16 B/record
 // percentile path; analyze.py:59-81).
 //
-//   sample   4096 stratified pseudo-random members give an ESTIMATE of the key range (one CTA)
-//   hist     ONE pass over the data (16 B/record): 13-bit digit of every member key relative to
-//            the estimated range (bins 0 and 8191 catch what lies far outside it), histogram in
-//            shared memory, and the digit written as a 2-byte record (0xFFFF = not a member)
-//   resolve  one CTA: exact member count = sum of the histogram, rank of every query, the bin
-//            holding it and the residual rank
+// Two launches, no memset; the second is a programmatic dependent launch (its CTAs become
+// resident while the first kernel drains, so there is no launch gap between the two):
+//   hist     prologue: every CTA draws the SAME 512 stratified pseudo-random members (one load per
+//            thread, L2 hits for all but the first CTA) and derives an ESTIMATE of the key range
+//            from them - no separate sampling launch, no grid-wide dependency; CTA 0 also clears
+//            the accumulators and publishes a per-call token that the flushes wait for.
+//            body: ONE pass over the data (16 B/record, 256-bit evict-first loads): 13-bit digit
+//            of every member key relative to the estimated range (bins 0 and 8191 catch what lies
+//            far outside it), histogram in shared memory, and the digit written as a 2-byte record
+//            (0xFFFF = not a member; stored with an L2 keep policy - the next kernel reads them).
+//            epilogue (last CTA to finish, ticket): exact member count = sum of the histogram,
+//            rank of every query, the bin holding it and the residual rank.
 //   collect  pass over the 2 B/record digit records; the value of a record is fetched only when
-//            its digit is a wanted bin (~0.1 % of the records)
-//   rank     one CTA per query: one narrowing histogram over the gathered keys, then counting
+//            its digit is a wanted bin (~0.1 % of the records): its key goes to that bin's list and
+//            its next 11 bits into that bin's sub-histogram.
+//            epilogue (last CTA, ticket): one 64-thread group per query walks the sub-histogram to
+//            the sub-bin holding the rank and ranks the handful of keys of that sub-bin.
 // Exact whenever it answers.  It declines (status word KVM_ERR_UNSUPPORTED, the caller runs the
 // general select) when a rank falls into a catch-all bin (the sample missed the range), when a
-// list overflows (heavy duplicates) or when the sample holds too few members.
+// list overflows (heavy duplicates spread over many keys) or when the sample holds too few members.
 
+#include <atomic>
 #include <cstddef>
+#include <cstdlib>
 
 #include "kvm_common.cuh"
 #include "kvm_log_device.cuh"
@@ -22,13 +32,16 @@
 namespace {
 
 constexpr int QD_MAXQ = 8;
-constexpr int QD_SAMPLE = 4096;
+constexpr int QD_THREADS = 512;
+constexpr int QD_SAMPLE = QD_THREADS;  // one stratified sample per thread, the same in every CTA
 constexpr int QD_BINS = 8192;
 constexpr int QD_SPAN_BITS = 12;   // the widened sample range spans at most 4096 bins; the rest lies beyond it
-constexpr int QD_THREADS = 512;
+constexpr int QD_SUB_BITS = 11;    // sub-histogram of a wanted bin
+constexpr int QD_SUB = 1 << QD_SUB_BITS;
 constexpr int QD_SMALL = 4096;     // keys ranked by counting at the very end
 constexpr int QD_QUEUE = 2048;     // wanted rows a CTA queues for the drain after its streaming loop
 constexpr int QD_STAGE = 384;      // keys a CTA stages per wanted bin before going to global memory
+constexpr int QD_GROUP = QD_THREADS / QD_MAXQ;   // threads that finish one query in the last CTA
 constexpr uint64_t QD_NONE = ~0ull;
 
 struct QdQuery {
@@ -47,17 +60,20 @@ struct QdWs {
   long long list_cap;   // keys per slot list
   QdQuery q[QD_MAXQ];
   int32_t slot_bin[QD_MAXQ];
-  // ---- cleared by one memset before every call (QD_CLEAR_* below)
-  unsigned long long s_inv_min, s_max;   // sample extremes (the minimum travels complemented)
-  unsigned int s_count, s_ticket;
+  unsigned long long ready;   // == the call's token once CTA 0 of the hist kernel has cleared the block below
+  // ---- cleared by CTA 0 of the hist kernel at the start of every call (QD_CLEAR_* below)
+  alignas(16) unsigned int s_ticket;
+  unsigned int c_ticket, pad4[2];
   unsigned long long list_n[QD_MAXQ];
   unsigned long long hist[QD_BINS];
+  unsigned int hist2[QD_MAXQ][QD_SUB];
   // ----
-  uint64_t small[QD_MAXQ][QD_SMALL];
+  alignas(16) uint64_t small[QD_MAXQ][QD_SMALL];
 };
 
 constexpr size_t QD_HEADER = (sizeof(QdWs) + 255) / 256 * 256;
-constexpr size_t QD_CLEAR_BEGIN = offsetof(QdWs, s_inv_min), QD_CLEAR_END = offsetof(QdWs, small);
+constexpr size_t QD_CLEAR_BEGIN = offsetof(QdWs, s_ticket), QD_CLEAR_END = offsetof(QdWs, small);
+static_assert(QD_CLEAR_BEGIN % 16 == 0 && QD_CLEAR_END % 16 == 0, "cleared with 16-byte stores");
 
 struct QdArgs {
   int32_t nq;
@@ -86,137 +102,27 @@ __device__ __forceinline__ bool qd_member(const void* member, int64_t i) {
   return true;
 }
 
-// ------------------------------------------------------------------ sample
-// 16 CTAs x 256 threads, one sample each (one CTA would serialise 4096 random DRAM accesses);
-// the last CTA to finish turns the sample's extremes into the digit parameters.  The words the
-// CTAs accumulate into are cleared by the host-side memset in front of the launch.
-constexpr int QD_SAMPLE_CTAS = 16;
-
-template <int MODE>
-__global__ void __launch_bounds__(QD_SAMPLE / QD_SAMPLE_CTAS)
-qd_sample_kernel(const double* __restrict__ values, int64_t n, const void* __restrict__ member, QdArgs a,
-                 QdWs* ws, long long list_cap) {
-  __shared__ bool is_last;
-  const int t = threadIdx.x;
-  const int s = blockIdx.x * blockDim.x + t;
-  const int64_t width = n / QD_SAMPLE;
-  const int64_t i = (int64_t)s * width + (int64_t)(qd_hash((uint32_t)s * 2654435761u + 12345u) % (uint64_t)width);
-  const double v = values[i];
-  const bool mem = qd_member<MODE>(member, i) && v == v;
-  uint64_t mx = mem ? kvm_key(v) : 0ull, inv_mn = mem ? ~kvm_key(v) : 0ull;
-  int cnt = mem;
-#pragma unroll
-  for (int o = 16; o; o >>= 1) {
-    const uint64_t a0 = __shfl_xor_sync(KVM_FULL, inv_mn, o), a1 = __shfl_xor_sync(KVM_FULL, mx, o);
-    inv_mn = a0 > inv_mn ? a0 : inv_mn;
-    mx = a1 > mx ? a1 : mx;
-    cnt += __shfl_xor_sync(KVM_FULL, cnt, o);
-  }
-  if ((t & 31) == 0 && cnt) {
-    atomicMax(&ws->s_inv_min, (unsigned long long)inv_mn);
-    atomicMax(&ws->s_max, (unsigned long long)mx);
-    atomicAdd(&ws->s_count, (unsigned int)cnt);
-  }
-  __threadfence();
-  __syncthreads();
-  if (t == 0) is_last = atomicAdd(&ws->s_ticket, 1u) == gridDim.x - 1;
-  __syncthreads();
-  if (!is_last) return;
-  __threadfence();
-  if (t == 0) {
-    const uint64_t mn = ~__ldcg(&ws->s_inv_min), mxk = __ldcg(&ws->s_max);
-    const int m = (int)__ldcg(&ws->s_count);
-    ws->nq = a.nq;
-    ws->list_cap = list_cap;
-    if (m < 256) {
-      ws->status = KVM_ERR_UNSUPPORTED;  // too few members in the sample to trust its range
-    } else {
-      // widen the sampled range by an eighth on both sides (saturating), 4096 in-range bins at most
-      const uint64_t range = mxk - mn, margin = (range >> 3) + 1;
-      const uint64_t lo = mn > margin ? mn - margin : 0ull;
-      const uint64_t hi = mxk < QD_NONE - 1 - margin ? mxk + margin : QD_NONE - 1;
-      const uint64_t r2 = hi - lo;
-      const int bits = r2 ? 64 - __clzll((long long)r2) : 0;
-      ws->base = lo;
-      ws->shift = bits > QD_SPAN_BITS ? bits - QD_SPAN_BITS : 0;
-      ws->status = KVM_OK;
-    }
-  }
-  if (t < QD_MAXQ) {
-    QdQuery q{};
-    q.kind = a.kind[t];
-    q.p = a.p[t];
-    ws->q[t] = q;
-  }
+__device__ __forceinline__ unsigned long long qd_ld_acquire(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void qd_st_release(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
-// ------------------------------------------------------------------ hist (+ digit records)
-template <int MODE, bool VEC>
-__global__ void __launch_bounds__(QD_THREADS, 2)
-qd_hist_kernel(const double* __restrict__ values, int64_t n, const void* __restrict__ member, QdWs* ws,
-               uint16_t* __restrict__ recs) {
-  __shared__ uint32_t hist[QD_BINS];
-  if (ws->status != KVM_OK) return;
-  for (int i = threadIdx.x; i < QD_BINS; i += QD_THREADS) hist[i] = 0;
-  const uint64_t base = ws->base;
-  const int shift = ws->shift;
-  __syncthreads();
-  auto digit_of_value = [&](double v, bool mem) -> uint32_t {
-    if (!(mem && v == v)) return 0xFFFFu;
-    const uint32_t d = qd_digit(kvm_key(v), base, shift);
-    atomicAdd(&hist[d], 1u);
-    return d;
-  };
-  if (VEC) {
-    // four records per thread and iteration: two 16-byte value loads, one 8-byte record store
-    const int64_t nquads = n >> 2;
-    for (int64_t qd = (int64_t)blockIdx.x * QD_THREADS + threadIdx.x; qd < nquads;
-         qd += (int64_t)gridDim.x * QD_THREADS) {
-      const int64_t i = qd << 2;
-      const double2 v0 = kvm_ld2(values + i), v1 = kvm_ld2(values + i + 2);
-      bool m0 = true, m1 = true, m2 = true, m3 = true;
-      if (MODE == KVM_MEMBER_STATUS) {
-        const int64_t* st = reinterpret_cast<const int64_t*>(member);
-        const longlong2 s0 = kvm_ld2(st + i), s1 = kvm_ld2(st + i + 2);
-        m0 = s0.x == 200;
-        m1 = s0.y == 200;
-        m2 = s1.x == 200;
-        m3 = s1.y == 200;
-      }
-      const uint32_t d0 = digit_of_value(v0.x, m0), d1 = digit_of_value(v0.y, m1);
-      const uint32_t d2 = digit_of_value(v1.x, m2), d3 = digit_of_value(v1.y, m3);
-      uint2 out;
-      out.x = d0 | (d1 << 16);
-      out.y = d2 | (d3 << 16);
-      *reinterpret_cast<uint2*>(recs + i) = out;
-    }
-    if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
-      const int64_t i = (n & ~3ll) + threadIdx.x;
-      recs[i] = (uint16_t)digit_of_value(values[i], qd_member<MODE>(member, i));
-    }
-  } else {
-    for (int64_t i = (int64_t)blockIdx.x * QD_THREADS + threadIdx.x; i < n; i += (int64_t)gridDim.x * QD_THREADS)
-      recs[i] = (uint16_t)digit_of_value(kvm_ld1(values + i), qd_member<MODE>(member, i));
-  }
-  __syncthreads();
-  for (int i = threadIdx.x; i < QD_BINS; i += QD_THREADS) {
-    const uint32_t c = hist[i];
-    if (c) atomicAdd(&ws->hist[i], (unsigned long long)c);
-  }
-}
-
-// ------------------------------------------------------------------ resolve
-__global__ void __launch_bounds__(1024, 1) qd_resolve_kernel(QdWs* ws) {
-  __shared__ uint32_t cum[QD_BINS];   // exclusive prefix of the histogram (n < 2^31 on this path)
-  __shared__ unsigned long long wtot[32];
+// ------------------------------------------------------------------ resolve (last CTA of the hist kernel)
+// `cum` (shared, QD_BINS words) receives the exclusive prefix of the global histogram; every
+// query finds its bin by bisection.
+__device__ __forceinline__ void qd_resolve(QdWs* ws, uint32_t* cum, const QdArgs& a) {
+  __shared__ unsigned long long wtot[QD_THREADS / 32];
   __shared__ QdQuery qs[QD_MAXQ];
-  if (ws->status != KVM_OK) return;
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-  constexpr int PER = QD_BINS / 1024;
+  constexpr int PER = QD_BINS / QD_THREADS;
   unsigned long long c[PER], local = 0;
 #pragma unroll
   for (int k = 0; k < PER; ++k) {
-    c[k] = ws->hist[t * PER + k];
+    c[k] = __ldcg(&ws->hist[t * PER + k]);
     local += c[k];
   }
   unsigned long long incl = local;
@@ -226,42 +132,53 @@ __global__ void __launch_bounds__(1024, 1) qd_resolve_kernel(QdWs* ws) {
     if (lane >= d) incl += o;
   }
   if (lane == 31) wtot[warp] = incl;
-  if (t < QD_MAXQ) qs[t] = ws->q[t];
   __syncthreads();
   unsigned long long before = incl - local;
   for (int w = 0; w < warp; ++w) before += wtot[w];
 #pragma unroll
   for (int k = 0; k < PER; ++k) {
-    cum[t * PER + k] = (uint32_t)before;
+    cum[t * PER + k] = (uint32_t)before;   // n < 2^31 on this path
     before += c[k];
   }
   __syncthreads();
   unsigned long long total = 0;
-  for (int w = 0; w < 32; ++w) total += wtot[w];
-  const int nq = ws->nq;
-  if (t < nq) {
-    QdQuery s = qs[t];
-    s.n = (long long)total;
-    s.valid = 1;
-    s.bin = -1;
-    s.slot = -1;
-    if (total == 0) {
-      s.qstatus = KVM_Q_EMPTY;
-    } else {
-      s.rank = resolve_rank(s.kind, s.p, s.n, 0);
-      if (s.rank < 0 || s.rank >= s.n) {
-        s.qstatus = KVM_Q_OUT_OF_RANGE;
-      } else {
-        s.qstatus = KVM_Q_OK;
-        int lo = 0, hi = QD_BINS - 1;   // last bin whose exclusive prefix is <= rank
-        while (lo < hi) {
-          const int mid = (lo + hi + 1) >> 1;
-          if ((long long)cum[mid] <= s.rank) lo = mid;
-          else hi = mid - 1;
+  for (int w = 0; w < QD_THREADS / 32; ++w) total += wtot[w];
+  const int nq = a.nq;
+  if (t < QD_MAXQ) {
+    QdQuery s{};
+    if (t < nq) {
+      int kind = 0;
+      double p = 0.0;
+#pragma unroll
+      for (int k = 0; k < QD_MAXQ; ++k)   // (no dynamic indexing of the kernel parameter)
+        if (k == t) {
+          kind = a.kind[k];
+          p = a.p[k];
         }
-        s.bin = lo;
-        s.resid = s.rank - (long long)cum[lo];
-        if (lo == 0 || lo == QD_BINS - 1) s.valid = 0;   // catch-all bins: the sample missed the range
+      s.kind = kind;
+      s.p = p;
+      s.n = (long long)total;
+      s.valid = 1;
+      s.bin = -1;
+      s.slot = -1;
+      if (total == 0) {
+        s.qstatus = KVM_Q_EMPTY;
+      } else {
+        s.rank = resolve_rank(s.kind, s.p, s.n, 0);
+        if (s.rank < 0 || s.rank >= s.n) {
+          s.qstatus = KVM_Q_OUT_OF_RANGE;
+        } else {
+          s.qstatus = KVM_Q_OK;
+          int lo = 0, hi = QD_BINS - 1;   // last bin whose exclusive prefix is <= rank
+          while (lo < hi) {
+            const int mid = (lo + hi + 1) >> 1;
+            if ((long long)cum[mid] <= s.rank) lo = mid;
+            else hi = mid - 1;
+          }
+          s.bin = lo;
+          s.resid = s.rank - (long long)cum[lo];
+          if (lo == 0 || lo == QD_BINS - 1) s.valid = 0;   // catch-all bins: the sample missed the range
+        }
       }
     }
     qs[t] = s;
@@ -270,75 +187,383 @@ __global__ void __launch_bounds__(1024, 1) qd_resolve_kernel(QdWs* ws) {
   if (t == 0) {
     int nslots = 0;
     bool ok = true;
+    int sb[QD_MAXQ];
     for (int q = 0; q < nq; ++q) {
       QdQuery& s = qs[q];
       if (!s.valid) ok = false;
       if (s.qstatus != KVM_Q_OK || !s.valid) continue;
       int slot = -1;
       for (int k = 0; k < nslots; ++k)
-        if (ws->slot_bin[k] == s.bin) slot = k;
+        if (sb[k] == s.bin) slot = k;
       if (slot < 0) {
         slot = nslots++;
-        ws->slot_bin[slot] = s.bin;
+        sb[slot] = s.bin;
       }
       s.slot = slot;
     }
-    for (int k = nslots; k < QD_MAXQ; ++k) ws->slot_bin[k] = -1;
+    for (int k = 0; k < QD_MAXQ; ++k) ws->slot_bin[k] = k < nslots ? sb[k] : -1;
     ws->nslots = nslots;
     if (!ok) ws->status = KVM_ERR_UNSUPPORTED;
     for (int q = 0; q < QD_MAXQ; ++q) ws->q[q] = qs[q];
   }
 }
 
-// ------------------------------------------------------------------ collect
+// ------------------------------------------------------------------ hist (sample + digit records + resolve)
+// VEC: both columns are 32-byte aligned -> eight records per thread and iteration (two 256-bit
+// loads per column, one 16-byte record store); CTA b owns the contiguous range of row octets
+// [b*chunk, (b+1)*chunk), so every CTA streams the same number of bytes.
+template <int MODE, bool VEC>
+__global__ void __launch_bounds__(QD_THREADS, 2)
+qd_hist_kernel(const double* __restrict__ values, int64_t n, const void* __restrict__ member, QdWs* ws,
+               uint16_t* __restrict__ recs, QdArgs a, long long list_cap, unsigned long long token) {
+  __shared__ uint32_t hist[QD_BINS];
+  __shared__ unsigned long long red_inv[QD_THREADS / 32], red_mx[QD_THREADS / 32];
+  __shared__ int red_cnt[QD_THREADS / 32];
+  __shared__ unsigned long long s_base;
+  __shared__ int s_shift, s_ok;
+  __shared__ bool is_last;
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  kvm_pdl_launch_dependents();   // the collect kernel may take the SM slots this grid frees as it drains
+
+  // ---- CTA 0: clear what the call accumulates into, then publish the call's token.  No other
+  // CTA touches those words before it has seen the token (the wait in front of the flush below),
+  // and CTA 0 waits for nobody, so there is no ordering between CTAs to rely on.
+  if (blockIdx.x == 0) {
+    uint4* z = reinterpret_cast<uint4*>(reinterpret_cast<unsigned char*>(ws) + QD_CLEAR_BEGIN);
+    constexpr int NZ = (int)((QD_CLEAR_END - QD_CLEAR_BEGIN) / 16);
+    for (int i = t; i < NZ; i += QD_THREADS) z[i] = make_uint4(0u, 0u, 0u, 0u);
+    __threadfence();
+    __syncthreads();
+    if (t == 0) qd_st_release(&ws->ready, token);
+  }
+  for (int i = t; i < QD_BINS; i += QD_THREADS) hist[i] = 0;
+
+  // ---- the first tile of the stream is requested before the sample is reduced (its latency
+  // hides the sample's)
+  const int64_t nocts = n >> 3;
+  const int64_t chunk = (nocts + gridDim.x - 1) / gridDim.x;
+  const int64_t o_end = min(nocts, ((int64_t)blockIdx.x + 1) * chunk);
+  int64_t o = (int64_t)blockIdx.x * chunk + t;
+  const int64_t* st = reinterpret_cast<const int64_t*>(member);
+  kvm_u64x4 v0{}, v1{}, s0{}, s1{};
+  auto load8 = [&](int64_t oc, kvm_u64x4& a0, kvm_u64x4& a1, kvm_u64x4& b0, kvm_u64x4& b1) {
+    const int64_t i = oc << 3;
+    a0 = kvm_ld4_stream(values + i);
+    a1 = kvm_ld4_stream(values + i + 4);
+    if (MODE == KVM_MEMBER_STATUS) {
+      b0 = kvm_ld4_stream(st + i);
+      b1 = kvm_ld4_stream(st + i + 4);
+    }
+  };
+  bool have = VEC && o < o_end;
+  if (have) load8(o, v0, v1, s0, s1);
+
+  // ---- sample: thread t draws one element of stratum t - the same element in every CTA, so all
+  // CTAs derive identical digit parameters without talking to each other
+  {
+    const int64_t width = n / QD_SAMPLE;
+    const int64_t i = (int64_t)t * width + (int64_t)(qd_hash((uint32_t)t * 2654435761u + 12345u) % (uint64_t)width);
+    const double v = __ldg(values + i);
+    bool mem = v == v;
+    if (MODE == KVM_MEMBER_STATUS) mem = mem && __ldg(st + i) == 200;
+    unsigned long long mx = mem ? kvm_key(v) : 0ull, inv_mn = mem ? ~kvm_key(v) : 0ull;
+    int cnt = mem;
+#pragma unroll
+    for (int d = 16; d; d >>= 1) {
+      const unsigned long long a0 = __shfl_xor_sync(KVM_FULL, inv_mn, d), a1 = __shfl_xor_sync(KVM_FULL, mx, d);
+      inv_mn = a0 > inv_mn ? a0 : inv_mn;
+      mx = a1 > mx ? a1 : mx;
+      cnt += __shfl_xor_sync(KVM_FULL, cnt, d);
+    }
+    if (lane == 0) {
+      red_inv[warp] = inv_mn;
+      red_mx[warp] = mx;
+      red_cnt[warp] = cnt;
+    }
+    __syncthreads();
+    if (t == 0) {
+      unsigned long long inv = 0, mxk = 0;
+      int m = 0;
+      for (int w = 0; w < QD_THREADS / 32; ++w) {
+        inv = red_inv[w] > inv ? red_inv[w] : inv;
+        mxk = red_mx[w] > mxk ? red_mx[w] : mxk;
+        m += red_cnt[w];
+      }
+      const uint64_t mn = ~inv;
+      const int ok = m >= QD_SAMPLE / 8;   // too few members in the sample to trust its range otherwise
+      uint64_t lo = 0;
+      int shift = 0;
+      if (ok) {
+        // widen the sampled range by an eighth on both sides (saturating), 4096 in-range bins at most
+        const uint64_t range = mxk - mn, margin = (range >> 3) + 1;
+        lo = mn > margin ? mn - margin : 0ull;
+        const uint64_t hi = mxk < QD_NONE - 1 - margin ? mxk + margin : QD_NONE - 1;
+        const uint64_t r2 = hi - lo;
+        const int bits = r2 ? 64 - __clzll((long long)r2) : 0;
+        shift = bits > QD_SPAN_BITS ? bits - QD_SPAN_BITS : 0;
+      }
+      s_base = lo;
+      s_shift = shift;
+      s_ok = ok;
+      if (blockIdx.x == 0) {
+        ws->nq = a.nq;
+        ws->list_cap = list_cap;
+        ws->base = lo;
+        ws->shift = shift;
+        ws->nslots = 0;
+        ws->status = ok ? KVM_OK : KVM_ERR_UNSUPPORTED;
+        if (!ok)
+          for (int q = 0; q < QD_MAXQ; ++q) ws->q[q] = QdQuery{};
+      }
+    }
+    __syncthreads();
+  }
+  if (!s_ok) return;   // every CTA takes the same decision; the status word says "declined"
+  const uint64_t base = s_base;
+  const int shift = s_shift;
+  auto digit_of_value = [&](double v, bool mem) -> uint32_t {
+    if (!(mem && v == v)) return 0xFFFFu;
+    const uint32_t d = qd_digit(kvm_key(v), base, shift);
+    atomicAdd(&hist[d], 1u);
+    return d;
+  };
+  auto dig = [&](unsigned long long vb, unsigned long long sb) -> uint32_t {
+    return digit_of_value(__longlong_as_double((long long)vb), MODE != KVM_MEMBER_STATUS || sb == 200ull);
+  };
+  if (VEC) {
+    const unsigned long long keep = kvm_policy_evict_last();
+    while (have) {
+      uint4 out;
+      out.x = dig(v0.x, s0.x) | (dig(v0.y, s0.y) << 16);
+      out.y = dig(v0.z, s0.z) | (dig(v0.w, s0.w) << 16);
+      out.z = dig(v1.x, s1.x) | (dig(v1.y, s1.y) << 16);
+      out.w = dig(v1.z, s1.z) | (dig(v1.w, s1.w) << 16);
+      kvm_st4_u32_keep(recs + (o << 3), out, keep);
+      // (no register double-buffering: 128 B in flight per thread x 1024 threads per SM is
+      // several times what the memory system needs; the other warps cover this one's wait)
+      o += QD_THREADS;
+      have = o < o_end;
+      if (have) load8(o, v0, v1, s0, s1);
+    }
+    if (blockIdx.x == 0 && t < (n & 7)) {
+      const int64_t i = (n & ~7ll) + t;
+      recs[i] = (uint16_t)digit_of_value(values[i], qd_member<MODE>(member, i));
+    }
+  } else {
+    for (int64_t i = (int64_t)blockIdx.x * QD_THREADS + t; i < n; i += (int64_t)gridDim.x * QD_THREADS)
+      recs[i] = (uint16_t)digit_of_value(kvm_ld1(values + i), qd_member<MODE>(member, i));
+  }
+  __syncthreads();
+  if (t == 0) {
+    while (qd_ld_acquire(&ws->ready) != token) {}   // CTA 0 has cleared the accumulators (long ago)
+  }
+  __syncthreads();
+  for (int i = t; i < QD_BINS; i += QD_THREADS) {
+    const uint32_t c = hist[i];
+    if (c) atomicAdd(&ws->hist[i], (unsigned long long)c);
+  }
+  __threadfence();
+  __syncthreads();
+  if (t == 0) is_last = atomicAdd(&ws->s_ticket, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  qd_resolve(ws, hist, a);
+}
+
+// ------------------------------------------------------------------ collect (+ rank in the last CTA)
+struct QdCollectSmem {
+  uint64_t stage[QD_MAXQ][QD_STAGE];
+  uint32_t queue[QD_QUEUE];
+  uint32_t stage_n[QD_MAXQ];
+  unsigned long long stage_pos[QD_MAXQ];
+  uint32_t queue_n;
+  int is_last;
+};
+
+// One query, finished by a group of QD_GROUP threads of the last CTA (named barrier `bar`):
+// walk the wanted bin's sub-histogram to the sub-bin holding the residual rank, then look at the
+// keys of that sub-bin only - usually a handful, or thousands of copies of ONE key (values
+// rounded to three decimals), which min == max settles without ranking anything.
+__device__ __forceinline__ void qd_finish_query(QdWs* ws, const uint64_t* __restrict__ lists, int q, int gt,
+                                                int bar, uint32_t* gs /* [QD_GROUP + 8] shared words of the group */,
+                                                kvm_query_result* __restrict__ results) {
+  auto gsync = [&]() { asm volatile("bar.sync %0, %1;" ::"r"(bar), "r"(QD_GROUP) : "memory"); };
+  const double nan = __longlong_as_double(0x7ff8000000000000ll);
+  const QdQuery s = ws->q[q];
+  const bool need = ws->status == KVM_OK && s.valid && s.qstatus == KVM_Q_OK;
+  if (!need) {   // empty multiset / rank out of range: nothing to look up; a declined call reports NaN
+    if (gt == 0) results[q] = kvm_query_result{nan, s.n, s.rank, s.qstatus, 0};
+    return;
+  }
+  const long long cap = ws->list_cap;
+  const unsigned long long m = __ldcg(&ws->list_n[s.slot]);
+  auto decline = [&]() {
+    if (gt == 0) {
+      ws->status = KVM_ERR_UNSUPPORTED;  // all writers agree
+      results[q] = kvm_query_result{nan, s.n, s.rank, s.qstatus, 0};
+    }
+  };
+  if (m > (unsigned long long)cap || (long long)m <= s.resid) {
+    decline();
+    return;
+  }
+  const int bshift = ws->shift;
+  const uint64_t bin_base = ws->base + ((uint64_t)(s.bin - 1) << bshift);
+  const int sh2 = bshift > QD_SUB_BITS ? bshift - QD_SUB_BITS : 0;
+  // ---- sub-bin: every thread sums QD_SUB / QD_GROUP consecutive sub-bins, the group scans the sums
+  constexpr int PER = QD_SUB / QD_GROUP;
+  const unsigned int* __restrict__ h2 = ws->hist2[s.slot];
+  uint32_t c[PER], local = 0;
+#pragma unroll
+  for (int k = 0; k < PER; k += 4) {
+    const uint4 x = __ldcg(reinterpret_cast<const uint4*>(h2 + gt * PER + k));
+    c[k] = x.x; c[k + 1] = x.y; c[k + 2] = x.z; c[k + 3] = x.w;
+    local += x.x + x.y + x.z + x.w;
+  }
+  gs[gt] = local;
+  gsync();
+  uint32_t before = 0;
+  for (int k = 0; k < gt; ++k) before += gs[k];
+  const uint32_t r = (uint32_t)s.resid;
+  if (before <= r && r < before + local) {
+    uint32_t b = before;
+    int k = 0;
+    for (; k < PER - 1; ++k) {
+      if (r < b + c[k]) break;
+      b += c[k];
+    }
+    gs[QD_GROUP] = (uint32_t)(gt * PER + k);   // the sub-bin
+    gs[QD_GROUP + 1] = r - b;                  // rank inside it
+    gs[QD_GROUP + 2] = c[k];                   // its population
+  }
+  if (gt == 0) {
+    gs[QD_GROUP + 3] = 0;   // keys gathered
+  }
+  gsync();
+  const uint32_t sb = gs[QD_GROUP], sr = gs[QD_GROUP + 1], scount = gs[QD_GROUP + 2];
+  if (sh2 == 0) {   // the sub-bin is one key
+    if (gt == 0) results[q] = kvm_query_result{kvm_unkey(bin_base + sb), s.n, s.rank, KVM_Q_OK, 0};
+    return;
+  }
+  // ---- keys of the sub-bin: min / max over the group decide the all-equal case, otherwise they
+  // are gathered (global scratch) and ranked by counting
+  const uint64_t* __restrict__ keys = lists + (size_t)s.slot * (size_t)cap;
+  uint64_t* small = ws->small[q];
+  uint64_t kmin = QD_NONE, kmax = 0;
+  const bool gather = scount <= (uint32_t)QD_SMALL;
+  for (unsigned long long i0 = gt; i0 < m; i0 += 4 * QD_GROUP) {
+    uint64_t kk[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) kk[u] = i0 + u * QD_GROUP < m ? __ldcg(keys + i0 + u * QD_GROUP) : QD_NONE;
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (kk[u] != QD_NONE && (uint32_t)((kk[u] - bin_base) >> sh2) == sb) {
+        kmin = kk[u] < kmin ? kk[u] : kmin;
+        kmax = kk[u] > kmax ? kk[u] : kmax;
+        if (gather) {
+          const uint32_t pos = atomicAdd(&gs[QD_GROUP + 3], 1u);
+          if (pos < (uint32_t)QD_SMALL) small[pos] = kk[u];
+        }
+      }
+  }
+  kmin = kvm_warp_min(kmin);
+  kmax = kvm_warp_max(kmax);
+  uint64_t* g64 = reinterpret_cast<uint64_t*>(gs + QD_GROUP + 4);   // [2 warps][2]
+  if ((gt & 31) == 0) {
+    g64[2 * (gt >> 5)] = kmin;
+    g64[2 * (gt >> 5) + 1] = kmax;
+  }
+  __threadfence_block();
+  gsync();
+  for (int w = 0; w < QD_GROUP / 32; ++w) {
+    kmin = g64[2 * w] < kmin ? g64[2 * w] : kmin;
+    kmax = g64[2 * w + 1] > kmax ? g64[2 * w + 1] : kmax;
+  }
+  if (kmin == kmax) {   // one distinct key (any number of copies)
+    if (gt == 0) results[q] = kvm_query_result{kvm_unkey(kmin), s.n, s.rank, KVM_Q_OK, 0};
+    return;
+  }
+  const uint32_t m2 = gs[QD_GROUP + 3];
+  if (!gather || m2 != scount) {   // too many distinct candidates for the scratch: the general select's job
+    decline();
+    return;
+  }
+  uint64_t ans = 0;
+  bool mine = false;
+  for (uint32_t i = gt; i < m2; i += QD_GROUP) {
+    const uint64_t k = small[i];
+    uint32_t less = 0, leq = 0;
+    for (uint32_t j = 0; j < m2; ++j) {
+      const uint64_t x = small[j];
+      less += x < k;
+      leq += x <= k;
+    }
+    if (less <= sr && sr < leq) {
+      ans = k;
+      mine = true;
+    }
+  }
+  if (mine) results[q] = kvm_query_result{kvm_unkey(ans), s.n, s.rank, KVM_Q_OK, 0};  // all writers agree
+}
+
 // Streams the 2 B/record digit records; a record whose digit is a wanted bin has its value
-// fetched and its key appended to that bin's list (staged per CTA, one cursor bump per flush).
+// fetched, its key appended to that bin's list (staged per CTA, one cursor bump per flush) and
+// the key's next 11 bits counted into the bin's sub-histogram.
 template <bool VEC>
 __global__ void __launch_bounds__(QD_THREADS, 2)
 qd_collect_kernel(const double* __restrict__ values, int64_t n, const uint16_t* __restrict__ recs, QdWs* ws,
-                  uint64_t* __restrict__ lists) {
-  __shared__ uint64_t stage[QD_MAXQ][QD_STAGE];
-  __shared__ uint32_t stage_n[QD_MAXQ];
-  __shared__ unsigned long long stage_pos[QD_MAXQ];
-  __shared__ uint32_t queue[QD_QUEUE];
-  __shared__ uint32_t queue_n;
-  if (ws->status != KVM_OK) return;
+                  uint64_t* __restrict__ lists, kvm_query_result* __restrict__ results) {
+  __shared__ QdCollectSmem S;
+  const int t = threadIdx.x;
+  if (t < QD_MAXQ) S.stage_n[t] = 0;
+  if (t == 0) S.queue_n = 0;
+  kvm_pdl_wait();   // everything above overlapped the hist kernel's tail; its results are visible from here on
+  if (ws->status != KVM_OK) {   // declined by the sample or by the resolve: report and re-arm the handshake
+    if (blockIdx.x == 0) {
+      const double nan = __longlong_as_double(0x7ff8000000000000ll);
+      if (t < ws->nq) results[t] = kvm_query_result{nan, ws->q[t].n, ws->q[t].rank, ws->q[t].qstatus, 0};
+      if (t == 0) ws->ready = 0ull;
+    }
+    return;
+  }
   const int nslots = ws->nslots;
   const long long cap = ws->list_cap;
+  const int bshift = ws->shift;
+  const uint64_t base = ws->base;
+  const int sh2 = bshift > QD_SUB_BITS ? bshift - QD_SUB_BITS : 0;
   uint32_t want[QD_MAXQ];
 #pragma unroll
   for (int k = 0; k < QD_MAXQ; ++k) want[k] = k < nslots ? (uint32_t)ws->slot_bin[k] : 0xFFFFFFFFu;
-  if (threadIdx.x < QD_MAXQ) stage_n[threadIdx.x] = 0;
-  if (threadIdx.x == 0) queue_n = 0;
   __syncthreads();
-  // a wanted record only queues its row index: the value fetch (a random access) happens after
-  // the streaming loop, all lanes at once, instead of stalling the warp in the middle of it
-  auto hit = [&](int64_t i, uint32_t d) {
-    const uint32_t qp = atomicAdd(&queue_n, 1u);
-    if (qp < (uint32_t)QD_QUEUE) {
-      queue[qp] = (uint32_t)i;   // n < 2^31 on this path
-      return;
-    }
-    // queue full (tens of thousands of wanted records in one CTA): handle it in place
+  // key of a wanted record -> sub-histogram + staged list entry
+  auto take = [&](int64_t i, uint32_t d) {
+    const uint64_t key = kvm_key(values[i]);
 #pragma unroll
     for (int k = 0; k < QD_MAXQ; ++k)
       if (d == want[k]) {
-        const uint64_t key = kvm_key(values[i]);
-        const uint32_t sp = atomicAdd(&stage_n[k], 1u);
+        const uint64_t bin_base = base + ((uint64_t)(d - 1) << bshift);
+        atomicAdd(&ws->hist2[k][(uint32_t)((key - bin_base) >> sh2) & (QD_SUB - 1)], 1u);
+        const uint32_t sp = atomicAdd(&S.stage_n[k], 1u);
         if (sp < (uint32_t)QD_STAGE) {
-          stage[k][sp] = key;
+          S.stage[k][sp] = key;
         } else {  // the stage is full: straight to the list
           const unsigned long long pos = atomicAdd(&ws->list_n[k], 1ull);
           if (pos < (unsigned long long)cap) lists[(size_t)k * (size_t)cap + pos] = key;
         }
       }
   };
-  // branch-free membership test in registers: a record's digit is compared with the wanted bins
-  // (4 of them when that is all there are - the usual case: three percentiles whose lo and hi
-  // ranks share a bin); only a real hit leaves the straight-line code
-  // both 16-bit records of a word are tested at once: x = w ^ (bin | bin << 16) has a zero half
-  // where a record equals the bin, and (x - 0x00010001) & ~x & 0x80008000 flags zero halves (a
-  // borrow can only raise a false flag above a true one; the hit path re-checks exactly)
+  // a wanted record only queues its row index: the value fetch (a random access) happens after
+  // the streaming loop, all lanes at once, instead of stalling the warp in the middle of it
+  auto hit = [&](int64_t i, uint32_t d) {
+    const uint32_t qp = atomicAdd(&S.queue_n, 1u);
+    if (qp < (uint32_t)QD_QUEUE) S.queue[qp] = (uint32_t)i;   // n < 2^31 on this path
+    else take(i, d);                                            // queue full: handle it in place
+  };
+  // branch-free membership test in registers: both 16-bit records of a word are tested at once:
+  // x = w ^ (bin | bin << 16) has a zero half where a record equals the bin, and
+  // (x - 0x00010001) & ~x & 0x80008000 flags zero halves (a borrow can only raise a false flag
+  // above a true one; the hit path re-checks exactly)
   const bool few = nslots <= 4;
   uint32_t want2[QD_MAXQ];
 #pragma unroll
@@ -360,186 +585,90 @@ qd_collect_kernel(const double* __restrict__ values, int64_t n, const uint16_t* 
     z &= 0x80008000u;
     if (z) {
       const uint32_t d0 = w & 0xFFFFu, d1 = w >> 16;
-      if ((z & 0x8000u) && d0 != 0xFFFFu) hit(i, d0);
-      if ((z >> 16) && d1 != 0xFFFFu) hit(i + 1, d1);
+      if ((z & 0x8000u) && d0 != 0xFFFFu) {
+        bool w0 = false;
+#pragma unroll
+        for (int k = 0; k < QD_MAXQ; ++k) w0 |= d0 == want[k];
+        if (w0) hit(i, d0);
+      }
+      if ((z >> 16) && d1 != 0xFFFFu) {
+        bool w1 = false;
+#pragma unroll
+        for (int k = 0; k < QD_MAXQ; ++k) w1 |= d1 == want[k];
+        if (w1) hit(i + 1, d1);
+      }
     }
   };
   if (VEC) {
-    const int64_t noct = n >> 3;
-    // 32 contiguous bytes (16 records) per thread and iteration, two loads in flight
-    const int64_t npair = noct >> 1;
-    const uint4* __restrict__ r16 = reinterpret_cast<const uint4*>(recs);
-    for (int64_t o = (int64_t)blockIdx.x * QD_THREADS + threadIdx.x; o < npair; o += (int64_t)gridDim.x * QD_THREADS) {
-      const uint4 r0 = __ldg(r16 + 2 * o), r1 = __ldg(r16 + 2 * o + 1);
-      const int64_t i = o << 4;
-      word(i, r0.x);
-      word(i + 2, r0.y);
-      word(i + 4, r0.z);
-      word(i + 6, r0.w);
-      word(i + 8, r1.x);
-      word(i + 10, r1.y);
-      word(i + 12, r1.z);
-      word(i + 14, r1.w);
+    // 32 contiguous bytes (16 records) per thread and iteration; CTA b owns a contiguous range
+    const int64_t nunits = n >> 4;
+    const int64_t chunk = (nunits + gridDim.x - 1) / gridDim.x;
+    const int64_t u_end = min(nunits, ((int64_t)blockIdx.x + 1) * chunk);
+    for (int64_t u0 = (int64_t)blockIdx.x * chunk + t; u0 < u_end; u0 += 2 * QD_THREADS) {
+      const int64_t u1 = u0 + QD_THREADS;
+      const kvm_u64x4 r0 = kvm_ld4(recs + (u0 << 4));
+      kvm_u64x4 r1{~0ull, ~0ull, ~0ull, ~0ull};
+      if (u1 < u_end) r1 = kvm_ld4(recs + (u1 << 4));
+      const int64_t i = u0 << 4, j = u1 << 4;
+      word(i, (uint32_t)r0.x); word(i + 2, (uint32_t)(r0.x >> 32));
+      word(i + 4, (uint32_t)r0.y); word(i + 6, (uint32_t)(r0.y >> 32));
+      word(i + 8, (uint32_t)r0.z); word(i + 10, (uint32_t)(r0.z >> 32));
+      word(i + 12, (uint32_t)r0.w); word(i + 14, (uint32_t)(r0.w >> 32));
+      word(j, (uint32_t)r1.x); word(j + 2, (uint32_t)(r1.x >> 32));
+      word(j + 4, (uint32_t)r1.y); word(j + 6, (uint32_t)(r1.y >> 32));
+      word(j + 8, (uint32_t)r1.z); word(j + 10, (uint32_t)(r1.z >> 32));
+      word(j + 12, (uint32_t)r1.w); word(j + 14, (uint32_t)(r1.w >> 32));
     }
-    if ((noct & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
-      const uint4 r0 = __ldg(r16 + noct - 1);
-      const int64_t i = (noct - 1) << 3;
-      word(i, r0.x);
-      word(i + 2, r0.y);
-      word(i + 4, r0.z);
-      word(i + 6, r0.w);
-    }
-    if (blockIdx.x == 0 && threadIdx.x < (n & 7)) {
-      const int64_t i = (n & ~7ll) + threadIdx.x;
+    if (blockIdx.x == 0 && t < (n & 15)) {
+      const int64_t i = (n & ~15ll) + t;
       word(i, (uint32_t)recs[i] | 0xFFFF0000u);   // upper half: "not a member"
     }
   } else {
-    for (int64_t i = (int64_t)blockIdx.x * QD_THREADS + threadIdx.x; i < n; i += (int64_t)gridDim.x * QD_THREADS)
+    for (int64_t i = (int64_t)blockIdx.x * QD_THREADS + t; i < n; i += (int64_t)gridDim.x * QD_THREADS)
       word(i, (uint32_t)recs[i] | 0xFFFF0000u);
   }
   __syncthreads();
   {  // drain the queue: every thread takes queued rows, fetches the value, appends the key
-    const uint32_t qn = queue_n < (uint32_t)QD_QUEUE ? queue_n : (uint32_t)QD_QUEUE;
-    for (uint32_t j = threadIdx.x; j < qn; j += QD_THREADS) {
-      const int64_t i = (int64_t)queue[j];
-      const uint32_t d = recs[i];
-      const uint64_t key = kvm_key(values[i]);
-#pragma unroll
-      for (int k = 0; k < QD_MAXQ; ++k)
-        if (d == want[k]) {
-          const uint32_t sp = atomicAdd(&stage_n[k], 1u);
-          if (sp < (uint32_t)QD_STAGE) {
-            stage[k][sp] = key;
-          } else {
-            const unsigned long long pos = atomicAdd(&ws->list_n[k], 1ull);
-            if (pos < (unsigned long long)cap) lists[(size_t)k * (size_t)cap + pos] = key;
-          }
-        }
+    const uint32_t qn = S.queue_n < (uint32_t)QD_QUEUE ? S.queue_n : (uint32_t)QD_QUEUE;
+    for (uint32_t j = t; j < qn; j += QD_THREADS) {
+      const int64_t i = (int64_t)S.queue[j];
+      take(i, (uint32_t)recs[i]);
     }
   }
   __syncthreads();
-  if (threadIdx.x < QD_MAXQ) {
-    const uint32_t c = stage_n[threadIdx.x] < (uint32_t)QD_STAGE ? stage_n[threadIdx.x] : (uint32_t)QD_STAGE;
-    stage_n[threadIdx.x] = c;
-    if (c) stage_pos[threadIdx.x] = atomicAdd(&ws->list_n[threadIdx.x], (unsigned long long)c);
+  if (t < QD_MAXQ) {
+    const uint32_t c = S.stage_n[t] < (uint32_t)QD_STAGE ? S.stage_n[t] : (uint32_t)QD_STAGE;
+    S.stage_n[t] = c;
+    if (c) S.stage_pos[t] = atomicAdd(&ws->list_n[t], (unsigned long long)c);
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < QD_MAXQ * QD_STAGE; i += QD_THREADS) {
+  for (int i = t; i < QD_MAXQ * QD_STAGE; i += QD_THREADS) {
     const int k = i / QD_STAGE, j = i % QD_STAGE;
-    if ((uint32_t)j < stage_n[k]) {
-      const unsigned long long pos = stage_pos[k] + j;
-      if (pos < (unsigned long long)cap) lists[(size_t)k * (size_t)cap + pos] = stage[k][j];
+    if ((uint32_t)j < S.stage_n[k]) {
+      const unsigned long long pos = S.stage_pos[k] + j;
+      if (pos < (unsigned long long)cap) lists[(size_t)k * (size_t)cap + pos] = S.stage[k][j];
     }
   }
-}
-
-// ------------------------------------------------------------------ rank
-__global__ void __launch_bounds__(1024, 1)
-qd_rank_kernel(QdWs* ws, const uint64_t* __restrict__ lists, kvm_query_result* __restrict__ results) {
-  __shared__ uint32_t hist[2048];
-  __shared__ uint64_t wmin[32], wmax[32];
-  __shared__ uint32_t wtot[32];
-  __shared__ uint32_t sel_bin, sel_resid, small_n;
-  __shared__ uint64_t answer;
-  const int q = blockIdx.x;
-  if (q >= ws->nq) return;
-  const QdQuery s = ws->q[q];
-  const double nan = __longlong_as_double(0x7ff8000000000000ll);
-  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-  const bool need = ws->status == KVM_OK && s.valid && s.qstatus == KVM_Q_OK;
-  if (!need) {
-    // empty multiset / rank out of range: nothing to look up; a declined call reports NaN
-    if (t == 0) results[q] = kvm_query_result{nan, s.n, s.rank, s.qstatus, 0};
-    return;
-  }
-  const long long cap = ws->list_cap;
-  const unsigned long long m = ws->list_n[s.slot];
-  if (m > (unsigned long long)cap || (long long)m <= s.resid) {
-    if (t == 0) {
-      ws->status = KVM_ERR_UNSUPPORTED;  // all writers agree
-      results[q] = kvm_query_result{nan, s.n, s.rank, s.qstatus, 0};
-    }
-    return;
-  }
-  const uint64_t* __restrict__ keys = lists + (size_t)s.slot * (size_t)cap;
-  uint64_t* small = ws->small[q];
-  // the keys of bin d lie in [base + (d-1) << shift, base + d << shift): no min/max pass needed
-  (void)wmin;
-  (void)wmax;
-  hist[t] = 0;
-  hist[t + 1024] = 0;
-  if (t == 0) small_n = 0;
-  const int bshift = ws->shift;
-  const uint64_t mn = ws->base + ((uint64_t)(s.bin - 1) << bshift);
-  const int sh2 = bshift > 11 ? bshift - 11 : 0;
+  // ---- last CTA to get here finishes the queries, one group of threads per query
+  __threadfence();
   __syncthreads();
-  for (unsigned long long i0 = t; i0 < m; i0 += 8 * 1024) {
-    uint64_t kk[8];
-#pragma unroll
-    for (int u = 0; u < 8; ++u) kk[u] = i0 + u * 1024 < m ? __ldcg(keys + i0 + u * 1024) : QD_NONE;
-#pragma unroll
-    for (int u = 0; u < 8; ++u)
-      if (kk[u] != QD_NONE) atomicAdd(&hist[(uint32_t)((kk[u] - mn) >> sh2) & 2047u], 1u);
-  }
+  if (t == 0) S.is_last = atomicAdd(&ws->c_ticket, 1u) == gridDim.x - 1;
   __syncthreads();
+  if (!S.is_last) return;
+  __threadfence();
   {
-    const uint32_t c0 = hist[2 * t], c1 = hist[2 * t + 1];
-    uint32_t incl = c0 + c1;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-      const uint32_t o = __shfl_up_sync(KVM_FULL, incl, d);
-      if (lane >= d) incl += o;
-    }
-    if (lane == 31) wtot[warp] = incl;
-    __syncthreads();
-    long long before = (long long)(incl - (c0 + c1));
-    for (int w = 0; w < warp; ++w) before += wtot[w];
-    const long long r = s.resid;
-    if (before <= r && r < before + c0) {
-      sel_bin = 2 * t;
-      sel_resid = (uint32_t)(r - before);
-    } else if (before + c0 <= r && r < before + c0 + c1) {
-      sel_bin = 2 * t + 1;
-      sel_resid = (uint32_t)(r - before - c0);
-    }
+    const int g = t / QD_GROUP, gt = t % QD_GROUP;
+    uint32_t* gs = reinterpret_cast<uint32_t*>(&S.stage[0][0]) + g * (QD_GROUP + 16);   // the stages are free now
+    if (g < ws->nq) qd_finish_query(ws, lists, g, gt, 1 + g, gs, results);
   }
   __syncthreads();
-  const uint32_t sb = sel_bin, sr = sel_resid;
-  for (unsigned long long i0 = t; i0 < m; i0 += 8 * 1024) {
-    uint64_t kk[8];
-#pragma unroll
-    for (int u = 0; u < 8; ++u) kk[u] = i0 + u * 1024 < m ? __ldcg(keys + i0 + u * 1024) : QD_NONE;
-#pragma unroll
-    for (int u = 0; u < 8; ++u)
-      if (kk[u] != QD_NONE && ((uint32_t)((kk[u] - mn) >> sh2) & 2047u) == sb) {
-        const uint32_t pos = atomicAdd(&small_n, 1u);
-        if (pos < (uint32_t)QD_SMALL) small[pos] = kk[u];
-      }
-  }
-  __syncthreads();
-  const uint32_t m2 = small_n;
-  if (m2 > (uint32_t)QD_SMALL) {  // one value repeated thousands of times: the general select's job
-    if (t == 0) {
-      ws->status = KVM_ERR_UNSUPPORTED;
-      results[q] = kvm_query_result{nan, s.n, s.rank, s.qstatus, 0};
-    }
-    return;
-  }
-  for (unsigned i = t; i < m2; i += 1024) {
-    const uint64_t k = small[i];
-    uint32_t less = 0, leq = 0;
-    for (unsigned j = 0; j < m2; ++j) {
-      const uint64_t o = small[j];
-      less += o < k;
-      leq += o <= k;
-    }
-    if (less <= sr && sr < leq) answer = k;  // all writers agree
-  }
-  __syncthreads();
-  if (t == 0) results[q] = kvm_query_result{kvm_unkey(answer), s.n, s.rank, KVM_Q_OK, 0};
+  if (t == 0) ws->ready = 0ull;   // a replay of the same launch sequence (same token) waits for its own clearing
 }
 
-int qd_grid(int64_t n) { return kvm_grid_for(n, QD_THREADS * 4 * 4, 2); }
+// two resident CTAs per SM, each with a contiguous share of the rows
+int qd_grid(int64_t n, int rows_per_thread_iter) {
+  return kvm_grid_for(n, QD_THREADS * rows_per_thread_iter, 2);
+}
 long long qd_list_cap(int64_t n) {
   const long long c = (long long)(n / 64) + 16384;   // a bin holds ~n/1500 of smooth data
   return (c + 1) & ~1ll;
@@ -551,7 +680,7 @@ extern "C" int64_t kvm_column_select_sampled_min_n(void) { return 1 << 18; }
 
 extern "C" size_t kvm_column_select_sampled_workspace_bytes(int64_t n) {
   if (n < 0) n = 0;
-  return QD_HEADER + kvm_align_up((size_t)n * sizeof(uint16_t) + 16, 256) +
+  return QD_HEADER + kvm_align_up((size_t)n * sizeof(uint16_t) + 32, 256) +
          (size_t)QD_MAXQ * (size_t)qd_list_cap(n) * sizeof(uint64_t) + 256;
 }
 
@@ -581,29 +710,42 @@ extern "C" int kvm_column_select_sampled(const double* values, int64_t n, int32_
                   kvm_column_select_sampled_workspace_bytes(n));
     return KVM_ERR_WORKSPACE;
   }
+  KVM_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255u) == 0, "kvm_column_select_sampled: workspace must be 256-byte aligned");
   cudaStream_t st = (cudaStream_t)stream;
   unsigned char* wsb = reinterpret_cast<unsigned char*>(workspace);
   QdWs* ws = reinterpret_cast<QdWs*>(wsb);
   uint16_t* recs = reinterpret_cast<uint16_t*>(wsb + QD_HEADER);
-  uint64_t* lists = reinterpret_cast<uint64_t*>(wsb + QD_HEADER + kvm_align_up((size_t)n * sizeof(uint16_t) + 16, 256));
+  uint64_t* lists = reinterpret_cast<uint64_t*>(wsb + QD_HEADER + kvm_align_up((size_t)n * sizeof(uint16_t) + 32, 256));
   const long long cap = qd_list_cap(n);
-  const int grid = qd_grid(n);
-  const bool vec = (reinterpret_cast<uintptr_t>(values) & 15u) == 0 &&
-                   (mode != KVM_MEMBER_STATUS || (reinterpret_cast<uintptr_t>(member) & 15u) == 0);
-  KVM_CUDA_CHECK(cudaMemsetAsync(wsb + QD_CLEAR_BEGIN, 0, QD_CLEAR_END - QD_CLEAR_BEGIN, st));
-  constexpr int STH = QD_SAMPLE / QD_SAMPLE_CTAS;
+  const int grid = qd_grid(n, 8 * 4);
+  const bool vec = (reinterpret_cast<uintptr_t>(values) & 31u) == 0 &&
+                   (mode != KVM_MEMBER_STATUS || (reinterpret_cast<uintptr_t>(member) & 31u) == 0);
+  // per-call token for the clear-then-flush handshake inside the hist kernel (never 0; the collect
+  // kernel resets the word at its end, so a graph replay with the same token works)
+  static std::atomic<unsigned long long> call_counter{0x9e3779b97f4a7c15ull};
+  const unsigned long long token = call_counter.fetch_add(0x9e3779b97f4a7c15ull) | 1ull;
   if (mode == KVM_MEMBER_STATUS) {
-    qd_sample_kernel<KVM_MEMBER_STATUS><<<QD_SAMPLE_CTAS, STH, 0, st>>>(values, n, member, a, ws, cap);
-    if (vec) qd_hist_kernel<KVM_MEMBER_STATUS, true><<<grid, QD_THREADS, 0, st>>>(values, n, member, ws, recs);
-    else qd_hist_kernel<KVM_MEMBER_STATUS, false><<<grid, QD_THREADS, 0, st>>>(values, n, member, ws, recs);
+    if (vec) qd_hist_kernel<KVM_MEMBER_STATUS, true><<<grid, QD_THREADS, 0, st>>>(values, n, member, ws, recs, a, cap, token);
+    else qd_hist_kernel<KVM_MEMBER_STATUS, false><<<grid, QD_THREADS, 0, st>>>(values, n, member, ws, recs, a, cap, token);
   } else {
-    qd_sample_kernel<KVM_MEMBER_ALL><<<QD_SAMPLE_CTAS, STH, 0, st>>>(values, n, member, a, ws, cap);
-    if (vec) qd_hist_kernel<KVM_MEMBER_ALL, true><<<grid, QD_THREADS, 0, st>>>(values, n, member, ws, recs);
-    else qd_hist_kernel<KVM_MEMBER_ALL, false><<<grid, QD_THREADS, 0, st>>>(values, n, member, ws, recs);
+    if (vec) qd_hist_kernel<KVM_MEMBER_ALL, true><<<grid, QD_THREADS, 0, st>>>(values, n, member, ws, recs, a, cap, token);
+    else qd_hist_kernel<KVM_MEMBER_ALL, false><<<grid, QD_THREADS, 0, st>>>(values, n, member, ws, recs, a, cap, token);
   }
-  qd_resolve_kernel<<<1, 1024, 0, st>>>(ws);
-  qd_collect_kernel<true><<<kvm_grid_for(n, QD_THREADS * 8 * 4, 2), QD_THREADS, 0, st>>>(values, n, recs, ws, lists);
-  qd_rank_kernel<<<nq, 1024, 0, st>>>(ws, lists, results);
   KVM_CUDA_CHECK(cudaGetLastError());
+  // the collect kernel is a programmatic dependent launch: it may become resident while the hist
+  // kernel drains and blocks in griddepcontrol.wait until that kernel has completed
+  static const bool no_pdl = getenv("KVM_NO_PDL") != nullptr;
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3((unsigned)qd_grid(n, 16 * 4));
+  cfg.blockDim = dim3(QD_THREADS);
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = no_pdl ? 0 : 1;
+  const uint16_t* recs_c = recs;
+  KVM_CUDA_CHECK(cudaLaunchKernelEx(&cfg, qd_collect_kernel<true>, values, n, recs_c, ws, lists, results));
   return KVM_OK;
 }

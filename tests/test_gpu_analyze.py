@@ -452,3 +452,74 @@ def test_sampled_select_edges():
     assert lib.kvm_column_select_sampled(d.data_ptr(), n, N.MEMBER_ALL, None, absolute, 1, res.data_ptr(),
                                          ws.data_ptr(), ws.numel(), None) == N.KVM_ERR_UNSUPPORTED
 
+
+
+def test_sampled_select_dirty_workspace_and_graph_replay():
+    """The sampled select clears its own accumulators inside its first kernel (no memset) behind a
+    per-call token: a workspace full of garbage, the same workspace reused for other data, and a
+    CUDA-graph replay of one captured call (same token every time) must all give exact answers."""
+    import ctypes as C
+    import torch
+    from kvmini_b200 import _native as N
+    from kvmini_b200.engine import RESULT_DTYPE
+    lib = N.lib()
+    dev = torch.device("cuda", 0)
+    rng = np.random.default_rng(5)
+    sizes = (1 << 18, 300_007, 1_000_000, 2_000_019)
+    q = (N.QueryC * 6)(*[N.QueryC(1, k, p, 0) for p in (0.5, 0.95, 0.99) for k in (N.RANK_LERP_LO, N.RANK_LERP_HI)])
+    ws = torch.empty(lib.kvm_column_select_sampled_workspace_bytes(max(sizes)), dtype=torch.uint8, device=dev)
+    res = torch.zeros(6 * 32, dtype=torch.uint8, device=dev)
+    st = torch.cuda.current_stream(dev).cuda_stream
+
+    def expect(v, s):
+        ok = np.sort(v[(s == 200) & ~np.isnan(v)])
+        out = []
+        for p in (0.5, 0.95, 0.99):
+            pos = p * (len(ok) - 1)
+            out += [ok[int(math.floor(pos))], ok[int(math.ceil(pos))]]
+        return out, len(ok)
+
+    def read():
+        torch.cuda.synchronize()
+        assert int(ws[0:4].view(torch.int32).item()) == 0, "declined"
+        return np.frombuffer(res.cpu().numpy().tobytes(), dtype=RESULT_DTYPE, count=6)
+
+    for rep, n in enumerate(sizes + sizes[::-1]):
+        v = np.round(rng.lognormal(5.0 + 0.2 * rep, 0.5, n), 3)
+        s = np.where(rng.random(n) < 0.9, 200, 500).astype(np.int64)
+        d_v, d_s = torch.from_numpy(v).to(dev), torch.from_numpy(s).to(dev)
+        if rep % 2 == 0:
+            ws.random_(0, 256)            # garbage everywhere, the handshake word included
+        N.check(lib.kvm_column_select_sampled(d_v.data_ptr(), n, N.MEMBER_STATUS, d_s.data_ptr(), q, 6,
+                                              res.data_ptr(), ws.data_ptr(), ws.numel(), st))
+        want, m = expect(v, s)
+        got = read()
+        assert [float(x) for x in got["value"]] == want and all(int(x) == m for x in got["n"]), (rep, n)
+    # one captured call replayed on changing data (in place): same token on every replay
+    n = 1_000_000
+    d_v = torch.empty(n, dtype=torch.float64, device=dev)
+    d_s = torch.empty(n, dtype=torch.int64, device=dev)
+    side = torch.cuda.Stream(dev)
+    with torch.cuda.stream(side):
+        def call():
+            N.check(lib.kvm_column_select_sampled(d_v.data_ptr(), n, N.MEMBER_STATUS, d_s.data_ptr(), q, 6,
+                                                  res.data_ptr(), ws.data_ptr(), ws.numel(),
+                                                  torch.cuda.current_stream(dev).cuda_stream))
+        d_v.fill_(1.0)
+        d_s.fill_(200)
+        call()
+        side.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=side):
+            call()
+        for rep in range(5):
+            v = np.round(rng.lognormal(4.0 + rep, 0.7, n), 3)
+            s = np.where(rng.random(n) < 0.8, 200, 503).astype(np.int64)
+            d_v.copy_(torch.from_numpy(v))
+            d_s.copy_(torch.from_numpy(s))
+            g.replay()
+            g.replay()       # back to back: the second replay must wait for its own clearing
+            side.synchronize()
+            want, m = expect(v, s)
+            got = read()
+            assert [float(x) for x in got["value"]] == want and all(int(x) == m for x in got["n"]), rep
