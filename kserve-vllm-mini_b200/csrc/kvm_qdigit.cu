@@ -17,7 +17,8 @@
 //            its digit is a wanted bin (~0.1 % of the records): its key goes to that bin's list and
 //            its next 11 bits into that bin's sub-histogram.
 //            epilogue (last CTA, ticket): one 64-thread group per query walks the sub-histogram to
-//            the sub-bin holding the rank and ranks the handful of keys of that sub-bin.
+//            the sub-bin holding the rank; all threads then stream the lists once and the handful
+//            of keys of each query's sub-bin is ranked.
 // Exact whenever it answers.  It declines (status word KVM_ERR_UNSUPPORTED, the caller runs the
 // general select) when a rank falls into a catch-all bin (the sample missed the range), when a
 // list overflows (heavy duplicates spread over many keys) or when the sample holds too few members.
@@ -381,130 +382,177 @@ struct QdCollectSmem {
   int is_last;
 };
 
-// One query, finished by a group of QD_GROUP threads of the last CTA (named barrier `bar`):
-// walk the wanted bin's sub-histogram to the sub-bin holding the residual rank, then look at the
-// keys of that sub-bin only - usually a handful, or thousands of copies of ONE key (values
-// rounded to three decimals), which min == max settles without ranking anything.
-__device__ __forceinline__ void qd_finish_query(QdWs* ws, const uint64_t* __restrict__ lists, int q, int gt,
-                                                int bar, uint32_t* gs /* [QD_GROUP + 8] shared words of the group */,
-                                                kvm_query_result* __restrict__ results) {
-  auto gsync = [&]() { asm volatile("bar.sync %0, %1;" ::"r"(bar), "r"(QD_GROUP) : "memory"); };
+// Finish of all queries by the last CTA of the collect kernel.  Three phases:
+//   A  one group of QD_GROUP threads per query walks the wanted bin's sub-histogram to the sub-bin
+//      holding the residual rank;
+//   B  ALL threads stream the slot lists once (every load of a thread is in flight at the same
+//      time - a 64-thread group would need dozens of dependent round trips to L2); a key that
+//      lies in the sub-bin of a query updates that query's min / max and is gathered;
+//   C  per query: min == max settles it (thousands of copies of one key - values rounded to three
+//      decimals - need no ranking), otherwise the handful of gathered keys is ranked by counting.
+struct QdFinSmem {
+  uint32_t gsum[QD_MAXQ][QD_GROUP];
+  uint32_t sb[QD_MAXQ], sr[QD_MAXQ], scount[QD_MAXQ], cnt[QD_MAXQ];
+  int32_t state[QD_MAXQ];   // 0: nothing to look up, 1: answered, 2: needs its sub-bin's keys, 3: decline
+  int32_t slot[QD_MAXQ];
+  unsigned long long kmin[QD_MAXQ], kmax[QD_MAXQ];
+  unsigned long long slot_m[QD_MAXQ], slot_base[QD_MAXQ], slot_begin[QD_MAXQ + 1];
+};
+
+__device__ __noinline__ void qd_finish(QdWs* ws, const uint64_t* __restrict__ lists, QdFinSmem& F,
+                                          kvm_query_result* __restrict__ results) {
+  const int t = threadIdx.x, g = t / QD_GROUP, gt = t % QD_GROUP;
   const double nan = __longlong_as_double(0x7ff8000000000000ll);
-  const QdQuery s = ws->q[q];
-  const bool need = ws->status == KVM_OK && s.valid && s.qstatus == KVM_Q_OK;
-  if (!need) {   // empty multiset / rank out of range: nothing to look up; a declined call reports NaN
-    if (gt == 0) results[q] = kvm_query_result{nan, s.n, s.rank, s.qstatus, 0};
+  const int nq = ws->nq, nslots = ws->nslots;
+  const long long cap = ws->list_cap;
+  const int bshift = ws->shift;
+  const int sh2 = bshift > QD_SUB_BITS ? bshift - QD_SUB_BITS : 0;
+  const uint64_t base = ws->base;
+  if (t < QD_MAXQ) {
+    const unsigned long long m = t < nslots ? __ldcg(&ws->list_n[t]) : 0ull;
+    F.slot_m[t] = m;
+    F.slot_base[t] = t < nslots ? base + ((uint64_t)(ws->slot_bin[t] - 1) << bshift) : 0ull;
+    F.kmin[t] = QD_NONE;
+    F.kmax[t] = 0ull;
+    F.cnt[t] = 0;
+    F.state[t] = 0;
+  }
+  __syncthreads();
+  if (t == 0) {
+    unsigned long long acc = 0;
+    for (int k = 0; k < QD_MAXQ; ++k) {
+      F.slot_begin[k] = acc;
+      acc += F.slot_m[k] <= (unsigned long long)cap ? F.slot_m[k] : 0ull;   // an overflowed list is not scanned
+    }
+    F.slot_begin[QD_MAXQ] = acc;
+  }
+  // ---- A: sub-bin of every query
+  QdQuery s{};
+  bool need = false;
+  if (g < nq) {
+    s = ws->q[g];
+    need = s.valid && s.qstatus == KVM_Q_OK;
+    if (gt == 0) F.slot[g] = need ? s.slot : -1;
+  }
+  constexpr int PER = QD_SUB / QD_GROUP;
+  uint32_t c[PER], local = 0;
+  bool overflow = false;
+  if (need) {
+    const unsigned long long m = F.slot_m[s.slot];
+    overflow = m > (unsigned long long)cap || (long long)m <= s.resid;
+    if (!overflow) {
+      const unsigned int* __restrict__ h2 = ws->hist2[s.slot];
+#pragma unroll
+      for (int k = 0; k < PER; k += 4) {
+        const uint4 x = __ldcg(reinterpret_cast<const uint4*>(h2 + gt * PER + k));
+        c[k] = x.x; c[k + 1] = x.y; c[k + 2] = x.z; c[k + 3] = x.w;
+        local += x.x + x.y + x.z + x.w;
+      }
+    }
+    F.gsum[g][gt] = local;
+  }
+  __syncthreads();
+  if (need && !overflow) {
+    uint32_t before = 0;
+    for (int k = 0; k < gt; ++k) before += F.gsum[g][k];
+    const uint32_t r = (uint32_t)s.resid;
+    if (before <= r && r < before + local) {
+      uint32_t b = before;
+      int k = 0;
+      for (; k < PER - 1; ++k) {
+        if (r < b + c[k]) break;
+        b += c[k];
+      }
+      F.sb[g] = (uint32_t)(gt * PER + k);   // the sub-bin
+      F.sr[g] = r - b;                      // rank inside it
+      F.scount[g] = c[k];                   // its population
+      F.state[g] = sh2 == 0 ? 1 : (c[k] <= (uint32_t)QD_SMALL ? 2 : 4);   // 4: too many to gather - min/max only
+    }
+  } else if (need && gt == 0) {
+    F.state[g] = 3;
+  }
+  __syncthreads();
+  // ---- B: one pass of all threads over all slot lists
+  {
+    const unsigned long long total = F.slot_begin[QD_MAXQ];
+    constexpr int U = 8;
+    for (unsigned long long i0 = t; i0 < total; i0 += (unsigned long long)U * QD_THREADS) {
+      uint64_t kk[U];
+      int ks[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const unsigned long long i = i0 + (unsigned long long)u * QD_THREADS;
+        ks[u] = -1;
+        kk[u] = 0;
+        if (i < total) {
+          int k = 0;
+#pragma unroll
+          for (int j = 1; j < QD_MAXQ; ++j) k += i >= F.slot_begin[j];
+          ks[u] = k;
+          kk[u] = __ldcg(lists + (size_t)k * (size_t)cap + (size_t)(i - F.slot_begin[k]));
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        if (ks[u] < 0) continue;
+        const uint32_t sub = (uint32_t)((kk[u] - F.slot_base[ks[u]]) >> sh2);
+        for (int q = 0; q < nq; ++q) {
+          const int stq = F.state[q];
+          if ((stq == 2 || stq == 4) && F.slot[q] == ks[u] && F.sb[q] == sub) {
+            atomicMin(&F.kmin[q], (unsigned long long)kk[u]);
+            atomicMax(&F.kmax[q], (unsigned long long)kk[u]);
+            if (stq == 2) {
+              const uint32_t pos = atomicAdd(&F.cnt[q], 1u);
+              if (pos < (uint32_t)QD_SMALL) ws->small[q][pos] = kk[u];
+            }
+          }
+        }
+      }
+    }
+  }
+  __threadfence_block();
+  __syncthreads();
+  // ---- C: answers
+  if (g >= nq) return;
+  const int stq = F.state[g];
+  if (stq == 0) {   // empty multiset / rank out of range: nothing to look up
+    if (gt == 0) results[g] = kvm_query_result{nan, s.n, s.rank, s.qstatus, 0};
     return;
   }
-  const long long cap = ws->list_cap;
-  const unsigned long long m = __ldcg(&ws->list_n[s.slot]);
   auto decline = [&]() {
     if (gt == 0) {
       ws->status = KVM_ERR_UNSUPPORTED;  // all writers agree
-      results[q] = kvm_query_result{nan, s.n, s.rank, s.qstatus, 0};
+      results[g] = kvm_query_result{nan, s.n, s.rank, s.qstatus, 0};
     }
   };
-  if (m > (unsigned long long)cap || (long long)m <= s.resid) {
+  if (stq == 3) {
     decline();
     return;
   }
-  const int bshift = ws->shift;
-  const uint64_t bin_base = ws->base + ((uint64_t)(s.bin - 1) << bshift);
-  const int sh2 = bshift > QD_SUB_BITS ? bshift - QD_SUB_BITS : 0;
-  // ---- sub-bin: every thread sums QD_SUB / QD_GROUP consecutive sub-bins, the group scans the sums
-  constexpr int PER = QD_SUB / QD_GROUP;
-  const unsigned int* __restrict__ h2 = ws->hist2[s.slot];
-  uint32_t c[PER], local = 0;
-#pragma unroll
-  for (int k = 0; k < PER; k += 4) {
-    const uint4 x = __ldcg(reinterpret_cast<const uint4*>(h2 + gt * PER + k));
-    c[k] = x.x; c[k + 1] = x.y; c[k + 2] = x.z; c[k + 3] = x.w;
-    local += x.x + x.y + x.z + x.w;
-  }
-  gs[gt] = local;
-  gsync();
-  uint32_t before = 0;
-  for (int k = 0; k < gt; ++k) before += gs[k];
-  const uint32_t r = (uint32_t)s.resid;
-  if (before <= r && r < before + local) {
-    uint32_t b = before;
-    int k = 0;
-    for (; k < PER - 1; ++k) {
-      if (r < b + c[k]) break;
-      b += c[k];
-    }
-    gs[QD_GROUP] = (uint32_t)(gt * PER + k);   // the sub-bin
-    gs[QD_GROUP + 1] = r - b;                  // rank inside it
-    gs[QD_GROUP + 2] = c[k];                   // its population
-  }
-  if (gt == 0) {
-    gs[QD_GROUP + 3] = 0;   // keys gathered
-  }
-  gsync();
-  const uint32_t sb = gs[QD_GROUP], sr = gs[QD_GROUP + 1], scount = gs[QD_GROUP + 2];
-  if (sh2 == 0) {   // the sub-bin is one key
-    if (gt == 0) results[q] = kvm_query_result{kvm_unkey(bin_base + sb), s.n, s.rank, KVM_Q_OK, 0};
+  if (stq == 1) {   // the sub-bin is one key
+    if (gt == 0) results[g] = kvm_query_result{kvm_unkey(F.slot_base[s.slot] + F.sb[g]), s.n, s.rank, KVM_Q_OK, 0};
     return;
   }
-  // ---- keys of the sub-bin: min / max over the group decide the all-equal case, otherwise they
-  // are gathered (global scratch) and ranked by counting
-  const uint64_t* __restrict__ keys = lists + (size_t)s.slot * (size_t)cap;
-  uint64_t* small = ws->small[q];
-  uint64_t kmin = QD_NONE, kmax = 0;
-  const bool gather = scount <= (uint32_t)QD_SMALL;
-  for (unsigned long long i0 = gt; i0 < m; i0 += 4 * QD_GROUP) {
-    uint64_t kk[4];
-#pragma unroll
-    for (int u = 0; u < 4; ++u) kk[u] = i0 + u * QD_GROUP < m ? __ldcg(keys + i0 + u * QD_GROUP) : QD_NONE;
-#pragma unroll
-    for (int u = 0; u < 4; ++u)
-      if (kk[u] != QD_NONE && (uint32_t)((kk[u] - bin_base) >> sh2) == sb) {
-        kmin = kk[u] < kmin ? kk[u] : kmin;
-        kmax = kk[u] > kmax ? kk[u] : kmax;
-        if (gather) {
-          const uint32_t pos = atomicAdd(&gs[QD_GROUP + 3], 1u);
-          if (pos < (uint32_t)QD_SMALL) small[pos] = kk[u];
-        }
-      }
-  }
-  kmin = kvm_warp_min(kmin);
-  kmax = kvm_warp_max(kmax);
-  uint64_t* g64 = reinterpret_cast<uint64_t*>(gs + QD_GROUP + 4);   // [2 warps][2]
-  if ((gt & 31) == 0) {
-    g64[2 * (gt >> 5)] = kmin;
-    g64[2 * (gt >> 5) + 1] = kmax;
-  }
-  __threadfence_block();
-  gsync();
-  for (int w = 0; w < QD_GROUP / 32; ++w) {
-    kmin = g64[2 * w] < kmin ? g64[2 * w] : kmin;
-    kmax = g64[2 * w + 1] > kmax ? g64[2 * w + 1] : kmax;
-  }
-  if (kmin == kmax) {   // one distinct key (any number of copies)
-    if (gt == 0) results[q] = kvm_query_result{kvm_unkey(kmin), s.n, s.rank, KVM_Q_OK, 0};
+  if (F.kmin[g] == F.kmax[g]) {   // one distinct key (any number of copies)
+    if (gt == 0) results[g] = kvm_query_result{kvm_unkey(F.kmin[g]), s.n, s.rank, KVM_Q_OK, 0};
     return;
   }
-  const uint32_t m2 = gs[QD_GROUP + 3];
-  if (!gather || m2 != scount) {   // too many distinct candidates for the scratch: the general select's job
+  const uint32_t m2 = F.cnt[g], sr = F.sr[g];
+  if (stq == 4 || m2 != F.scount[g]) {   // too many distinct candidates for the scratch: the general select's job
     decline();
     return;
   }
-  uint64_t ans = 0;
-  bool mine = false;
+  const uint64_t* small = ws->small[g];
   for (uint32_t i = gt; i < m2; i += QD_GROUP) {
-    const uint64_t k = small[i];
+    const uint64_t k = __ldcg(small + i);
     uint32_t less = 0, leq = 0;
     for (uint32_t j = 0; j < m2; ++j) {
-      const uint64_t x = small[j];
+      const uint64_t x = __ldcg(small + j);
       less += x < k;
       leq += x <= k;
     }
-    if (less <= sr && sr < leq) {
-      ans = k;
-      mine = true;
-    }
+    if (less <= sr && sr < leq) results[g] = kvm_query_result{kvm_unkey(k), s.n, s.rank, KVM_Q_OK, 0};  // all writers agree
   }
-  if (mine) results[q] = kvm_query_result{kvm_unkey(ans), s.n, s.rank, KVM_Q_OK, 0};  // all writers agree
 }
 
 // Streams the 2 B/record digit records; a record whose digit is a wanted bin has its value
@@ -656,11 +704,9 @@ qd_collect_kernel(const double* __restrict__ values, int64_t n, const uint16_t* 
   __syncthreads();
   if (!S.is_last) return;
   __threadfence();
-  {
-    const int g = t / QD_GROUP, gt = t % QD_GROUP;
-    uint32_t* gs = reinterpret_cast<uint32_t*>(&S.stage[0][0]) + g * (QD_GROUP + 16);   // the stages are free now
-    if (g < ws->nq) qd_finish_query(ws, lists, g, gt, 1 + g, gs, results);
-  }
+  // (the stages are free now: the finish uses their shared memory)
+  static_assert(sizeof(QdFinSmem) <= sizeof(S.stage), "finish state lives in the stage area");
+  qd_finish(ws, lists, *reinterpret_cast<QdFinSmem*>(&S.stage[0][0]), results);
   __syncthreads();
   if (t == 0) ws->ready = 0ull;   // a replay of the same launch sequence (same token) waits for its own clearing
 }
