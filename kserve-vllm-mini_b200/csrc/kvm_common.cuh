@@ -97,14 +97,22 @@ __device__ __forceinline__ uint8_t kvm_ld_u8(const uint8_t* p) {
 }
 
 // 256-bit streaming loads (sm_100: LDG.256): four 8-byte elements per thread, not allocated in
-// L1 and marked evict-first in L2 - the column is read once, so it should not push out what
-// later passes want to find in L2 (digit records, histograms).  32-byte aligned addresses only.
+// L1.  32-byte aligned addresses only.  Measured on B200 (tools/probe/bw_probe.cu, two 8-byte
+// columns + 2 B/row stores, 1e8 rows): plain 256-bit loads 5.8 TB/s; the same loads marked
+// L2::evict_first 3.9 TB/s - so the evict-first form below is NOT used by the streaming kernels.
 struct kvm_u64x4 {
   unsigned long long x, y, z, w;
 };
 __device__ __forceinline__ kvm_u64x4 kvm_ld4_stream(const void* p) {
   kvm_u64x4 r;
   asm volatile("ld.global.nc.L1::no_allocate.L2::evict_first.v4.b64 {%0,%1,%2,%3}, [%4];"
+               : "=l"(r.x), "=l"(r.y), "=l"(r.z), "=l"(r.w)
+               : "l"(p));
+  return r;
+}
+__device__ __forceinline__ kvm_u64x4 kvm_ld4_nc(const void* p) {
+  kvm_u64x4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.b64 {%0,%1,%2,%3}, [%4];"
                : "=l"(r.x), "=l"(r.y), "=l"(r.z), "=l"(r.w)
                : "l"(p));
   return r;

@@ -1,24 +1,23 @@
 // kvm_qdigit.cu - one-and-an-eighth-pass exact quantiles of one multiset (the 16 B/record
 // percentile path; analyze.py:59-81).
 //
-// Two launches, no memset; the second is a programmatic dependent launch (its CTAs become
-// resident while the first kernel drains, so there is no launch gap between the two):
+// Three launches, no memset; the second and third are programmatic dependent launches (their
+// CTAs become resident while the kernel in front drains):
 //   hist     prologue: every CTA draws the SAME 512 stratified pseudo-random members (one load per
 //            thread, L2 hits for all but the first CTA) and derives an ESTIMATE of the key range
 //            from them - no separate sampling launch, no grid-wide dependency; CTA 0 also clears
 //            the accumulators and publishes a per-call token that the flushes wait for.
-//            body: ONE pass over the data (16 B/record, 256-bit evict-first loads): 13-bit digit
+//            body: ONE pass over the data (16 B/record, 256-bit loads): 13-bit digit
 //            of every member key relative to the estimated range (bins 0 and 8191 catch what lies
 //            far outside it), histogram in shared memory, and the digit written as a 2-byte record
-//            (0xFFFF = not a member; stored with an L2 keep policy - the next kernel reads them).
+//            (0xFFFF = not a member).
 //            epilogue (last CTA to finish, ticket): exact member count = sum of the histogram,
 //            rank of every query, the bin holding it and the residual rank.
 //   collect  pass over the 2 B/record digit records; the value of a record is fetched only when
 //            its digit is a wanted bin (~0.1 % of the records): its key goes to that bin's list and
 //            its next 11 bits into that bin's sub-histogram.
-//            epilogue (last CTA, ticket): one 64-thread group per query walks the sub-histogram to
-//            the sub-bin holding the rank; all threads then stream the lists once and the handful
-//            of keys of each query's sub-bin is ranked.
+//   rank     one CTA per query: the sub-histogram gives the sub-bin holding the rank, the handful
+//            of keys of that sub-bin is ranked by counting.
 // Exact whenever it answers.  It declines (status word KVM_ERR_UNSUPPORTED, the caller runs the
 // general select) when a rank falls into a catch-all bin (the sample missed the range), when a
 // list overflows (heavy duplicates spread over many keys) or when the sample holds too few members.
@@ -61,19 +60,20 @@ struct QdWs {
   long long list_cap;   // keys per slot list
   QdQuery q[QD_MAXQ];
   int32_t slot_bin[QD_MAXQ];
+  unsigned long long dbg[16];   // phase time stamps of the last call (globaltimer ns / SM clocks), for profiling
   unsigned long long ready;   // == the call's token once CTA 0 of the hist kernel has cleared the block below
   // ---- cleared by CTA 0 of the hist kernel at the start of every call (QD_CLEAR_* below)
   alignas(16) unsigned int s_ticket;
-  unsigned int c_ticket, pad4[2];
+  unsigned int pad4[3];
   unsigned long long list_n[QD_MAXQ];
-  unsigned long long hist[QD_BINS];
-  unsigned int hist2[QD_MAXQ][QD_SUB];
+  unsigned int hist[QD_BINS];   // n < 2^31 on this path
   // ----
+  alignas(16) unsigned int hist2[QD_MAXQ][QD_SUB];   // rows of the wanted bins are cleared by the resolve
   alignas(16) uint64_t small[QD_MAXQ][QD_SMALL];
 };
 
 constexpr size_t QD_HEADER = (sizeof(QdWs) + 255) / 256 * 256;
-constexpr size_t QD_CLEAR_BEGIN = offsetof(QdWs, s_ticket), QD_CLEAR_END = offsetof(QdWs, small);
+constexpr size_t QD_CLEAR_BEGIN = offsetof(QdWs, s_ticket), QD_CLEAR_END = offsetof(QdWs, hist2);
 static_assert(QD_CLEAR_BEGIN % 16 == 0 && QD_CLEAR_END % 16 == 0, "cleared with 16-byte stores");
 
 struct QdArgs {
@@ -103,6 +103,11 @@ __device__ __forceinline__ bool qd_member(const void* member, int64_t i) {
   return true;
 }
 
+__device__ __forceinline__ unsigned long long qd_now() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
 __device__ __forceinline__ unsigned long long qd_ld_acquire(const unsigned long long* p) {
   unsigned long long v;
   asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
@@ -116,34 +121,43 @@ __device__ __forceinline__ void qd_st_release(unsigned long long* p, unsigned lo
 // `cum` (shared, QD_BINS words) receives the exclusive prefix of the global histogram; every
 // query finds its bin by bisection.
 __device__ __forceinline__ void qd_resolve(QdWs* ws, uint32_t* cum, const QdArgs& a) {
-  __shared__ unsigned long long wtot[QD_THREADS / 32];
+  __shared__ unsigned long long wtot[QD_THREADS / 32 + 1];
   __shared__ QdQuery qs[QD_MAXQ];
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-  constexpr int PER = QD_BINS / QD_THREADS;
-  unsigned long long c[PER], local = 0;
+  // warp w owns bins [w*SEG, (w+1)*SEG): lane-contiguous (coalesced) loads, all in flight at once,
+  // then one warp scan per 32 bins; `cum` gets the exclusive prefix inside the warp's segment and
+  // wtot the segment totals (a bin's global prefix = cum[bin] + sum of the segments before it)
+  constexpr int NW = QD_THREADS / 32, SEG = QD_BINS / NW, IT = SEG / 32;
+  uint32_t c[IT];
 #pragma unroll
-  for (int k = 0; k < PER; ++k) {
-    c[k] = __ldcg(&ws->hist[t * PER + k]);
-    local += c[k];
-  }
-  unsigned long long incl = local;
+  for (int k = 0; k < IT; ++k) c[k] = __ldcg(&ws->hist[warp * SEG + k * 32 + lane]);
+  uint32_t carry = 0;
 #pragma unroll
-  for (int d = 1; d < 32; d <<= 1) {
-    const unsigned long long o = __shfl_up_sync(KVM_FULL, incl, d);
-    if (lane >= d) incl += o;
+  for (int k = 0; k < IT; ++k) {
+    const uint32_t ck = c[k];
+    uint32_t incl = ck;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t o = __shfl_up_sync(KVM_FULL, incl, d);
+      if (lane >= d) incl += o;
+    }
+    cum[warp * SEG + k * 32 + lane] = carry + incl - ck;
+    carry += __shfl_sync(KVM_FULL, incl, 31);
   }
-  if (lane == 31) wtot[warp] = incl;
+  if (lane == 0) wtot[warp] = carry;
   __syncthreads();
-  unsigned long long before = incl - local;
-  for (int w = 0; w < warp; ++w) before += wtot[w];
-#pragma unroll
-  for (int k = 0; k < PER; ++k) {
-    cum[t * PER + k] = (uint32_t)before;   // n < 2^31 on this path
-    before += c[k];
+  if (t == 0) {   // segment totals -> exclusive offsets, grand total in wtot[NW]
+    unsigned long long acc = 0;
+    for (int w = 0; w < NW; ++w) {
+      const unsigned long long x = wtot[w];
+      wtot[w] = acc;
+      acc += x;
+    }
+    wtot[NW] = acc;
   }
   __syncthreads();
-  unsigned long long total = 0;
-  for (int w = 0; w < QD_THREADS / 32; ++w) total += wtot[w];
+  const unsigned long long total = wtot[NW];
+  auto prefix = [&](int bin) -> long long { return (long long)cum[bin] + (long long)wtot[bin / SEG]; };
   const int nq = a.nq;
   if (t < QD_MAXQ) {
     QdQuery s{};
@@ -173,11 +187,11 @@ __device__ __forceinline__ void qd_resolve(QdWs* ws, uint32_t* cum, const QdArgs
           int lo = 0, hi = QD_BINS - 1;   // last bin whose exclusive prefix is <= rank
           while (lo < hi) {
             const int mid = (lo + hi + 1) >> 1;
-            if ((long long)cum[mid] <= s.rank) lo = mid;
+            if (prefix(mid) <= s.rank) lo = mid;
             else hi = mid - 1;
           }
           s.bin = lo;
-          s.resid = s.rank - (long long)cum[lo];
+          s.resid = s.rank - prefix(lo);
           if (lo == 0 || lo == QD_BINS - 1) s.valid = 0;   // catch-all bins: the sample missed the range
         }
       }
@@ -205,7 +219,18 @@ __device__ __forceinline__ void qd_resolve(QdWs* ws, uint32_t* cum, const QdArgs
     for (int k = 0; k < QD_MAXQ; ++k) ws->slot_bin[k] = k < nslots ? sb[k] : -1;
     ws->nslots = nslots;
     if (!ok) ws->status = KVM_ERR_UNSUPPORTED;
-    for (int q = 0; q < QD_MAXQ; ++q) ws->q[q] = qs[q];
+    qs[0].pad = nslots;
+  }
+  __syncthreads();
+  if (t < QD_MAXQ) {
+    QdQuery o = qs[t];
+    o.pad = 0;
+    ws->q[t] = o;
+  }
+  {   // the sub-histograms the collect kernel counts into
+    const int nslots = qs[0].pad;
+    uint4* z = reinterpret_cast<uint4*>(&ws->hist2[0][0]);
+    for (int i = t; i < nslots * (QD_SUB / 4); i += QD_THREADS) z[i] = make_uint4(0u, 0u, 0u, 0u);
   }
 }
 
@@ -225,7 +250,24 @@ qd_hist_kernel(const double* __restrict__ values, int64_t n, const void* __restr
   __shared__ bool is_last;
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   kvm_pdl_launch_dependents();   // the collect kernel may take the SM slots this grid frees as it drains
+  if (blockIdx.x == 0 && t == 0) ws->dbg[0] = qd_now();
 
+  // ---- sample loads first (they are the longest latency of the prologue: cold TLB): thread t
+  // draws one element - the same element in every CTA, so all CTAs derive identical digit
+  // parameters without talking to each other.  16 regions spread evenly over the column (the
+  // first at its start, the last at its end: a sorted column shows its extremes), 32
+  // pseudo-random elements inside a 4096-element window of each: 512 values from ~32 pages.
+  const int64_t* st = reinterpret_cast<const int64_t*>(member);
+  double sample_v;
+  long long sample_s = 200;
+  {
+    const int64_t region = t >> 5;
+    const int64_t win = 4096;
+    const int64_t off = region * ((n - win) / (QD_SAMPLE / 32 - 1));
+    const int64_t i = off + (int64_t)(qd_hash((uint32_t)t * 2654435761u + 12345u) & (uint32_t)(win - 1));
+    sample_v = __ldg(values + i);
+    if (MODE == KVM_MEMBER_STATUS) sample_s = __ldg(st + i);
+  }
   // ---- CTA 0: clear what the call accumulates into, then publish the call's token.  No other
   // CTA touches those words before it has seen the token (the wait in front of the flush below),
   // and CTA 0 waits for nobody, so there is no ordering between CTAs to rely on.
@@ -242,31 +284,25 @@ qd_hist_kernel(const double* __restrict__ values, int64_t n, const void* __restr
   // ---- the first tile of the stream is requested before the sample is reduced (its latency
   // hides the sample's)
   const int64_t nocts = n >> 3;
-  const int64_t chunk = (nocts + gridDim.x - 1) / gridDim.x;
-  const int64_t o_end = min(nocts, ((int64_t)blockIdx.x + 1) * chunk);
-  int64_t o = (int64_t)blockIdx.x * chunk + t;
-  const int64_t* st = reinterpret_cast<const int64_t*>(member);
+  const int64_t o_end = nocts, o_step = (int64_t)gridDim.x * QD_THREADS;   // grid-stride (measured faster than per-CTA ranges)
+  int64_t o = (int64_t)blockIdx.x * QD_THREADS + t;
   kvm_u64x4 v0{}, v1{}, s0{}, s1{};
   auto load8 = [&](int64_t oc, kvm_u64x4& a0, kvm_u64x4& a1, kvm_u64x4& b0, kvm_u64x4& b1) {
     const int64_t i = oc << 3;
-    a0 = kvm_ld4_stream(values + i);
-    a1 = kvm_ld4_stream(values + i + 4);
+    a0 = kvm_ld4_nc(values + i);
+    a1 = kvm_ld4_nc(values + i + 4);
     if (MODE == KVM_MEMBER_STATUS) {
-      b0 = kvm_ld4_stream(st + i);
-      b1 = kvm_ld4_stream(st + i + 4);
+      b0 = kvm_ld4_nc(st + i);
+      b1 = kvm_ld4_nc(st + i + 4);
     }
   };
   bool have = VEC && o < o_end;
   if (have) load8(o, v0, v1, s0, s1);
 
-  // ---- sample: thread t draws one element of stratum t - the same element in every CTA, so all
-  // CTAs derive identical digit parameters without talking to each other
+  // ---- reduce the sample
   {
-    const int64_t width = n / QD_SAMPLE;
-    const int64_t i = (int64_t)t * width + (int64_t)(qd_hash((uint32_t)t * 2654435761u + 12345u) % (uint64_t)width);
-    const double v = __ldg(values + i);
-    bool mem = v == v;
-    if (MODE == KVM_MEMBER_STATUS) mem = mem && __ldg(st + i) == 200;
+    const double v = sample_v;
+    const bool mem = v == v && sample_s == 200;
     unsigned long long mx = mem ? kvm_key(v) : 0ull, inv_mn = mem ? ~kvm_key(v) : 0ull;
     int cnt = mem;
 #pragma unroll
@@ -320,6 +356,7 @@ qd_hist_kernel(const double* __restrict__ values, int64_t n, const void* __restr
     __syncthreads();
   }
   if (!s_ok) return;   // every CTA takes the same decision; the status word says "declined"
+  if (blockIdx.x == 0 && t == 0) ws->dbg[1] = qd_now();
   const uint64_t base = s_base;
   const int shift = s_shift;
   auto digit_of_value = [&](double v, bool mem) -> uint32_t {
@@ -332,17 +369,16 @@ qd_hist_kernel(const double* __restrict__ values, int64_t n, const void* __restr
     return digit_of_value(__longlong_as_double((long long)vb), MODE != KVM_MEMBER_STATUS || sb == 200ull);
   };
   if (VEC) {
-    const unsigned long long keep = kvm_policy_evict_last();
     while (have) {
       uint4 out;
       out.x = dig(v0.x, s0.x) | (dig(v0.y, s0.y) << 16);
       out.y = dig(v0.z, s0.z) | (dig(v0.w, s0.w) << 16);
       out.z = dig(v1.x, s1.x) | (dig(v1.y, s1.y) << 16);
       out.w = dig(v1.z, s1.z) | (dig(v1.w, s1.w) << 16);
-      kvm_st4_u32_keep(recs + (o << 3), out, keep);
+      *reinterpret_cast<uint4*>(recs + (o << 3)) = out;
       // (no register double-buffering: 128 B in flight per thread x 1024 threads per SM is
       // several times what the memory system needs; the other warps cover this one's wait)
-      o += QD_THREADS;
+      o += o_step;
       have = o < o_end;
       if (have) load8(o, v0, v1, s0, s1);
     }
@@ -361,15 +397,18 @@ qd_hist_kernel(const double* __restrict__ values, int64_t n, const void* __restr
   __syncthreads();
   for (int i = t; i < QD_BINS; i += QD_THREADS) {
     const uint32_t c = hist[i];
-    if (c) atomicAdd(&ws->hist[i], (unsigned long long)c);
+    if (c) atomicAdd(&ws->hist[i], c);
   }
   __threadfence();
   __syncthreads();
   if (t == 0) is_last = atomicAdd(&ws->s_ticket, 1u) == gridDim.x - 1;
   __syncthreads();
+  if (blockIdx.x == 0 && t == 0) ws->dbg[2] = qd_now();
   if (!is_last) return;
   __threadfence();
+  if (t == 0) ws->dbg[3] = qd_now();
   qd_resolve(ws, hist, a);
+  if (t == 0) ws->dbg[4] = qd_now();
 }
 
 // ------------------------------------------------------------------ collect (+ rank in the last CTA)
@@ -380,178 +419,45 @@ struct QdCollectSmem {
   unsigned long long stage_pos[QD_MAXQ];
   uint32_t queue_n;
   int is_last;
+  // parameters of the rare paths (kept out of line so that the streaming loop stays small)
+  uint32_t want[QD_MAXQ];
+  uint64_t base;
+  long long cap;
+  int32_t bshift, sh2;
 };
 
-// Finish of all queries by the last CTA of the collect kernel.  Three phases:
-//   A  one group of QD_GROUP threads per query walks the wanted bin's sub-histogram to the sub-bin
-//      holding the residual rank;
-//   B  ALL threads stream the slot lists once (every load of a thread is in flight at the same
-//      time - a 64-thread group would need dozens of dependent round trips to L2); a key that
-//      lies in the sub-bin of a query updates that query's min / max and is gathered;
-//   C  per query: min == max settles it (thousands of copies of one key - values rounded to three
-//      decimals - need no ranking), otherwise the handful of gathered keys is ranked by counting.
-struct QdFinSmem {
-  uint32_t gsum[QD_MAXQ][QD_GROUP];
-  uint32_t sb[QD_MAXQ], sr[QD_MAXQ], scount[QD_MAXQ], cnt[QD_MAXQ];
-  int32_t state[QD_MAXQ];   // 0: nothing to look up, 1: answered, 2: needs its sub-bin's keys, 3: decline
-  int32_t slot[QD_MAXQ];
-  unsigned long long kmin[QD_MAXQ], kmax[QD_MAXQ];
-  unsigned long long slot_m[QD_MAXQ], slot_base[QD_MAXQ], slot_begin[QD_MAXQ + 1];
-};
+// key of a wanted record -> sub-histogram + staged list entry
+__device__ __noinline__ void qd_take(QdCollectSmem& S, QdWs* ws, const double* __restrict__ values,
+                                     uint64_t* __restrict__ lists, int64_t i, uint32_t d) {
+  const uint64_t key = kvm_key(values[i]);
+  for (int k = 0; k < QD_MAXQ; ++k)
+    if (d == S.want[k]) {
+      const uint64_t bin_base = S.base + ((uint64_t)(d - 1) << S.bshift);
+      atomicAdd(&ws->hist2[k][(uint32_t)((key - bin_base) >> S.sh2) & (QD_SUB - 1)], 1u);
+      const uint32_t sp = atomicAdd(&S.stage_n[k], 1u);
+      if (sp < (uint32_t)QD_STAGE) {
+        S.stage[k][sp] = key;
+      } else {  // the stage is full: straight to the list
+        const unsigned long long pos = atomicAdd(&ws->list_n[k], 1ull);
+        if (pos < (unsigned long long)S.cap) lists[(size_t)k * (size_t)S.cap + pos] = key;
+      }
+    }
+}
 
-__device__ __noinline__ void qd_finish(QdWs* ws, const uint64_t* __restrict__ lists, QdFinSmem& F,
-                                          kvm_query_result* __restrict__ results) {
-  const int t = threadIdx.x, g = t / QD_GROUP, gt = t % QD_GROUP;
-  const double nan = __longlong_as_double(0x7ff8000000000000ll);
-  const int nq = ws->nq, nslots = ws->nslots;
-  const long long cap = ws->list_cap;
-  const int bshift = ws->shift;
-  const int sh2 = bshift > QD_SUB_BITS ? bshift - QD_SUB_BITS : 0;
-  const uint64_t base = ws->base;
-  if (t < QD_MAXQ) {
-    const unsigned long long m = t < nslots ? __ldcg(&ws->list_n[t]) : 0ull;
-    F.slot_m[t] = m;
-    F.slot_base[t] = t < nslots ? base + ((uint64_t)(ws->slot_bin[t] - 1) << bshift) : 0ull;
-    F.kmin[t] = QD_NONE;
-    F.kmax[t] = 0ull;
-    F.cnt[t] = 0;
-    F.state[t] = 0;
-  }
-  __syncthreads();
-  if (t == 0) {
-    unsigned long long acc = 0;
-    for (int k = 0; k < QD_MAXQ; ++k) {
-      F.slot_begin[k] = acc;
-      acc += F.slot_m[k] <= (unsigned long long)cap ? F.slot_m[k] : 0ull;   // an overflowed list is not scanned
-    }
-    F.slot_begin[QD_MAXQ] = acc;
-  }
-  // ---- A: sub-bin of every query
-  QdQuery s{};
-  bool need = false;
-  if (g < nq) {
-    s = ws->q[g];
-    need = s.valid && s.qstatus == KVM_Q_OK;
-    if (gt == 0) F.slot[g] = need ? s.slot : -1;
-  }
-  constexpr int PER = QD_SUB / QD_GROUP;
-  uint32_t c[PER], local = 0;
-  bool overflow = false;
-  if (need) {
-    const unsigned long long m = F.slot_m[s.slot];
-    overflow = m > (unsigned long long)cap || (long long)m <= s.resid;
-    if (!overflow) {
-      const unsigned int* __restrict__ h2 = ws->hist2[s.slot];
-#pragma unroll
-      for (int k = 0; k < PER; k += 4) {
-        const uint4 x = __ldcg(reinterpret_cast<const uint4*>(h2 + gt * PER + k));
-        c[k] = x.x; c[k + 1] = x.y; c[k + 2] = x.z; c[k + 3] = x.w;
-        local += x.x + x.y + x.z + x.w;
-      }
-    }
-    F.gsum[g][gt] = local;
-  }
-  __syncthreads();
-  if (need && !overflow) {
-    uint32_t before = 0;
-    for (int k = 0; k < gt; ++k) before += F.gsum[g][k];
-    const uint32_t r = (uint32_t)s.resid;
-    if (before <= r && r < before + local) {
-      uint32_t b = before;
-      int k = 0;
-      for (; k < PER - 1; ++k) {
-        if (r < b + c[k]) break;
-        b += c[k];
-      }
-      F.sb[g] = (uint32_t)(gt * PER + k);   // the sub-bin
-      F.sr[g] = r - b;                      // rank inside it
-      F.scount[g] = c[k];                   // its population
-      F.state[g] = sh2 == 0 ? 1 : (c[k] <= (uint32_t)QD_SMALL ? 2 : 4);   // 4: too many to gather - min/max only
-    }
-  } else if (need && gt == 0) {
-    F.state[g] = 3;
-  }
-  __syncthreads();
-  // ---- B: one pass of all threads over all slot lists
-  {
-    const unsigned long long total = F.slot_begin[QD_MAXQ];
-    constexpr int U = 8;
-    for (unsigned long long i0 = t; i0 < total; i0 += (unsigned long long)U * QD_THREADS) {
-      uint64_t kk[U];
-      int ks[U];
-#pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const unsigned long long i = i0 + (unsigned long long)u * QD_THREADS;
-        ks[u] = -1;
-        kk[u] = 0;
-        if (i < total) {
-          int k = 0;
-#pragma unroll
-          for (int j = 1; j < QD_MAXQ; ++j) k += i >= F.slot_begin[j];
-          ks[u] = k;
-          kk[u] = __ldcg(lists + (size_t)k * (size_t)cap + (size_t)(i - F.slot_begin[k]));
-        }
-      }
-#pragma unroll
-      for (int u = 0; u < U; ++u) {
-        if (ks[u] < 0) continue;
-        const uint32_t sub = (uint32_t)((kk[u] - F.slot_base[ks[u]]) >> sh2);
-        for (int q = 0; q < nq; ++q) {
-          const int stq = F.state[q];
-          if ((stq == 2 || stq == 4) && F.slot[q] == ks[u] && F.sb[q] == sub) {
-            atomicMin(&F.kmin[q], (unsigned long long)kk[u]);
-            atomicMax(&F.kmax[q], (unsigned long long)kk[u]);
-            if (stq == 2) {
-              const uint32_t pos = atomicAdd(&F.cnt[q], 1u);
-              if (pos < (uint32_t)QD_SMALL) ws->small[q][pos] = kk[u];
-            }
-          }
-        }
-      }
-    }
-  }
-  __threadfence_block();
-  __syncthreads();
-  // ---- C: answers
-  if (g >= nq) return;
-  const int stq = F.state[g];
-  if (stq == 0) {   // empty multiset / rank out of range: nothing to look up
-    if (gt == 0) results[g] = kvm_query_result{nan, s.n, s.rank, s.qstatus, 0};
-    return;
-  }
-  auto decline = [&]() {
-    if (gt == 0) {
-      ws->status = KVM_ERR_UNSUPPORTED;  // all writers agree
-      results[g] = kvm_query_result{nan, s.n, s.rank, s.qstatus, 0};
-    }
-  };
-  if (stq == 3) {
-    decline();
-    return;
-  }
-  if (stq == 1) {   // the sub-bin is one key
-    if (gt == 0) results[g] = kvm_query_result{kvm_unkey(F.slot_base[s.slot] + F.sb[g]), s.n, s.rank, KVM_Q_OK, 0};
-    return;
-  }
-  if (F.kmin[g] == F.kmax[g]) {   // one distinct key (any number of copies)
-    if (gt == 0) results[g] = kvm_query_result{kvm_unkey(F.kmin[g]), s.n, s.rank, KVM_Q_OK, 0};
-    return;
-  }
-  const uint32_t m2 = F.cnt[g], sr = F.sr[g];
-  if (stq == 4 || m2 != F.scount[g]) {   // too many distinct candidates for the scratch: the general select's job
-    decline();
-    return;
-  }
-  const uint64_t* small = ws->small[g];
-  for (uint32_t i = gt; i < m2; i += QD_GROUP) {
-    const uint64_t k = __ldcg(small + i);
-    uint32_t less = 0, leq = 0;
-    for (uint32_t j = 0; j < m2; ++j) {
-      const uint64_t x = __ldcg(small + j);
-      less += x < k;
-      leq += x <= k;
-    }
-    if (less <= sr && sr < leq) results[g] = kvm_query_result{kvm_unkey(k), s.n, s.rank, KVM_Q_OK, 0};  // all writers agree
+// a word of two records raised the (conservative) flag: re-check exactly; a wanted record only
+// queues its row index - the value fetch (a random access) happens after the streaming loop, all
+// lanes at once, instead of stalling the warp in the middle of it
+__device__ __noinline__ void qd_hit_word(QdCollectSmem& S, QdWs* ws, const double* __restrict__ values,
+                                         uint64_t* __restrict__ lists, int64_t i, uint32_t w) {
+  for (int h = 0; h < 2; ++h) {
+    const uint32_t d = h ? (w >> 16) : (w & 0xFFFFu);
+    if (d == 0xFFFFu) continue;
+    bool wanted = false;
+    for (int k = 0; k < QD_MAXQ; ++k) wanted |= d == S.want[k];
+    if (!wanted) continue;
+    const uint32_t qp = atomicAdd(&S.queue_n, 1u);
+    if (qp < (uint32_t)QD_QUEUE) S.queue[qp] = (uint32_t)(i + h);   // n < 2^31 on this path
+    else qd_take(S, ws, values, lists, i + h, d);                    // queue full: handle it in place
   }
 }
 
@@ -561,20 +467,15 @@ __device__ __noinline__ void qd_finish(QdWs* ws, const uint64_t* __restrict__ li
 template <bool VEC>
 __global__ void __launch_bounds__(QD_THREADS, 2)
 qd_collect_kernel(const double* __restrict__ values, int64_t n, const uint16_t* __restrict__ recs, QdWs* ws,
-                  uint64_t* __restrict__ lists, kvm_query_result* __restrict__ results) {
+                  uint64_t* __restrict__ lists) {
   __shared__ QdCollectSmem S;
   const int t = threadIdx.x;
   if (t < QD_MAXQ) S.stage_n[t] = 0;
   if (t == 0) S.queue_n = 0;
+  kvm_pdl_launch_dependents();   // the rank kernel may become resident as this grid drains
   kvm_pdl_wait();   // everything above overlapped the hist kernel's tail; its results are visible from here on
-  if (ws->status != KVM_OK) {   // declined by the sample or by the resolve: report and re-arm the handshake
-    if (blockIdx.x == 0) {
-      const double nan = __longlong_as_double(0x7ff8000000000000ll);
-      if (t < ws->nq) results[t] = kvm_query_result{nan, ws->q[t].n, ws->q[t].rank, ws->q[t].qstatus, 0};
-      if (t == 0) ws->ready = 0ull;
-    }
-    return;
-  }
+  if (blockIdx.x == 0 && t == 0) ws->dbg[5] = qd_now();
+  if (ws->status != KVM_OK) return;   // declined by the sample or by the resolve: the rank kernel reports
   const int nslots = ws->nslots;
   const long long cap = ws->list_cap;
   const int bshift = ws->shift;
@@ -583,31 +484,14 @@ qd_collect_kernel(const double* __restrict__ values, int64_t n, const uint16_t* 
   uint32_t want[QD_MAXQ];
 #pragma unroll
   for (int k = 0; k < QD_MAXQ; ++k) want[k] = k < nslots ? (uint32_t)ws->slot_bin[k] : 0xFFFFFFFFu;
+  if (t < QD_MAXQ) S.want[t] = t < nslots ? (uint32_t)ws->slot_bin[t] : 0xFFFFFFFFu;
+  if (t == 0) {
+    S.base = base;
+    S.cap = cap;
+    S.bshift = bshift;
+    S.sh2 = sh2;
+  }
   __syncthreads();
-  // key of a wanted record -> sub-histogram + staged list entry
-  auto take = [&](int64_t i, uint32_t d) {
-    const uint64_t key = kvm_key(values[i]);
-#pragma unroll
-    for (int k = 0; k < QD_MAXQ; ++k)
-      if (d == want[k]) {
-        const uint64_t bin_base = base + ((uint64_t)(d - 1) << bshift);
-        atomicAdd(&ws->hist2[k][(uint32_t)((key - bin_base) >> sh2) & (QD_SUB - 1)], 1u);
-        const uint32_t sp = atomicAdd(&S.stage_n[k], 1u);
-        if (sp < (uint32_t)QD_STAGE) {
-          S.stage[k][sp] = key;
-        } else {  // the stage is full: straight to the list
-          const unsigned long long pos = atomicAdd(&ws->list_n[k], 1ull);
-          if (pos < (unsigned long long)cap) lists[(size_t)k * (size_t)cap + pos] = key;
-        }
-      }
-  };
-  // a wanted record only queues its row index: the value fetch (a random access) happens after
-  // the streaming loop, all lanes at once, instead of stalling the warp in the middle of it
-  auto hit = [&](int64_t i, uint32_t d) {
-    const uint32_t qp = atomicAdd(&S.queue_n, 1u);
-    if (qp < (uint32_t)QD_QUEUE) S.queue[qp] = (uint32_t)i;   // n < 2^31 on this path
-    else take(i, d);                                            // queue full: handle it in place
-  };
   // branch-free membership test in registers: both 16-bit records of a word are tested at once:
   // x = w ^ (bin | bin << 16) has a zero half where a record equals the bin, and
   // (x - 0x00010001) & ~x & 0x80008000 flags zero halves (a borrow can only raise a false flag
@@ -631,29 +515,13 @@ qd_collect_kernel(const double* __restrict__ values, int64_t n, const uint16_t* 
       }
     }
     z &= 0x80008000u;
-    if (z) {
-      const uint32_t d0 = w & 0xFFFFu, d1 = w >> 16;
-      if ((z & 0x8000u) && d0 != 0xFFFFu) {
-        bool w0 = false;
-#pragma unroll
-        for (int k = 0; k < QD_MAXQ; ++k) w0 |= d0 == want[k];
-        if (w0) hit(i, d0);
-      }
-      if ((z >> 16) && d1 != 0xFFFFu) {
-        bool w1 = false;
-#pragma unroll
-        for (int k = 0; k < QD_MAXQ; ++k) w1 |= d1 == want[k];
-        if (w1) hit(i + 1, d1);
-      }
-    }
+    if (z) qd_hit_word(S, ws, values, lists, i, w);
   };
   if (VEC) {
     // 32 contiguous bytes (16 records) per thread and iteration; CTA b owns a contiguous range
-    const int64_t nunits = n >> 4;
-    const int64_t chunk = (nunits + gridDim.x - 1) / gridDim.x;
-    const int64_t u_end = min(nunits, ((int64_t)blockIdx.x + 1) * chunk);
-    for (int64_t u0 = (int64_t)blockIdx.x * chunk + t; u0 < u_end; u0 += 2 * QD_THREADS) {
-      const int64_t u1 = u0 + QD_THREADS;
+    const int64_t u_end = n >> 4, u_step = (int64_t)gridDim.x * QD_THREADS;
+    for (int64_t u0 = (int64_t)blockIdx.x * QD_THREADS + t; u0 < u_end; u0 += 2 * u_step) {
+      const int64_t u1 = u0 + u_step;
       const kvm_u64x4 r0 = kvm_ld4(recs + (u0 << 4));
       kvm_u64x4 r1{~0ull, ~0ull, ~0ull, ~0ull};
       if (u1 < u_end) r1 = kvm_ld4(recs + (u1 << 4));
@@ -676,11 +544,12 @@ qd_collect_kernel(const double* __restrict__ values, int64_t n, const uint16_t* 
       word(i, (uint32_t)recs[i] | 0xFFFF0000u);
   }
   __syncthreads();
+  if (blockIdx.x == 0 && t == 0) ws->dbg[6] = qd_now();
   {  // drain the queue: every thread takes queued rows, fetches the value, appends the key
     const uint32_t qn = S.queue_n < (uint32_t)QD_QUEUE ? S.queue_n : (uint32_t)QD_QUEUE;
     for (uint32_t j = t; j < qn; j += QD_THREADS) {
       const int64_t i = (int64_t)S.queue[j];
-      take(i, (uint32_t)recs[i]);
+      qd_take(S, ws, values, lists, i, (uint32_t)recs[i]);
     }
   }
   __syncthreads();
@@ -697,18 +566,155 @@ qd_collect_kernel(const double* __restrict__ values, int64_t n, const uint16_t* 
       if (pos < (unsigned long long)cap) lists[(size_t)k * (size_t)cap + pos] = S.stage[k][j];
     }
   }
-  // ---- last CTA to get here finishes the queries, one group of threads per query
-  __threadfence();
+  if (blockIdx.x == 0 && t == 0) ws->dbg[7] = qd_now();
+}
+
+// ------------------------------------------------------------------ rank
+// One CTA per query (a programmatic dependent launch behind the collect kernel).  The wanted
+// bin's sub-histogram, its list length and the first 8 keys of every thread are requested
+// together (one round trip); the sub-histogram gives the sub-bin holding the residual rank, the
+// keys of that sub-bin - usually a handful, or thousands of copies of ONE key (values rounded to
+// three decimals), which min == max settles without ranking anything - are gathered in shared
+// memory and ranked by counting.
+constexpr int QR_THREADS = 512;
+constexpr int QR_U = 8;
+
+__global__ void __launch_bounds__(QR_THREADS, 1)
+qd_rank_kernel(QdWs* ws, const uint64_t* __restrict__ lists, kvm_query_result* __restrict__ results) {
+  __shared__ uint32_t h2[QD_SUB];
+  __shared__ uint32_t wsum[QR_THREADS / 32];
+  __shared__ uint64_t small[QD_SMALL];
+  __shared__ unsigned long long kmin_s, kmax_s;
+  __shared__ uint32_t sb_s, sr_s, scount_s, cnt_s;
+  __shared__ int found_s;
+  const int q = blockIdx.x, t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const double nan = __longlong_as_double(0x7ff8000000000000ll);
+  if (t == 0) {
+    kmin_s = QD_NONE;
+    kmax_s = 0ull;
+    cnt_s = 0;
+    found_s = 0;
+  }
+  kvm_pdl_wait();   // the collect kernel has completed; its lists and sub-histograms are visible
+  if (q == 0 && t == 0) ws->dbg[8] = qd_now();
+  const QdQuery s = ws->q[q];
+  const int status = ws->status;
+  const long long cap = ws->list_cap;
+  const int bshift = ws->shift;
+  const uint64_t base = ws->base;
+  // last kernel of the call: a replay of the same launch sequence (same token) must wait for its
+  // own clearing again (the hist kernel of the next call starts after this grid has completed)
+  if (q == 0 && t == 0) ws->ready = 0ull;
+  const bool need = status == KVM_OK && s.valid && s.qstatus == KVM_Q_OK;
+  if (!need) {   // empty multiset / rank out of range: nothing to look up; a declined call reports NaN
+    if (t == 0) results[q] = kvm_query_result{nan, s.n, s.rank, s.qstatus, 0};
+    return;
+  }
+  const int sh2 = bshift > QD_SUB_BITS ? bshift - QD_SUB_BITS : 0;
+  const uint64_t bin_base = base + ((uint64_t)(s.bin - 1) << bshift);
+  const uint64_t* __restrict__ keys = lists + (size_t)s.slot * (size_t)cap;
+  // ---- one round trip: list length, sub-histogram (coalesced), first keys of every thread
+  const unsigned long long m = __ldcg(&ws->list_n[s.slot]);
+  const uint4 hv = __ldcg(reinterpret_cast<const uint4*>(ws->hist2[s.slot]) + t);   // bins 4t .. 4t+3
+  uint64_t kk[QR_U];
+#pragma unroll
+  for (int u = 0; u < QR_U; ++u) kk[u] = __ldcg(keys + (size_t)u * QR_THREADS + t);   // inside the list area (cap >= 16384)
+  auto decline = [&]() {
+    if (t == 0) {
+      ws->status = KVM_ERR_UNSUPPORTED;  // all writers agree
+      results[q] = kvm_query_result{nan, s.n, s.rank, s.qstatus, 0};
+    }
+  };
+  if (m > (unsigned long long)cap || (long long)m <= s.resid) {
+    decline();
+    return;
+  }
+  // ---- sub-bin holding the residual rank
+  const uint32_t lsum = hv.x + hv.y + hv.z + hv.w;
+  uint32_t incl = lsum;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const uint32_t o = __shfl_up_sync(KVM_FULL, incl, d);
+    if (lane >= d) incl += o;
+  }
+  if (lane == 31) wsum[warp] = incl;
   __syncthreads();
-  if (t == 0) S.is_last = atomicAdd(&ws->c_ticket, 1u) == gridDim.x - 1;
+  uint32_t before = incl - lsum;
+  for (int w = 0; w < warp; ++w) before += wsum[w];
+  const uint32_t r = (uint32_t)s.resid;
+  if (before <= r && r < before + lsum) {   // exactly one thread
+    uint32_t b = before;
+    int k = 0;
+    const uint32_t cc[4] = {hv.x, hv.y, hv.z, hv.w};
+    for (; k < 3; ++k) {
+      if (r < b + cc[k]) break;
+      b += cc[k];
+    }
+    sb_s = (uint32_t)(4 * t + k);
+    sr_s = r - b;
+    scount_s = cc[k];
+    found_s = 1;
+  }
   __syncthreads();
-  if (!S.is_last) return;
-  __threadfence();
-  // (the stages are free now: the finish uses their shared memory)
-  static_assert(sizeof(QdFinSmem) <= sizeof(S.stage), "finish state lives in the stage area");
-  qd_finish(ws, lists, *reinterpret_cast<QdFinSmem*>(&S.stage[0][0]), results);
+  if (!found_s) {   // sub-histogram inconsistent with the list length
+    decline();
+    return;
+  }
+  const uint32_t sb = sb_s, sr = sr_s, scount = scount_s;
+  if (sh2 == 0) {   // the sub-bin is one key
+    if (t == 0) results[q] = kvm_query_result{kvm_unkey(bin_base + sb), s.n, s.rank, KVM_Q_OK, 0};
+    return;
+  }
+  // ---- keys of the sub-bin
+  const bool gather = scount <= (uint32_t)QD_SMALL;
+  uint64_t mn = QD_NONE, mx = 0;
+  auto look = [&](uint64_t key) {
+    if ((uint32_t)((key - bin_base) >> sh2) == sb) {
+      mn = key < mn ? key : mn;
+      mx = key > mx ? key : mx;
+      if (gather) {
+        const uint32_t pos = atomicAdd(&cnt_s, 1u);
+        if (pos < (uint32_t)QD_SMALL) small[pos] = key;
+      }
+    }
+  };
+#pragma unroll
+  for (int u = 0; u < QR_U; ++u)
+    if ((unsigned long long)u * QR_THREADS + t < m) look(kk[u]);
+  for (unsigned long long i0 = (unsigned long long)QR_U * QR_THREADS + t; i0 < m; i0 += (unsigned long long)QR_U * QR_THREADS) {
+    uint64_t k2[QR_U];
+#pragma unroll
+    for (int u = 0; u < QR_U; ++u) k2[u] = i0 + (unsigned long long)u * QR_THREADS < m ? __ldcg(keys + i0 + (size_t)u * QR_THREADS) : QD_NONE;
+#pragma unroll
+    for (int u = 0; u < QR_U; ++u)
+      if (k2[u] != QD_NONE) look(k2[u]);
+  }
+  mn = kvm_warp_min(mn);
+  mx = kvm_warp_max(mx);
+  if (lane == 0 && mn != QD_NONE) {
+    atomicMin(&kmin_s, (unsigned long long)mn);
+    atomicMax(&kmax_s, (unsigned long long)mx);
+  }
   __syncthreads();
-  if (t == 0) ws->ready = 0ull;   // a replay of the same launch sequence (same token) waits for its own clearing
+  if (kmin_s == kmax_s) {   // one distinct key (any number of copies)
+    if (t == 0) results[q] = kvm_query_result{kvm_unkey(kmin_s), s.n, s.rank, KVM_Q_OK, 0};
+    return;
+  }
+  const uint32_t m2 = cnt_s;
+  if (!gather || m2 != scount) {   // too many distinct candidates for the scratch: the general select's job
+    decline();
+    return;
+  }
+  for (uint32_t i = t; i < m2; i += QR_THREADS) {
+    const uint64_t k = small[i];
+    uint32_t less = 0, leq = 0;
+    for (uint32_t j = 0; j < m2; ++j) {
+      const uint64_t x = small[j];
+      less += x < k;
+      leq += x <= k;
+    }
+    if (less <= sr && sr < leq) results[q] = kvm_query_result{kvm_unkey(k), s.n, s.rank, KVM_Q_OK, 0};  // all writers agree
+  }
 }
 
 // two resident CTAs per SM, each with a contiguous share of the rows
@@ -723,6 +729,8 @@ long long qd_list_cap(int64_t n) {
 }  // namespace
 
 extern "C" int64_t kvm_column_select_sampled_min_n(void) { return 1 << 18; }
+// byte offset of the 16 phase time stamps (ns, %globaltimer) of the last call inside the workspace
+extern "C" int64_t kvm_column_select_sampled_dbg_offset(void) { return (int64_t)offsetof(QdWs, dbg); }
 
 extern "C" size_t kvm_column_select_sampled_workspace_bytes(int64_t n) {
   if (n < 0) n = 0;
@@ -792,6 +800,10 @@ extern "C" int kvm_column_select_sampled(const double* values, int64_t n, int32_
   cfg.attrs = attr;
   cfg.numAttrs = no_pdl ? 0 : 1;
   const uint16_t* recs_c = recs;
-  KVM_CUDA_CHECK(cudaLaunchKernelEx(&cfg, qd_collect_kernel<true>, values, n, recs_c, ws, lists, results));
+  KVM_CUDA_CHECK(cudaLaunchKernelEx(&cfg, qd_collect_kernel<true>, values, n, recs_c, ws, lists));
+  cfg.gridDim = dim3((unsigned)nq);
+  cfg.blockDim = dim3(QR_THREADS);
+  const uint64_t* lists_c = lists;
+  KVM_CUDA_CHECK(cudaLaunchKernelEx(&cfg, qd_rank_kernel, ws, lists_c, results));
   return KVM_OK;
 }
