@@ -220,6 +220,37 @@ int kvm_log_select(const kvm_request_log* log_host, const uint8_t* flags,
                    kvm_query_result* results, const kvm_log_extras* extras_host, void* workspace,
                    size_t workspace_bytes, int64_t arena_capacity, void* stream);
 
+/* ---- one-pass form (csrc/kvm_fused.cu).  kvm_log_scan and the select's histogram pass in ONE
+ * kernel: 56 B/row read once, flags + digit records written, statistics, the seven digit
+ * histograms and the window series produced together.  The digit parameters come from a 512-row
+ * sample drawn identically by every CTA; the two end bins catch what lies outside the sampled
+ * range and are resolved exactly by the select (plan_preset marks them, resolve spans their
+ * buckets with the true range), so the results are exact for any input.  Needs every column
+ * 32-byte aligned (256-bit loads), flags 4-byte and extras->digit_records (required) 32-byte
+ * aligned, n >= 1: otherwise KVM_ERR_UNSUPPORTED and the caller uses kvm_log_scan + kvm_log_select.
+ * The window series is binned relative to the minimum start_ms of the sample + first + last row;
+ * that reference is stored (as double bits) in extras->series_dropped[2] (the buffer needs three
+ * int64 here): when it differs from stats->min_start_ms (a log that is not time-ordered), the
+ * series must be recomputed with kvm_log_series.
+ * Stage order: fused_pass -> plan_preset -> resolve -> {refine_hist -> refine}* -> compact -> finish;
+ * kvm_log_analyze_fused chains them.  Replaces analyze.py:59-189,402-514 like scan + select. */
+size_t kvm_log_analyze_fused_scan_workspace_bytes(void);
+int kvm_log_fused_pass(const kvm_request_log* log_host, const double* cold_times, int32_t n_cold_times,
+                       double cold_window_s, uint8_t* flags, kvm_log_stats* stats,
+                       const kvm_log_extras* extras_host, void* scan_workspace, size_t scan_workspace_bytes,
+                       void* select_workspace, size_t select_workspace_bytes, int64_t arena_capacity,
+                       void* stream);
+int kvm_select_plan_preset(const kvm_set_info* info, const kvm_query* queries_host, int32_t nq,
+                           const kvm_hist_spec* hists_host, void* workspace, size_t workspace_bytes,
+                           int64_t arena_capacity, int32_t refine_rounds, int64_t refine_min_keys,
+                           void* stream);
+int kvm_log_analyze_fused(const kvm_request_log* log_host, const double* cold_times, int32_t n_cold_times,
+                          double cold_window_s, uint8_t* flags, kvm_log_stats* stats,
+                          const kvm_query* queries_host, int32_t nq, kvm_query_result* results,
+                          const kvm_log_extras* extras_host, void* scan_workspace, size_t scan_workspace_bytes,
+                          void* select_workspace, size_t select_workspace_bytes, int64_t arena_capacity,
+                          int32_t refine_rounds, int64_t refine_min_keys, void* stream);
+
 /* Generic single-column variant.  Set membership of element i:
  *   mode 0: every element is in set 0
  *   mode 1: set_ids[i] (uint8; 255 = excluded)

@@ -112,6 +112,11 @@ def _declare(lib: C.CDLL) -> None:
         "kvm_select_workspace_bytes": (sz, [i64]),
         "kvm_select_default_arena": (i64, [i64]),
         "kvm_log_select": (C.c_int, [P(RequestLogC), vp, vp, P(QueryC), i32, vp, P(LogExtrasC), vp, sz, i64, vp]),
+        "kvm_log_analyze_fused_scan_workspace_bytes": (sz, []),
+        "kvm_log_fused_pass": (C.c_int, [P(RequestLogC), vp, i32, f64, vp, vp, P(LogExtrasC), vp, sz, vp, sz, i64, vp]),
+        "kvm_select_plan_preset": (C.c_int, [vp, P(QueryC), i32, P(HistSpecC), vp, sz, i64, i32, i64, vp]),
+        "kvm_log_analyze_fused": (C.c_int, [P(RequestLogC), vp, i32, f64, vp, vp, P(QueryC), i32, vp, P(LogExtrasC),
+                                            vp, sz, vp, sz, i64, i32, i64, vp]),
         "kvm_column_select": (C.c_int, [vp, i64, i32, vp, i32, P(QueryC), i32, vp, vp, sz, i64, vp]),
         "kvm_column_select_sampled": (C.c_int, [vp, i64, i32, vp, P(QueryC), i32, vp, vp, sz, vp]),
         "kvm_column_select_sampled_workspace_bytes": (sz, [i64]),

@@ -1,0 +1,595 @@
+// kvm_fused.cu - ONE pass over the request log that does the work of kvm_log_scan (K1+K7) AND of
+// the select's histogram pass (K2/K6/K8): window bounds, cold/warm flags, counts, token sums,
+// double-double sums, exact key ranges, the seven per-set digit histograms, the 8-byte digit
+// records and the 1-s window series - 56 B/row read, 9 B/row written (57 + 49 B/row in two passes
+// before).
+//
+// The histogram pass used to need the exact key range of every value column (digit =
+// (key - kmin) >> shift), i.e. a pass of its own.  Here every CTA draws the SAME 512 rows (16
+// regions x 32 rows inside a 4096-row window: few pages, the sample's cost is TLB misses) and
+// takes the digit parameters from the sample's range: kbase = sampled minimum, shift so that the
+// sampled range spans <= 2048 bins.  Keys outside the sampled range fall into the two end bins
+// (digit_of clamps), which the select treats as catch-alls (kvm_select.cu: plan marks them for
+// exact histogram binning, resolve spans their buckets with the true range) - so the result is
+// exact for any input, the sample only decides how evenly the bins are filled.  A sampled value
+// is a real member of its column, hence values inside the sampled hull can never be the column's
+// extreme: the exact range costs one extra comparison per value and a rare shared-memory update.
+//
+// Replaces (reference file:line) analyze.py:183-189, :402-419, :496-514, :68,:89,:143 filters,
+// :581, the histogram side of :59-81 / :84-122 (via kvm_select.cu) and extension A12.
+
+#include "kvm_common.cuh"
+#include "kvm_log_device.cuh"
+#include "kvm_select_ws.cuh"
+
+namespace {
+
+constexpr int FU_THREADS = 256;
+constexpr int FU_WARPS = FU_THREADS / 32;
+constexpr int FU_COLD_SMEM = 512;
+constexpr int FU_MAX_GRID = 148 * 8;
+constexpr int NC = KVM_LOG_NCOLS;
+
+struct FusedWs {   // lives in the scan workspace (kvm_log_scan_workspace_bytes)
+  unsigned int ticket;
+  unsigned int pad[63];
+  uint64_t partial[1];  // [grid][NSLOTS]
+};
+
+struct FusedSeries {
+  double window_ms;
+  int64_t max_bins;
+  unsigned long long* series;   // [3][max_bins]
+  unsigned long long* dropped;  // [0] rows outside [0, max_bins); [2] = bits of the reference start the bins are relative to
+};
+
+struct FusedSmem {
+  uint64_t red[FU_WARPS][NSLOTS];
+  uint64_t fin[NSLOTS];
+  unsigned long long kmin[NC], kmax[NC];     // exact key range of every value column (CTA level)
+  unsigned long long hull_max[NC];           // sampled maximum: keys above it may be a new maximum
+  unsigned long long s_inv[FU_WARPS][NC], s_max[FU_WARPS][NC];
+  double s_start[FU_WARPS];
+  uint64_t kbase[NC];
+  int32_t shift[NC];
+  double series_ref;
+  double cold_lo[FU_COLD_SMEM], cold_hi[FU_COLD_SMEM];
+  int is_last;
+};
+
+// u64 min / max on shared memory, called on the rare path only
+__device__ __forceinline__ void range_update(unsigned long long* lo, unsigned long long* hi, uint64_t key) {
+  if (key < *reinterpret_cast<volatile unsigned long long*>(lo)) atomicMin(lo, (unsigned long long)key);
+  if (key > *reinterpret_cast<volatile unsigned long long*>(hi)) atomicMax(hi, (unsigned long long)key);
+}
+
+struct FAcc {
+  int32_t n_success, n_cold, n_cold_success, n_gen;
+  int64_t ctok, ttok, ttok_cold;
+  double st_min, end_max;
+  double ttfb_s, ttfb_e, lat_s, lat_e;   // sum and accumulated rounding error (two_sum)
+};
+
+__device__ __forceinline__ void dd_acc(double& s, double& e, double x) {
+  const double t = s + x;
+  const double bb = t - s;
+  e += (s - (t - bb)) + (x - bb);
+  s = t;
+}
+
+template <bool COLD_SMEM_TABLE, bool SERIES>
+__global__ void __launch_bounds__(FU_THREADS, 2)
+log_fused_kernel(kvm_request_log log, const double* __restrict__ cold_lo_g, const double* __restrict__ cold_hi_g,
+                 int nc, uint8_t* __restrict__ flags, uint64_t* __restrict__ recs, kvm_log_stats* __restrict__ out,
+                 FusedWs* fws, SelWs* ws, FusedSeries sa) {
+  extern __shared__ __align__(16) unsigned char fraw[];
+  uint32_t* sh = reinterpret_cast<uint32_t*>(fraw);   // [KVM_LOG_NSETS][BINS]
+  FusedSmem& S = *reinterpret_cast<FusedSmem*>(fraw + sizeof(uint32_t) * KVM_LOG_NSETS * BINS);
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const int64_t n = log.n;
+
+  // ---- sample: thread t takes rows 2t and 2t+1 of the 512-row sample (same rows in every CTA)
+  uint64_t s_inv[NC], s_mx[NC];
+  double s_st = __longlong_as_double(0x7ff0000000000000ll);
+#pragma unroll
+  for (int c = 0; c < NC; ++c) {
+    s_inv[c] = 0ull;
+    s_mx[c] = 0ull;
+  }
+  {
+    const int64_t win = n < 4096 ? n : 4096;
+    for (int k = 0; k < 2; ++k) {
+      const int sidx = 2 * t + k;
+      const int64_t region = sidx >> 5;
+      const int64_t off = n > win ? region * ((n - win) / 15) : 0;
+      int64_t i = off + (int64_t)(((uint32_t)sidx * 2654435761u >> 7) % (uint32_t)win);
+      if (sidx == 0) i = 0;
+      if (sidx == 511) i = n - 1;
+      const double la = __ldg(log.latency_ms + i), tf = __ldg(log.ttfb_ms + i), tl = __ldg(log.tllt_ms + i);
+      const double st = __ldg(log.start_ms + i);
+      const bool ok = __ldg(log.status + i) == 200;
+      const long long ct = __ldg(log.completion_tokens + i);
+      s_st = fmin(s_st, st);
+      auto take = [&](int c, bool mem, double v) {
+        if (mem) {
+          const uint64_t key = kvm_key(v);
+          s_inv[c] = ~key > s_inv[c] ? ~key : s_inv[c];
+          s_mx[c] = key > s_mx[c] ? key : s_mx[c];
+        }
+      };
+      take(KVM_COL_LAT, ok && la == la, la);
+      take(KVM_COL_TTFB, ok && tf == tf, tf);
+      take(KVM_COL_TLLT, ok && tl == tl, tl);
+      const bool gen = ok && tf == tf && tl == tl && ct > 0;
+      const double g = tl - tf;
+      take(KVM_COL_GEN, gen && g == g, g);
+      const double pt = g / (double)ct;
+      take(KVM_COL_PERTOK, gen && g == g && pt == pt, pt);
+    }
+  }
+  // (shared memory set-up overlaps the sample's loads)
+  for (int i = t; i < KVM_LOG_NSETS * BINS; i += FU_THREADS) sh[i] = 0;
+  ColdTable cold{COLD_SMEM_TABLE ? S.cold_lo : cold_lo_g, COLD_SMEM_TABLE ? S.cold_hi : cold_hi_g, nc};
+  kvm_pdl_wait();   // the cold-interval table is written by the kernel in front of this one
+  if (COLD_SMEM_TABLE)
+    for (int i = t; i < nc; i += FU_THREADS) {
+      S.cold_lo[i] = cold_lo_g[i];
+      S.cold_hi[i] = cold_hi_g[i];
+    }
+#pragma unroll
+  for (int c = 0; c < NC; ++c) {
+    const uint64_t a = kvm_warp_max(s_inv[c]), b = kvm_warp_max(s_mx[c]);
+    if (lane == 0) {
+      S.s_inv[warp][c] = a;
+      S.s_max[warp][c] = b;
+    }
+  }
+#pragma unroll
+  for (int m = 16; m; m >>= 1) s_st = fmin(s_st, __shfl_xor_sync(KVM_FULL, s_st, m));
+  if (lane == 0) S.s_start[warp] = s_st;
+  __syncthreads();
+  if (t < NC) {
+    uint64_t inv = 0, mx = 0;
+    for (int w = 0; w < FU_WARPS; ++w) {
+      inv = S.s_inv[w][t] > inv ? S.s_inv[w][t] : inv;
+      mx = S.s_max[w][t] > mx ? S.s_max[w][t] : mx;
+    }
+    ColParam cp;
+    if (inv == 0ull) {   // no member of this column in the sample: coarse bins over all keys
+      cp.kbase = 0ull;
+      cp.shift = 64 - BINS_LOG2;
+      cp.width = 64;
+      S.kmin[t] = ~0ull;
+      S.kmax[t] = 0ull;
+      S.hull_max[t] = 0ull;
+    } else {
+      const uint64_t mn = ~inv, range = mx - mn;
+      cp.kbase = mn;
+      cp.width = range ? 64 - __clzll((long long)range) : 1;
+      cp.shift = cp.width > BINS_LOG2 ? cp.width - BINS_LOG2 : 0;
+      S.kmin[t] = mn;   // sampled values are members: the exact range starts from their hull
+      S.kmax[t] = mx;
+      S.hull_max[t] = mx;
+    }
+    S.kbase[t] = cp.kbase;
+    S.shift[t] = cp.shift;
+    if (blockIdx.x == 0) ws->col[t] = cp;
+  }
+  if (t == 32) {
+    double s0 = S.s_start[0];
+    for (int w = 1; w < FU_WARPS; ++w) s0 = fmin(s0, S.s_start[w]);
+    S.series_ref = s0;
+    if (SERIES && blockIdx.x == 0) sa.dropped[2] = (unsigned long long)__double_as_longlong(s0);
+  }
+  __syncthreads();
+  uint64_t kb[NC];
+  int shf[NC];
+#pragma unroll
+  for (int c = 0; c < NC; ++c) {
+    kb[c] = S.kbase[c];
+    shf[c] = S.shift[c];
+  }
+  const double s0 = S.series_ref;
+  const double cold_first = nc > 0 ? cold.lo[0] : 0.0, cold_last = nc > 0 ? cold.hi[nc - 1] : -1.0;
+
+  FAcc a;
+  a.n_success = a.n_cold = a.n_cold_success = a.n_gen = 0;
+  a.ctok = a.ttok = a.ttok_cold = 0;
+  a.st_min = __longlong_as_double(0x7ff0000000000000ll);
+  a.end_max = -a.st_min;
+  a.ttfb_s = a.ttfb_e = a.lat_s = a.lat_e = 0.0;
+
+  // one (set, column, value) site: digit -> shared histogram + record; exact range on the rare path
+  uint64_t rec;
+  auto site = [&](int set, int col, double v) {
+    const uint64_t key = kvm_key(v);
+    uint32_t d = 0;
+    if (key < kb[col]) {
+      range_update(&S.kmin[col], &S.kmax[col], key);
+    } else {
+      const uint64_t x = (key - kb[col]) >> shf[col];
+      d = x < (uint64_t)BINS ? (uint32_t)x : (uint32_t)(BINS - 1);
+      if (key > S.hull_max[col]) range_update(&S.kmin[col], &S.kmax[col], key);
+    }
+    atomicAdd(&sh[set * BINS + d], 1u);
+    rec ^= (uint64_t)(0xFFFu ^ d) << (12 * col);
+  };
+  auto row = [&](double st, double la, double tf, double tl, long long status, long long ct, long long tt,
+                 uint32_t& flag_out) -> uint64_t {
+    const bool ok = status == 200;
+    bool cold_row = false;
+    if (st >= cold_first && st <= cold_last) cold_row = is_cold(st, cold);   // (nc == 0: empty hull)
+    a.st_min = fmin(a.st_min, st);         // NaN skipped by fmin / fmax
+    a.end_max = fmax(a.end_max, st + la);  // analyze.py:187
+    a.n_cold += cold_row;
+    uint32_t f = (ok ? KVM_F_SUCCESS : 0) | (cold_row ? KVM_F_COLD : 0) | (ct > 0 ? KVM_F_TOKENS : 0);
+    rec = DIGITS_NONE;
+    if (ok) {
+      a.n_success += 1;
+      a.n_cold_success += cold_row;
+      a.ctok += ct;
+      a.ttok += tt;
+      a.ttok_cold += cold_row ? tt : 0;
+      if (la == la) {
+        site(cold_row ? KVM_SET_LAT_COLD : KVM_SET_LAT_WARM, KVM_COL_LAT, la);
+        dd_acc(a.lat_s, a.lat_e, la);
+      }
+      const bool has_tf = tf == tf, has_tl = tl == tl;
+      if (has_tf) {
+        site(cold_row ? KVM_SET_TTFB_COLD : KVM_SET_TTFB_WARM, KVM_COL_TTFB, tf);
+        dd_acc(a.ttfb_s, a.ttfb_e, tf);
+      }
+      if (has_tl) site(KVM_SET_TLLT, KVM_COL_TLLT, tl);
+      if (has_tf && has_tl && ct > 0) {
+        f |= KVM_F_GEN;
+        a.n_gen += 1;
+        const double g = tl - tf;  // analyze.py:144
+        if (g == g) {
+          site(KVM_SET_GEN, KVM_COL_GEN, g);
+          const double pt = g / (double)ct;  // analyze.py:146
+          if (pt == pt) site(KVM_SET_PERTOK, KVM_COL_PERTOK, pt);
+        }
+      }
+    }
+    flag_out = f;
+    return rec;
+  };
+  auto series_row = [&](long long bin, bool ok, long long tok) {
+    if (bin >= 0) {
+      atomicAdd(&sa.series[bin], 1ull);
+      if (ok) {
+        atomicAdd(&sa.series[sa.max_bins + bin], 1ull);
+        atomicAdd(&sa.series[2 * sa.max_bins + bin], (unsigned long long)tok);
+      }
+    } else if (bin == -2) {
+      atomicAdd(sa.dropped, 1ull);
+    }
+  };
+  auto sbin = [&](double st) -> long long {
+    const double b = floor((st - s0) / sa.window_ms);
+    if (b >= 0.0 && b < (double)sa.max_bins) return (long long)b;
+    return b == b ? -2 : -1;
+  };
+
+  // ---- the stream: four consecutive rows per thread and iteration, one 256-bit load per column
+  const int64_t nquads = n >> 2;
+  for (int64_t base = (int64_t)blockIdx.x * FU_THREADS + (t & ~31); base < nquads;
+       base += (int64_t)gridDim.x * FU_THREADS) {
+    const int64_t u = base + lane;
+    const bool live = u < nquads;
+    const int64_t i = u << 2;
+    uint32_t f0 = 0, f1 = 0, f2 = 0, f3 = 0;
+    long long b0 = -1, b1 = -1, b2 = -1, b3 = -1;
+    long long t0 = 0, t1 = 0, t2 = 0, t3 = 0;
+    if (live) {
+      const kvm_u64x4 qs = kvm_ld4_nc(log.start_ms + i), ql = kvm_ld4_nc(log.latency_ms + i);
+      const kvm_u64x4 qf = kvm_ld4_nc(log.ttfb_ms + i), qt = kvm_ld4_nc(log.tllt_ms + i);
+      const kvm_u64x4 qx = kvm_ld4_nc(log.status + i), qc = kvm_ld4_nc(log.completion_tokens + i);
+      const kvm_u64x4 qo = kvm_ld4_nc(log.total_tokens + i);
+#define KVM_D(x) __longlong_as_double((long long)(x))
+      const uint64_t r0 = row(KVM_D(qs.x), KVM_D(ql.x), KVM_D(qf.x), KVM_D(qt.x), (long long)qx.x, (long long)qc.x, (long long)qo.x, f0);
+      const uint64_t r1 = row(KVM_D(qs.y), KVM_D(ql.y), KVM_D(qf.y), KVM_D(qt.y), (long long)qx.y, (long long)qc.y, (long long)qo.y, f1);
+      const uint64_t r2 = row(KVM_D(qs.z), KVM_D(ql.z), KVM_D(qf.z), KVM_D(qt.z), (long long)qx.z, (long long)qc.z, (long long)qo.z, f2);
+      const uint64_t r3 = row(KVM_D(qs.w), KVM_D(ql.w), KVM_D(qf.w), KVM_D(qt.w), (long long)qx.w, (long long)qc.w, (long long)qo.w, f3);
+      asm volatile("st.global.v4.b64 [%0], {%1,%2,%3,%4};" ::"l"(recs + i), "l"(r0), "l"(r1), "l"(r2), "l"(r3) : "memory");
+      *reinterpret_cast<uint32_t*>(flags + i) = f0 | (f1 << 8) | (f2 << 16) | (f3 << 24);
+      if (SERIES) {
+        const double sx = KVM_D(qs.x), sy = KVM_D(qs.y), sz = KVM_D(qs.z), sw = KVM_D(qs.w);
+        b0 = sbin(sx);
+        b3 = sbin(sw);
+        // rows in time order inside the quad and the same window at both ends: the middle rows
+        // are in it too (x -> floor((x - s0) / w) is monotone) - two divisions instead of four
+        if (b0 == b3 && sx <= sy && sy <= sz && sz <= sw) {
+          b1 = b2 = b0;
+        } else {
+          b1 = sbin(sy);
+          b2 = sbin(sz);
+        }
+        t0 = (long long)qc.x; t1 = (long long)qc.y; t2 = (long long)qc.z; t3 = (long long)qc.w;
+      }
+#undef KVM_D
+    }
+    if (SERIES) {
+      const bool k0 = f0 & KVM_F_SUCCESS, k1 = f1 & KVM_F_SUCCESS, k2 = f2 & KVM_F_SUCCESS, k3 = f3 & KVM_F_SUCCESS;
+      const long long lead = __shfl_sync(KVM_FULL, b0, 0);
+      if (__all_sync(KVM_FULL, live && b0 == lead && b1 == lead && b2 == lead && b3 == lead && lead >= 0)) {
+        const int nok = __reduce_add_sync(KVM_FULL, (int)k0 + (int)k1 + (int)k2 + (int)k3);
+        const int64_t tsum = kvm_warp_sum((int64_t)((k0 ? t0 : 0) + (k1 ? t1 : 0) + (k2 ? t2 : 0) + (k3 ? t3 : 0)));
+        if (lane == 0) {
+          atomicAdd(&sa.series[lead], 128ull);
+          if (nok) {
+            atomicAdd(&sa.series[sa.max_bins + lead], (unsigned long long)nok);
+            atomicAdd(&sa.series[2 * sa.max_bins + lead], (unsigned long long)tsum);
+          }
+        }
+      } else if (live) {
+        series_row(b0, k0, t0);
+        series_row(b1, k1, t1);
+        series_row(b2, k2, t2);
+        series_row(b3, k3, t3);
+      }
+    }
+  }
+  if (blockIdx.x == 0 && t < (int)(n & 3)) {   // tail rows
+    const int64_t i = (n & ~3ll) + t;
+    uint32_t f;
+    const uint64_t r = row(log.start_ms[i], log.latency_ms[i], log.ttfb_ms[i], log.tllt_ms[i], log.status[i],
+                           log.completion_tokens[i], log.total_tokens[i], f);
+    recs[i] = r;
+    flags[i] = (uint8_t)f;
+    if (SERIES) series_row(sbin(log.start_ms[i]), f & KVM_F_SUCCESS, log.completion_tokens[i]);
+  }
+
+  // ---- per-thread accumulators -> warp -> CTA partial (slot layout of kvm_log_device.cuh)
+  {
+    auto wsum = [&](int64_t v) { return (uint64_t)kvm_warp_sum(v); };
+    const uint64_t v_succ = wsum(a.n_success), v_cold = wsum(a.n_cold), v_cs = wsum(a.n_cold_success);
+    const uint64_t v_gen = wsum(a.n_gen), v_ct = wsum(a.ctok), v_tt = wsum(a.ttok), v_tc = wsum(a.ttok_cold);
+    // start / end as ordered keys (untouched: +inf / -inf, which stats_from_slots maps to NaN)
+    const uint64_t v_st = kvm_warp_min(kvm_key(a.st_min)), v_en = kvm_warp_max(kvm_key(a.end_max));
+    auto dd_of = [](double s, double e) {
+      const double hi = s + e;
+      return kvm_dd{hi, e - (hi - s)};
+    };
+    const kvm_dd tfs = kvm_warp_sum(dd_of(a.ttfb_s, a.ttfb_e)), las = kvm_warp_sum(dd_of(a.lat_s, a.lat_e));
+    if (lane == 0) {
+      uint64_t* r = S.red[warp];
+      r[S_SUCCESS] = v_succ; r[S_COLD] = v_cold; r[S_COLD_SUCCESS] = v_cs; r[S_CTOK] = v_ct;
+      r[S_TTOK] = v_tt; r[S_TTOK_COLD] = v_tc; r[S_GEN_ROWS] = v_gen;
+      r[M_START] = v_st; r[X_END] = v_en;
+      r[D_TTFB] = (uint64_t)__double_as_longlong(tfs.hi); r[D_TTFB + 1] = (uint64_t)__double_as_longlong(tfs.lo);
+      r[D_LAT] = (uint64_t)__double_as_longlong(las.hi); r[D_LAT + 1] = (uint64_t)__double_as_longlong(las.lo);
+    }
+  }
+  __syncthreads();
+  // flush the histograms (64-bit global atomics on the non-zero bins) and count the sets on the way
+  {
+    uint32_t setsum[KVM_LOG_NSETS];
+#pragma unroll
+    for (int s = 0; s < KVM_LOG_NSETS; ++s) setsum[s] = 0;
+#pragma unroll
+    for (int s = 0; s < KVM_LOG_NSETS; ++s)
+      for (int b = t; b < BINS; b += FU_THREADS) {
+        const uint32_t c = sh[s * BINS + b];
+        if (c) {
+          atomicAdd(reinterpret_cast<unsigned long long*>(&ws->hist[s][b]), (unsigned long long)c);
+          setsum[s] += c;
+        }
+      }
+#pragma unroll
+    for (int s = 0; s < KVM_LOG_NSETS; ++s) {
+      const uint32_t v = __reduce_add_sync(KVM_FULL, setsum[s]);
+      if (lane == 0) S.red[warp][S_CNT0 + s] = v;
+    }
+  }
+  __syncthreads();
+  auto dd_bits = [](uint64_t hi, uint64_t lo) {
+    return kvm_dd{__longlong_as_double((long long)hi), __longlong_as_double((long long)lo)};
+  };
+  auto combine = [](int slot, uint64_t acc, uint64_t v) -> uint64_t {
+    if (slot < NSUM) return (uint64_t)((int64_t)acc + (int64_t)v);
+    if (slot < NMIN_END) return v < acc ? v : acc;
+    return v > acc ? v : acc;
+  };
+  uint64_t* mine = fws->partial + (size_t)blockIdx.x * NSLOTS;
+  if (t < NMAX_END) {
+    const int s = t;
+    uint64_t acc;
+    if (s >= M_KMIN0 && s < M_KMIN0 + NC) acc = S.kmin[s - M_KMIN0];
+    else if (s >= X_KMAX0 && s < X_KMAX0 + NC) acc = S.kmax[s - X_KMAX0];
+    else {
+      acc = S.red[0][s];
+      for (int w = 1; w < FU_WARPS; ++w) acc = combine(s, acc, S.red[w][s]);
+    }
+    mine[s] = acc;
+  } else if (t == NMAX_END || t == NMAX_END + 1) {
+    const int s = t == NMAX_END ? D_TTFB : D_LAT;
+    kvm_dd acc = dd_bits(S.red[0][s], S.red[0][s + 1]);
+    for (int w = 1; w < FU_WARPS; ++w) acc = kvm_dd_add(acc, dd_bits(S.red[w][s], S.red[w][s + 1]));
+    mine[s] = (uint64_t)__double_as_longlong(acc.hi);
+    mine[s + 1] = (uint64_t)__double_as_longlong(acc.lo);
+  }
+  __threadfence();
+  __syncthreads();
+  if (t == 0) S.is_last = atomicAdd(&fws->ticket, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (!S.is_last) return;
+  __threadfence();
+  // ---- last CTA: fixed-shape reduction over the CTA partials (see kvm_stats.cu)
+  const uint64_t* part = fws->partial;
+  for (int s = warp; s < NSLOTS; s += FU_WARPS) {
+    if (s < NMAX_END) {
+      uint64_t acc = s < NSUM ? 0ull : (s < NMIN_END ? ~0ull : 0ull);
+      for (unsigned g = lane; g < gridDim.x; g += 32) acc = combine(s, acc, __ldcg(part + (size_t)g * NSLOTS + s));
+#pragma unroll
+      for (int m = 16; m; m >>= 1) acc = combine(s, acc, kvm_shfl_xor(acc, m));
+      if (lane == 0) S.fin[s] = acc;
+    } else if (s == D_TTFB || s == D_LAT) {
+      kvm_dd acc{0.0, 0.0};
+      for (unsigned g = lane; g < gridDim.x; g += 32) {
+        const size_t o = (size_t)g * NSLOTS + s;
+        acc = kvm_dd_add(acc, dd_bits(__ldcg(part + o), __ldcg(part + o + 1)));
+      }
+      acc = kvm_warp_sum(acc);
+      if (lane == 0) {
+        S.fin[s] = (uint64_t)__double_as_longlong(acc.hi);
+        S.fin[s + 1] = (uint64_t)__double_as_longlong(acc.lo);
+      }
+    }
+  }
+  __syncthreads();
+  if (t == 0) {
+    kvm_log_stats r;
+    stats_from_slots(S.fin, n, r);
+    *out = r;
+    fws->ticket = 0;
+  }
+}
+
+// One thread per cold start: the closed start_ms interval that the reference classifies cold.
+__global__ void fused_cold_table_kernel(const double* __restrict__ cold_times, int nc, double window,
+                                        double* __restrict__ lo, double* __restrict__ hi) {
+  kvm_pdl_launch_dependents();
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < nc) cold_interval(cold_times[i], window, lo + i, hi + i);
+}
+
+constexpr int FU_MAX_COLD = 16384;
+size_t fused_partials_bytes() { return kvm_align_up(256 + sizeof(uint64_t) * (size_t)NSLOTS * FU_MAX_GRID, 256); }
+bool aligned_to(const void* p, uintptr_t a) { return (reinterpret_cast<uintptr_t>(p) & (a - 1)) == 0; }
+
+}  // namespace
+
+extern "C" size_t kvm_log_analyze_fused_scan_workspace_bytes(void) {
+  return fused_partials_bytes() + 2 * sizeof(double) * (size_t)FU_MAX_COLD;
+}
+
+extern "C" int kvm_log_fused_pass(const kvm_request_log* log, const double* cold_times, int32_t n_cold,
+                                  double cold_window_s, uint8_t* flags, kvm_log_stats* stats,
+                                  const kvm_log_extras* extras, void* scan_workspace, size_t scan_workspace_bytes,
+                                  void* select_workspace, size_t select_workspace_bytes, int64_t arena_capacity,
+                                  void* stream) {
+  KVM_REQUIRE(log && flags && stats && extras && scan_workspace && select_workspace,
+              "kvm_log_analyze_fused: null argument");
+  KVM_REQUIRE(log->n >= 0 && n_cold >= 0 && (n_cold == 0 || cold_times), "kvm_log_analyze_fused: bad sizes");
+  KVM_REQUIRE(n_cold <= FU_MAX_COLD, "kvm_log_analyze_fused: %d cold starts exceed the supported %d", n_cold, FU_MAX_COLD);
+  KVM_REQUIRE(extras->digit_records, "kvm_log_analyze_fused: digit_records scratch is required");
+  const bool series = extras->series_window_ms > 0.0;
+  if (series)
+    KVM_REQUIRE(extras->series && extras->series_dropped && extras->series_max_bins >= 1,
+                "kvm_log_analyze_fused: series requested without buffers");
+  // the one-pass kernel streams with 256-bit loads: every column 32-byte aligned (whole logs are;
+  // a shard cut at an odd row is not - the caller then uses the two-pass entry points)
+  if (!(aligned_to(log->start_ms, 32) && aligned_to(log->latency_ms, 32) && aligned_to(log->ttfb_ms, 32) &&
+        aligned_to(log->tllt_ms, 32) && aligned_to(log->status, 32) && aligned_to(log->completion_tokens, 32) &&
+        aligned_to(log->total_tokens, 32) && aligned_to(flags, 4) && aligned_to(extras->digit_records, 32)) ||
+      log->n < 1) {
+    kvm_set_error("kvm_log_analyze_fused: needs a non-empty log with 32-byte aligned columns; use kvm_log_scan + kvm_log_select");
+    return KVM_ERR_UNSUPPORTED;
+  }
+  if (scan_workspace_bytes < kvm_log_analyze_fused_scan_workspace_bytes()) {
+    kvm_set_error("kvm_log_analyze_fused: scan workspace %zu < %zu bytes", scan_workspace_bytes,
+                  kvm_log_analyze_fused_scan_workspace_bytes());
+    return KVM_ERR_WORKSPACE;
+  }
+  if (select_workspace_bytes < kvm_select_workspace_bytes(arena_capacity)) {
+    kvm_set_error("kvm_log_analyze_fused: select workspace %zu < %zu bytes", select_workspace_bytes,
+                  kvm_select_workspace_bytes(arena_capacity));
+    return KVM_ERR_WORKSPACE;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  FusedWs* fws = reinterpret_cast<FusedWs*>(scan_workspace);
+  SelWs* ws = reinterpret_cast<SelWs*>(select_workspace);
+  double* cold_lo = reinterpret_cast<double*>(reinterpret_cast<unsigned char*>(scan_workspace) + fused_partials_bytes());
+  double* cold_hi = cold_lo + FU_MAX_COLD;
+  KVM_CUDA_CHECK(cudaMemsetAsync(fws, 0, 256, st));
+  KVM_CUDA_CHECK(cudaMemsetAsync(&ws->hist[0][0], 0, sizeof(ws->hist), st));
+  FusedSeries sa{};
+  if (series) {
+    sa.window_ms = extras->series_window_ms;
+    sa.max_bins = extras->series_max_bins;
+    sa.series = reinterpret_cast<unsigned long long*>(extras->series);
+    sa.dropped = reinterpret_cast<unsigned long long*>(extras->series_dropped);
+    KVM_CUDA_CHECK(cudaMemsetAsync(extras->series, 0, sizeof(int64_t) * 3 * (size_t)extras->series_max_bins, st));
+    KVM_CUDA_CHECK(cudaMemsetAsync(extras->series_dropped, 0, 3 * sizeof(int64_t), st));
+  }
+  if (n_cold > 0)
+    fused_cold_table_kernel<<<(n_cold + 127) / 128, 128, 0, st>>>(cold_times, n_cold, cold_window_s, cold_lo, cold_hi);
+  const size_t smem = sizeof(uint32_t) * KVM_LOG_NSETS * BINS + sizeof(FusedSmem);
+  int grid = kvm_grid_for(log->n, FU_THREADS * 4 * 2, 2);
+  if (grid > FU_MAX_GRID) grid = FU_MAX_GRID;
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3((unsigned)grid);
+  cfg.blockDim = dim3(FU_THREADS);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = n_cold > 0 ? 1 : 0;   // behind the cold-table kernel: the sample overlaps it
+  uint64_t* recs = reinterpret_cast<uint64_t*>(extras->digit_records);
+  const double* lo_c = cold_lo;
+  const double* hi_c = cold_hi;
+  const bool smem_table = n_cold <= FU_COLD_SMEM;
+#define KVM_LAUNCH_FUSED(T, S)                                                                                 \
+  do {                                                                                                         \
+    KVM_CUDA_CHECK(cudaFuncSetAttribute((const void*)log_fused_kernel<T, S>,                                   \
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));              \
+    KVM_CUDA_CHECK(cudaLaunchKernelEx(&cfg, log_fused_kernel<T, S>, *log, lo_c, hi_c, (int)n_cold, flags, recs, \
+                                      stats, fws, ws, sa));                                                    \
+  } while (0)
+  if (smem_table && series) KVM_LAUNCH_FUSED(true, true);
+  else if (smem_table) KVM_LAUNCH_FUSED(true, false);
+  else if (series) KVM_LAUNCH_FUSED(false, true);
+  else KVM_LAUNCH_FUSED(false, false);
+#undef KVM_LAUNCH_FUSED
+  return KVM_OK;
+}
+
+static kvm_hist_spec fused_hist_spec(int32_t num_bins) {
+  kvm_hist_spec hs{};
+  hs.nhist = 4;
+  hs.num_bins = num_bins;
+  hs.col[0] = KVM_COL_TTFB; hs.col[1] = KVM_COL_TLLT; hs.col[2] = KVM_COL_GEN; hs.col[3] = KVM_COL_PERTOK;
+  hs.set_mask[0] = (1u << KVM_SET_TTFB_COLD) | (1u << KVM_SET_TTFB_WARM);
+  hs.set_mask[1] = 1u << KVM_SET_TLLT;
+  hs.set_mask[2] = 1u << KVM_SET_GEN;
+  hs.set_mask[3] = 1u << KVM_SET_PERTOK;
+  return hs;
+}
+
+extern "C" int kvm_select_plan_preset(const kvm_set_info* info, const kvm_query* queries, int32_t nq,
+                                      const kvm_hist_spec* hists, void* workspace, size_t workspace_bytes,
+                                      int64_t arena_capacity, int32_t refine_rounds, int64_t refine_min_keys,
+                                      void* stream) {
+  return kvm_select_plan_internal(info, queries, nq, hists, workspace, workspace_bytes, arena_capacity,
+                                  refine_rounds, refine_min_keys, 1, stream);
+}
+
+extern "C" int kvm_log_analyze_fused(const kvm_request_log* log, const double* cold_times, int32_t n_cold,
+                                     double cold_window_s, uint8_t* flags, kvm_log_stats* stats,
+                                     const kvm_query* queries, int32_t nq, kvm_query_result* results,
+                                     const kvm_log_extras* extras, void* scan_workspace,
+                                     size_t scan_workspace_bytes, void* select_workspace,
+                                     size_t select_workspace_bytes, int64_t arena_capacity,
+                                     int32_t refine_rounds, int64_t refine_min_keys, void* stream) {
+  KVM_REQUIRE(queries && results, "kvm_log_analyze_fused: null argument");
+  int rc = kvm_log_fused_pass(log, cold_times, n_cold, cold_window_s, flags, stats, extras, scan_workspace,
+                              scan_workspace_bytes, select_workspace, select_workspace_bytes, arena_capacity, stream);
+  if (rc) return rc;
+  const uint64_t* recs = reinterpret_cast<const uint64_t*>(extras->digit_records);
+  const bool hists = extras->num_bins > 0;
+  KVM_REQUIRE(!hists || extras->hist_counts, "kvm_log_analyze_fused: hist_counts is null");
+  const kvm_hist_spec hs = fused_hist_spec(extras->num_bins);
+  rc = kvm_select_plan_internal(&stats->sets, queries, nq, hists ? &hs : nullptr, select_workspace,
+                                select_workspace_bytes, arena_capacity, refine_rounds, refine_min_keys, 1, stream);
+  if (rc) return rc;
+  if ((rc = kvm_select_resolve(select_workspace, stream))) return rc;
+  for (int r = 0; r < refine_rounds; ++r) {
+    if ((rc = kvm_log_select_refine_hist(log, flags, recs, select_workspace, stream))) return rc;
+    if ((rc = kvm_select_refine(select_workspace, stream))) return rc;
+  }
+  if ((rc = kvm_log_select_compact(log, flags, recs, select_workspace, stream))) return rc;
+  return kvm_select_finish(select_workspace, nullptr, 0, nullptr, results, hists ? extras->hist_counts : nullptr, stream);
+}

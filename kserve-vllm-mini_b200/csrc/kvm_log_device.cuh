@@ -263,10 +263,17 @@ __device__ __forceinline__ int64_t resolve_rank(int kind, double p, int64_t n, i
   return -1;
 }
 
+// Bin 0 also takes every key below kbase and bin BINS-1 every key beyond the last bin: with
+// digit parameters taken from the exact column range neither happens; with parameters estimated
+// from a sample (csrc/kvm_fused.cu) the two end bins are catch-alls.
 __device__ __forceinline__ uint32_t digit_of(uint64_t key, uint64_t kbase, int shift) {
+  if (key < kbase) return 0u;
   uint64_t d = (key - kbase) >> shift;
   return d < (uint64_t)BINS ? (uint32_t)d : (uint32_t)(BINS - 1);
 }
+// x >> s for s in [0, 64]
+__device__ __forceinline__ uint64_t shr64(uint64_t x, int s) { return s >= 64 ? 0ull : x >> s; }
+__device__ __forceinline__ int bit_width64(uint64_t x) { return x ? 64 - __clzll((long long)x) : 0; }
 
 // Calls f(set, col, key) for every base set the row belongs to (KVM_SET_* semantics).
 template <class F>

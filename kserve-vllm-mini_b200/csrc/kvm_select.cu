@@ -32,111 +32,16 @@
 #include "kvm_common.cuh"
 #include "kvm_log_device.cuh"
 #include "kvm_peer.cuh"
+#include "kvm_select_ws.cuh"
 
 namespace {
-
-constexpr int SEL_THREADS = 512;
-constexpr int MAXQ = KVM_MAX_QUERIES;
-constexpr int MAX_SRC = 16;
-constexpr int STATS_SCRATCH = 256 + 8 * (KVM_MAX_SETS + 2) * 148 * 8;
-constexpr int NH = KVM_MAX_HISTS;   // value histograms per problem
-constexpr int NB_MAX = KVM_HIST_MAX_BINS;
-
-struct ColParam {
-  uint64_t kbase;
-  int32_t shift;  // digit = (key - kbase) >> shift
-  int32_t width;  // significant bits of (kmax - kmin); 0 => column holds one distinct key
-};
-
-struct Bucket {
-  uint64_t base;  // keys of the bucket lie in [base, base + 2^shift)
-  int32_t shift;
-  int32_t col;
-  uint32_t set_mask;
-  uint32_t bin;
-  int64_t count;  // global number of keys in the bucket
-  int32_t run;    // buckets sharing (col, bin) starting at this one (valid in the first)
-  int32_t pad;
-};
-
-struct QState {
-  int64_t n;
-  int64_t rank;
-  int64_t resid;  // rank inside the bucket
-  uint64_t key;   // valid when resolved
-  int32_t status; // KVM_Q_*
-  int32_t bucket; // -1 when resolved without candidates
-  int32_t col;
-  int32_t resolved;
-};
-
-struct SelWs {
-  int32_t status;
-  int32_t nq;
-  int32_t nbuckets;
-  int32_t refine;          // 1: the candidate buckets are still too large - one more refine round runs
-  int64_t arena_capacity;
-  int64_t arena_used;
-  int32_t refine_budget;   // refine rounds the host will still launch
-  int32_t level;           // 1 after resolve, +1 per refine round that ran
-  int64_t refine_min;      // refine while the buckets hold more keys than this in total
-  int32_t nparents;        // level-1 buckets (the lookup table's targets)
-  int32_t pad1;
-  kvm_set_info info;
-  kvm_query queries[MAXQ];
-  ColParam col[KVM_MAX_COLS];
-  QState q[MAXQ];
-  Bucket bucket[MAXQ];           // the candidate buckets keys are appended to ("targets")
-  int64_t bucket_offsets[MAXQ + 1];
-  int64_t bucket_counts[MAXQ];  // local append cursors (compact)
-  Bucket parent[MAXQ];           // the level-1 buckets the lookup table points at; after a refine
-  uint8_t child_first[MAXQ];     // round each one owns the contiguous targets
-  uint8_t child_n[MAXQ];         // [child_first, child_first + child_n) that subdivide it
-  int32_t tparent[MAXQ];         // level-1 bucket of each target
-  kvm_hist_spec hspec;
-  int32_t active20[NH];
-  int32_t col_hist[KVM_MAX_COLS];  // value histogram fed by each column, -1 = none
-  uint64_t thr20[NH][NB_MAX];
-  uint32_t flag20[NH][BINS / 32];
-  unsigned long long edge20[NH][NB_MAX];
-  uint8_t edge_code[KVM_MAX_COLS][BINS];  // 0: no histogram edge in this fine bin; b: exactly edge b;
-                                          // 255: several edges (rank against all of them)
-  uint16_t tab[KVM_MAX_COLS][BINS];       // low byte: first bucket with that (col, bin), 255 = none;
-                                          // high byte: edge_code
-  uint64_t hist[KVM_MAX_SETS][BINS];
-  uint64_t hist2[MAXQ][BINS];  // refine round: per target, histogram of the next 11 key bits
-  unsigned char stats_scratch[STATS_SCRATCH];
-};
-
-constexpr size_t WS_HEADER = (sizeof(SelWs) + 255) / 256 * 256;
-
-struct QueryPack {
-  kvm_query q[MAXQ];
-  int32_t nq;
-};
-
-struct SrcPack {
-  const uint64_t* arena[MAX_SRC];
-  int32_t nsrc;
-};
-
-constexpr uint64_t DIGITS_NONE = 0x0FFFFFFFFFFFFFFFull;  // five 12-bit fields, all "not in a set"
-
-struct SeriesArgs {
-  const double* start_ms;
-  const kvm_log_stats* stats;  // min_start_ms read on the device
-  double window_ms;
-  int64_t max_bins;
-  unsigned long long* series;  // [3][max_bins]
-  unsigned long long* dropped;
-};
 
 // ------------------------------------------------------------------ plan
 constexpr int PLAN_THREADS = 512;
 
 __global__ void __launch_bounds__(PLAN_THREADS)
 select_plan_kernel(SelWs* ws, const kvm_set_info* info_in, QueryPack qp, kvm_hist_spec hs,
-                   int64_t arena_capacity, int refine_rounds, int64_t refine_min) {
+                   int64_t arena_capacity, int refine_rounds, int64_t refine_min, int preset) {
   __shared__ kvm_set_info info;
   __shared__ ColParam cps[KVM_MAX_COLS];
   __shared__ uint64_t thr_s[NH][NB_MAX];
@@ -146,8 +51,9 @@ select_plan_kernel(SelWs* ws, const kvm_set_info* info_in, QueryPack qp, kvm_his
   static_assert(sizeof(kvm_set_info) % 8 == 0, "kvm_set_info is copied as 8-byte words");
   if (t < (int)(sizeof(kvm_set_info) / 8))
     reinterpret_cast<uint64_t*>(&info)[t] = reinterpret_cast<const uint64_t*>(info_in)[t];
-  // zero what the passes accumulate into
-  for (int i = t; i < KVM_MAX_SETS * BINS; i += PLAN_THREADS) (&ws->hist[0][0])[i] = 0;
+  // zero what the passes accumulate into (preset: the fused pass has already filled the histograms)
+  if (!preset)
+    for (int i = t; i < KVM_MAX_SETS * BINS; i += PLAN_THREADS) (&ws->hist[0][0])[i] = 0;
   for (int i = t; i < NH * NB_MAX; i += PLAN_THREADS) {
     (&ws->edge20[0][0])[i] = 0;
     (&thr_s[0][0])[i] = ~0ull;
@@ -167,13 +73,16 @@ select_plan_kernel(SelWs* ws, const kvm_set_info* info_in, QueryPack qp, kvm_his
     ws->refine_min = refine_min;
     ws->level = 0;
     ws->nparents = 0;
+    ws->preset_cols = preset;
     ws->hspec = hs;
   }
   if (t < (int)(sizeof(kvm_set_info) / 8))
     reinterpret_cast<uint64_t*>(&ws->info)[t] = reinterpret_cast<const uint64_t*>(&info)[t];
   if (t < KVM_MAX_COLS) {
     ColParam cp{0, 0, 0};
-    if (t < info.ncols && info.kmin[t] <= info.kmax[t]) {
+    if (preset) {
+      cp = ws->col[t];   // written by the fused pass from its sample
+    } else if (t < info.ncols && info.kmin[t] <= info.kmax[t]) {
       const uint64_t range = info.kmax[t] - info.kmin[t];
       cp.kbase = info.kmin[t];
       cp.width = range ? 64 - __clzll((long long)range) : 0;
@@ -248,6 +157,20 @@ select_plan_kernel(SelWs* ws, const kvm_set_info* info_in, QueryPack qp, kvm_his
         const uint32_t d = digit_of(T, cps[c].kbase, cps[c].shift);
         edge_s[c][d] = d == prev ? 255 : (uint8_t)b;
         prev = d;
+      }
+      if (preset) {
+        // sampled digit parameters: an end bin that holds keys from outside its nominal range
+        // cannot be added wholesale - its keys are ranked against all thresholds one by one
+        const ColParam cp = cps[c];
+        const uint64_t top = cp.kbase + ((uint64_t)(BINS - 1) << cp.shift);
+        if (info.kmin[c] < cp.kbase) {
+          edge_s[c][0] = 255;
+          atomicOr(&ws->flag20[h][0], 1u);
+        }
+        if (info.kmax[c] >= top && shr64(info.kmax[c] - top, cp.shift) != 0) {
+          edge_s[c][BINS - 1] = 255;
+          atomicOr(&ws->flag20[h][(BINS - 1) >> 5], 1u << ((BINS - 1) & 31));
+        }
       }
     }
   }
@@ -522,6 +445,7 @@ __global__ void __launch_bounds__(RES_THREADS, 1) select_resolve_kernel(SelWs* w
   __shared__ uint32_t qmask[MAXQ];
   __shared__ ColParam cps[KVM_MAX_COLS];
   __shared__ int64_t gsum[KVM_MAX_SETS][BINS / 32];
+  __shared__ int q_catch[MAXQ];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = RES_THREADS / 32;
   const int nq = ws->nq;
   const int nsets = ws->info.nsets;
@@ -530,6 +454,7 @@ __global__ void __launch_bounds__(RES_THREADS, 1) select_resolve_kernel(SelWs* w
   if (threadIdx.x < MAXQ) {
     qs[threadIdx.x] = ws->q[threadIdx.x];
     qmask[threadIdx.x] = ws->queries[threadIdx.x].set_mask;
+    q_catch[threadIdx.x] = 0;
   }
   if (threadIdx.x < KVM_MAX_COLS) cps[threadIdx.x] = ws->col[threadIdx.x];
   __syncthreads();
@@ -547,7 +472,7 @@ __global__ void __launch_bounds__(RES_THREADS, 1) select_resolve_kernel(SelWs* w
     if (s.status != KVM_Q_OK) continue;
     const ColParam cp = cps[s.col];
     const uint32_t mask = qmask[q];
-    if (cp.width == 0) {  // one distinct key in the column
+    if (cp.width == 0 && !ws->preset_cols) {  // one distinct key in the column
       if (lane == 0) {
         s.key = cp.kbase;
         s.resolved = 1;
@@ -600,7 +525,14 @@ __global__ void __launch_bounds__(RES_THREADS, 1) select_resolve_kernel(SelWs* w
           q_bin[q] = (uint32_t)(base + l);
           q_cnt[q] = cnt;
           s.resid = s.rank - (before + excl);
-          if (cp.shift == 0) {  // the digit is the whole key
+          // (sampled digit parameters: an end bin may hold keys from outside its nominal range)
+          const uint64_t kmn = ws->info.kmin[s.col], kmx = ws->info.kmax[s.col];
+          const uint64_t top = cp.kbase + ((uint64_t)(BINS - 1) << cp.shift);
+          const bool impure = ws->preset_cols &&
+                              ((base + l == 0 && kmn < cp.kbase) ||
+                               (base + l == BINS - 1 && kmx >= top && shr64(kmx - top, cp.shift) != 0));
+          q_catch[q] = impure ? 1 : 0;
+          if (cp.shift == 0 && !impure) {  // the digit is the whole key
             s.key = cp.kbase + (uint64_t)(base + l);
             s.resolved = 1;
             s.bucket = -1;
@@ -681,6 +613,19 @@ __global__ void __launch_bounds__(RES_THREADS, 1) select_resolve_kernel(SelWs* w
     Bucket b;
     b.base = cp.kbase + ((uint64_t)q_bin[t] << cp.shift);
     b.shift = cp.shift;
+    if (q_catch[t]) {
+      // catch-all end bin: the bucket spans from the column's true minimum (bin 0) / up to its
+      // true maximum (last bin); shift = bits needed for (key - base) inside it
+      const uint64_t kmn = ws->info.kmin[s.col], kmx = ws->info.kmax[s.col];
+      if (q_bin[t] == 0) {
+        const uint64_t hi = cp.kbase + ((1ull << cp.shift) - 1ull);   // last key of the nominal bin
+        b.base = kmn;
+        b.shift = bit_width64((kmx < hi ? kmx : hi) - kmn);
+      } else {
+        b.shift = bit_width64(kmx - b.base);
+      }
+      if (b.shift == 0) b.shift = 1;   // (a bucket is always narrowed by at least one pass)
+    }
     b.col = s.col;
     b.set_mask = qmask[t];
     b.bin = q_bin[t];
@@ -1105,7 +1050,7 @@ __device__ __forceinline__ void target_hits_warp(SelWs* ws, CompactSmem& S, uint
     const int cf = j >= 0 ? (int)S.cf[j] : 0, cn = j >= 0 ? (int)S.cn[j] : 0;
     for (int cc = 0; cc < maxc; ++cc) {
       int c = -1;
-      if (cc < cn && ((key - S.tbase[cf + cc]) >> S.tshift[cf + cc]) == 0) c = cf + cc;
+      if (cc < cn && shr64(key - S.tbase[cf + cc], S.tshift[cf + cc]) == 0) c = cf + cc;
       if (PHASE == 1) {
         if (c >= 0) {
           const int sh2 = S.tshift[c] > BINS_LOG2 ? S.tshift[c] - BINS_LOG2 : 0;
@@ -1575,7 +1520,7 @@ select_finish_kernel(SelWs* ws, SrcPack src, const int64_t* __restrict__ src_cou
         const uint64_t* __restrict__ keys = src.arena[sidx] + off;
         for (int64_t i = threadIdx.x; i < cnt; i += FIN_THREADS) {
           const uint64_t k = keys[i];
-          if (((k - b.base) >> rem) == prefix) {
+          if (shr64(k - b.base, rem) == prefix) {
             const uint32_t p = atomicAdd(&small_n, 1u);
             if (p < FIN_SMALL) small[p] = k;
           }
@@ -1616,7 +1561,7 @@ select_finish_kernel(SelWs* ws, SrcPack src, const int64_t* __restrict__ src_cou
         for (int u = 0; u < 4; ++u) {
           const int64_t i = i0 + (int64_t)u * FIN_THREADS;
           const uint64_t low = kk[u] - b.base;
-          if (i < cnt && (low >> rem) == prefix) atomicAdd(&hist[(uint32_t)(low >> sh) & dmask], 1u);
+          if (i < cnt && shr64(low, rem) == prefix) atomicAdd(&hist[(uint32_t)(low >> sh) & dmask], 1u);
         }
       }
     }
@@ -1748,6 +1693,16 @@ extern "C" int kvm_select_plan_refine(const kvm_set_info* info, const kvm_query*
                                       const kvm_hist_spec* hists, void* workspace, size_t workspace_bytes,
                                       int64_t arena_capacity, int32_t refine_rounds, int64_t refine_min_keys,
                                       void* stream) {
+  return kvm_select_plan_internal(info, queries, nq, hists, workspace, workspace_bytes, arena_capacity,
+                                  refine_rounds, refine_min_keys, 0, stream);
+}
+
+// preset != 0: the digit parameters (ws->col) and the histograms are already in the workspace -
+// written by the fused pass (csrc/kvm_fused.cu) from a sample; the plan leaves both alone.
+int kvm_select_plan_internal(const kvm_set_info* info, const kvm_query* queries, int32_t nq,
+                             const kvm_hist_spec* hists, void* workspace, size_t workspace_bytes,
+                             int64_t arena_capacity, int32_t refine_rounds, int64_t refine_min_keys,
+                             int32_t preset, void* stream) {
   KVM_REQUIRE(info && queries && workspace, "kvm_select_plan: null argument");
   KVM_REQUIRE(refine_rounds >= 0 && refine_rounds <= 4 && refine_min_keys >= 0,
               "kvm_select_plan: refine_rounds=%d outside [0,4] or negative refine_min_keys", refine_rounds);
@@ -1766,7 +1721,7 @@ extern "C" int kvm_select_plan_refine(const kvm_set_info* info, const kvm_query*
   for (int i = 0; i < MAXQ; ++i) qp.q[i] = i < nq ? queries[i] : kvm_query{0, 0, 0.0, 0};
   qp.nq = nq;
   select_plan_kernel<<<1, PLAN_THREADS, 0, (cudaStream_t)stream>>>(ws, info, qp, hs, arena_capacity,
-                                                                  refine_rounds, refine_min_keys);
+                                                                  refine_rounds, refine_min_keys, preset ? 1 : 0);
   KVM_CUDA_CHECK(cudaGetLastError());
   return KVM_OK;
 }

@@ -239,7 +239,9 @@ class LogAnalyzer:
         # resolving kernels of one analysis run beside the streaming passes of the other
         self.stream = stream
         assert C.sizeof(N.LogStatsC) <= self._OFF_RESULTS and C.sizeof(N.QueryResultC) == 32
-        self._scan_ws = torch.empty(self.lib.kvm_log_scan_workspace_bytes(), dtype=torch.uint8, device=self.device)
+        self._scan_ws = torch.empty(max(int(self.lib.kvm_log_scan_workspace_bytes()),
+                                        int(self.lib.kvm_log_analyze_fused_scan_workspace_bytes())),
+                                    dtype=torch.uint8, device=self.device)
         self._out_d = torch.zeros(self._OUTBOX, dtype=torch.uint8, device=self.device)
         self._out_h = torch.zeros(self._OUTBOX, dtype=torch.uint8).pin_memory()
         base = self._out_d.data_ptr()
@@ -265,6 +267,10 @@ class LogAnalyzer:
         self._done = torch.cuda.Event()
         self.launches = 0   # kernels launched by the last analyze() (for bench accounting)
         self.timer = _NoTimer()   # bench.py swaps in a StageTimer
+        # one-pass form (kvm_log_fused_pass: scan + histograms in one kernel) whenever the columns
+        # allow it (32-byte aligned); False: always the two-pass form (scan, then histogram pass)
+        self.use_fused = True
+        self.last_path = ""
         self.refine_rounds: Optional[int] = None            # None: by log size (_refine_rounds)
         self.refine_min_keys: int = self.REFINE_MIN_KEYS    # a round works only above this many candidates
 
@@ -291,6 +297,14 @@ class LogAnalyzer:
         if self.refine_rounds is not None:
             return int(self.refine_rounds)
         return 1 if n_rows >= self.REFINE_MIN_ROWS else 0
+
+    def _fused_ok(self, dlog: "DeviceLog", fused_hists: bool) -> bool:
+        """The one-pass form needs 32-byte aligned columns and the histograms folded into the select."""
+        if not (self.use_fused and fused_hists and dlog.n >= 1 and not getattr(self, "_fused_off", False)):
+            return False
+        if (dlog.cols["start_ms"].data_ptr(), dlog.n) in getattr(self, "_unordered_logs", ()):
+            return False   # seen before: rows out of time order, the series needs the exact minimum first
+        return all(dlog.cols[k].data_ptr() % 32 == 0 for k in F64_COLS + I64_COLS)
 
     def _cold_device(self, cold_times: Sequence[float]) -> Tuple[torch.Tensor, int]:
         key = tuple(sorted(float(c) for c in cold_times))
@@ -355,7 +369,9 @@ class LogAnalyzer:
         hspec = self.hist_spec(num_bins) if fused_hists else None
         log_c = dlog.c_struct()
         st = _stream_ptr(dev)
-        self._launch_scan(dlog, cold_times)
+        fused = self._fused_ok(dlog, fused_hists)
+        if not fused:
+            self._launch_scan(dlog, cold_times)
         extras = N.LogExtrasC()
         if series_window_s is not None and dlog.n > 0:
             extras.series_window_ms = float(series_window_s) * 1000.0
@@ -365,14 +381,29 @@ class LogAnalyzer:
         extras.digit_records = self._digits.data_ptr()
         ws, fl = self._sel_ws.data_ptr(), self._flags.data_ptr()
         rounds = self._refine_rounds(dlog.n)
-        with tm.stage("select_plan"):
-            N.check(lib.kvm_select_plan_refine(self._stats_ptr + N.LogStatsC.sets.offset, queries, nq,
-                                               C.byref(hspec) if hspec is not None else None, ws,
-                                               self._sel_ws.numel(), arena, rounds, int(self.refine_min_keys), st),
-                    "kvm_select_plan")
-        with tm.stage("select_hist"):
-            N.check(lib.kvm_log_select_hist(C.byref(log_c), fl, self._stats_ptr, C.byref(extras), ws, st),
-                    "kvm_log_select_hist")
+        self.last_path = "fused" if fused else "two-pass"
+        if fused:
+            cold_d, nc = self._cold_device(cold_times)
+            with tm.stage("log_fused"):
+                N.check(lib.kvm_log_fused_pass(C.byref(log_c), cold_d.data_ptr(), nc, 30.0, fl, self._stats_ptr,
+                                               C.byref(extras), self._scan_ws.data_ptr(), self._scan_ws.numel(),
+                                               ws, self._sel_ws.numel(), arena, st), "kvm_log_fused_pass")
+            self.launches += 1 + (1 if nc else 0)
+            with tm.stage("select_plan"):
+                N.check(lib.kvm_select_plan_preset(self._stats_ptr + N.LogStatsC.sets.offset, queries, nq,
+                                                   C.byref(hspec) if hspec is not None else None, ws,
+                                                   self._sel_ws.numel(), arena, rounds, int(self.refine_min_keys), st),
+                        "kvm_select_plan_preset")
+            self.launches -= 1   # (no separate histogram pass; the common count below assumes one)
+        else:
+            with tm.stage("select_plan"):
+                N.check(lib.kvm_select_plan_refine(self._stats_ptr + N.LogStatsC.sets.offset, queries, nq,
+                                                   C.byref(hspec) if hspec is not None else None, ws,
+                                                   self._sel_ws.numel(), arena, rounds, int(self.refine_min_keys), st),
+                        "kvm_select_plan")
+            with tm.stage("select_hist"):
+                N.check(lib.kvm_log_select_hist(C.byref(log_c), fl, self._stats_ptr, C.byref(extras), ws, st),
+                        "kvm_log_select_hist")
         with tm.stage("select_resolve"):
             N.check(lib.kvm_select_resolve(ws, st), "kvm_select_resolve")
         for _ in range(rounds):   # large logs: narrow every candidate bucket 2048x before compacting
@@ -417,7 +448,8 @@ class LogAnalyzer:
                          tuple(sorted(float(c) for c in cold_times)), num_bins, series_window_s,
                          id(quantiles), arena, self._sel_ws.data_ptr(), self._flags.data_ptr(),
                          self._series_d.data_ptr() if want_series else 0,
-                         self._refine_rounds(dlog.n), self.refine_min_keys)
+                         self._refine_rounds(dlog.n), self.refine_min_keys,
+                         self._fused_ok(dlog, hist_big is None))
             entry = self._graphs.get(graph_key)
             if entry is None:
                 # eager run first (sets function attributes, fills caches), then capture
@@ -429,10 +461,11 @@ class LogAnalyzer:
                     self._enqueue(dlog, cold_times, num_bins, series_window_s, quantiles, arena, hist_big)
                 if len(self._graphs) >= 4:
                     self._graphs.pop(next(iter(self._graphs)))
-                entry = (g, self.launches)
+                entry = (g, self.launches, self.last_path)
                 self._graphs[graph_key] = entry
             entry[0].replay()
             self.launches = entry[1]
+            self.last_path = entry[2]
         else:
             self._enqueue(dlog, cold_times, num_bins, series_window_s, quantiles, arena, hist_big)
         self._done.record(torch.cuda.current_stream(dev))
@@ -482,6 +515,21 @@ class LogAnalyzer:
                 if rc != N.KVM_OK:
                     raise N.NativeError(f"select failed with status {rc}")
                 series = None
+                if (want_series and self.last_path == "fused" and not math.isnan(stats.min_start_ms)
+                        and np.frombuffer(out, dtype=np.float64, count=1, offset=self._OFF_DROPPED + 16)[0]
+                        != stats.min_start_ms):
+                    # the one-pass kernel binned the series relative to the start of its sample, which
+                    # is not the log's minimum (rows out of time order): redo with the two-pass form
+                    if not hasattr(self, "_unordered_logs"):
+                        self._unordered_logs = set()
+                    if len(self._unordered_logs) < 64:
+                        self._unordered_logs.add((dlog.cols["start_ms"].data_ptr(), dlog.n))
+                    self._fused_off = True
+                    try:
+                        submit()
+                    finally:
+                        self._fused_off = False
+                    continue
                 if want_series and not math.isnan(stats.min_start_ms):
                     t0, t1 = stats.min_start_ms / 1000.0, stats.max_end_ms / 1000.0
                     nb = max(1, int(math.ceil((t1 - t0) / series_window_s)) + 1)

@@ -523,3 +523,99 @@ def test_sampled_select_dirty_workspace_and_graph_replay():
             want, m = expect(v, s)
             got = read()
             assert [float(x) for x in got["value"]] == want and all(int(x) == m for x in got["n"]), rep
+
+
+# ---- one-pass form (csrc/kvm_fused.cu): sampled digit parameters, catch-all end bins -----------
+def _extreme_quantiles():
+    from kvmini_b200 import _native as N
+    from kvmini_b200 import engine
+    qs = []
+    for name, mask in (("lat", engine.LAT_ALL), ("ttfb", engine.TTFB_ALL), ("tllt", 1 << N.SET_TLLT),
+                       ("gen", 1 << N.SET_GEN), ("pertok", 1 << N.SET_PERTOK)):
+        for p in (0.0, 0.00001, 0.5, 0.9999, 1.0):
+            qs.append(engine.Quantile(f"{name}_{p}", mask, p))
+    return tuple(qs[:24])      # 48 queries at most
+
+
+@pytest.mark.parametrize("shape", ["outliers", "unsorted", "sample_sees_failures_only", "two_clusters", "tiny"])
+def test_fused_pass_equals_two_pass_and_oracle(shape):
+    """The one-pass kernel takes its digit parameters from a 512-row sample; whatever lies outside
+    the sampled range lands in the two end bins.  Extreme quantiles (p = 0, 1e-5, 0.9999, 1) force
+    ranks into those bins; the answers must equal the two-pass form and a numpy sort."""
+    import torch
+    from kvmini_b200 import _native as N
+    from kvmini_b200 import analyze_api, columns, engine, report
+    from oracle import np_port
+    n = 300_000 if shape != "tiny" else 37
+    cols = _random_log(n, 91, nan_rows=n // 60, zero_tok_rows=n // 50)
+    rng = np.random.default_rng(17)
+    if shape == "outliers":
+        idx = rng.integers(0, n, 40)
+        cols["latency_ms"][idx] = 30000.0 + rng.random(40)            # time-outs far above the sampled range
+        cols["tllt_ms"][idx] = 29999.0
+        cols["ttfb_ms"][rng.integers(0, n, 40)] = 1e-6                # and far below it
+    elif shape == "unsorted":
+        perm = rng.permutation(n)
+        cols = {k: v[perm].copy() for k, v in cols.items()}
+    elif shape == "sample_sees_failures_only":
+        cols["status"][:] = 500
+        ok = rng.integers(0, n, 2000)                                 # a sparse set of successes
+        cols["status"][ok] = 200
+    elif shape == "two_clusters":
+        half = cols["status"] == 200
+        cols["latency_ms"] = np.where(rng.random(n) < 0.5, 10.0, 1.0e9) + rng.random(n) * 1e-3
+    t0 = float(np.nanmin(cols["start_ms"])) / 1000.0
+    cold = [t0 + 2.0, t0 + 300.0]
+    quantiles = _extreme_quantiles()
+    dev = {k: torch.from_numpy(np.ascontiguousarray(v)).cuda() for k, v in cols.items()}
+    dlog = engine.DeviceLog.from_tensors(dev)
+    one = engine.LogAnalyzer()
+    two = engine.LogAnalyzer()
+    two.use_fused = False
+    ra = one.analyze(dlog, cold, quantiles=quantiles)
+    rb = two.analyze(dlog, cold, quantiles=quantiles)
+    assert two.last_path == "two-pass"
+    assert one.last_path == ("two-pass" if shape == "unsorted" else "fused")     # unsorted: the series needs the true minimum
+    for f in ("n_total", "n_success", "n_cold", "n_cold_success", "sum_completion_tokens", "sum_total_tokens",
+              "sum_total_tokens_cold", "n_gen_rows", "min_start_ms", "max_end_ms"):
+        assert same(getattr(ra.stats, f), getattr(rb.stats, f)), f
+    for hi, lo in (("ttfb_sum_hi", "ttfb_sum_lo"), ("lat_sum_hi", "lat_sum_lo")):     # double-double sums: same to ~1e-30
+        va = getattr(ra.stats, hi) + getattr(ra.stats, lo)
+        vb = getattr(rb.stats, hi) + getattr(rb.stats, lo)
+        assert va == vb or abs(va - vb) <= 1e-15 * abs(vb), hi
+    assert list(ra.stats.sets.count) == list(rb.stats.sets.count)
+    assert list(ra.stats.sets.kmin)[:5] == list(rb.stats.sets.kmin)[:5] and list(ra.stats.sets.kmax)[:5] == list(rb.stats.sets.kmax)[:5]
+    for q in quantiles:
+        a, b = ra.order[q.name], rb.order[q.name]
+        assert (a.n, a.status) == (b.n, b.status), q.name
+        assert same(a.v_lo, b.v_lo) and same(a.v_hi, b.v_hi), (q.name, a, b)
+    assert np.array_equal(ra.hist_counts, rb.hist_counts)
+    assert np.array_equal(ra.flags.cpu().numpy(), rb.flags.cpu().numpy())
+    assert same(report.trim_series(ra), report.trim_series(rb))
+    # and against numpy for the latency column
+    lat_ok = np.sort(cols["latency_ms"][(cols["status"] == 200) & ~np.isnan(cols["latency_ms"])])
+    for p in (0.0, 0.00001, 0.5, 0.9999, 1.0):
+        st = ra.order[f"lat_{p}"]
+        if len(lat_ok):
+            pos = p * (len(lat_ok) - 1)
+            assert st.v_lo == lat_ok[int(math.floor(pos))] and st.v_hi == lat_ok[int(math.ceil(pos))], p
+    # the default analysis through the public API: every results.json key against the oracle
+    log = columns.columns_from_arrays(**cols)
+    got, _ = analyze_api.analyze_log(log, cold, one)
+    exp = np_port.analyze(cols, cold)
+    assert diff_keys(got, {k: exp[k] for k in got}, rel=MEAN_TOL) == []
+
+
+def test_fused_pass_graph_replay_and_repeat():
+    import torch
+    from kvmini_b200 import engine, report
+    cols = _random_log(500_003, 5)
+    dev = {k: torch.from_numpy(v).cuda() for k, v in cols.items()}
+    dlog = engine.DeviceLog.from_tensors(dev)
+    t0 = float(cols["start_ms"].min()) / 1000.0
+    an = engine.LogAnalyzer()
+    first = report.core_results(an.analyze(dlog, [t0 + 5.0]), 1)
+    assert an.last_path == "fused"
+    for _ in range(4):
+        again = report.core_results(an.analyze(dlog, [t0 + 5.0], use_graph=True), 1)
+        assert an.last_path == "fused" and diff_keys(again, first) == []
