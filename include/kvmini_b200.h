@@ -226,7 +226,7 @@ int kvm_log_select(const kvm_request_log* log_host, const uint8_t* flags,
  * sample drawn identically by every CTA; the two end bins catch what lies outside the sampled
  * range and are resolved exactly by the select (plan_preset marks them, resolve spans their
  * buckets with the true range), so the results are exact for any input.  Needs every column
- * 32-byte aligned (256-bit loads), flags 4-byte and extras->digit_records (required) 32-byte
+ * 16-byte aligned (128-bit loads), flags 2-byte and extras->digit_records (required) 16-byte
  * aligned, n >= 1: otherwise KVM_ERR_UNSUPPORTED and the caller uses kvm_log_scan + kvm_log_select.
  * The window series is binned relative to the minimum start_ms of the sample + first + last row;
  * that reference is stored (as double bits) in extras->series_dropped[2] (the buffer needs three

@@ -24,7 +24,7 @@
 
 namespace {
 
-constexpr int FU_THREADS = 256;
+constexpr int FU_THREADS = 384;   // x 2 CTAs per SM at <= 85 registers: 24 warps per SM hide the row arithmetic's latencies
 constexpr int FU_WARPS = FU_THREADS / 32;
 constexpr int FU_COLD_SMEM = 512;
 constexpr int FU_MAX_GRID = 148 * 8;
@@ -52,6 +52,7 @@ struct FusedSmem {
   double s_start[FU_WARPS];
   uint64_t kbase[NC];
   int32_t shift[NC];
+  uint4 par[NC];   // fast-path parameters per column: kbase lo / hi word, hull span high word, shift - 32
   double series_ref;
   double cold_lo[FU_COLD_SMEM], cold_hi[FU_COLD_SMEM];
   int is_last;
@@ -61,6 +62,30 @@ struct FusedSmem {
 __device__ __forceinline__ void range_update(unsigned long long* lo, unsigned long long* hi, uint64_t key) {
   if (key < *reinterpret_cast<volatile unsigned long long*>(lo)) atomicMin(lo, (unsigned long long)key);
   if (key > *reinterpret_cast<volatile unsigned long long*>(hi)) atomicMax(hi, (unsigned long long)key);
+}
+
+// Sites of one row whose key lies outside the sampled hull (bit c of `rare` = value column c),
+// redone exactly: digit with both clamps, exact range, histogram count, record field.
+__device__ __noinline__ uint64_t fused_fix_sites(FusedSmem& S, uint32_t* sh, uint32_t rare, uint32_t f, double la,
+                                                 double tf, double tl, long long ct, uint64_t r) {
+  const bool cold_row = f & KVM_F_COLD;
+  const double g = tl - tf;
+  for (int c = 0; c < NC; ++c) {
+    if (!((rare >> c) & 1u)) continue;
+    double v;
+    int set;
+    if (c == KVM_COL_LAT) { v = la; set = cold_row ? KVM_SET_LAT_COLD : KVM_SET_LAT_WARM; }
+    else if (c == KVM_COL_TTFB) { v = tf; set = cold_row ? KVM_SET_TTFB_COLD : KVM_SET_TTFB_WARM; }
+    else if (c == KVM_COL_TLLT) { v = tl; set = KVM_SET_TLLT; }
+    else if (c == KVM_COL_GEN) { v = g; set = KVM_SET_GEN; }
+    else { v = g / (double)ct; set = KVM_SET_PERTOK; }
+    const uint64_t key = kvm_key(v);
+    const uint32_t d = digit_of(key, S.kbase[c], S.shift[c]);
+    range_update(&S.kmin[c], &S.kmax[c], key);
+    atomicAdd(&sh[set * BINS + d], 1u);
+    r = (r & ~(0xFFFull << (12 * c))) | ((uint64_t)d << (12 * c));
+  }
+  return r;
 }
 
 struct FAcc {
@@ -88,7 +113,7 @@ log_fused_kernel(kvm_request_log log, const double* __restrict__ cold_lo_g, cons
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const int64_t n = log.n;
 
-  // ---- sample: thread t takes rows 2t and 2t+1 of the 512-row sample (same rows in every CTA)
+  // ---- sample: 512 rows, the same in every CTA
   uint64_t s_inv[NC], s_mx[NC];
   double s_st = __longlong_as_double(0x7ff0000000000000ll);
 #pragma unroll
@@ -98,8 +123,7 @@ log_fused_kernel(kvm_request_log log, const double* __restrict__ cold_lo_g, cons
   }
   {
     const int64_t win = n < 4096 ? n : 4096;
-    for (int k = 0; k < 2; ++k) {
-      const int sidx = 2 * t + k;
+    for (int sidx = t; sidx < 512; sidx += FU_THREADS) {
       const int64_t region = sidx >> 5;
       const int64_t off = n > win ? region * ((n - win) / 15) : 0;
       int64_t i = off + (int64_t)(((uint32_t)sidx * 2654435761u >> 7) % (uint32_t)win);
@@ -182,13 +206,27 @@ log_fused_kernel(kvm_request_log log, const double* __restrict__ cold_lo_g, cons
     if (SERIES && blockIdx.x == 0) sa.dropped[2] = (unsigned long long)__double_as_longlong(s0);
   }
   __syncthreads();
-  uint64_t kb[NC];
-  int shf[NC];
-#pragma unroll
-  for (int c = 0; c < NC; ++c) {
-    kb[c] = S.kbase[c];
-    shf[c] = S.shift[c];
+  // fast-path parameters (shared memory: one 16-byte load per site): with every shift >= 32 a digit
+  // is a 32-bit shift of the HIGH word of (key - kbase), and "outside the sampled hull" is one
+  // unsigned comparison of that word (a key below kbase wraps to >= 2^31; hulls wider than 2^63
+  // keys disable the trick: span word 0).  A column narrower than 2^43 keys (shift < 32) sends
+  // every site through the exact (slow) route.
+  if (t == 0) {
+    bool fast_ok = true;
+    for (int c = 0; c < NC; ++c) fast_ok = fast_ok && S.shift[c] >= 32;
+    for (int c = 0; c < NC; ++c) {
+      const uint64_t kbc = S.kbase[c];
+      const uint64_t hm = S.hull_max[c];
+      const uint64_t span = hm >= kbc ? hm - kbc : 0ull;
+      uint4 P;
+      P.x = (uint32_t)kbc;
+      P.y = (uint32_t)(kbc >> 32);
+      P.z = (!fast_ok || (span >> 63)) ? 0u : (uint32_t)(span >> 32);
+      P.w = fast_ok ? (uint32_t)(S.shift[c] - 32) : 0u;
+      S.par[c] = P;
+    }
   }
+  __syncthreads();
   const double s0 = S.series_ref;
   const double cold_first = nc > 0 ? cold.lo[0] : 0.0, cold_last = nc > 0 ? cold.hi[nc - 1] : -1.0;
 
@@ -199,60 +237,58 @@ log_fused_kernel(kvm_request_log log, const double* __restrict__ cold_lo_g, cons
   a.end_max = -a.st_min;
   a.ttfb_s = a.ttfb_e = a.lat_s = a.lat_e = 0.0;
 
-  // one (set, column, value) site: digit -> shared histogram + record; exact range on the rare path
-  uint64_t rec;
-  auto site = [&](int set, int col, double v) {
-    const uint64_t key = kvm_key(v);
-    uint32_t d = 0;
-    if (key < kb[col]) {
-      range_update(&S.kmin[col], &S.kmax[col], key);
-    } else {
-      const uint64_t x = (key - kb[col]) >> shf[col];
-      d = x < (uint64_t)BINS ? (uint32_t)x : (uint32_t)(BINS - 1);
-      if (key > S.hull_max[col]) range_update(&S.kmin[col], &S.kmax[col], key);
-    }
-    atomicAdd(&sh[set * BINS + d], 1u);
-    rec ^= (uint64_t)(0xFFFu ^ d) << (12 * col);
-  };
-  auto row = [&](double st, double la, double tf, double tl, long long status, long long ct, long long tt,
-                 uint32_t& flag_out) -> uint64_t {
+  // ---- fast row: branch-free; sites whose key lies outside the sampled hull are only noted in
+  // `rare` and redone exactly by fix_sites (a fraction of a percent of the rows)
+  auto row_fast = [&](double st, double la, double tf, double tl, long long status, long long ct, long long tt,
+                      uint32_t& flag_out) -> uint64_t {
     const bool ok = status == 200;
     bool cold_row = false;
-    if (st >= cold_first && st <= cold_last) cold_row = is_cold(st, cold);   // (nc == 0: empty hull)
-    a.st_min = fmin(a.st_min, st);         // NaN skipped by fmin / fmax
-    a.end_max = fmax(a.end_max, st + la);  // analyze.py:187
+    if (st >= cold_first && st <= cold_last) cold_row = is_cold(st, cold);
+    a.st_min = fmin(a.st_min, st);
+    a.end_max = fmax(a.end_max, st + la);
+    const bool okc = ok && cold_row;
     a.n_cold += cold_row;
-    uint32_t f = (ok ? KVM_F_SUCCESS : 0) | (cold_row ? KVM_F_COLD : 0) | (ct > 0 ? KVM_F_TOKENS : 0);
-    rec = DIGITS_NONE;
-    if (ok) {
-      a.n_success += 1;
-      a.n_cold_success += cold_row;
-      a.ctok += ct;
-      a.ttok += tt;
-      a.ttok_cold += cold_row ? tt : 0;
-      if (la == la) {
-        site(cold_row ? KVM_SET_LAT_COLD : KVM_SET_LAT_WARM, KVM_COL_LAT, la);
-        dd_acc(a.lat_s, a.lat_e, la);
-      }
-      const bool has_tf = tf == tf, has_tl = tl == tl;
-      if (has_tf) {
-        site(cold_row ? KVM_SET_TTFB_COLD : KVM_SET_TTFB_WARM, KVM_COL_TTFB, tf);
-        dd_acc(a.ttfb_s, a.ttfb_e, tf);
-      }
-      if (has_tl) site(KVM_SET_TLLT, KVM_COL_TLLT, tl);
-      if (has_tf && has_tl && ct > 0) {
-        f |= KVM_F_GEN;
-        a.n_gen += 1;
-        const double g = tl - tf;  // analyze.py:144
-        if (g == g) {
-          site(KVM_SET_GEN, KVM_COL_GEN, g);
-          const double pt = g / (double)ct;  // analyze.py:146
-          if (pt == pt) site(KVM_SET_PERTOK, KVM_COL_PERTOK, pt);
-        }
-      }
-    }
+    a.n_success += ok;
+    a.n_cold_success += okc;
+    a.ctok += ok ? ct : 0;
+    a.ttok += ok ? tt : 0;
+    a.ttok_cold += okc ? tt : 0;
+    const bool has_tf = tf == tf, has_tl = tl == tl;
+    const bool m_la = ok && la == la, m_tf = ok && has_tf, m_tl = ok && has_tl;
+    const bool gen = m_tf && has_tl && ct > 0;
+    const double g = tl - tf;                 // analyze.py:144
+    const bool m_g = gen && g == g;
+    const double pt = g / (double)ct;         // analyze.py:146 (garbage where !gen: never used)
+    const bool m_pt = m_g && pt == pt;
+    a.n_gen += gen;
+    dd_acc(a.lat_s, a.lat_e, m_la ? la : 0.0);
+    dd_acc(a.ttfb_s, a.ttfb_e, m_tf ? tf : 0.0);
+    uint32_t rare = 0;
+    auto site = [&](bool m, int setoff, int col, double v) -> uint32_t {
+      const uint32_t hi = (uint32_t)__double2hiint(v), lo = (uint32_t)__double2loint(v);
+      const uint32_t sgn = (uint32_t)((int32_t)hi >> 31);
+      const uint32_t klo = lo ^ sgn, khi = hi ^ (sgn | 0x80000000u);
+      const uint4 P = S.par[col];
+      const uint32_t dhi = khi - P.y - (klo < P.x ? 1u : 0u);
+      const bool out = dhi >= P.z;
+      const uint32_t d = dhi >> P.w;
+      if (m && !out) atomicAdd(&sh[setoff + d], 1u);
+      rare |= (m && out) ? (1u << col) : 0u;
+      return m ? (out ? 0u : d) : 0xFFFu;
+    };
+    const int coff = cold_row ? 0 : BINS;
+    const uint32_t d0 = site(m_la, KVM_SET_LAT_COLD * BINS + coff, KVM_COL_LAT, la);
+    const uint32_t d1 = site(m_tf, KVM_SET_TTFB_COLD * BINS + coff, KVM_COL_TTFB, tf);
+    const uint32_t d2 = site(m_tl, KVM_SET_TLLT * BINS, KVM_COL_TLLT, tl);
+    const uint32_t d3 = site(m_g, KVM_SET_GEN * BINS, KVM_COL_GEN, g);
+    const uint32_t d4 = site(m_pt, KVM_SET_PERTOK * BINS, KVM_COL_PERTOK, pt);
+    const uint32_t f = (ok ? KVM_F_SUCCESS : 0) | (cold_row ? KVM_F_COLD : 0) | (ct > 0 ? KVM_F_TOKENS : 0) |
+                       (gen ? KVM_F_GEN : 0);
     flag_out = f;
-    return rec;
+    const uint32_t rlo = d0 | (d1 << 12) | (d2 << 24), rhi = (d2 >> 8) | (d3 << 4) | (d4 << 16);
+    uint64_t r = ((uint64_t)rhi << 32) | rlo;
+    if (rare) r = fused_fix_sites(S, sh, rare, f, la, tf, tl, ct, r);
+    return r;
   };
   auto series_row = [&](long long bin, bool ok, long long tok) {
     if (bin >= 0) {
@@ -271,69 +307,63 @@ log_fused_kernel(kvm_request_log log, const double* __restrict__ cold_lo_g, cons
     return b == b ? -2 : -1;
   };
 
-  // ---- the stream: four consecutive rows per thread and iteration, one 256-bit load per column
-  const int64_t nquads = n >> 2;
-  for (int64_t base = (int64_t)blockIdx.x * FU_THREADS + (t & ~31); base < nquads;
+  // ---- the stream: two consecutive rows per thread and iteration, one 128-bit load per column
+  const int64_t npairs = n >> 1;
+  for (int64_t base = (int64_t)blockIdx.x * FU_THREADS + (t & ~31); base < npairs;
        base += (int64_t)gridDim.x * FU_THREADS) {
     const int64_t u = base + lane;
-    const bool live = u < nquads;
-    const int64_t i = u << 2;
-    uint32_t f0 = 0, f1 = 0, f2 = 0, f3 = 0;
-    long long b0 = -1, b1 = -1, b2 = -1, b3 = -1;
-    long long t0 = 0, t1 = 0, t2 = 0, t3 = 0;
+    const bool live = u < npairs;
+    const int64_t i = u << 1;
+    uint32_t f0 = 0, f1 = 0;
+    double sx = 0.0, sy = 0.0;
+    long long t0 = 0, t1 = 0;
     if (live) {
-      const kvm_u64x4 qs = kvm_ld4_nc(log.start_ms + i), ql = kvm_ld4_nc(log.latency_ms + i);
-      const kvm_u64x4 qf = kvm_ld4_nc(log.ttfb_ms + i), qt = kvm_ld4_nc(log.tllt_ms + i);
-      const kvm_u64x4 qx = kvm_ld4_nc(log.status + i), qc = kvm_ld4_nc(log.completion_tokens + i);
-      const kvm_u64x4 qo = kvm_ld4_nc(log.total_tokens + i);
-#define KVM_D(x) __longlong_as_double((long long)(x))
-      const uint64_t r0 = row(KVM_D(qs.x), KVM_D(ql.x), KVM_D(qf.x), KVM_D(qt.x), (long long)qx.x, (long long)qc.x, (long long)qo.x, f0);
-      const uint64_t r1 = row(KVM_D(qs.y), KVM_D(ql.y), KVM_D(qf.y), KVM_D(qt.y), (long long)qx.y, (long long)qc.y, (long long)qo.y, f1);
-      const uint64_t r2 = row(KVM_D(qs.z), KVM_D(ql.z), KVM_D(qf.z), KVM_D(qt.z), (long long)qx.z, (long long)qc.z, (long long)qo.z, f2);
-      const uint64_t r3 = row(KVM_D(qs.w), KVM_D(ql.w), KVM_D(qf.w), KVM_D(qt.w), (long long)qx.w, (long long)qc.w, (long long)qo.w, f3);
-      asm volatile("st.global.v4.b64 [%0], {%1,%2,%3,%4};" ::"l"(recs + i), "l"(r0), "l"(r1), "l"(r2), "l"(r3) : "memory");
-      *reinterpret_cast<uint32_t*>(flags + i) = f0 | (f1 << 8) | (f2 << 16) | (f3 << 24);
+      const double2 qs = kvm_ld2(log.start_ms + i), ql = kvm_ld2(log.latency_ms + i);
+      const double2 qf = kvm_ld2(log.ttfb_ms + i), qt = kvm_ld2(log.tllt_ms + i);
+      const longlong2 qx = kvm_ld2(log.status + i), qc = kvm_ld2(log.completion_tokens + i);
+      const longlong2 qo = kvm_ld2(log.total_tokens + i);
+      const uint64_t r0 = row_fast(qs.x, ql.x, qf.x, qt.x, qx.x, qc.x, qo.x, f0);
+      const uint64_t r1 = row_fast(qs.y, ql.y, qf.y, qt.y, qx.y, qc.y, qo.y, f1);
+      *reinterpret_cast<ulonglong2*>(recs + i) = make_ulonglong2(r0, r1);
+      *reinterpret_cast<uint16_t*>(flags + i) = (uint16_t)(f0 | (f1 << 8));
       if (SERIES) {
-        const double sx = KVM_D(qs.x), sy = KVM_D(qs.y), sz = KVM_D(qs.z), sw = KVM_D(qs.w);
-        b0 = sbin(sx);
-        b3 = sbin(sw);
-        // rows in time order inside the quad and the same window at both ends: the middle rows
-        // are in it too (x -> floor((x - s0) / w) is monotone) - two divisions instead of four
-        if (b0 == b3 && sx <= sy && sy <= sz && sz <= sw) {
-          b1 = b2 = b0;
-        } else {
-          b1 = sbin(sy);
-          b2 = sbin(sz);
-        }
-        t0 = (long long)qc.x; t1 = (long long)qc.y; t2 = (long long)qc.z; t3 = (long long)qc.w;
+        sx = qs.x;
+        sy = qs.y;
+        t0 = qc.x;
+        t1 = qc.y;
       }
-#undef KVM_D
     }
     if (SERIES) {
-      const bool k0 = f0 & KVM_F_SUCCESS, k1 = f1 & KVM_F_SUCCESS, k2 = f2 & KVM_F_SUCCESS, k3 = f3 & KVM_F_SUCCESS;
-      const long long lead = __shfl_sync(KVM_FULL, b0, 0);
-      if (__all_sync(KVM_FULL, live && b0 == lead && b1 == lead && b2 == lead && b3 == lead && lead >= 0)) {
-        const int nok = __reduce_add_sync(KVM_FULL, (int)k0 + (int)k1 + (int)k2 + (int)k3);
-        const int64_t tsum = kvm_warp_sum((int64_t)((k0 ? t0 : 0) + (k1 ? t1 : 0) + (k2 ? t2 : 0) + (k3 ? t3 : 0)));
+      const bool k0 = f0 & KVM_F_SUCCESS, k1 = f1 & KVM_F_SUCCESS;
+      // One division per warp iteration instead of two per lane: lane 0 bins the first row of
+      // the warp's 64, lane 31 the last one (every other lane its first row).  x -> floor((x - s0) / w)
+      // is monotone, so when both ends share a window and every start of the warp lies between
+      // them, all 64 rows are in that window (the usual case: logs are time-ordered and a window
+      // holds thousands of rows).
+      const double first = __shfl_sync(KVM_FULL, sx, 0), last = __shfl_sync(KVM_FULL, sy, 31);
+      const long long bx = sbin(lane == 31 ? sy : sx);
+      const long long lead = __shfl_sync(KVM_FULL, bx, 0), tail = __shfl_sync(KVM_FULL, bx, 31);
+      const bool inside = sx >= first && sx <= last && sy >= first && sy <= last;
+      if (__all_sync(KVM_FULL, live && inside) && lead == tail && lead >= 0) {
+        const int nok = __reduce_add_sync(KVM_FULL, (int)k0 + (int)k1);
+        const int64_t tsum = kvm_warp_sum((int64_t)((k0 ? t0 : 0) + (k1 ? t1 : 0)));
         if (lane == 0) {
-          atomicAdd(&sa.series[lead], 128ull);
+          atomicAdd(&sa.series[lead], 64ull);
           if (nok) {
             atomicAdd(&sa.series[sa.max_bins + lead], (unsigned long long)nok);
             atomicAdd(&sa.series[2 * sa.max_bins + lead], (unsigned long long)tsum);
           }
         }
-      } else if (live) {
-        series_row(b0, k0, t0);
-        series_row(b1, k1, t1);
-        series_row(b2, k2, t2);
-        series_row(b3, k3, t3);
+      } else if (live) {   // a window boundary inside the warp's rows, or rows out of order
+        series_row(lane == 31 ? sbin(sx) : bx, k0, t0);
+        series_row(lane == 31 ? bx : sbin(sy), k1, t1);
       }
     }
   }
-  if (blockIdx.x == 0 && t < (int)(n & 3)) {   // tail rows
-    const int64_t i = (n & ~3ll) + t;
+  if (blockIdx.x == 0 && t < (int)(n & 1)) {   // tail row
+    const int64_t i = (n & ~1ll) + t;
     uint32_t f;
-    const uint64_t r = row(log.start_ms[i], log.latency_ms[i], log.ttfb_ms[i], log.tllt_ms[i], log.status[i],
+    const uint64_t r = row_fast(log.start_ms[i], log.latency_ms[i], log.ttfb_ms[i], log.tllt_ms[i], log.status[i],
                            log.completion_tokens[i], log.total_tokens[i], f);
     recs[i] = r;
     flags[i] = (uint8_t)f;
@@ -478,13 +508,13 @@ extern "C" int kvm_log_fused_pass(const kvm_request_log* log, const double* cold
   if (series)
     KVM_REQUIRE(extras->series && extras->series_dropped && extras->series_max_bins >= 1,
                 "kvm_log_analyze_fused: series requested without buffers");
-  // the one-pass kernel streams with 256-bit loads: every column 32-byte aligned (whole logs are;
+  // the one-pass kernel streams with 128-bit loads: every column 16-byte aligned (whole logs are;
   // a shard cut at an odd row is not - the caller then uses the two-pass entry points)
-  if (!(aligned_to(log->start_ms, 32) && aligned_to(log->latency_ms, 32) && aligned_to(log->ttfb_ms, 32) &&
-        aligned_to(log->tllt_ms, 32) && aligned_to(log->status, 32) && aligned_to(log->completion_tokens, 32) &&
-        aligned_to(log->total_tokens, 32) && aligned_to(flags, 4) && aligned_to(extras->digit_records, 32)) ||
+  if (!(aligned_to(log->start_ms, 16) && aligned_to(log->latency_ms, 16) && aligned_to(log->ttfb_ms, 16) &&
+        aligned_to(log->tllt_ms, 16) && aligned_to(log->status, 16) && aligned_to(log->completion_tokens, 16) &&
+        aligned_to(log->total_tokens, 16) && aligned_to(flags, 2) && aligned_to(extras->digit_records, 16)) ||
       log->n < 1) {
-    kvm_set_error("kvm_log_analyze_fused: needs a non-empty log with 32-byte aligned columns; use kvm_log_scan + kvm_log_select");
+    kvm_set_error("kvm_log_analyze_fused: needs a non-empty log with 16-byte aligned columns; use kvm_log_scan + kvm_log_select");
     return KVM_ERR_UNSUPPORTED;
   }
   if (scan_workspace_bytes < kvm_log_analyze_fused_scan_workspace_bytes()) {
@@ -516,7 +546,7 @@ extern "C" int kvm_log_fused_pass(const kvm_request_log* log, const double* cold
   if (n_cold > 0)
     fused_cold_table_kernel<<<(n_cold + 127) / 128, 128, 0, st>>>(cold_times, n_cold, cold_window_s, cold_lo, cold_hi);
   const size_t smem = sizeof(uint32_t) * KVM_LOG_NSETS * BINS + sizeof(FusedSmem);
-  int grid = kvm_grid_for(log->n, FU_THREADS * 4 * 2, 2);
+  int grid = kvm_grid_for(log->n, FU_THREADS * 2 * 4, 2);
   if (grid > FU_MAX_GRID) grid = FU_MAX_GRID;
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3((unsigned)grid);

@@ -299,12 +299,12 @@ class LogAnalyzer:
         return 1 if n_rows >= self.REFINE_MIN_ROWS else 0
 
     def _fused_ok(self, dlog: "DeviceLog", fused_hists: bool) -> bool:
-        """The one-pass form needs 32-byte aligned columns and the histograms folded into the select."""
+        """The one-pass form needs 16-byte aligned columns and the histograms folded into the select."""
         if not (self.use_fused and fused_hists and dlog.n >= 1 and not getattr(self, "_fused_off", False)):
             return False
         if (dlog.cols["start_ms"].data_ptr(), dlog.n) in getattr(self, "_unordered_logs", ()):
             return False   # seen before: rows out of time order, the series needs the exact minimum first
-        return all(dlog.cols[k].data_ptr() % 32 == 0 for k in F64_COLS + I64_COLS)
+        return all(dlog.cols[k].data_ptr() % 16 == 0 for k in F64_COLS + I64_COLS)
 
     def _cold_device(self, cold_times: Sequence[float]) -> Tuple[torch.Tensor, int]:
         key = tuple(sorted(float(c) for c in cold_times))
