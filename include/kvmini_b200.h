@@ -566,6 +566,26 @@ int kvm_interval_energy(const double* ts, const double* watts, const double* p_h
                         const double* p_lo, int64_t m, const double* start_ms,
                         const double* latency_ms, int64_t n, double* energy_wh, int32_t accumulate,
                         void* stream);
+/* All traces (one per GPU of the served model; PromQL `sum(...)`, collector.py:45) in one pass over
+ * the intervals: per-trace energies are added in trace order in a register, the interval columns
+ * are read once and energy_wh[] written once.  The two boundary searches per interval and trace
+ * start from an interpolated guess (traces are sampled regularly) and gallop: time-ordered
+ * intervals stream through ts / prefix instead of bisecting 27 levels each. */
+/* Diagnostic: out[i] = the library's division-free evaluation of x[i] / 3600.0 (the trapezoid and
+ * prefix kernels use it for collector.py:146); must equal the IEEE quotient bit for bit. */
+int kvm_selfcheck_div3600(const double* x, double* out, int64_t n, void* stream);
+
+#define KVM_MAX_TRACES 8
+typedef struct kvm_power_trace {
+  const double* ts;
+  const double* watts;
+  const double* p_hi; /* kvm_energy_prefix */
+  const double* p_lo;
+  int64_t m;
+} kvm_power_trace;
+int kvm_interval_energy_multi(const kvm_power_trace* traces_host, int32_t ntraces, const double* start_ms,
+                              const double* latency_ms, int64_t n, double* energy_wh, int32_t accumulate,
+                              void* stream);
 
 #ifdef __cplusplus
 }

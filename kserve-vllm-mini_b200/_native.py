@@ -69,6 +69,14 @@ class PowerStatsC(C.Structure):
                 ("ts_max", C.c_double), ("step_sum_hi", C.c_double), ("step_sum_lo", C.c_double)]
 
 
+class PowerTraceC(C.Structure):
+    _fields_ = [("ts", C.c_void_p), ("watts", C.c_void_p), ("p_hi", C.c_void_p), ("p_lo", C.c_void_p),
+                ("m", C.c_int64)]
+
+
+KVM_MAX_TRACES = 8
+
+
 class HistSpecC(C.Structure):
     _fields_ = [("nhist", C.c_int32), ("num_bins", C.c_int32), ("col", C.c_int32 * 4),
                 ("set_mask", C.c_uint32 * 4)]
@@ -181,6 +189,8 @@ def _declare(lib: C.CDLL) -> None:
         "kvm_trapezoid_wh": (C.c_int, [vp, vp, i64, P(f64), i32, vp, vp, sz, vp]),
         "kvm_energy_prefix": (C.c_int, [vp, vp, i64, vp, vp, vp, sz, vp]),
         "kvm_interval_energy": (C.c_int, [vp, vp, vp, vp, i64, vp, vp, i64, vp, i32, vp]),
+        "kvm_selfcheck_div3600": (C.c_int, [vp, vp, i64, vp]),
+        "kvm_interval_energy_multi": (C.c_int, [P(PowerTraceC), i32, vp, vp, i64, vp, i32, vp]),
     }
     for name, (res, args) in sigs.items():
         fn = getattr(lib, name)

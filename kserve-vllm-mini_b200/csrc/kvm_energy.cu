@@ -32,6 +32,27 @@ struct Windows {
   int k;
 };
 
+// x / 3600.0 without the 30-instruction fp64 division: q = RN(x * RN(1/3600)) corrected by the
+// exactly computed residual (fma), then PROVEN: with r2 = x - 3600*q2 (exact, fma) the candidate
+// q2 is the correctly rounded quotient iff |r2| / 3600 < ulp(q2) / 2 (a quotient is never a
+// rounding tie); the check uses a slightly smaller bound and anything it does not accept -
+// including non-finite, tiny and huge operands - takes the hardware division.  Bit-identical to
+// `x / 3600.0` (collector.py:146) by construction.
+__device__ __forceinline__ double div3600(double x) {
+  const double d = 3600.0, rcp = 1.0 / 3600.0;   // RN(1/3600), folded at compile time
+  const double q = x * rcp;
+  const double q2 = __fma_rn(__fma_rn(-d, q, x), rcp, q);
+  const double r2 = __fma_rn(-d, q2, x);
+  const int hi = __double2hiint(q2) & 0x7ff00000;
+  // half an ulp of q2 times 3600 = 2^(e-53) * 3600 with e the unbiased exponent of q2
+  const double bound = __hiloint2double(hi - (53 << 20), 0) * (d * 0.999);
+  const double ax = fabs(x);
+  // (a power of two has a finer grid below it: left to the hardware division)
+  const bool pow2 = ((__double2hiint(q2) & 0x000fffff) | __double2loint(q2)) == 0;
+  if (ax > 1e-250 && ax < 1e250 && fabs(r2) < bound && !pow2) return q2;
+  return x / d;
+}
+
 // energy of the segment ending at sample i (0 if i is null, has no non-null predecessor, or dt<=0)
 __device__ __forceinline__ double segment_wh(const double* __restrict__ ts, const double* __restrict__ watts,
                                              int64_t i, double ti, double wi, double* t_prev) {
@@ -49,9 +70,65 @@ __device__ __forceinline__ double segment_wh(const double* __restrict__ ts, cons
   }
   const double tj = ts[j];
   *t_prev = tj;
-  const double dt_h = (ti - tj) / 3600.0;        // collector.py:146
+  const double dt_h = div3600(ti - tj);          // collector.py:146: (ts1 - ts0) / 3600.0, exactly
   if (!(dt_h > 0)) return 0.0;                   // collector.py:147
   return ((wj + wi) / 2.0) * dt_h;               // collector.py:148
+}
+
+// Eight consecutive samples of one thread (two 256-bit loads per column when the tile is full and
+// the columns are 32-byte aligned).  The segment ending at sample i starts at the previous
+// non-null sample; inside the thread that sample is carried in registers, only the first of the
+// eight looks back into memory.  f(r, i, ti, tj, area) is called for every sample (area = 0 for a
+// null sample, a sample without a non-null predecessor, or dt <= 0; tj = NaN without predecessor).
+constexpr int SEG_ITEMS = 8;
+template <class F>
+__device__ __forceinline__ void for_eight_samples(const double* __restrict__ ts, const double* __restrict__ watts,
+                                                  int64_t m, int64_t base, bool vec, F&& f) {
+  if (base >= m) return;
+  double t[SEG_ITEMS], w[SEG_ITEMS];
+  if (vec && base + SEG_ITEMS <= m) {
+    const kvm_u64x4 a0 = kvm_ld4_nc(ts + base), a1 = kvm_ld4_nc(ts + base + 4);
+    const kvm_u64x4 b0 = kvm_ld4_nc(watts + base), b1 = kvm_ld4_nc(watts + base + 4);
+#define KVM_D(x) __longlong_as_double((long long)(x))
+    t[0] = KVM_D(a0.x); t[1] = KVM_D(a0.y); t[2] = KVM_D(a0.z); t[3] = KVM_D(a0.w);
+    t[4] = KVM_D(a1.x); t[5] = KVM_D(a1.y); t[6] = KVM_D(a1.z); t[7] = KVM_D(a1.w);
+    w[0] = KVM_D(b0.x); w[1] = KVM_D(b0.y); w[2] = KVM_D(b0.z); w[3] = KVM_D(b0.w);
+    w[4] = KVM_D(b1.x); w[5] = KVM_D(b1.y); w[6] = KVM_D(b1.z); w[7] = KVM_D(b1.w);
+#undef KVM_D
+  } else {
+#pragma unroll
+    for (int r = 0; r < SEG_ITEMS; ++r) {
+      const bool in = base + r < m;
+      t[r] = in ? ts[base + r] : 0.0;
+      w[r] = in ? watts[base + r] : __longlong_as_double(0x7ff8000000000000ll);
+    }
+  }
+  // previous non-null sample before `base`
+  const double nan = __longlong_as_double(0x7ff8000000000000ll);
+  double tp = nan, wp = nan;
+  for (int64_t j = base - 1; j >= 0; --j) {
+    const double wj = watts[j];
+    if (!kvm_isnan(wj)) {
+      wp = wj;
+      tp = ts[j];
+      break;
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < SEG_ITEMS; ++r) {
+    if (base + r >= m) break;
+    double area = 0.0, tj = nan;
+    if (!kvm_isnan(w[r])) {
+      tj = tp;
+      if (!kvm_isnan(wp)) {
+        const double dt_h = div3600(t[r] - tp);          // collector.py:146
+        if (dt_h > 0) area = ((wp + w[r]) / 2.0) * dt_h;  // collector.py:147-148
+      }
+      tp = t[r];
+      wp = w[r];
+    }
+    f(r, base + r, t[r], tj, area);
+  }
 }
 
 // fixed-order block reduction of `cnt` double-double values per thread -> out[cnt] (thread 0 valid)
@@ -198,17 +275,29 @@ trapezoid_kernel(const double* __restrict__ ts, const double* __restrict__ watts
   kvm_dd acc[K];
 #pragma unroll
   for (int w = 0; w < K; ++w) acc[w] = {0.0, 0.0};
-  for (int64_t i = (int64_t)blockIdx.x * E_THREADS + threadIdx.x; i < m;
-       i += (int64_t)gridDim.x * E_THREADS) {
-    const double ti = kvm_ld1(ts + i), wi = kvm_ld1(watts + i);
-    double tj;
-    const double area = segment_wh(ts, watts, i, ti, wi, &tj);
-    if (area != 0.0) {
+  const bool vec = ((reinterpret_cast<uintptr_t>(ts) | reinterpret_cast<uintptr_t>(watts)) & 31u) == 0;
+  const int64_t ntiles = (m + E_THREADS * SEG_ITEMS - 1) / (E_THREADS * SEG_ITEMS);
+  for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const int64_t base = (tile * E_THREADS + threadIdx.x) * SEG_ITEMS;
+    for_eight_samples(ts, watts, m, base, vec, [&](int, int64_t, double ti, double tj, double area) {
+      if (area != 0.0) {
 #pragma unroll
-      for (int w = 0; w < K; ++w)
-        if (w < win.k && win.t1[w] > win.t0[w] && win.t0[w] <= tj && ti <= win.t1[w])
-          acc[w] = kvm_dd_add(acc[w], area);
-    }
+        for (int w = 0; w < K; ++w)
+          if (w < win.k && win.t1[w] > win.t0[w] && win.t0[w] <= tj && ti <= win.t1[w]) {
+            // sum + accumulated rounding error (two_sum): 7 flops instead of a double-double add
+            const double t = acc[w].hi + area;
+            const double bb = t - acc[w].hi;
+            acc[w].lo += (acc[w].hi - (t - bb)) + (area - bb);
+            acc[w].hi = t;
+          }
+      }
+    });
+  }
+#pragma unroll
+  for (int w = 0; w < K; ++w) {   // (sum, error) -> normalised double-double
+    const double hi = acc[w].hi + acc[w].lo;
+    acc[w].lo = acc[w].lo - (hi - acc[w].hi);
+    acc[w].hi = hi;
   }
   kvm_dd tot[K];
   block_reduce_dd<K>(acc, red, tot);
@@ -252,17 +341,15 @@ __global__ void __launch_bounds__(E_THREADS)
 prefix_tile_sum_kernel(const double* __restrict__ ts, const double* __restrict__ watts, int64_t m,
                        int64_t ntiles, double* __restrict__ tile_sum /* [ntiles][2] */) {
   __shared__ kvm_dd red[E_WARPS][1];
+  const bool vec = ((reinterpret_cast<uintptr_t>(ts) | reinterpret_cast<uintptr_t>(watts)) & 31u) == 0;
   for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-    kvm_dd acc[1] = {{0.0, 0.0}};
+    // eight consecutive segments per thread are added in plain fp64 (their sum is ~1e-3 Wh: the
+    // rounding error, ~1e-18 Wh, is far below the 1e-12 relative bound of any interval energy);
+    // everything ACROSS threads and tiles is double-double
+    double local = 0.0;
     const int64_t base = tile * PFX_TILE + (int64_t)threadIdx.x * PFX_ITEMS;
-#pragma unroll
-    for (int r = 0; r < PFX_ITEMS; ++r) {
-      const int64_t i = base + r;
-      if (i < m) {
-        double tj;
-        acc[0] = kvm_dd_add(acc[0], segment_wh(ts, watts, i, ts[i], watts[i], &tj));
-      }
-    }
+    for_eight_samples(ts, watts, m, base, vec, [&](int, int64_t, double, double, double area) { local += area; });
+    kvm_dd acc[1] = {{local, 0.0}};
     kvm_dd tot[1];
     block_reduce_dd<1>(acc, red, tot);
     if (threadIdx.x == 0) {
@@ -299,17 +386,19 @@ prefix_apply_kernel(const double* __restrict__ ts, const double* __restrict__ wa
                     int64_t ntiles, const double* __restrict__ tile_excl, double* __restrict__ p_hi,
                     double* __restrict__ p_lo) {
   __shared__ kvm_dd thread_tot[E_THREADS];
+  const bool vec = ((reinterpret_cast<uintptr_t>(ts) | reinterpret_cast<uintptr_t>(watts)) & 31u) == 0;
+  const bool vec_out = ((reinterpret_cast<uintptr_t>(p_hi) | reinterpret_cast<uintptr_t>(p_lo)) & 31u) == 0;
   for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const int64_t base = tile * PFX_TILE + (int64_t)threadIdx.x * PFX_ITEMS;
-    double a[PFX_ITEMS];
-    kvm_dd acc{0.0, 0.0};
+    double a[PFX_ITEMS];   // inclusive plain sums inside the thread (see prefix_tile_sum_kernel)
+    double local = 0.0;
 #pragma unroll
-    for (int r = 0; r < PFX_ITEMS; ++r) {
-      const int64_t i = base + r;
-      double tj;
-      a[r] = i < m ? segment_wh(ts, watts, i, ts[i], watts[i], &tj) : 0.0;
-      acc = kvm_dd_add(acc, a[r]);
-    }
+    for (int r = 0; r < PFX_ITEMS; ++r) a[r] = 0.0;
+    for_eight_samples(ts, watts, m, base, vec, [&](int r, int64_t, double, double, double area) {
+      local += area;
+      a[r] = local;
+    });
+    kvm_dd acc{local, 0.0};
     // exclusive prefix over the threads of the tile: inclusive shuffle scan inside each warp,
     // then the warp totals are folded in warp order (fixed shape -> deterministic)
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -328,14 +417,27 @@ prefix_apply_kernel(const double* __restrict__ ts, const double* __restrict__ wa
       if (lane == 0) excl = kvm_dd{0.0, 0.0};
       run = kvm_dd_add(run, excl);   // + exclusive prefix inside the warp
     }
+    double ph[PFX_ITEMS], pl[PFX_ITEMS];
 #pragma unroll
     for (int r = 0; r < PFX_ITEMS; ++r) {
-      const int64_t i = base + r;
-      run = kvm_dd_add(run, a[r]);
-      if (i < m) {
-        p_hi[i] = run.hi;
-        p_lo[i] = run.lo;
-      }
+      const kvm_dd p = kvm_dd_add(run, a[r]);   // prefix before the thread + plain sum inside it
+      ph[r] = p.hi;
+      pl[r] = p.lo;
+    }
+    if (vec_out && base + PFX_ITEMS <= m) {
+#define KVM_B(x) (unsigned long long)__double_as_longlong(x)
+      asm volatile("st.global.v4.b64 [%0], {%1,%2,%3,%4};" ::"l"(p_hi + base), "l"(KVM_B(ph[0])), "l"(KVM_B(ph[1])), "l"(KVM_B(ph[2])), "l"(KVM_B(ph[3])) : "memory");
+      asm volatile("st.global.v4.b64 [%0], {%1,%2,%3,%4};" ::"l"(p_hi + base + 4), "l"(KVM_B(ph[4])), "l"(KVM_B(ph[5])), "l"(KVM_B(ph[6])), "l"(KVM_B(ph[7])) : "memory");
+      asm volatile("st.global.v4.b64 [%0], {%1,%2,%3,%4};" ::"l"(p_lo + base), "l"(KVM_B(pl[0])), "l"(KVM_B(pl[1])), "l"(KVM_B(pl[2])), "l"(KVM_B(pl[3])) : "memory");
+      asm volatile("st.global.v4.b64 [%0], {%1,%2,%3,%4};" ::"l"(p_lo + base + 4), "l"(KVM_B(pl[4])), "l"(KVM_B(pl[5])), "l"(KVM_B(pl[6])), "l"(KVM_B(pl[7])) : "memory");
+#undef KVM_B
+    } else {
+#pragma unroll
+      for (int r = 0; r < PFX_ITEMS; ++r)
+        if (base + r < m) {
+          p_hi[base + r] = ph[r];
+          p_lo[base + r] = pl[r];
+        }
     }
     __syncthreads();
   }
@@ -359,26 +461,105 @@ __device__ __forceinline__ int64_t upper_bound_ts(const double* __restrict__ ts,
   return lo;
 }
 
+// ---- search from a guess.  A power trace is sampled (nearly) regularly, so the index of time x
+// is close to (x - ts[0]) * (m - 1) / (ts[m-1] - ts[0]); the search gallops outward from that
+// guess and bisects the bracket - two or three probes instead of ~27 dependent loads, and (the
+// intervals arriving in time order) neighbouring threads probe neighbouring cache lines: the
+// join streams through ts and the prefix arrays instead of hopping over them.  Any trace, any
+// interval order: the guess only decides how many probes are needed.
+__device__ __forceinline__ int64_t lower_bound_from(const double* __restrict__ ts, int64_t m, double x, int64_t g) {
+  g = g < 0 ? 0 : (g > m - 1 ? m - 1 : g);
+  int64_t lo, hi;   // answer (first index with ts >= x) in [lo, hi]
+  if (ts[g] < x) {
+    lo = g + 1;
+    for (int64_t step = 1;; step <<= 1) {
+      hi = lo + step - 1;
+      if (hi >= m) { hi = m; break; }
+      if (!(ts[hi] < x)) break;
+      lo = hi + 1;
+    }
+  } else {
+    hi = g;
+    for (int64_t step = 1;; step <<= 1) {
+      const int64_t p = hi - step;
+      if (p < 0) { lo = 0; break; }
+      if (ts[p] < x) { lo = p + 1; break; }
+      hi = p;
+    }
+  }
+  while (lo < hi) {
+    const int64_t mid = (lo + hi) >> 1;
+    if (ts[mid] < x) lo = mid + 1; else hi = mid;
+  }
+  return lo;
+}
+__device__ __forceinline__ int64_t upper_bound_from(const double* __restrict__ ts, int64_t m, double x, int64_t g) {
+  g = g < 0 ? 0 : (g > m - 1 ? m - 1 : g);
+  int64_t lo, hi;   // answer (first index with ts > x) in [lo, hi]
+  if (ts[g] <= x) {
+    lo = g + 1;
+    for (int64_t step = 1;; step <<= 1) {
+      hi = lo + step - 1;
+      if (hi >= m) { hi = m; break; }
+      if (!(ts[hi] <= x)) break;
+      lo = hi + 1;
+    }
+  } else {
+    hi = g;
+    for (int64_t step = 1;; step <<= 1) {
+      const int64_t p = hi - step;
+      if (p < 0) { lo = 0; break; }
+      if (ts[p] <= x) { lo = p + 1; break; }
+      hi = p;
+    }
+  }
+  while (lo < hi) {
+    const int64_t mid = (lo + hi) >> 1;
+    if (ts[mid] <= x) lo = mid + 1; else hi = mid;
+  }
+  return lo;
+}
+
+struct TraceTable {
+  kvm_power_trace tr[KVM_MAX_TRACES];
+  int32_t n;
+};
+
+// Every interval against every trace in ONE pass: the interval columns are read once, the
+// per-trace energies are added in trace order (PromQL `sum`, collector.py:45) in a register and
+// written once.  accumulate != 0 adds to what energy[] holds.
 __global__ void __launch_bounds__(E_THREADS)
-interval_energy_kernel(const double* __restrict__ ts, const double* __restrict__ watts,
-                       const double* __restrict__ p_hi, const double* __restrict__ p_lo, int64_t m,
-                       const double* __restrict__ start_ms, const double* __restrict__ latency_ms,
+interval_energy_kernel(TraceTable tt, const double* __restrict__ start_ms, const double* __restrict__ latency_ms,
                        int64_t n, double* __restrict__ energy, int accumulate) {
   for (int64_t r = (int64_t)blockIdx.x * E_THREADS + threadIdx.x; r < n;
        r += (int64_t)gridDim.x * E_THREADS) {
     const double st = kvm_ld1(start_ms + r), la = kvm_ld1(latency_ms + r);
     const double s = st / 1000.0, e = (st + la) / 1000.0;
-    double wh = 0.0;
-    if (e > s && m > 1) {
-      int64_t first = lower_bound_ts(ts, m, s);
-      const int64_t last = upper_bound_ts(ts, m, e) - 1;
-      while (first <= last && kvm_isnan(watts[first])) ++first;  // first kept sample of the interval
-      if (first < last) {
-        const kvm_dd d = kvm_dd_sub(kvm_dd{p_hi[last], p_lo[last]}, kvm_dd{p_hi[first], p_lo[first]});
-        wh = d.hi + d.lo;
+    double total = accumulate ? energy[r] : 0.0;
+    bool first_term = !accumulate;
+    for (int k = 0; k < tt.n; ++k) {
+      const kvm_power_trace T = tt.tr[k];
+      const int64_t m = T.m;
+      double wh = 0.0;
+      if (e > s && m > 1) {
+        const double t0 = T.ts[0], tn = T.ts[m - 1];
+        const double rate = tn > t0 ? (double)(m - 1) / (tn - t0) : 0.0;
+        const double gs = (s - t0) * rate;
+        const int64_t g0 = gs > 0.0 ? (gs < (double)m ? (int64_t)gs : m - 1) : 0;
+        int64_t first = lower_bound_from(T.ts, m, s, g0);
+        const double span = (e - s) * rate;
+        const int64_t g1 = first + (span < (double)m ? (int64_t)span : m);
+        const int64_t last = upper_bound_from(T.ts, m, e, g1) - 1;
+        while (first <= last && kvm_isnan(T.watts[first])) ++first;  // first kept sample of the interval
+        if (first < last) {
+          const kvm_dd d = kvm_dd_sub(kvm_dd{T.p_hi[last], T.p_lo[last]}, kvm_dd{T.p_hi[first], T.p_lo[first]});
+          wh = d.hi + d.lo;
+        }
       }
+      total = first_term ? wh : total + wh;
+      first_term = false;
     }
-    energy[r] = accumulate ? energy[r] + wh : wh;
+    energy[r] = total;
   }
 }
 
@@ -388,6 +569,21 @@ int grid_for(int64_t items, int per_cta) {
 }
 
 }  // namespace
+
+namespace {
+__global__ void div3600_check_kernel(const double* __restrict__ x, double* __restrict__ out, int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    out[i] = div3600(x[i]);
+}
+}  // namespace
+
+extern "C" int kvm_selfcheck_div3600(const double* x, double* out, int64_t n, void* stream) {
+  KVM_REQUIRE(n >= 0 && (n == 0 || (x && out)), "kvm_selfcheck_div3600: bad argument");
+  if (n == 0) return KVM_OK;
+  div3600_check_kernel<<<grid_for(n, 1024), 256, 0, (cudaStream_t)stream>>>(x, out, n);
+  KVM_CUDA_CHECK(cudaGetLastError());
+  return KVM_OK;
+}
 
 extern "C" size_t kvm_energy_workspace_bytes(int64_t m) {
   const int64_t ntiles = (m + PFX_TILE - 1) / PFX_TILE + 1;
@@ -459,16 +655,30 @@ extern "C" int kvm_energy_prefix(const double* ts, const double* watts, int64_t 
   return KVM_OK;
 }
 
+extern "C" int kvm_interval_energy_multi(const kvm_power_trace* traces, int32_t ntraces, const double* start_ms,
+                                         const double* latency_ms, int64_t n, double* energy_wh,
+                                         int32_t accumulate, void* stream) {
+  KVM_REQUIRE(traces && ntraces >= 1 && ntraces <= KVM_MAX_TRACES, "kvm_interval_energy_multi: 1..%d traces", KVM_MAX_TRACES);
+  KVM_REQUIRE(n >= 0, "kvm_interval_energy_multi: negative size");
+  if (n == 0) return KVM_OK;
+  KVM_REQUIRE(start_ms && latency_ms && energy_wh, "kvm_interval_energy_multi: null argument");
+  TraceTable tt{};
+  tt.n = ntraces;
+  for (int k = 0; k < ntraces; ++k) {
+    KVM_REQUIRE(traces[k].m >= 0 && (traces[k].m == 0 || (traces[k].ts && traces[k].watts && traces[k].p_hi && traces[k].p_lo)),
+                "kvm_interval_energy_multi: trace %d has null columns", k);
+    tt.tr[k] = traces[k];
+  }
+  interval_energy_kernel<<<grid_for(n, E_THREADS * 4), E_THREADS, 0, (cudaStream_t)stream>>>(
+      tt, start_ms, latency_ms, n, energy_wh, accumulate);
+  KVM_CUDA_CHECK(cudaGetLastError());
+  return KVM_OK;
+}
+
 extern "C" int kvm_interval_energy(const double* ts, const double* watts, const double* p_hi,
                                    const double* p_lo, int64_t m, const double* start_ms,
                                    const double* latency_ms, int64_t n, double* energy_wh,
                                    int32_t accumulate, void* stream) {
-  KVM_REQUIRE(n >= 0 && m >= 0, "kvm_interval_energy: negative size");
-  if (n == 0) return KVM_OK;
-  KVM_REQUIRE(start_ms && latency_ms && energy_wh && ((ts && watts && p_hi && p_lo) || m == 0),
-              "kvm_interval_energy: null argument");
-  interval_energy_kernel<<<grid_for(n, E_THREADS * 4), E_THREADS, 0, (cudaStream_t)stream>>>(
-      ts, watts, p_hi, p_lo, m, start_ms, latency_ms, n, energy_wh, accumulate);
-  KVM_CUDA_CHECK(cudaGetLastError());
-  return KVM_OK;
+  const kvm_power_trace one{ts, watts, p_hi, p_lo, m};
+  return kvm_interval_energy_multi(&one, 1, start_ms, latency_ms, n, energy_wh, accumulate, stream);
 }

@@ -150,9 +150,20 @@ class PowerTrace:
 def interval_energy_multi(traces: Sequence[PowerTrace], start_ms: torch.Tensor, latency_ms: torch.Tensor
                           ) -> torch.Tensor:
     """Per-request Wh summed over several GPU traces in index order (PromQL `sum`, collector.py:45)."""
-    out = None
-    for tr in traces:
-        out = tr.interval_energy(start_ms, latency_ms, out, accumulate=out is not None)
+    n = int(start_ms.shape[0])
+    if not traces:
+        return torch.zeros(n, dtype=torch.float64, device=start_ms.device)
+    lib, dev = traces[0].lib, traces[0].device
+    out = torch.zeros(n, dtype=torch.float64, device=dev)
+    for b in range(0, len(traces), N.KVM_MAX_TRACES):      # eight traces per pass over the intervals
+        chunk = traces[b:b + N.KVM_MAX_TRACES]
+        table = (N.PowerTraceC * len(chunk))()
+        for k, tr in enumerate(chunk):
+            p_hi, p_lo = tr.prefix()
+            table[k] = N.PowerTraceC(tr.ts.data_ptr(), tr.watts.data_ptr(), p_hi.data_ptr(), p_lo.data_ptr(), tr.m)
+        N.check(lib.kvm_interval_energy_multi(table, len(chunk), start_ms.data_ptr(), latency_ms.data_ptr(), n,
+                                              out.data_ptr(), 1 if b else 0, traces[0]._stream()),
+                "kvm_interval_energy_multi")
     return out
 
 

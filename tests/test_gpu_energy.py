@@ -167,3 +167,60 @@ def test_interval_energy_join_vs_oracle(m, n, null_p):
                for t, x in zip(ts0[lo:hi], w0[lo:hi])]
     one = trs[0].interval_energy(s_d[i:i + 1].clone(), l_d[i:i + 1].clone()).item()
     assert close(one, trapezoidal_wh(samples, s, e))
+
+
+def test_division_free_quotient_is_the_ieee_quotient():
+    """The energy kernels evaluate (ts1 - ts0) / 3600.0 (collector.py:146) without the hardware
+    division (reciprocal multiply + exact fma residual + a proof check, else the real division):
+    bit-identical to x / 3600.0 on 2e7 doubles of every magnitude, sign and special value."""
+    import torch
+    from kvmini_b200 import _native as N
+    rng = np.random.default_rng(3600)
+    parts = [rng.uniform(0.0, 2e-3, 4_000_000),                                # sample steps at 1 kHz
+             rng.uniform(0.0, 10.0, 4_000_000),
+             np.ldexp(rng.uniform(1.0, 2.0, 4_000_000), rng.integers(-1070, 1020, 4_000_000)),
+             -np.ldexp(rng.uniform(1.0, 2.0, 2_000_000), rng.integers(-300, 300, 2_000_000)),
+             3600.0 * np.ldexp(rng.integers(1, 1 << 53, 2_000_000).astype(np.float64), rng.integers(-80, 20, 2_000_000)),
+             (3600.0 * rng.integers(1, 1 << 40, 2_000_000)).astype(np.float64),  # exact quotients
+             np.nextafter(3600.0 * rng.integers(1, 1 << 40, 1_000_000).astype(np.float64), np.inf),
+             np.array([0.0, -0.0, np.inf, -np.inf, np.nan, 5e-324, 1e-308, 1.7976931348623157e308, 3600.0, 1.0])]
+    x = np.concatenate(parts)
+    d = torch.from_numpy(x).cuda()
+    out = torch.empty_like(d)
+    N.check(N.lib().kvm_selfcheck_div3600(d.data_ptr(), out.data_ptr(), x.size, torch.cuda.current_stream().cuda_stream))
+    got = out.cpu().numpy()
+    with np.errstate(all="ignore"):
+        exp = x / 3600.0
+    assert np.array_equal(got.view(np.uint64)[~np.isnan(exp)], exp.view(np.uint64)[~np.isnan(exp)])
+    assert np.isnan(got[np.isnan(exp)]).all()
+
+
+def test_interval_join_unsorted_intervals_irregular_trace_and_many_traces():
+    """The join searches from an interpolated guess: intervals in random order, a trace with a long
+    gap and bursts (guess far off), 9 traces (two passes of <= 8), intervals outside the trace."""
+    import torch
+    from kvmini_b200 import energy_api, synth
+    from oracle import np_port
+    rng = np.random.default_rng(8)
+    m, n = 300_000, 60_000
+    traces = []
+    for g in range(9):
+        ts, w = synth.power_trace(m, gpu=g, hz=50.0, null_p=0.02)
+        if g == 1:
+            ts = np.sort(np.concatenate([ts[: m // 3], ts[m // 3:] + 5000.0]))      # a 5000 s hole
+        if g == 2:
+            ts = np.sort(ts[0] + (ts - ts[0]) ** 1.3 / (ts[-1] - ts[0]) ** 0.3)     # accelerating clock
+        traces.append((ts, w))
+    span_ms = m / 50.0 * 1000.0
+    cols = synth.request_columns(n, seed=3, span_ms=span_ms * 1.2, t_epoch_ms=1.7e12 - 0.1 * span_ms)
+    perm = rng.permutation(n)
+    start, lat = cols["start_ms"][perm].copy(), cols["latency_ms"][perm].copy() * 20.0
+    dev = torch.device("cuda", 0)
+    trs = [energy_api.PowerTrace(ts, w) for ts, w in traces]
+    got = energy_api.interval_energy_multi(trs, torch.from_numpy(start).to(dev), torch.from_numpy(lat).to(dev)).cpu().numpy()
+    exp = np.zeros(n)
+    for ts, w in traces:            # trace order, like the device
+        exp = exp + np_port.interval_energy(ts, w, start, lat)
+    rel = np.abs(got - exp) / np.maximum(np.abs(exp), 1e-300)
+    assert np.all((rel <= TOL) | (got == exp)), float(rel.max())
+    assert (exp > 0).sum() > n // 2
