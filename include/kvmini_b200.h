@@ -571,6 +571,12 @@ int kvm_interval_energy(const double* ts, const double* watts, const double* p_h
  * are read once and energy_wh[] written once.  The two boundary searches per interval and trace
  * start from an interpolated guess (traces are sampled regularly) and gallop: time-ordered
  * intervals stream through ts / prefix instead of bisecting 27 levels each. */
+/* Multi-GPU energy (one trace per rank; no reference counterpart - the reference is one process
+ * and lets PromQL add the GPUs, collector.py:45): out[i] = ((s_0[i] + s_1[i]) + s_2[i]) + ... with
+ * s_r = slices + r*stride - the per-interval energies of the ranks added in RANK ORDER, never by a
+ * floating-point all-reduce (kserve-vllm-mini_b200/dist_energy.py). */
+int kvm_ordered_sum_f64(const double* slices, int32_t world, int64_t n, int64_t stride, double* out, void* stream);
+
 /* Diagnostic: out[i] = the library's division-free evaluation of x[i] / 3600.0 (the trapezoid and
  * prefix kernels use it for collector.py:146); must equal the IEEE quotient bit for bit. */
 int kvm_selfcheck_div3600(const double* x, double* out, int64_t n, void* stream);

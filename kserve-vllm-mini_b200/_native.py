@@ -189,6 +189,7 @@ def _declare(lib: C.CDLL) -> None:
         "kvm_trapezoid_wh": (C.c_int, [vp, vp, i64, P(f64), i32, vp, vp, sz, vp]),
         "kvm_energy_prefix": (C.c_int, [vp, vp, i64, vp, vp, vp, sz, vp]),
         "kvm_interval_energy": (C.c_int, [vp, vp, vp, vp, i64, vp, vp, i64, vp, i32, vp]),
+        "kvm_ordered_sum_f64": (C.c_int, [vp, i32, i64, i64, vp, vp]),
         "kvm_selfcheck_div3600": (C.c_int, [vp, vp, i64, vp]),
         "kvm_interval_energy_multi": (C.c_int, [P(PowerTraceC), i32, vp, vp, i64, vp, i32, vp]),
     }

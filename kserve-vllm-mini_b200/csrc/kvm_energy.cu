@@ -655,6 +655,28 @@ extern "C" int kvm_energy_prefix(const double* ts, const double* watts, int64_t 
   return KVM_OK;
 }
 
+namespace {
+// out[i] = ((s0[i] + s1[i]) + s2[i]) + ...: the contributions of the ranks added in rank order
+__global__ void __launch_bounds__(256)
+ordered_sum_kernel(const double* __restrict__ slices, int world, int64_t n, int64_t stride, double* __restrict__ out) {
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (int64_t)gridDim.x * 256) {
+    double acc = kvm_ld1(slices + i);
+    for (int r = 1; r < world; ++r) acc = acc + kvm_ld1(slices + (size_t)r * stride + i);
+    out[i] = acc;
+  }
+}
+}  // namespace
+
+extern "C" int kvm_ordered_sum_f64(const double* slices, int32_t world, int64_t n, int64_t stride, double* out,
+                                   void* stream) {
+  KVM_REQUIRE(world >= 1 && n >= 0 && stride >= n, "kvm_ordered_sum_f64: bad sizes");
+  if (n == 0) return KVM_OK;
+  KVM_REQUIRE(slices && out, "kvm_ordered_sum_f64: null argument");
+  ordered_sum_kernel<<<grid_for(n, 256 * 8), 256, 0, (cudaStream_t)stream>>>(slices, world, n, stride, out);
+  KVM_CUDA_CHECK(cudaGetLastError());
+  return KVM_OK;
+}
+
 extern "C" int kvm_interval_energy_multi(const kvm_power_trace* traces, int32_t ntraces, const double* start_ms,
                                          const double* latency_ms, int64_t n, double* energy_wh,
                                          int32_t accumulate, void* stream) {

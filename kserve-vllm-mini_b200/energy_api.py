@@ -99,6 +99,18 @@ class PowerTrace:
                                             self._stream()), "kvm_sort_pairs_f64")
         self.ts, self.watts = ts_s, w_s
 
+    def trapezoid_dd(self, windows: Sequence[Tuple[float, float]]) -> List[Tuple[float, float]]:
+        """Wh over each window as the device's double-double (hi, lo) pair - what the multi-GPU path
+        exchanges so that the ranks' values can be added exactly, in rank order (dist_energy.py)."""
+        k = len(windows)
+        flat = (C.c_double * (2 * k))(*[float(x) for w in windows for x in w])
+        out = torch.zeros(2 * k, dtype=torch.float64, device=self.device)
+        N.check(self.lib.kvm_trapezoid_wh(self.ts.data_ptr(), self.watts.data_ptr(), self.m, flat, k,
+                                          out.data_ptr(), self._ws.data_ptr(), self._ws.numel(),
+                                          self._stream()), "kvm_trapezoid_wh")
+        o = out.cpu().tolist()
+        return [(o[2 * i], o[2 * i + 1]) for i in range(k)]
+
     def trapezoid(self, windows: Sequence[Tuple[float, float]]) -> List[float]:
         """Wh over each (t0, t1) window in one pass (kvm_trapezoid_wh)."""
         k = len(windows)

@@ -110,3 +110,85 @@ def test_rank_ordered_dd_total_is_exact():
     parts = [(1e16, 1.0), (-1e16, 0.25), (3.0, 1e-20)]
     hi, lo = dist_api._exact_dd_total(parts)
     assert hi == 4.25 and abs(lo - 1e-20) < 1e-35
+
+
+# ---- multi-GPU energy host logic (dist_energy.py) over gloo, numpy stand-ins for the kernels ----
+class _NpTrace:
+    """Test-side stand-in for energy_api.PowerTrace: same two methods, oracle arithmetic."""
+
+    def __init__(self, ts, watts):
+        self.ts, self.watts = np.asarray(ts, dtype=np.float64), np.asarray(watts, dtype=np.float64)
+
+    def trapezoid_dd(self, windows):
+        from oracle import np_port
+        return [(np_port.trapezoid_wh(self.ts, self.watts, a, b, exact=True), 0.0) for a, b in windows]
+
+    def interval_energy(self, start_ms, latency_ms):
+        from oracle import np_port
+        return torch.from_numpy(np_port.interval_energy(self.ts, self.watts, start_ms.numpy(), latency_ms.numpy()))
+
+
+def _energy_worker(rank, world, port, ret):
+    sys.path.insert(0, REPO)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from kvmini_b200 import dist_energy, synth
+    from oracle import np_port
+    dev = torch.device("cpu")
+    bad = []
+    # (1) trace-sharded: rank r owns trace r; windows and per-interval energies are rank-ordered sums
+    traces = [synth.power_trace(20_000, gpu=g, hz=50.0, null_p=0.01) for g in range(world)]
+    cols = synth.request_columns(3001, seed=4, span_ms=20_000 / 50.0 * 1000.0)
+    start, lat = torch.from_numpy(cols["start_ms"]), torch.from_numpy(cols["latency_ms"] * 5.0)
+    sh = dist_energy.TraceShardedEnergy(_NpTrace(*traces[rank]), dev)
+    t0 = float(traces[0][0][100])
+    wins = [(t0, t0 + 200.0), (t0 + 10.0, t0 + 11.0)]
+    got = sh.window_wh(wins)
+    exp = [math.fsum(np_port.trapezoid_wh(ts, w, a, b, exact=True) for ts, w in traces) for a, b in wins]
+    if not all(abs(g - e) <= 1e-15 * abs(e) for g, e in zip(got, exp)):
+        bad.append(("window_wh", got, exp))
+    e = sh.interval_energy(start, lat).numpy()
+    ref = np.zeros(len(cols["start_ms"]))
+    for ts, w in traces:
+        ref = ref + np_port.interval_energy(ts, w, cols["start_ms"], cols["latency_ms"] * 5.0)
+    if not np.array_equal(e, ref):     # same additions in the same (rank) order: bit-equal
+        bad.append(("interval_energy", float(np.abs(e - ref).max())))
+    # (2) time-sharded: one trace cut in `world` pieces, the cut inside a run of nulls
+    ts, w = synth.power_trace(30_000, gpu=7, hz=20.0, null_p=0.0)
+    cut = 30_000 // world
+    w[cut - 3:cut + 2] = np.nan                    # the segment across the cut spans 6 samples
+    lo, hi = rank * cut, (rank + 1) * cut if rank < world - 1 else 30_000
+    ts_r, w_r = ts[lo:hi], w[lo:hi]
+    nn = np.flatnonzero(~np.isnan(w_r))
+    last = (float(ts_r[nn[-1]]), float(w_r[nn[-1]])) if len(nn) else (0.0, math.nan)
+    tsh = dist_energy.TimeShardedEnergy(ts_r, w_r, dev, _NpTrace, last)
+    if (rank == 0) != (tsh.halo is None):
+        bad.append(("halo", tsh.halo))
+    wins = [(float(ts[0]), float(ts[-1])), (float(ts[cut - 50]), float(ts[cut + 50])), (float(ts[5]), float(ts[50]))]
+    got = tsh.window_wh(wins)
+    exp = [np_port.trapezoid_wh(ts, w, a, b, exact=True) for a, b in wins]
+    if not all(abs(g - e) <= 1e-14 * abs(e) for g, e in zip(got, exp)):
+        bad.append(("time_sharded", got, exp))
+    ret[rank] = bad
+    dist.destroy_process_group()
+
+
+def test_energy_sharding_world2_gloo():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    mp.spawn(_energy_worker, args=(2, port, ret), nprocs=2, join=True)
+    assert dict(ret) == {0: [], 1: []}
+
+
+def test_halo_skips_shards_without_samples():
+    from kvmini_b200 import dist_energy
+    nan = math.nan
+    last = [(10.0, 5.0), (0.0, nan), (30.0, 7.0), (0.0, nan)]
+    assert dist_energy.halo_for_rank(last, 0) is None
+    assert dist_energy.halo_for_rank(last, 1) == (10.0, 5.0)
+    assert dist_energy.halo_for_rank(last, 2) == (10.0, 5.0)      # shard 1 had no non-null sample
+    assert dist_energy.halo_for_rank(last, 3) == (30.0, 7.0)
+    assert dist_energy.rank_ordered_total([(1e16, 1.0), (-1e16, 0.5)]) == 1.5
