@@ -475,6 +475,22 @@ int kvm_csv_match_any(const kvm_csv* csv, int32_t col, const char* const* option
 int kvm_csv_write_classified(const kvm_csv* csv, const char* out_path, const uint8_t* is_cold,
                              const int32_t* coerced_cols, int32_t ncoerced, int32_t threads);
 
+/* ------------------------------------------------------------------ power-sample ingest (host only)
+ * SURVEY.md section 8f F3.  Columnar fast path for `load_power_samples` (energy/collector.py:152-177:
+ * power.json = {"samples": [{"ts" | "ts_s": t, "watts": w | null}, ...]} or the bare list) and for
+ * Prometheus query / query_range responses (analyze.py:219-247, energy/collector.py:203-251:
+ * "values": [[t, "v"], ...] per series): the text is scanned once, in parallel, into two fp64
+ * columns per series (timestamp, value; NaN = null) - no object per sample.  Numbers are parsed
+ * with std::from_chars (the same double as Python's float()).  Text the scanner does not model
+ * returns KVM_ERR_UNSUPPORTED and the caller falls back to the json module. */
+typedef struct kvm_samples kvm_samples;
+int kvm_power_json_parse(const char* path, int32_t threads, kvm_samples** out);
+int kvm_prom_result_parse(const char* text, int64_t len, int32_t threads, kvm_samples** out);
+int32_t kvm_samples_series(const kvm_samples* s);
+int64_t kvm_samples_count(const kvm_samples* s, int32_t series);
+int kvm_samples_copy(const kvm_samples* s, int32_t series, double* ts_host, double* values_host);
+void kvm_samples_free(kvm_samples* s);
+
 /* ------------------------------------------------------------------ histograms / series */
 
 /* K5: the four 20-bin value histograms of analyze.py:84-122,149-152 in one pass.

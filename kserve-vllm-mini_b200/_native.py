@@ -177,6 +177,12 @@ def _declare(lib: C.CDLL) -> None:
         "kvm_csv_cell": (i64, [vp, i64, i32, vp, i64]),
         "kvm_csv_match_any": (C.c_int, [vp, i32, P(C.c_char_p), i32, vp, i32]),
         "kvm_csv_write_classified": (C.c_int, [vp, C.c_char_p, vp, vp, i32, i32]),
+        "kvm_power_json_parse": (C.c_int, [C.c_char_p, i32, P(vp)]),
+        "kvm_prom_result_parse": (C.c_int, [C.c_char_p, i64, i32, P(vp)]),
+        "kvm_samples_series": (i32, [vp]),
+        "kvm_samples_count": (i64, [vp, i32]),
+        "kvm_samples_copy": (C.c_int, [vp, i32, vp, vp]),
+        "kvm_samples_free": (None, [vp]),
         "kvm_log_histograms_workspace_bytes": (sz, [i32]),
         "kvm_log_histograms": (C.c_int, [P(RequestLogC), vp, vp, i32, vp, vp, sz, vp]),
         "kvm_column_histogram": (C.c_int, [vp, i64, f64, f64, i32, vp, vp, sz, vp]),

@@ -87,6 +87,27 @@ def prom_matrix_timeavg(result: Dict[str, Any]) -> Optional[float]:
         return None
 
 
+def prom_matrix_timeavg_body(body: bytes) -> Optional[float]:
+    """prom_matrix_timeavg (analyze.py:233-247) straight from the response BODY: large range-query
+    results (hours of 1 kHz power samples) are scanned into columns by the native parser instead
+    of becoming one Python object per point; the mean is then taken exactly like the reference
+    does (`sum(pts) / len(pts)` over the points in series order).  Falls back to the json module."""
+    try:
+        from . import energy_api
+        cols = energy_api.prom_result_columns(body)
+    except Exception:
+        cols = None
+    if cols is None:
+        try:
+            return prom_matrix_timeavg(json.loads(body))
+        except Exception:
+            return None
+    pts: List[float] = []
+    for _ts, vals in cols:
+        pts.extend(vals.tolist())
+    return sum(pts) / len(pts) if pts else None
+
+
 def _first_avg(prom_url: str, queries: List[str]) -> Optional[float]:
     for q in queries:
         v = prom_vector_avg(prom_query(prom_url, q))

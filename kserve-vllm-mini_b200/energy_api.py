@@ -242,6 +242,45 @@ def trapezoidal_wh(samples: List[PowerSample], t0: float, t1: float) -> float:
     return PowerTrace.from_samples(samples).trapezoid([(t0, t1)])[0]
 
 
+def _samples_to_columns(handle) -> List[Tuple[np.ndarray, np.ndarray]]:
+    lib = N.lib()
+    try:
+        out = []
+        for k in range(int(lib.kvm_samples_series(handle))):
+            n = int(lib.kvm_samples_count(handle, k))
+            ts, val = np.empty(n, dtype=np.float64), np.empty(n, dtype=np.float64)
+            N.check(lib.kvm_samples_copy(handle, k, ts.ctypes.data, val.ctypes.data), "kvm_samples_copy")
+            out.append((ts, val))
+        return out
+    finally:
+        lib.kvm_samples_free(handle)
+
+
+def load_power_columns(path: str, threads: Optional[int] = None) -> Tuple[np.ndarray, np.ndarray]:
+    """power.json -> (ts, watts) fp64 columns, NaN = null watts: what `load_power_samples`
+    (collector.py:152-177) yields, without one PowerSample object per sample.  The native scanner
+    (csrc/kvm_samples.cu) takes the file when it is plain; anything else goes through json."""
+    handle = C.c_void_p()
+    rc = N.lib().kvm_power_json_parse(os.fsencode(path), threads or min(32, os.cpu_count() or 1), C.byref(handle))
+    if rc == N.KVM_OK:
+        cols = _samples_to_columns(handle)
+        return cols[0] if cols else (np.empty(0), np.empty(0))
+    samples = load_power_samples(path)      # raises what the reference raises on malformed input
+    ts = np.fromiter((s.ts for s in samples), dtype=np.float64, count=len(samples))
+    w = np.fromiter((math.nan if s.watts is None else s.watts for s in samples), dtype=np.float64, count=len(samples))
+    return ts, w
+
+
+def prom_result_columns(body: bytes, threads: Optional[int] = None) -> Optional[List[Tuple[np.ndarray, np.ndarray]]]:
+    """A Prometheus query / query_range response body -> [(ts, values)] per series (values: the
+    quoted numbers, NaN / +-Inf included), or None when the scanner declines (use json.loads)."""
+    handle = C.c_void_p()
+    rc = N.lib().kvm_prom_result_parse(body, len(body), threads or min(32, os.cpu_count() or 1), C.byref(handle))
+    if rc != N.KVM_OK:
+        return None
+    return _samples_to_columns(handle)
+
+
 def load_power_samples(path: str) -> List[PowerSample]:
     """collector.py:152-177: bare list or {"samples": [...]}; `ts_s` accepted for `ts`."""
     with open(path) as f:
@@ -343,8 +382,8 @@ def integrate_energy(args: argparse.Namespace) -> int:
 
     rows = read_requests_csv(req_csv)
     stats = _scan_rows(rows) if rows else None
-    samples = load_power_samples(power_path)
-    trace = PowerTrace.from_samples(samples) if samples else None
+    ts_col, w_col = load_power_columns(power_path)      # columnar: no PowerSample object per sample
+    trace = PowerTrace(ts_col, w_col) if ts_col.size else None
     energy = integrate_core(stats, trace, args.include_warmup, args.idle_tax)
     if energy is None:
         print("ERROR: Invalid integration window", file=sys.stderr)
