@@ -299,6 +299,76 @@ def percentile_path_block(device, peak, sizes=(10_000_000, 100_000_000), steps=5
     return out
 
 
+def cfg5_block(args, device, rank, world, dist, cold):
+    """BASELINE.json configs[4] in the driver's own line: 1.25e8 rows per GPU (1e9 at 8 GPUs), the
+    log sharded by time range, generated on the device (no host copy: 7 GB per GPU).  Every rank
+    runs the sharded analysis; then the SAME shard is analysed by the single-GPU analyzer in the
+    same run (what one GPU does alone on 1/world of the log) for the scaling ratio.  Parity at this
+    size: a rank certificate - for every reported latency order statistic v with rank k, all ranks
+    count their success rows below / up to v; the counts, summed, must bracket k (an exact
+    order statistic of the WHOLE log, independent of any oracle)."""
+    import torch
+    from kvmini_b200 import dist_api, engine, report, synth
+    rows = args.cfg5_rows
+    cols = synth.request_columns_device(rows, device, seed=4321 + rank, t_epoch_ms=1.7e12, t_offset_ms=rank * 3.6e6)
+    dlog = engine.DeviceLog.from_tensors(cols)
+    steps = max(3, min(args.steps, 10))
+    sharded = dist_api.ShardedAnalyzer(device, exchange=args.exchange)
+    for _ in range(3):
+        raw = sharded.analyze(dlog, cold, use_graph=not args.eager)
+    dist.barrier()
+    torch.cuda.synchronize(device)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        raw = sharded.analyze(dlog, cold, use_graph=not args.eager)
+    e1.record()
+    dist.barrier()
+    torch.cuda.synchronize(device)
+    ms = e0.elapsed_time(e1) / steps
+    core = report.core_results(raw, len(cold))
+    sharded.close()
+    # one GPU alone on its shard (same run, same data)
+    single = engine.LogAnalyzer(device)
+    for _ in range(3):
+        single.analyze(dlog, cold, use_graph=True)
+    torch.cuda.synchronize(device)
+    s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s0.record()
+    for _ in range(steps):
+        single.analyze(dlog, cold, use_graph=True)
+    s1.record()
+    torch.cuda.synchronize(device)
+    ms_single = s0.elapsed_time(s1) / steps
+    single.close()
+    # rank certificate of the global latency order statistics
+    ok_lat = cols["latency_ms"][(cols["status"] == 200) & ~torch.isnan(cols["latency_ms"])]
+    checks = []
+    for name, p in (("lat_p50", 0.50), ("lat_p95", 0.95), ("lat_p99", 0.99)):
+        st = raw.order[name]
+        for v, fn in ((st.v_lo, math.floor), (st.v_hi, math.ceil)):
+            checks.append((float(v), fn, p))
+    cnt = torch.tensor([[int((ok_lat < v).sum()), int((ok_lat <= v).sum())] for v, _, _ in checks] + [[ok_lat.numel(), 0]],
+                       dtype=torch.int64, device=device)
+    dist.all_reduce(cnt)
+    t = torch.tensor([ms, ms_single], dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    n_glob = int(cnt[-1, 0])
+    certified = all(int(cnt[i, 0]) <= int(fn(p * (n_glob - 1))) < int(cnt[i, 1]) for i, (_, fn, p) in enumerate(checks))
+    del cols, dlog, ok_lat
+    torch.cuda.empty_cache()
+    ms, ms_single = float(t[0]), float(t[1])
+    return {"workload": "configs[4]: 1e9-record log sharded by time range over 8 GPUs (rows_per_gpu x n_gpus here)",
+            "rows_per_gpu": rows, "rows_total": rows * world, "steps": steps, "ms_per_step": ms,
+            "records_per_s": rows * world / ms * 1e3,
+            "one_gpu_on_one_shard_ms": ms_single, "one_gpu_records_per_s": rows / ms_single * 1e3,
+            "speedup_vs_one_gpu_on_one_shard": (rows * world / ms) / (rows / ms_single),
+            "parity": {"method": "rank certificate of lat p50/p95/p99 (lo and hi order statistics): global counts "
+                                 "below / up to the reported value bracket the rank", "success_rows": n_glob,
+                       "equal": bool(certified)},
+            "check": {"p50_ms": core["p50_ms"], "p99_ms": core["p99_ms"]}}
+
+
 # --------------------------------------------------------------------------- our arm
 def run_ours(args):
     import numpy as np
@@ -482,6 +552,9 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms_total, ms_e2e, ms_eager = float(t[0]), float(t[1]), float(t[2])
 
+    cfg5 = None
+    if world > 1 and not args.no_cfg5:
+        cfg5 = cfg5_block(args, device, rank, world, dist, cold)
     host_all = None
     if rank == 0 and host is not None and not args.no_parity:
         # the whole (sharded) log on the host of rank 0: every shard is regenerated from its seed
@@ -550,6 +623,8 @@ def run_ours(args):
         }
         if not args.no_parity and host_all is not None:
             line["parity"] = parity_block(core, report.trim_series(raw), host_all, cold)
+        if cfg5 is not None:
+            line["cfg5"] = cfg5
         if world == 1 and not args.no_percentile_path:
             line["percentile_path"] = percentile_path_block(device, peak)
         if world == 1 and not args.no_cpu_baseline and host is not None:
@@ -579,6 +654,8 @@ def main():
     ap.add_argument("--rows", type=int, default=10_000_000, help="rows per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-parity", action="store_true", help="skip the oracle comparison of the timed log")
+    ap.add_argument("--no-cfg5", action="store_true", help="N>1: skip the 1.25e8-rows-per-GPU block")
+    ap.add_argument("--cfg5-rows", type=int, default=125_000_000, help="rows per GPU of the cfg5 block")
     ap.add_argument("--no-percentile-path", action="store_true",
                     help="N=1: skip the 16 B/record percentile-path block")
     ap.add_argument("--port", action="store_true",
