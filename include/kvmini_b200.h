@@ -240,6 +240,21 @@ int kvm_log_fused_pass(const kvm_request_log* log_host, const double* cold_times
                        const kvm_log_extras* extras_host, void* scan_workspace, size_t scan_workspace_bytes,
                        void* select_workspace, size_t select_workspace_bytes, int64_t arena_capacity,
                        void* stream);
+/* Sharded logs (one rank per GPU): the digit histograms of the ranks are summed, so every rank must
+ * bin with the SAME parameters.  kvm_log_fused_sample writes a shard's sample record
+ * (kvm_log_fused_preset_words() u64 words), the ranks exchange the records,
+ * kvm_log_fused_preset_combine folds them (records `stride_words` apart) into the agreed hull, and
+ * kvm_log_fused_pass_preset runs the pass with it (any alignment, empty shards included; the series
+ * reference is the minimum over all ranks' samples).  No reference counterpart (one process). */
+int32_t kvm_log_fused_preset_words(void);
+int kvm_log_fused_sample(const kvm_request_log* log_host, uint64_t* record, void* stream);
+int kvm_log_fused_preset_combine(const uint64_t* records, int32_t world, int64_t stride_words, uint64_t* preset,
+                                 void* stream);
+int kvm_log_fused_pass_preset(const kvm_request_log* log_host, const double* cold_times, int32_t n_cold_times,
+                              double cold_window_s, uint8_t* flags, kvm_log_stats* stats,
+                              const kvm_log_extras* extras_host, void* scan_workspace, size_t scan_workspace_bytes,
+                              void* select_workspace, size_t select_workspace_bytes, int64_t arena_capacity,
+                              const uint64_t* preset, void* stream);
 int kvm_select_plan_preset(const kvm_set_info* info, const kvm_query* queries_host, int32_t nq,
                            const kvm_hist_spec* hists_host, void* workspace, size_t workspace_bytes,
                            int64_t arena_capacity, int32_t refine_rounds, int64_t refine_min_keys,

@@ -122,6 +122,10 @@ def _declare(lib: C.CDLL) -> None:
         "kvm_log_select": (C.c_int, [P(RequestLogC), vp, vp, P(QueryC), i32, vp, P(LogExtrasC), vp, sz, i64, vp]),
         "kvm_log_analyze_fused_scan_workspace_bytes": (sz, []),
         "kvm_log_fused_pass": (C.c_int, [P(RequestLogC), vp, i32, f64, vp, vp, P(LogExtrasC), vp, sz, vp, sz, i64, vp]),
+        "kvm_log_fused_preset_words": (i32, []),
+        "kvm_log_fused_sample": (C.c_int, [P(RequestLogC), vp, vp]),
+        "kvm_log_fused_preset_combine": (C.c_int, [vp, i32, i64, vp, vp]),
+        "kvm_log_fused_pass_preset": (C.c_int, [P(RequestLogC), vp, i32, f64, vp, vp, P(LogExtrasC), vp, sz, vp, sz, i64, vp, vp]),
         "kvm_select_plan_preset": (C.c_int, [vp, P(QueryC), i32, P(HistSpecC), vp, sz, i64, i32, i64, vp]),
         "kvm_log_analyze_fused": (C.c_int, [P(RequestLogC), vp, i32, f64, vp, vp, P(QueryC), i32, vp, P(LogExtrasC),
                                             vp, sz, vp, sz, i64, i32, i64, vp]),

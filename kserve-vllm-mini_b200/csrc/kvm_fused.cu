@@ -102,18 +102,50 @@ __device__ __forceinline__ void dd_acc(double& s, double& e, double x) {
   s = t;
 }
 
-template <bool COLD_SMEM_TABLE, bool SERIES>
-__global__ void __launch_bounds__(FU_THREADS, 2)
-log_fused_kernel(kvm_request_log log, const double* __restrict__ cold_lo_g, const double* __restrict__ cold_hi_g,
-                 int nc, uint8_t* __restrict__ flags, uint64_t* __restrict__ recs, kvm_log_stats* __restrict__ out,
-                 FusedWs* fws, SelWs* ws, FusedSeries sa) {
-  extern __shared__ __align__(16) unsigned char fraw[];
-  uint32_t* sh = reinterpret_cast<uint32_t*>(fraw);   // [KVM_LOG_NSETS][BINS]
-  FusedSmem& S = *reinterpret_cast<FusedSmem*>(fraw + sizeof(uint32_t) * KVM_LOG_NSETS * BINS);
-  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+// The 512-row sample: 16 regions spread evenly over the log (the first row and the last row
+// included), 32 pseudo-random rows inside a 4096-row window of each.  Per value column the
+// complemented minimum and the maximum key of the sampled MEMBERS (0 / 0: none), and the minimum
+// sampled start_ms.  Thread t of `nthreads` takes rows t, t + nthreads, ...
+constexpr int FU_PRESET_WORDS = 2 * NC + 1;   // [inv_min[NC] | max[NC] | bits of the start reference]
+__device__ __forceinline__ void fused_sample_rows(const kvm_request_log& log, int t, int nthreads,
+                                                  uint64_t (&s_inv)[NC], uint64_t (&s_mx)[NC], double& s_st) {
   const int64_t n = log.n;
+  if (n < 1) return;
+  const int64_t win = n < 4096 ? n : 4096;
+  for (int sidx = t; sidx < 512; sidx += nthreads) {
+    const int64_t region = sidx >> 5;
+    const int64_t off = n > win ? region * ((n - win) / 15) : 0;
+    int64_t i = off + (int64_t)(((uint32_t)sidx * 2654435761u >> 7) % (uint32_t)win);
+    if (sidx == 0) i = 0;
+    if (sidx == 511) i = n - 1;
+    const double la = __ldg(log.latency_ms + i), tf = __ldg(log.ttfb_ms + i), tl = __ldg(log.tllt_ms + i);
+    const double st = __ldg(log.start_ms + i);
+    const bool ok = __ldg(log.status + i) == 200;
+    const long long ct = __ldg(log.completion_tokens + i);
+    s_st = fmin(s_st, st);
+    auto take = [&](int c, bool mem, double v) {
+      if (mem) {
+        const uint64_t key = kvm_key(v);
+        s_inv[c] = ~key > s_inv[c] ? ~key : s_inv[c];
+        s_mx[c] = key > s_mx[c] ? key : s_mx[c];
+      }
+    };
+    take(KVM_COL_LAT, ok && la == la, la);
+    take(KVM_COL_TTFB, ok && tf == tf, tf);
+    take(KVM_COL_TLLT, ok && tl == tl, tl);
+    const bool gen = ok && tf == tf && tl == tl && ct > 0;
+    const double g = tl - tf;
+    take(KVM_COL_GEN, gen && g == g, g);
+    const double pt = g / (double)ct;
+    take(KVM_COL_PERTOK, gen && g == g && pt == pt, pt);
+  }
+}
 
-  // ---- sample: 512 rows, the same in every CTA
+// A shard's sample record, for the ranks to agree on one hull before the pass (sharded logs).
+__global__ void __launch_bounds__(512) fused_sample_kernel(kvm_request_log log, unsigned long long* __restrict__ record) {
+  __shared__ unsigned long long r_inv[16][NC], r_mx[16][NC];
+  __shared__ double r_st[16];
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   uint64_t s_inv[NC], s_mx[NC];
   double s_st = __longlong_as_double(0x7ff0000000000000ll);
 #pragma unroll
@@ -121,36 +153,75 @@ log_fused_kernel(kvm_request_log log, const double* __restrict__ cold_lo_g, cons
     s_inv[c] = 0ull;
     s_mx[c] = 0ull;
   }
-  {
-    const int64_t win = n < 4096 ? n : 4096;
-    for (int sidx = t; sidx < 512; sidx += FU_THREADS) {
-      const int64_t region = sidx >> 5;
-      const int64_t off = n > win ? region * ((n - win) / 15) : 0;
-      int64_t i = off + (int64_t)(((uint32_t)sidx * 2654435761u >> 7) % (uint32_t)win);
-      if (sidx == 0) i = 0;
-      if (sidx == 511) i = n - 1;
-      const double la = __ldg(log.latency_ms + i), tf = __ldg(log.ttfb_ms + i), tl = __ldg(log.tllt_ms + i);
-      const double st = __ldg(log.start_ms + i);
-      const bool ok = __ldg(log.status + i) == 200;
-      const long long ct = __ldg(log.completion_tokens + i);
-      s_st = fmin(s_st, st);
-      auto take = [&](int c, bool mem, double v) {
-        if (mem) {
-          const uint64_t key = kvm_key(v);
-          s_inv[c] = ~key > s_inv[c] ? ~key : s_inv[c];
-          s_mx[c] = key > s_mx[c] ? key : s_mx[c];
-        }
-      };
-      take(KVM_COL_LAT, ok && la == la, la);
-      take(KVM_COL_TTFB, ok && tf == tf, tf);
-      take(KVM_COL_TLLT, ok && tl == tl, tl);
-      const bool gen = ok && tf == tf && tl == tl && ct > 0;
-      const double g = tl - tf;
-      take(KVM_COL_GEN, gen && g == g, g);
-      const double pt = g / (double)ct;
-      take(KVM_COL_PERTOK, gen && g == g && pt == pt, pt);
+  fused_sample_rows(log, t, 512, s_inv, s_mx, s_st);
+#pragma unroll
+  for (int c = 0; c < NC; ++c) {
+    const uint64_t a = kvm_warp_max(s_inv[c]), b = kvm_warp_max(s_mx[c]);
+    if (lane == 0) {
+      r_inv[warp][c] = a;
+      r_mx[warp][c] = b;
     }
   }
+#pragma unroll
+  for (int m = 16; m; m >>= 1) s_st = fmin(s_st, __shfl_xor_sync(KVM_FULL, s_st, m));
+  if (lane == 0) r_st[warp] = s_st;
+  __syncthreads();
+  if (t < NC) {
+    unsigned long long inv = 0, mx = 0;
+    for (int w = 0; w < 16; ++w) {
+      inv = r_inv[w][t] > inv ? r_inv[w][t] : inv;
+      mx = r_mx[w][t] > mx ? r_mx[w][t] : mx;
+    }
+    record[t] = inv;
+    record[NC + t] = mx;
+  }
+  if (t == 32) {
+    double s0 = r_st[0];
+    for (int w = 1; w < 16; ++w) s0 = fmin(s0, r_st[w]);
+    record[2 * NC] = (unsigned long long)__double_as_longlong(s0);
+  }
+}
+
+// records of all ranks (stride words apart) -> the hull every rank's pass uses
+__global__ void fused_preset_combine_kernel(const unsigned long long* __restrict__ records, int world, int64_t stride,
+                                            unsigned long long* __restrict__ preset) {
+  const int t = threadIdx.x;
+  if (t < 2 * NC) {
+    unsigned long long a = 0;
+    for (int r = 0; r < world; ++r) {
+      const unsigned long long v = records[(size_t)r * stride + t];
+      a = v > a ? v : a;
+    }
+    preset[t] = a;
+  } else if (t == 2 * NC) {
+    double s0 = __longlong_as_double(0x7ff0000000000000ll);
+    for (int r = 0; r < world; ++r) s0 = fmin(s0, __longlong_as_double((long long)records[(size_t)r * stride + t]));
+    preset[t] = (unsigned long long)__double_as_longlong(s0);
+  }
+}
+
+template <bool COLD_SMEM_TABLE, bool SERIES>
+__global__ void __launch_bounds__(FU_THREADS, 2)
+log_fused_kernel(kvm_request_log log, const double* __restrict__ cold_lo_g, const double* __restrict__ cold_hi_g,
+                 int nc, uint8_t* __restrict__ flags, uint64_t* __restrict__ recs, kvm_log_stats* __restrict__ out,
+                 FusedWs* fws, SelWs* ws, FusedSeries sa, const unsigned long long* __restrict__ preset, int vec) {
+  extern __shared__ __align__(16) unsigned char fraw[];
+  uint32_t* sh = reinterpret_cast<uint32_t*>(fraw);   // [KVM_LOG_NSETS][BINS]
+  FusedSmem& S = *reinterpret_cast<FusedSmem*>(fraw + sizeof(uint32_t) * KVM_LOG_NSETS * BINS);
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const int64_t n = log.n;
+
+  // ---- sample: 512 rows, the same in every CTA (or, for a sharded log, the hull that all ranks
+  // have agreed on before the pass: `preset`)
+  uint64_t s_inv[NC], s_mx[NC];
+  double s_st = __longlong_as_double(0x7ff0000000000000ll);
+  const bool use_preset = preset != nullptr;
+#pragma unroll
+  for (int c = 0; c < NC; ++c) {
+    s_inv[c] = 0ull;
+    s_mx[c] = 0ull;
+  }
+  if (!use_preset) fused_sample_rows(log, t, FU_THREADS, s_inv, s_mx, s_st);
   // (shared memory set-up overlaps the sample's loads)
   for (int i = t; i < KVM_LOG_NSETS * BINS; i += FU_THREADS) sh[i] = 0;
   ColdTable cold{COLD_SMEM_TABLE ? S.cold_lo : cold_lo_g, COLD_SMEM_TABLE ? S.cold_hi : cold_hi_g, nc};
@@ -174,9 +245,14 @@ log_fused_kernel(kvm_request_log log, const double* __restrict__ cold_lo_g, cons
   __syncthreads();
   if (t < NC) {
     uint64_t inv = 0, mx = 0;
-    for (int w = 0; w < FU_WARPS; ++w) {
-      inv = S.s_inv[w][t] > inv ? S.s_inv[w][t] : inv;
-      mx = S.s_max[w][t] > mx ? S.s_max[w][t] : mx;
+    if (use_preset) {
+      inv = preset[t];
+      mx = preset[NC + t];
+    } else {
+      for (int w = 0; w < FU_WARPS; ++w) {
+        inv = S.s_inv[w][t] > inv ? S.s_inv[w][t] : inv;
+        mx = S.s_max[w][t] > mx ? S.s_max[w][t] : mx;
+      }
     }
     ColParam cp;
     if (inv == 0ull) {   // no member of this column in the sample: coarse bins over all keys
@@ -202,6 +278,7 @@ log_fused_kernel(kvm_request_log log, const double* __restrict__ cold_lo_g, cons
   if (t == 32) {
     double s0 = S.s_start[0];
     for (int w = 1; w < FU_WARPS; ++w) s0 = fmin(s0, S.s_start[w]);
+    if (use_preset) s0 = __longlong_as_double((long long)preset[2 * NC]);
     S.series_ref = s0;
     if (SERIES && blockIdx.x == 0) sa.dropped[2] = (unsigned long long)__double_as_longlong(s0);
   }
@@ -308,7 +385,19 @@ log_fused_kernel(kvm_request_log log, const double* __restrict__ cold_lo_g, cons
   };
 
   // ---- the stream: two consecutive rows per thread and iteration, one 128-bit load per column
-  const int64_t npairs = n >> 1;
+  // (a shard cut at an odd row has columns that are only 8-byte aligned: one row per thread then)
+  if (!vec) {
+    for (int64_t i = (int64_t)blockIdx.x * FU_THREADS + t; i < n; i += (int64_t)gridDim.x * FU_THREADS) {
+      uint32_t f;
+      const double st = kvm_ld1(log.start_ms + i);
+      const long long ct = kvm_ld1(log.completion_tokens + i);
+      recs[i] = row_fast(st, kvm_ld1(log.latency_ms + i), kvm_ld1(log.ttfb_ms + i), kvm_ld1(log.tllt_ms + i),
+                         kvm_ld1(log.status + i), ct, kvm_ld1(log.total_tokens + i), f);
+      flags[i] = (uint8_t)f;
+      if (SERIES) series_row(sbin(st), f & KVM_F_SUCCESS, ct);
+    }
+  }
+  const int64_t npairs = vec ? (n >> 1) : 0;
   for (int64_t base = (int64_t)blockIdx.x * FU_THREADS + (t & ~31); base < npairs;
        base += (int64_t)gridDim.x * FU_THREADS) {
     const int64_t u = base + lane;
@@ -360,7 +449,7 @@ log_fused_kernel(kvm_request_log log, const double* __restrict__ cold_lo_g, cons
       }
     }
   }
-  if (blockIdx.x == 0 && t < (int)(n & 1)) {   // tail row
+  if (vec && blockIdx.x == 0 && t < (int)(n & 1)) {   // tail row
     const int64_t i = (n & ~1ll) + t;
     uint32_t f;
     const uint64_t r = row_fast(log.start_ms[i], log.latency_ms[i], log.ttfb_ms[i], log.tllt_ms[i], log.status[i],
@@ -494,11 +583,55 @@ extern "C" size_t kvm_log_analyze_fused_scan_workspace_bytes(void) {
   return fused_partials_bytes() + 2 * sizeof(double) * (size_t)FU_MAX_COLD;
 }
 
+static int fused_pass_impl(const kvm_request_log* log, const double* cold_times, int32_t n_cold,
+                           double cold_window_s, uint8_t* flags, kvm_log_stats* stats,
+                           const kvm_log_extras* extras, void* scan_workspace, size_t scan_workspace_bytes,
+                           void* select_workspace, size_t select_workspace_bytes, int64_t arena_capacity,
+                           const unsigned long long* preset, void* stream);
+
 extern "C" int kvm_log_fused_pass(const kvm_request_log* log, const double* cold_times, int32_t n_cold,
                                   double cold_window_s, uint8_t* flags, kvm_log_stats* stats,
                                   const kvm_log_extras* extras, void* scan_workspace, size_t scan_workspace_bytes,
                                   void* select_workspace, size_t select_workspace_bytes, int64_t arena_capacity,
                                   void* stream) {
+  return fused_pass_impl(log, cold_times, n_cold, cold_window_s, flags, stats, extras, scan_workspace,
+                         scan_workspace_bytes, select_workspace, select_workspace_bytes, arena_capacity, nullptr, stream);
+}
+
+extern "C" int32_t kvm_log_fused_preset_words(void) { return FU_PRESET_WORDS; }
+
+extern "C" int kvm_log_fused_sample(const kvm_request_log* log, uint64_t* record, void* stream) {
+  KVM_REQUIRE(log && record && log->n >= 0, "kvm_log_fused_sample: bad argument");
+  fused_sample_kernel<<<1, 512, 0, (cudaStream_t)stream>>>(*log, reinterpret_cast<unsigned long long*>(record));
+  KVM_CUDA_CHECK(cudaGetLastError());
+  return KVM_OK;
+}
+
+extern "C" int kvm_log_fused_preset_combine(const uint64_t* records, int32_t world, int64_t stride_words,
+                                            uint64_t* preset, void* stream) {
+  KVM_REQUIRE(records && preset && world >= 1 && stride_words >= FU_PRESET_WORDS, "kvm_log_fused_preset_combine: bad argument");
+  fused_preset_combine_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(
+      reinterpret_cast<const unsigned long long*>(records), world, stride_words, reinterpret_cast<unsigned long long*>(preset));
+  KVM_CUDA_CHECK(cudaGetLastError());
+  return KVM_OK;
+}
+
+extern "C" int kvm_log_fused_pass_preset(const kvm_request_log* log, const double* cold_times, int32_t n_cold,
+                                         double cold_window_s, uint8_t* flags, kvm_log_stats* stats,
+                                         const kvm_log_extras* extras, void* scan_workspace, size_t scan_workspace_bytes,
+                                         void* select_workspace, size_t select_workspace_bytes, int64_t arena_capacity,
+                                         const uint64_t* preset, void* stream) {
+  KVM_REQUIRE(preset, "kvm_log_fused_pass_preset: preset is null");
+  return fused_pass_impl(log, cold_times, n_cold, cold_window_s, flags, stats, extras, scan_workspace,
+                         scan_workspace_bytes, select_workspace, select_workspace_bytes, arena_capacity,
+                         reinterpret_cast<const unsigned long long*>(preset), stream);
+}
+
+static int fused_pass_impl(const kvm_request_log* log, const double* cold_times, int32_t n_cold,
+                           double cold_window_s, uint8_t* flags, kvm_log_stats* stats,
+                           const kvm_log_extras* extras, void* scan_workspace, size_t scan_workspace_bytes,
+                           void* select_workspace, size_t select_workspace_bytes, int64_t arena_capacity,
+                           const unsigned long long* preset, void* stream) {
   KVM_REQUIRE(log && flags && stats && extras && scan_workspace && select_workspace,
               "kvm_log_analyze_fused: null argument");
   KVM_REQUIRE(log->n >= 0 && n_cold >= 0 && (n_cold == 0 || cold_times), "kvm_log_analyze_fused: bad sizes");
@@ -510,10 +643,10 @@ extern "C" int kvm_log_fused_pass(const kvm_request_log* log, const double* cold
                 "kvm_log_analyze_fused: series requested without buffers");
   // the one-pass kernel streams with 128-bit loads: every column 16-byte aligned (whole logs are;
   // a shard cut at an odd row is not - the caller then uses the two-pass entry points)
-  if (!(aligned_to(log->start_ms, 16) && aligned_to(log->latency_ms, 16) && aligned_to(log->ttfb_ms, 16) &&
-        aligned_to(log->tllt_ms, 16) && aligned_to(log->status, 16) && aligned_to(log->completion_tokens, 16) &&
-        aligned_to(log->total_tokens, 16) && aligned_to(flags, 2) && aligned_to(extras->digit_records, 16)) ||
-      log->n < 1) {
+  const int vec = aligned_to(log->start_ms, 16) && aligned_to(log->latency_ms, 16) && aligned_to(log->ttfb_ms, 16) &&
+                  aligned_to(log->tllt_ms, 16) && aligned_to(log->status, 16) && aligned_to(log->completion_tokens, 16) &&
+                  aligned_to(log->total_tokens, 16) && aligned_to(flags, 2) && aligned_to(extras->digit_records, 16);
+  if ((!vec && !preset) || (log->n < 1 && !preset)) {
     kvm_set_error("kvm_log_analyze_fused: needs a non-empty log with 16-byte aligned columns; use kvm_log_scan + kvm_log_select");
     return KVM_ERR_UNSUPPORTED;
   }
@@ -567,7 +700,7 @@ extern "C" int kvm_log_fused_pass(const kvm_request_log* log, const double* cold
     KVM_CUDA_CHECK(cudaFuncSetAttribute((const void*)log_fused_kernel<T, S>,                                   \
                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));              \
     KVM_CUDA_CHECK(cudaLaunchKernelEx(&cfg, log_fused_kernel<T, S>, *log, lo_c, hi_c, (int)n_cold, flags, recs, \
-                                      stats, fws, ws, sa));                                                    \
+                                      stats, fws, ws, sa, preset, vec));                                                    \
   } while (0)
   if (smem_table && series) KVM_LAUNCH_FUSED(true, true);
   else if (smem_table) KVM_LAUNCH_FUSED(true, false);

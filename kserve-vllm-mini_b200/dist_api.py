@@ -108,7 +108,7 @@ class PeerFabric:
     hist..series are accumulators the peers add into: zeroed by the owner at the start of a step."""
 
     def __init__(self, device: torch.device, group, world: int, rank: int, stats_words: int, hist_words: int,
-                 hist2_words: int, series_cap: int, post_words: int, slot_keys: int):
+                 hist2_words: int, series_cap: int, post_words: int, slot_keys: int, sample_words: int = 16):
         import torch.distributed._symmetric_memory as symm
         lib = N.lib()
         self.world, self.rank = world, rank
@@ -119,6 +119,8 @@ class PeerFabric:
         off = _align(off + int(lib.kvm_peer_flag_bytes()))
         self.stats_off, self.stats_stride = off, 8 * stats_words
         off = _align(off + world * self.stats_stride)
+        self.sample_off, self.sample_stride = off, 8 * sample_words   # sample records of the one-pass form
+        off = _align(off + world * self.sample_stride)
         self.hist_off = off
         off = _align(off + 8 * hist_words)
         self.hist2_off = off
@@ -202,6 +204,9 @@ class ShardedAnalyzer(engine.LogAnalyzer):
         self._gather_n = self.GATHER_KEYS
         self._arena_all: Optional[torch.Tensor] = None
         self._hist_glob = torch.zeros(N.KVM_MAX_HISTS * N.KVM_HIST_MAX_BINS, dtype=torch.int64, device=dev)
+        pw = int(self.lib.kvm_log_fused_preset_words())
+        self._sample_local = torch.zeros(pw, dtype=torch.int64, device=dev)
+        self._preset_d = torch.zeros(pw, dtype=torch.int64, device=dev)
         # a refine round costs about one more 9 B/row pass and shrinks the candidate exchange
         # (world x candidates x 8 B into every rank) and the finish to almost nothing; measured on
         # 2 x 1e7 rows it already pays at 64K candidates (profiles/r1_scaling.md)
@@ -234,7 +239,7 @@ class ShardedAnalyzer(engine.LogAnalyzer):
             self._fabric = PeerFabric(self.device, self.group, self.world, self.rank,
                                       int(self.lib.kvm_log_stats_pack_words()), N.KVM_MAX_SETS * self._bins,
                                       int(self.lib.kvm_select_hist2_words()), max(cap, 1), self._post_words,
-                                      self._fabric_slot)
+                                      self._fabric_slot, int(self.lib.kvm_log_fused_preset_words()))
             self._peer_err_h = torch.zeros(1, dtype=torch.int64).pin_memory()
         except Exception as exc:   # no symmetric memory on this node / torch build
             if self.exchange == "peer":
@@ -252,13 +257,16 @@ class ShardedAnalyzer(engine.LogAnalyzer):
         # accumulators the peers add into: cleared before this rank's first barrier of the step -
         # the peers' adds of this step start only after they have passed that barrier
         fb.zero_view.zero_()
-        self._launch_scan(dlog, cold_times)
-        N.check(lib.kvm_log_stats_pack_words_into(self._stats_ptr, self._pack_local.data_ptr(), st))
-        with tm.stage("exchange_stats"):
-            fb.put(self._pack_local.data_ptr(), fb.stats_stride, fb.stats_off + rank * fb.stats_stride, st)
-            fb.barrier(st)
-        N.check(lib.kvm_log_stats_combine(self._stats_ptr, fb.base + fb.stats_off, world, st))
-        self.launches += 4
+        fused = bool(self.use_fused) and not getattr(self, "_fused_off", False)
+        self.last_path = "fused" if fused else "two-pass"
+        if not fused:
+            self._launch_scan(dlog, cold_times)
+            N.check(lib.kvm_log_stats_pack_words_into(self._stats_ptr, self._pack_local.data_ptr(), st))
+            with tm.stage("exchange_stats"):
+                fb.put(self._pack_local.data_ptr(), fb.stats_stride, fb.stats_off + rank * fb.stats_stride, st)
+                fb.barrier(st)
+            N.check(lib.kvm_log_stats_combine(self._stats_ptr, fb.base + fb.stats_off, world, st))
+            self.launches += 4
         extras = N.LogExtrasC()
         if want_series:
             extras.series_window_ms = float(series_window_s) * 1000.0
@@ -277,17 +285,46 @@ class ShardedAnalyzer(engine.LogAnalyzer):
             self._views[vk] = views
         hist, _, offsets, hist2 = views
         rounds = self._refine_rounds(dlog.n)
-        with tm.stage("select_plan"):
-            N.check(lib.kvm_select_plan_refine(self._stats_ptr + N.LogStatsC.sets.offset, queries, nq,
-                                               C.byref(hspec), ws, self._sel_ws.numel(), arena, rounds,
-                                               int(self.refine_min_keys), st), "kvm_select_plan")
-        with tm.stage("select_hist"):
-            N.check(lib.kvm_log_select_hist(C.byref(log_c), fl, self._stats_ptr, C.byref(extras), ws, st),
-                    "kvm_log_select_hist")
-        with tm.stage("exchange_hist"):
-            fb.add(hist.data_ptr(), hist.numel(), fb.hist_off, st)
-            fb.barrier(st)
-            hist.copy_(fb.hist, non_blocking=True)
+        if fused:
+            # one-pass form: the ranks first agree on the digit parameters (a 512-row sample per
+            # shard, 88 bytes exchanged), then ONE pass per shard produces statistics AND histograms,
+            # which travel together: two exchange points instead of the two-pass form's three
+            cold_d, nc = self._cold_device(cold_times)
+            N.check(lib.kvm_log_fused_sample(C.byref(log_c), self._sample_local.data_ptr(), st), "kvm_log_fused_sample")
+            with tm.stage("exchange_sample"):
+                fb.put(self._sample_local.data_ptr(), fb.sample_stride, fb.sample_off + rank * fb.sample_stride, st)
+                fb.barrier(st)
+            N.check(lib.kvm_log_fused_preset_combine(fb.base + fb.sample_off, world, fb.sample_stride // 8,
+                                                     self._preset_d.data_ptr(), st), "kvm_log_fused_preset_combine")
+            with tm.stage("log_fused"):
+                N.check(lib.kvm_log_fused_pass_preset(C.byref(log_c), cold_d.data_ptr(), nc, 30.0, fl, self._stats_ptr,
+                                                      C.byref(extras), self._scan_ws.data_ptr(), self._scan_ws.numel(),
+                                                      ws, self._sel_ws.numel(), arena, self._preset_d.data_ptr(), st),
+                        "kvm_log_fused_pass_preset")
+            N.check(lib.kvm_log_stats_pack_words_into(self._stats_ptr, self._pack_local.data_ptr(), st))
+            with tm.stage("exchange_hist"):
+                fb.put(self._pack_local.data_ptr(), fb.stats_stride, fb.stats_off + rank * fb.stats_stride, st)
+                fb.add(hist.data_ptr(), hist.numel(), fb.hist_off, st)
+                fb.barrier(st)
+                hist.copy_(fb.hist, non_blocking=True)
+            N.check(lib.kvm_log_stats_combine(self._stats_ptr, fb.base + fb.stats_off, world, st))
+            with tm.stage("select_plan"):
+                N.check(lib.kvm_select_plan_preset(self._stats_ptr + N.LogStatsC.sets.offset, queries, nq,
+                                                   C.byref(hspec), ws, self._sel_ws.numel(), arena, rounds,
+                                                   int(self.refine_min_keys), st), "kvm_select_plan_preset")
+            self.launches += 9
+        else:
+            with tm.stage("select_plan"):
+                N.check(lib.kvm_select_plan_refine(self._stats_ptr + N.LogStatsC.sets.offset, queries, nq,
+                                                   C.byref(hspec), ws, self._sel_ws.numel(), arena, rounds,
+                                                   int(self.refine_min_keys), st), "kvm_select_plan")
+            with tm.stage("select_hist"):
+                N.check(lib.kvm_log_select_hist(C.byref(log_c), fl, self._stats_ptr, C.byref(extras), ws, st),
+                        "kvm_log_select_hist")
+            with tm.stage("exchange_hist"):
+                fb.add(hist.data_ptr(), hist.numel(), fb.hist_off, st)
+                fb.barrier(st)
+                hist.copy_(fb.hist, non_blocking=True)
         with tm.stage("select_resolve"):
             N.check(lib.kvm_select_resolve(ws, st), "kvm_select_resolve")
         self.launches += 2
@@ -428,6 +465,7 @@ class ShardedAnalyzer(engine.LogAnalyzer):
                tuple(sorted(float(c) for c in cold_times)), hspec.num_bins, series_window_s, id(queries), arena,
                self._sel_ws.data_ptr(), self._flags.data_ptr(), self._gather_n,
                self._refine_rounds(dlog.n), self.refine_min_keys,
+               bool(self.use_fused) and not getattr(self, "_fused_off", False),
                self._fabric.base if self._fabric is not None else 0,
                self._series_d.data_ptr() if want_series else 0,
                self._arena_all.data_ptr() if self._arena_all is not None else 0)
@@ -441,10 +479,11 @@ class ShardedAnalyzer(engine.LogAnalyzer):
                 self._enqueue_sharded(dlog, cold_times, queries, nq, hspec, want_series, series_window_s, arena, log_c)
             if len(self._graphs) >= 4:
                 self._graphs.pop(next(iter(self._graphs)))
-            entry = (g, self.launches)
+            entry = (g, self.launches, self.last_path)
             self._graphs[key] = entry
         entry[0].replay()
         self.launches = entry[1]
+        self.last_path = entry[2]
 
     def analyze_async(self, dlog: engine.DeviceLog, cold_times: Sequence[float] = (), num_bins: int = 20,
                       series_window_s: Optional[float] = 1.0, max_series_bins: int = 1 << 24,
@@ -527,6 +566,19 @@ class ShardedAnalyzer(engine.LogAnalyzer):
                     submit()
                     continue
                 series = None
+                if (want_series and self.last_path == "fused" and self._fabric is not None and n_global > 0
+                        and not math.isnan(stats.min_start_ms)
+                        and np.frombuffer(out, dtype=np.float64, count=1, offset=self._OFF_DROPPED + 16)[0]
+                        != stats.min_start_ms):
+                    # the one-pass kernels binned the series relative to the minimum of the ranks' samples,
+                    # which is not the log's minimum (rows out of time order): every rank sees the same
+                    # two global numbers and redoes the analysis with the two-pass form
+                    self._fused_off = True
+                    try:
+                        submit()
+                    finally:
+                        self._fused_off = False
+                    continue
                 if want_series and n_global > 0 and not math.isnan(stats.min_start_ms):
                     t0, t1 = stats.min_start_ms / 1000.0, stats.max_end_ms / 1000.0
                     nb = max(1, int(math.ceil((t1 - t0) / series_window_s)) + 1)
