@@ -483,6 +483,7 @@ __global__ void __launch_bounds__(RES_THREADS, 1) select_resolve_kernel(SelWs* w
     }
     // two-level walk: 64 group totals (2 per lane) locate the 32-bin group, one scan finishes
     int64_t g0 = 0, g1 = 0;
+    #pragma unroll 1
     for (int b = 0; b < nsets; ++b)
       if ((mask >> b) & 1u) {
         g0 += gsum[b][lane];
@@ -507,6 +508,7 @@ __global__ void __launch_bounds__(RES_THREADS, 1) select_resolve_kernel(SelWs* w
       const int64_t before = h0 ? __shfl_sync(KVM_FULL, i0 - g0, gl) : __shfl_sync(KVM_FULL, i1 - g1, gl);
       const int base = grp * 32;
       int64_t c = 0;
+      #pragma unroll 1
       for (int b = 0; b < nsets; ++b)
         if ((mask >> b) & 1u) c += (int64_t)hs[b * BINS + base + lane];
       int64_t incl = c;
@@ -570,6 +572,7 @@ __global__ void __launch_bounds__(RES_THREADS, 1) select_resolve_kernel(SelWs* w
   if (t < MAXQ) {
     const uint64_t k = bkey[t];
     int first = k != ~0ull;
+    #pragma unroll 1
     for (int o = 0; o < t && first; ++o) first = bkey[o] != k;
     is_first[t] = first;
   }
@@ -579,6 +582,7 @@ __global__ void __launch_bounds__(RES_THREADS, 1) select_resolve_kernel(SelWs* w
     int pos = 0;
     int64_t off = 0;
     if (k != ~0ull)
+      #pragma unroll 1
       for (int o = 0; o < MAXQ; ++o)
         if (is_first[o] && bkey[o] < k) {
           ++pos;
@@ -590,6 +594,7 @@ __global__ void __launch_bounds__(RES_THREADS, 1) select_resolve_kernel(SelWs* w
   if (t == 0) {
     int nb = 0;
     int64_t used = 0;
+    #pragma unroll 1
     for (int o = 0; o < MAXQ; ++o)
       if (is_first[o]) {
         ++nb;
@@ -605,6 +610,7 @@ __global__ void __launch_bounds__(RES_THREADS, 1) select_resolve_kernel(SelWs* w
     const uint64_t k = bkey[t];
     // (col, bin) group: first bucket of the group carries the group's length
     int smaller_same = 0, group = 0;
+    #pragma unroll 1
     for (int o = 0; o < MAXQ; ++o)
       if (is_first[o] && (bkey[o] >> 32) == (k >> 32)) {
         ++group;
@@ -772,6 +778,7 @@ __global__ void __launch_bounds__(REF_THREADS, 1) select_refine_kernel(SelWs* ws
   if (t < MAXQ) {
     const uint64_t k = bkey[t];
     int first = k != ~0ull;
+    #pragma unroll 1
     for (int o = 0; o < t && first; ++o) first = bkey[o] != k;
     is_first[t] = first;
   }
@@ -781,6 +788,7 @@ __global__ void __launch_bounds__(REF_THREADS, 1) select_refine_kernel(SelWs* ws
     int pos = 0;
     int64_t off = 0;
     if (k != ~0ull)
+      #pragma unroll 1
       for (int o = 0; o < MAXQ; ++o)
         if (is_first[o] && bkey[o] < k) {
           ++pos;
@@ -792,6 +800,7 @@ __global__ void __launch_bounds__(REF_THREADS, 1) select_refine_kernel(SelWs* ws
   if (t == 0) {
     int nb = 0;
     int64_t used = 0;
+    #pragma unroll 1
     for (int o = 0; o < MAXQ; ++o)
       if (is_first[o]) {
         ++nb;
@@ -819,6 +828,7 @@ __global__ void __launch_bounds__(REF_THREADS, 1) select_refine_kernel(SelWs* ws
   __syncthreads();
   if (t < MAXQ) {  // t as a level-1 bucket: the run of targets below it
     int first = 0, cnt = 0;
+    #pragma unroll 1
     for (int p = nb_s - 1; p >= 0; --p)
       if (newpar[p] == t) {
         first = p;
@@ -981,8 +991,8 @@ __device__ __forceinline__ void compact_hit(SelWs* ws, CompactSmem& S, uint64_t*
 // Warp-cooperative form of compact_hit for the drain phase: all 32 lanes call it (lanes
 // without an entry pass valid=false).  Lanes that append to the same bucket are merged with
 // __match_any_sync so that one shared-memory atomic reserves the slots of the whole group.
-__device__ __forceinline__ void compact_hits_warp(SelWs* ws, CompactSmem& S, uint64_t* __restrict__ arena,
-                                                  bool valid, int set, int col, uint32_t e, uint64_t key) {
+__device__ __noinline__ void compact_hits_warp(SelWs* ws, CompactSmem& S, uint64_t* __restrict__ arena,
+                                               bool valid, int set, int col, uint32_t e, uint64_t key) {
   const int lane = threadIdx.x & 31;
   const unsigned lt = (1u << lane) - 1u;
   const uint32_t j0 = valid ? (e & 0xffu) : 255u;
@@ -1029,9 +1039,12 @@ __device__ __forceinline__ void compact_hits_warp(SelWs* ws, CompactSmem& S, uin
 // merged with __match_any_sync so that one shared-memory atomic reserves the slots of the group;
 // keys in a fine bin with a histogram edge are also binned exactly.
 // PHASE 1 (refine): count the key's next 11 bits into the target's row of ws->hist2.
+// (kept OUT of line and the callers' column loops rolled: this code runs a few times per warp, and
+// five inlined copies of it made the kernel 19,000 instructions long - the profile showed as many
+// stall samples on fetching those once-executed instructions as in the streaming loop itself)
 template <int PHASE>
-__device__ __forceinline__ void target_hits_warp(SelWs* ws, CompactSmem& S, uint64_t* __restrict__ arena,
-                                                 bool valid, int set, int col, uint32_t e, uint64_t key) {
+__device__ __noinline__ void target_hits_warp(SelWs* ws, CompactSmem& S, uint64_t* __restrict__ arena,
+                                              bool valid, int set, int col, uint32_t e, uint64_t key) {
   const int lane = threadIdx.x & 31;
   const unsigned lt = (1u << lane) - 1u;
   const uint32_t j0 = valid ? (e & 0xffu) : 255u;
@@ -1320,7 +1333,7 @@ log_rec_kernel(kvm_request_log log, const uint8_t* __restrict__ flags,
         tf = log.ttfb_ms[r];
         tl = log.tllt_ms[r];
       }
-#pragma unroll
+#pragma unroll 1
       for (int c = 0; c < KVM_LOG_NCOLS; ++c) {
         const bool valid = (hm >> c) & 1u;
         if (!__any_sync(KVM_FULL, valid)) continue;
@@ -1440,6 +1453,7 @@ constexpr int FIN_BITS = 11;
 constexpr int FIN_BINS = 1 << FIN_BITS;
 constexpr int FIN_SMALL = 1024;  // candidates ranked by counting once this few remain
 constexpr int HIST_CTAS = 16;    // extra CTAs that assemble the value histograms
+constexpr int FIN_CACHE = 16384;  // bucket keys kept in shared memory (128 KB) by the finish
 
 // CTAs 0..MAXQ-1: one query each - radix select inside the query's bucket, FIN_BITS per pass,
 // switching to rank-by-counting in shared memory once <= FIN_SMALL candidates remain.
@@ -1504,6 +1518,31 @@ select_finish_kernel(SelWs* ws, SrcPack src, const int64_t* __restrict__ src_cou
   }
   const Bucket b = ws->bucket[s.bucket];
   const int64_t off = ws->bucket_offsets[s.bucket];
+  // The bucket's keys (all sources) are brought into shared memory once - every load of a thread
+  // in flight together - when they fit; the narrowing passes below then never go back to global
+  // memory (each pass used to cost several dependent round trips to L2).
+  extern __shared__ uint64_t kcache[];   // [FIN_CACHE]
+  __shared__ int cached_n;
+  {
+    int64_t tot = 0;
+    for (int sidx = 0; sidx < src.nsrc; ++sidx) {
+      const int64_t c = src_counts[(size_t)sidx * MAXQ + s.bucket];
+      tot += c < b.count ? c : b.count;
+    }
+    if (threadIdx.x == 0) cached_n = tot <= FIN_CACHE ? (int)tot : -1;
+    if (tot <= FIN_CACHE) {
+      int64_t base = 0;
+      for (int sidx = 0; sidx < src.nsrc; ++sidx) {
+        int64_t cnt = src_counts[(size_t)sidx * MAXQ + s.bucket];
+        cnt = cnt < b.count ? cnt : b.count;
+        const uint64_t* __restrict__ keys = src.arena[sidx] + off;
+        for (int64_t i = threadIdx.x; i < cnt; i += FIN_THREADS) kcache[base + i] = keys[i];
+        base += cnt;
+      }
+    }
+    __syncthreads();
+  }
+  const int ncache = cached_n;
   int rem = b.shift;        // unresolved low bits
   uint64_t prefix = 0;      // resolved part of (key - b.base) >> rem
   int64_t resid = s.resid;
@@ -1515,6 +1554,15 @@ select_finish_kernel(SelWs* ws, SrcPack src, const int64_t* __restrict__ src_cou
       // gather the survivors and rank by counting
       if (threadIdx.x == 0) small_n = 0;
       __syncthreads();
+      if (ncache >= 0) {
+        for (int i = threadIdx.x; i < ncache; i += FIN_THREADS) {
+          const uint64_t k = kcache[i];
+          if (shr64(k - b.base, rem) == prefix) {
+            const uint32_t p = atomicAdd(&small_n, 1u);
+            if (p < FIN_SMALL) small[p] = k;
+          }
+        }
+      } else
       for (int sidx = 0; sidx < src.nsrc; ++sidx) {
         const int64_t cnt = src_counts[(size_t)sidx * MAXQ + s.bucket];
         const uint64_t* __restrict__ keys = src.arena[sidx] + off;
@@ -1547,6 +1595,12 @@ select_finish_kernel(SelWs* ws, SrcPack src, const int64_t* __restrict__ src_cou
     const uint32_t dmask = (1u << take) - 1u;
     for (int i = threadIdx.x; i < FIN_BINS; i += FIN_THREADS) hist[i] = 0;
     __syncthreads();
+    if (ncache >= 0) {
+      for (int i = threadIdx.x; i < ncache; i += FIN_THREADS) {
+        const uint64_t low = kcache[i] - b.base;
+        if (shr64(low, rem) == prefix) atomicAdd(&hist[(uint32_t)(low >> sh) & dmask], 1u);
+      }
+    } else
     for (int sidx = 0; sidx < src.nsrc; ++sidx) {
       const int64_t cnt = src_counts[(size_t)sidx * MAXQ + s.bucket];
       const uint64_t* __restrict__ keys = src.arena[sidx] + off;
@@ -1886,8 +1940,12 @@ extern "C" int kvm_select_finish(void* workspace, const uint64_t* const* arenas,
   if (hist_counts)  // the assembling CTAs accumulate into it
     KVM_CUDA_CHECK(cudaMemsetAsync(hist_counts, 0, sizeof(int64_t) * KVM_MAX_HISTS * KVM_HIST_MAX_BINS,
                                    (cudaStream_t)stream));
-  select_finish_kernel<<<MAXQ + HIST_CTAS, FIN_THREADS, 0, (cudaStream_t)stream>>>(ws, sp, src_counts, results,
-                                                                          hist_counts);
+  {
+    const int rc = ensure_smem((const void*)select_finish_kernel, sizeof(uint64_t) * FIN_CACHE);
+    if (rc) return rc;
+  }
+  select_finish_kernel<<<MAXQ + HIST_CTAS, FIN_THREADS, sizeof(uint64_t) * FIN_CACHE, (cudaStream_t)stream>>>(
+      ws, sp, src_counts, results, hist_counts);
   KVM_CUDA_CHECK(cudaGetLastError());
   return KVM_OK;
 }
