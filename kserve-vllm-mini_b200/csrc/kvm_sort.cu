@@ -112,6 +112,15 @@ __global__ void __launch_bounds__(32 * NPASS) sort_plan_kernel(SortPlan* plan, i
   }
 }
 
+__device__ __forceinline__ uint32_t ld_status(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_status(uint32_t* p, uint32_t v) {
+  asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
 struct SortSmem {
   uint64_t keys[TILE];
   double vals[TILE];
@@ -189,19 +198,19 @@ sort_onesweep_kernel(int pass, const double* __restrict__ in_k, const double* __
       uint32_t* mine = status + (size_t)tile * RADIX + t;
       unsigned long long excl = 0;
       if (tile == 0) {
-        __stcg(mine, FLAG_PREFIX | run);
+        st_status(mine, FLAG_PREFIX | run);
       } else {
-        __stcg(mine, FLAG_AGG | run);
+        st_status(mine, FLAG_AGG | run);
         for (int64_t q = tile - 1; q >= 0; --q) {
           uint32_t v;
-          do {
-            v = __ldcg(status + (size_t)q * RADIX + t);
+          do {   // (a volatile load: a plain one lets the compiler assume the loop ends and read once)
+            v = ld_status(status + (size_t)q * RADIX + t);
           } while ((v >> 30) == 0u);
           excl += v & VALUE_MASK;
           if ((v >> 30) == 2u) break;
         }
         // the inclusive prefix may exceed 30 bits only when m >= 2^30: the entry point refuses that
-        __stcg(mine, FLAG_PREFIX | (uint32_t)(excl + run));
+        st_status(mine, FLAG_PREFIX | (uint32_t)(excl + run));
       }
       S.global_base[t] = plan->ghist[pass][t] + excl;
     }
