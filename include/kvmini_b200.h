@@ -532,20 +532,30 @@ int kvm_log_series(const kvm_request_log* log_host, const uint8_t* flags,
 /* ------------------------------------------------------------------ segmented (sweep) analysis */
 
 /* K4: the numeric core of analyze.py for `runs` independent logs stored back to back
- * (CSR: run r = rows [run_offsets[r], run_offsets[r+1])), one persistent CTA per run, all
- * intermediate state in shared memory.  Replaces the per-run loop of grid-sweep.sh:103-174
- * (one analyze.py process per run).  Per run it writes the same kvm_log_stats as kvm_log_scan,
- * the order statistics of the nq queries (results[run*nq + q]) and the four num_bins-bin
- * histograms (hist_counts[(run*4 + h)*num_bins + b]; h = ttfb, tllt, generation, per-token).
+ * (CSR: run r = rows [run_offsets[r], run_offsets[r+1])).  A persistent CTA takes one run at a
+ * time and reads its columns ONCE (sampled digit range, shared-memory histograms, one 8-byte
+ * digit record per row into `scratch`), then finds the candidates from the records; all other
+ * intermediate state stays in shared memory.  Replaces the per-run loop of
+ * grid-sweep.sh:103-174 (one analyze.py process per run).  Per run it writes the same
+ * kvm_log_stats as kvm_log_scan, the order statistics of the nq queries (results[run*nq + q])
+ * and the four num_bins-bin histograms (hist_counts[(run*4 + h)*num_bins + b]; h = ttfb, tllt,
+ * generation, per-token).
  * cold_offsets/cold_times: CSR of sorted cold-start times per run (cold_offsets NULL = none).
  * run_status[run] = 1 when the run's candidates did not fit on chip: analyse that run with
- * the flat entry points instead (stats[run] is still valid).  flags[n] is scratch + output.
- * No workspace; one launch; stream-ordered. */
+ * the flat entry points instead (stats[run] is still valid).  flags[n] is scratch + output;
+ * scratch: kvm_seg_analyze_scratch_bytes(n) bytes of device memory (contents undefined after).
+ * One launch; stream-ordered; allocates nothing. */
+size_t kvm_seg_analyze_scratch_bytes(int64_t n);
 int kvm_seg_analyze(const kvm_request_log* log_host, const int64_t* run_offsets, int64_t runs,
                     const int64_t* cold_offsets, const double* cold_times, double cold_window_s,
                     const kvm_query* queries_host, int32_t nq, int32_t num_bins, uint8_t* flags,
-                    kvm_log_stats* stats, kvm_query_result* results, int64_t* hist_counts,
-                    int32_t* run_status, void* stream);
+                    void* scratch, size_t scratch_bytes, kvm_log_stats* stats,
+                    kvm_query_result* results, int64_t* hist_counts, int32_t* run_status, void* stream);
+
+/* Debug aid: nanoseconds the segmented kernel spent per phase, summed over all runs and CTAs since
+ * the last reset - [0] sample + set-up, [1] stream, [2] plan / resolve, [3] records pass,
+ * [4] finish + emit.  Synchronises the device. */
+int kvm_seg_phase_times(uint64_t* out5, int32_t reset);
 
 /* ------------------------------------------------------------------ sort */
 

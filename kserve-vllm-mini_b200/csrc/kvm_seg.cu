@@ -1,44 +1,50 @@
 // kvm_seg.cu - K4: segmented run analysis for sweep roll-ups (BASELINE.json configs[2]:
-// 4096 runs x 250k requests).  One persistent CTA per run does the WHOLE analysis of that
-// run with all intermediate state in shared memory - no global histograms, no workspace,
-// no inter-CTA synchronisation:
+// 4096 runs x 250k requests).  One persistent CTA (two per SM) takes a run at a time and does the
+// WHOLE analysis of that run with all intermediate state in shared memory - no global
+// histograms, no inter-CTA synchronisation - reading the run's columns ONCE:
 //
-//   P1 scan      window, cold/warm, counts, token sums, key ranges           (56 B/row + 1 B flags)
-//   P2 plan      digit parameters per value column, rank of every query
-//   P3 hist      7 x 2048-bin digit histograms in shared memory              (33 B/row)
-//   P4 resolve   bin + residual rank per query, candidate buckets, 20-bin thresholds
-//   P5 compact   candidates -> shared-memory arena; rows whose fine bin holds a 20-bin
-//                edge are binned exactly                                      (33 B/row)
-//   P6 finish    each query: exact rank inside its bucket by counting (candidates on chip)
-//   P7 emit      stats, order statistics, 4 x num_bins histogram counts
+//   P0 sample    512 rows of the run -> digit parameters of every value column (kvm_fused_row.cuh)
+//   P1 stream    the one-pass row of kvm_fused.cu: window, cold/warm, counts, token sums, exact key
+//                ranges, 7 x 2048-bin digit histograms in shared memory; per row one flag byte
+//                and one 8-byte digit record leave the SM          (56 B/row read, 9 B/row written)
+//   P2 plan      statistics, rank of every query, 20-bin thresholds from the exact ranges
+//   P4 resolve   bin + residual rank per query, candidate buckets
+//   P5 20-bin    fine bins that hold no 20-bin edge are added wholesale; the shared-memory
+//                histograms are then dead and their space becomes the candidate arena
+//   P6 compact   second look at the run through its 9 B/row records only: rows whose digit
+//                falls into a candidate bucket or a fine bin with a 20-bin edge fetch their value
+//                (a few percent of the rows)
+//   P7 finish    each query: exact rank inside its bucket by counting (candidates on chip)
+//   P8 emit      stats, order statistics, 4 x num_bins histogram counts
 //
 // Replaces the per-run loop of grid-sweep.sh:103-174 (bench.sh -> analyze.py per run) for the
 // numeric core of analyze.py; semantics per row are the shared device functions of
-// kvm_log_device.cuh, so a run analysed here equals the same run through the flat kernels.
-// The 20-bin histograms are derived from the fine digit histogram: a fine bin that contains no
-// 20-bin edge lies inside one 20-bin (added wholesale in P7); only rows in the <= 4*(nb-1)
-// edge bins are binned one by one in P5.
+// kvm_log_device.cuh / kvm_fused_row.cuh, so a run analysed here equals the same run through the
+// flat kernels.  The digit parameters come from a sample, so the two end bins of a column are
+// catch-alls for keys outside the sampled hull: buckets are defined by DIGIT (not key range), and
+// an end bin that holds such keys is binned row by row for the 20-bin histograms.
 // Runs whose candidates do not fit the on-chip arena are flagged (status 1) and redone by the
 // host through the flat path; results stay exact either way.
-// HBM-bound: 123 B/row over three streaming phases.
+// HBM-bound by design: 56 B/row algorithmic; 74 B/row moved (records written and read back).
 
 #include "kvm_common.cuh"
 #include "kvm_log_device.cuh"
+#include "kvm_fused_row.cuh"
 
 namespace {
 
-constexpr int SEG_THREADS = 512;
+constexpr int SEG_THREADS = 384;      // x 2 CTAs per SM, like the flat one-pass kernel
 constexpr int SEG_WARPS = SEG_THREADS / 32;
-constexpr int SEG_ARENA = 12288;      // candidate keys kept on chip per run
+constexpr int SEG_ARENA = KVM_LOG_NSETS * BINS * 4 / 8;   // candidate keys per run: the space of the histograms
 constexpr int SEG_BUCKET_MAX = 2048;  // largest bucket finished by counting
 constexpr int SEG_COLD = 256;
+constexpr int SEG_HITQ = 64;
 constexpr int SEG_MAXQ = KVM_MAX_QUERIES;
 constexpr int SEG_NB_MAX = 64;
 constexpr int NH = 4;  // 20-bin histograms: ttfb, tllt, generation, per-token
 
 struct SegBucket {
-  uint64_t base;
-  int32_t shift, col;
+  int32_t col;
   uint32_t set_mask, bin;
   uint32_t count, offset;
 };
@@ -49,32 +55,31 @@ struct SegQ {
   int32_t status, bucket, col, resolved;
 };
 
-struct SegCol {
-  uint64_t kbase;
-  int32_t shift, width;
-};
-
 struct SegSmem {
-  uint32_t hist[KVM_LOG_NSETS][BINS];
-  uint64_t arena[SEG_ARENA];
+  uint32_t hist[KVM_LOG_NSETS * BINS];        // P1-P5; the candidate arena from P6 on
+  FusedCols fc;
   uint64_t red[SEG_WARPS][NSLOTS];
   uint64_t fin[NSLOTS];
+  unsigned long long s_inv[SEG_WARPS][NC], s_max[SEG_WARPS][NC];
   uint64_t thr[NH][SEG_NB_MAX];
   uint32_t edge[NH][SEG_NB_MAX];
   uint32_t cnt20[NH][SEG_NB_MAX];
   uint32_t flag20[NH][BINS / 32];
-  uint32_t bmap[KVM_LOG_NCOLS][BINS / 32];
+  uint32_t bmap[NC][BINS / 32];
+  uint32_t anyhit[NC][2 * BINS / 32];         // bmap | flag20, 4096 bits: a 12-bit record field indexes it unchecked
   double cold_lo[SEG_COLD];
   double cold_hi[SEG_COLD];
   SegBucket bk[SEG_MAXQ];
   SegQ q[SEG_MAXQ];
-  SegCol col[KVM_MAX_COLS];
   uint32_t q_bin[SEG_MAXQ];
   uint32_t q_cnt[SEG_MAXQ];
   uint32_t cursor[SEG_MAXQ];
   int32_t active20[NH];
+  int32_t impure[NC];                         // bit 0: keys below kbase exist, bit 1: keys beyond the last bin exist
   int32_t nbuckets;
   int32_t overflow;
+  uint32_t arena_used;
+  uint64_t hitq[SEG_WARPS][SEG_HITQ];          // P6: rows waiting for their value, per warp
   kvm_log_stats stats;
 };
 
@@ -89,70 +94,13 @@ __device__ __forceinline__ int col_hist(int col) {  // inverse of hist_col, -1 f
   return col == KVM_COL_TTFB ? 0 : col == KVM_COL_TLLT ? 1 : col == KVM_COL_GEN ? 2 : col == KVM_COL_PERTOK ? 3 : -1;
 }
 
-// rows [r0, r1) of the log: f(i, start, lat, ttfb, tllt, status, ctok, ttok)
-template <class F>
-__device__ __forceinline__ void seg_rows_full(const kvm_request_log& log, int64_t r0, int64_t r1, bool vec, F&& f) {
-  int64_t a = r0;
-  if (vec) {
-    if ((a & 1) && a < r1) {
-      if (threadIdx.x == 0)
-        f(a, log.start_ms[a], log.latency_ms[a], log.ttfb_ms[a], log.tllt_ms[a], log.status[a],
-          log.completion_tokens[a], log.total_tokens[a]);
-      ++a;
-    }
-    const int64_t npairs = (r1 - a) >> 1;
-    for (int64_t p = threadIdx.x; p < npairs; p += SEG_THREADS) {
-      const int64_t i = a + (p << 1);
-      const double2 st = kvm_ld2(log.start_ms + i), la = kvm_ld2(log.latency_ms + i);
-      const double2 tf = kvm_ld2(log.ttfb_ms + i), tl = kvm_ld2(log.tllt_ms + i);
-      const longlong2 ss = kvm_ld2(log.status + i), ct = kvm_ld2(log.completion_tokens + i);
-      const longlong2 tt = kvm_ld2(log.total_tokens + i);
-      f(i, st.x, la.x, tf.x, tl.x, ss.x, ct.x, tt.x);
-      f(i + 1, st.y, la.y, tf.y, tl.y, ss.y, ct.y, tt.y);
-    }
-    a += npairs << 1;
-    if (a < r1 && threadIdx.x == 0)
-      f(a, log.start_ms[a], log.latency_ms[a], log.ttfb_ms[a], log.tllt_ms[a], log.status[a],
-        log.completion_tokens[a], log.total_tokens[a]);
-  } else {
-    for (int64_t i = a + threadIdx.x; i < r1; i += SEG_THREADS)
-      f(i, kvm_ld1(log.start_ms + i), kvm_ld1(log.latency_ms + i), kvm_ld1(log.ttfb_ms + i),
-        kvm_ld1(log.tllt_ms + i), kvm_ld1(log.status + i), kvm_ld1(log.completion_tokens + i),
-        kvm_ld1(log.total_tokens + i));
-  }
-}
-
-// rows [r0, r1): f(flags, lat, ttfb, tllt, ctok) - the columns the select passes read
-template <class F>
-__device__ __forceinline__ void seg_rows_keys(const kvm_request_log& log, const uint8_t* __restrict__ flags,
-                                              int64_t r0, int64_t r1, bool vec, F&& f) {
-  int64_t a = r0;
-  if (vec) {
-    if ((a & 1) && a < r1) {
-      if (threadIdx.x == 0) f(flags[a], log.latency_ms[a], log.ttfb_ms[a], log.tllt_ms[a], log.completion_tokens[a]);
-      ++a;
-    }
-    const int64_t npairs = (r1 - a) >> 1;
-    for (int64_t p = threadIdx.x; p < npairs; p += SEG_THREADS) {
-      const int64_t i = a + (p << 1);
-      const uint16_t ff = *reinterpret_cast<const uint16_t*>(flags + i);
-      if (!((ff | (ff >> 8)) & KVM_F_SUCCESS)) continue;
-      const double2 la = kvm_ld2(log.latency_ms + i), tf = kvm_ld2(log.ttfb_ms + i);
-      const double2 tl = kvm_ld2(log.tllt_ms + i);
-      const longlong2 ct = kvm_ld2(log.completion_tokens + i);
-      f((uint8_t)(ff & 0xff), la.x, tf.x, tl.x, ct.x);
-      f((uint8_t)(ff >> 8), la.y, tf.y, tl.y, ct.y);
-    }
-    a += npairs << 1;
-    if (a < r1 && threadIdx.x == 0) f(flags[a], log.latency_ms[a], log.ttfb_ms[a], log.tllt_ms[a], log.completion_tokens[a]);
-  } else {
-    for (int64_t i = a + threadIdx.x; i < r1; i += SEG_THREADS) {
-      const uint8_t fl = flags[i];
-      if (!(fl & KVM_F_SUCCESS)) continue;
-      f(fl, kvm_ld1(log.latency_ms + i), kvm_ld1(log.ttfb_ms + i), kvm_ld1(log.tllt_ms + i),
-        kvm_ld1(log.completion_tokens + i));
-    }
-  }
+// Where the time of a run goes (debug aid): nanoseconds summed over all runs, per phase -
+// [0] sample + set-up, [1] stream, [2] plan / resolve / wholesale bins, [3] records pass, [4] finish + emit.
+__device__ unsigned long long seg_phase_ns[8];
+__device__ __forceinline__ unsigned long long seg_now() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
 }
 
 struct SegQueries {
@@ -160,22 +108,71 @@ struct SegQueries {
   int32_t nq;
 };
 
-__global__ void __launch_bounds__(SEG_THREADS, 1)
+// A row of P6 whose digit in column c is wanted: fetch the value, append it to the buckets it
+// belongs to and / or bin it exactly.  Out of line: a few percent of the rows come here.
+__device__ __noinline__ void seg_hit(SegSmem& S, const kvm_request_log& log, int64_t i, int c, uint32_t d,
+                                     uint32_t fl, int nb) {
+  const bool cold_row = fl & KVM_F_COLD;
+  double v;
+  int set;
+  if (c == KVM_COL_LAT) { v = __ldg(log.latency_ms + i); set = cold_row ? KVM_SET_LAT_COLD : KVM_SET_LAT_WARM; }
+  else if (c == KVM_COL_TTFB) { v = __ldg(log.ttfb_ms + i); set = cold_row ? KVM_SET_TTFB_COLD : KVM_SET_TTFB_WARM; }
+  else if (c == KVM_COL_TLLT) { v = __ldg(log.tllt_ms + i); set = KVM_SET_TLLT; }
+  else {
+    const double g = __ldg(log.tllt_ms + i) - __ldg(log.ttfb_ms + i);   // analyze.py:144
+    if (c == KVM_COL_GEN) { v = g; set = KVM_SET_GEN; }
+    else { v = g / (double)__ldg(log.completion_tokens + i); set = KVM_SET_PERTOK; }   // analyze.py:146
+  }
+  const uint64_t key = kvm_key(v);
+  uint64_t* arena = reinterpret_cast<uint64_t*>(S.hist);
+  if ((S.bmap[c][d >> 5] >> (d & 31)) & 1u) {
+    const int nbk = S.nbuckets;
+    for (int j = 0; j < nbk; ++j)
+      if (S.bk[j].col == c && S.bk[j].bin == d && ((S.bk[j].set_mask >> set) & 1u)) {
+        const uint32_t pos = atomicAdd(&S.cursor[j], 1u);
+        if (pos < S.bk[j].count) arena[S.bk[j].offset + pos] = key;
+      }
+  }
+  const int h = col_hist(c);
+  if (h >= 0 && ((S.flag20[h][d >> 5] >> (d & 31)) & 1u)) atomicAdd(&S.edge[h][bin_of(key, S.thr[h], nb)], 1u);
+}
+
+__global__ void __launch_bounds__(SEG_THREADS, 2)
 seg_analyze_kernel(kvm_request_log log, const int64_t* __restrict__ run_offsets, int64_t runs,
                    const int64_t* __restrict__ cold_offsets, const double* __restrict__ cold_times,
                    double cold_window, SegQueries qp, int nb, bool base_aligned,
-                   uint8_t* __restrict__ flags, kvm_log_stats* __restrict__ out_stats,
+                   uint8_t* __restrict__ flags, uint64_t* __restrict__ recs, kvm_log_stats* __restrict__ out_stats,
                    kvm_query_result* __restrict__ out_results, int64_t* __restrict__ out_hist,
                    int32_t* __restrict__ out_status) {
   extern __shared__ __align__(16) unsigned char seg_raw[];
   SegSmem& S = *reinterpret_cast<SegSmem*>(seg_raw);
+  uint32_t* sh = S.hist;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const double nan = __longlong_as_double(0x7ff8000000000000ll);
 
   for (int64_t run = blockIdx.x; run < runs; run += gridDim.x) {
     const int64_t r0 = run_offsets[run], r1 = run_offsets[run + 1];
-    const bool vec = base_aligned;
-    // ---------------- P1 scan
+    unsigned long long tp = tid == 0 ? seg_now() : 0ull;
+    auto phase = [&](int k) {   // after a __syncthreads
+      if (tid == 0) {
+        const unsigned long long now = seg_now();
+        atomicAdd(&seg_phase_ns[k], now - tp);
+        tp = now;
+      }
+    };
+    // ---------------- P0 sample + set-up
+    kvm_request_log sub = log;   // the run as a log of its own (sampling)
+    sub.start_ms += r0; sub.latency_ms += r0; sub.ttfb_ms += r0; sub.tllt_ms += r0;
+    sub.status += r0; sub.completion_tokens += r0; sub.total_tokens += r0;
+    sub.n = r1 - r0;
+    uint64_t s_inv[NC], s_mx[NC];
+    double s_st = 0.0;
+#pragma unroll
+    for (int c = 0; c < NC; ++c) {
+      s_inv[c] = 0ull;
+      s_mx[c] = 0ull;
+    }
+    fused_sample_rows(sub, tid, SEG_THREADS, s_inv, s_mx, s_st);
     ColdTable cold{S.cold_lo, S.cold_hi, 0};
     bool cold_too_many = false;
     if (cold_offsets) {
@@ -188,44 +185,111 @@ seg_analyze_kernel(kvm_request_log log, const int64_t* __restrict__ run_offsets,
           cold_interval(cold_times[c0 + i], cold_window, &S.cold_lo[i], &S.cold_hi[i]);
       }
     }
-    for (int i = tid; i < KVM_LOG_NSETS * BINS; i += SEG_THREADS) (&S.hist[0][0])[i] = 0;
+    for (int i = tid; i < KVM_LOG_NSETS * BINS / 4; i += SEG_THREADS) reinterpret_cast<uint4*>(sh)[i] = make_uint4(0, 0, 0, 0);
     for (int i = tid; i < NH * SEG_NB_MAX; i += SEG_THREADS) {
       (&S.edge[0][0])[i] = 0;
       (&S.cnt20[0][0])[i] = 0;
       (&S.thr[0][0])[i] = ~0ull;
     }
     for (int i = tid; i < NH * (BINS / 32); i += SEG_THREADS) (&S.flag20[0][0])[i] = 0;
-    for (int i = tid; i < KVM_LOG_NCOLS * (BINS / 32); i += SEG_THREADS) (&S.bmap[0][0])[i] = 0;
+    for (int i = tid; i < NC * (BINS / 32); i += SEG_THREADS) (&S.bmap[0][0])[i] = 0;
+    for (int i = tid; i < NC * (2 * BINS / 32); i += SEG_THREADS) (&S.anyhit[0][0])[i] = 0;
     if (tid < SEG_MAXQ) S.cursor[tid] = 0;
     if (tid == 0) {
       S.nbuckets = 0;
       S.overflow = 0;
     }
+#pragma unroll
+    for (int c = 0; c < NC; ++c) {
+      const uint64_t a = kvm_warp_max(s_inv[c]), b = kvm_warp_max(s_mx[c]);
+      if (lane == 0) {
+        S.s_inv[warp][c] = a;
+        S.s_max[warp][c] = b;
+      }
+    }
     __syncthreads();
+    if (tid < NC) {
+      uint64_t inv = 0, mx = 0;
+      for (int w = 0; w < SEG_WARPS; ++w) {
+        inv = S.s_inv[w][tid] > inv ? S.s_inv[w][tid] : inv;
+        mx = S.s_max[w][tid] > mx ? S.s_max[w][tid] : mx;
+      }
+      fused_cols_setup(S.fc, tid, inv, mx);
+    }
+    __syncthreads();
+    if (tid == 0) fused_cols_fast_params(S.fc);
+    __syncthreads();
+    phase(0);
 
-    LogAcc a;
+    // ---------------- P1 stream: two consecutive rows per thread, one 128-bit load per column
+    const double cold_first = cold.n > 0 ? cold.lo[0] : 0.0, cold_last = cold.n > 0 ? cold.hi[cold.n - 1] : -1.0;
+    FAcc a;
     a.init();
-    seg_rows_full(log, r0, r1, vec, [&](int64_t i, double st, double la, double tf, double tl, int64_t ss,
-                                        int64_t ct, int64_t tt) {
-      flags[i] = process_row(a, st, la, tf, tl, ss, ct, tt, cold, -1);
-    });
-    acc_warp_reduce(a, S.red[warp], lane);
+    auto one_row = [&](int64_t i) {
+      uint32_t f;
+      recs[i] = fused_row(a, S.fc, sh, cold, cold_first, cold_last, log.start_ms[i], log.latency_ms[i], log.ttfb_ms[i],
+                          log.tllt_ms[i], log.status[i], log.completion_tokens[i], log.total_tokens[i], f);
+      flags[i] = (uint8_t)f;
+    };
+    // columns are 16-byte aligned at even rows (base_aligned): an odd first / last row is peeled
+    const int64_t a0 = base_aligned ? r0 + (r0 & 1) : r1;
+    const int64_t npairs = a0 < r1 ? (r1 - a0) >> 1 : 0;
+    if (base_aligned) {
+      if (tid == 0 && a0 > r0 && r0 < r1) one_row(r0);
+      if (tid == 32 && a0 < r1 && ((r1 - a0) & 1)) one_row(r1 - 1);
+    } else {
+      for (int64_t i = r0 + tid; i < r1; i += SEG_THREADS) {
+        uint32_t f;
+        recs[i] = fused_row(a, S.fc, sh, cold, cold_first, cold_last, kvm_ld1(log.start_ms + i), kvm_ld1(log.latency_ms + i),
+                            kvm_ld1(log.ttfb_ms + i), kvm_ld1(log.tllt_ms + i), kvm_ld1(log.status + i),
+                            kvm_ld1(log.completion_tokens + i), kvm_ld1(log.total_tokens + i), f);
+        flags[i] = (uint8_t)f;
+      }
+    }
+    for (int64_t p = tid; p < npairs; p += SEG_THREADS) {
+      const int64_t i = a0 + (p << 1);
+      const double2 qs = kvm_ld2(log.start_ms + i), ql = kvm_ld2(log.latency_ms + i);
+      const double2 qf = kvm_ld2(log.ttfb_ms + i), qt = kvm_ld2(log.tllt_ms + i);
+      const longlong2 qx = kvm_ld2(log.status + i), qc = kvm_ld2(log.completion_tokens + i);
+      const longlong2 qo = kvm_ld2(log.total_tokens + i);
+      uint32_t f0, f1;
+      const uint64_t q0 = fused_row(a, S.fc, sh, cold, cold_first, cold_last, qs.x, ql.x, qf.x, qt.x, qx.x, qc.x, qo.x, f0);
+      const uint64_t q1 = fused_row(a, S.fc, sh, cold, cold_first, cold_last, qs.y, ql.y, qf.y, qt.y, qx.y, qc.y, qo.y, f1);
+      *reinterpret_cast<ulonglong2*>(recs + i) = make_ulonglong2(q0, q1);
+      *reinterpret_cast<uint16_t*>(flags + i) = (uint16_t)(f0 | (f1 << 8));
+    }
+    facc_warp_reduce(a, S.red[warp], lane);
+    __syncthreads();
+    phase(1);
+    // set counts = sums of the histograms
+    {
+      uint32_t setsum[KVM_LOG_NSETS];
+#pragma unroll
+      for (int s = 0; s < KVM_LOG_NSETS; ++s) {
+        setsum[s] = 0;
+        for (int b = tid; b < BINS; b += SEG_THREADS) setsum[s] += sh[s * BINS + b];
+      }
+#pragma unroll
+      for (int s = 0; s < KVM_LOG_NSETS; ++s) {
+        const uint32_t v = __reduce_add_sync(KVM_FULL, setsum[s]);
+        if (lane == 0) S.red[warp][S_CNT0 + s] = v;
+      }
+    }
     __syncthreads();
     if (tid < NMAX_END) {
-      uint64_t acc = S.red[0][tid];
-      for (int w = 1; w < SEG_WARPS; ++w) {
-        const uint64_t v = S.red[w][tid];
-        if (tid < NSUM) acc = (uint64_t)((int64_t)acc + (int64_t)v);
-        else if (tid < NMIN_END) acc = v < acc ? v : acc;
-        else acc = v > acc ? v : acc;
+      const int s = tid;
+      uint64_t acc;
+      if (s >= M_KMIN0 && s < M_KMIN0 + NC) acc = S.fc.kmin[s - M_KMIN0];
+      else if (s >= X_KMAX0 && s < X_KMAX0 + NC) acc = S.fc.kmax[s - X_KMAX0];
+      else {
+        acc = S.red[0][s];
+        for (int w = 1; w < SEG_WARPS; ++w) acc = slot_combine(s, acc, S.red[w][s]);
       }
-      S.fin[tid] = acc;
+      S.fin[s] = acc;
     } else if (tid == NMAX_END || tid == NMAX_END + 1) {
       const int s = tid == NMAX_END ? D_TTFB : D_LAT;
-      kvm_dd acc{__longlong_as_double((long long)S.red[0][s]), __longlong_as_double((long long)S.red[0][s + 1])};
-      for (int w = 1; w < SEG_WARPS; ++w)
-        acc = kvm_dd_add(acc, kvm_dd{__longlong_as_double((long long)S.red[w][s]),
-                                     __longlong_as_double((long long)S.red[w][s + 1])});
+      kvm_dd acc = dd_from_bits(S.red[0][s], S.red[0][s + 1]);
+      for (int w = 1; w < SEG_WARPS; ++w) acc = kvm_dd_add(acc, dd_from_bits(S.red[w][s], S.red[w][s + 1]));
       S.fin[s] = (uint64_t)__double_as_longlong(acc.hi);
       S.fin[s + 1] = (uint64_t)__double_as_longlong(acc.lo);
     }
@@ -236,15 +300,14 @@ seg_analyze_kernel(kvm_request_log log, const int64_t* __restrict__ run_offsets,
       if (cold_too_many) S.overflow = 1;
     }
     __syncthreads();
-    if (tid < KVM_MAX_COLS) {
-      SegCol cp{0, 0, 0};
-      if (tid < KVM_LOG_NCOLS && S.stats.sets.kmin[tid] <= S.stats.sets.kmax[tid]) {
-        const uint64_t range = S.stats.sets.kmax[tid] - S.stats.sets.kmin[tid];
-        cp.kbase = S.stats.sets.kmin[tid];
-        cp.width = range ? 64 - __clzll((long long)range) : 0;
-        cp.shift = cp.width > BINS_LOG2 ? cp.width - BINS_LOG2 : 0;
+    if (tid < NC) {   // which end bins hold keys from outside the sampled hull
+      int imp = 0;
+      const uint64_t kmin = S.stats.sets.kmin[tid], kmax = S.stats.sets.kmax[tid], kb = S.fc.kbase[tid];
+      if (kmin <= kmax) {
+        if (kmin < kb) imp |= 1;
+        if (kmax >= kb && ((kmax - kb) >> S.fc.shift[tid]) >= (uint64_t)BINS) imp |= 2;
       }
-      S.col[tid] = cp;
+      S.impure[tid] = imp;
     }
     if (tid >= 32 && tid < 32 + SEG_MAXQ) {
       const int qi = tid - 32;
@@ -269,41 +332,39 @@ seg_analyze_kernel(kvm_request_log log, const int64_t* __restrict__ run_offsets,
       S.q[qi] = s;
     }
     // 20-bin thresholds (bisection with the reference expression); one thread per edge
-    if (tid >= 128 && tid < 128 + NH * (SEG_NB_MAX - 1)) {
-      const int t = tid - 128, h = t / (SEG_NB_MAX - 1), b = 1 + t % (SEG_NB_MAX - 1);
+    if (tid >= 96 && tid < 96 + NH * (SEG_NB_MAX - 1)) {
+      const int t = tid - 96, h = t / (SEG_NB_MAX - 1), b = 1 + t % (SEG_NB_MAX - 1);
       const int c = hist_col(h);
       const uint64_t klo = S.stats.sets.kmin[c], khi = S.stats.sets.kmax[c];
       if (b == 1) S.active20[h] = klo < khi ? 1 : 0;
       if (b < nb && klo < khi) S.thr[h][b - 1] = bin_threshold(klo, khi, nb, b);
     }
     __syncthreads();
-    // edge bins of the fine histogram (those that contain a 20-bin threshold)
+    // fine bins that must be binned row by row: those that contain a 20-bin threshold, and the
+    // end bins that hold keys from outside the sampled hull
     if (tid < NH * (SEG_NB_MAX - 1)) {
       const int h = tid / (SEG_NB_MAX - 1), b = 1 + tid % (SEG_NB_MAX - 1);
       const uint64_t T = S.thr[h][b - 1];
+      const int c = hist_col(h);
       if (b < nb && S.active20[h] && T != ~0ull) {
-        const SegCol cp = S.col[hist_col(h)];
-        const uint32_t d = digit_of(T, cp.kbase, cp.shift);
+        const uint32_t d = digit_of(T, S.fc.kbase[c], S.fc.shift[c]);
         atomicOr(&S.flag20[h][d >> 5], 1u << (d & 31));
       }
+      if (b == 1 && S.active20[h]) {
+        if (S.impure[c] & 1) atomicOr(&S.flag20[h][0], 1u);
+        if (S.impure[c] & 2) atomicOr(&S.flag20[h][(BINS - 1) >> 5], 1u << ((BINS - 1) & 31));
+      }
     }
-    __syncthreads();
-    // ---------------- P3 hist
-    seg_rows_keys(log, flags, r0, r1, vec, [&](uint8_t fl, double la, double tf, double tl, int64_t ct) {
-      log_row_keys(fl, la, tf, tl, ct, [&](int set, int col, uint64_t key) {
-        atomicAdd(&S.hist[set][digit_of(key, S.col[col].kbase, S.col[col].shift)], 1u);
-      });
-    });
     __syncthreads();
     // ---------------- P4 resolve (one warp per query)
     for (int qi = warp; qi < qp.nq; qi += SEG_WARPS) {
       SegQ s = S.q[qi];
       if (s.status != KVM_Q_OK) continue;
-      const SegCol cp = S.col[s.col];
       const uint32_t mask = qp.q[qi].set_mask;
-      if (cp.width == 0) {
+      const uint64_t ckmin = S.stats.sets.kmin[s.col], ckmax = S.stats.sets.kmax[s.col];
+      if (ckmin == ckmax) {   // one distinct key in the column
         if (lane == 0) {
-          s.key = cp.kbase;
+          s.key = ckmin;
           s.resolved = 1;
           S.q[qi] = s;
         }
@@ -314,7 +375,7 @@ seg_analyze_kernel(kvm_request_log log, const int64_t* __restrict__ run_offsets,
       for (int base = 0; base < BINS && !found; base += 32) {
         int64_t c = 0;
         for (int b = 0; b < KVM_LOG_NSETS; ++b)
-          if ((mask >> b) & 1u) c += (int64_t)S.hist[b][base + lane];
+          if ((mask >> b) & 1u) c += (int64_t)sh[b * BINS + base + lane];
         int64_t incl = c;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
@@ -327,11 +388,14 @@ seg_analyze_kernel(kvm_request_log log, const int64_t* __restrict__ run_offsets,
           const int64_t excl = __shfl_sync(KVM_FULL, incl - c, l);
           const int64_t cnt = __shfl_sync(KVM_FULL, c, l);
           if (lane == 0) {
-            S.q_bin[qi] = (uint32_t)(base + l);
+            const int bin = base + l;
+            S.q_bin[qi] = (uint32_t)bin;
             S.q_cnt[qi] = (uint32_t)cnt;
             s.resid = s.rank - (running + excl);
-            if (cp.shift == 0) {
-              s.key = cp.kbase + (uint64_t)(base + l);
+            const int imp = S.impure[s.col];
+            const bool pure = !((bin == 0 && (imp & 1)) || (bin == BINS - 1 && (imp & 2)));
+            if (S.fc.shift[s.col] == 0 && pure) {   // one key per bin
+              s.key = S.fc.kbase[s.col] + (uint64_t)bin;
               s.resolved = 1;
             } else {
               s.resolved = 0;
@@ -365,10 +429,7 @@ seg_analyze_kernel(kvm_request_log log, const int64_t* __restrict__ run_offsets,
           }
         if (j < 0) {
           j = nbk++;
-          const SegCol cp = S.col[s.col];
           SegBucket b;
-          b.base = cp.kbase + ((uint64_t)S.q_bin[qi] << cp.shift);
-          b.shift = cp.shift;
           b.col = s.col;
           b.set_mask = mask;
           b.bin = S.q_bin[qi];
@@ -382,7 +443,8 @@ seg_analyze_kernel(kvm_request_log log, const int64_t* __restrict__ run_offsets,
         s.bucket = j;
       }
       S.nbuckets = nbk;
-      if (off > (uint32_t)SEG_ARENA) S.overflow = 1;
+      S.arena_used = off;
+      if (off > (uint32_t)SEG_ARENA || r1 - r0 >= (1ll << 32)) S.overflow = 1;
     }
     __syncthreads();
     if (S.overflow) {  // host redoes this run through the flat path
@@ -393,61 +455,134 @@ seg_analyze_kernel(kvm_request_log log, const int64_t* __restrict__ run_offsets,
       __syncthreads();
       continue;
     }
-    // ---------------- P5 compact + exact binning of the rows in edge bins
-    {
-      const int nbk = S.nbuckets;
-      seg_rows_keys(log, flags, r0, r1, vec, [&](uint8_t fl, double la, double tf, double tl, int64_t ct) {
-        log_row_keys(fl, la, tf, tl, ct, [&](int set, int col, uint64_t key) {
-          const uint32_t d = digit_of(key, S.col[col].kbase, S.col[col].shift);
-          if ((S.bmap[col][d >> 5] >> (d & 31)) & 1u) {
-            for (int j = 0; j < nbk; ++j)
-              if (S.bk[j].col == col && S.bk[j].bin == d && ((S.bk[j].set_mask >> set) & 1u)) {
-                const uint32_t pos = atomicAdd(&S.cursor[j], 1u);
-                if (pos < S.bk[j].count) S.arena[S.bk[j].offset + pos] = key;
-              }
-          }
-          const int h = col_hist(col);
-          if (h >= 0 && ((S.flag20[h][d >> 5] >> (d & 31)) & 1u))
-            atomicAdd(&S.edge[h][bin_of(key, S.thr[h], nb)], 1u);
-        });
-      });
-    }
-    __syncthreads();
-    // ---------------- P6 finish: rank inside the bucket by counting (one warp per query)
-    for (int qi = warp; qi < qp.nq; qi += SEG_WARPS) {
-      SegQ s = S.q[qi];
-      if (s.status != KVM_Q_OK || s.resolved) continue;
-      const SegBucket b = S.bk[s.bucket];
-      const uint64_t* keys = S.arena + b.offset;
-      const uint32_t m = b.count;
-      for (uint32_t i = lane; i < m; i += 32) {
-        const uint64_t k = keys[i];
-        uint32_t less = 0, leq = 0;
-        for (uint32_t j = 0; j < m; ++j) {
-          const uint64_t o = keys[j];
-          less += o < k;
-          leq += o <= k;
-        }
-        if ((int64_t)less <= s.resid && s.resid < (int64_t)leq) S.q[qi].key = k;  // all writers agree
-      }
-    }
-    __syncthreads();
-    // ---------------- P7 emit
-    // fine bins without an edge lie inside a single 20-bin: add them wholesale
+    // ---------------- P5 fine bins without an edge lie inside a single 20-bin: add them wholesale
     for (int t = tid; t < NH * BINS; t += SEG_THREADS) {
       const int h = t / BINS, d = t % BINS;
       if (!S.active20[h] || ((S.flag20[h][d >> 5] >> (d & 31)) & 1u)) continue;
       const uint32_t sets = hist_sets(h);
       uint32_t c = 0;
       for (int b = 0; b < KVM_LOG_NSETS; ++b)
-        if ((sets >> b) & 1u) c += S.hist[b][d];
+        if ((sets >> b) & 1u) c += sh[b * BINS + d];
       if (c) {
-        const SegCol cp = S.col[hist_col(h)];
-        const uint64_t lowkey = cp.kbase + ((uint64_t)d << cp.shift);
+        const int col = hist_col(h);
+        const uint64_t lowkey = S.fc.kbase[col] + ((uint64_t)d << S.fc.shift[col]);
         atomicAdd(&S.cnt20[h][bin_of(lowkey, S.thr[h], nb)], c);
       }
     }
+    for (int t = tid; t < NC * (BINS / 32); t += SEG_THREADS) {
+      const int c = t / (BINS / 32), w = t % (BINS / 32);
+      const int h = col_hist(c);
+      S.anyhit[c][w] = S.bmap[c][w] | (h >= 0 ? S.flag20[h][w] : 0u);
+    }
+    __syncthreads();   // the histograms are dead from here on: their space is the arena
+    phase(2);
+    // ---------------- P6 compact + exact binning of the rows in edge bins, from the records.
+    // A wanted (row, column) is rare and costs a dependent fetch: the warp queues them and serves
+    // 32 at a time with every lane busy, instead of stalling on each where it is found.
+    {
+      auto rec_row = [&](int64_t i, uint64_t r, uint32_t fl) {
+#pragma unroll
+        for (int c = 0; c < NC; ++c) {
+          const uint32_t d = (uint32_t)(r >> (12 * c)) & 0xFFFu;
+          if ((S.anyhit[c][d >> 5] >> (d & 31)) & 1u) seg_hit(S, log, i, c, d, fl, nb);
+        }
+      };
+      if (base_aligned) {
+        if (tid == 0 && a0 > r0 && r0 < r1) rec_row(r0, recs[r0], flags[r0]);
+        if (tid == 32 && a0 < r1 && ((r1 - a0) & 1)) rec_row(r1 - 1, recs[r1 - 1], flags[r1 - 1]);
+      } else {
+        for (int64_t i = r0 + tid; i < r1; i += SEG_THREADS) rec_row(i, recs[i], flags[i]);
+      }
+      uint64_t* hq = S.hitq[warp];
+      int qn = 0;   // warp-uniform
+      auto flush = [&]() {
+        __syncwarp();
+        for (int e = lane; e < qn; e += 32) {
+          const uint64_t w = hq[e];
+          seg_hit(S, log, r0 + (int64_t)(uint32_t)w, (int)((w >> 44) & 7u), (uint32_t)(w >> 32) & 0xFFFu,
+                  (uint32_t)(w >> 48) & 0xFFu, nb);
+        }
+        __syncwarp();
+        qn = 0;
+      };
+      for (int64_t pb = tid & ~31; pb < npairs; pb += SEG_THREADS) {
+        const int64_t p = pb + lane;
+        const int64_t i = a0 + (p << 1);
+        uint32_t hm = 0, ff = 0;
+        ulonglong2 rr = make_ulonglong2(0ull, 0ull);
+        if (p < npairs) {
+          rr = *reinterpret_cast<const ulonglong2*>(recs + i);
+          ff = *reinterpret_cast<const uint16_t*>(flags + i);
+#pragma unroll
+          for (int c = 0; c < NC; ++c) {
+            const uint32_t d0 = (uint32_t)(rr.x >> (12 * c)) & 0xFFFu, d1 = (uint32_t)(rr.y >> (12 * c)) & 0xFFFu;
+            hm |= ((S.anyhit[c][d0 >> 5] >> (d0 & 31)) & 1u) << c;
+            hm |= ((S.anyhit[c][d1 >> 5] >> (d1 & 31)) & 1u) << (NC + c);
+          }
+        }
+        const int nh = __popc(hm);
+        int incl = nh;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+          const int o = __shfl_up_sync(KVM_FULL, incl, d);
+          if (lane >= d) incl += o;
+        }
+        const int total = __shfl_sync(KVM_FULL, incl, 31);
+        if (total == 0) continue;
+        if (total > 32 || qn + total > SEG_HITQ) flush();
+        if (total > 32) {   // a dense stretch: served where found
+          while (hm) {
+            const int b = __ffs(hm) - 1;
+            hm &= hm - 1;
+            const int second = b >= NC, c = b - (second ? NC : 0);
+            const uint64_t r = second ? rr.y : rr.x;
+            seg_hit(S, log, i + second, c, (uint32_t)(r >> (12 * c)) & 0xFFFu, second ? ff >> 8 : ff & 0xffu, nb);
+          }
+          continue;
+        }
+        int pos = qn + incl - nh;
+        while (hm) {
+          const int b = __ffs(hm) - 1;
+          hm &= hm - 1;
+          const int second = b >= NC, c = b - (second ? NC : 0);
+          const uint64_t r = second ? rr.y : rr.x;
+          const uint64_t d = (r >> (12 * c)) & 0xFFFull;
+          hq[pos++] = (uint64_t)(uint32_t)(i + second - r0) | (d << 32) | ((uint64_t)c << 44) |
+                      ((uint64_t)(second ? ff >> 8 : ff & 0xffu) << 48);
+        }
+        qn += total;
+      }
+      flush();
+    }
     __syncthreads();
+    phase(3);
+    // ---------------- P7 finish: rank inside the bucket by counting.  One thread per candidate
+    // key: its rank range among the keys of its bucket, matched against the bucket's queries.
+    {
+      const uint64_t* arena = reinterpret_cast<const uint64_t*>(sh);
+      const int nbk = S.nbuckets;
+      for (uint32_t x = tid; x < S.arena_used; x += SEG_THREADS) {
+        int j = 0;
+        while (j + 1 < nbk && S.bk[j + 1].offset <= x) ++j;
+        const uint64_t* keys = arena + S.bk[j].offset;
+        const uint32_t m = S.bk[j].count;
+        const uint64_t k = arena[x];
+        uint32_t less = 0, leq = 0;
+        for (uint32_t y = 0; y < m; ++y) {
+          const uint64_t o = keys[y];
+          less += o < k;
+          leq += o <= k;
+        }
+        for (int qi = 0; qi < qp.nq; ++qi) {
+          const int64_t resid = S.q[qi].resid;
+          if (S.q[qi].bucket == j && S.q[qi].status == KVM_Q_OK && !S.q[qi].resolved && (int64_t)less <= resid &&
+              resid < (int64_t)leq)
+            S.q[qi].key = k;  // all writers agree
+        }
+      }
+    }
+    __syncthreads();
+    // ---------------- P8 emit
     for (int t = tid; t < NH * nb; t += SEG_THREADS) {
       const int h = t / nb, b = t % nb;
       out_hist[(run * NH + h) * nb + b] = (int64_t)S.cnt20[h][b] + (int64_t)S.edge[h][b];
@@ -467,24 +602,44 @@ seg_analyze_kernel(kvm_request_log log, const int64_t* __restrict__ run_offsets,
       out_stats[run] = S.stats;
     }
     __syncthreads();
+    phase(4);
   }
 }
 
 }  // namespace
 
+// debug aid: the per-phase nanoseconds summed over all runs since the last reset (synchronises)
+extern "C" int kvm_seg_phase_times(uint64_t* out5, int32_t reset) {
+  KVM_REQUIRE(out5, "kvm_seg_phase_times: null argument");
+  unsigned long long h[8];
+  KVM_CUDA_CHECK(cudaMemcpyFromSymbol(h, seg_phase_ns, sizeof(h)));
+  for (int i = 0; i < 5; ++i) out5[i] = h[i];
+  if (reset) {
+    for (int i = 0; i < 8; ++i) h[i] = 0;
+    KVM_CUDA_CHECK(cudaMemcpyToSymbol(seg_phase_ns, h, sizeof(h)));
+  }
+  return KVM_OK;
+}
+
+extern "C" size_t kvm_seg_analyze_scratch_bytes(int64_t n) { return sizeof(uint64_t) * (size_t)(n < 0 ? 0 : n + 2); }
+
 extern "C" int kvm_seg_analyze(const kvm_request_log* log, const int64_t* run_offsets, int64_t runs,
                                const int64_t* cold_offsets, const double* cold_times,
                                double cold_window_s, const kvm_query* queries, int32_t nq,
-                               int32_t num_bins, uint8_t* flags, kvm_log_stats* stats,
-                               kvm_query_result* results, int64_t* hist_counts, int32_t* run_status,
-                               void* stream) {
-  KVM_REQUIRE(log && run_offsets && queries && flags && stats && results && hist_counts && run_status,
+                               int32_t num_bins, uint8_t* flags, void* scratch, size_t scratch_bytes,
+                               kvm_log_stats* stats, kvm_query_result* results, int64_t* hist_counts,
+                               int32_t* run_status, void* stream) {
+  KVM_REQUIRE(log && run_offsets && queries && flags && scratch && stats && results && hist_counts && run_status,
               "kvm_seg_analyze: null argument");
   KVM_REQUIRE(runs >= 0, "kvm_seg_analyze: negative run count");
   KVM_REQUIRE(nq >= 1 && nq <= SEG_MAXQ, "kvm_seg_analyze: nq=%d outside [1,%d]", nq, SEG_MAXQ);
   KVM_REQUIRE(num_bins >= 1 && num_bins <= SEG_NB_MAX, "kvm_seg_analyze: num_bins=%d outside [1,%d]",
               num_bins, SEG_NB_MAX);
   KVM_REQUIRE(cold_offsets == nullptr || cold_times != nullptr, "kvm_seg_analyze: cold_times is null");
+  if (scratch_bytes < kvm_seg_analyze_scratch_bytes(log->n)) {
+    kvm_set_error("kvm_seg_analyze: scratch %zu < %zu bytes", scratch_bytes, kvm_seg_analyze_scratch_bytes(log->n));
+    return KVM_ERR_WORKSPACE;
+  }
   if (runs == 0) return KVM_OK;
   SegQueries qp;
   for (int i = 0; i < SEG_MAXQ; ++i) qp.q[i] = i < nq ? queries[i] : kvm_query{0, 0, 0.0, 0};
@@ -495,12 +650,12 @@ extern "C" int kvm_seg_analyze(const kvm_request_log* log, const int64_t* run_of
   auto al16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; };
   const bool aligned = al16(log->start_ms) && al16(log->latency_ms) && al16(log->ttfb_ms) &&
                        al16(log->tllt_ms) && al16(log->status) && al16(log->completion_tokens) &&
-                       al16(log->total_tokens) && (reinterpret_cast<uintptr_t>(flags) & 1u) == 0;
-  int grid = kvm_num_sms();
+                       al16(log->total_tokens) && (reinterpret_cast<uintptr_t>(flags) & 1u) == 0 && al16(scratch);
+  int grid = 2 * kvm_num_sms();
   if ((int64_t)grid > runs) grid = (int)runs;
   seg_analyze_kernel<<<grid, SEG_THREADS, smem, (cudaStream_t)stream>>>(
       *log, run_offsets, runs, cold_offsets, cold_times, cold_window_s, qp, num_bins, aligned, flags,
-      stats, results, hist_counts, run_status);
+      reinterpret_cast<uint64_t*>(scratch), stats, results, hist_counts, run_status);
   KVM_CUDA_CHECK(cudaGetLastError());
   return KVM_OK;
 }

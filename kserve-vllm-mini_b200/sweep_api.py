@@ -4,8 +4,9 @@ configs[2]: 4096 runs x 250k requests).
 The reference does this with one `analyze.py` process per run (grid-sweep.sh:103-174 ->
 bench.sh:263) and then pulls 11 keys out of each results.json (grid-sweep.sh:136-161).
 Here the runs are CSR segments of one columnar log; `kvm_seg_analyze` gives every run to one
-persistent CTA.  Runs whose candidate set does not fit on chip are redone through the flat
-path, so every run's result equals `analyze_api.analyze_log` on that run alone.
+persistent CTA, which reads the run's columns once.  Runs whose candidate set does not fit on
+chip are redone through the flat path, so every run's result equals `analyze_api.analyze_log`
+on that run alone.
 Runs are independent, so multi-GPU = whole runs per GPU and no collective.
 """
 
@@ -31,6 +32,7 @@ class SweepAnalyzer:
         self.lib = N.lib()
         self._flat: Optional[engine.LogAnalyzer] = None
         self.fallback_runs = 0
+        self._scratch: Optional[torch.Tensor] = None   # 8 B/row digit records of the segmented kernel
 
     def analyze(self, dlog: engine.DeviceLog, run_offsets: Sequence[int],
                 cold_times: Optional[Sequence[Sequence[float]]] = None, num_bins: int = 20,
@@ -54,6 +56,11 @@ class SweepAnalyzer:
         queries = engine.build_queries(quantiles)
         nq = len(queries)
         flags = torch.empty(dlog.n + 2, dtype=torch.uint8, device=dev)
+        need = int(lib.kvm_seg_analyze_scratch_bytes(dlog.n))
+        if self._scratch is None or self._scratch.numel() < need:
+            self._scratch = None
+            self._scratch = torch.empty(need, dtype=torch.uint8, device=dev)
+        scratch = self._scratch
         stats_d = torch.zeros(max(runs, 1) * C.sizeof(N.LogStatsC), dtype=torch.uint8, device=dev)
         res_d = torch.zeros(max(runs, 1) * nq * C.sizeof(N.QueryResultC), dtype=torch.uint8, device=dev)
         hist_d = torch.zeros((max(runs, 1), 4, num_bins), dtype=torch.int64, device=dev)
@@ -64,7 +71,8 @@ class SweepAnalyzer:
         N.check(lib.kvm_seg_analyze(C.byref(log_c), offs_d.data_ptr(), runs,
                                     cold_off_d.data_ptr() if cold_off_d is not None else None,
                                     cold_d.data_ptr() if cold_d is not None else None, 30.0,
-                                    queries, nq, num_bins, flags.data_ptr(), stats_d.data_ptr(),
+                                    queries, nq, num_bins, flags.data_ptr(), scratch.data_ptr(), scratch.numel(),
+                                    stats_d.data_ptr(),
                                     res_d.data_ptr(), hist_d.data_ptr(), status_d.data_ptr(),
                                     engine._stream_ptr(dev)), "kvm_seg_analyze")
         ev1.record(torch.cuda.current_stream(dev))
