@@ -38,7 +38,9 @@ constexpr int SEG_WARPS = SEG_THREADS / 32;
 constexpr int SEG_ARENA = KVM_LOG_NSETS * BINS * 4 / 8;   // candidate keys per run: the space of the histograms
 constexpr int SEG_BUCKET_MAX = 2048;  // largest bucket finished by counting
 constexpr int SEG_COLD = 256;
-constexpr int SEG_HITQ = 64;
+constexpr int SEG_HITQ = 256;   // (row, column) pairs a warp collects before it fetches their values
+constexpr int SEG_DIRECT = 160; // more than this in one iteration (of up to 320): served where found
+constexpr int SEG_RK = 4;       // row pairs per lane and iteration of the records pass
 constexpr int SEG_MAXQ = KVM_MAX_QUERIES;
 constexpr int SEG_NB_MAX = 64;
 constexpr int NH = 4;  // 20-bin histograms: ttfb, tllt, generation, per-token
@@ -80,6 +82,7 @@ struct SegSmem {
   int32_t overflow;
   uint32_t arena_used;
   uint64_t hitq[SEG_WARPS][SEG_HITQ];          // P6: rows waiting for their value, per warp
+  uint32_t hitq_n[SEG_WARPS];
   kvm_log_stats stats;
 };
 
@@ -103,27 +106,29 @@ __device__ __forceinline__ unsigned long long seg_now() {
   return t;
 }
 
+static_assert(sizeof(SegSmem) <= 113 * 1024, "two CTAs per SM");
+
 struct SegQueries {
   kvm_query q[SEG_MAXQ];
   int32_t nq;
 };
 
-// A row of P6 whose digit in column c is wanted: fetch the value, append it to the buckets it
-// belongs to and / or bin it exactly.  Out of line: a few percent of the rows come here.
-__device__ __noinline__ void seg_hit(SegSmem& S, const kvm_request_log& log, int64_t i, int c, uint32_t d,
-                                     uint32_t fl, int nb) {
+// A row of P6 whose digit in column c is wanted: fetch the value ...
+__device__ __forceinline__ double seg_value(const kvm_request_log& log, int64_t i, int c) {
+  if (c == KVM_COL_LAT) return __ldg(log.latency_ms + i);
+  if (c == KVM_COL_TTFB) return __ldg(log.ttfb_ms + i);
+  if (c == KVM_COL_TLLT) return __ldg(log.tllt_ms + i);
+  const double g = __ldg(log.tllt_ms + i) - __ldg(log.ttfb_ms + i);   // analyze.py:144
+  if (c == KVM_COL_GEN) return g;
+  return g / (double)__ldg(log.completion_tokens + i);                 // analyze.py:146
+}
+// ... then append it to the buckets it belongs to and / or bin it exactly.  Out of line: a few
+// percent of the rows come here.
+__device__ __noinline__ void seg_place(SegSmem& S, int c, uint32_t d, uint32_t fl, uint64_t key, int nb) {
   const bool cold_row = fl & KVM_F_COLD;
-  double v;
-  int set;
-  if (c == KVM_COL_LAT) { v = __ldg(log.latency_ms + i); set = cold_row ? KVM_SET_LAT_COLD : KVM_SET_LAT_WARM; }
-  else if (c == KVM_COL_TTFB) { v = __ldg(log.ttfb_ms + i); set = cold_row ? KVM_SET_TTFB_COLD : KVM_SET_TTFB_WARM; }
-  else if (c == KVM_COL_TLLT) { v = __ldg(log.tllt_ms + i); set = KVM_SET_TLLT; }
-  else {
-    const double g = __ldg(log.tllt_ms + i) - __ldg(log.ttfb_ms + i);   // analyze.py:144
-    if (c == KVM_COL_GEN) { v = g; set = KVM_SET_GEN; }
-    else { v = g / (double)__ldg(log.completion_tokens + i); set = KVM_SET_PERTOK; }   // analyze.py:146
-  }
-  const uint64_t key = kvm_key(v);
+  const int set = c == KVM_COL_LAT ? (cold_row ? KVM_SET_LAT_COLD : KVM_SET_LAT_WARM)
+                  : c == KVM_COL_TTFB ? (cold_row ? KVM_SET_TTFB_COLD : KVM_SET_TTFB_WARM)
+                  : c == KVM_COL_TLLT ? KVM_SET_TLLT : c == KVM_COL_GEN ? KVM_SET_GEN : KVM_SET_PERTOK;
   uint64_t* arena = reinterpret_cast<uint64_t*>(S.hist);
   if ((S.bmap[c][d >> 5] >> (d & 31)) & 1u) {
     const int nbk = S.nbuckets;
@@ -135,6 +140,10 @@ __device__ __noinline__ void seg_hit(SegSmem& S, const kvm_request_log& log, int
   }
   const int h = col_hist(c);
   if (h >= 0 && ((S.flag20[h][d >> 5] >> (d & 31)) & 1u)) atomicAdd(&S.edge[h][bin_of(key, S.thr[h], nb)], 1u);
+}
+__device__ __forceinline__ void seg_hit(SegSmem& S, const kvm_request_log& log, int64_t i, int c, uint32_t d,
+                                        uint32_t fl, int nb) {
+  seg_place(S, c, d, fl, kvm_key(seg_value(log, i, c)), nb);
 }
 
 __global__ void __launch_bounds__(SEG_THREADS, 2)
@@ -494,91 +503,128 @@ seg_analyze_kernel(kvm_request_log log, const int64_t* __restrict__ run_offsets,
         for (int64_t i = r0 + tid; i < r1; i += SEG_THREADS) rec_row(i, recs[i], flags[i]);
       }
       uint64_t* hq = S.hitq[warp];
-      int qn = 0;   // warp-uniform
+      int qn = 0;   // warp-uniform copy of hitq_n[warp]
+      if (lane == 0) S.hitq_n[warp] = 0;
+      __syncwarp();
       auto flush = [&]() {
         __syncwarp();
-        for (int e = lane; e < qn; e += 32) {
-          const uint64_t w = hq[e];
-          seg_hit(S, log, r0 + (int64_t)(uint32_t)w, (int)((w >> 44) & 7u), (uint32_t)(w >> 32) & 0xFFFu,
-                  (uint32_t)(w >> 48) & 0xFFu, nb);
+        for (int e0 = 0; e0 < qn; e0 += 64) {
+          uint64_t w[2];
+          double v[2];
+#pragma unroll
+          for (int u = 0; u < 2; ++u) {   // the fetches of both entries are in flight together
+            const int e = e0 + u * 32 + lane;
+            w[u] = e < qn ? hq[e] : ~0ull;
+            if (e < qn) v[u] = seg_value(log, r0 + (int64_t)(uint32_t)w[u], (int)((w[u] >> 44) & 7u));
+          }
+#pragma unroll
+          for (int u = 0; u < 2; ++u)
+            if (e0 + u * 32 + lane < qn)
+              seg_place(S, (int)((w[u] >> 44) & 7u), (uint32_t)(w[u] >> 32) & 0xFFFu, (uint32_t)(w[u] >> 48) & 0xFFu,
+                        kvm_key(v[u]), nb);
         }
+        if (lane == 0) S.hitq_n[warp] = 0;
         __syncwarp();
         qn = 0;
       };
-      for (int64_t pb = tid & ~31; pb < npairs; pb += SEG_THREADS) {
-        const int64_t p = pb + lane;
-        const int64_t i = a0 + (p << 1);
-        uint32_t hm = 0, ff = 0;
-        ulonglong2 rr = make_ulonglong2(0ull, 0ull);
-        if (p < npairs) {
-          rr = *reinterpret_cast<const ulonglong2*>(recs + i);
-          ff = *reinterpret_cast<const uint16_t*>(flags + i);
+      // four row pairs per lane and iteration (every load of a warp covers 512 consecutive bytes)
+      for (int64_t pb = (int64_t)warp * (32 * SEG_RK); pb < npairs; pb += (int64_t)SEG_THREADS * SEG_RK) {
+        ulonglong2 rr[SEG_RK];
+        uint32_t ff[SEG_RK];
+#pragma unroll
+        for (int k = 0; k < SEG_RK; ++k) {
+          const int64_t p = pb + k * 32 + lane;
+          rr[k] = make_ulonglong2(~0ull, ~0ull);   // fields 0xFFF: wanted nowhere
+          ff[k] = 0;
+          if (p < npairs) {
+            rr[k] = *reinterpret_cast<const ulonglong2*>(recs + a0 + (p << 1));
+            ff[k] = *reinterpret_cast<const uint16_t*>(flags + a0 + (p << 1));
+          }
+        }
+        uint64_t hm = 0;
+#pragma unroll
+        for (int k = 0; k < SEG_RK; ++k)
 #pragma unroll
           for (int c = 0; c < NC; ++c) {
-            const uint32_t d0 = (uint32_t)(rr.x >> (12 * c)) & 0xFFFu, d1 = (uint32_t)(rr.y >> (12 * c)) & 0xFFFu;
-            hm |= ((S.anyhit[c][d0 >> 5] >> (d0 & 31)) & 1u) << c;
-            hm |= ((S.anyhit[c][d1 >> 5] >> (d1 & 31)) & 1u) << (NC + c);
+            const uint32_t d0 = (uint32_t)(rr[k].x >> (12 * c)) & 0xFFFu, d1 = (uint32_t)(rr[k].y >> (12 * c)) & 0xFFFu;
+            hm |= (uint64_t)((S.anyhit[c][d0 >> 5] >> (d0 & 31)) & 1u) << (k * 2 * NC + c);
+            hm |= (uint64_t)((S.anyhit[c][d1 >> 5] >> (d1 & 31)) & 1u) << (k * 2 * NC + NC + c);
           }
-        }
-        const int nh = __popc(hm);
-        int incl = nh;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-          const int o = __shfl_up_sync(KVM_FULL, incl, d);
-          if (lane >= d) incl += o;
-        }
-        const int total = __shfl_sync(KVM_FULL, incl, 31);
+        const int nh = __popcll(hm);
+        const int total = __reduce_add_sync(KVM_FULL, nh);
         if (total == 0) continue;
-        if (total > 32 || qn + total > SEG_HITQ) flush();
-        if (total > 32) {   // a dense stretch: served where found
-          while (hm) {
-            const int b = __ffs(hm) - 1;
-            hm &= hm - 1;
-            const int second = b >= NC, c = b - (second ? NC : 0);
-            const uint64_t r = second ? rr.y : rr.x;
-            seg_hit(S, log, i + second, c, (uint32_t)(r >> (12 * c)) & 0xFFFu, second ? ff >> 8 : ff & 0xffu, nb);
-          }
-          continue;
-        }
-        int pos = qn + incl - nh;
+        if (total > SEG_DIRECT || qn + total > SEG_HITQ) flush();
+        const bool direct = total > SEG_DIRECT;   // a dense stretch: served where found
+        int pos = 0;
+        if (!direct && nh) pos = (int)atomicAdd(&S.hitq_n[warp], (uint32_t)nh);
         while (hm) {
-          const int b = __ffs(hm) - 1;
+          const int b = __ffsll((long long)hm) - 1;
           hm &= hm - 1;
-          const int second = b >= NC, c = b - (second ? NC : 0);
-          const uint64_t r = second ? rr.y : rr.x;
+          const int k = b / (2 * NC), second = (b % (2 * NC)) >= NC, c = b % NC;
+          uint64_t r = rr[0].x;
+          uint32_t f = ff[0];
+#pragma unroll
+          for (int kk = 0; kk < SEG_RK; ++kk)
+            if (kk == k) {
+              r = second ? rr[kk].y : rr[kk].x;
+              f = ff[kk];
+            }
+          const uint32_t fl = second ? f >> 8 : f & 0xffu;
+          const int64_t i = a0 + ((pb + k * 32 + lane) << 1) + second;
           const uint64_t d = (r >> (12 * c)) & 0xFFFull;
-          hq[pos++] = (uint64_t)(uint32_t)(i + second - r0) | (d << 32) | ((uint64_t)c << 44) |
-                      ((uint64_t)(second ? ff >> 8 : ff & 0xffu) << 48);
+          if (direct) seg_hit(S, log, i, c, (uint32_t)d, fl, nb);
+          else hq[pos++] = (uint64_t)(uint32_t)(i - r0) | (d << 32) | ((uint64_t)c << 44) | ((uint64_t)fl << 48);
         }
-        qn += total;
+        if (!direct) qn += total;
       }
       flush();
     }
     __syncthreads();
     phase(3);
-    // ---------------- P7 finish: rank inside the bucket by counting.  One thread per candidate
-    // key: its rank range among the keys of its bucket, matched against the bucket's queries.
+    // ---------------- P7 finish: a warp per query selects the wanted rank among its bucket's keys by
+    // radix steps over the bits that differ inside the bucket, five bits (one lane per bin) a step
     {
       const uint64_t* arena = reinterpret_cast<const uint64_t*>(sh);
-      const int nbk = S.nbuckets;
-      for (uint32_t x = tid; x < S.arena_used; x += SEG_THREADS) {
-        int j = 0;
-        while (j + 1 < nbk && S.bk[j + 1].offset <= x) ++j;
-        const uint64_t* keys = arena + S.bk[j].offset;
-        const uint32_t m = S.bk[j].count;
-        const uint64_t k = arena[x];
-        uint32_t less = 0, leq = 0;
-        for (uint32_t y = 0; y < m; ++y) {
-          const uint64_t o = keys[y];
-          less += o < k;
-          leq += o <= k;
+      uint32_t* cnt = reinterpret_cast<uint32_t*>(S.hitq[warp]);
+      for (int qi = warp; qi < qp.nq; qi += SEG_WARPS) {
+        const SegQ s = S.q[qi];
+        if (s.status != KVM_Q_OK || s.resolved) continue;
+        const SegBucket b = S.bk[s.bucket];
+        const uint64_t* keys = arena + b.offset;
+        const uint32_t m = b.count;
+        const uint64_t k0 = keys[0];
+        uint64_t diff = 0;
+        for (uint32_t i = lane; i < m; i += 32) diff |= keys[i] ^ k0;
+        diff = ((uint64_t)__reduce_or_sync(KVM_FULL, (uint32_t)(diff >> 32)) << 32) |
+               (uint64_t)__reduce_or_sync(KVM_FULL, (uint32_t)diff);
+        int top = bit_width64(diff);   // the low `top` bits vary inside the bucket
+        uint64_t fixed = top >= 64 ? 0ull : ~0ull << top, value = k0 & fixed;
+        int64_t r = s.resid;
+        while (top > 0) {
+          const int w = top >= 5 ? 5 : top, sft = top - w;
+          cnt[lane] = 0;
+          __syncwarp();
+          for (uint32_t i = lane; i < m; i += 32) {
+            const uint64_t k = keys[i];
+            if ((k & fixed) == value) atomicAdd(&cnt[(uint32_t)(k >> sft) & ((1u << w) - 1u)], 1u);
+          }
+          __syncwarp();
+          const uint32_t c = cnt[lane];
+          uint32_t incl = c;
+#pragma unroll
+          for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t o = __shfl_up_sync(KVM_FULL, incl, d);
+            if (lane >= d) incl += o;
+          }
+          const unsigned hit = __ballot_sync(KVM_FULL, (int64_t)incl > r);
+          const int l = hit ? __ffs(hit) - 1 : 31;
+          r -= (int64_t)__shfl_sync(KVM_FULL, incl - c, l);
+          value |= (uint64_t)l << sft;
+          fixed |= (uint64_t)((1u << w) - 1u) << sft;
+          top = sft;
+          __syncwarp();
         }
-        for (int qi = 0; qi < qp.nq; ++qi) {
-          const int64_t resid = S.q[qi].resid;
-          if (S.q[qi].bucket == j && S.q[qi].status == KVM_Q_OK && !S.q[qi].resolved && (int64_t)less <= resid &&
-              resid < (int64_t)leq)
-            S.q[qi].key = k;  // all writers agree
-        }
+        if (lane == 0) S.q[qi].key = value;
       }
     }
     __syncthreads();
