@@ -138,6 +138,12 @@ __device__ __forceinline__ void kvm_st4_u32_keep(void* p, uint4 v, unsigned long
 }
 // programmatic dependent launch (PDL): the dependent kernel may be made resident while this one
 // still runs / wait until every kernel this one depends on has completed and its writes are visible
+__device__ __forceinline__ void kvm_prefetch_l2(const void* p) {
+  asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+}
+__device__ __forceinline__ void kvm_prefetch_l1(const void* p) {
+  asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
+}
 __device__ __forceinline__ void kvm_pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;"); }
 __device__ __forceinline__ void kvm_pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 

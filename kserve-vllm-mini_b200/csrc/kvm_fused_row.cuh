@@ -180,30 +180,34 @@ __device__ __forceinline__ uint64_t fused_row(FAcc& a, FusedCols& S, uint32_t* s
   const bool gen = m_tf && has_tl && ct > 0;
   const double g = tl - tf;                 // analyze.py:144
   const bool m_g = gen && g == g;
-  const double pt = g / (double)ct;         // analyze.py:146 (garbage where !gen: never used)
+  // analyze.py:146.  The quotient is only used where m_g holds (then ct > 0).  A zero numerator
+  // or divisor would send the division through its slow subroutine on every non-streaming row
+  // (tllt == ttfb): x/ct is x itself for x = +-0, so those rows divide 1.0 by 1.0 instead.
+  const bool dv = m_g && g != 0.0;
+  const double quo = (dv ? g : 1.0) / (dv ? (double)ct : 1.0);
+  const double pt = dv ? quo : g;
   const bool m_pt = m_g && pt == pt;
   a.n_gen += gen;
   dd_acc(a.lat_s, a.lat_e, m_la ? la : 0.0);
   dd_acc(a.ttfb_s, a.ttfb_e, m_tf ? tf : 0.0);
   uint32_t rare = 0;
-  auto site = [&](bool m, int setoff, int col, double v) -> uint32_t {
-    const uint32_t hi = (uint32_t)__double2hiint(v), lo = (uint32_t)__double2loint(v);
-    const uint32_t sgn = (uint32_t)((int32_t)hi >> 31);
-    const uint32_t klo = lo ^ sgn, khi = hi ^ (sgn | 0x80000000u);
+  auto site = [&](bool m, uint32_t* hist, int col, double v) -> uint32_t {
+    const uint64_t b = (uint64_t)__double_as_longlong(v);
+    const uint64_t key = b ^ ((uint64_t)((int64_t)b >> 63) | 0x8000000000000000ull);
     const uint4 P = S.par[col];
-    const uint32_t dhi = khi - P.y - (klo < P.x ? 1u : 0u);
+    const uint32_t dhi = (uint32_t)((key - (((uint64_t)P.y << 32) | P.x)) >> 32);
     const bool out = dhi >= P.z;
     const uint32_t d = dhi >> P.w;
-    if (m && !out) atomicAdd(&sh[setoff + d], 1u);
+    if (m && !out) atomicAdd(hist + d, 1u);
     rare |= (m && out) ? (1u << col) : 0u;
     return m ? (out ? 0u : d) : 0xFFFu;
   };
-  const int coff = cold_row ? 0 : BINS;
-  const uint32_t d0 = site(m_la, KVM_SET_LAT_COLD * BINS + coff, KVM_COL_LAT, la);
-  const uint32_t d1 = site(m_tf, KVM_SET_TTFB_COLD * BINS + coff, KVM_COL_TTFB, tf);
-  const uint32_t d2 = site(m_tl, KVM_SET_TLLT * BINS, KVM_COL_TLLT, tl);
-  const uint32_t d3 = site(m_g, KVM_SET_GEN * BINS, KVM_COL_GEN, g);
-  const uint32_t d4 = site(m_pt, KVM_SET_PERTOK * BINS, KVM_COL_PERTOK, pt);
+  uint32_t* hcw = sh + (cold_row ? 0 : BINS);   // the cold / warm pair of a column: two consecutive sets
+  const uint32_t d0 = site(m_la, hcw + KVM_SET_LAT_COLD * BINS, KVM_COL_LAT, la);
+  const uint32_t d1 = site(m_tf, hcw + KVM_SET_TTFB_COLD * BINS, KVM_COL_TTFB, tf);
+  const uint32_t d2 = site(m_tl, sh + KVM_SET_TLLT * BINS, KVM_COL_TLLT, tl);
+  const uint32_t d3 = site(m_g, sh + KVM_SET_GEN * BINS, KVM_COL_GEN, g);
+  const uint32_t d4 = site(m_pt, sh + KVM_SET_PERTOK * BINS, KVM_COL_PERTOK, pt);
   const uint32_t f = (ok ? KVM_F_SUCCESS : 0) | (cold_row ? KVM_F_COLD : 0) | (ct > 0 ? KVM_F_TOKENS : 0) |
                      (gen ? KVM_F_GEN : 0);
   flag_out = f;

@@ -257,6 +257,13 @@ seg_analyze_kernel(kvm_request_log log, const int64_t* __restrict__ run_offsets,
     }
     for (int64_t p = tid; p < npairs; p += SEG_THREADS) {
       const int64_t i = a0 + (p << 1);
+      // next iteration's lines on their way from DRAM to L2 while this one computes (one lane per 128-byte line)
+      if ((lane & 7) == 0 && p + SEG_THREADS < npairs) {
+        const int64_t j = i + 2 * SEG_THREADS;
+        kvm_prefetch_l2(log.start_ms + j); kvm_prefetch_l2(log.latency_ms + j); kvm_prefetch_l2(log.ttfb_ms + j);
+        kvm_prefetch_l2(log.tllt_ms + j); kvm_prefetch_l2(log.status + j); kvm_prefetch_l2(log.completion_tokens + j);
+        kvm_prefetch_l2(log.total_tokens + j);
+      }
       const double2 qs = kvm_ld2(log.start_ms + i), ql = kvm_ld2(log.latency_ms + i);
       const double2 qf = kvm_ld2(log.ttfb_ms + i), qt = kvm_ld2(log.tllt_ms + i);
       const longlong2 qx = kvm_ld2(log.status + i), qc = kvm_ld2(log.completion_tokens + i);
