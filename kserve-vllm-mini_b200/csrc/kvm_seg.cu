@@ -36,7 +36,7 @@ namespace {
 constexpr int SEG_THREADS = 384;      // x 2 CTAs per SM, like the flat one-pass kernel
 constexpr int SEG_WARPS = SEG_THREADS / 32;
 constexpr int SEG_ARENA = KVM_LOG_NSETS * BINS * 4 / 8;   // candidate keys per run: the space of the histograms
-constexpr int SEG_BUCKET_MAX = 2048;  // largest bucket finished by counting
+constexpr int SEG_BUCKET_MAX = SEG_ARENA;  // a bucket may fill the arena (the finish is linear in its size)
 constexpr int SEG_COLD = 256;
 constexpr int SEG_HITQ = 256;   // (row, column) pairs a warp collects before it fetches their values
 constexpr int SEG_DIRECT = 160; // more than this in one iteration (of up to 320): served where found

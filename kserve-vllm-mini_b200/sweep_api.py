@@ -173,3 +173,57 @@ class SweepAnalyzer:
         raws = self.analyze(dlog, run_offsets, cold_times)
         return [report.core_results(raw, len(cold_times[i]) if cold_times is not None else 0)
                 for i, raw in enumerate(raws)]
+
+
+# --------------------------------------------------------------------------- runs across GPUs
+def partition_runs(run_offsets: Sequence[int], world: int) -> List[int]:
+    """Cut `runs` into `world` contiguous groups of whole runs with row counts as even as whole
+    runs allow (configs[2] on 8 GPUs = 512 runs each).  Returns world + 1
+    run indices; group r = runs [cut[r], cut[r+1]).  Deterministic, the same on every rank."""
+    offs = np.asarray(run_offsets, dtype=np.int64)
+    runs = int(offs.shape[0]) - 1
+    total = int(offs[-1] - offs[0]) if runs > 0 else 0
+    cuts = [0]
+    for r in range(1, world):
+        target = offs[0] + (total * r) // world
+        # the run boundary nearest to the ideal cut, never behind the previous cut
+        j = int(np.searchsorted(offs, target, side="left"))
+        if j > 0 and j <= runs and abs(int(offs[j - 1]) - int(target)) <= abs(int(offs[min(j, runs)]) - int(target)):
+            j -= 1
+        cuts.append(max(cuts[-1], min(j, runs)))
+    cuts.append(runs)
+    return cuts
+
+
+def gather_sweep_tables(local: Dict[str, Any], keys: Sequence[str], group=None) -> Dict[str, Any]:
+    """Per-rank sweep tables (run order inside a rank, rank order = run order) -> the whole
+    table on every rank.  Results travel, not data: 8 doubles and 8 flags per run."""
+    import torch.distributed as dist
+    world = dist.get_world_size(group)
+    parts: List[Any] = [None] * world
+    dist.all_gather_object(parts, {"t": {k: np.asarray(local[k]) for k in keys},
+                                   "n": {k: np.asarray(local["is_none"][k]) for k in keys}}, group=group)
+    out: Dict[str, Any] = {k: np.concatenate([p["t"][k] for p in parts]) for k in keys}
+    out["is_none"] = {k: np.concatenate([p["n"][k] for p in parts]) for k in keys}
+    return out
+
+
+class ShardedSweep:
+    """configs[2] on N GPUs: rank r holds the rows of its runs only (whole runs, no collective on
+    the data path) and analyses them with the segmented kernel; the per-run table is gathered."""
+
+    def __init__(self, device: Optional[torch.device] = None, group=None):
+        import torch.distributed as dist
+        self.group = group
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        self.local = SweepAnalyzer(device)
+
+    def my_runs(self, run_offsets: Sequence[int]) -> range:
+        cuts = partition_runs(run_offsets, self.world)
+        return range(cuts[self.rank], cuts[self.rank + 1])
+
+    def sweep_table(self, dlog_local: engine.DeviceLog, local_offsets: Sequence[int],
+                    colds_local: Optional[Sequence[Sequence[float]]] = None) -> Dict[str, Any]:
+        """dlog_local / local_offsets / colds_local describe THIS rank's runs (offsets start at 0)."""
+        t = self.local.sweep_table(dlog_local, local_offsets, colds_local)
+        return gather_sweep_tables(t, SweepAnalyzer.SWEEP_KEYS, self.group)

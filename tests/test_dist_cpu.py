@@ -192,3 +192,55 @@ def test_halo_skips_shards_without_samples():
     assert dist_energy.halo_for_rank(last, 2) == (10.0, 5.0)      # shard 1 had no non-null sample
     assert dist_energy.halo_for_rank(last, 3) == (30.0, 7.0)
     assert dist_energy.rank_ordered_total([(1e16, 1.0), (-1e16, 0.5)]) == 1.5
+
+
+# ---- sweep roll-up across ranks (sweep_api.partition_runs / gather_sweep_tables) ----------------
+def test_partition_runs_whole_runs_balanced_and_ordered():
+    from kvmini_b200 import sweep_api
+    offs = np.arange(4097, dtype=np.int64) * 250_000              # configs[2]
+    assert sweep_api.partition_runs(offs, 8) == [512 * r for r in range(9)]
+    rng = np.random.default_rng(2)
+    sizes = rng.integers(0, 5000, 301)
+    sizes[17] = 0
+    sizes[100] = 400_000                                           # one run larger than an even share
+    offs = np.concatenate([[0], np.cumsum(sizes)])
+    for world in (1, 2, 3, 8):
+        cuts = sweep_api.partition_runs(offs, world)
+        assert len(cuts) == world + 1 and cuts[0] == 0 and cuts[-1] == 301
+        assert all(a <= b for a, b in zip(cuts, cuts[1:]))         # contiguous groups of whole runs, in order
+        rows = [int(offs[b] - offs[a]) for a, b in zip(cuts, cuts[1:])]
+        assert sum(rows) == int(offs[-1])
+        assert max(rows) <= int(offs[-1]) // world + 400_000       # never worse than one run off the even share
+    assert sweep_api.partition_runs([0], 4) == [0, 0, 0, 0, 0]
+    assert sweep_api.partition_runs([0, 10], 4)[-1] == 1
+
+
+def _sweep_worker(rank, world, port, ret):
+    sys.path.insert(0, REPO)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from kvmini_b200 import sweep_api
+    keys = sweep_api.SweepAnalyzer.SWEEP_KEYS
+    offs = np.concatenate([[0], np.cumsum([5, 0, 7, 1000, 3, 900, 2])])
+    cuts = sweep_api.partition_runs(offs, world)
+    mine = range(cuts[rank], cuts[rank + 1])
+    # stand-in for the per-run analysis: a value that names (key, run)
+    local = {k: np.array([1000.0 * i + r for r in mine]) for i, k in enumerate(keys)}
+    local["is_none"] = {k: np.array([(r + i) % 3 == 0 for r in mine], dtype=bool) for i, k in enumerate(keys)}
+    got = sweep_api.gather_sweep_tables(local, keys)
+    runs = len(offs) - 1
+    bad = [k for i, k in enumerate(keys)
+           if got[k].tolist() != [1000.0 * i + r for r in range(runs)]
+           or got["is_none"][k].tolist() != [(r + i) % 3 == 0 for r in range(runs)]]
+    ret[rank] = bad
+    dist.destroy_process_group()
+
+
+def test_sweep_tables_gather_in_run_order_world2_gloo():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    mp.spawn(_sweep_worker, args=(2, port, ret), nprocs=2, join=True)
+    assert dict(ret) == {0: [], 1: []}
