@@ -369,6 +369,81 @@ def cfg5_block(args, device, rank, world, dist, cold):
             "check": {"p50_ms": core["p50_ms"], "p99_ms": core["p99_ms"]}}
 
 
+def sweep_block(args, device, rank, world, dist):
+    """BASELINE.json configs[2] in the driver's own line: whole runs per GPU (SURVEY.md section
+    8e: 4096 runs x 250k rows = 512 runs per GPU at 8 GPUs; `--sweep-runs` per GPU here), generated
+    on the device, analysed by the segmented kernel (kvm_seg_analyze), per-run tables gathered in
+    run order.  Roofline on 56 B/row (every column read once).  Parity: two runs of rank 0 are
+    copied to the host and compared with the oracle, all 8 sweep columns bit for bit."""
+    import numpy as np
+    import torch
+    from kvmini_b200 import engine, sweep_api, synth
+    per, rows = args.sweep_runs, 250_000
+    n = per * rows
+    g = {k: torch.empty(n, dtype=torch.float64, device=device) for k in ("start_ms", "latency_ms", "ttfb_ms", "tllt_ms")}
+    g.update({k: torch.empty(n, dtype=torch.int64, device=device) for k in ("status", "completion_tokens", "total_tokens")})
+    for r0 in range(0, per, 64):
+        r1 = min(per, r0 + 64)
+        gr = rank * per + r0
+        c = synth.request_columns_device(rows * (r1 - r0), device, seed=1000 + gr, span_ms=rows * 25.0 * (r1 - r0),
+                                         mu=5.0 + 1.5 * ((gr * 37) % 100) / 100.0, sigma=0.3 + 0.5 * ((gr * 17) % 100) / 100.0,
+                                         fail_p=0.05 * ((gr * 7) % 100) / 100.0, t_epoch_ms=1.7e12 + gr * rows * 25.0)
+        for k in g:
+            g[k][r0 * rows:r1 * rows] = c[k]
+        del c
+    offs = (np.arange(per + 1, dtype=np.int64) * rows).tolist()
+    starts = g["start_ms"][::rows].cpu().numpy() / 1000.0
+    colds = [[float(starts[r]) + 1.0 + (r % 5)] if r % 3 else [] for r in range(per)]
+    dlog = engine.DeviceLog.from_tensors(g)
+    if dist is not None:
+        sh = sweep_api.ShardedSweep(device)
+        local, table_fn = sh.local, (lambda: sh.sweep_table(dlog, offs, colds))
+    else:
+        local = sweep_api.SweepAnalyzer(device)
+        table_fn = lambda: local.sweep_table(dlog, offs, colds)
+    table_fn()
+    steps, ms_tab, ms_k = 3, 0.0, 0.0
+    for _ in range(steps):
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize(device)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        table = table_fn()
+        e1.record()
+        torch.cuda.synchronize(device)
+        ms_tab += e0.elapsed_time(e1) / steps
+        ms_k += local.last_kernel_ms / steps
+    t = torch.tensor([ms_tab, ms_k], dtype=torch.float64, device=device)
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    out = None
+    if rank == 0:
+        from oracle import np_port   # the checker
+        equal = True
+        for r in (1, per - 1):
+            sub = {k: v[offs[r]:offs[r + 1]].cpu().numpy() for k, v in g.items()}
+            ref = np_port.analyze(sub, colds[r])
+            for k in sweep_api.SweepAnalyzer.SWEEP_KEYS:
+                got = None if bool(table["is_none"][k][r]) else float(table[k][r])
+                equal = equal and (got == ref[k])
+        peak, _ = measured_peaks()
+        tot = n * world
+        out = {"workload": "configs[2]: 4096 runs x 250k rows, whole runs per GPU (runs_per_gpu x n_gpus here)",
+               "runs_per_gpu": per, "runs_total": per * world, "rows_total": tot,
+               "ms_kernel": float(t[1]), "ms_table_incl_host_and_gather": float(t[0]),
+               "records_per_s_kernel": tot / float(t[1]) * 1e3, "records_per_s_table": tot / float(t[0]) * 1e3,
+               "roofline": {"bound": "hbm", "kernel": "seg_analyze", "algorithmic_bytes_per_row": 56,
+                            "achieved_per_gpu": 56.0 * n / float(t[1]) / 1e6, "peak": peak, "unit": "GB/s",
+                            "frac": 56.0 * n / float(t[1]) / 1e6 / peak},
+               "fallback_runs_rank0": local.fallback_runs,
+               "parity": {"method": "runs 1 and runs_per_gpu-1 of rank 0 vs oracle/np_port.analyze, 8 sweep columns, bit for bit",
+                          "equal": bool(equal)}}
+    del g, dlog
+    torch.cuda.empty_cache()
+    return out
+
+
 # --------------------------------------------------------------------------- our arm
 def run_ours(args):
     import numpy as np
@@ -555,6 +630,9 @@ def run_ours(args):
     cfg5 = None
     if world > 1 and not args.no_cfg5:
         cfg5 = cfg5_block(args, device, rank, world, dist, cold)
+    sweep = None
+    if not args.no_sweep:
+        sweep = sweep_block(args, device, rank, world, dist)
     host_all = None
     if rank == 0 and host is not None and not args.no_parity:
         # the whole (sharded) log on the host of rank 0: every shard is regenerated from its seed
@@ -566,7 +644,9 @@ def run_ours(args):
     if rank == 0:
         peak, peak_src = measured_peaks()
         # algorithmic bytes per launch of each streaming kernel (DESIGN.md "Kernels")
-        alg = {"log_scan": 57.0 * n, "select_hist": 49.0 * n, "select_compact": 9.0 * n,
+        # (56 B/row of input read once + the 1 B/row flag output; the 8-byte
+        # digit records the one-pass kernel writes are workspace and earn no credit)
+        alg = {"log_fused": 57.0 * n, "log_scan": 57.0 * n, "select_hist": 49.0 * n, "select_compact": 9.0 * n,
                "select_refine_hist": 9.0 * n}
         kernels = {}
         for name, (ms, cnt) in stage_ms.items():
@@ -625,6 +705,8 @@ def run_ours(args):
             line["parity"] = parity_block(core, report.trim_series(raw), host_all, cold)
         if cfg5 is not None:
             line["cfg5"] = cfg5
+        if sweep is not None:
+            line["sweep"] = sweep
         if world == 1 and not args.no_percentile_path:
             line["percentile_path"] = percentile_path_block(device, peak)
         if world == 1 and not args.no_cpu_baseline and host is not None:
@@ -656,6 +738,8 @@ def main():
     ap.add_argument("--no-parity", action="store_true", help="skip the oracle comparison of the timed log")
     ap.add_argument("--no-cfg5", action="store_true", help="N>1: skip the 1.25e8-rows-per-GPU block")
     ap.add_argument("--cfg5-rows", type=int, default=125_000_000, help="rows per GPU of the cfg5 block")
+    ap.add_argument("--no-sweep", action="store_true", help="skip the configs[2] (sweep roll-up) block")
+    ap.add_argument("--sweep-runs", type=int, default=512, help="runs per GPU of the sweep block (250k rows each)")
     ap.add_argument("--no-percentile-path", action="store_true",
                     help="N=1: skip the 16 B/record percentile-path block")
     ap.add_argument("--port", action="store_true",
