@@ -214,7 +214,7 @@ __device__ __forceinline__ uint64_t fused_row(FAcc& a, FusedCols& S, uint32_t* s
   const uint32_t rlo = d0 | (d1 << 12) | (d2 << 24), rhi = (d2 >> 8) | (d3 << 4) | (d4 << 16);
   uint64_t r = ((uint64_t)rhi << 32) | rlo;
   if (rare) r = fused_fix_sites(S, sh, rare, f, la, tf, tl, ct, r);
-  return r;
+  return r | ((uint64_t)cold_row << 60);   // bit 60 (REC_COLD_BIT): the compact pass needs no flag byte
 }
 
 // Per-thread accumulators -> one warp's row of 64-bit slots (slot layout of kvm_log_device.cuh;

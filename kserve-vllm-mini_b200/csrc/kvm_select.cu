@@ -356,10 +356,10 @@ log_hist_kernel(kvm_request_log log, const uint8_t* __restrict__ flags, SelWs* w
           const double2 la = kvm_ld2(log.latency_ms + i), tf = kvm_ld2(log.ttfb_ms + i);
           const double2 tl = kvm_ld2(log.tllt_ms + i);
           const longlong2 ct = kvm_ld2(log.completion_tokens + i);
-          rec = DIGITS_NONE;
+          rec = rec_blank(f0);
           log_row_keys(f0, la.x, tf.x, tl.x, ct.x, add);
           const uint64_t rec0 = rec;
-          rec = DIGITS_NONE;
+          rec = rec_blank(f1);
           log_row_keys(f1, la.y, tf.y, tl.y, ct.y, add);
           if (digit_records)
             *reinterpret_cast<ulonglong2*>(digit_records + i) = make_ulonglong2(rec0, rec);
@@ -367,7 +367,7 @@ log_hist_kernel(kvm_request_log log, const uint8_t* __restrict__ flags, SelWs* w
           tok1 = ct.y;
         } else {
           const long long ct = kvm_ld1(log.completion_tokens + i);
-          rec = DIGITS_NONE;
+          rec = rec_blank(f0);
           log_row_keys(f0, kvm_ld1(log.latency_ms + i), kvm_ld1(log.ttfb_ms + i), kvm_ld1(log.tllt_ms + i), ct, add);
           if (digit_records) digit_records[i] = rec;
           tok0 = ct;
@@ -410,7 +410,7 @@ log_hist_kernel(kvm_request_log log, const uint8_t* __restrict__ flags, SelWs* w
   if (ROWS == 2 && (n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {  // odd tail row
     const int64_t i = n - 1;
     const uint8_t fl = flags[i];
-    rec = DIGITS_NONE;
+    rec = rec_blank(fl);
     log_row_keys(fl, log.latency_ms[i], log.ttfb_ms[i], log.tllt_ms[i], log.completion_tokens[i], add);
     if (digit_records) digit_records[i] = rec;
     if (SERIES)
@@ -1324,15 +1324,19 @@ log_rec_kernel(kvm_request_log log, const uint8_t* __restrict__ flags,
     for (int k0 = 0; k0 < qn; k0 += 32) {
       const int k = k0 + lane;
       const bool have = k < qn;
-      const int64_t r = have ? Q.row[warp][k] : 0;
+      const int64_t qr = have ? Q.row[warp][k] : 0;
+      const int64_t r = qr & ((1ll << 62) - 1);
+      const bool cold = (qr >> 62) & 1;               // the record carries the row's cold flag
       const uint32_t hm = have ? Q.hitmask[warp][k] : 0u;
-      const uint8_t fl = have ? flags[r] : 0;
-      const bool cold = fl & KVM_F_COLD;
-      double tf = 0.0, tl = 0.0;
+      // every value the row needs is requested before the first is used (one memory latency a batch)
+      double la = 0.0, tf = 0.0, tl = 0.0;
+      long long ct = 1;
+      if (hm & 0x01u) la = log.latency_ms[r];
       if (hm & 0x1Eu) {            // ttfb / tllt feed four of the five columns
         tf = log.ttfb_ms[r];
         tl = log.tllt_ms[r];
       }
+      if (hm & 0x10u) ct = log.completion_tokens[r];
 #pragma unroll 1
       for (int c = 0; c < KVM_LOG_NCOLS; ++c) {
         const bool valid = (hm >> c) & 1u;
@@ -1341,7 +1345,7 @@ log_rec_kernel(kvm_request_log log, const uint8_t* __restrict__ flags,
         int set = 0;
         if (valid) {
           if (c == KVM_COL_LAT) {
-            v = log.latency_ms[r];
+            v = la;
             set = cold ? KVM_SET_LAT_COLD : KVM_SET_LAT_WARM;
           } else if (c == KVM_COL_TTFB) {
             v = tf;
@@ -1353,7 +1357,7 @@ log_rec_kernel(kvm_request_log log, const uint8_t* __restrict__ flags,
             v = tl - tf;                                        // analyze.py:144
             set = KVM_SET_GEN;
           } else {
-            v = (tl - tf) / (double)log.completion_tokens[r];   // analyze.py:146
+            v = (tl - tf) / (double)ct;                         // analyze.py:146
             set = KVM_SET_PERTOK;
           }
         }
@@ -1384,7 +1388,7 @@ log_rec_kernel(kvm_request_log log, const uint8_t* __restrict__ flags,
       if (qn + cnt > CQ_CAP) drain();
       if (hm) {
         const int pos = qn + __popc(hits & lt);
-        Q.row[warp][pos] = r;
+        Q.row[warp][pos] = r | (int64_t)((rec >> REC_COLD_BIT) & 1ull) << 62;
         Q.hitmask[warp][pos] = hm;
       }
       qn += cnt;
@@ -1392,25 +1396,35 @@ log_rec_kernel(kvm_request_log log, const uint8_t* __restrict__ flags,
   };
   const int64_t n = log.n;
   const int64_t nunits = ROWS == 2 ? (n >> 1) : n;
-  for (int64_t base = (int64_t)blockIdx.x * SEL_THREADS + (threadIdx.x & ~31); base < nunits;
-       base += (int64_t)gridDim.x * SEL_THREADS) {
-    const int64_t u = base + lane;
-    const bool live = u < nunits;
-    const int64_t i = ROWS == 2 ? (u << 1) : u;
-    uint64_t r0 = DIGITS_NONE, r1 = DIGITS_NONE;
-    if (live) {
-      if (ROWS == 2) {
-        const longlong2 rr = kvm_ld2(reinterpret_cast<const int64_t*>(recs) + i);
-        r0 = (uint64_t)rr.x;
-        r1 = (uint64_t)rr.y;
-      } else {
-        r0 = kvm_ld1(recs + i);
+  // REC_K units per lane and iteration, all loads issued before the first is used (a warp's load
+  // covers 512 consecutive bytes); a warp takes 32 * REC_K consecutive units
+  constexpr int REC_K = 4;
+  for (int64_t base = ((int64_t)blockIdx.x * (SEL_THREADS / 32) + warp) * (32 * REC_K); base < nunits;
+       base += (int64_t)gridDim.x * SEL_THREADS * REC_K) {
+    uint64_t r0[REC_K], r1[REC_K];
+#pragma unroll
+    for (int k = 0; k < REC_K; ++k) {
+      const int64_t u = base + k * 32 + lane;
+      r0[k] = DIGITS_NONE;
+      r1[k] = DIGITS_NONE;
+      if (u < nunits) {
+        if (ROWS == 2) {
+          const longlong2 rr = kvm_ld2(reinterpret_cast<const int64_t*>(recs) + (u << 1));
+          r0[k] = (uint64_t)rr.x;
+          r1[k] = (uint64_t)rr.y;
+        } else {
+          r0[k] = kvm_ld1(recs + u);
+        }
       }
     }
-    if (!__any_sync(KVM_FULL, (r0 & r1) != DIGITS_NONE)) continue;
-    row(i, r0);
-    if (ROWS == 2) row(i + 1, r1);
-    if (qn >= 32) drain();
+#pragma unroll
+    for (int k = 0; k < REC_K; ++k) {
+      const int64_t u = base + k * 32 + lane;
+      const int64_t i = ROWS == 2 ? (u << 1) : u;
+      if (!__any_sync(KVM_FULL, (r0[k] & r1[k] & DIGITS_NONE) != DIGITS_NONE)) continue;
+      row(i, r0[k]);
+      if (ROWS == 2) row(i + 1, r1[k]);
+    }
   }
   drain();
   if (ROWS == 2 && (n & 1) && blockIdx.x == 0 && threadIdx.x < 32) {  // odd tail row, one warp

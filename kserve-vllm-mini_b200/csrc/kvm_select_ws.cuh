@@ -101,6 +101,10 @@ struct SrcPack {
 };
 
 constexpr uint64_t DIGITS_NONE = 0x0FFFFFFFFFFFFFFFull;  // five 12-bit fields, all "not in a set"
+constexpr int REC_COLD_BIT = 60;                           // bit 60 of a digit record: the row's KVM_F_COLD
+__host__ __device__ __forceinline__ uint64_t rec_blank(uint32_t flags) {
+  return DIGITS_NONE | ((flags & KVM_F_COLD) ? (1ull << REC_COLD_BIT) : 0ull);
+}
 
 struct SeriesArgs {
   const double* start_ms;
