@@ -15,11 +15,13 @@ constexpr int NC = KVM_LOG_NCOLS;
 // Per value column: exact key range so far, the sampled hull, digit parameters.
 struct FusedCols {
   unsigned long long kmin[NC], kmax[NC];     // exact key range of every value column (CTA level)
-  unsigned long long hull_max[NC];           // sampled maximum: keys above it may be a new maximum
   uint64_t kbase[NC];
   int32_t shift[NC];
-  uint4 par[NC];   // fast-path parameters per column: kbase lo / hi word, hull span high word, shift - 32
+  int32_t fast_ok;
+  uint4 par[NC];   // fast-path parameters per column: kbase high word, inside floor, inside width, shift - 32
 };
+
+__device__ __forceinline__ void fused_cols_publish(FusedCols& S, int c);
 
 // u64 min / max on shared memory, called on the rare path only
 __device__ __forceinline__ void range_update(unsigned long long* lo, unsigned long long* hi, uint64_t key) {
@@ -45,6 +47,7 @@ __device__ __noinline__ uint64_t fused_fix_sites(FusedCols& S, uint32_t* sh, uin
     const uint64_t key = kvm_key(v);
     const uint32_t d = digit_of(key, S.kbase[c], S.shift[c]);
     range_update(&S.kmin[c], &S.kmax[c], key);
+    fused_cols_publish(S, c);   // keys below this one are inside from now on
     atomicAdd(&sh[set * BINS + d], 1u);
     r = (r & ~(0xFFFull << (12 * c))) | ((uint64_t)d << (12 * c));
   }
@@ -113,7 +116,10 @@ __device__ __forceinline__ void fused_sample_rows(const kvm_request_log& log, in
 }
 
 // Digit parameters of column c from the sample's hull (inv = complemented sampled minimum, 0:
-// the sample holds no member of the column).  Returns the significant bits of the hull.
+// the sample holds no member of the column).  The bins span the hull widened by an eighth of its
+// width on either side, so that what the sample missed still lands in a bin of its own; for a
+// column wide enough (shift >= 32) the base is rounded down to a multiple of 2^32, which makes a
+// digit a function of the key's HIGH word alone.  Returns the significant bits of the span.
 __device__ __forceinline__ int fused_cols_setup(FusedCols& S, int c, uint64_t inv, uint64_t mx) {
   int width;
   if (inv == 0ull) {   // no member of this column in the sample: coarse bins over all keys
@@ -122,42 +128,61 @@ __device__ __forceinline__ int fused_cols_setup(FusedCols& S, int c, uint64_t in
     width = 64;
     S.kmin[c] = ~0ull;
     S.kmax[c] = 0ull;
-    S.hull_max[c] = 0ull;
   } else {
-    const uint64_t mn = ~inv, range = mx - mn;
-    S.kbase[c] = mn;
-    width = range ? 64 - __clzll((long long)range) : 1;
+    const uint64_t mn = ~inv, margin = (mx - mn) >> 3;
+    uint64_t lo = mn > margin ? mn - margin : 0ull;
+    const uint64_t hi = mx + margin < mx ? ~0ull : mx + margin;
+    if (bit_width64(hi - lo) >= BINS_LOG2 + 32) lo &= ~0xFFFFFFFFull;
+    const uint64_t range = hi - lo;
+    S.kbase[c] = lo;
+    width = range ? bit_width64(range) : 1;
     S.shift[c] = width > BINS_LOG2 ? width - BINS_LOG2 : 0;
     S.kmin[c] = mn;   // sampled values are members: the exact range starts from their hull
     S.kmax[c] = mx;
-    S.hull_max[c] = mx;
   }
   return width;
 }
 
-// Fast-path parameters (shared memory: one 16-byte load per site): with every shift >= 32 a digit
-// is a 32-bit shift of the HIGH word of (key - kbase), and "outside the sampled hull" is one
-// unsigned comparison of that word (a key below kbase wraps to >= 2^31; hulls wider than 2^63
-// keys disable the trick: span word 0).  A column narrower than 2^43 keys (shift < 32) sends
-// every site through the exact (slow) route.  One thread.
-__device__ __forceinline__ void fused_cols_fast_params(FusedCols& S) {
+// Fast-path parameters of column c (shared memory: one 16-byte load per site).  With every shift
+// >= 32 the digit is a 32-bit shift of x = (high word of the key) - (high word of kbase), and a key
+// is "inside" when x lies STRICTLY between the high words of the column's smallest and largest key
+// so far (one subtraction, one unsigned comparison).  Inside keys cannot move the exact range;
+// everything else takes the exact route, which republishes these parameters when it widens the
+// range - so after the sample only record-setting keys (and the two boundary words) are rare.
+// The inside interval never leaves the span of the bins, hence an inside digit needs no clamp.
+__device__ __forceinline__ void fused_cols_publish(FusedCols& S, int c) {
+  uint4 P;
+  P.x = (uint32_t)(S.kbase[c] >> 32);
+  P.y = 0u;
+  P.z = 0u;   // nothing is inside: every site takes the exact route
+  P.w = S.fast_ok ? (uint32_t)(S.shift[c] - 32) : 0u;
+  if (S.fast_ok) {
+    const uint64_t kb = S.kbase[c];
+    const int sh = S.shift[c];
+    const uint64_t cover = sh + BINS_LOG2 >= 64 ? ~0ull : (((uint64_t)BINS << sh) - 1ull);
+    const uint64_t top_key = kb + cover < kb ? ~0ull : kb + cover;
+    const uint64_t kmin = *reinterpret_cast<volatile unsigned long long*>(&S.kmin[c]);
+    const uint64_t kmax = *reinterpret_cast<volatile unsigned long long*>(&S.kmax[c]);
+    const uint64_t lo = kmin > kb ? kmin : kb, hi = kmax < top_key ? kmax : top_key;
+    if (lo <= hi) {
+      const uint64_t a = (lo - kb) >> 32, t = (hi - kb) >> 32;
+      if (t > a + 1) {
+        P.y = (uint32_t)(a + 1);
+        P.z = (uint32_t)(t - a - 1);
+      }
+    }
+  }
+  S.par[c] = P;
+}
+__device__ __forceinline__ void fused_cols_fast_params(FusedCols& S) {   // one thread, after the set-up
   bool fast_ok = true;
   for (int c = 0; c < NC; ++c) fast_ok = fast_ok && S.shift[c] >= 32;
-  for (int c = 0; c < NC; ++c) {
-    const uint64_t kbc = S.kbase[c];
-    const uint64_t hm = S.hull_max[c];
-    const uint64_t span = hm >= kbc ? hm - kbc : 0ull;
-    uint4 P;
-    P.x = (uint32_t)kbc;
-    P.y = (uint32_t)(kbc >> 32);
-    P.z = (!fast_ok || (span >> 63)) ? 0u : (uint32_t)(span >> 32);
-    P.w = fast_ok ? (uint32_t)(S.shift[c] - 32) : 0u;
-    S.par[c] = P;
-  }
+  S.fast_ok = fast_ok ? 1 : 0;
+  for (int c = 0; c < NC; ++c) fused_cols_publish(S, c);
 }
 
-// The fast row: branch-free; sites whose key lies outside the sampled hull are only noted in
-// `rare` and redone exactly by fused_fix_sites (a fraction of a percent of the rows).  Returns
+// The fast row: branch-free; sites whose key is not inside (fused_cols_publish) are only noted in
+// `rare` and redone exactly by fused_fix_sites.  Returns
 // the row's digit record (five 12-bit fields, 0xFFF: not a member of that column).
 __device__ __forceinline__ uint64_t fused_row(FAcc& a, FusedCols& S, uint32_t* sh, const ColdTable& cold,
                                               double cold_first, double cold_last, double st, double la, double tf,
@@ -192,12 +217,12 @@ __device__ __forceinline__ uint64_t fused_row(FAcc& a, FusedCols& S, uint32_t* s
   dd_acc(a.ttfb_s, a.ttfb_e, m_tf ? tf : 0.0);
   uint32_t rare = 0;
   auto site = [&](bool m, uint32_t* hist, int col, double v) -> uint32_t {
-    const uint64_t b = (uint64_t)__double_as_longlong(v);
-    const uint64_t key = b ^ ((uint64_t)((int64_t)b >> 63) | 0x8000000000000000ull);
+    const uint32_t hi = (uint32_t)__double2hiint(v);
+    const uint32_t khi = hi ^ ((uint32_t)((int32_t)hi >> 31) | 0x80000000u);   // high word of the ordered key
     const uint4 P = S.par[col];
-    const uint32_t dhi = (uint32_t)((key - (((uint64_t)P.y << 32) | P.x)) >> 32);
-    const bool out = dhi >= P.z;
-    const uint32_t d = dhi >> P.w;
+    const uint32_t x = khi - P.x;
+    const bool out = (x - P.y) >= P.z;
+    const uint32_t d = x >> P.w;
     if (m && !out) atomicAdd(hist + d, 1u);
     rare |= (m && out) ? (1u << col) : 0u;
     return m ? (out ? 0u : d) : 0xFFFu;

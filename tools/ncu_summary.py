@@ -19,7 +19,9 @@ KEEP = ("gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum
         "smsp__average_warps_issue_stalled_wait_per_issue_active.ratio",
         "smsp__average_warps_issue_stalled_short_scoreboard_per_issue_active.ratio",
         "smsp__average_warps_issue_stalled_barrier_per_issue_active.ratio")
-STAGE = {"log_scan_kernel": "log_scan", "log_hist_kernel": "select_hist", "log_rec_kernel": "select_compact"}
+STAGE = {"log_fused_kernel": "log_fused", "log_scan_kernel": "log_scan", "log_hist_kernel": "select_hist",
+         "log_rec_kernel": "select_compact", "seg_analyze_kernel": "seg_analyze", "qd_hist_kernel": "qd_hist",
+         "qd_collect_kernel": "qd_collect", "qd_rank_kernel": "qd_rank"}
 
 
 def short(name):
