@@ -552,6 +552,11 @@ int kvm_seg_analyze(const kvm_request_log* log_host, const int64_t* run_offsets,
                     void* scratch, size_t scratch_bytes, kvm_log_stats* stats,
                     kvm_query_result* results, int64_t* hist_counts, int32_t* run_status, void* stream);
 
+/* Debug aid: microseconds since the first CTA entered the last one-pass kernel that used this scan
+ * workspace - [0] last CTA set up (sample + parameters), [1] last CTA done streaming, [2] last CTA
+ * flushed its histograms, [3] statistics written.  Synchronises (one small copy). */
+int kvm_log_fused_phase_us(const void* scan_workspace, double* out4);
+
 /* Debug aid: nanoseconds the segmented kernel spent per phase, summed over all runs and CTAs since
  * the last reset - [0] sample + set-up, [1] stream, [2] plan / resolve, [3] records pass,
  * [4] finish + emit.  Synchronises the device. */

@@ -18,6 +18,8 @@
 // Replaces (reference file:line) analyze.py:183-189, :402-419, :496-514, :68,:89,:143 filters,
 // :581, the histogram side of :59-81 / :84-122 (via kvm_select.cu) and extension A12.
 
+#include <cstddef>
+
 #include "kvm_common.cuh"
 #include "kvm_log_device.cuh"
 #include "kvm_fused_row.cuh"
@@ -32,9 +34,22 @@ constexpr int FU_MAX_GRID = 148 * 8;
 
 struct FusedWs {   // lives in the scan workspace (kvm_log_scan_workspace_bytes)
   unsigned int ticket;
-  unsigned int pad[63];
+  unsigned int pad[3];
+  // phase time stamps of the last pass (globaltimer ns; cleared with the ticket): [0] ~first CTA entry
+  // (as ~t), [1] last "sample + set-up done", [2] last "stream done", [3] last "flushed", [4] end
+  unsigned long long dbg[8];
+  // totals of the integer / range slots, accumulated by every CTA with atomics on a cleared block
+  // (minima stored complemented, so that every slot is a sum or a maximum over zero)
+  unsigned long long fin[NMAX_END];
+  unsigned int pad2[2 * (64 - 10 - NMAX_END) + 2];
   uint64_t partial[1];  // [grid][NSLOTS]
 };
+
+__device__ __forceinline__ unsigned long long fu_now() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
 
 struct FusedSeries {
   double window_ms;
@@ -66,7 +81,7 @@ __global__ void __launch_bounds__(512) fused_sample_kernel(kvm_request_log log, 
     s_inv[c] = 0ull;
     s_mx[c] = 0ull;
   }
-  fused_sample_rows(log, t, 512, s_inv, s_mx, s_st);
+  fused_sample_rows<512>(log, t, 512, s_inv, s_mx, s_st);
 #pragma unroll
   for (int c = 0; c < NC; ++c) {
     const uint64_t a = kvm_warp_max(s_inv[c]), b = kvm_warp_max(s_mx[c]);
@@ -123,6 +138,7 @@ log_fused_kernel(kvm_request_log log, const double* __restrict__ cold_lo_g, cons
   FusedSmem& S = *reinterpret_cast<FusedSmem*>(fraw + sizeof(uint32_t) * KVM_LOG_NSETS * BINS);
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const int64_t n = log.n;
+  if (t == 0) atomicMax(&fws->dbg[0], ~fu_now());
 
   // ---- sample: 512 rows, the same in every CTA (or, for a sharded log, the hull that all ranks
   // have agreed on before the pass: `preset`)
@@ -134,7 +150,7 @@ log_fused_kernel(kvm_request_log log, const double* __restrict__ cold_lo_g, cons
     s_inv[c] = 0ull;
     s_mx[c] = 0ull;
   }
-  if (!use_preset) fused_sample_rows(log, t, FU_THREADS, s_inv, s_mx, s_st);
+  if (!use_preset) fused_sample_rows<FU_THREADS>(log, t, FU_THREADS, s_inv, s_mx, s_st);   // one row per thread
   // (shared memory set-up overlaps the sample's loads)
   for (int i = t; i < KVM_LOG_NSETS * BINS; i += FU_THREADS) sh[i] = 0;
   ColdTable cold{COLD_SMEM_TABLE ? S.cold_lo : cold_lo_g, COLD_SMEM_TABLE ? S.cold_hi : cold_hi_g, nc};
@@ -183,6 +199,7 @@ log_fused_kernel(kvm_request_log log, const double* __restrict__ cold_lo_g, cons
   __syncthreads();
   if (t == 0) fused_cols_fast_params(S.fc);
   __syncthreads();
+  if (t == 0) atomicMax(&fws->dbg[1], fu_now());
   const double s0 = S.series_ref;
   const double cold_first = nc > 0 ? cold.lo[0] : 0.0, cold_last = nc > 0 ? cold.hi[nc - 1] : -1.0;
 
@@ -287,6 +304,7 @@ log_fused_kernel(kvm_request_log log, const double* __restrict__ cold_lo_g, cons
   // ---- per-thread accumulators -> warp -> CTA partial (slot layout of kvm_log_device.cuh)
   facc_warp_reduce(a, S.red[warp], lane);
   __syncthreads();
+  if (t == 0) atomicMax(&fws->dbg[2], fu_now());
   // flush the histograms (64-bit global atomics on the non-zero bins) and count the sets on the way
   {
     uint32_t setsum[KVM_LOG_NSETS];
@@ -320,7 +338,11 @@ log_fused_kernel(kvm_request_log log, const double* __restrict__ cold_lo_g, cons
       acc = S.red[0][s];
       for (int w = 1; w < FU_WARPS; ++w) acc = combine(s, acc, S.red[w][s]);
     }
-    mine[s] = acc;
+    if (s < NSUM) {
+      if (acc) atomicAdd(&fws->fin[s], (unsigned long long)acc);
+    } else {
+      atomicMax(&fws->fin[s], (unsigned long long)(s < NMIN_END ? ~acc : acc));
+    }
   } else if (t == NMAX_END || t == NMAX_END + 1) {
     const int s = t == NMAX_END ? D_TTFB : D_LAT;
     kvm_dd acc = dd_bits(S.red[0][s], S.red[0][s + 1]);
@@ -330,30 +352,29 @@ log_fused_kernel(kvm_request_log log, const double* __restrict__ cold_lo_g, cons
   }
   __threadfence();
   __syncthreads();
+  if (t == 0) atomicMax(&fws->dbg[3], fu_now());
   if (t == 0) S.is_last = atomicAdd(&fws->ticket, 1u) == gridDim.x - 1;
   __syncthreads();
   if (!S.is_last) return;
   __threadfence();
-  // ---- last CTA: fixed-shape reduction over the CTA partials (see kvm_stats.cu)
+  // ---- last CTA: the integer / range totals are complete; the two double-double sums are added
+  // in a fixed shape over the CTA partials (the same bits whatever order the CTAs finished in)
   const uint64_t* part = fws->partial;
-  for (int s = warp; s < NSLOTS; s += FU_WARPS) {
-    if (s < NMAX_END) {
-      uint64_t acc = s < NSUM ? 0ull : (s < NMIN_END ? ~0ull : 0ull);
-      for (unsigned g = lane; g < gridDim.x; g += 32) acc = combine(s, acc, __ldcg(part + (size_t)g * NSLOTS + s));
-#pragma unroll
-      for (int m = 16; m; m >>= 1) acc = combine(s, acc, kvm_shfl_xor(acc, m));
-      if (lane == 0) S.fin[s] = acc;
-    } else if (s == D_TTFB || s == D_LAT) {
-      kvm_dd acc{0.0, 0.0};
-      for (unsigned g = lane; g < gridDim.x; g += 32) {
-        const size_t o = (size_t)g * NSLOTS + s;
-        acc = kvm_dd_add(acc, dd_bits(__ldcg(part + o), __ldcg(part + o + 1)));
-      }
-      acc = kvm_warp_sum(acc);
-      if (lane == 0) {
-        S.fin[s] = (uint64_t)__double_as_longlong(acc.hi);
-        S.fin[s + 1] = (uint64_t)__double_as_longlong(acc.lo);
-      }
+  if (t < NMAX_END) {
+    const unsigned long long v = __ldcg(&fws->fin[t]);
+    S.fin[t] = (t >= NSUM && t < NMIN_END) ? ~v : v;
+  }
+  if (warp < 2) {
+    const int s = warp == 0 ? D_TTFB : D_LAT;
+    kvm_dd acc{0.0, 0.0};
+    for (unsigned g = lane; g < gridDim.x; g += 32) {
+      const size_t o = (size_t)g * NSLOTS + s;
+      acc = kvm_dd_add(acc, dd_bits(__ldcg(part + o), __ldcg(part + o + 1)));
+    }
+    acc = kvm_warp_sum(acc);
+    if (lane == 0) {
+      S.fin[s] = (uint64_t)__double_as_longlong(acc.hi);
+      S.fin[s + 1] = (uint64_t)__double_as_longlong(acc.lo);
     }
   }
   __syncthreads();
@@ -362,6 +383,7 @@ log_fused_kernel(kvm_request_log log, const double* __restrict__ cold_lo_g, cons
     stats_from_slots(S.fin, n, r);
     *out = r;
     fws->ticket = 0;
+    fws->dbg[4] = fu_now();
   }
 }
 
@@ -374,10 +396,22 @@ __global__ void fused_cold_table_kernel(const double* __restrict__ cold_times, i
 }
 
 constexpr int FU_MAX_COLD = 16384;
-size_t fused_partials_bytes() { return kvm_align_up(256 + sizeof(uint64_t) * (size_t)NSLOTS * FU_MAX_GRID, 256); }
+size_t fused_partials_bytes() { return kvm_align_up(offsetof(FusedWs, partial) + sizeof(uint64_t) * (size_t)NSLOTS * FU_MAX_GRID, 256); }
 bool aligned_to(const void* p, uintptr_t a) { return (reinterpret_cast<uintptr_t>(p) & (a - 1)) == 0; }
 
 }  // namespace
+
+// debug aid: microseconds since the first CTA entered the last one-pass kernel that used this scan
+// workspace - [0] last CTA set up, [1] last CTA streamed, [2] last CTA flushed, [3] statistics out
+extern "C" int kvm_log_fused_phase_us(const void* scan_workspace, double* out4) {
+  KVM_REQUIRE(scan_workspace && out4, "kvm_log_fused_phase_us: null argument");
+  unsigned long long h[8];
+  KVM_CUDA_CHECK(cudaMemcpy(h, reinterpret_cast<const unsigned char*>(scan_workspace) + offsetof(FusedWs, dbg), sizeof(h),
+                            cudaMemcpyDeviceToHost));
+  const unsigned long long t0 = ~h[0];
+  for (int i = 0; i < 4; ++i) out4[i] = (double)(long long)(h[i + 1] - t0) / 1000.0;
+  return KVM_OK;
+}
 
 extern "C" size_t kvm_log_analyze_fused_scan_workspace_bytes(void) {
   return fused_partials_bytes() + 2 * sizeof(double) * (size_t)FU_MAX_COLD;
@@ -465,7 +499,7 @@ static int fused_pass_impl(const kvm_request_log* log, const double* cold_times,
   SelWs* ws = reinterpret_cast<SelWs*>(select_workspace);
   double* cold_lo = reinterpret_cast<double*>(reinterpret_cast<unsigned char*>(scan_workspace) + fused_partials_bytes());
   double* cold_hi = cold_lo + FU_MAX_COLD;
-  KVM_CUDA_CHECK(cudaMemsetAsync(fws, 0, 256, st));
+  KVM_CUDA_CHECK(cudaMemsetAsync(fws, 0, offsetof(FusedWs, partial), st));
   KVM_CUDA_CHECK(cudaMemsetAsync(&ws->hist[0][0], 0, sizeof(ws->hist), st));
   FusedSeries sa{};
   if (series) {

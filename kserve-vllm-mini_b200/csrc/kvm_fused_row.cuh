@@ -76,22 +76,24 @@ __device__ __forceinline__ void dd_acc(double& s, double& e, double x) {
   s = t;
 }
 
-// The 512-row sample: 16 regions spread evenly over the log (the first row and the last row
-// included), 32 pseudo-random rows inside a 4096-row window of each.  Per value column the
+// The NSAMPLE-row sample (a multiple of 32, at least 64): NSAMPLE / 32 regions spread evenly over
+// the log (the first row and the last row included), 32 pseudo-random rows inside a 4096-row
+// window of each.  Per value column the
 // complemented minimum and the maximum key of the sampled MEMBERS (0 / 0: none), and the minimum
 // sampled start_ms.  Thread t of `nthreads` takes rows t, t + nthreads, ...
 constexpr int FU_PRESET_WORDS = 2 * NC + 1;   // [inv_min[NC] | max[NC] | bits of the start reference]
+template <int NSAMPLE>
 __device__ __forceinline__ void fused_sample_rows(const kvm_request_log& log, int t, int nthreads,
                                                   uint64_t (&s_inv)[NC], uint64_t (&s_mx)[NC], double& s_st) {
   const int64_t n = log.n;
   if (n < 1) return;
   const int64_t win = n < 4096 ? n : 4096;
-  for (int sidx = t; sidx < 512; sidx += nthreads) {
+  for (int sidx = t; sidx < NSAMPLE; sidx += nthreads) {
     const int64_t region = sidx >> 5;
-    const int64_t off = n > win ? region * ((n - win) / 15) : 0;
+    const int64_t off = n > win ? region * ((n - win) / (NSAMPLE / 32 - 1)) : 0;
     int64_t i = off + (int64_t)(((uint32_t)sidx * 2654435761u >> 7) % (uint32_t)win);
     if (sidx == 0) i = 0;
-    if (sidx == 511) i = n - 1;
+    if (sidx == NSAMPLE - 1) i = n - 1;
     const double la = __ldg(log.latency_ms + i), tf = __ldg(log.ttfb_ms + i), tl = __ldg(log.tllt_ms + i);
     const double st = __ldg(log.start_ms + i);
     const bool ok = __ldg(log.status + i) == 200;

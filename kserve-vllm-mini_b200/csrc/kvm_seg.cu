@@ -181,7 +181,7 @@ seg_analyze_kernel(kvm_request_log log, const int64_t* __restrict__ run_offsets,
       s_inv[c] = 0ull;
       s_mx[c] = 0ull;
     }
-    fused_sample_rows(sub, tid, SEG_THREADS, s_inv, s_mx, s_st);
+    fused_sample_rows<512>(sub, tid, SEG_THREADS, s_inv, s_mx, s_st);
     ColdTable cold{S.cold_lo, S.cold_hi, 0};
     bool cold_too_many = false;
     if (cold_offsets) {
