@@ -18,6 +18,7 @@
 // Replaces (reference file:line) analyze.py:183-189, :402-419, :496-514, :68,:89,:143 filters,
 // :581, the histogram side of :59-81 / :84-122 (via kvm_select.cu) and extension A12.
 
+#include <algorithm>
 #include <cstddef>
 
 #include "kvm_common.cuh"
@@ -42,7 +43,7 @@ struct FusedWs {   // lives in the scan workspace (kvm_log_scan_workspace_bytes)
   // (minima stored complemented, so that every slot is a sum or a maximum over zero)
   unsigned long long fin[NMAX_END];
   unsigned int pad2[2 * (64 - 10 - NMAX_END) + 2];
-  uint64_t partial[1];  // [grid][NSLOTS]
+  alignas(16) uint64_t partial[1];  // [grid][NSLOTS]
 };
 
 __device__ __forceinline__ unsigned long long fu_now() {
@@ -138,7 +139,6 @@ log_fused_kernel(kvm_request_log log, const double* __restrict__ cold_lo_g, cons
   FusedSmem& S = *reinterpret_cast<FusedSmem*>(fraw + sizeof(uint32_t) * KVM_LOG_NSETS * BINS);
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const int64_t n = log.n;
-  if (t == 0) atomicMax(&fws->dbg[0], ~fu_now());
 
   // ---- sample: 512 rows, the same in every CTA (or, for a sharded log, the hull that all ranks
   // have agreed on before the pass: `preset`)
@@ -154,7 +154,8 @@ log_fused_kernel(kvm_request_log log, const double* __restrict__ cold_lo_g, cons
   // (shared memory set-up overlaps the sample's loads)
   for (int i = t; i < KVM_LOG_NSETS * BINS; i += FU_THREADS) sh[i] = 0;
   ColdTable cold{COLD_SMEM_TABLE ? S.cold_lo : cold_lo_g, COLD_SMEM_TABLE ? S.cold_hi : cold_hi_g, nc};
-  kvm_pdl_wait();   // the cold-interval table is written by the kernel in front of this one
+  kvm_pdl_wait();   // the cold-interval table is written (and the accumulators cleared) by the kernel in front
+  if (t == 0) atomicMax(&fws->dbg[0], ~fu_now());
   if (COLD_SMEM_TABLE)
     for (int i = t; i < nc; i += FU_THREADS) {
       S.cold_lo[i] = cold_lo_g[i];
@@ -387,12 +388,24 @@ log_fused_kernel(kvm_request_log log, const double* __restrict__ cold_lo_g, cons
   }
 }
 
-// One thread per cold start: the closed start_ms interval that the reference classifies cold.
-__global__ void fused_cold_table_kernel(const double* __restrict__ cold_times, int nc, double window,
-                                        double* __restrict__ lo, double* __restrict__ hi) {
+// The launch in front of the pass: one thread per cold start turns it into the closed start_ms
+// interval that the reference classifies cold, and the whole grid clears what the pass accumulates
+// into - the header of the scan workspace, the select's histograms, the window series - in place
+// of four memset nodes.  The pass is a programmatic dependent launch behind it: its sample and its
+// shared-memory set-up run while this kernel drains.
+__global__ void __launch_bounds__(256)
+fused_prep_kernel(const double* __restrict__ cold_times, int nc, double window, double* __restrict__ lo,
+                  double* __restrict__ hi, uint4* __restrict__ header, int header_words16, uint4* __restrict__ hist,
+                  int hist_words16, unsigned long long* __restrict__ series, int64_t series_words,
+                  unsigned long long* __restrict__ dropped) {
   kvm_pdl_launch_dependents();
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (int64_t)gridDim.x * blockDim.x;
+  const uint4 z = make_uint4(0u, 0u, 0u, 0u);
   if (i < nc) cold_interval(cold_times[i], window, lo + i, hi + i);
+  if (i < header_words16) header[i] = z;
+  for (int64_t k = i; k < hist_words16; k += stride) hist[k] = z;
+  for (int64_t k = i; k < series_words; k += stride) series[k] = 0ull;
+  if (dropped && i < 3) dropped[i] = 0ull;
 }
 
 constexpr int FU_MAX_COLD = 16384;
@@ -499,19 +512,24 @@ static int fused_pass_impl(const kvm_request_log* log, const double* cold_times,
   SelWs* ws = reinterpret_cast<SelWs*>(select_workspace);
   double* cold_lo = reinterpret_cast<double*>(reinterpret_cast<unsigned char*>(scan_workspace) + fused_partials_bytes());
   double* cold_hi = cold_lo + FU_MAX_COLD;
-  KVM_CUDA_CHECK(cudaMemsetAsync(fws, 0, offsetof(FusedWs, partial), st));
-  KVM_CUDA_CHECK(cudaMemsetAsync(&ws->hist[0][0], 0, sizeof(ws->hist), st));
   FusedSeries sa{};
+  int64_t series_words = 0;
   if (series) {
     sa.window_ms = extras->series_window_ms;
     sa.max_bins = extras->series_max_bins;
     sa.series = reinterpret_cast<unsigned long long*>(extras->series);
     sa.dropped = reinterpret_cast<unsigned long long*>(extras->series_dropped);
-    KVM_CUDA_CHECK(cudaMemsetAsync(extras->series, 0, sizeof(int64_t) * 3 * (size_t)extras->series_max_bins, st));
-    KVM_CUDA_CHECK(cudaMemsetAsync(extras->series_dropped, 0, 3 * sizeof(int64_t), st));
+    series_words = 3 * (int64_t)extras->series_max_bins;
   }
-  if (n_cold > 0)
-    fused_cold_table_kernel<<<(n_cold + 127) / 128, 128, 0, st>>>(cold_times, n_cold, cold_window_s, cold_lo, cold_hi);
+  {
+    static_assert(offsetof(FusedWs, partial) % 16 == 0 && sizeof(ws->hist) % 16 == 0, "cleared with 16-byte stores");
+    const int64_t items = std::max<int64_t>(std::max<int64_t>(n_cold, (int64_t)(sizeof(ws->hist) / 16)), series_words / 4);
+    const int grid = (int)std::min<int64_t>((items + 255) / 256, 2 * (int64_t)kvm_num_sms());
+    fused_prep_kernel<<<grid < 1 ? 1 : grid, 256, 0, st>>>(
+        cold_times, (int)n_cold, cold_window_s, cold_lo, cold_hi, reinterpret_cast<uint4*>(fws),
+        (int)(offsetof(FusedWs, partial) / 16), reinterpret_cast<uint4*>(&ws->hist[0][0]), (int)(sizeof(ws->hist) / 16),
+        sa.series, series_words, sa.dropped);
+  }
   const size_t smem = sizeof(uint32_t) * KVM_LOG_NSETS * BINS + sizeof(FusedSmem);
   int grid = kvm_grid_for(log->n, FU_THREADS * 2 * 4, 2);
   if (grid > FU_MAX_GRID) grid = FU_MAX_GRID;
@@ -524,7 +542,7 @@ static int fused_pass_impl(const kvm_request_log* log, const double* cold_times,
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = n_cold > 0 ? 1 : 0;   // behind the cold-table kernel: the sample overlaps it
+  cfg.numAttrs = 1;   // behind the prep kernel: the sample and the set-up overlap it
   uint64_t* recs = reinterpret_cast<uint64_t*>(extras->digit_records);
   const double* lo_c = cold_lo;
   const double* hi_c = cold_hi;
