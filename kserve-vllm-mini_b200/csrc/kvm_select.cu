@@ -1465,9 +1465,10 @@ column_compact_kernel(const double* __restrict__ values, int64_t n, int mode,
 constexpr int FIN_THREADS = 1024;
 constexpr int FIN_BITS = 11;
 constexpr int FIN_BINS = 1 << FIN_BITS;
-constexpr int FIN_SMALL = 1024;  // candidates ranked by counting once this few remain
+constexpr int FIN_SMALL = 128;   // candidates ranked by counting once this few remain (counting is quadratic)
+constexpr int FIN_SURV = 2048;   // candidates gathered into a list of their own once this few remain
 constexpr int HIST_CTAS = 16;    // extra CTAs that assemble the value histograms
-constexpr int FIN_CACHE = 16384;  // bucket keys kept in shared memory (128 KB) by the finish
+constexpr int FIN_CACHE = 24576;  // bucket keys kept in shared memory (192 KB) by the finish
 
 // CTAs 0..MAXQ-1: one query each - radix select inside the query's bucket, FIN_BITS per pass,
 // switching to rank-by-counting in shared memory once <= FIN_SMALL candidates remain.
@@ -1477,7 +1478,6 @@ select_finish_kernel(SelWs* ws, SrcPack src, const int64_t* __restrict__ src_cou
                      kvm_query_result* __restrict__ results, int64_t* __restrict__ hist_out) {
   __shared__ uint32_t hist[FIN_BINS];
   __shared__ uint32_t chunk_sum[FIN_THREADS];
-  __shared__ uint64_t small[FIN_SMALL];
   __shared__ uint32_t sel_digit, sel_count, small_n;
   __shared__ int64_t sel_below;
   __shared__ uint64_t answer;
@@ -1562,39 +1562,51 @@ select_finish_kernel(SelWs* ws, SrcPack src, const int64_t* __restrict__ src_cou
   int64_t resid = s.resid;
   int64_t live = b.count;   // candidates matching the prefix
   bool done = false;
+  // Once few enough candidates match the prefix they are gathered into a list of their own (two
+  // lists, used in turn): every later pass touches the survivors only, and a key repeated many
+  // times costs its count per pass instead of the whole bucket.
+  // (list 0 is an array of its own, list 1 reuses the start of the key cache, which is dead once
+  // list 0 has been gathered from it)
+  __shared__ uint64_t surv0[FIN_SURV];
+  uint64_t* const surv[2] = {surv0, kcache};
+  int cur = -1;             // list holding exactly the candidates that match the prefix (-1: none yet)
+  int curn = 0;
 
   while (rem > 0 && !done) {
-    if (live <= FIN_SMALL) {
-      // gather the survivors and rank by counting
+    if (live <= FIN_SURV && (cur < 0 || live < curn)) {
+      const int nxt = cur < 0 ? 0 : cur ^ 1;
       if (threadIdx.x == 0) small_n = 0;
       __syncthreads();
-      if (ncache >= 0) {
-        for (int i = threadIdx.x; i < ncache; i += FIN_THREADS) {
-          const uint64_t k = kcache[i];
-          if (shr64(k - b.base, rem) == prefix) {
-            const uint32_t p = atomicAdd(&small_n, 1u);
-            if (p < FIN_SMALL) small[p] = k;
-          }
+      auto take = [&](uint64_t k) {
+        if (shr64(k - b.base, rem) == prefix) {
+          const uint32_t p = atomicAdd(&small_n, 1u);
+          if (p < (uint32_t)FIN_SURV) surv[nxt][p] = k;
         }
-      } else
-      for (int sidx = 0; sidx < src.nsrc; ++sidx) {
-        const int64_t cnt = src_counts[(size_t)sidx * MAXQ + s.bucket];
-        const uint64_t* __restrict__ keys = src.arena[sidx] + off;
-        for (int64_t i = threadIdx.x; i < cnt; i += FIN_THREADS) {
-          const uint64_t k = keys[i];
-          if (shr64(k - b.base, rem) == prefix) {
-            const uint32_t p = atomicAdd(&small_n, 1u);
-            if (p < FIN_SMALL) small[p] = k;
-          }
+      };
+      if (cur >= 0) {
+        for (int i = threadIdx.x; i < curn; i += FIN_THREADS) take(surv[cur][i]);
+      } else if (ncache >= 0) {
+        for (int i = threadIdx.x; i < ncache; i += FIN_THREADS) take(kcache[i]);
+      } else {
+        for (int sidx = 0; sidx < src.nsrc; ++sidx) {
+          const int64_t cnt = src_counts[(size_t)sidx * MAXQ + s.bucket];
+          const uint64_t* __restrict__ keys = src.arena[sidx] + off;
+          for (int64_t i = threadIdx.x; i < cnt; i += FIN_THREADS) take(keys[i]);
         }
       }
       __syncthreads();
-      const uint32_t m = small_n < FIN_SMALL ? small_n : FIN_SMALL;
+      cur = nxt;
+      curn = (int)(small_n < (uint32_t)FIN_SURV ? small_n : (uint32_t)FIN_SURV);
+      __syncthreads();
+    }
+    if (cur >= 0 && curn <= FIN_SMALL) {
+      // rank by counting among the survivors
+      const uint32_t m = (uint32_t)curn;
       for (uint32_t i = threadIdx.x; i < m; i += FIN_THREADS) {
-        const uint64_t k = small[i];
+        const uint64_t k = surv[cur][i];
         uint32_t less = 0, leq = 0;
         for (uint32_t j = 0; j < m; ++j) {
-          const uint64_t o = small[j];
+          const uint64_t o = surv[cur][j];
           less += o < k;
           leq += o <= k;
         }
@@ -1604,12 +1616,15 @@ select_finish_kernel(SelWs* ws, SrcPack src, const int64_t* __restrict__ src_cou
       done = true;
       break;
     }
-    const int take = rem < FIN_BITS ? rem : FIN_BITS;
-    const int sh = rem - take;
-    const uint32_t dmask = (1u << take) - 1u;
+    const int take_bits = rem < FIN_BITS ? rem : FIN_BITS;
+    const int sh = rem - take_bits;
+    const uint32_t dmask = (1u << take_bits) - 1u;
     for (int i = threadIdx.x; i < FIN_BINS; i += FIN_THREADS) hist[i] = 0;
     __syncthreads();
-    if (ncache >= 0) {
+    if (cur >= 0) {
+      for (int i = threadIdx.x; i < curn; i += FIN_THREADS)
+        atomicAdd(&hist[(uint32_t)((surv[cur][i] - b.base) >> sh) & dmask], 1u);
+    } else if (ncache >= 0) {
       for (int i = threadIdx.x; i < ncache; i += FIN_THREADS) {
         const uint64_t low = kcache[i] - b.base;
         if (shr64(low, rem) == prefix) atomicAdd(&hist[(uint32_t)(low >> sh) & dmask], 1u);
@@ -1671,7 +1686,7 @@ select_finish_kernel(SelWs* ws, SrcPack src, const int64_t* __restrict__ src_cou
       }
     }
     __syncthreads();
-    prefix = (prefix << take) | sel_digit;
+    prefix = (prefix << take_bits) | sel_digit;
     resid -= sel_below;
     live = sel_count;
     rem = sh;
