@@ -195,16 +195,30 @@ def partition_runs(run_offsets: Sequence[int], world: int) -> List[int]:
     return cuts
 
 
-def gather_sweep_tables(local: Dict[str, Any], keys: Sequence[str], group=None) -> Dict[str, Any]:
+def gather_sweep_tables(local: Dict[str, Any], keys: Sequence[str], counts: Sequence[int],
+                        device: Optional[torch.device] = None, group=None) -> Dict[str, Any]:
     """Per-rank sweep tables (run order inside a rank, rank order = run order) -> the whole
-    table on every rank.  Results travel, not data: 8 doubles and 8 flags per run."""
+    table on every rank.  Results travel, not data: 8 doubles and 8 flags per run, as ONE
+    float64 tensor per rank (padded to the largest group; `counts[r]` = runs of rank r, known to
+    every rank from partition_runs) through one all-gather."""
     import torch.distributed as dist
-    world = dist.get_world_size(group)
-    parts: List[Any] = [None] * world
-    dist.all_gather_object(parts, {"t": {k: np.asarray(local[k]) for k in keys},
-                                   "n": {k: np.asarray(local["is_none"][k]) for k in keys}}, group=group)
-    out: Dict[str, Any] = {k: np.concatenate([p["t"][k] for p in parts]) for k in keys}
-    out["is_none"] = {k: np.concatenate([p["n"][k] for p in parts]) for k in keys}
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    nk, width = len(keys), max(1, max(counts))
+    mine = np.zeros((2 * nk, width), dtype=np.float64)
+    for i, k in enumerate(keys):
+        mine[i, :counts[rank]] = np.asarray(local[k], dtype=np.float64)
+        mine[nk + i, :counts[rank]] = np.asarray(local["is_none"][k], dtype=np.float64)
+    dev = device if device is not None else torch.device("cpu")
+    loc = torch.from_numpy(mine).to(dev)
+    allv = torch.empty((world,) + tuple(loc.shape), dtype=torch.float64, device=dev)
+    if dev.type == "cuda":
+        dist.all_gather_into_tensor(allv.view(-1), loc.view(-1), group=group)
+    else:
+        dist.all_gather(list(allv.unbind(0)), loc, group=group)
+    allv = allv.cpu().numpy()
+    out: Dict[str, Any] = {k: np.concatenate([allv[r, i, :counts[r]] for r in range(world)]) for i, k in enumerate(keys)}
+    out["is_none"] = {k: np.concatenate([allv[r, nk + i, :counts[r]] for r in range(world)]) != 0.0
+                      for i, k in enumerate(keys)}
     return out
 
 
@@ -223,7 +237,12 @@ class ShardedSweep:
         return range(cuts[self.rank], cuts[self.rank + 1])
 
     def sweep_table(self, dlog_local: engine.DeviceLog, local_offsets: Sequence[int],
-                    colds_local: Optional[Sequence[Sequence[float]]] = None) -> Dict[str, Any]:
-        """dlog_local / local_offsets / colds_local describe THIS rank's runs (offsets start at 0)."""
+                    colds_local: Optional[Sequence[Sequence[float]]] = None,
+                    counts: Optional[Sequence[int]] = None) -> Dict[str, Any]:
+        """dlog_local / local_offsets / colds_local describe THIS rank's runs (offsets start at 0).
+        counts[r] = number of runs of rank r (from partition_runs; default: every rank holds as
+        many runs as this one)."""
         t = self.local.sweep_table(dlog_local, local_offsets, colds_local)
-        return gather_sweep_tables(t, SweepAnalyzer.SWEEP_KEYS, self.group)
+        if counts is None:
+            counts = [len(local_offsets) - 1] * self.world
+        return gather_sweep_tables(t, SweepAnalyzer.SWEEP_KEYS, counts, self.local.device, self.group)

@@ -38,7 +38,9 @@ def main():
         lo, hi = int(offsets[mine.start]), int(offsets[mine.stop])
         local_cols = {k: torch.from_numpy(np.ascontiguousarray(v[lo:hi])).to(dev) for k, v in cols.items()}
         local_offs = (np.asarray(offsets[mine.start:mine.stop + 1]) - lo).tolist()
-        got = sh.sweep_table(engine.DeviceLog.from_tensors(local_cols), local_offs, colds[mine.start:mine.stop])
+        cuts = sweep_api.partition_runs(offsets, world)
+        got = sh.sweep_table(engine.DeviceLog.from_tensors(local_cols), local_offs, colds[mine.start:mine.stop],
+                             counts=[cuts[r + 1] - cuts[r] for r in range(world)])
         if rank == 0:
             whole = {k: torch.from_numpy(v).to(dev) for k, v in cols.items()}
             exp = sweep_api.SweepAnalyzer(dev).sweep_table(engine.DeviceLog.from_tensors(whole), offsets.tolist(), colds)

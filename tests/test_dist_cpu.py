@@ -227,7 +227,7 @@ def _sweep_worker(rank, world, port, ret):
     # stand-in for the per-run analysis: a value that names (key, run)
     local = {k: np.array([1000.0 * i + r for r in mine]) for i, k in enumerate(keys)}
     local["is_none"] = {k: np.array([(r + i) % 3 == 0 for r in mine], dtype=bool) for i, k in enumerate(keys)}
-    got = sweep_api.gather_sweep_tables(local, keys)
+    got = sweep_api.gather_sweep_tables(local, keys, [cuts[r + 1] - cuts[r] for r in range(world)])
     runs = len(offs) - 1
     bad = [k for i, k in enumerate(keys)
            if got[k].tolist() != [1000.0 * i + r for r in range(runs)]
