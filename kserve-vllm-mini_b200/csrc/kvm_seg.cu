@@ -38,8 +38,8 @@ constexpr int SEG_WARPS = SEG_THREADS / 32;
 constexpr int SEG_ARENA = KVM_LOG_NSETS * BINS * 4 / 8;   // candidate keys per run: the space of the histograms
 constexpr int SEG_BUCKET_MAX = SEG_ARENA;  // a bucket may fill the arena (the finish is linear in its size)
 constexpr int SEG_COLD = 256;
-constexpr int SEG_HITQ = 256;   // (row, column) pairs a warp collects before it fetches their values
-constexpr int SEG_DIRECT = 160; // more than this in one iteration (of up to 320): served where found
+constexpr int SEG_HITQ = 128;   // (row, column) pairs a warp collects before it fetches their values
+constexpr int SEG_DIRECT = 96;  // more than this in one iteration (of up to 320): served where found
 constexpr int SEG_RK = 4;       // row pairs per lane and iteration of the records pass
 constexpr int SEG_MAXQ = KVM_MAX_QUERIES;
 constexpr int SEG_NB_MAX = 64;
@@ -68,7 +68,7 @@ struct SegSmem {
   uint32_t cnt20[NH][SEG_NB_MAX];
   uint32_t flag20[NH][BINS / 32];
   uint32_t bmap[NC][BINS / 32];
-  uint32_t anyhit[NC][2 * BINS / 32];         // bmap | flag20, 4096 bits: a 12-bit record field indexes it unchecked
+  uint8_t hit8[NC][2 * BINS];                 // bmap | flag20 as bytes (1 << column): a 12-bit record field indexes it unchecked
   double cold_lo[SEG_COLD];
   double cold_hi[SEG_COLD];
   SegBucket bk[SEG_MAXQ];
@@ -152,14 +152,18 @@ seg_analyze_kernel(kvm_request_log log, const int64_t* __restrict__ run_offsets,
                    double cold_window, SegQueries qp, int nb, bool base_aligned,
                    uint8_t* __restrict__ flags, uint64_t* __restrict__ recs, kvm_log_stats* __restrict__ out_stats,
                    kvm_query_result* __restrict__ out_results, int64_t* __restrict__ out_hist,
-                   int32_t* __restrict__ out_status) {
+                   int32_t* __restrict__ out_status, unsigned int* __restrict__ ticket) {
   extern __shared__ __align__(16) unsigned char seg_raw[];
   SegSmem& S = *reinterpret_cast<SegSmem*>(seg_raw);
   uint32_t* sh = S.hist;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const double nan = __longlong_as_double(0x7ff8000000000000ll);
 
-  for (int64_t run = blockIdx.x; run < runs; run += gridDim.x) {
+  // runs are handed out by ticket (the first one per CTA by its index): a CTA that finishes early
+  // takes the next run instead of idling behind a static schedule
+  __shared__ unsigned int next_run;
+  for (int64_t run = blockIdx.x; run < runs;) {
+    if (tid == 0) next_run = gridDim.x + atomicAdd(ticket, 1u);
     const int64_t r0 = run_offsets[run], r1 = run_offsets[run + 1];
     unsigned long long tp = tid == 0 ? seg_now() : 0ull;
     auto phase = [&](int k) {   // after a __syncthreads
@@ -202,7 +206,7 @@ seg_analyze_kernel(kvm_request_log log, const int64_t* __restrict__ run_offsets,
     }
     for (int i = tid; i < NH * (BINS / 32); i += SEG_THREADS) (&S.flag20[0][0])[i] = 0;
     for (int i = tid; i < NC * (BINS / 32); i += SEG_THREADS) (&S.bmap[0][0])[i] = 0;
-    for (int i = tid; i < NC * (2 * BINS / 32); i += SEG_THREADS) (&S.anyhit[0][0])[i] = 0;
+    for (int i = tid; i < NC * 2 * BINS / 4; i += SEG_THREADS) reinterpret_cast<uint32_t*>(&S.hit8[0][0])[i] = 0;
     if (tid < SEG_MAXQ) S.cursor[tid] = 0;
     if (tid == 0) {
       S.nbuckets = 0;
@@ -469,6 +473,8 @@ seg_analyze_kernel(kvm_request_log log, const int64_t* __restrict__ run_offsets,
         out_stats[run] = S.stats;
       }
       __syncthreads();
+      run = next_run;
+      __syncthreads();
       continue;
     }
     // ---------------- P5 fine bins without an edge lie inside a single 20-bin: add them wholesale
@@ -485,10 +491,11 @@ seg_analyze_kernel(kvm_request_log log, const int64_t* __restrict__ run_offsets,
         atomicAdd(&S.cnt20[h][bin_of(lowkey, S.thr[h], nb)], c);
       }
     }
-    for (int t = tid; t < NC * (BINS / 32); t += SEG_THREADS) {
-      const int c = t / (BINS / 32), w = t % (BINS / 32);
+    for (int t = tid; t < NC * BINS; t += SEG_THREADS) {
+      const int c = t / BINS, d = t % BINS;
       const int h = col_hist(c);
-      S.anyhit[c][w] = S.bmap[c][w] | (h >= 0 ? S.flag20[h][w] : 0u);
+      const uint32_t w = S.bmap[c][d >> 5] | (h >= 0 ? S.flag20[h][d >> 5] : 0u);
+      S.hit8[c][d] = (uint8_t)(((w >> (d & 31)) & 1u) << c);
     }
     __syncthreads();   // the histograms are dead from here on: their space is the arena
     phase(2);
@@ -500,7 +507,7 @@ seg_analyze_kernel(kvm_request_log log, const int64_t* __restrict__ run_offsets,
 #pragma unroll
         for (int c = 0; c < NC; ++c) {
           const uint32_t d = (uint32_t)(r >> (12 * c)) & 0xFFFu;
-          if ((S.anyhit[c][d >> 5] >> (d & 31)) & 1u) seg_hit(S, log, i, c, d, fl, nb);
+          if (S.hit8[c][d]) seg_hit(S, log, i, c, d, fl, nb);
         }
       };
       if (base_aligned) {
@@ -548,15 +555,18 @@ seg_analyze_kernel(kvm_request_log log, const int64_t* __restrict__ run_offsets,
             ff[k] = *reinterpret_cast<const uint16_t*>(flags + a0 + (p << 1));
           }
         }
+        // one byte per (column, digit): bit c set when the row's value in column c is wanted
         uint64_t hm = 0;
 #pragma unroll
-        for (int k = 0; k < SEG_RK; ++k)
+        for (int k = 0; k < SEG_RK; ++k) {
+          uint32_t m0 = 0, m1 = 0;
 #pragma unroll
           for (int c = 0; c < NC; ++c) {
-            const uint32_t d0 = (uint32_t)(rr[k].x >> (12 * c)) & 0xFFFu, d1 = (uint32_t)(rr[k].y >> (12 * c)) & 0xFFFu;
-            hm |= (uint64_t)((S.anyhit[c][d0 >> 5] >> (d0 & 31)) & 1u) << (k * 2 * NC + c);
-            hm |= (uint64_t)((S.anyhit[c][d1 >> 5] >> (d1 & 31)) & 1u) << (k * 2 * NC + NC + c);
+            m0 |= S.hit8[c][(uint32_t)(rr[k].x >> (12 * c)) & 0xFFFu];
+            m1 |= S.hit8[c][(uint32_t)(rr[k].y >> (12 * c)) & 0xFFFu];
           }
+          hm |= (uint64_t)(m0 | (m1 << NC)) << (k * 2 * NC);
+        }
         const int nh = __popcll(hm);
         const int total = __reduce_add_sync(KVM_FULL, nh);
         if (total == 0) continue;
@@ -656,6 +666,8 @@ seg_analyze_kernel(kvm_request_log log, const int64_t* __restrict__ run_offsets,
     }
     __syncthreads();
     phase(4);
+    run = next_run;
+    __syncthreads();   // (next_run is rewritten at the top of the next run)
   }
 }
 
@@ -674,7 +686,8 @@ extern "C" int kvm_seg_phase_times(uint64_t* out5, int32_t reset) {
   return KVM_OK;
 }
 
-extern "C" size_t kvm_seg_analyze_scratch_bytes(int64_t n) { return sizeof(uint64_t) * (size_t)(n < 0 ? 0 : n + 2); }
+// 8 B/row digit records (+ 2 rows of slack) and one 16-byte slot for the run ticket
+extern "C" size_t kvm_seg_analyze_scratch_bytes(int64_t n) { return sizeof(uint64_t) * (size_t)(n < 0 ? 0 : n + 2) + 16; }
 
 extern "C" int kvm_seg_analyze(const kvm_request_log* log, const int64_t* run_offsets, int64_t runs,
                                const int64_t* cold_offsets, const double* cold_times,
@@ -706,9 +719,11 @@ extern "C" int kvm_seg_analyze(const kvm_request_log* log, const int64_t* run_of
                        al16(log->total_tokens) && (reinterpret_cast<uintptr_t>(flags) & 1u) == 0 && al16(scratch);
   int grid = 2 * kvm_num_sms();
   if ((int64_t)grid > runs) grid = (int)runs;
+  unsigned int* ticket = reinterpret_cast<unsigned int*>(reinterpret_cast<uint64_t*>(scratch) + (log->n + 2));
+  KVM_CUDA_CHECK(cudaMemsetAsync(ticket, 0, 16, (cudaStream_t)stream));
   seg_analyze_kernel<<<grid, SEG_THREADS, smem, (cudaStream_t)stream>>>(
       *log, run_offsets, runs, cold_offsets, cold_times, cold_window_s, qp, num_bins, aligned, flags,
-      reinterpret_cast<uint64_t*>(scratch), stats, results, hist_counts, run_status);
+      reinterpret_cast<uint64_t*>(scratch), stats, results, hist_counts, run_status, ticket);
   KVM_CUDA_CHECK(cudaGetLastError());
   return KVM_OK;
 }
