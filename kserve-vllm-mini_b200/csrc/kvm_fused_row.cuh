@@ -118,10 +118,9 @@ __device__ __forceinline__ void fused_sample_rows(const kvm_request_log& log, in
 }
 
 // Digit parameters of column c from the sample's hull (inv = complemented sampled minimum, 0:
-// the sample holds no member of the column).  The bins span the hull widened by an eighth of its
-// width on either side, so that what the sample missed still lands in a bin of its own; for a
-// column wide enough (shift >= 32) the base is rounded down to a multiple of 2^32, which makes a
-// digit a function of the key's HIGH word alone.  Returns the significant bits of the span.
+// the sample holds no member of the column).  For a column wide enough (shift >= 32) the base is
+// rounded down to a multiple of 2^32, which makes a digit a function of the key's HIGH word alone.
+// Returns the significant bits of the span.
 __device__ __forceinline__ int fused_cols_setup(FusedCols& S, int c, uint64_t inv, uint64_t mx) {
   int width;
   if (inv == 0ull) {   // no member of this column in the sample: coarse bins over all keys
@@ -131,13 +130,22 @@ __device__ __forceinline__ int fused_cols_setup(FusedCols& S, int c, uint64_t in
     S.kmin[c] = ~0ull;
     S.kmax[c] = 0ull;
   } else {
-    const uint64_t mn = ~inv, margin = (mx - mn) >> 3;
-    uint64_t lo = mn > margin ? mn - margin : 0ull;
-    const uint64_t hi = mx + margin < mx ? ~0ull : mx + margin;
-    if (bit_width64(hi - lo) >= BINS_LOG2 + 32) lo &= ~0xFFFFFFFFull;
-    const uint64_t range = hi - lo;
-    S.kbase[c] = lo;
+    // the bins span the smallest power of two that holds the hull; the hull sits in the middle of
+    // that span, so what the sample missed on either side still lands in a bin of its own
+    const uint64_t mn = ~inv, range = mx - mn;
     width = range ? bit_width64(range) : 1;
+    uint64_t lo = mn;
+    if (width >= BINS_LOG2 + 32) {
+      if (width < 64) {
+        const uint64_t span = 1ull << width, slack = span - 1ull - range;
+        const uint64_t back = slack >> 1;
+        lo = (mn > back ? mn - back : 0ull) & ~0xFFFFFFFFull;
+        if (mx - lo >= span) ++width;   // (no slack to speak of: the rounding of the base cost a bit)
+      } else {
+        lo = mn & ~0xFFFFFFFFull;
+      }
+    }
+    S.kbase[c] = lo;
     S.shift[c] = width > BINS_LOG2 ? width - BINS_LOG2 : 0;
     S.kmin[c] = mn;   // sampled values are members: the exact range starts from their hull
     S.kmax[c] = mx;

@@ -83,6 +83,7 @@ struct SegSmem {
   uint32_t arena_used;
   uint64_t hitq[SEG_WARPS][SEG_HITQ];          // P6: rows waiting for their value, per warp
   uint32_t hitq_n[SEG_WARPS];
+  uint32_t gsum[KVM_LOG_NSETS][BINS / 32];     // totals of every 32-bin group of every set
   kvm_log_stats stats;
 };
 
@@ -281,19 +282,17 @@ seg_analyze_kernel(kvm_request_log log, const int64_t* __restrict__ run_offsets,
     facc_warp_reduce(a, S.red[warp], lane);
     __syncthreads();
     phase(1);
-    // set counts = sums of the histograms
-    {
-      uint32_t setsum[KVM_LOG_NSETS];
-#pragma unroll
-      for (int s = 0; s < KVM_LOG_NSETS; ++s) {
-        setsum[s] = 0;
-        for (int b = tid; b < BINS; b += SEG_THREADS) setsum[s] += sh[s * BINS + b];
-      }
-#pragma unroll
-      for (int s = 0; s < KVM_LOG_NSETS; ++s) {
-        const uint32_t v = __reduce_add_sync(KVM_FULL, setsum[s]);
-        if (lane == 0) S.red[warp][S_CNT0 + s] = v;
-      }
+    // totals of every 32-bin group of every set (one warp reduction each); a set's count is the sum of
+    // its 64 group totals
+    for (int g = warp; g < KVM_LOG_NSETS * (BINS / 32); g += SEG_WARPS) {
+      const uint32_t v = __reduce_add_sync(KVM_FULL, sh[g * 32 + lane]);
+      if (lane == 0) (&S.gsum[0][0])[g] = v;
+    }
+    __syncthreads();
+    if (warp < KVM_LOG_NSETS) {
+      const uint32_t v = __reduce_add_sync(KVM_FULL, S.gsum[warp][lane] + S.gsum[warp][32 + lane]);
+      if (lane == 0)
+        for (int w = 0; w < SEG_WARPS; ++w) S.red[w][S_CNT0 + warp] = w == 0 ? v : 0u;
     }
     __syncthreads();
     if (tid < NMAX_END) {
@@ -390,9 +389,29 @@ seg_analyze_kernel(kvm_request_log log, const int64_t* __restrict__ run_offsets,
         }
         continue;
       }
-      int64_t running = 0;
-      bool found = false;
-      for (int base = 0; base < BINS && !found; base += 32) {
+      // two-level walk: 64 group totals (2 per lane) locate the 32-bin group, one scan finishes
+      int64_t g0 = 0, g1 = 0;
+      for (int b = 0; b < KVM_LOG_NSETS; ++b)
+        if ((mask >> b) & 1u) {
+          g0 += (int64_t)S.gsum[b][lane];
+          g1 += (int64_t)S.gsum[b][32 + lane];
+        }
+      int64_t i0 = g0, i1 = g1;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const int64_t o0 = __shfl_up_sync(KVM_FULL, i0, d), o1 = __shfl_up_sync(KVM_FULL, i1, d);
+        if (lane >= d) {
+          i0 += o0;
+          i1 += o1;
+        }
+      }
+      i1 += __shfl_sync(KVM_FULL, i0, 31);
+      const unsigned h0 = __ballot_sync(KVM_FULL, i0 > s.rank), h1 = __ballot_sync(KVM_FULL, i1 > s.rank);
+      bool found = (h0 | h1) != 0;
+      if (found) {
+        const int gl = h0 ? __ffs(h0) - 1 : __ffs(h1) - 1;
+        const int base = (h0 ? gl : 32 + gl) * 32;
+        const int64_t running = h0 ? __shfl_sync(KVM_FULL, i0 - g0, gl) : __shfl_sync(KVM_FULL, i1 - g1, gl);
         int64_t c = 0;
         for (int b = 0; b < KVM_LOG_NSETS; ++b)
           if ((mask >> b) & 1u) c += (int64_t)sh[b * BINS + base + lane];
@@ -403,6 +422,7 @@ seg_analyze_kernel(kvm_request_log log, const int64_t* __restrict__ run_offsets,
           if (lane >= d) incl += o;
         }
         const unsigned hit = __ballot_sync(KVM_FULL, running + incl > s.rank);
+        found = hit != 0;
         if (hit) {
           const int l = __ffs(hit) - 1;
           const int64_t excl = __shfl_sync(KVM_FULL, incl - c, l);
@@ -423,9 +443,7 @@ seg_analyze_kernel(kvm_request_log log, const int64_t* __restrict__ run_offsets,
             }
             S.q[qi] = s;
           }
-          found = true;
         }
-        running += __shfl_sync(KVM_FULL, incl, 31);
       }
       if (!found && lane == 0) {
         s.status = KVM_Q_OUT_OF_RANGE;
