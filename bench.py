@@ -15,6 +15,7 @@ Prints ONE JSON line (rank 0).  See DESIGN.md "Measurement" for how each field i
 """
 
 import argparse
+import collections
 import json
 import math
 import os
@@ -507,36 +508,39 @@ def run_ours(args):
     # while analysis k+1 is on the GPU (single-GPU path)
     pipe = None
     if world == 1:
-        pipe = (engine.LogAnalyzer(device, stream=torch.cuda.Stream(device)),
-                engine.LogAnalyzer(device, stream=torch.cuda.Stream(device)))
+        # (three: while the host collects analysis k and submits k+3, k+1 and k+2 are both on the GPU -
+        # with two, the GPU holds a single analysis for the ~100 us the host needs per step)
+        pipe = tuple(engine.LogAnalyzer(device, stream=torch.cuda.Stream(device)) for _ in range(max(2, args.pipeline_depth)))
     elif not args.no_pipeline:
         # N>1: only with the peer-memory exchange (no collective library call on the data path, so
         # two analyses can be in flight); every rank takes the same branch
         analyzer.analyze(engine.DeviceLog.from_tensors(resident), cold)
         if analyzer.exchange != "nccl":
             pipe = tuple(dist_api.ShardedAnalyzer(device, exchange="peer", stream=torch.cuda.Stream(device))
-                         for _ in range(2))
+                         for _ in range(max(2, args.pipeline_depth)))
     pipelined = pipe is not None
     if args.refine_min_keys is not None:
         for an in (analyzer,) + tuple(pipe or ()):
             an.refine_min_keys = args.refine_min_keys
 
-    def run_pipelined(dlog, k, before_submit=None):
+    def run_pipelined(dlog, k, before_submit=None, depth=None):
         """`dlog`: one DeviceLog, or one per analyzer of the pair (the e2e leg: each analyzer has
         its own staging columns; before_submit(slot) fills them)."""
-        pair = pipe
-        dlogs = dlog if isinstance(dlog, (tuple, list)) else (dlog, dlog)
-        pending, out, launches = None, None, 0
+        depth = len(pipe) if depth is None else min(depth, len(pipe))
+        pair = pipe[:depth]
+        dlogs = dlog if isinstance(dlog, (tuple, list)) else (dlog,) * depth
+        pending, out, launches = collections.deque(), None, 0
         for it in range(k):
-            an = pair[it & 1]
+            slot = it % depth          # its previous analysis (it - depth) has been collected below
+            an = pair[slot]
             if before_submit is not None:
-                before_submit(it & 1)
-            nxt = an.analyze_async(dlogs[it & 1], cold, use_graph=graphs)
+                before_submit(slot)
+            pending.append(an.analyze_async(dlogs[slot], cold, use_graph=graphs))
             launches += an.launches
-            if pending is not None:
-                out = finish(pending())
-            pending = nxt
-        out = finish(pending())
+            if len(pending) == depth:
+                out = finish(pending.popleft()())
+        while pending:
+            out = finish(pending.popleft()())
         for an in pair:   # join the side streams before the caller records its end event
             torch.cuda.current_stream(device).wait_stream(an.stream)
         return out, launches
@@ -551,6 +555,7 @@ def run_ours(args):
     # refilled only after the analysis that used it has been collected (run_pipelined's order).
     staging2 = dlog_staging2 = None
     if pinned is not None and pipelined:
+        # (the e2e leg is PCIe-bound: two analyses in flight are enough, more staging copies only add traffic)
         staging2 = (staging, {k: torch.empty_like(v) for k, v in resident.items()})
         dlog_staging2 = tuple(engine.DeviceLog.from_tensors(s) for s in staging2)
 
@@ -567,7 +572,7 @@ def run_ours(args):
     for _ in range(args.warmup):
         step(dlog_resident, graphs)
     if pipelined:
-        run_pipelined(dlog_resident, 2 * args.warmup)
+        run_pipelined(dlog_resident, max(2 * args.warmup, 2 * len(pipe)))   # every analyzer captures and replays its graph once
     barrier()
 
     # ---- timed region 1: inputs resident in HBM
@@ -607,14 +612,14 @@ def run_ours(args):
     e2e_steps = max(3, min(args.steps, 20))
     if pinned is not None:
         if dlog_staging2 is not None:
-            run_pipelined(dlog_staging2, 2, e2e_fill)
+            run_pipelined(dlog_staging2, 4, e2e_fill, depth=2)
         else:
             e2e_step()
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         if dlog_staging2 is not None:
-            (core, cost, raw), _ = run_pipelined(dlog_staging2, e2e_steps, e2e_fill)
+            (core, cost, raw), _ = run_pipelined(dlog_staging2, e2e_steps, e2e_fill, depth=2)
         else:
             for _ in range(e2e_steps):
                 core, cost, raw = e2e_step()
@@ -684,13 +689,14 @@ def run_ours(args):
                          "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": kernels[dom]["algorithmic_bytes"]},
             "kernels": kernels,
-            "launch_mode": ("timed region: CUDA-graph replay of the 7-kernel sequence, two analyses in flight on "
-                            "two streams (host post-processing of step k and the single-CTA kernels of one "
-                            "analysis overlap the streaming passes of the other); per-kernel durations from "
+            "launch_mode": (f"timed region: CUDA-graph replay of the kernel sequence, {len(pipe) if pipe else 1} analyses in flight on "
+                            "their own streams (host post-processing of step k and the few-CTA kernels of one "
+                            "analysis overlap the streaming passes of the others: the streaming kernels leave "
+                            "kvm_tail_slots CTAs out of their grids); per-kernel durations from "
                             "the same K steps launched eagerly on one stream with CUDA events"
                             if pipelined and world == 1 else
                             ("timed region: CUDA-graph replay (kernels + exchanges), " +
-                             ("two analyses in flight on two streams, " if pipelined else "one analysis at a time, ") +
+                             (f"{len(pipe)} analyses in flight on their own streams, " if pipelined else "one analysis at a time, ") +
                              "one host sync per step; per-kernel durations from the same K steps launched eagerly "
                              "with CUDA events")),
             "exchange": (None if world == 1 else
@@ -738,6 +744,7 @@ def main():
     ap.add_argument("--no-parity", action="store_true", help="skip the oracle comparison of the timed log")
     ap.add_argument("--no-cfg5", action="store_true", help="N>1: skip the 1.25e8-rows-per-GPU block")
     ap.add_argument("--cfg5-rows", type=int, default=125_000_000, help="rows per GPU of the cfg5 block")
+    ap.add_argument("--pipeline-depth", type=int, default=4, help="analyses kept in flight on their own streams (>= 2)")
     ap.add_argument("--no-sweep", action="store_true", help="skip the configs[2] (sweep roll-up) block")
     ap.add_argument("--sweep-runs", type=int, default=512, help="runs per GPU of the sweep block (250k rows each)")
     ap.add_argument("--no-percentile-path", action="store_true",

@@ -552,6 +552,12 @@ int kvm_seg_analyze(const kvm_request_log* log_host, const int64_t* run_offsets,
                     void* scratch, size_t scratch_bytes, kvm_log_stats* stats,
                     kvm_query_result* results, int64_t* hist_counts, int32_t* run_status, void* stream);
 
+/* The machine-filling streaming kernels (one-pass scan, compact) leave `slots` CTAs out of their
+ * 2-per-SM grid, so that many SMs keep half their registers and shared memory free for the few-CTA
+ * kernels (plan, resolve, finish) of another analysis in flight on another stream.  Default 16
+ * (environment KVM_TAIL_SLOTS); 0 = full grids.  Process-wide; call before capturing graphs. */
+int kvm_set_tail_slots(int32_t slots);
+
 /* Debug aid: microseconds since the first CTA entered the last one-pass kernel that used this scan
  * workspace - [0] last CTA set up (sample + parameters), [1] last CTA done streaming, [2] last CTA
  * flushed its histograms, [3] statistics written.  Synchronises (one small copy). */

@@ -192,6 +192,7 @@ def _declare(lib: C.CDLL) -> None:
         "kvm_column_histogram": (C.c_int, [vp, i64, f64, f64, i32, vp, vp, sz, vp]),
         "kvm_log_series": (C.c_int, [P(RequestLogC), vp, vp, f64, i64, vp, vp, vp]),
         "kvm_log_fused_phase_us": (C.c_int, [vp, vp]),
+        "kvm_set_tail_slots": (C.c_int, [i32]),
         "kvm_seg_analyze_scratch_bytes": (sz, [i64]),
         "kvm_seg_phase_times": (C.c_int, [vp, i32]),
         "kvm_seg_analyze": (C.c_int, [P(RequestLogC), vp, i64, vp, vp, f64, P(QueryC), i32, i32, vp, vp, sz, vp, vp, vp, vp, vp]),

@@ -1,5 +1,6 @@
 // kvm_abi.cu - error reporting and device queries of the C ABI.
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "kvm_common.cuh"
@@ -25,6 +26,22 @@ int kvm_num_sms() {
     cached_dev = dev;
   }
   return cached;
+}
+
+// CTAs the streaming kernels leave out of a machine-filling grid (kvm_stream_grid); settable for
+// experiments: KVM_TAIL_SLOTS=0 restores full grids.
+static int g_tail_slots = -1;
+int kvm_tail_slots() {
+  if (g_tail_slots < 0) {
+    const char* e = getenv("KVM_TAIL_SLOTS");
+    int v = e ? atoi(e) : 16;
+    g_tail_slots = v < 0 ? 0 : v;
+  }
+  return g_tail_slots;
+}
+extern "C" int kvm_set_tail_slots(int32_t slots) {
+  g_tail_slots = slots < 0 ? 0 : slots;
+  return KVM_OK;
 }
 
 extern "C" const char* kvm_last_error(void) { return g_err; }

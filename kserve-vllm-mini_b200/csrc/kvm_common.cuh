@@ -231,3 +231,14 @@ static inline int kvm_grid_for(int64_t items, int items_per_cta, int ctas_per_sm
   if (want < 1) want = 1;
   return (int)(want < cap ? want : cap);
 }
+// Grid of a streaming kernel that fills the machine with two CTAs per SM, minus `kvm_tail_slots()`
+// CTAs: that many SMs then hold ONE of its CTAs and keep half their registers and shared memory
+// free, which is where the few-CTA kernels of ANOTHER analysis in flight (plan, resolve, finish: 512
+// threads, 64 registers) run at the same time instead of waiting for the whole grid to drain.
+int kvm_tail_slots();
+static inline int kvm_stream_grid(int64_t items, int items_per_cta) {
+  const int full = 2 * kvm_num_sms();
+  int g = kvm_grid_for(items, items_per_cta, 2);
+  if (g == full && full - kvm_tail_slots() >= full / 2) g = full - kvm_tail_slots();
+  return g;
+}

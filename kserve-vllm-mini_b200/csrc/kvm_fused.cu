@@ -531,7 +531,7 @@ static int fused_pass_impl(const kvm_request_log* log, const double* cold_times,
         sa.series, series_words, sa.dropped);
   }
   const size_t smem = sizeof(uint32_t) * KVM_LOG_NSETS * BINS + sizeof(FusedSmem);
-  int grid = kvm_grid_for(log->n, FU_THREADS * 2 * 4, 2);
+  int grid = kvm_stream_grid(log->n, FU_THREADS * 2 * 4);
   if (grid > FU_MAX_GRID) grid = FU_MAX_GRID;
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3((unsigned)grid);

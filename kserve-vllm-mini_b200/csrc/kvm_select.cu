@@ -39,7 +39,7 @@ namespace {
 // ------------------------------------------------------------------ plan
 constexpr int PLAN_THREADS = 512;
 
-__global__ void __launch_bounds__(PLAN_THREADS)
+__global__ void __launch_bounds__(PLAN_THREADS, 2)
 select_plan_kernel(SelWs* ws, const kvm_set_info* info_in, QueryPack qp, kvm_hist_spec hs,
                    int64_t arena_capacity, int refine_rounds, int64_t refine_min, int preset) {
   __shared__ kvm_set_info info;
@@ -433,7 +433,7 @@ column_hist_kernel(const double* __restrict__ values, int64_t n, int mode,
 }
 
 // ------------------------------------------------------------------ resolve
-constexpr int RES_THREADS = 1024;
+constexpr int RES_THREADS = 512;   // (512 threads x 64 registers: fits beside ONE CTA of a streaming kernel, kvm_stream_grid)
 
 // The global histograms are staged in shared memory; one warp per query then walks the
 // (summed) histogram of its sets to the bin holding the rank.
@@ -1462,18 +1462,18 @@ column_compact_kernel(const double* __restrict__ values, int64_t n, int mode,
 }
 
 // ------------------------------------------------------------------ finish
-constexpr int FIN_THREADS = 1024;
+constexpr int FIN_THREADS = 512;
 constexpr int FIN_BITS = 11;
 constexpr int FIN_BINS = 1 << FIN_BITS;
 constexpr int FIN_SMALL = 128;   // candidates ranked by counting once this few remain (counting is quadratic)
 constexpr int FIN_SURV = 2048;   // candidates gathered into a list of their own once this few remain
 constexpr int HIST_CTAS = 16;    // extra CTAs that assemble the value histograms
-constexpr int FIN_CACHE = 24576;  // bucket keys kept in shared memory (192 KB) by the finish
+constexpr int FIN_CACHE = 14336;  // bucket keys kept in shared memory (112 KB) by the finish: fits beside one CTA of the one-pass kernel
 
 // CTAs 0..MAXQ-1: one query each - radix select inside the query's bucket, FIN_BITS per pass,
 // switching to rank-by-counting in shared memory once <= FIN_SMALL candidates remain.
 // CTAs MAXQ..: assemble the value histograms (edge counters + fine bins without an edge).
-__global__ void __launch_bounds__(FIN_THREADS, 1)
+__global__ void __launch_bounds__(FIN_THREADS, 2)
 select_finish_kernel(SelWs* ws, SrcPack src, const int64_t* __restrict__ src_counts,
                      kvm_query_result* __restrict__ results, int64_t* __restrict__ hist_out) {
   __shared__ uint32_t hist[FIN_BINS];
@@ -1881,7 +1881,7 @@ template <int PHASE>
 int launch_log_rec(const kvm_request_log* log, const uint8_t* flags, const uint64_t* digit_records,
                    void* workspace, cudaStream_t st) {
   const size_t smem = ((sizeof(CompactSmem) + 15) / 16) * 16 + sizeof(RecQueue);
-  const int grid = kvm_grid_for(log->n, SEL_THREADS * 2 * 8, 2);
+  const int grid = kvm_stream_grid(log->n, SEL_THREADS * 2 * 8);
   int rc;
   if (aligned16(digit_records) && (reinterpret_cast<uintptr_t>(flags) & 1u) == 0) {
     if ((rc = ensure_smem((const void*)log_rec_kernel<2, PHASE>, smem))) return rc;
