@@ -744,7 +744,7 @@ def main():
     ap.add_argument("--no-parity", action="store_true", help="skip the oracle comparison of the timed log")
     ap.add_argument("--no-cfg5", action="store_true", help="N>1: skip the 1.25e8-rows-per-GPU block")
     ap.add_argument("--cfg5-rows", type=int, default=125_000_000, help="rows per GPU of the cfg5 block")
-    ap.add_argument("--pipeline-depth", type=int, default=4, help="analyses kept in flight on their own streams (>= 2)")
+    ap.add_argument("--pipeline-depth", type=int, default=6, help="analyses kept in flight on their own streams (>= 2)")
     ap.add_argument("--no-sweep", action="store_true", help="skip the configs[2] (sweep roll-up) block")
     ap.add_argument("--sweep-runs", type=int, default=512, help="runs per GPU of the sweep block (250k rows each)")
     ap.add_argument("--no-percentile-path", action="store_true",
