@@ -733,6 +733,10 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+def default_depth(world):
+    return 6 if world <= 2 else 3
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -744,7 +748,10 @@ def main():
     ap.add_argument("--no-parity", action="store_true", help="skip the oracle comparison of the timed log")
     ap.add_argument("--no-cfg5", action="store_true", help="N>1: skip the 1.25e8-rows-per-GPU block")
     ap.add_argument("--cfg5-rows", type=int, default=125_000_000, help="rows per GPU of the cfg5 block")
-    ap.add_argument("--pipeline-depth", type=int, default=6, help="analyses kept in flight on their own streams (>= 2)")
+    ap.add_argument("--pipeline-depth", type=int, default=0,
+                    help="analyses kept in flight on their own streams (>= 2); 0 = 6 on one or two GPUs, 3 beyond "
+                         "(measured: with more ranks the spinning barrier kernels of many analyses in flight "
+                         "get in each other's way)")
     ap.add_argument("--no-sweep", action="store_true", help="skip the configs[2] (sweep roll-up) block")
     ap.add_argument("--sweep-runs", type=int, default=512, help="runs per GPU of the sweep block (250k rows each)")
     ap.add_argument("--no-percentile-path", action="store_true",
@@ -761,6 +768,8 @@ def main():
                     help="N>1: how the ranks exchange intermediate results")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.pipeline_depth <= 0:
+        args.pipeline_depth = default_depth(int(os.environ.get("WORLD_SIZE", "1")))
     if args.impl == "reference":
         run_reference(args)
     else:
