@@ -294,6 +294,51 @@ def percentile_path_block(device, peak, sizes=(10_000_000, 100_000_000), steps=5
                 entry[name] = {"ms": ms, "gbs": 16.0 * n / ms / 1e6, "frac": 16.0 * n / ms / 1e6 / peak,
                                "equal_to_sorted_ranks": [float(x) for x in got["value"]] == want
                                and all(int(x) == m for x in got["n"])}
+        # the same call with several in flight (own workspace, result block and stream each): what
+        # a monitor pays per column when it asks for the quantiles of several columns / logs at
+        # once - the single-CTA phases of one call overlap the streaming pass of the others
+        if "ms" in entry.get("sampled", {}):
+            depth, rounds = int(os.environ.get("KVM_PP_DEPTH", "8")), max(8, steps // 2)
+            lanes = []
+            for _ in range(depth):
+                w = torch.empty_like(ws_s)
+                r = torch.zeros_like(res)
+                sst = torch.cuda.Stream(device)
+                with torch.cuda.stream(sst):
+                    def call(w=w, r=r):
+                        N.check(lib.kvm_column_select_sampled(lat.data_ptr(), n, N.MEMBER_STATUS, st.data_ptr(), arr, len(q),
+                                                              r.data_ptr(), w.data_ptr(), w.numel(),
+                                                              torch.cuda.current_stream(device).cuda_stream))
+                    for _ in range(2):
+                        call()
+                    sst.synchronize()
+                    g = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(g, stream=sst):
+                        call()
+                    g.replay()
+                    sst.synchronize()
+                lanes.append((sst, g, w, r))
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize(device)
+            e0.record(stream)
+            for sst, _, _, _ in lanes:
+                sst.wait_event(e0)
+            for _ in range(rounds):
+                for sst, g, _, _ in lanes:
+                    with torch.cuda.stream(sst):
+                        g.replay()
+            for sst, _, _, _ in lanes:
+                stream.wait_stream(sst)
+            e1.record(stream)
+            stream.synchronize()
+            ms = e0.elapsed_time(e1) / (rounds * depth)
+            ok = True
+            for _, _, w, r in lanes:
+                got = np.frombuffer(r.cpu().numpy().tobytes(), dtype=engine.RESULT_DTYPE, count=len(q))
+                ok = ok and int(w[0:4].view(torch.int32).item()) == 0 and [float(x) for x in got["value"]] == want
+            entry["sampled_in_flight"] = {"ms_per_call": ms, "gbs": 16.0 * n / ms / 1e6, "frac": 16.0 * n / ms / 1e6 / peak,
+                                            "calls_in_flight": depth, "equal_to_sorted_ranks": ok}
+            del lanes
         out["rows_%g" % n] = entry
         del lat, st, ws_s, ws_g, res
         torch.cuda.empty_cache()

@@ -719,7 +719,8 @@ qd_rank_kernel(QdWs* ws, const uint64_t* __restrict__ lists, kvm_query_result* _
 
 // two resident CTAs per SM, each with a contiguous share of the rows
 int qd_grid(int64_t n, int rows_per_thread_iter) {
-  return kvm_grid_for(n, QD_THREADS * rows_per_thread_iter, 2);
+  // (a machine-filling grid leaves kvm_tail_slots() CTAs out: room for the rank kernel of another call in flight)
+  return kvm_stream_grid(n, QD_THREADS * rows_per_thread_iter);
 }
 long long qd_list_cap(int64_t n) {
   const long long c = (long long)(n / 64) + 16384;   // a bin holds ~n/1500 of smooth data
