@@ -619,3 +619,33 @@ def test_fused_pass_graph_replay_and_repeat():
     for _ in range(4):
         again = report.core_results(an.analyze(dlog, [t0 + 5.0], use_graph=True), 1)
         assert an.last_path == "fused" and diff_keys(again, first) == []
+
+
+def test_tail_slots_change_grids_not_results():
+    """kvm_set_tail_slots: the streaming kernels leave that many CTAs out of their machine-filling
+    grids (room for the few-CTA kernels of another analysis in flight).  A log large enough for a
+    full grid gives bit-identical results with 0, 16 and 40 slots - and with three analyses in
+    flight on their own streams."""
+    import torch
+    from kvmini_b200 import engine, report
+    from kvmini_b200 import _native as N
+    lib = N.lib()
+    cols = _random_log(3_000_001, 9)
+    dev = {k: torch.from_numpy(v).cuda() for k, v in cols.items()}
+    dlog = engine.DeviceLog.from_tensors(dev)
+    t0 = float(cols["start_ms"].min()) / 1000.0
+    try:
+        outs = []
+        for slots in (0, 16, 40):
+            N.check(lib.kvm_set_tail_slots(slots), "kvm_set_tail_slots")
+            an = engine.LogAnalyzer()
+            outs.append(report.core_results(an.analyze(dlog, [t0 + 5.0]), 1))
+            assert an.last_path == "fused"
+        assert diff_keys(outs[1], outs[0]) == [] and diff_keys(outs[2], outs[0]) == []
+        N.check(lib.kvm_set_tail_slots(16), "kvm_set_tail_slots")
+        ring = [engine.LogAnalyzer(stream=torch.cuda.Stream()) for _ in range(3)]
+        pending = [an.analyze_async(dlog, [t0 + 5.0], use_graph=False) for an in ring]
+        for p in pending:
+            assert diff_keys(report.core_results(p(), 1), outs[0]) == []
+    finally:
+        lib.kvm_set_tail_slots(16)
